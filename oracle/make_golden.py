@@ -1,0 +1,303 @@
+"""Pin the oracle against the reference's own Python code and write tests/golden/*.npz.
+
+TEST INFRASTRUCTURE ONLY.  Runs only in the build container (needs /root/reference):
+
+    python -m oracle.make_golden
+
+For every stage of the hot path it (1) runs the *reference* function, imported in place by
+oracle/ref_import.py, on seeded inputs, (2) runs the numpy restatement in oracle/reid_oracle.py
+on the same inputs, (3) asserts agreement (bit-exact for integer/index work, tight fp
+tolerances otherwise) and (4) stores inputs + reference outputs as a small fixture.  The
+fixtures travel to the GPU box; /root/reference does not.
+"""
+from __future__ import annotations
+
+import os
+import sys
+import types
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+from oracle import ref_import, reid_oracle as O  # noqa: E402
+
+GOLD = os.path.join(ROOT, "tests", "golden")
+
+
+def _save(name, **arrs):
+    os.makedirs(GOLD, exist_ok=True)
+    path = os.path.join(GOLD, name + ".npz")
+    np.savez_compressed(path, **arrs)
+    print("  wrote %-28s %7.1f KB" % (name + ".npz", os.path.getsize(path) / 1024))
+
+
+def _unit(x):
+    return (x / np.linalg.norm(x, axis=1, keepdims=True)).astype(np.float32)
+
+
+# ---------------------------------------------------------------- B1/B2 distances
+def gold_dist():
+    U = ref_import.load_file("ref_losses_utils", "reid/losses/utils.py")
+    rng = np.random.default_rng(0)
+    x = rng.standard_normal((37, 48)).astype(np.float32)
+    y = rng.standard_normal((53, 48)).astype(np.float32)
+    y[5] = x[3]  # a duplicate row: exercises the clamp(1e-12) branch
+    e = U.euclidean_dist(torch.from_numpy(x), torch.from_numpy(y)).numpy()
+    c = U.cosine_dist(torch.from_numpy(x), torch.from_numpy(y)).numpy()
+    np.testing.assert_allclose(O.euclidean_dist(x, y), e, rtol=2e-5, atol=1e-2)  # the duplicate pair: sqrt of fp32 cancellation noise
+    mask = e > 1e-2
+    np.testing.assert_allclose(O.euclidean_dist(x, y)[mask], e[mask], rtol=1e-5)
+    np.testing.assert_allclose(O.cosine_dist(x, y), c, rtol=0, atol=2e-7)
+    _save("dist", x=x, y=y, euclid=e, cosine=c)
+
+
+# ---------------------------------------------------------------- B3-B6 evaluation
+def gold_eval():
+    E = ref_import.load_file("ref_evaluate", "reid/evaluate.py")
+    sys.path.insert(0, os.path.join(ROOT, "real-time-reid-tracking_b200"))
+    import synth  # noqa
+
+    d = synth.market_like(Q=60, G=500, D=32, n_ids=40, seed=3, orphan_frac=0.05)
+    t = {k: torch.from_numpy(v) for k, v in d.items()}
+    import contextlib, io
+    with contextlib.redirect_stdout(io.StringIO()):
+        cmc, ap = E.evaluate_all(t["qf"], t["ql"], t["qc"], t["gf"], t["gl"], t["gc"])
+    cmc = cmc.numpy()
+    ocmc, oap = O.evaluate_all(d["qf"], d["ql"], d["qc"], d["gf"], d["gl"], d["gc"])
+    assert np.array_equal(ocmc, cmc), "CMC mismatch"
+    assert abs(oap - ap) < 1e-12, (oap, ap)
+    # per-query AP and first-hit rank (reference evaluate())
+    aps, first = [], []
+    for i in range(len(d["ql"])):
+        a, c = E.evaluate(t["qf"][i], t["ql"][i], t["qc"][i], t["gf"], t["gl"], t["gc"])
+        c = c.numpy()
+        aps.append(float(a))
+        first.append(-1 if c[0] == -1 else int(np.argmax(c)))
+    _save("eval", **d, cmc=cmc, ap=np.float64(ap), ap_per_query=np.array(aps), first_hit=np.array(first, np.int32))
+
+
+# ---------------------------------------------------------------- D1-D7 Jaccard re-ranking
+def gold_jaccard():
+    F = ref_import.load_file("ref_faiss_utils", "reid/faiss_utils.py")
+    rng = np.random.default_rng(5)
+    N, D = 260, 32
+    cent = rng.standard_normal((30, D)).astype(np.float32)
+    feats = _unit(cent[rng.integers(0, 30, N)] + 0.5 * rng.standard_normal((N, D)).astype(np.float32))
+    out = {}
+    for tag, k1, k2, f16 in (("k20_6", 20, 6, False), ("k10_1", 10, 1, False), ("k20_6_f16", 20, 6, True)):
+        J = F.compute_jaccard_distance(torch.from_numpy(feats), k1=k1, k2=k2, print_flag=False,
+                                       search_option=3, use_float16=f16)
+        Jo = O.compute_jaccard_distance(feats, k1, k2, f16)
+        assert J.dtype == Jo.dtype and J.shape == Jo.shape
+        np.testing.assert_allclose(Jo.astype(np.float32), J.astype(np.float32), rtol=0, atol=2e-3 if f16 else 2e-6)
+        out["J_" + tag] = J
+    _, rank = O.knn_l2(feats, feats, 20)
+    # k_reciprocal_neigh on a few rows
+    for i in (0, 17, 255):
+        assert np.array_equal(F.k_reciprocal_neigh(rank, i, 20), O.k_reciprocal_neigh(rank, i, 20))
+        assert np.array_equal(F.k_reciprocal_neigh(rank, i, 10), O.k_reciprocal_neigh(rank, i, 10))
+    # sparse rows restatement agrees with the dense reference V path (through J): covered above.
+    _save("jaccard", feats=feats, initial_rank=rank.astype(np.int32), **out)
+
+
+# ---------------------------------------------------------------- A1-A3 crop / resize / normalise
+def gold_preprocess():
+    FE = None
+    # feature_extractor.py imports a backbone that does not exist: stub the module tree
+    for name in ("reid", "reid.backbones", "reid.backbones.SERes18_IBN"):
+        sys.modules.setdefault(name, types.ModuleType(name))
+    sys.modules["reid.backbones.SERes18_IBN"].SEDense18_IBN = object
+    FE = ref_import.load_file("ref_feature_extractor", "modification_deepsort/feature_extractor.py")
+    for name in ("reid.backbones.SERes18_IBN", "reid.backbones", "reid"):
+        sys.modules.pop(name, None)
+    ex = object.__new__(FE.Extractor)
+    import torchvision.transforms as transforms
+    ex.size = (128, 256)
+    ex.norm = transforms.Compose([transforms.ToTensor(), transforms.Normalize([0.5, 0.5, 0.5], [0.5, 0.5, 0.5])])
+
+    rng = np.random.default_rng(7)
+    H, W = 270, 480
+    img = rng.integers(0, 256, (H, W, 3), dtype=np.uint8)
+    # smooth part so that interpolation is exercised on structured data too
+    yy, xx = np.mgrid[0:H, 0:W]
+    img[:, : W // 2, 0] = ((np.sin(xx[:, : W // 2] / 9.0) * 0.5 + 0.5) * 255).astype(np.uint8)
+    # centre-xywh boxes: upscale, downscale, clamped at borders, 1-pixel-wide, identity size
+    boxes_xywh = np.array([[100.3, 120.7, 40.2, 90.9], [240.0, 135.0, 300.0, 260.0], [5.0, 8.0, 30.0, 40.0],
+                           [470.0, 260.0, 40.0, 60.0], [200.5, 100.5, 128.0, 256.0], [300.0, 50.0, 1.2, 37.0],
+                           [64.0, 128.0, 128.5, 256.5]], np.float32)
+
+    class _S:  # StrongSORT._xywh_to_xyxy needs width/height attributes only
+        pass
+    SS = ref_import.load_file_pkg("boxmot.trackers.strongsort.strong_sort")
+    s = _S()
+    s.width, s.height = W, H
+    xyxy = np.array([SS.StrongSORT._xywh_to_xyxy(s, b) for b in boxes_xywh], np.int32)
+    oxyxy = np.array([O.xywh_to_xyxy(b, W, H) for b in boxes_xywh], np.int32)
+    assert np.array_equal(xyxy, oxyxy)
+    crops = [img[y1:y2, x1:x2] for x1, y1, x2, y2 in xyxy]
+    ref_cv = ex._preprocess(crops).numpy()
+    ocv = O.preprocess_deepsort(crops)
+    err = np.abs(ocv - ref_cv).max()
+    assert err <= 4.8e-7, err  # 1 ulp of the [0,1] image scaled by 1/std=2
+    # boxmot PIL path
+    RM = ref_import.load_file_pkg("boxmot.appearance.reid_multibackend")
+    import torchvision.transforms as T
+    rm = object.__new__(RM.ReIDDetectMultiBackend)
+    torch.nn.Module.__init__(rm)
+    rm.device = torch.device("cpu")
+    rm.preprocess = T.Compose([T.Resize((256, 128)), T.ToTensor(),
+                               T.Normalize(mean=[0.485, 0.456, 0.406], std=[0.229, 0.224, 0.225])])
+    rm.to_pil = T.ToPILImage()
+    ref_pil = rm._preprocess(crops).numpy()
+    opil = O.preprocess_boxmot(crops)
+    err2 = np.abs(opil - ref_pil).max()
+    assert err2 <= 1e-6, err2
+    # the uint8 resample must be bit-exact
+    from PIL import Image
+    for c in crops:
+        want = np.asarray(Image.fromarray(c).resize((128, 256), Image.BILINEAR))
+        assert np.array_equal(O.resize_pil_bilinear_u8(c, 256, 128), want)
+    pil_u8 = np.stack([np.asarray(Image.fromarray(c).resize((128, 256), Image.BILINEAR)) for c in crops])
+    # the PIL path is stored as its bit-exact uint8 resample plus the normalised float of crop 0
+    _save("preprocess", img=img, boxes_xywh=boxes_xywh, xyxy=xyxy,
+          cv_full_idx=np.array([0, 1, 5], np.int32), cv_full=ref_cv[[0, 1, 5]].astype(np.float32),
+          cv_sub=ref_cv[:, :, ::3, ::3].astype(np.float32), pil_u8=pil_u8, pil0=ref_pil[0].astype(np.float32))
+
+
+# ---------------------------------------------------------------- E  association costs
+def _mk_tracker(seed=11, frames=9, M=9, D=24, max_dist=0.2, max_iou_dist=0.7):
+    """Run the reference StrongSORT Tracker on a synthetic sequence and record, per frame, the
+    state that feeds _match() and what _match() returned."""
+    TR = ref_import.load_file_pkg("boxmot.trackers.strongsort.sort.tracker")
+    DET = ref_import.load_file_pkg("boxmot.trackers.strongsort.sort.detection")
+    MT = ref_import.load_file_pkg("boxmot.utils.matching")
+    rng = np.random.default_rng(seed)
+    metric = MT.NearestNeighborDistanceMetric("cosine", max_dist, 5)
+    trk = TR.Tracker(metric, max_iou_dist=max_iou_dist, max_age=4, n_init=2, mc_lambda=0.995, ema_alpha=0.9)
+    ids = rng.standard_normal((M, D)).astype(np.float32)
+    pos = np.stack([rng.uniform(100, 1700, M), rng.uniform(100, 900, M)], 1)
+    hh = rng.uniform(80, 300, M)
+    frames_out = []
+    for f in range(frames):
+        pos += rng.normal(0, 4, pos.shape)
+        present = rng.random(M) > 0.2
+        if f == 5:
+            pos[0] += 400  # a jump: Mahalanobis gate must reject it
+        dets = []
+        for m in np.where(present)[0]:
+            h = hh[m] * rng.uniform(0.97, 1.03)
+            w = 0.4 * h
+            tlwh = np.array([pos[m, 0] - w / 2, pos[m, 1] - h / 2, w, h], np.float32)
+            feat = ids[m] + 0.25 * rng.standard_normal(D).astype(np.float32)
+            dets.append(DET.Detection(tlwh, 0.5 + 0.4 * rng.random(), torch.from_numpy(feat.copy())))
+        # two clutter detections
+        for _ in range(2):
+            h = rng.uniform(80, 300)
+            tlwh = np.array([rng.uniform(0, 1800), rng.uniform(0, 900), 0.4 * h, h], np.float32)
+            dets.append(DET.Detection(tlwh, 0.6, torch.from_numpy(rng.standard_normal(D).astype(np.float32))))
+        trk.predict()
+        rec = dict(
+            det_tlwh=np.stack([d.tlwh for d in dets]).astype(np.float32),
+            det_feat=np.stack([d.feature for d in dets]).astype(np.float32),
+            trk_id=np.array([t.track_id for t in trk.tracks], np.int64),
+            trk_confirmed=np.array([t.is_confirmed() for t in trk.tracks], np.bool_),
+            trk_tsu=np.array([t.time_since_update for t in trk.tracks], np.int32),
+            trk_mean=np.array([t.mean for t in trk.tracks], np.float64).reshape(-1, 8),
+            trk_SI=np.array([t.kf.SI for t in trk.tracks], np.float64).reshape(-1, 4, 4),
+        )
+        samples = {int(k): np.stack(v).astype(np.float32) for k, v in metric.samples.items()}
+        m_, ut, ud = trk._match(dets)
+        rec["matches"] = np.array(sorted(m_), np.int64).reshape(-1, 2)
+        rec["unmatched_tracks"] = np.array(sorted(ut), np.int64)
+        rec["unmatched_dets"] = np.array(sorted(ud), np.int64)
+        # cost matrices of both stages on the *full* track/detection sets (what the fused kernel emits)
+        conf_idx = [i for i, t in enumerate(trk.tracks) if t.is_confirmed()]
+        if conf_idx and dets:
+            LA = sys.modules["boxmot.trackers.strongsort.sort.linear_assignment"]
+            feats = np.array([d.feature for d in dets])
+            cost = metric.distance(feats, np.array([trk.tracks[i].track_id for i in conf_idx]))
+            raw = cost.copy()
+            cost = LA.gate_cost_matrix(cost, trk.tracks, dets, conf_idx, list(range(len(dets))), trk.mc_lambda)
+            rec["app_raw"] = raw
+            rec["app_gated"] = cost.copy()
+            # oracle check
+            oraw = O.nn_distance_matrix([samples[int(trk.tracks[i].track_id)] for i in conf_idx], feats)
+            np.testing.assert_allclose(oraw, raw, rtol=0, atol=3e-7)
+            meas = O.tlwh_to_xyah_f32(rec["det_tlwh"])
+            og = O.gate_cost_matrix(raw.copy(), rec["trk_mean"][conf_idx, :4], rec["trk_SI"][conf_idx], meas, trk.mc_lambda)
+            np.testing.assert_allclose(og, cost, rtol=1e-13, atol=0)
+        else:
+            rec["app_raw"] = np.zeros((0, len(dets)))
+            rec["app_gated"] = np.zeros((0, len(dets)))
+        IM = sys.modules["boxmot.trackers.strongsort.sort.iou_matching"]
+        if trk.tracks and dets:
+            ic = IM.iou_cost(trk.tracks, dets)
+            oic = O.iou_cost([O.track_to_tlwh(m[:4]) for m in rec["trk_mean"]], rec["trk_tsu"], rec["det_tlwh"])
+            np.testing.assert_allclose(oic, ic, rtol=1e-14, atol=0)
+            rec["iou_cost"] = ic
+        else:
+            rec["iou_cost"] = np.zeros((len(trk.tracks), len(dets)))
+        rec["sample_ids"] = np.array(sorted(samples), np.int64)
+        rec["sample_cnt"] = np.array([len(samples[k]) for k in sorted(samples)], np.int32)
+        rec["sample_rows"] = (np.concatenate([samples[k] for k in sorted(samples)], 0)
+                              if samples else np.zeros((0, D), np.float32))
+        frames_out.append(rec)
+        cls = np.zeros(len(dets))
+        confs = np.array([d.confidence for d in dets])
+        trk.update(dets, cls, confs)
+    return frames_out, dict(max_dist=max_dist, max_iou_dist=max_iou_dist, mc_lambda=0.995, budget=5)
+
+
+def gold_assoc():
+    frames, cfg = _mk_tracker()
+    flat = {"n_frames": np.int32(len(frames))}
+    for k, v in cfg.items():
+        flat["cfg_" + k] = np.float64(v)
+    n_match = 0
+    for f, rec in enumerate(frames):
+        for k, v in rec.items():
+            flat["f%d_%s" % (f, k)] = v
+        n_match += len(rec["matches"])
+    assert n_match > 20, "sequence too easy/hard: %d matches" % n_match
+    assert any((rec["app_gated"] > 1e4).any() for rec in frames), "gate never fired"
+    _save("assoc_seq", **flat)
+
+    # DIoU (modification_deepsort/iou_matching.py) incl. its __main__ example
+    DI = ref_import.load_file("ref_diou", "modification_deepsort/iou_matching.py")
+    bbox = np.array([10, 12, 8, 9], np.float64)
+    rng = np.random.default_rng(2)
+    cands = np.concatenate([np.array([[10, 12, 8, 9], [12, 14, 8, 9], [30, 40, 5, 5]], np.float64),
+                            rng.uniform(1, 40, (20, 4))])
+    want = DI.iou(bbox, cands)
+    np.testing.assert_allclose(O.diou(bbox, cands), want, rtol=1e-14)
+    IM = ref_import.load_file_pkg("boxmot.trackers.strongsort.sort.iou_matching")
+    want_iou = IM.iou(bbox, cands)
+    np.testing.assert_allclose(O.iou(bbox, cands), want_iou, rtol=1e-14)
+    # matching.py helpers
+    MT = ref_import.load_file_pkg("boxmot.utils.matching")
+    a = rng.standard_normal((7, 16)).astype(np.float32)
+    b = rng.standard_normal((5, 16)).astype(np.float32)
+    cd = MT._cosine_distance(a, b)
+    pd = MT._pdist(a, b)
+    nn = MT._nn_cosine_distance(a, b)
+    np.testing.assert_allclose(O.cosine_distance(a, b), cd, atol=2e-7)
+    np.testing.assert_allclose(O.pdist(a, b), pd, atol=1e-5)
+    np.testing.assert_allclose(O.nn_cosine_distance(a, b), np.asarray(nn), atol=2e-7)
+    _save("assoc_misc", bbox=bbox, cands=cands, diou=want, iou=want_iou, a=a, b=b,
+          cosine=np.asarray(cd), pdist=np.asarray(pd), nn_cosine=np.asarray(nn))
+
+
+def main():
+    assert ref_import.available(), "/root/reference not present: fixtures can only be (re)generated in the build container"
+    ref_import.install()
+    for fn in (gold_dist, gold_eval, gold_jaccard, gold_preprocess, gold_assoc):
+        print(fn.__name__)
+        fn()
+    print("oracle pinned against the reference; fixtures in tests/golden/")
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,100 @@
+"""CPU: the oracle (oracle/reid_oracle.py) against the golden vectors that oracle/make_golden.py
+produced by running the reference's own code (reid/evaluate.py, reid/faiss_utils.py,
+reid/losses/utils.py, boxmot matching / linear_assignment / iou_matching / KF adapter,
+modification_deepsort feature_extractor + iou_matching)."""
+import numpy as np
+
+from oracle import reid_oracle as O
+
+
+def test_dist(golden):
+    g = golden("dist")
+    e = O.euclidean_dist(g["x"], g["y"])
+    mask = g["euclid"] > 1e-2
+    np.testing.assert_allclose(e[mask], g["euclid"][mask], rtol=1e-5)
+    np.testing.assert_allclose(O.cosine_dist(g["x"], g["y"]), g["cosine"], atol=2e-7)
+
+
+def test_eval(golden):
+    g = golden("eval")
+    cmc, ap = O.evaluate_all(g["qf"], g["ql"], g["qc"], g["gf"], g["gl"], g["gc"])
+    assert np.array_equal(cmc, g["cmc"])
+    assert abs(ap - float(g["ap"])) < 1e-12
+    assert (g["first_hit"] == -1).any(), "fixture must exercise the no-good-match sentinel"
+
+
+def test_eval_from_dist_matches_score_path(golden):
+    g = golden("eval")
+    dist = -(g["qf"] @ g["gf"].T)
+    cmc, ap = O.evaluate_all_from_dist(dist, g["ql"], g["qc"], g["gl"], g["gc"])
+    np.testing.assert_allclose(cmc, g["cmc"], atol=1e-7)
+    assert abs(ap - float(g["ap"])) < 1e-9
+
+
+def test_jaccard(golden):
+    g = golden("jaccard")
+    _, rank = O.knn_l2(g["feats"], g["feats"], 20)
+    assert np.array_equal(rank, g["initial_rank"])
+    np.testing.assert_allclose(O.compute_jaccard_distance(g["feats"], 20, 6), g["J_k20_6"], atol=2e-6)
+    np.testing.assert_allclose(O.compute_jaccard_distance(g["feats"], 10, 1), g["J_k10_1"], atol=2e-6)
+    J16 = O.compute_jaccard_distance(g["feats"], 20, 6, use_float16=True)
+    assert J16.dtype == np.float16
+    np.testing.assert_allclose(J16.astype(np.float32), g["J_k20_6_f16"].astype(np.float32), atol=2e-3)
+
+
+def test_jaccard_sparse_rows_equal_dense(golden):
+    """The sparse restatement (what the CUDA kernels mirror) gives the dense reference result."""
+    g = golden("jaccard")
+    feats, rank = g["feats"], g["initial_rank"].astype(np.int64)
+    rows = O.jaccard_sparse_rows(feats, rank, 20, 6)
+    N = feats.shape[0]
+    V = np.zeros((N, N), np.float32)
+    for i, (c, v) in enumerate(rows):
+        V[i, c] = v
+    m = np.minimum(V[:, None, :], V[None, :, :]).sum(-1)
+    J = np.maximum(1 - m / (2 - m), 0)
+    np.testing.assert_allclose(J, g["J_k20_6"], atol=3e-6)
+
+
+def test_preprocess(golden):
+    g = golden("preprocess")
+    img, xyxy = g["img"], g["xyxy"]
+    H, W = img.shape[:2]
+    assert np.array_equal(np.array([O.xywh_to_xyxy(b, W, H) for b in g["boxes_xywh"]], np.int32), xyxy)
+    crops = [img[y1:y2, x1:x2] for x1, y1, x2, y2 in xyxy]
+    cv = O.preprocess_deepsort(crops)
+    assert np.abs(cv[g["cv_full_idx"]] - g["cv_full"]).max() <= 4.8e-7
+    assert np.abs(cv[:, :, ::3, ::3] - g["cv_sub"]).max() <= 4.8e-7
+    for c, want in zip(crops, g["pil_u8"]):
+        assert np.array_equal(O.resize_pil_bilinear_u8(c, 256, 128), want)
+    assert np.abs(O.preprocess_boxmot(crops[:1])[0] - g["pil0"]).max() <= 1e-6
+
+
+def test_assoc_misc(golden):
+    g = golden("assoc_misc")
+    np.testing.assert_allclose(O.iou(g["bbox"], g["cands"]), g["iou"], rtol=1e-14)
+    np.testing.assert_allclose(O.diou(g["bbox"], g["cands"]), g["diou"], rtol=1e-14)
+    np.testing.assert_allclose(O.cosine_distance(g["a"], g["b"]), g["cosine"], atol=2e-7)
+    np.testing.assert_allclose(O.pdist(g["a"], g["b"]), g["pdist"], atol=1e-5)
+    np.testing.assert_allclose(O.nn_cosine_distance(g["a"], g["b"]), g["nn_cosine"], atol=2e-7)
+    assert O.pdist(np.zeros((0, 4)), g["b"][:, :4]).shape == (0, 5)
+
+
+def _frames(g):
+    for f in range(int(g["n_frames"])):
+        yield {k[len("f%d_" % f):]: g[k] for k in g.files if k.startswith("f%d_" % f)}
+
+
+def test_assoc_sequence(golden):
+    """Replay of a reference StrongSORT Tracker run: cost matrices and the assignments."""
+    g = golden("assoc_seq")
+    max_dist, max_iou = float(g["cfg_max_dist"]), float(g["cfg_max_iou_dist"])
+    lam = float(g["cfg_mc_lambda"])
+    n = 0
+    for fr in _frames(g):
+        m, ut, ud = O.match_frame(fr, max_dist, max_iou, lam)
+        assert np.array_equal(np.array(sorted(m), np.int64).reshape(-1, 2), fr["matches"])
+        assert sorted(ut) == fr["unmatched_tracks"].tolist()
+        assert sorted(ud) == fr["unmatched_dets"].tolist()
+        n += len(m)
+    assert n > 20
