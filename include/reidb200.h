@@ -1,0 +1,222 @@
+/* reidb200.h -- C ABI of libreidb200.so, the B200 (sm_100a) ReID matching hot path.
+ *
+ * Drop-in boundary for the reference SuperbTUM/real-time-ReID-tracking @ bb113fd.  The reference
+ * has no FFI of its own (its hot path is plain Python calling NumPy / torch / faiss); every entry
+ * point below names the reference function (file:line) whose arithmetic it replaces, and the
+ * Python shims in real-time-reid-tracking_b200/ keep the reference call signatures on top of it.
+ *
+ * Conventions
+ *   - every pointer is a DEVICE pointer unless its name ends in _host; the caller owns all buffers;
+ *   - every call is asynchronous on `stream` (a cudaStream_t passed as void*), takes no locks and
+ *     keeps no global state except the last-error string (thread local);
+ *   - return value: 0 = ok, negative = REIDB200_E* ; reidb200_last_error() describes the failure;
+ *   - scratch memory is passed in by the caller, sized by the matching *_workspace_bytes();
+ *   - there is no CPU fallback anywhere behind this interface.
+ */
+#ifndef REIDB200_H_
+#define REIDB200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define REIDB200_OK 0
+#define REIDB200_EINVAL (-1)  /* bad argument (shape, alignment, enum, workspace too small) */
+#define REIDB200_ECUDA (-2)   /* CUDA runtime / driver error */
+#define REIDB200_ELIMIT (-3)  /* size outside what this build supports */
+
+const char* reidb200_last_error(void);
+/* ABI version of this header (checked by the Python loader). */
+int reidb200_abi_version(void);
+/* 0 when the current device is sm_100 class with tcgen05/TMA, REIDB200_ECUDA otherwise. */
+int reidb200_check_device(void);
+
+/* ------------------------------------------------------------------------------------------
+ * (1) crop + resize + normalise
+ *   CV_LINEAR     modification_deepsort/feature_extractor.py:31-46  Extractor._preprocess
+ *                 (u8 -> f32 /255, cv2.resize INTER_LINEAR half-pixel no antialias, HWC->CHW,
+ *                 (x-mean)/std)
+ *   PIL_ANTIALIAS yolov8_tracking/boxmot/appearance/reid_multibackend.py:58-66,210-220
+ *                 ReIDDetectMultiBackend._preprocess (PIL two-pass fixed-point bilinear on uint8,
+ *                 /255, ImageNet normalise)
+ *   crop boxes    yolov8_tracking/boxmot/trackers/strongsort/strong_sort.py:115-121,149-159
+ *                 (img[y1:y2, x1:x2]; the int-truncated clamped xyxy is computed by the shim)
+ * src        u8 bytes holding HWC (3-channel interleaved) pixels
+ * crop_off   i64[M]  byte offset of pixel (0,0) of crop i inside src
+ * crop_geom  i32[M,3] = (h, w, row_stride_bytes) of crop i (h,w >= 1)
+ * out        f32[M,3,out_h,out_w]
+ * ------------------------------------------------------------------------------------------ */
+enum { REIDB200_RESIZE_CV_LINEAR = 0, REIDB200_RESIZE_PIL_ANTIALIAS = 1 };
+
+int reidb200_crop_resize_norm(const uint8_t* src, const int64_t* crop_off, const int32_t* crop_geom,
+                              int M, int out_h, int out_w, const float mean_host[3],
+                              const float std_host[3], int mode, float* out, void* stream);
+/* Same with a scratch buffer; required for PIL_ANTIALIAS (uint8 intermediate of the horizontal pass,
+ * sized by reidb200_resize_pil_workspace_bytes), ignored for CV_LINEAR. */
+int reidb200_crop_resize_norm_ws(const uint8_t* src, const int64_t* crop_off, const int32_t* crop_geom,
+                                 int M, int out_h, int out_w, const float mean_host[3],
+                                 const float std_host[3], int mode, float* out, void* workspace,
+                                 size_t workspace_bytes, void* stream);
+/* PIL mode only: the bit-exact uint8 resample (what PIL.Image.resize returns), u8[M,out_h,out_w,3]. */
+int reidb200_resize_pil_u8(const uint8_t* src, const int64_t* crop_off, const int32_t* crop_geom,
+                           int M, int out_h, int out_w, uint8_t* out_u8, void* workspace,
+                           size_t workspace_bytes, void* stream);
+size_t reidb200_resize_pil_workspace_bytes(int M, int max_crop_h, int out_w);
+
+/* ------------------------------------------------------------------------------------------
+ * (2) distance matrix, tcgen05 / TMA tensor-core GEMM with fp32-accurate (bf16x3 split) operands
+ *   EUCLID       reid/losses/utils.py:21-35   euclidean_dist: sqrt(clamp(xx+yy-2xy, 1e-12))
+ *   COSINE_HALF  reid/losses/utils.py:12-18   cosine_dist: (1 - xy/(|x||y|))/2
+ *   DOT          reid/evaluate.py:58          score = gf . q
+ *   SQL2         reid/faiss_utils.py:97-111   faiss METRIC_L2 (squared L2): xx+yy-2xy
+ * x f32[m,d] (row stride ldx), y f32[n,d] (ldy) -> out f32[m,n] (row stride ldo, in elements).
+ * ------------------------------------------------------------------------------------------ */
+enum { REIDB200_DIST_EUCLID = 0, REIDB200_DIST_COSINE_HALF = 1, REIDB200_DIST_DOT = 2,
+       REIDB200_DIST_SQL2 = 3 };
+
+size_t reidb200_distmat_workspace_bytes(int m, int n, int d);
+int reidb200_distmat(const float* x, int m, int64_t ldx, const float* y, int n, int64_t ldy, int d,
+                     int kind, float* out, int64_t ldo, void* workspace, size_t workspace_bytes,
+                     void* stream);
+/* Plain fp32 SIMT kernel with the same epilogues: the on-device cross-check of the tensor-core
+ * path used by the GPU tests.  Not called by any product path. */
+int reidb200_distmat_simt(const float* x, int m, int64_t ldx, const float* y, int n, int64_t ldy,
+                          int d, int kind, float* out, int64_t ldo, void* stream);
+
+/* Operand packing used by distmat/knn: f32[rows,d] -> bf16 hi|lo planes [rows, 2*dp]
+ * (dp = d rounded up to 64, zero padded) and the fp32 squared row norms.  Exposed so a gallery can
+ * be packed once and searched many times (every search entry point packs on the fly today). */
+size_t reidb200_pack_bytes(int rows, int d);
+int reidb200_pack_rows(const float* x, int rows, int64_t ldx, int d, void* packed, float* sqnorm,
+                       void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * (2b) brute-force k-NN (reid/faiss_utils.py:30-139: faiss bfKnn / GpuIndexFlatL2 / IndexFlatL2 /
+ *      IndexShards stand-in; exact, ascending, ties -> lower index).  metric: SQL2 (ascending),
+ *      DOT (descending inner product).
+ * xq f32[nq,d], xb f32[nb,d] -> out_d f32[nq,k], out_i i64[nq,k] or i32[nq,k] (idx64 flag);
+ * index_base is added to every returned index (gallery shard offset).  k <= 1024.
+ * ------------------------------------------------------------------------------------------ */
+size_t reidb200_knn_workspace_bytes(int nq, int nb, int d, int k);
+int reidb200_knn(const float* xq, int nq, int64_t ldq, const float* xb, int nb, int64_t ldb, int d,
+                 int k, int metric, int64_t index_base, float* out_d, void* out_i, int idx64,
+                 void* workspace, size_t workspace_bytes, void* stream);
+/* Row-wise top-k of a materialised matrix (ascending unless descending != 0); optional explicit
+ * candidate ids (cand_i, i64[rows, cols]) for merging per-shard results, else id = column +
+ * index_base.  Used for the per-shard merge after the NCCL all-gather. */
+int reidb200_topk_rows(const float* vals, int rows, int cols, int64_t ldv, const int64_t* cand_i,
+                       int k, int descending, int64_t index_base, float* out_d, void* out_i,
+                       int idx64, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * (4) CMC / mAP  (reid/evaluate.py:33-105  evaluate_all / evaluate / compute_mAP)
+ * mat  f32[Q,G] (row stride ldm): similarity scores (descending = 1, the reference's gf.q) or
+ *      distances (descending = 0, re-ranked evaluation)
+ * ql,qc i32[Q]; gl,gc i32[G]
+ * out_cmc f32[G] = sum_q cmc_q / Q ; out_ap f64[1] = sum_q ap_q / Q  (all Q, reid/evaluate.py:49-50)
+ * out_ap_q f64[Q] (per-query AP, 0 for skipped) and out_first i32[Q] (first-hit rank, -1 =
+ * no valid gallery match, the cmc[0] == -1 sentinel of reid/evaluate.py:80-82) may be NULL.
+ * ------------------------------------------------------------------------------------------ */
+size_t reidb200_eval_workspace_bytes(int Q, int G);
+int reidb200_eval_cmc_map(const float* mat, int Q, int G, int64_t ldm, int descending,
+                          const int32_t* ql, const int32_t* qc, const int32_t* gl, const int32_t* gc,
+                          float* out_cmc, double* out_ap, double* out_ap_q, int32_t* out_first,
+                          void* workspace, size_t workspace_bytes, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * (3) k-reciprocal re-ranking (reid/faiss_utils.py:142-244 compute_jaccard_distance,
+ *     k_reciprocal_neigh) on ONE merged set of N rows.
+ * feats f32[N,d].  Output rows [row0, row0+nrows) x columns [col0, col0+ncols) of the N x N
+ * Jaccard distance, f32 (or f16 when use_float16, the reference's mat_type) with row stride ldo.
+ * lambda_value > 0 blends the classic way (not in the reference):
+ *      out = (1-lambda) * jaccard + lambda * sqrt(max(sql2, 1e-12))
+ * rank_out (optional) i32[N,k1]: the initial ranking (stage D2).
+ * ------------------------------------------------------------------------------------------ */
+size_t reidb200_jaccard_workspace_bytes(int N, int d, int k1, int k2);
+int reidb200_jaccard(const float* feats, int N, int64_t ldf, int d, int k1, int k2, int use_float16,
+                     float lambda_value, int row0, int nrows, int col0, int ncols, void* out,
+                     int64_t ldo, int32_t* rank_out, void* workspace, size_t workspace_bytes,
+                     void* stream);
+/* Stages D3-D7 only, from a caller-supplied initial ranking i32[N,k1] and the materialised
+ * squared-L2 matrix f32[N,N] (row stride lds). */
+int reidb200_jaccard_from_rank(const int32_t* rank, const float* sql2, int64_t lds,
+                               const float* sqnorm, int N, int k1, int k2, int use_float16,
+                               float lambda_value, int row0, int nrows, int col0, int ncols,
+                               void* out, int64_t ldo, void* workspace, size_t workspace_bytes,
+                               void* stream);
+/* R(i,k) lists for inspection/tests: out_idx i32[N,k+1] (-1 padded), out_cnt i32[N]
+ * (reid/faiss_utils.py:142-146). */
+int reidb200_k_reciprocal(const int32_t* rank, int N, int k1_cols, int k, int32_t* out_idx,
+                          int32_t* out_cnt, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * (5) DeepSort / StrongSort association cost, one fused kernel per frame.
+ *   gallery     boxmot/utils/matching.py:363-409  NearestNeighborDistanceMetric
+ *               (partial_fit keeps the last `budget` features per track id; distance = per-track
+ *               min over samples of the cosine distance, rows re-normalised, :278-339)
+ *   gate        boxmot/motion/adapters/strongsort_kf_adapter.py:137-169 -> kalman_filter.py:577-586
+ *               sqrt(y^T SI y), y = z - x[:4]  (stale SI)
+ *               boxmot/trackers/strongsort/sort/linear_assignment.py:147-198 gate_cost_matrix,
+ *               :58-59 clamp of min_cost_matching
+ *   iou         boxmot/trackers/strongsort/sort/iou_matching.py:9-86 (iou, iou_cost) and the DIoU of
+ *               modification_deepsort/iou_matching.py:5-47
+ * The gallery is an opaque device-resident ring buffer [slots, budget, d].
+ * ------------------------------------------------------------------------------------------ */
+typedef struct reidb200_gallery reidb200_gallery;
+
+int reidb200_gallery_create(int slots, int budget, int d, reidb200_gallery** out);
+int reidb200_gallery_destroy(reidb200_gallery* g);
+/* Append n feature rows f32[n,d]; row i goes to slot slot_of_row[i] (i32[n], device).  Rows for one
+ * slot are appended in row order; only the last `budget` survive (matching.py:385-386). */
+int reidb200_gallery_partial_fit(reidb200_gallery* g, const float* feats, int64_t ldf,
+                                 const int32_t* slot_of_row, int n, void* stream);
+/* Forget slots (tracks that are no longer active, matching.py:387-389). slots i32[n] device. */
+int reidb200_gallery_reset_slots(reidb200_gallery* g, const int32_t* slots, int n, void* stream);
+/* counts i32[slots] (device copy out), for tests. */
+int reidb200_gallery_counts(reidb200_gallery* g, int32_t* out_counts, void* stream);
+/* sample rows of a slot as stored (L2-normalised), f32[budget,d], oldest first; for tests. */
+int reidb200_gallery_read_slot(reidb200_gallery* g, int slot, float* out_rows, void* stream);
+
+enum { REIDB200_IOU_PLAIN = 0, REIDB200_IOU_DIOU = 1 };
+enum { REIDB200_ASSOC_CLAMP_APP = 1, REIDB200_ASSOC_CLAMP_IOU = 2, REIDB200_ASSOC_NO_GATE = 4 };
+
+/* One frame:
+ *   det_feat f32[M,d]; det_tlwh f32[M,4];
+ *   trk_slot i32[T] gallery slot per track row; trk_mean f64[T,8] KF mean (xyah + velocities);
+ *   trk_SI f64[T,16] inverse innovation covariance as stored on the track (stale, F6);
+ *   trk_tsu i32[T] time_since_update.
+ * Outputs (f64[T,M] each, row-major):
+ *   out_app   gated+blended appearance cost (what gate_cost_matrix returns; with
+ *             REIDB200_ASSOC_CLAMP_APP also `cost > max_dist -> max_dist + 1e-5`)
+ *   out_raw   (optional) NearestNeighborDistanceMetric.distance before gating
+ *   out_iou   iou_cost for every (track,det) pair (rows with tsu > 1 = 1e5; with
+ *             REIDB200_ASSOC_CLAMP_IOU also clamped at max_iou_dist + 1e-5)
+ */
+int reidb200_assoc_frame(reidb200_gallery* g, const float* det_feat, int64_t ldf,
+                         const float* det_tlwh, int M, const int32_t* trk_slot,
+                         const double* trk_mean, const double* trk_SI, const int32_t* trk_tsu, int T,
+                         double mc_lambda, double max_dist, double max_iou_dist, int iou_mode,
+                         int flags, double* out_app, double* out_raw, double* out_iou, void* stream);
+
+/* Stand-alone pieces of the same kernel family (the reference's free functions):
+ *   iou / DIoU of T boxes (f64 tlwh) against M candidates (f32 or f64 tlwh) -> f64[T,M] */
+int reidb200_iou_matrix(const double* bbox_tlwh, int T, const void* cand_tlwh, int cand_is_f64, int M,
+                        int iou_mode, double* out, void* stream);
+/*   Mahalanobis gate distances f64[T,M] from x4 f64[T,4], SI f64[T,16], measurements f64[M,4]
+ *   (the values are whatever the caller passes: Detection.to_xyah() is float32-rounded) */
+int reidb200_gating_distance(const double* x4, const double* SI, const double* meas, int T, int M,
+                             double* out, void* stream);
+/*   cosine distance 1 - a^.b^T (both re-normalised unless normalized != 0), f32[na,nb]
+ *   (boxmot/utils/matching.py:278-298) */
+size_t reidb200_cosine_distance_workspace_bytes(int na, int nb, int d);
+int reidb200_cosine_distance(const float* a, int na, int64_t lda, const float* b, int nb, int64_t ldb,
+                             int d, int normalized, float* out, void* workspace,
+                             size_t workspace_bytes, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* REIDB200_H_ */

@@ -1,0 +1,146 @@
+"""ctypes loader for libreidb200.so (the C ABI in include/reidb200.h).
+
+There is no CPU fallback: if the library is missing it is built with nvcc; if that is impossible, or no
+sm_100 device is visible when a kernel is requested, the call raises.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import threading
+
+import torch
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libreidb200.so")
+ABI_VERSION = 1
+
+OK, EINVAL, ECUDA, ELIMIT = 0, -1, -2, -3
+RESIZE_CV_LINEAR, RESIZE_PIL_ANTIALIAS = 0, 1
+DIST_EUCLID, DIST_COSINE_HALF, DIST_DOT, DIST_SQL2 = 0, 1, 2, 3
+IOU_PLAIN, IOU_DIOU = 0, 1
+ASSOC_CLAMP_APP, ASSOC_CLAMP_IOU, ASSOC_NO_GATE = 1, 2, 4
+
+_vp, _i, _i64, _sz, _f, _d = C.c_void_p, C.c_int, C.c_int64, C.c_size_t, C.c_float, C.c_double
+_f3 = C.POINTER(C.c_float)
+
+# name -> (restype, argtypes); mirrors include/reidb200.h line by line
+SIGNATURES = {
+    "reidb200_last_error": (C.c_char_p, []),
+    "reidb200_abi_version": (_i, []),
+    "reidb200_check_device": (_i, []),
+    "reidb200_crop_resize_norm": (_i, [_vp, _vp, _vp, _i, _i, _i, _f3, _f3, _i, _vp, _vp]),
+    "reidb200_crop_resize_norm_ws": (_i, [_vp, _vp, _vp, _i, _i, _i, _f3, _f3, _i, _vp, _vp, _sz, _vp]),
+    "reidb200_resize_pil_u8": (_i, [_vp, _vp, _vp, _i, _i, _i, _vp, _vp, _sz, _vp]),
+    "reidb200_resize_pil_workspace_bytes": (_sz, [_i, _i, _i]),
+    "reidb200_distmat_workspace_bytes": (_sz, [_i, _i, _i]),
+    "reidb200_distmat": (_i, [_vp, _i, _i64, _vp, _i, _i64, _i, _i, _vp, _i64, _vp, _sz, _vp]),
+    "reidb200_distmat_simt": (_i, [_vp, _i, _i64, _vp, _i, _i64, _i, _i, _vp, _i64, _vp]),
+    "reidb200_pack_bytes": (_sz, [_i, _i]),
+    "reidb200_pack_rows": (_i, [_vp, _i, _i64, _i, _vp, _vp, _vp]),
+    "reidb200_knn_workspace_bytes": (_sz, [_i, _i, _i, _i]),
+    "reidb200_knn": (_i, [_vp, _i, _i64, _vp, _i, _i64, _i, _i, _i, _i64, _vp, _vp, _i, _vp, _sz, _vp]),
+    "reidb200_topk_rows": (_i, [_vp, _i, _i, _i64, _vp, _i, _i, _i64, _vp, _vp, _i, _vp]),
+    "reidb200_eval_workspace_bytes": (_sz, [_i, _i]),
+    "reidb200_eval_cmc_map": (_i, [_vp, _i, _i, _i64, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _sz, _vp]),
+    "reidb200_jaccard_workspace_bytes": (_sz, [_i, _i, _i, _i]),
+    "reidb200_jaccard": (_i, [_vp, _i, _i64, _i, _i, _i, _i, _f, _i, _i, _i, _i, _vp, _i64, _vp, _vp, _sz, _vp]),
+    "reidb200_jaccard_from_rank": (_i, [_vp, _vp, _i64, _vp, _i, _i, _i, _i, _f, _i, _i, _i, _i, _vp, _i64, _vp, _sz, _vp]),
+    "reidb200_k_reciprocal": (_i, [_vp, _i, _i, _i, _vp, _vp, _vp]),
+    "reidb200_gallery_create": (_i, [_i, _i, _i, C.POINTER(_vp)]),
+    "reidb200_gallery_destroy": (_i, [_vp]),
+    "reidb200_gallery_partial_fit": (_i, [_vp, _vp, _i64, _vp, _i, _vp]),
+    "reidb200_gallery_reset_slots": (_i, [_vp, _vp, _i, _vp]),
+    "reidb200_gallery_counts": (_i, [_vp, _vp, _vp]),
+    "reidb200_gallery_read_slot": (_i, [_vp, _i, _vp, _vp]),
+    "reidb200_assoc_frame": (_i, [_vp, _vp, _i64, _vp, _i, _vp, _vp, _vp, _vp, _i, _d, _d, _d, _i, _i, _vp, _vp, _vp, _vp]),
+    "reidb200_iou_matrix": (_i, [_vp, _i, _vp, _i, _i, _i, _vp, _vp]),
+    "reidb200_gating_distance": (_i, [_vp, _vp, _vp, _i, _i, _vp, _vp]),
+    "reidb200_cosine_distance_workspace_bytes": (_sz, [_i, _i, _i]),
+    "reidb200_cosine_distance": (_i, [_vp, _i, _i64, _vp, _i, _i64, _i, _i, _vp, _vp, _sz, _vp]),
+}
+
+_lib = None
+_lock = threading.Lock()
+_device_ok = set()
+
+
+class Reidb200Error(RuntimeError):
+    pass
+
+
+def load(build_if_missing: bool = True) -> C.CDLL:
+    """Load (building first if needed) libreidb200.so and bind every symbol of the header."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    with _lock:
+        if _lib is not None:
+            return _lib
+        if not os.path.exists(LIB_PATH):
+            if not build_if_missing:
+                raise Reidb200Error("libreidb200.so is missing (%s): run `python __graft_entry__.py build`" % LIB_PATH)
+            from . import build as _build
+
+            _build.build()
+        lib = C.CDLL(LIB_PATH)
+        for name, (res, args) in SIGNATURES.items():
+            fn = getattr(lib, name)  # AttributeError here == header/library mismatch: fail loudly
+            fn.restype = res
+            fn.argtypes = args
+        if lib.reidb200_abi_version() != ABI_VERSION:
+            raise Reidb200Error("libreidb200.so ABI %d != loader ABI %d: rebuild" % (lib.reidb200_abi_version(), ABI_VERSION))
+        _lib = lib
+    return _lib
+
+
+def last_error() -> str:
+    return load().reidb200_last_error().decode("utf-8", "replace")
+
+
+def check(rc: int, exc=None):
+    """Convert a C status into the exception type the reference would raise."""
+    if rc == OK:
+        return
+    msg = last_error()
+    if rc == EINVAL:
+        raise (exc or ValueError)(msg)
+    if rc == ELIMIT:
+        raise NotImplementedError(msg)
+    raise Reidb200Error(msg)
+
+
+def require_device(t: torch.Tensor = None) -> torch.device:
+    """The CUDA device work will run on; raises when there is none (no CPU fallback)."""
+    if not torch.cuda.is_available():
+        raise Reidb200Error("reidb200 needs an sm_100 (B200) CUDA device; none is visible and there is no CPU fallback")
+    dev = t.device if (t is not None and t.is_cuda) else torch.device("cuda", torch.cuda.current_device())
+    if dev.index not in _device_ok:
+        with torch.cuda.device(dev):
+            check(load().reidb200_check_device())
+        _device_ok.add(dev.index)
+    return dev
+
+
+def stream_ptr() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def ptr(t) -> int:
+    return 0 if t is None else t.data_ptr()
+
+
+def workspace(nbytes: int, device) -> torch.Tensor:
+    """256-byte aligned scratch (torch's caching allocator hands out 512-byte aligned blocks)."""
+    return torch.empty(max(int(nbytes), 256), dtype=torch.uint8, device=device)
+
+
+def as_f32_cuda(x, device=None) -> torch.Tensor:
+    """Any array-like -> contiguous float32 CUDA tensor (H2D when it lives on the host)."""
+    if not isinstance(x, torch.Tensor):
+        import numpy as np
+
+        x = torch.from_numpy(np.ascontiguousarray(np.asarray(x, dtype=np.float32)))
+    dev = device or (x.device if x.is_cuda else require_device())
+    x = x.to(device=dev, dtype=torch.float32, non_blocking=True)
+    return x if x.is_contiguous() else x.contiguous()

@@ -1,0 +1,473 @@
+// (5) DeepSort / StrongSort association cost.
+//   gallery   boxmot/utils/matching.py:363-409  NearestNeighborDistanceMetric (device-resident ring buffer)
+//   cosine    boxmot/utils/matching.py:278-339  _cosine_distance / _nn_cosine_distance
+//   gate      boxmot/motion/adapters/strongsort_kf_adapter.py:137-169 -> kalman_filter.py:577-586 and
+//             boxmot/trackers/strongsort/sort/linear_assignment.py:147-198 (gate_cost_matrix), :58-59 (clamp)
+//   iou       boxmot/trackers/strongsort/sort/iou_matching.py:9-86, modification_deepsort/iou_matching.py:5-47
+// One kernel per frame: CTA t owns track t: per-track gallery x detections cosine minimum (fp32),
+// Mahalanobis gate + blend (fp64), IoU / DIoU row (fp64).
+#include "common.cuh"
+
+struct reidb200_gallery {
+  int slots, budget, d;
+  float* feats;      // [slots, budget, d] L2-normalised rows (ring per slot)
+  int32_t* count;    // [slots] valid rows
+  int32_t* head;     // [slots] next write position
+  int32_t* scratch;  // [2*scratch_rows] per-row destination / rows-after
+  int scratch_rows;
+};
+
+namespace reidb200 {
+
+constexpr double INFTY_COST = 1e5;        // sort/linear_assignment.py:9
+constexpr double CHI2INV95_4 = 9.4877;    // boxmot/utils/matching.py:12-22
+
+// ------------------------------------------------------------------------------------ gallery
+// dst[i] = ring position of row i (or -1 when a later row of the same call overwrites it)
+__global__ void pf_assign_kernel(const int32_t* __restrict__ slot_of_row, int n, int budget,
+                                 const int32_t* __restrict__ head, int32_t* __restrict__ dst,
+                                 int32_t* __restrict__ after) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const int s = slot_of_row[i];
+  int before = 0, aft = 0;
+  for (int o = 0; o < n; ++o) {
+    const bool same = slot_of_row[o] == s;
+    before += same && o < i;
+    aft += same && o > i;
+  }
+  after[i] = aft;
+  dst[i] = aft < budget ? (head[s] + before) % budget : -1;
+}
+
+// warp per row: a / ||a|| in fp32 (matching.py:294-296), written to its ring position
+__global__ void __launch_bounds__(256)
+pf_write_kernel(const float* __restrict__ feats, int64_t ldf, const int32_t* __restrict__ slot_of_row,
+                const int32_t* __restrict__ dst, int n, int budget, int d, float* __restrict__ gal) {
+  const int i = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (i >= n) return;
+  const int p = dst[i];
+  if (p < 0) return;
+  const float* src = feats + (size_t)i * ldf;
+  float s = 0.f;
+  for (int k = lane; k < d; k += 32) { const float v = src[k]; s = fmaf(v, v, s); }
+  s = sqrtf(warp_sum(s));
+  float* o = gal + ((size_t)slot_of_row[i] * budget + p) * d;
+  for (int k = lane; k < d; k += 32) o[k] = __fdiv_rn(src[k], s);
+}
+
+__global__ void pf_update_kernel(const int32_t* __restrict__ slot_of_row, const int32_t* __restrict__ after, int n,
+                                 int budget, int32_t* __restrict__ head, int32_t* __restrict__ count) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n || after[i] != 0) return;  // the last row of each slot updates the slot
+  const int s = slot_of_row[i];
+  int total = 0;
+  for (int o = 0; o < n; ++o) total += slot_of_row[o] == s;
+  head[s] = (head[s] + total) % budget;
+  count[s] = min(budget, count[s] + total);
+}
+
+__global__ void gal_reset_kernel(const int32_t* __restrict__ slots, int n, int32_t* __restrict__ head,
+                                 int32_t* __restrict__ count) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) { head[slots[i]] = 0; count[slots[i]] = 0; }
+}
+
+// rows of one slot, oldest first
+__global__ void gal_read_kernel(const float* __restrict__ gal, const int32_t* __restrict__ head,
+                                const int32_t* __restrict__ count, int slot, int budget, int d, float* __restrict__ out) {
+  const int c = count[slot], h = head[slot];
+  for (int r = blockIdx.x; r < budget; r += gridDim.x) {
+    for (int k = threadIdx.x; k < d; k += blockDim.x) {
+      float v = 0.f;
+      if (r < c) v = gal[((size_t)slot * budget + ((h - c + r) % budget + budget) % budget) * d + k];
+      out[(size_t)r * d + k] = v;
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------ box / gate math
+// Detection.to_xyah in float32 (sort/detection.py:42-50), promoted to double by z - Hx
+__device__ __forceinline__ void tlwh_to_xyah_f32(const float* t, double z[4]) {
+  const float x = __fadd_rn(t[0], __fdiv_rn(t[2], 2.0f));
+  const float y = __fadd_rn(t[1], __fdiv_rn(t[3], 2.0f));
+  const float a = __fdiv_rn(t[2], t[3]);
+  z[0] = (double)x; z[1] = (double)y; z[2] = (double)a; z[3] = (double)t[3];
+}
+
+// sqrt(y^T SI y) with y = z - x[:4] (kalman_filter.py:577-586)
+__device__ __forceinline__ double maha(const double z[4], const double* x4, const double* SI) {
+  double y[4];
+#pragma unroll
+  for (int r = 0; r < 4; ++r) y[r] = z[r] - x4[r];
+  double acc = 0.0;
+#pragma unroll
+  for (int c = 0; c < 4; ++c) {
+    double v = 0.0;
+#pragma unroll
+    for (int r = 0; r < 4; ++r) v += y[r] * SI[r * 4 + c];
+    acc += v * y[c];
+  }
+  return sqrt(acc);
+}
+
+// Track.to_tlwh from the KF mean (sort/track.py:107-120), fp64
+__device__ __forceinline__ void mean_to_tlwh(const double* mean, double b[4]) {
+  b[2] = mean[2] * mean[3];
+  b[3] = mean[3];
+  b[0] = mean[0] - b[2] / 2;
+  b[1] = mean[1] - b[3] / 2;
+}
+
+// iou / DIoU of a f64 tlwh box against one candidate whose own arithmetic runs in its dtype CT
+// (numpy: candidates[:, :2] + candidates[:, 2:] and the area product stay float32 for float32 input).
+template <typename CT>
+__device__ __forceinline__ double iou_one(const double b[4], const CT* c, int mode) {
+  const double b_tlx = b[0], b_tly = b[1], b_brx = b[0] + b[2], b_bry = b[1] + b[3];
+  const CT cbx = c[0] + c[2], cby = c[1] + c[3];
+  const CT carea = c[2] * c[3];
+  const double c_tlx = (double)c[0], c_tly = (double)c[1], c_brx = (double)cbx, c_bry = (double)cby;
+  const double tlx = fmax(b_tlx, c_tlx), tly = fmax(b_tly, c_tly);
+  const double brx = fmin(b_brx, c_brx), bry = fmin(b_bry, c_bry);
+  const double w = fmax(0.0, brx - tlx), h = fmax(0.0, bry - tly);
+  const double inter = w * h;
+  const double area_b = b[2] * b[3];
+  const double iou = inter / (area_b + (double)carea - inter);
+  if (mode == REIDB200_IOU_PLAIN) return iou;
+  // DIoU: centre distance over outer diagonal (modification_deepsort/iou_matching.py:26-46)
+  const double bcx = (b_tly + b_bry) / 2, bcy = (b_tlx + b_brx) / 2;
+  const double ccx = (c_tly + c_bry) / 2, ccy = (c_tlx + c_brx) / 2;
+  const double dd = (bcx - ccx) * (bcx - ccx) + (bcy - ccy) * (bcy - ccy);
+  const double otlx = fmin(b_tlx, c_tlx), otly = fmin(b_tly, c_tly);
+  const double obrx = fmax(b_brx, c_brx), obry = fmax(b_bry, c_bry);
+  const double rou = (otlx - obrx) * (otlx - obrx) + (otly - obry) * (otly - obry);
+  return iou - dd / rou;
+}
+
+// ------------------------------------------------------------------------------------ fused frame kernel
+// CTA = one track.  Appearance: 64 gallery rows x 64 detections per tile, 4x4 register micro-tile,
+// k-chunks of 16 staged k-major in shared memory; the running per-detection maximum of the dot product
+// stays in registers over the row tiles (min(1-dot) == 1-max(dot) exactly).
+constexpr int AS_THREADS = 256;
+constexpr int AS_TR = 64, AS_TD = 64, AS_TK = 16;
+
+struct AssocArgs {
+  const float* gal; const int32_t* gcount; const int32_t* ghead; int budget, d;
+  const float* det_feat; int64_t ldf; const float* det_tlwh; int M;
+  const int32_t* trk_slot; const double* trk_mean; const double* trk_SI; const int32_t* trk_tsu; int T;
+  double mc_lambda, max_dist, max_iou_dist; int iou_mode, flags;
+  double* out_app; double* out_raw; double* out_iou;
+};
+
+__global__ void __launch_bounds__(AS_THREADS)
+assoc_frame_kernel(AssocArgs a) {
+  __shared__ float Gs[AS_TK][AS_TR + 4];
+  __shared__ float Fs[AS_TK][AS_TD + 4];
+  __shared__ float red[16][AS_TD + 1];
+  __shared__ float fsq[AS_TD];
+  __shared__ double s_x4[4], s_SI[16], s_box[4];
+
+  const int t = blockIdx.x;
+  const int tid = threadIdx.x;
+  const int tx = tid & 15, ty = tid >> 4;  // tx -> detections, ty -> gallery rows
+  const int slot = a.trk_slot ? a.trk_slot[t] : -1;
+  const int cnt = (slot >= 0 && a.gal) ? a.gcount[slot] : 0;
+  const float* G = a.gal + (size_t)(slot >= 0 ? slot : 0) * a.budget * a.d;
+  if (tid < 4) s_x4[tid] = a.trk_mean[(size_t)t * 8 + tid];
+  if (tid < 16) s_SI[tid] = a.trk_SI ? a.trk_SI[(size_t)t * 16 + tid] : 0.0;
+  if (tid == 0) mean_to_tlwh(a.trk_mean + (size_t)t * 8, s_box);
+  __syncthreads();
+  const bool tsu_far = a.trk_tsu[t] > 1;
+
+  for (int d0 = 0; d0 < a.M; d0 += AS_TD) {
+    float best[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
+    if (cnt > 0 && a.out_app) {
+      for (int r0 = 0; r0 < cnt; r0 += AS_TR) {
+        float acc[4][4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+#pragma unroll
+          for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
+        float sq = 0.f;
+        for (int k0 = 0; k0 < a.d; k0 += AS_TK) {
+          // 64 rows x 16 k = 1024 elements per operand: 4 per thread (row = tid/4, k = (tid%4)*4..+3)
+          const int lr = tid >> 2, lk = (tid & 3) * 4;
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            const int k = k0 + lk + e;
+            const int gr = r0 + lr, dm = d0 + lr;
+            Gs[lk + e][lr] = (gr < cnt && k < a.d) ? G[(size_t)gr * a.d + k] : 0.f;
+            const float fv = (dm < a.M && k < a.d) ? a.det_feat[(size_t)dm * a.ldf + k] : 0.f;
+            Fs[lk + e][lr] = fv;
+            sq = fmaf(fv, fv, sq);
+          }
+          __syncthreads();
+#pragma unroll
+          for (int k = 0; k < AS_TK; ++k) {
+            float g[4], f[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) g[i] = Gs[k][ty * 4 + i];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) f[j] = Fs[k][tx * 4 + j];
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+#pragma unroll
+              for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(g[i], f[j], acc[i][j]);
+          }
+          __syncthreads();
+        }
+        if (r0 == 0) {  // |f|^2 of detection d0 + tid/4: partial sums sit in 4 consecutive lanes
+          sq += __shfl_xor_sync(0xffffffffu, sq, 1);
+          sq += __shfl_xor_sync(0xffffffffu, sq, 2);
+          if ((tid & 3) == 0) fsq[tid >> 2] = sq;
+        }
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          if (r0 + ty * 4 + i < cnt) {
+#pragma unroll
+            for (int j = 0; j < 4; ++j) best[j] = fmaxf(best[j], acc[i][j]);
+          }
+        }
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < 4; ++j) red[ty][tx * 4 + j] = best[j];
+    __syncthreads();
+    if (tid < AS_TD) {
+      const int m = d0 + tid;
+      if (m < a.M) {
+        const size_t o = (size_t)t * a.M + m;
+        // ---- appearance + gate (linear_assignment.py:147-198)
+        if (a.out_app) {
+          double cost = INFTY_COST, raw = INFTY_COST;
+          if (cnt > 0) {
+            float mx = red[0][tid];
+#pragma unroll
+            for (int r = 1; r < 16; ++r) mx = fmaxf(mx, red[r][tid]);
+            const float dist = __fsub_rn(1.0f, __fdiv_rn(mx, sqrtf(fsq[tid])));
+            raw = (double)dist;
+            cost = raw;
+          }
+          if (a.out_raw) a.out_raw[o] = raw;
+          if (!(a.flags & REIDB200_ASSOC_NO_GATE)) {
+            double z[4];
+            tlwh_to_xyah_f32(a.det_tlwh + (size_t)m * 4, z);
+            const double gd = maha(z, s_x4, s_SI);
+            if (gd > CHI2INV95_4) cost = INFTY_COST;
+            cost = a.mc_lambda * cost + (1 - a.mc_lambda) * gd;
+          }
+          if ((a.flags & REIDB200_ASSOC_CLAMP_APP) && cost > a.max_dist) cost = a.max_dist + 1e-5;
+          a.out_app[o] = cost;
+        }
+        // ---- IoU row (iou_matching.py:77-86)
+        if (a.out_iou) {
+          double c = INFTY_COST;
+          if (!tsu_far) c = 1.0 - iou_one<float>(s_box, a.det_tlwh + (size_t)m * 4, a.iou_mode);
+          if ((a.flags & REIDB200_ASSOC_CLAMP_IOU) && c > a.max_iou_dist) c = a.max_iou_dist + 1e-5;
+          a.out_iou[o] = c;
+        }
+      }
+    }
+    __syncthreads();
+  }
+}
+
+// ------------------------------------------------------------------------------------ stand-alone pieces
+template <typename CT>
+__global__ void iou_matrix_kernel(const double* __restrict__ bbox, int T, const CT* __restrict__ cand, int M, int mode,
+                                  double* __restrict__ out) {
+  const int m = blockIdx.x * blockDim.x + threadIdx.x, t = blockIdx.y;
+  if (m >= M) return;
+  double b[4] = {bbox[t * 4 + 0], bbox[t * 4 + 1], bbox[t * 4 + 2], bbox[t * 4 + 3]};
+  out[(size_t)t * M + m] = iou_one<CT>(b, cand + (size_t)m * 4, mode);
+}
+
+__global__ void gating_kernel(const double* __restrict__ x4, const double* __restrict__ SI,
+                              const double* __restrict__ meas, int T, int M, double* __restrict__ out) {
+  const int m = blockIdx.x * blockDim.x + threadIdx.x, t = blockIdx.y;
+  if (m >= M) return;
+  double z[4] = {meas[m * 4 + 0], meas[m * 4 + 1], meas[m * 4 + 2], meas[m * 4 + 3]};
+  out[(size_t)t * M + m] = maha(z, x4 + (size_t)t * 4, SI + (size_t)t * 16);
+}
+
+// warp per row: out = a / ||a||
+__global__ void normalize_rows_kernel(const float* __restrict__ x, int n, int64_t ld, int d, float* __restrict__ out) {
+  const int i = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (i >= n) return;
+  float s = 0.f;
+  for (int k = lane; k < d; k += 32) { const float v = x[(size_t)i * ld + k]; s = fmaf(v, v, s); }
+  s = sqrtf(warp_sum(s));
+  for (int k = lane; k < d; k += 32) out[(size_t)i * d + k] = __fdiv_rn(x[(size_t)i * ld + k], s);
+}
+
+__global__ void one_minus_kernel(float* __restrict__ x, size_t n) {
+  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) x[i] = __fsub_rn(1.0f, x[i]);
+}
+
+}  // namespace reidb200
+
+#include "gemm.cuh"
+
+using namespace reidb200;
+
+extern "C" int reidb200_gallery_create(int slots, int budget, int d, reidb200_gallery** out) {
+  RB_REQUIRE(out && slots > 0 && budget > 0 && d > 0, "gallery_create: bad argument");
+  reidb200_gallery* g = new reidb200_gallery();
+  g->slots = slots; g->budget = budget; g->d = d;
+  g->feats = nullptr; g->count = nullptr; g->head = nullptr; g->scratch = nullptr;
+  g->scratch_rows = slots > 1024 ? slots : 1024;
+  cudaError_t e = cudaMalloc(&g->feats, (size_t)slots * budget * d * sizeof(float));
+  if (e == cudaSuccess) e = cudaMalloc(&g->count, (size_t)slots * sizeof(int32_t));
+  if (e == cudaSuccess) e = cudaMalloc(&g->head, (size_t)slots * sizeof(int32_t));
+  if (e == cudaSuccess) e = cudaMalloc(&g->scratch, (size_t)2 * g->scratch_rows * sizeof(int32_t));
+  if (e == cudaSuccess) e = cudaMemset(g->count, 0, (size_t)slots * sizeof(int32_t));
+  if (e == cudaSuccess) e = cudaMemset(g->head, 0, (size_t)slots * sizeof(int32_t));
+  if (e != cudaSuccess) {
+    reidb200_gallery_destroy(g);
+    return cuda_fail(e, "gallery_create", __FILE__, __LINE__);
+  }
+  *out = g;
+  return REIDB200_OK;
+}
+
+extern "C" int reidb200_gallery_destroy(reidb200_gallery* g) {
+  if (!g) return REIDB200_OK;
+  cudaFree(g->feats); cudaFree(g->count); cudaFree(g->head); cudaFree(g->scratch);
+  delete g;
+  return REIDB200_OK;
+}
+
+extern "C" int reidb200_gallery_partial_fit(reidb200_gallery* g, const float* feats, int64_t ldf,
+                                            const int32_t* slot_of_row, int n, void* stream) {
+  if (n == 0) return REIDB200_OK;
+  RB_REQUIRE(g && feats && slot_of_row && n > 0 && ldf >= g->d, "gallery_partial_fit: bad argument");
+  cudaStream_t st = (cudaStream_t)stream;
+  for (int b0 = 0; b0 < n; b0 += g->scratch_rows) {  // batches keep the append order
+    const int nb = n - b0 < g->scratch_rows ? n - b0 : g->scratch_rows;
+    int32_t* dst = g->scratch;
+    int32_t* after = g->scratch + g->scratch_rows;
+    pf_assign_kernel<<<ceil_div(nb, 128), 128, 0, st>>>(slot_of_row + b0, nb, g->budget, g->head, dst, after);
+    RB_LAUNCH_CHECK("pf_assign_kernel");
+    pf_write_kernel<<<ceil_div(nb, 8), 256, 0, st>>>(feats + (size_t)b0 * ldf, ldf, slot_of_row + b0, dst, nb, g->budget,
+                                                    g->d, g->feats);
+    RB_LAUNCH_CHECK("pf_write_kernel");
+    pf_update_kernel<<<ceil_div(nb, 128), 128, 0, st>>>(slot_of_row + b0, after, nb, g->budget, g->head, g->count);
+    RB_LAUNCH_CHECK("pf_update_kernel");
+  }
+  return REIDB200_OK;
+}
+
+extern "C" int reidb200_gallery_reset_slots(reidb200_gallery* g, const int32_t* slots, int n, void* stream) {
+  if (n == 0) return REIDB200_OK;
+  RB_REQUIRE(g && slots && n > 0, "gallery_reset_slots: bad argument");
+  gal_reset_kernel<<<ceil_div(n, 128), 128, 0, (cudaStream_t)stream>>>(slots, n, g->head, g->count);
+  RB_LAUNCH_CHECK("gal_reset_kernel");
+  return REIDB200_OK;
+}
+
+extern "C" int reidb200_gallery_counts(reidb200_gallery* g, int32_t* out_counts, void* stream) {
+  RB_REQUIRE(g && out_counts, "gallery_counts: bad argument");
+  RB_CUDA(cudaMemcpyAsync(out_counts, g->count, (size_t)g->slots * sizeof(int32_t), cudaMemcpyDeviceToDevice,
+                          (cudaStream_t)stream));
+  return REIDB200_OK;
+}
+
+extern "C" int reidb200_gallery_read_slot(reidb200_gallery* g, int slot, float* out_rows, void* stream) {
+  RB_REQUIRE(g && out_rows && slot >= 0 && slot < g->slots, "gallery_read_slot: bad argument");
+  gal_read_kernel<<<g->budget, 128, 0, (cudaStream_t)stream>>>(g->feats, g->head, g->count, slot, g->budget, g->d,
+                                                              out_rows);
+  RB_LAUNCH_CHECK("gal_read_kernel");
+  return REIDB200_OK;
+}
+
+extern "C" int reidb200_assoc_frame(reidb200_gallery* g, const float* det_feat, int64_t ldf, const float* det_tlwh, int M,
+                                    const int32_t* trk_slot, const double* trk_mean, const double* trk_SI,
+                                    const int32_t* trk_tsu, int T, double mc_lambda, double max_dist,
+                                    double max_iou_dist, int iou_mode, int flags, double* out_app, double* out_raw,
+                                    double* out_iou, void* stream) {
+  if (T == 0 || M == 0) return REIDB200_OK;  // the reference returns early for empty inputs (linear_assignment.py:55-56)
+  RB_REQUIRE(T > 0 && M > 0 && det_tlwh && trk_mean && trk_tsu, "assoc_frame: bad argument");
+  RB_REQUIRE(out_app || out_iou, "assoc_frame: no output requested");
+  RB_REQUIRE(!out_app || (g && det_feat && trk_slot && ldf >= g->d), "assoc_frame: appearance cost needs gallery, features and slots");
+  RB_REQUIRE(!out_app || (flags & REIDB200_ASSOC_NO_GATE) || trk_SI, "assoc_frame: gate needs trk_SI");
+  RB_REQUIRE(iou_mode == REIDB200_IOU_PLAIN || iou_mode == REIDB200_IOU_DIOU, "assoc_frame: bad iou_mode");
+  AssocArgs a;
+  a.gal = g ? g->feats : nullptr; a.gcount = g ? g->count : nullptr; a.ghead = g ? g->head : nullptr;
+  a.budget = g ? g->budget : 0; a.d = g ? g->d : 0;
+  a.det_feat = det_feat; a.ldf = ldf; a.det_tlwh = det_tlwh; a.M = M;
+  a.trk_slot = trk_slot; a.trk_mean = trk_mean; a.trk_SI = trk_SI; a.trk_tsu = trk_tsu; a.T = T;
+  a.mc_lambda = mc_lambda; a.max_dist = max_dist; a.max_iou_dist = max_iou_dist; a.iou_mode = iou_mode; a.flags = flags;
+  a.out_app = out_app; a.out_raw = out_app ? out_raw : nullptr; a.out_iou = out_iou;
+  assoc_frame_kernel<<<T, AS_THREADS, 0, (cudaStream_t)stream>>>(a);
+  RB_LAUNCH_CHECK("assoc_frame_kernel");
+  return REIDB200_OK;
+}
+
+extern "C" int reidb200_iou_matrix(const double* bbox_tlwh, int T, const void* cand_tlwh, int cand_is_f64, int M,
+                                   int iou_mode, double* out, void* stream) {
+  if (T == 0 || M == 0) return REIDB200_OK;
+  RB_REQUIRE(bbox_tlwh && cand_tlwh && out && T > 0 && M > 0, "iou_matrix: bad argument");
+  dim3 grid(ceil_div(M, 128), T);
+  if (cand_is_f64)
+    iou_matrix_kernel<double><<<grid, 128, 0, (cudaStream_t)stream>>>(bbox_tlwh, T, (const double*)cand_tlwh, M, iou_mode, out);
+  else
+    iou_matrix_kernel<float><<<grid, 128, 0, (cudaStream_t)stream>>>(bbox_tlwh, T, (const float*)cand_tlwh, M, iou_mode, out);
+  RB_LAUNCH_CHECK("iou_matrix_kernel");
+  return REIDB200_OK;
+}
+
+extern "C" int reidb200_gating_distance(const double* x4, const double* SI, const double* meas, int T, int M, double* out,
+                                        void* stream) {
+  if (T == 0 || M == 0) return REIDB200_OK;
+  RB_REQUIRE(x4 && SI && meas && out && T > 0 && M > 0, "gating_distance: bad argument");
+  dim3 grid(ceil_div(M, 128), T);
+  gating_kernel<<<grid, 128, 0, (cudaStream_t)stream>>>(x4, SI, meas, T, M, out);
+  RB_LAUNCH_CHECK("gating_kernel");
+  return REIDB200_OK;
+}
+
+extern "C" size_t reidb200_cosine_distance_workspace_bytes(int na, int nb, int d) {
+  if (na <= 0 || nb <= 0 || d <= 0) return 0;
+  CarveSize c;
+  c.take<float>((size_t)na * d);
+  c.take<float>((size_t)nb * d);
+  c.take<char>(packed_bytes(na, d));
+  c.take<char>(packed_bytes(nb, d));
+  return align_up(c.off, 256);
+}
+
+extern "C" int reidb200_cosine_distance(const float* a, int na, int64_t lda, const float* b, int nb, int64_t ldb, int d,
+                                        int normalized, float* out, void* workspace, size_t workspace_bytes,
+                                        void* stream) {
+  if (na == 0 || nb == 0) return REIDB200_OK;
+  RB_REQUIRE(a && b && out && na > 0 && nb > 0 && d > 0, "cosine_distance: bad argument");
+  RB_REQUIRE(workspace && workspace_bytes >= reidb200_cosine_distance_workspace_bytes(na, nb, d),
+             "cosine_distance: workspace too small");
+  cudaStream_t st = (cudaStream_t)stream;
+  Carver c(workspace, workspace_bytes);
+  float* an = c.take<float>((size_t)na * d);
+  float* bn = c.take<float>((size_t)nb * d);
+  char* pa = c.take<char>(packed_bytes(na, d));
+  char* pb = c.take<char>(packed_bytes(nb, d));
+  const float* ax = a; const float* bx = b;
+  int64_t la = lda, lb = ldb;
+  if (!normalized) {
+    normalize_rows_kernel<<<ceil_div(na, 8), 256, 0, st>>>(a, na, lda, d, an);
+    RB_LAUNCH_CHECK("normalize_rows_kernel");
+    normalize_rows_kernel<<<ceil_div(nb, 8), 256, 0, st>>>(b, nb, ldb, d, bn);
+    RB_LAUNCH_CHECK("normalize_rows_kernel");
+    ax = an; bx = bn; la = d; lb = d;
+  }
+  int rc = pack_rows_launch(ax, na, la, d, pa, nullptr, st);
+  if (rc) return rc;
+  rc = pack_rows_launch(bx, nb, lb, d, pb, nullptr, st);
+  if (rc) return rc;
+  rc = gemm_split_launch(pa, nullptr, na, pb, nullptr, nb, d, REIDB200_DIST_DOT, out, nb, st);
+  if (rc) return rc;
+  const size_t n = (size_t)na * nb;
+  one_minus_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(out, n);
+  RB_LAUNCH_CHECK("one_minus_kernel");
+  return REIDB200_OK;
+}

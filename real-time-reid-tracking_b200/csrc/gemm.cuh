@@ -1,0 +1,24 @@
+// Internal interface of the split-bf16 tensor-core GEMM (gemm.cu), shared by distmat / knn /
+// jaccard / association.
+#pragma once
+#include "common.cuh"
+
+namespace reidb200 {
+
+// K (feature dimension) rounded up to the 64-element k-block of the GEMM.
+inline int padded_dim(int d) { return (d + 63) / 64 * 64; }
+// bytes of the packed hi|lo bf16 planes of `rows` rows
+inline size_t packed_bytes(int rows, int d) { return (size_t)rows * 2 * padded_dim(d) * sizeof(__nv_bfloat16); }
+
+// f32[rows,d] -> bf16 [rows, 2*dp] (hi plane then lo plane per row) + squared norms (may be null).
+int pack_rows_launch(const float* x, int rows, int64_t ldx, int d, void* packed, float* sqnorm, cudaStream_t st);
+
+// out[m,n] = epilogue(kind, A.B^T, xx, yy) with A,B packed operands.  xx/yy may be null for DOT.
+int gemm_split_launch(const void* packedA, const float* xx, int m, const void* packedB, const float* yy, int n, int d,
+                      int kind, float* out, int64_t ldo, cudaStream_t st);
+
+// row-wise exact top-k (topk.cu); out_i is i64 when idx64 else i32; ids = cand_i[col] or col + index_base
+int topk_rows_launch(const float* vals, int rows, int cols, int64_t ldv, const int64_t* cand_i, int k, int descending,
+                     int64_t index_base, float* out_d, void* out_i, int idx64, cudaStream_t st);
+
+}  // namespace reidb200

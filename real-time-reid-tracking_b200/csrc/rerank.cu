@@ -1,0 +1,529 @@
+// (3) k-reciprocal re-ranking: reid/faiss_utils.py:142-244 (k_reciprocal_neigh,
+// compute_jaccard_distance) restated with a SPARSE V (the reference's dense N x N V, V_qe and
+// inverted-index scans become ELL rows of at most k1 + k1*(k1/2+1) and k2 times that many entries).
+//
+//   D2  initial_rank = top-k1 of the squared-L2 matrix (tensor-core GEMM + row select)
+//   D3  R(i,k1), R(i,k1/2)                                    krecip_kernel       (warp / row)
+//   D4  local expansion (2/3 rule), unique, softmax weights   expand_v_kernel     (CTA / row)
+//   D5  query expansion: mean of the k2 nearest rows          qexpand_kernel      (CTA / row)
+//   D6  inverted index (CSR by column)                        inv_* kernels
+//   D7  Jaccard: min-sum over shared columns, 1 - t/(2-t)     jaccard_rows_kernel (CTA / output row,
+//       dense accumulator staged in shared memory, coalesced dense row written once)
+//   D8  optional lambda blend with the Euclidean distance (north_star; not in the reference)
+#include "gemm.cuh"
+
+namespace reidb200 {
+
+// ------------------------------------------------------------------------------------ D3
+// out_idx[i, 0..cnt) = forward neighbours c = rank[i,f], f < kc, with i in rank[c, 0..kc)
+// (kc = min(k+1, k1_cols): the reference slices [:k+1] of a k1-column table).
+__global__ void __launch_bounds__(256)
+krecip_kernel(const int32_t* __restrict__ rank, int N, int k1_cols, int kc, int out_w, int32_t* __restrict__ out_idx,
+              int32_t* __restrict__ out_cnt) {
+  const int i = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (i >= N) return;
+  int cnt = 0;
+  for (int f0 = 0; f0 < kc; f0 += 32) {
+    const int f = f0 + lane;
+    bool keep = false;
+    int c = -1;
+    if (f < kc) {
+      c = rank[(size_t)i * k1_cols + f];
+      if (c >= 0 && c < N) {
+        const int32_t* b = rank + (size_t)c * k1_cols;
+        for (int t = 0; t < kc; ++t) keep |= (b[t] == i);
+      }
+    }
+    const uint32_t ballot = __ballot_sync(0xffffffffu, keep);
+    if (keep) out_idx[(size_t)i * out_w + cnt + __popc(ballot & ((1u << lane) - 1))] = c;
+    cnt += __popc(ballot);
+  }
+  for (int t = cnt + lane; t < out_w; t += 32) out_idx[(size_t)i * out_w + t] = -1;
+  if (lane == 0) out_cnt[i] = cnt;
+}
+
+// ------------------------------------------------------------------------------------ D4
+constexpr int EXP_THREADS = 128;
+
+// exclusive scan of flags[0..n) in shared memory by one CTA; returns the total.  n <= 8192.
+__device__ int block_exclusive_scan(int* data, int n, int* warp_tot) {
+  const int tid = threadIdx.x, nthr = blockDim.x, lane = tid & 31, warp = tid >> 5;
+  const int per = (n + nthr - 1) / nthr;
+  const int b = tid * per, e = min(n, b + per);
+  int s = 0;
+  for (int t = b; t < e; ++t) s += data[t];
+  int incl = s;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const int v = __shfl_up_sync(0xffffffffu, incl, o);
+    if (lane >= o) incl += v;
+  }
+  if (lane == 31) warp_tot[warp] = incl;
+  __syncthreads();
+  int before = 0, total = 0;
+  for (int w = 0; w < nthr / 32; ++w) { if (w < warp) before += warp_tot[w]; total += warp_tot[w]; }
+  int run = before + incl - s;
+  for (int t = b; t < e; ++t) { const int v = data[t]; data[t] = run; run += v; }
+  __syncthreads();
+  return total;
+}
+
+// One CTA per row i.  Dynamic smem: L[cap] S[cap] flag[cap] (ints) + val[cap] (floats).
+__global__ void __launch_bounds__(EXP_THREADS)
+expand_v_kernel(const int32_t* __restrict__ rfull, const int32_t* __restrict__ rfull_cnt, int wf,
+                const int32_t* __restrict__ rhalf, const int32_t* __restrict__ rhalf_cnt, int wh,
+                const float* __restrict__ sql2, int64_t lds, const float* __restrict__ sqnorm, int N, int cap,
+                int use_f16, int32_t* __restrict__ vcols, float* __restrict__ vvals, int32_t* __restrict__ vcnt) {
+  extern __shared__ int sm_i[];
+  int* L = sm_i;
+  int* S = L + cap;
+  int* flag = S + cap;
+  float* val = reinterpret_cast<float*>(flag + cap);
+  __shared__ int s_off[129];
+  __shared__ int warp_tot[EXP_THREADS / 32];
+  __shared__ float s_red[EXP_THREADS / 32];
+
+  const int i = blockIdx.x;
+  const int tid = threadIdx.x;
+  const int nb = rfull_cnt[i];
+  const int32_t* base = rfull + (size_t)i * wf;
+
+  // 2/3 rule against the UNEXPANDED R(i,k1) (faiss_utils.py:192-197)
+  for (int t = tid; t < nb; t += EXP_THREADS) {
+    const int c = base[t];
+    const int nc = rhalf_cnt[c];
+    const int32_t* rc = rhalf + (size_t)c * wh;
+    int inter = 0;
+    for (int a = 0; a < nc; ++a) {
+      const int x = rc[a];
+      for (int b = 0; b < nb; ++b) inter += (base[b] == x);
+    }
+    s_off[t] = ((double)inter > (2.0 / 3.0) * (double)nc) ? nc : 0;
+  }
+  __syncthreads();
+  if (tid == 0) {
+    int run = nb;
+    for (int t = 0; t < nb; ++t) { const int v = s_off[t]; s_off[t] = run; run += v; }
+    s_off[nb] = run;
+  }
+  __syncthreads();
+  const int n = s_off[nb];
+  for (int t = tid; t < nb; t += EXP_THREADS) L[t] = base[t];
+  for (int t = 0; t < nb; ++t) {
+    const int o = s_off[t], len = s_off[t + 1] - o;
+    const int32_t* rc = rhalf + (size_t)base[t] * wh;
+    for (int a = tid; a < len; a += EXP_THREADS) L[o + a] = rc[a];
+  }
+  __syncthreads();
+  // np.unique: sort ascending, drop duplicates (rank sort; n <= cap is small)
+  for (int e = tid; e < n; e += EXP_THREADS) {
+    const int x = L[e];
+    int r = 0, dup = 0;
+    for (int o = 0; o < n; ++o) {
+      const int y = L[o];
+      r += (y < x) || (y == x && o < e);
+      dup |= (y == x && o < e);
+    }
+    S[r] = x;
+    flag[r] = dup ? 0 : 1;
+  }
+  __syncthreads();
+  const int nu = block_exclusive_scan(flag, n, warp_tot);  // flag[r] -> output slot of S[r]
+  // S[r] is unique iff it differs from S[r-1]
+  float lmax = -INFINITY;
+  const float xi = sqnorm[i];
+  for (int r = tid; r < n; r += EXP_THREADS) {
+    const int c = S[r];
+    if (r == 0 || S[r - 1] != c) {
+      // dist = 2 - 2 x_i.x_c (faiss_utils.py:201-204), with x_i.x_c = (|x_i|^2 + |x_c|^2 - sql2)/2
+      const float dot = 0.5f * ((xi + sqnorm[c]) - sql2[(size_t)i * lds + c]);
+      const float nd = -(2.0f - 2.0f * dot);
+      val[flag[r]] = nd;
+      L[flag[r]] = c;
+      lmax = fmaxf(lmax, nd);
+    }
+  }
+  // softmax over the nu entries
+  lmax = fmaxf(lmax, __shfl_xor_sync(0xffffffffu, lmax, 16));
+  lmax = fmaxf(lmax, __shfl_xor_sync(0xffffffffu, lmax, 8));
+  lmax = fmaxf(lmax, __shfl_xor_sync(0xffffffffu, lmax, 4));
+  lmax = fmaxf(lmax, __shfl_xor_sync(0xffffffffu, lmax, 2));
+  lmax = fmaxf(lmax, __shfl_xor_sync(0xffffffffu, lmax, 1));
+  if ((tid & 31) == 0) s_red[tid >> 5] = lmax;
+  __syncthreads();
+  float gmax = s_red[0];
+  for (int w = 1; w < EXP_THREADS / 32; ++w) gmax = fmaxf(gmax, s_red[w]);
+  __syncthreads();
+  float lsum = 0.f;
+  for (int u = tid; u < nu; u += EXP_THREADS) {
+    const float e = expf(val[u] - gmax);
+    val[u] = e;
+    lsum += e;
+  }
+  lsum = warp_sum(lsum);
+  if ((tid & 31) == 0) s_red[tid >> 5] = lsum;
+  __syncthreads();
+  float gsum = 0.f;
+  for (int w = 0; w < EXP_THREADS / 32; ++w) gsum += s_red[w];
+  for (int u = tid; u < nu; u += EXP_THREADS) {
+    float v = __fdiv_rn(val[u], gsum);
+    if (use_f16) v = __half2float(__float2half_rn(v));
+    vcols[(size_t)i * cap + u] = L[u];
+    vvals[(size_t)i * cap + u] = v;
+  }
+  if (tid == 0) vcnt[i] = nu;
+}
+
+// ------------------------------------------------------------------------------------ D5
+// V_qe[i] = mean(V[rank[i,:k2]], axis=0) (faiss_utils.py:209-214): merge of k2 sorted sparse rows.
+// Sums run in neighbour order j = 0..k2-1 like the reference's row-by-row reduction (zeros are exact
+// no-ops), then one fp32 division by k2.  Dynamic smem: mcol[cap2] head[cap2] (ints), mval[cap2].
+constexpr int QE_THREADS = 128;
+constexpr int QE_MAX_K2 = 32;
+
+__global__ void __launch_bounds__(QE_THREADS)
+qexpand_kernel(const int32_t* __restrict__ rank, int k1_cols, int k2, const int32_t* __restrict__ vcols,
+               const float* __restrict__ vvals, const int32_t* __restrict__ vcnt, int cap1, int cap2, int use_f16,
+               int32_t* __restrict__ qcols, float* __restrict__ qvals, int32_t* __restrict__ qcnt) {
+  extern __shared__ int sm_i[];
+  int* mcol = sm_i;
+  int* head = mcol + cap2;
+  float* mval = reinterpret_cast<float*>(head + cap2);
+  __shared__ int s_row[QE_MAX_K2], s_len[QE_MAX_K2], s_off[QE_MAX_K2 + 1];
+  __shared__ int warp_tot[QE_THREADS / 32];
+
+  const int i = blockIdx.x, tid = threadIdx.x;
+  if (tid < k2) {
+    const int r = rank[(size_t)i * k1_cols + tid];
+    s_row[tid] = r;
+    s_len[tid] = vcnt[r];
+  }
+  __syncthreads();
+  if (tid == 0) {
+    int run = 0;
+    for (int j = 0; j < k2; ++j) { s_off[j] = run; run += s_len[j]; }
+    s_off[k2] = run;
+  }
+  __syncthreads();
+  const int n = s_off[k2];
+  // merged position of element (j,t): #elements with smaller column, or equal column and smaller j
+  for (int e = tid; e < n; e += QE_THREADS) {
+    int j = 0;
+    while (e >= s_off[j + 1]) ++j;
+    const int t = e - s_off[j];
+    const int32_t* mine = vcols + (size_t)s_row[j] * cap1;
+    const int c = mine[t];
+    int pos = t;
+    for (int o = 0; o < k2; ++o) {
+      if (o == j) continue;
+      const int32_t* oc = vcols + (size_t)s_row[o] * cap1;
+      int lo = 0, hi = s_len[o];
+      if (o < j) {  // upper bound: entries <= c
+        while (lo < hi) { const int mid = (lo + hi) >> 1; if (oc[mid] <= c) lo = mid + 1; else hi = mid; }
+      } else {      // lower bound: entries < c
+        while (lo < hi) { const int mid = (lo + hi) >> 1; if (oc[mid] < c) lo = mid + 1; else hi = mid; }
+      }
+      pos += lo;
+    }
+    mcol[pos] = c;
+    mval[pos] = vvals[(size_t)s_row[j] * cap1 + t];
+  }
+  __syncthreads();
+  for (int p = tid; p < n; p += QE_THREADS) head[p] = (p == 0 || mcol[p - 1] != mcol[p]) ? 1 : 0;
+  __syncthreads();
+  // keep the head flags readable after the scan: stash them in the sign of mcol? no -- recompute below
+  const int nu = block_exclusive_scan(head, n, warp_tot);
+  for (int p = tid; p < n; p += QE_THREADS) {
+    if (p == 0 || mcol[p - 1] != mcol[p]) {
+      const int c = mcol[p];
+      float s = mval[p];
+      for (int t = p + 1; t < n && mcol[t] == c; ++t) s = __fadd_rn(s, mval[t]);
+      float v = __fdiv_rn(s, (float)k2);
+      if (use_f16) v = __half2float(__float2half_rn(v));
+      const int slot = head[p];
+      qcols[(size_t)i * cap2 + slot] = c;
+      qvals[(size_t)i * cap2 + slot] = v;
+    }
+  }
+  if (tid == 0) qcnt[i] = nu;
+}
+
+// ------------------------------------------------------------------------------------ D6
+__global__ void inv_count_kernel(const int32_t* __restrict__ cols, const float* __restrict__ vals,
+                                 const int32_t* __restrict__ cnt, int N, int cap, int32_t* __restrict__ colcnt) {
+  const int i = blockIdx.x;
+  const int n = cnt[i];
+  for (int t = threadIdx.x; t < n; t += blockDim.x)
+    if (vals[(size_t)i * cap + t] != 0.f) atomicAdd(colcnt + cols[(size_t)i * cap + t], 1);
+}
+
+// colptr[0..N] = exclusive scan of colcnt; cursor = copy of colptr.  Single CTA.
+__global__ void __launch_bounds__(1024)
+inv_scan_kernel(const int32_t* __restrict__ colcnt, int N, int32_t* __restrict__ colptr, int32_t* __restrict__ cursor) {
+  __shared__ int wsum[32];
+  __shared__ int carry_s;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  if (tid == 0) carry_s = 0;
+  __syncthreads();
+  for (int r0 = 0; r0 < N; r0 += 1024) {
+    const int r = r0 + tid;
+    const int x = r < N ? colcnt[r] : 0;
+    int v = x;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int nb = __shfl_up_sync(0xffffffffu, v, o);
+      if (lane >= o) v += nb;
+    }
+    if (lane == 31) wsum[warp] = v;
+    __syncthreads();
+    int before = carry_s;
+    for (int w = 0; w < warp; ++w) before += wsum[w];
+    if (r < N) { colptr[r] = before + v - x; cursor[r] = before + v - x; }
+    __syncthreads();
+    if (tid == 1023) carry_s = before + v;
+    __syncthreads();
+  }
+  if (tid == 0) colptr[N] = carry_s;
+}
+
+__global__ void inv_fill_kernel(const int32_t* __restrict__ cols, const float* __restrict__ vals,
+                                const int32_t* __restrict__ cnt, int N, int cap, int32_t* __restrict__ cursor,
+                                int32_t* __restrict__ inv_row, float* __restrict__ inv_val) {
+  const int i = blockIdx.x;
+  const int n = cnt[i];
+  for (int t = threadIdx.x; t < n; t += blockDim.x) {
+    const float v = vals[(size_t)i * cap + t];
+    if (v != 0.f) {
+      const int p = atomicAdd(cursor + cols[(size_t)i * cap + t], 1);
+      inv_row[p] = i;
+      inv_val[p] = v;
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------ D7 (+ D8)
+// One CTA per output row i: acc[r] = sum_j min(V[i,j], V[r,j]) over the inverted lists of the
+// non-zeros of row i (faiss_utils.py:223-234), staged in shared memory (N floats), then the whole
+// dense row 1 - t/(2-t) (clamped at 0, :236-240) is written once, coalesced.
+constexpr int JR_THREADS = 512;
+
+__global__ void __launch_bounds__(JR_THREADS)
+jaccard_rows_kernel(const int32_t* __restrict__ qcols, const float* __restrict__ qvals, const int32_t* __restrict__ qcnt,
+                    int cap, const int32_t* __restrict__ colptr, const int32_t* __restrict__ inv_row,
+                    const float* __restrict__ inv_val, int N, int row0, int col0, int ncols, float lambda_value,
+                    const float* __restrict__ sql2, int64_t lds, int use_f16, void* __restrict__ out, int64_t ldo) {
+  extern __shared__ float acc[];
+  const int i = row0 + blockIdx.x;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  for (int r = tid; r < N; r += JR_THREADS) acc[r] = 0.f;
+  __syncthreads();
+  const int n = qcnt[i];
+  for (int t = warp; t < n; t += JR_THREADS / 32) {
+    const float v = qvals[(size_t)i * cap + t];
+    if (v == 0.f) continue;
+    const int j = qcols[(size_t)i * cap + t];
+    const int b = colptr[j], e = colptr[j + 1];
+    for (int p = b + lane; p < e; p += 32) atomicAdd(acc + inv_row[p], fminf(v, inv_val[p]));
+  }
+  __syncthreads();
+  const float one_m_l = 1.0f - lambda_value;
+  for (int c = tid; c < ncols; c += JR_THREADS) {
+    float t = acc[col0 + c];
+    if (use_f16) t = __half2float(__float2half_rn(t));
+    float jd = __fsub_rn(1.0f, __fdiv_rn(t, __fsub_rn(2.0f, t)));
+    if (jd < 0.f) jd = 0.f;
+    if (lambda_value > 0.f) {
+      const float orig = sqrtf(fmaxf(sql2[(size_t)i * lds + col0 + c], 1e-12f));
+      jd = __fadd_rn(__fmul_rn(jd, one_m_l), __fmul_rn(orig, lambda_value));
+    }
+    if (use_f16) reinterpret_cast<__half*>(out)[(size_t)blockIdx.x * ldo + c] = __float2half_rn(jd);
+    else __stcs(reinterpret_cast<float*>(out) + (size_t)blockIdx.x * ldo + c, jd);
+  }
+}
+
+// ------------------------------------------------------------------------------------ host side
+struct RerankDims {
+  int half, wh, cap1, cap2;
+  int64_t lds;
+};
+
+static RerankDims rerank_dims(int N, int k1, int k2) {
+  RerankDims d;
+  d.half = (int)rint(k1 / 2.0);  // np.around: round half to even (faiss_utils.py:187)
+  d.wh = d.half + 1 < k1 ? d.half + 1 : k1;
+  d.cap1 = k1 + k1 * d.wh;
+  d.cap2 = k2 > 1 ? k2 * d.cap1 : d.cap1;
+  d.lds = (int64_t)align_up((size_t)N, 4);
+  return d;
+}
+
+struct SparseWs {
+  int32_t *rfull, *rfull_cnt, *rhalf, *rhalf_cnt, *v1cols, *v1cnt, *v2cols, *v2cnt, *colcnt, *colptr, *cursor, *inv_row;
+  float *v1vals, *v2vals, *inv_val;
+};
+
+template <class C>
+static void carve_sparse(C& c, int N, int k1, int k2, const RerankDims& d, SparseWs* w) {
+  SparseWs t;
+  t.rfull = c.template take<int32_t>((size_t)N * k1);
+  t.rfull_cnt = c.template take<int32_t>(N);
+  t.rhalf = c.template take<int32_t>((size_t)N * d.wh);
+  t.rhalf_cnt = c.template take<int32_t>(N);
+  t.v1cols = c.template take<int32_t>((size_t)N * d.cap1);
+  t.v1vals = c.template take<float>((size_t)N * d.cap1);
+  t.v1cnt = c.template take<int32_t>(N);
+  if (k2 > 1) {
+    t.v2cols = c.template take<int32_t>((size_t)N * d.cap2);
+    t.v2vals = c.template take<float>((size_t)N * d.cap2);
+    t.v2cnt = c.template take<int32_t>(N);
+  } else {
+    t.v2cols = t.v1cols; t.v2vals = t.v1vals; t.v2cnt = t.v1cnt;
+  }
+  t.colcnt = c.template take<int32_t>(N + 1);
+  t.colptr = c.template take<int32_t>(N + 1);
+  t.cursor = c.template take<int32_t>(N + 1);
+  t.inv_row = c.template take<int32_t>((size_t)N * d.cap2);
+  t.inv_val = c.template take<float>((size_t)N * d.cap2);
+  if (w) *w = t;
+}
+
+struct NullCarver {  // size-only twin of Carver
+  size_t off = 0;
+  template <typename T>
+  T* take(size_t count) { off = align_up(off, 256); off += count * sizeof(T); return nullptr; }
+};
+
+static int rerank_check(int N, int k1, int k2, const RerankDims& d) {
+  RB_REQUIRE(k1 >= 1 && k1 <= 128 && k1 < N, "jaccard: need 1 <= k1 <= 128 and k1 < N (k1=%d, N=%d)", k1, N);
+  RB_REQUIRE(k2 >= 1 && k2 <= QE_MAX_K2 && k2 <= k1, "jaccard: need 1 <= k2 <= min(k1,%d) (k2=%d)", QE_MAX_K2, k2);
+  if (d.cap1 > 4096 || d.cap2 > 8192 || (size_t)N * 4 > 220 * 1024) {
+    set_error("jaccard: size outside this build's limits (N=%d <= 56320, cap1=%d <= 4096, cap2=%d <= 8192)", N, d.cap1, d.cap2);
+    return REIDB200_ELIMIT;
+  }
+  return REIDB200_OK;
+}
+
+static int jaccard_sparse_stages(const int32_t* rank, const float* sql2, int64_t lds, const float* sqnorm, int N, int k1,
+                                 int k2, int use_f16, float lambda_value, int row0, int nrows, int col0, int ncols,
+                                 void* out, int64_t ldo, const RerankDims& d, const SparseWs& w, cudaStream_t st) {
+  static bool attr = false;
+  if (!attr) {
+    RB_CUDA(cudaFuncSetAttribute(expand_v_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 4096 * 16));
+    RB_CUDA(cudaFuncSetAttribute(qexpand_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 8192 * 12));
+    RB_CUDA(cudaFuncSetAttribute(jaccard_rows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
+    attr = true;
+  }
+  const int wpb = 8;
+  krecip_kernel<<<ceil_div(N, wpb), wpb * 32, 0, st>>>(rank, N, k1, k1, k1, w.rfull, w.rfull_cnt);
+  RB_LAUNCH_CHECK("krecip_kernel(k1)");
+  krecip_kernel<<<ceil_div(N, wpb), wpb * 32, 0, st>>>(rank, N, k1, d.wh, d.wh, w.rhalf, w.rhalf_cnt);
+  RB_LAUNCH_CHECK("krecip_kernel(k1/2)");
+  expand_v_kernel<<<N, EXP_THREADS, (size_t)d.cap1 * 16, st>>>(w.rfull, w.rfull_cnt, k1, w.rhalf, w.rhalf_cnt, d.wh, sql2,
+                                                                lds, sqnorm, N, d.cap1, use_f16, w.v1cols, w.v1vals,
+                                                                w.v1cnt);
+  RB_LAUNCH_CHECK("expand_v_kernel");
+  if (k2 > 1) {
+    qexpand_kernel<<<N, QE_THREADS, (size_t)d.cap2 * 12, st>>>(rank, k1, k2, w.v1cols, w.v1vals, w.v1cnt, d.cap1, d.cap2,
+                                                               use_f16, w.v2cols, w.v2vals, w.v2cnt);
+    RB_LAUNCH_CHECK("qexpand_kernel");
+  }
+  RB_CUDA(cudaMemsetAsync(w.colcnt, 0, (size_t)(N + 1) * sizeof(int32_t), st));
+  inv_count_kernel<<<N, 128, 0, st>>>(w.v2cols, w.v2vals, w.v2cnt, N, d.cap2, w.colcnt);
+  RB_LAUNCH_CHECK("inv_count_kernel");
+  inv_scan_kernel<<<1, 1024, 0, st>>>(w.colcnt, N, w.colptr, w.cursor);
+  RB_LAUNCH_CHECK("inv_scan_kernel");
+  inv_fill_kernel<<<N, 128, 0, st>>>(w.v2cols, w.v2vals, w.v2cnt, N, d.cap2, w.cursor, w.inv_row, w.inv_val);
+  RB_LAUNCH_CHECK("inv_fill_kernel");
+  jaccard_rows_kernel<<<nrows, JR_THREADS, (size_t)N * sizeof(float), st>>>(
+      w.v2cols, w.v2vals, w.v2cnt, d.cap2, w.colptr, w.inv_row, w.inv_val, N, row0, col0, ncols, lambda_value, sql2, lds,
+      use_f16, out, ldo);
+  RB_LAUNCH_CHECK("jaccard_rows_kernel");
+  return REIDB200_OK;
+}
+
+}  // namespace reidb200
+
+using namespace reidb200;
+
+extern "C" size_t reidb200_jaccard_workspace_bytes(int N, int d, int k1, int k2) {
+  if (N <= 0 || d <= 0 || k1 <= 0 || k2 <= 0) return 0;
+  const RerankDims rd = rerank_dims(N, k1, k2);
+  NullCarver c;
+  c.take<char>(packed_bytes(N, d));
+  c.take<float>(N);
+  c.take<float>((size_t)N * rd.lds);
+  c.take<float>((size_t)N * k1);
+  c.take<int32_t>((size_t)N * k1);
+  carve_sparse(c, N, k1, k2, rd, nullptr);
+  return align_up(c.off, 256);
+}
+
+static int region_check(int N, int row0, int nrows, int col0, int ncols, int64_t ldo) {
+  RB_REQUIRE(row0 >= 0 && nrows >= 0 && row0 + nrows <= N && col0 >= 0 && ncols >= 0 && col0 + ncols <= N,
+             "jaccard: output region [%d,+%d) x [%d,+%d) outside N=%d", row0, nrows, col0, ncols, N);
+  RB_REQUIRE(ldo >= ncols, "jaccard: ldo too small");
+  return REIDB200_OK;
+}
+
+extern "C" int reidb200_jaccard_from_rank(const int32_t* rank, const float* sql2, int64_t lds, const float* sqnorm, int N,
+                                          int k1, int k2, int use_float16, float lambda_value, int row0, int nrows,
+                                          int col0, int ncols, void* out, int64_t ldo, void* workspace,
+                                          size_t workspace_bytes, void* stream) {
+  RB_REQUIRE(rank && sql2 && sqnorm && out && N > 0 && lds >= N, "jaccard_from_rank: bad argument");
+  const RerankDims rd = rerank_dims(N, k1, k2);
+  int rc = rerank_check(N, k1, k2, rd);
+  if (rc) return rc;
+  rc = region_check(N, row0, nrows, col0, ncols, ldo);
+  if (rc) return rc;
+  if (nrows == 0 || ncols == 0) return REIDB200_OK;
+  NullCarver nc;
+  carve_sparse(nc, N, k1, k2, rd, nullptr);
+  RB_REQUIRE(workspace && workspace_bytes >= nc.off, "jaccard_from_rank: workspace too small");
+  Carver c(workspace, workspace_bytes);
+  SparseWs w;
+  carve_sparse(c, N, k1, k2, rd, &w);
+  return jaccard_sparse_stages(rank, sql2, lds, sqnorm, N, k1, k2, use_float16, lambda_value, row0, nrows, col0, ncols,
+                               out, ldo, rd, w, (cudaStream_t)stream);
+}
+
+extern "C" int reidb200_jaccard(const float* feats, int N, int64_t ldf, int d, int k1, int k2, int use_float16,
+                                float lambda_value, int row0, int nrows, int col0, int ncols, void* out, int64_t ldo,
+                                int32_t* rank_out, void* workspace, size_t workspace_bytes, void* stream) {
+  RB_REQUIRE(feats && out && N > 0 && d > 0 && ldf >= d, "jaccard: bad argument");
+  const RerankDims rd = rerank_dims(N, k1, k2);
+  int rc = rerank_check(N, k1, k2, rd);
+  if (rc) return rc;
+  rc = region_check(N, row0, nrows, col0, ncols, ldo);
+  if (rc) return rc;
+  RB_REQUIRE(workspace && workspace_bytes >= reidb200_jaccard_workspace_bytes(N, d, k1, k2), "jaccard: workspace too small");
+  RB_REQUIRE((reinterpret_cast<uintptr_t>(workspace) & 255) == 0, "jaccard: workspace must be 256-byte aligned");
+  cudaStream_t st = (cudaStream_t)stream;
+  Carver c(workspace, workspace_bytes);
+  char* packed = c.take<char>(packed_bytes(N, d));
+  float* sqn = c.take<float>(N);
+  float* sql2 = c.take<float>((size_t)N * rd.lds);
+  float* rank_d = c.take<float>((size_t)N * k1);
+  int32_t* rank_i = c.take<int32_t>((size_t)N * k1);
+  SparseWs w;
+  carve_sparse(c, N, k1, k2, rd, &w);
+  rc = pack_rows_launch(feats, N, ldf, d, packed, sqn, st);
+  if (rc) return rc;
+  rc = gemm_split_launch(packed, sqn, N, packed, sqn, N, d, REIDB200_DIST_SQL2, sql2, rd.lds, st);
+  if (rc) return rc;
+  rc = topk_rows_launch(sql2, N, N, rd.lds, nullptr, k1, 0, 0, rank_d, rank_i, 0, st);
+  if (rc) return rc;
+  if (rank_out) RB_CUDA(cudaMemcpyAsync(rank_out, rank_i, (size_t)N * k1 * sizeof(int32_t), cudaMemcpyDeviceToDevice, st));
+  if (nrows == 0 || ncols == 0) return REIDB200_OK;
+  return jaccard_sparse_stages(rank_i, sql2, rd.lds, sqn, N, k1, k2, use_float16, lambda_value, row0, nrows, col0, ncols,
+                               out, ldo, rd, w, st);
+}
+
+extern "C" int reidb200_k_reciprocal(const int32_t* rank, int N, int k1_cols, int k, int32_t* out_idx, int32_t* out_cnt,
+                                     void* stream) {
+  RB_REQUIRE(rank && out_idx && out_cnt && N > 0 && k1_cols > 0 && k > 0, "k_reciprocal: bad argument");
+  const int kc = k + 1 < k1_cols ? k + 1 : k1_cols;
+  krecip_kernel<<<ceil_div(N, 8), 256, 0, (cudaStream_t)stream>>>(rank, N, k1_cols, kc, k + 1, out_idx, out_cnt);
+  RB_LAUNCH_CHECK("krecip_kernel");
+  return REIDB200_OK;
+}

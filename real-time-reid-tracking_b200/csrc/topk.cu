@@ -1,0 +1,303 @@
+// (2b) exact row-wise top-k selection and the brute-force k-NN built on it
+// (reid/faiss_utils.py:30-139: faiss bfKnn / GpuIndexFlatL2 / IndexFlatL2 / IndexShards stand-in).
+//
+// Selection, one CTA per row, no sorting of the row and no shared-memory atomics in the hot loop:
+//   pass 1  every thread keeps the minimum key of its strided sub-stream(s): G group minima
+//           (G = 256 or 1024 >= k).  The k-th smallest group minimum t0 is an upper bound of the k-th
+//           smallest element (k distinct elements are <= t0) and is nearly tight because k << G.
+//   pass 2  re-read the row (L1/L2 hit) and append every element with key <= t0 to a small candidate
+//           list (warp-aggregated append).
+//   finish  rank-sort the candidates by (key, id) and emit the first k.
+// If the candidate list overflows (heavy ties / adversarial order) the CTA falls back to an exact
+// bisection on the 32-bit ordered key.  Ties are broken by the lower id, like a stable argsort.
+#include "gemm.cuh"
+
+namespace reidb200 {
+
+constexpr int TOPK_THREADS = 256;
+constexpr int TOPK_CAP = 4096;   // candidate capacity (key + id in shared memory)
+constexpr int TOPK_MAX_K = 1024;
+
+__device__ __forceinline__ uint32_t sel_key(float v, int descending) {
+  const uint32_t u = float_to_ordered(v);
+  return descending ? ~u : u;
+}
+__device__ __forceinline__ float sel_val(uint32_t key, int descending) {
+  uint32_t u = descending ? ~key : key;
+  u = (u & 0x80000000u) ? (u & 0x7fffffffu) : ~u;
+  return __uint_as_float(u);
+}
+
+__device__ __forceinline__ int block_sum_int(int v, int* red) {
+  v = warp_sum_i(v);
+  __syncthreads();
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = v;
+  __syncthreads();
+  int t = 0;
+#pragma unroll
+  for (int w = 0; w < TOPK_THREADS / 32; ++w) t += red[w];
+  return t;
+}
+
+__global__ void __launch_bounds__(TOPK_THREADS)
+topk_rows_kernel(const float* __restrict__ vals, int cols, int64_t ldv, const int64_t* __restrict__ cand_i, int k,
+                 int descending, int64_t index_base, float* __restrict__ out_d, void* __restrict__ out_i, int idx64) {
+  __shared__ uint32_t ckey[TOPK_CAP];
+  __shared__ int32_t ccol[TOPK_CAP];
+  __shared__ uint32_t gmin[1024];
+  __shared__ int red[TOPK_THREADS / 32];
+  __shared__ uint32_t s_t0;
+  __shared__ int s_count;
+
+  const int row = blockIdx.x;
+  const float* v = vals + (size_t)row * ldv;
+  const int64_t* ci = cand_i ? cand_i + (size_t)row * cols : nullptr;
+  const int tid = threadIdx.x;
+  const int kk = min(k, cols);
+  float* od = out_d + (size_t)row * k;
+
+  // ---- pass 1: group minima
+  const int groups = (kk <= 256) ? 256 : 1024;
+  const int per_thread = groups / TOPK_THREADS;  // 1 or 4
+  uint32_t m[4] = {0xffffffffu, 0xffffffffu, 0xffffffffu, 0xffffffffu};
+  if (per_thread == 1) {
+    for (int c = tid; c < cols; c += TOPK_THREADS) m[0] = min(m[0], sel_key(__ldg(v + c), descending));
+  } else {
+    for (int c0 = 0; c0 < cols; c0 += 4 * TOPK_THREADS) {
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int c = c0 + j * TOPK_THREADS + tid;
+        if (c < cols) m[j] = min(m[j], sel_key(__ldg(v + c), descending));
+      }
+    }
+  }
+  for (int j = 0; j < per_thread; ++j) gmin[j * TOPK_THREADS + tid] = m[j];
+  if (tid == 0) { s_count = 0; s_t0 = 0xffffffffu; }
+  __syncthreads();
+  // k-th smallest group minimum (rank by (key, group index); exactly one group gets rank kk-1)
+  if (kk > 0) {
+    for (int j = 0; j < per_thread; ++j) {
+      const int g = j * TOPK_THREADS + tid;
+      const uint32_t mine = m[j];
+      int rank = 0;
+      for (int o = 0; o < groups; ++o) {
+        const uint32_t other = gmin[o];
+        rank += (other < mine) || (other == mine && o < g);
+      }
+      if (rank == kk - 1) s_t0 = mine;
+    }
+  }
+  __syncthreads();
+  uint32_t t0 = s_t0;
+
+  // ---- pass 2: collect candidates <= t0
+  const int lane = tid & 31;
+  for (int c0 = 0; c0 < cols; c0 += TOPK_THREADS) {
+    const int c = c0 + tid;
+    uint32_t key = 0xffffffffu;
+    bool take = false;
+    if (c < cols) {
+      key = sel_key(__ldg(v + c), descending);
+      take = key <= t0;
+    }
+    const uint32_t ballot = __ballot_sync(0xffffffffu, take);
+    if (ballot) {
+      int base = 0;
+      if (lane == 0) base = atomicAdd(&s_count, __popc(ballot));
+      base = __shfl_sync(0xffffffffu, base, 0);
+      if (take) {
+        const int pos = base + __popc(ballot & ((1u << lane) - 1));
+        if (pos < TOPK_CAP) { ckey[pos] = key; ccol[pos] = c; }
+      }
+    }
+  }
+  __syncthreads();
+  int count = s_count;
+
+  if (count > TOPK_CAP) {
+    // ---- fallback: exact k-th key by bisection, then ordered collection
+    uint32_t lo = 0, hi = 0xffffffffu;  // invariant: count(key <= hi) >= kk, count(key <= lo-1) < kk
+    while (lo < hi) {
+      const uint32_t mid = lo + ((hi - lo) >> 1);
+      int cnt = 0;
+      for (int c = tid; c < cols; c += TOPK_THREADS) cnt += sel_key(__ldg(v + c), descending) <= mid;
+      cnt = block_sum_int(cnt, red);
+      if (cnt >= kk) hi = mid; else lo = mid + 1;
+    }
+    t0 = lo;  // the kk-th smallest key
+    __syncthreads();
+    if (tid == 0) s_count = 0;
+    __syncthreads();
+    // strictly smaller keys (fewer than kk of them) in any order
+    for (int c0 = 0; c0 < cols; c0 += TOPK_THREADS) {
+      const int c = c0 + tid;
+      uint32_t key = 0xffffffffu;
+      bool take = false;
+      if (c < cols) { key = sel_key(__ldg(v + c), descending); take = key < t0; }
+      const uint32_t ballot = __ballot_sync(0xffffffffu, take);
+      if (ballot) {
+        int base = 0;
+        if (lane == 0) base = atomicAdd(&s_count, __popc(ballot));
+        base = __shfl_sync(0xffffffffu, base, 0);
+        if (take) { const int pos = base + __popc(ballot & ((1u << lane) - 1)); ckey[pos] = key; ccol[pos] = c; }
+      }
+    }
+    __syncthreads();
+    int have = s_count;
+    // ties == t0 in column order until kk are held (chunk by chunk, ordered prefix over the CTA)
+    for (int c0 = 0; c0 < cols && have < kk; c0 += TOPK_THREADS) {
+      const int c = c0 + tid;
+      const bool take = c < cols && sel_key(__ldg(v + c), descending) == t0;
+      const uint32_t ballot = __ballot_sync(0xffffffffu, take);
+      __syncthreads();
+      if (lane == 0) red[tid >> 5] = __popc(ballot);
+      __syncthreads();
+      int before = 0, total = 0;
+      for (int w = 0; w < TOPK_THREADS / 32; ++w) { if (w < (tid >> 5)) before += red[w]; total += red[w]; }
+      if (take) {
+        const int pos = have + before + __popc(ballot & ((1u << lane) - 1));
+        if (pos < kk) { ckey[pos] = t0; ccol[pos] = c; }
+      }
+      have = min(kk, have + total);
+    }
+    __syncthreads();
+    count = kk;
+  }
+
+  // ---- finish: rank-sort candidates by (key, id) and emit the first kk
+  for (int e = tid; e < count; e += TOPK_THREADS) {
+    const uint32_t key = ckey[e];
+    const int c = ccol[e];
+    const int64_t id = ci ? ci[c] : (int64_t)c;
+    int rank = 0;
+    for (int o = 0; o < count; ++o) {
+      const uint32_t ok = ckey[o];
+      if (ok < key) { ++rank; continue; }
+      if (ok == key && o != e) {
+        const int oc = ccol[o];
+        const int64_t oid = ci ? ci[oc] : (int64_t)oc;
+        rank += (oid < id) || (oid == id && o < e);
+      }
+    }
+    if (rank < kk) {
+      od[rank] = sel_val(key, descending);
+      const int64_t gid = ci ? id : id + index_base;
+      if (idx64) reinterpret_cast<int64_t*>(out_i)[(size_t)row * k + rank] = gid;
+      else reinterpret_cast<int32_t*>(out_i)[(size_t)row * k + rank] = (int32_t)gid;
+    }
+  }
+  // fewer columns than k: pad like faiss (distance = +/-inf, id = -1)
+  for (int e = kk + tid; e < k; e += TOPK_THREADS) {
+    od[e] = descending ? -INFINITY : INFINITY;
+    if (idx64) reinterpret_cast<int64_t*>(out_i)[(size_t)row * k + e] = -1;
+    else reinterpret_cast<int32_t*>(out_i)[(size_t)row * k + e] = -1;
+  }
+}
+
+int topk_rows_launch(const float* vals, int rows, int cols, int64_t ldv, const int64_t* cand_i, int k, int descending,
+                     int64_t index_base, float* out_d, void* out_i, int idx64, cudaStream_t st) {
+  if (rows == 0 || k == 0) return REIDB200_OK;
+  RB_REQUIRE(k > 0 && k <= TOPK_MAX_K, "topk: k=%d outside [1,%d]", k, TOPK_MAX_K);
+  RB_REQUIRE(cols >= 0 && ldv >= cols, "topk: bad cols/ld");
+  topk_rows_kernel<<<rows, TOPK_THREADS, 0, st>>>(vals, cols, ldv, cand_i, k, descending, index_base, out_d, out_i,
+                                                  idx64);
+  RB_LAUNCH_CHECK("topk_rows_kernel");
+  return REIDB200_OK;
+}
+
+// gallery columns per GEMM + select pass: distance block of at most 2^29 floats (2 GiB)
+static int knn_chunk_cols(int nq, int nb) {
+  long long c = (1LL << 29) / (nq > 0 ? nq : 1);
+  c = c / 256 * 256;
+  if (c < 256) c = 256;
+  if (c > nb) c = nb;
+  return (int)c;
+}
+
+}  // namespace reidb200
+
+using namespace reidb200;
+
+extern "C" int reidb200_topk_rows(const float* vals, int rows, int cols, int64_t ldv, const int64_t* cand_i, int k,
+                                  int descending, int64_t index_base, float* out_d, void* out_i, int idx64,
+                                  void* stream) {
+  if (rows == 0) return REIDB200_OK;
+  RB_REQUIRE(vals && out_d && out_i && rows > 0, "topk_rows: bad argument");
+  return topk_rows_launch(vals, rows, cols, ldv, cand_i, k, descending, index_base, out_d, out_i, idx64,
+                          (cudaStream_t)stream);
+}
+
+extern "C" size_t reidb200_knn_workspace_bytes(int nq, int nb, int d, int k) {
+  if (nq <= 0 || nb <= 0 || d <= 0 || k <= 0) return 0;
+  const int chunk = knn_chunk_cols(nq, nb);
+  const int nchunks = ceil_div(nb, chunk);
+  CarveSize c;
+  c.take<char>(packed_bytes(nq, d));
+  c.take<float>(nq);
+  c.take<char>(packed_bytes(nb, d));
+  c.take<float>(nb);
+  c.take<float>((size_t)nq * chunk);
+  if (nchunks > 1) {
+    c.take<float>((size_t)nq * nchunks * k);
+    c.take<int64_t>((size_t)nq * nchunks * k);
+  }
+  return align_up(c.off, 256);
+}
+
+extern "C" int reidb200_knn(const float* xq, int nq, int64_t ldq, const float* xb, int nb, int64_t ldb, int d, int k,
+                            int metric, int64_t index_base, float* out_d, void* out_i, int idx64, void* workspace,
+                            size_t workspace_bytes, void* stream) {
+  if (nq == 0) return REIDB200_OK;
+  RB_REQUIRE(xq && xb && out_d && out_i && nq > 0 && nb > 0 && d > 0, "knn: bad argument nq=%d nb=%d d=%d", nq, nb, d);
+  RB_REQUIRE(k > 0 && k <= TOPK_MAX_K, "knn: k=%d outside [1,%d]", k, TOPK_MAX_K);
+  RB_REQUIRE(metric == REIDB200_DIST_SQL2 || metric == REIDB200_DIST_DOT, "knn: metric must be SQL2 or DOT");
+  RB_REQUIRE(workspace && workspace_bytes >= reidb200_knn_workspace_bytes(nq, nb, d, k), "knn: workspace too small");
+  RB_REQUIRE((reinterpret_cast<uintptr_t>(workspace) & 255) == 0, "knn: workspace must be 256-byte aligned");
+  cudaStream_t st = (cudaStream_t)stream;
+  const int chunk = knn_chunk_cols(nq, nb);
+  const int nchunks = ceil_div(nb, chunk);
+  const int dp = padded_dim(d);
+  const int desc = metric == REIDB200_DIST_DOT;
+  Carver c(workspace, workspace_bytes);
+  char* pq = c.take<char>(packed_bytes(nq, d));
+  float* qq = c.take<float>(nq);
+  char* pb = c.take<char>(packed_bytes(nb, d));
+  float* bb = c.take<float>(nb);
+  float* dist = c.take<float>((size_t)nq * chunk);
+  float* cd = nullptr;
+  int64_t* cid = nullptr;
+  if (nchunks > 1) {
+    cd = c.take<float>((size_t)nq * nchunks * k);
+    cid = c.take<int64_t>((size_t)nq * nchunks * k);
+  }
+  int rc = pack_rows_launch(xq, nq, ldq, d, pq, qq, st);
+  if (rc) return rc;
+  if (xq == xb && nq == nb && ldq == ldb) { pb = pq; bb = qq; }
+  else { rc = pack_rows_launch(xb, nb, ldb, d, pb, bb, st); if (rc) return rc; }
+  for (int ch = 0; ch < nchunks; ++ch) {
+    const int c0 = ch * chunk;
+    const int nc = min(chunk, nb - c0);
+    rc = gemm_split_launch(pq, qq, nq, pb + (size_t)c0 * 2 * dp * sizeof(__nv_bfloat16), bb + c0, nc, d, metric, dist,
+                           chunk, st);
+    if (rc) return rc;
+    if (nchunks == 1) return topk_rows_launch(dist, nq, nc, chunk, nullptr, k, desc, index_base, out_d, out_i, idx64, st);
+    // per-chunk partial result -> slot ch of the candidate table [nq, nchunks*k] (row stride nchunks*k)
+    // written through a strided view: out row stride is k, so select into a compact temp then merge below.
+    rc = topk_rows_launch(dist, nq, nc, chunk, nullptr, k, desc, index_base + c0, cd + (size_t)ch * nq * k,
+                          cid + (size_t)ch * nq * k, 1, st);
+    if (rc) return rc;
+  }
+  // merge: candidate tables are [nchunks][nq][k]; gather per query through a transposing copy
+  // (nchunks*k values per query) and run one more selection with explicit ids.
+  float* md = dist;  // the distance block is free again: reuse as [nq, nchunks*k]
+  int64_t* mi = reinterpret_cast<int64_t*>(dist + (size_t)nq * nchunks * k + 2);
+  mi = reinterpret_cast<int64_t*>((reinterpret_cast<uintptr_t>(mi) + 7) & ~(uintptr_t)7);
+  RB_REQUIRE((size_t)nq * nchunks * k * 12 + 16 <= (size_t)nq * chunk * 4, "knn: merge buffer does not fit (k too large)");
+  for (int ch = 0; ch < nchunks; ++ch) {
+    RB_CUDA(cudaMemcpy2DAsync(md + (size_t)ch * k, (size_t)nchunks * k * 4, cd + (size_t)ch * nq * k, (size_t)k * 4,
+                              (size_t)k * 4, nq, cudaMemcpyDeviceToDevice, st));
+    RB_CUDA(cudaMemcpy2DAsync(mi + (size_t)ch * k, (size_t)nchunks * k * 8, cid + (size_t)ch * nq * k, (size_t)k * 8,
+                              (size_t)k * 8, nq, cudaMemcpyDeviceToDevice, st));
+  }
+  return topk_rows_launch(md, nq, nchunks * k, (int64_t)nchunks * k, mi, k, desc, 0, out_d, out_i, idx64, st);
+}

@@ -1,0 +1,117 @@
+"""Drop-in for reid/evaluate.py (evaluate_all :33-52, evaluate :55-75, compute_mAP :78-105, get_feats :5-20,
+get_evaluate_result :23-27).
+
+The Q x G score matrix is one tensor-core GEMM (reid/evaluate.py:58 does Q separate GEMVs + Q host
+syncs + Q full sorts); CMC / mAP come from the counting kernel in csrc/evalmap.cu -- no sort, one
+device->host copy of G+1 numbers at the end.
+"""
+from __future__ import annotations
+
+import numpy as np
+import torch
+
+from . import _lib as L
+from . import ops
+
+
+def _labels(x):
+    if isinstance(x, torch.Tensor):
+        return x.reshape(-1)
+    return torch.from_numpy(np.ascontiguousarray(np.asarray(x))).reshape(-1)
+
+
+def evaluate_all_device(qf, ql, qc, gf, gl, gc):
+    """Device-resident variant: returns (CMC f32[G], mAP f64[1]) CUDA tensors, no host sync."""
+    qf = L.as_f32_cuda(qf)
+    gf = L.as_f32_cuda(gf, qf.device)
+    if qf.shape[0] == 0 or gf.shape[0] == 0:
+        raise ValueError("evaluate_all: empty query or gallery set")
+    score = ops.distmat(qf, gf, "dot")
+    return ops.eval_cmc_map(score, _labels(ql), _labels(qc), _labels(gl), _labels(gc), descending=True)
+
+
+def evaluate_all(qf, ql, qc, gf, gl, gc):
+    """(CMC FloatTensor[G] averaged over ALL Q queries, mAP float); prints Rank@1/5/10 + mAP like the reference."""
+    cmc, ap = evaluate_all_device(qf, ql, qc, gf, gl, gc)
+    CMC = cmc.cpu()
+    ap = float(ap.cpu()[0])
+    if ap != ap:
+        raise L.Reidb200Error("evaluate_all: a query has more good matches than this build holds (2048)")
+    r = lambda k: float(CMC[k]) if CMC.numel() > k else float("nan")
+    print('Rank@1:%f Rank@5:%f Rank@10:%f mAP:%f' % (r(0), r(4), r(9), ap))
+    return CMC, ap
+
+
+def evaluate_dist(dist, ql, qc, gl, gc):
+    """Same reduction on a precomputed Q x G DISTANCE matrix (ascending = better), e.g. a re-ranked one."""
+    cmc, ap = ops.eval_cmc_map(dist, _labels(ql), _labels(qc), _labels(gl), _labels(gc), descending=False)
+    return cmc.cpu(), float(ap.cpu()[0])
+
+
+def evaluate(qf, ql, qc, gf, gl, gc):
+    """One query: (ap float, cmc IntTensor[G]); cmc[0] == -1 when the query has no valid gallery match."""
+    qf = L.as_f32_cuda(qf).reshape(1, -1)
+    gf = L.as_f32_cuda(gf, qf.device)
+    G = gf.shape[0]
+    score = ops.distmat(qf, gf, "dot")
+    one = lambda v: torch.as_tensor(v).reshape(1)
+    _, _, ap_q, first = ops.eval_cmc_map(score, one(ql), one(qc), _labels(gl), _labels(gc), descending=True, per_query=True)
+    first = int(first.cpu()[0])
+    cmc = torch.IntTensor(G).zero_()
+    if first < 0:
+        cmc[0] = -1
+        return 0, cmc
+    cmc[first:] = 1
+    return float(ap_q.cpu()[0]), cmc
+
+
+def compute_mAP(index, good_index, junk_index):
+    """(ap, cmc IntTensor[len(index)]) for a given ranking `index` (best first) -- runs the same CUDA
+    counting kernel on a synthetic score row (score = -position)."""
+    index = np.asarray(index).reshape(-1)
+    good_index = np.asarray(good_index).reshape(-1)
+    junk_index = np.asarray(junk_index).reshape(-1)
+    n = len(index)
+    cmc = torch.IntTensor(n).zero_()
+    if good_index.size == 0:
+        cmc[0] = -1
+        return 0, cmc
+    G = int(max(index.max(initial=-1), good_index.max(initial=-1), junk_index.max(initial=-1))) + 1
+    score = np.full((1, G), -float(n + 1), np.float32)
+    score[0, index] = -np.arange(n, dtype=np.float32)
+    gl = np.zeros(G, np.int32)
+    gc = np.zeros(G, np.int32)
+    gl[junk_index.astype(np.int64)] = -1
+    gl[good_index.astype(np.int64)] = 1
+    gc[good_index.astype(np.int64)] = 1
+    not_ranked = np.ones(G, bool)
+    not_ranked[index] = False
+    gl[not_ranked & (gl == 0)] = -1  # items absent from `index` never count
+    _, _, ap_q, first = ops.eval_cmc_map(torch.from_numpy(score), np.array([1], np.int32), np.array([0], np.int32),
+                                         gl, gc, descending=True, per_query=True)
+    first = int(first.cpu()[0])
+    cmc[first:] = 1
+    return float(ap_q.cpu()[0]), cmc
+
+
+def get_feats(model, dataloader):
+    """Backbone forward over a loader (PyTorch; the backbone is outside the kernel scope)."""
+    model.eval()
+    labels, features, cams = [], [], []
+    for sample in dataloader:
+        image, label, cam = sample[:3]
+        feat = model(image.cuda(), cam)
+        features.append(feat[1])
+        labels.append(label)
+        cams.append(cam)
+    labels = torch.cat(labels, dim=0)
+    features = torch.cat(features, dim=0)
+    cams = torch.cat(cams, dim=0)
+    model.train()
+    return labels, features, cams
+
+
+def get_evaluate_result(model, dataloader_query, dataloader_gallery):
+    labels_query, features_query, cams_query = get_feats(model, dataloader_query)
+    labels_gallery, features_gallery, cams_gallery = get_feats(model, dataloader_gallery)
+    return evaluate_all(features_query, labels_query, cams_query, features_gallery, labels_gallery, cams_gallery)

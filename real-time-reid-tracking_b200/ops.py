@@ -1,0 +1,350 @@
+"""Tensor-level bindings: torch CUDA tensors in, torch CUDA tensors out, every call one or more sm_100a
+kernels of libreidb200.so on the current torch stream.  The reference-named modules (evaluate.py,
+losses_utils.py, faiss_utils.py, matching.py, ...) are thin shims over these."""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+import torch
+
+from . import _lib as L
+
+_KIND = {"euclid": L.DIST_EUCLID, "cosine_half": L.DIST_COSINE_HALF, "dot": L.DIST_DOT, "sql2": L.DIST_SQL2}
+
+
+def _f32(x, device=None):
+    return L.as_f32_cuda(x, device)
+
+
+def _i32(x, device):
+    if not isinstance(x, torch.Tensor):
+        x = torch.from_numpy(np.ascontiguousarray(np.asarray(x)))
+    return x.to(device=device, dtype=torch.int32, non_blocking=True).contiguous()
+
+
+def _f3(v):
+    return (C.c_float * 3)(*[float(a) for a in v])
+
+
+# ----------------------------------------------------------------------------------------- distances
+def distmat(x, y, kind="euclid", out=None):
+    x = _f32(x)
+    dev = L.require_device(x)
+    y = _f32(y, dev)
+    m, d = x.shape
+    n, d2 = y.shape
+    if d != d2:
+        raise ValueError("feature dimensions differ: %d vs %d" % (d, d2))
+    if out is None:
+        out = torch.empty((m, n), dtype=torch.float32, device=dev)
+    if m == 0 or n == 0:
+        return out
+    lib = L.load()
+    ws = L.workspace(lib.reidb200_distmat_workspace_bytes(m, n, d), dev)
+    with torch.cuda.device(dev):
+        L.check(lib.reidb200_distmat(x.data_ptr(), m, x.stride(0), y.data_ptr(), n, y.stride(0), d, _KIND[kind],
+                                     out.data_ptr(), out.stride(0), ws.data_ptr(), ws.numel(), L.stream_ptr()))
+    return out
+
+
+def distmat_simt(x, y, kind="euclid"):
+    """fp32 SIMT cross-check kernel (tests only)."""
+    x = _f32(x)
+    dev = L.require_device(x)
+    y = _f32(y, dev)
+    m, d = x.shape
+    n = y.shape[0]
+    out = torch.empty((m, n), dtype=torch.float32, device=dev)
+    if m and n:
+        with torch.cuda.device(dev):
+            L.check(L.load().reidb200_distmat_simt(x.data_ptr(), m, x.stride(0), y.data_ptr(), n, y.stride(0), d,
+                                                  _KIND[kind], out.data_ptr(), out.stride(0), L.stream_ptr()))
+    return out
+
+
+def knn(xq, xb, k, metric="sql2", index_base=0, idx64=True):
+    """Exact brute-force k-NN: (D f32[nq,k], I i64|i32[nq,k]), ascending for sql2, descending for dot."""
+    xq = _f32(xq)
+    dev = L.require_device(xq)
+    xb = _f32(xb, dev)
+    nq, d = xq.shape
+    nb = xb.shape[0]
+    D = torch.empty((nq, k), dtype=torch.float32, device=dev)
+    I = torch.empty((nq, k), dtype=torch.int64 if idx64 else torch.int32, device=dev)
+    if nq == 0:
+        return D, I
+    if nb == 0:
+        raise ValueError("knn: empty database")
+    lib = L.load()
+    ws = L.workspace(lib.reidb200_knn_workspace_bytes(nq, nb, d, k), dev)
+    with torch.cuda.device(dev):
+        L.check(lib.reidb200_knn(xq.data_ptr(), nq, xq.stride(0), xb.data_ptr(), nb, xb.stride(0), d, k, _KIND[metric],
+                                 int(index_base), D.data_ptr(), I.data_ptr(), 1 if idx64 else 0, ws.data_ptr(),
+                                 ws.numel(), L.stream_ptr()))
+    return D, I
+
+
+def topk_rows(vals, k, descending=False, cand_i=None, index_base=0, idx64=True):
+    vals = _f32(vals)
+    dev = L.require_device(vals)
+    rows, cols = vals.shape
+    D = torch.empty((rows, k), dtype=torch.float32, device=dev)
+    I = torch.empty((rows, k), dtype=torch.int64 if idx64 else torch.int32, device=dev)
+    if cand_i is not None:
+        cand_i = cand_i.to(device=dev, dtype=torch.int64).contiguous()
+        assert cand_i.shape == vals.shape
+    if rows:
+        with torch.cuda.device(dev):
+            L.check(L.load().reidb200_topk_rows(vals.data_ptr(), rows, cols, vals.stride(0), L.ptr(cand_i), k,
+                                               1 if descending else 0, int(index_base), D.data_ptr(), I.data_ptr(),
+                                               1 if idx64 else 0, L.stream_ptr()))
+    return D, I
+
+
+# ----------------------------------------------------------------------------------------- CMC / mAP
+def eval_cmc_map(mat, ql, qc, gl, gc, descending=True, per_query=False):
+    """mat f32[Q,G] on device -> (cmc f32[G], ap f64[1]) device tensors (+ ap_q f64[Q], first i32[Q])."""
+    mat = _f32(mat)
+    dev = L.require_device(mat)
+    Q, G = mat.shape
+    ql, qc, gl, gc = _i32(ql, dev), _i32(qc, dev), _i32(gl, dev), _i32(gc, dev)
+    if ql.numel() != Q or qc.numel() != Q or gl.numel() != G or gc.numel() != G:
+        raise ValueError("label / camera vectors do not match the score matrix")
+    cmc = torch.empty(G, dtype=torch.float32, device=dev)
+    ap = torch.empty(1, dtype=torch.float64, device=dev)
+    ap_q = torch.empty(Q, dtype=torch.float64, device=dev) if per_query else None
+    first = torch.empty(Q, dtype=torch.int32, device=dev) if per_query else None
+    lib = L.load()
+    ws = L.workspace(lib.reidb200_eval_workspace_bytes(Q, G), dev)
+    with torch.cuda.device(dev):
+        L.check(lib.reidb200_eval_cmc_map(mat.data_ptr(), Q, G, mat.stride(0), 1 if descending else 0, ql.data_ptr(),
+                                          qc.data_ptr(), gl.data_ptr(), gc.data_ptr(), cmc.data_ptr(), ap.data_ptr(),
+                                          L.ptr(ap_q), L.ptr(first), ws.data_ptr(), ws.numel(), L.stream_ptr()))
+    if per_query:
+        return cmc, ap, ap_q, first
+    return cmc, ap
+
+
+# ----------------------------------------------------------------------------------------- re-ranking
+def jaccard(feats, k1=20, k2=6, use_float16=False, lambda_value=0.0, rows=None, cols=None, want_rank=False):
+    """Jaccard distance of the merged set `feats` f32[N,d]; rows/cols = (start, count) sub-block.
+    Returns the device matrix (f32 or f16) and optionally the initial ranking i32[N,k1]."""
+    feats = _f32(feats)
+    dev = L.require_device(feats)
+    N, d = feats.shape
+    row0, nrows = rows if rows is not None else (0, N)
+    col0, ncols = cols if cols is not None else (0, N)
+    out = torch.empty((nrows, ncols), dtype=torch.float16 if use_float16 else torch.float32, device=dev)
+    rank = torch.empty((N, k1), dtype=torch.int32, device=dev) if want_rank else None
+    lib = L.load()
+    ws = L.workspace(lib.reidb200_jaccard_workspace_bytes(N, d, k1, k2), dev)
+    with torch.cuda.device(dev):
+        L.check(lib.reidb200_jaccard(feats.data_ptr(), N, feats.stride(0), d, k1, k2, 1 if use_float16 else 0,
+                                     float(lambda_value), row0, nrows, col0, ncols, out.data_ptr(), out.stride(0),
+                                     L.ptr(rank), ws.data_ptr(), ws.numel(), L.stream_ptr()))
+    return (out, rank) if want_rank else out
+
+
+def k_reciprocal_lists(rank, k):
+    """R(i,k) for every row: (idx i32[N,k+1] padded with -1, cnt i32[N])."""
+    dev = L.require_device(rank if isinstance(rank, torch.Tensor) else None)
+    rank = _i32(rank, dev)
+    N, k1c = rank.shape
+    idx = torch.empty((N, k + 1), dtype=torch.int32, device=dev)
+    cnt = torch.empty(N, dtype=torch.int32, device=dev)
+    with torch.cuda.device(dev):
+        L.check(L.load().reidb200_k_reciprocal(rank.data_ptr(), N, k1c, k, idx.data_ptr(), cnt.data_ptr(), L.stream_ptr()))
+    return idx, cnt
+
+
+# ----------------------------------------------------------------------------------------- crop / resize
+def crop_resize_norm(src, crop_off, crop_geom, out_h=256, out_w=128, mean=(0.5, 0.5, 0.5), std=(0.5, 0.5, 0.5),
+                     mode="cv_linear", out=None):
+    """src u8 device bytes, crop_off i64[M], crop_geom i32[M,3]=(h,w,stride) -> f32[M,3,out_h,out_w]."""
+    dev = L.require_device(src)
+    M = crop_off.numel()
+    if out is None:
+        out = torch.empty((M, 3, out_h, out_w), dtype=torch.float32, device=dev)
+    if M == 0:
+        return out
+    lib = L.load()
+    with torch.cuda.device(dev):
+        if mode == "cv_linear":
+            L.check(lib.reidb200_crop_resize_norm(src.data_ptr(), crop_off.data_ptr(), crop_geom.data_ptr(), M, out_h, out_w,
+                                                  _f3(mean), _f3(std), L.RESIZE_CV_LINEAR, out.data_ptr(), L.stream_ptr()))
+        elif mode == "pil_antialias":
+            max_h = int(crop_geom[:, 0].max().item()) if crop_geom.is_cuda else int(crop_geom[:, 0].max())
+            ws = L.workspace(lib.reidb200_resize_pil_workspace_bytes(M, max_h, out_w), dev)
+            L.check(lib.reidb200_crop_resize_norm_ws(src.data_ptr(), crop_off.data_ptr(), crop_geom.data_ptr(), M, out_h,
+                                                     out_w, _f3(mean), _f3(std), L.RESIZE_PIL_ANTIALIAS, out.data_ptr(),
+                                                     ws.data_ptr(), ws.numel(), L.stream_ptr()))
+        else:
+            raise ValueError("unknown resize mode %r" % (mode,))
+    return out
+
+
+def resize_pil_u8(src, crop_off, crop_geom, max_h, out_h=256, out_w=128):
+    dev = L.require_device(src)
+    M = crop_off.numel()
+    out = torch.empty((M, out_h, out_w, 3), dtype=torch.uint8, device=dev)
+    if M == 0:
+        return out
+    lib = L.load()
+    ws = L.workspace(lib.reidb200_resize_pil_workspace_bytes(M, int(max_h), out_w), dev)
+    with torch.cuda.device(dev):
+        L.check(lib.reidb200_resize_pil_u8(src.data_ptr(), crop_off.data_ptr(), crop_geom.data_ptr(), M, out_h, out_w,
+                                           out.data_ptr(), ws.data_ptr(), ws.numel(), L.stream_ptr()))
+    return out
+
+
+# ----------------------------------------------------------------------------------------- association
+class Gallery:
+    """Device-resident per-track feature ring buffer [slots, budget, d] (NearestNeighborDistanceMetric.samples)."""
+
+    def __init__(self, slots, budget, d, device=None):
+        self.device = device or L.require_device()
+        self.slots, self.budget, self.d = int(slots), int(budget), int(d)
+        h = C.c_void_p()
+        with torch.cuda.device(self.device):
+            L.check(L.load().reidb200_gallery_create(self.slots, self.budget, self.d, C.byref(h)))
+        self._h = h
+
+    def close(self):
+        if getattr(self, "_h", None):
+            L.load().reidb200_gallery_destroy(self._h)
+            self._h = None
+
+    __del__ = close
+
+    def partial_fit(self, feats, slot_of_row):
+        feats = _f32(feats, self.device)
+        slot_of_row = _i32(slot_of_row, self.device)
+        n = feats.shape[0]
+        if n:
+            with torch.cuda.device(self.device):
+                L.check(L.load().reidb200_gallery_partial_fit(self._h, feats.data_ptr(), feats.stride(0),
+                                                             slot_of_row.data_ptr(), n, L.stream_ptr()))
+
+    def reset_slots(self, slots):
+        slots = _i32(slots, self.device)
+        if slots.numel():
+            with torch.cuda.device(self.device):
+                L.check(L.load().reidb200_gallery_reset_slots(self._h, slots.data_ptr(), slots.numel(), L.stream_ptr()))
+
+    def counts(self):
+        out = torch.empty(self.slots, dtype=torch.int32, device=self.device)
+        with torch.cuda.device(self.device):
+            L.check(L.load().reidb200_gallery_counts(self._h, out.data_ptr(), L.stream_ptr()))
+        return out
+
+    def read_slot(self, slot):
+        out = torch.empty((self.budget, self.d), dtype=torch.float32, device=self.device)
+        with torch.cuda.device(self.device):
+            L.check(L.load().reidb200_gallery_read_slot(self._h, int(slot), out.data_ptr(), L.stream_ptr()))
+        return out
+
+
+def assoc_frame(gallery, det_feat, det_tlwh, trk_slot, trk_mean, trk_SI, trk_tsu, mc_lambda=0.995, max_dist=0.2,
+                max_iou_dist=0.7, iou_mode="iou", clamp_app=False, clamp_iou=False, gate=True, want_raw=False,
+                want_app=True, want_iou=True):
+    """One fused launch: (app f64[T,M] or None, raw or None, iou f64[T,M] or None), all on device."""
+    dev = gallery.device if gallery is not None else L.require_device()
+    det_tlwh = _f32(det_tlwh, dev)
+    M = det_tlwh.shape[0]
+    trk_mean = torch.as_tensor(trk_mean).to(device=dev, dtype=torch.float64).contiguous()
+    T = trk_mean.shape[0]
+    trk_tsu = _i32(trk_tsu, dev)
+    app = raw = iou = None
+    det_feat_t = None
+    slot_t = si_t = None
+    if want_app:
+        det_feat_t = _f32(det_feat, dev)
+        slot_t = _i32(trk_slot, dev)
+        si_t = torch.as_tensor(trk_SI).to(device=dev, dtype=torch.float64).contiguous()
+        app = torch.empty((T, M), dtype=torch.float64, device=dev)
+        raw = torch.empty((T, M), dtype=torch.float64, device=dev) if want_raw else None
+    if want_iou:
+        iou = torch.empty((T, M), dtype=torch.float64, device=dev)
+    if T == 0 or M == 0:
+        return app, raw, iou
+    flags = (L.ASSOC_CLAMP_APP if clamp_app else 0) | (L.ASSOC_CLAMP_IOU if clamp_iou else 0) | (0 if gate else L.ASSOC_NO_GATE)
+    with torch.cuda.device(dev):
+        L.check(L.load().reidb200_assoc_frame(gallery._h if gallery is not None else None, L.ptr(det_feat_t),
+                                             det_feat_t.stride(0) if det_feat_t is not None else 0, det_tlwh.data_ptr(), M,
+                                             L.ptr(slot_t), trk_mean.data_ptr(), L.ptr(si_t), trk_tsu.data_ptr(), T,
+                                             float(mc_lambda), float(max_dist), float(max_iou_dist),
+                                             L.IOU_DIOU if iou_mode == "diou" else L.IOU_PLAIN, flags, L.ptr(app), L.ptr(raw),
+                                             L.ptr(iou), L.stream_ptr()))
+    return app, raw, iou
+
+
+def iou_matrix(bbox_tlwh, cand_tlwh, mode="iou"):
+    """T boxes f64 tlwh vs M candidates (float32 or float64 arithmetic as numpy would) -> f64[T,M] device."""
+    dev = L.require_device()
+    b = torch.as_tensor(np.asarray(bbox_tlwh, dtype=np.float64)).reshape(-1, 4).to(dev)
+    c_np = np.asarray(cand_tlwh)
+    is64 = c_np.dtype != np.float32
+    c = torch.as_tensor(np.ascontiguousarray(c_np, dtype=np.float64 if is64 else np.float32)).reshape(-1, 4).to(dev)
+    out = torch.empty((b.shape[0], c.shape[0]), dtype=torch.float64, device=dev)
+    if b.shape[0] and c.shape[0]:
+        with torch.cuda.device(dev):
+            L.check(L.load().reidb200_iou_matrix(b.data_ptr(), b.shape[0], c.data_ptr(), 1 if is64 else 0, c.shape[0],
+                                                L.IOU_DIOU if mode == "diou" else L.IOU_PLAIN, out.data_ptr(), L.stream_ptr()))
+    return out
+
+
+def gating_distance(x4, SI, meas):
+    dev = L.require_device()
+    x4 = torch.as_tensor(np.asarray(x4, dtype=np.float64)).reshape(-1, 4).to(dev)
+    SI = torch.as_tensor(np.asarray(SI, dtype=np.float64)).reshape(-1, 16).to(dev)
+    meas = torch.as_tensor(np.asarray(meas, dtype=np.float64)).reshape(-1, 4).to(dev)
+    out = torch.empty((x4.shape[0], meas.shape[0]), dtype=torch.float64, device=dev)
+    if x4.shape[0] and meas.shape[0]:
+        with torch.cuda.device(dev):
+            L.check(L.load().reidb200_gating_distance(x4.data_ptr(), SI.data_ptr(), meas.data_ptr(), x4.shape[0],
+                                                     meas.shape[0], out.data_ptr(), L.stream_ptr()))
+    return out
+
+
+def cosine_distance(a, b, data_is_normalized=False):
+    a = _f32(a)
+    dev = L.require_device(a)
+    b = _f32(b, dev)
+    na, d = a.shape
+    nb = b.shape[0]
+    out = torch.empty((na, nb), dtype=torch.float32, device=dev)
+    if na and nb:
+        lib = L.load()
+        ws = L.workspace(lib.reidb200_cosine_distance_workspace_bytes(na, nb, d), dev)
+        with torch.cuda.device(dev):
+            L.check(lib.reidb200_cosine_distance(a.data_ptr(), na, a.stride(0), b.data_ptr(), nb, b.stride(0), d,
+                                                 1 if data_is_normalized else 0, out.data_ptr(), ws.data_ptr(), ws.numel(),
+                                                 L.stream_ptr()))
+    return out
+
+
+def jaccard_from_sql2(sql2, k1=20, k2=6, use_float16=False, lambda_value=0.0, rows=None, cols=None, sqnorm=None,
+                      want_rank=False):
+    """Stages D2(select)-D7 from a materialised squared-L2 matrix f32[N,N] of the merged set.
+    sqnorm defaults to ones (L2-normalised features, where 2 - 2 x.y == sql2)."""
+    sql2 = _f32(sql2)
+    dev = L.require_device(sql2)
+    N = sql2.shape[0]
+    if sql2.shape[1] != N:
+        raise ValueError("jaccard_from_sql2: square matrix expected")
+    if sqnorm is None:
+        sqnorm = torch.ones(N, dtype=torch.float32, device=dev)
+    sqnorm = _f32(sqnorm, dev)
+    _, rank = topk_rows(sql2, k1, descending=False, idx64=False)
+    row0, nrows = rows if rows is not None else (0, N)
+    col0, ncols = cols if cols is not None else (0, N)
+    out = torch.empty((nrows, ncols), dtype=torch.float16 if use_float16 else torch.float32, device=dev)
+    lib = L.load()
+    d_any = 64  # feature dimension only sizes the dense part of the workspace, unused on this path
+    ws = L.workspace(lib.reidb200_jaccard_workspace_bytes(N, d_any, k1, k2), dev)
+    with torch.cuda.device(dev):
+        L.check(lib.reidb200_jaccard_from_rank(rank.data_ptr(), sql2.data_ptr(), sql2.stride(0), sqnorm.data_ptr(), N, k1, k2,
+                                               1 if use_float16 else 0, float(lambda_value), row0, nrows, col0, ncols,
+                                               out.data_ptr(), out.stride(0), ws.data_ptr(), ws.numel(), L.stream_ptr()))
+    return (out, rank) if want_rank else out
