@@ -20,3 +20,11 @@ def golden():
         return np.load(os.path.join(ROOT, "tests", "golden", name + ".npz"))
 
     return load
+
+
+@pytest.fixture(scope="session")
+def rb():
+    """The product package (import alias reidb200 -> real-time-reid-tracking_b200/)."""
+    import reidb200  # noqa: F401
+
+    return reidb200

@@ -1,0 +1,72 @@
+"""GPU parity: crop + resize + normalise vs the oracle (bit-exact) and the golden cv2 / PIL outputs."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import reid_oracle as O
+
+pytestmark = pytest.mark.gpu
+
+
+def _crops(g):
+    img, xyxy = g["img"], g["xyxy"]
+    return img, xyxy, [img[y1:y2, x1:x2] for x1, y1, x2, y2 in xyxy]
+
+
+def test_cv_linear_frame_and_crops(rb, golden):
+    from reidb200 import feature_extractor as FE, preprocess as P
+
+    g = golden("preprocess")
+    img, xyxy, crops = _crops(g)
+    want = O.preprocess_deepsort(crops)
+    got_frame = P.preprocess_frame(img, xyxy).cpu().numpy()
+    assert got_frame.shape == (len(crops), 3, 256, 128)
+    assert np.array_equal(got_frame, want), np.abs(got_frame - want).max()  # bit-exact vs the restatement
+    ex = object.__new__(FE.Extractor)
+    ex.size, ex.norm = (128, 256), P.DEEPSORT_NORM
+    got_list = ex._preprocess(crops).cpu().numpy()
+    assert np.array_equal(got_list, want)
+    # vs cv2 itself (reference output): within 1 ulp of the /255 image scaled by 1/std
+    assert np.abs(got_frame[g["cv_full_idx"]] - g["cv_full"]).max() <= 4.8e-7
+    assert np.abs(got_frame[:, :, ::3, ::3] - g["cv_sub"]).max() <= 4.8e-7
+
+
+def test_pil_antialias(rb, golden):
+    from reidb200 import feature_extractor as FE, preprocess as P
+
+    g = golden("preprocess")
+    img, xyxy, crops = _crops(g)
+    u8 = P.resize_pil_u8_crops(crops).cpu().numpy()
+    assert np.array_equal(u8, g["pil_u8"])  # bit-exact integer resample
+    got = FE.ReIDPreprocess()._preprocess(crops).cpu().numpy()
+    assert np.abs(got[0] - g["pil0"]).max() <= 1e-6
+    want = O.preprocess_boxmot(crops)
+    assert np.abs(got - want).max() <= 1e-6
+    got2 = FE.ReIDPreprocess().preprocess_frame(img, xyxy).cpu().numpy()
+    assert np.array_equal(got, got2)
+
+
+def test_mot_shaped_frame(rb):
+    """1080p frame, 200 boxes incl. clamped ones: device crops equal the oracle on host slices."""
+    from reidb200 import preprocess as P, synth
+
+    fr = synth.mot_frame(M=200, T=4, seed=3)
+    H, W = fr["img"].shape[:2]
+    xyxy = P.xywh_to_xyxy(fr["det_xywh"], W, H)
+    keep = (xyxy[:, 2] > xyxy[:, 0]) & (xyxy[:, 3] > xyxy[:, 1])
+    xyxy = xyxy[keep]
+    got = P.preprocess_frame(fr["img"], xyxy).cpu().numpy()
+    sel = [0, 7, len(xyxy) // 2, len(xyxy) - 1]
+    want = O.preprocess_deepsort([fr["img"][xyxy[i, 1]:xyxy[i, 3], xyxy[i, 0]:xyxy[i, 2]] for i in sel])
+    assert np.array_equal(got[sel], want)
+
+
+def test_empty_and_bad_crops(rb):
+    from reidb200 import preprocess as P
+
+    img = np.zeros((50, 60, 3), np.uint8)
+    assert P.preprocess_frame(img, np.zeros((0, 4), np.int32)).shape == (0, 3, 256, 128)
+    with pytest.raises(ValueError):
+        P.preprocess_frame(img, np.array([[5, 5, 5, 20]], np.int32))
+    with pytest.raises(ValueError):
+        P.preprocess_crops([np.zeros((0, 4, 3), np.uint8)])

@@ -1,0 +1,158 @@
+"""GPU parity: distance matrices, k-NN, CMC/mAP through the C ABI vs the oracle and the golden vectors."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import reid_oracle as O
+
+pytestmark = pytest.mark.gpu
+
+REL = 1e-4  # north_star: distances within 1e-4 relative
+
+
+def _unit(x):
+    return (x / np.linalg.norm(x, axis=1, keepdims=True)).astype(np.float32)
+
+
+def test_distmat_golden(rb, golden):
+    from reidb200 import losses_utils as U
+
+    g = golden("dist")
+    e = U.euclidean_dist(torch.from_numpy(g["x"]), torch.from_numpy(g["y"])).cpu().numpy()
+    c = U.cosine_dist(torch.from_numpy(g["x"]), torch.from_numpy(g["y"])).cpu().numpy()
+    mask = g["euclid"] > 1e-2  # the duplicate pair is sqrt of fp32 cancellation noise in the reference itself
+    np.testing.assert_allclose(e[mask], g["euclid"][mask], rtol=REL)
+    assert e[~mask].max() < 2e-2
+    np.testing.assert_allclose(c, g["cosine"], atol=1e-6)
+
+
+@pytest.mark.parametrize("m,n,d", [(1, 1, 1), (37, 53, 48), (128, 256, 64), (129, 257, 65), (300, 1000, 512),
+                                   (1000, 300, 2048), (513, 777, 100)])
+@pytest.mark.parametrize("kind", ["euclid", "cosine_half", "dot", "sql2"])
+def test_distmat_tc_vs_simt_vs_oracle(rb, m, n, d, kind):
+    from reidb200 import ops
+
+    rng = np.random.default_rng(m * 7 + n * 3 + d)
+    x = rng.standard_normal((m, d)).astype(np.float32)
+    y = rng.standard_normal((n, d)).astype(np.float32)
+    tc = ops.distmat(x, y, kind).cpu().numpy()
+    simt = ops.distmat_simt(x, y, kind).cpu().numpy()
+    want = {"euclid": O.euclidean_dist, "cosine_half": O.cosine_dist, "sql2": O.sql2_dist,
+            "dot": lambda a, b: a @ b.T}[kind](x, y)
+    scale = np.abs(want).max() + 1e-6
+    # the split-bf16 tensor-core result is fp32-accurate: same error budget as the fp32 SIMT kernel
+    assert np.abs(simt - want).max() <= 2e-5 * scale
+    assert np.abs(tc - want).max() <= 2e-5 * scale, np.abs(tc - want).max()
+    if kind in ("euclid", "sql2"):
+        big = want > 0.1 * scale
+        np.testing.assert_allclose(tc[big], want[big], rtol=REL)
+
+
+def test_distmat_unit_features_ranking(rb):
+    """Market-shaped unit features: rankings by the tensor-core distances equal fp64 rankings except ties."""
+    from reidb200 import ops, synth
+
+    d = synth.market_like(Q=200, G=3000, D=512, n_ids=150, seed=1)
+    tc = ops.distmat(d["qf"], d["gf"], "euclid").cpu().numpy()
+    ref = np.sqrt(np.maximum(2 - 2 * (d["qf"].astype(np.float64) @ d["gf"].astype(np.float64).T), 1e-12))
+    np.testing.assert_allclose(tc, ref, rtol=REL)
+    a, b = np.argsort(tc, 1, kind="stable")[:, :50], np.argsort(ref, 1, kind="stable")[:, :50]
+    bad = a != b
+    if bad.any():  # any disagreement must be a tie within tolerance
+        r, c = np.where(bad)
+        assert np.allclose(ref[r, a[r, c]], ref[r, b[r, c]], rtol=REL)
+
+
+def test_distmat_errors(rb):
+    from reidb200 import ops
+
+    with pytest.raises(ValueError):
+        ops.distmat(np.zeros((3, 4), np.float32), np.zeros((3, 5), np.float32))
+    assert ops.distmat(np.zeros((0, 4), np.float32), np.zeros((3, 4), np.float32)).shape == (0, 3)
+
+
+@pytest.mark.parametrize("nq,nb,d,k", [(5, 40, 16, 7), (260, 260, 32, 20), (64, 5000, 128, 100), (33, 70000, 64, 10),
+                                       (7, 300, 32, 300)])
+def test_knn_vs_oracle(rb, nq, nb, d, k):
+    from reidb200 import ops
+
+    rng = np.random.default_rng(nq + nb)
+    xb = _unit(rng.standard_normal((nb, d)))
+    xq = _unit(rng.standard_normal((nq, d)))
+    if nb >= 50:
+        xb[17] = xb[3]  # exact duplicates: tie -> lower index first
+    D, I = ops.knn(xq, xb, k, "sql2")
+    D, I = D.cpu().numpy(), I.cpu().numpy()
+    Do, Io = O.knn_l2(xb, xq, k)
+    np.testing.assert_allclose(D, Do, atol=3e-6)
+    bad = I != Io
+    if bad.any():
+        full = O.sql2_dist(xq, xb).astype(np.float64)
+        r, c = np.where(bad)
+        assert np.allclose(full[r, I[r, c]], full[r, Io[r, c]], atol=3e-6), "non-tie index mismatch"
+    assert (np.diff(D, axis=1) >= 0).all()
+
+
+def test_knn_golden_rank(rb, golden):
+    from reidb200 import ops
+
+    g = golden("jaccard")
+    _, I = ops.knn(g["feats"], g["feats"], 20, "sql2", idx64=False)
+    assert np.array_equal(I.cpu().numpy(), g["initial_rank"])
+
+
+def test_topk_ties_and_fallback(rb):
+    """Constant rows (all ties) overflow the candidate buffer and take the bisection fallback."""
+    from reidb200 import ops
+
+    v = np.zeros((3, 9000), np.float32)
+    v[1, 100:] = 1.0
+    v[2] = np.arange(9000, 0, -1)
+    D, I = ops.topk_rows(torch.from_numpy(v), 25)
+    D, I = D.cpu().numpy(), I.cpu().numpy()
+    assert np.array_equal(I[0], np.arange(25)) and (D[0] == 0).all()
+    assert np.array_equal(I[1], np.arange(25))
+    assert np.array_equal(I[2], np.arange(8999, 8999 - 25, -1))
+    D, I = ops.topk_rows(torch.from_numpy(v), 25, descending=True)
+    assert np.array_equal(I.cpu().numpy()[2], np.arange(25))
+
+
+def test_eval_golden(rb, golden):
+    from reidb200 import evaluate as E
+
+    g = golden("eval")
+    t = {k: torch.from_numpy(g[k]) for k in ("qf", "ql", "qc", "gf", "gl", "gc")}
+    cmc, ap = E.evaluate_all(t["qf"], t["ql"], t["qc"], t["gf"], t["gl"], t["gc"])
+    assert cmc.dtype == torch.float32 and tuple(cmc.shape) == (g["gf"].shape[0],)
+    np.testing.assert_allclose(cmc.numpy(), g["cmc"], atol=1e-6)  # north_star: CMC/mAP within 1e-6 absolute
+    assert abs(ap - float(g["ap"])) < 1e-6
+    # per query
+    for i in (0, 5, int(np.argmin(g["first_hit"]))):
+        a, c = E.evaluate(t["qf"][i], t["ql"][i], t["qc"][i], t["gf"], t["gl"], t["gc"])
+        if g["first_hit"][i] < 0:
+            assert c[0] == -1
+        else:
+            assert abs(a - g["ap_per_query"][i]) < 1e-9
+            assert int(np.argmax(c.numpy())) == g["first_hit"][i]
+
+
+def test_eval_market_shape_vs_oracle(rb):
+    from reidb200 import evaluate as E, synth
+
+    d = synth.market_like(Q=300, G=4000, D=128, n_ids=200, seed=2, orphan_frac=0.03)
+    cmc, ap = E.evaluate_all(*[torch.from_numpy(d[k]) for k in ("qf", "ql", "qc", "gf", "gl", "gc")])
+    ocmc, oap = O.evaluate_all(d["qf"], d["ql"], d["qc"], d["gf"], d["gl"], d["gc"])
+    np.testing.assert_allclose(cmc.numpy(), ocmc, atol=1e-6)
+    assert abs(ap - oap) < 1e-6
+
+
+def test_compute_map_entry(rb):
+    from reidb200 import evaluate as E
+
+    index = np.array([4, 2, 7, 0, 1, 3, 5, 6])
+    good, junk = np.array([7, 3]), np.array([2, 6])
+    ap, cmc = E.compute_mAP(index, good, junk)
+    oap, ocmc = O.compute_mAP(index, good, junk)
+    assert abs(ap - oap) < 1e-12 and np.array_equal(cmc.numpy(), ocmc)
+    ap, cmc = E.compute_mAP(index, np.array([], np.int64), junk)
+    assert cmc[0] == -1

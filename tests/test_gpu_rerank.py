@@ -1,0 +1,67 @@
+"""GPU parity: k-reciprocal Jaccard re-ranking vs the golden vectors (reference compute_jaccard_distance)."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import reid_oracle as O
+
+pytestmark = pytest.mark.gpu
+
+
+def test_k_reciprocal_lists(rb, golden):
+    from reidb200 import faiss_utils as F
+
+    g = golden("jaccard")
+    rank = g["initial_rank"].astype(np.int64)
+    for i in (0, 17, 100, 255):
+        assert np.array_equal(F.k_reciprocal_neigh(rank, i, 20), O.k_reciprocal_neigh(rank, i, 20))
+        assert np.array_equal(F.k_reciprocal_neigh(rank, i, 10), O.k_reciprocal_neigh(rank, i, 10))
+
+
+@pytest.mark.parametrize("tag,k1,k2,f16,tol", [("k20_6", 20, 6, False, 5e-6), ("k10_1", 10, 1, False, 5e-6),
+                                               ("k20_6_f16", 20, 6, True, 4e-3)])
+def test_jaccard_golden(rb, golden, tag, k1, k2, f16, tol):
+    from reidb200 import faiss_utils as F
+
+    g = golden("jaccard")
+    J = F.compute_jaccard_distance(torch.from_numpy(g["feats"]), k1=k1, k2=k2, print_flag=False, search_option=0,
+                                   use_float16=f16)
+    want = g["J_" + tag]
+    assert J.dtype == want.dtype and J.shape == want.shape
+    np.testing.assert_allclose(J.astype(np.float32), want.astype(np.float32), atol=tol)
+    assert (J >= 0).all() and (J <= 1).all()
+
+
+def test_jaccard_larger_vs_oracle(rb):
+    from reidb200 import faiss_utils as F, synth
+
+    d = synth.market_like(Q=150, G=850, D=64, n_ids=60, seed=4)
+    feats = np.concatenate([d["gf"], d["qf"]], 0)
+    J = F.compute_jaccard_distance(torch.from_numpy(feats), print_flag=False)
+    Jo = O.compute_jaccard_distance(feats)
+    np.testing.assert_allclose(J, Jo, atol=5e-6)
+    np.testing.assert_allclose(J, J.T, atol=2e-6)  # symmetric like the reference
+
+
+def test_re_ranking_blend(rb):
+    from reidb200 import faiss_utils as F, losses_utils as U, synth
+
+    d = synth.market_like(Q=80, G=500, D=64, n_ids=40, seed=6)
+    qf, gf = d["qf"], d["gf"]
+    want = O.re_ranking_from_feats(qf, gf, 20, 6, 0.3)
+    got = F.re_ranking_feats(qf, gf, 20, 6, 0.3)
+    np.testing.assert_allclose(got, want, atol=1e-5)
+    # classic signature from Euclidean distance matrices of unit features
+    qg = U.euclidean_dist(qf, gf).cpu().numpy()
+    qq = U.euclidean_dist(qf, qf).cpu().numpy()
+    gg = U.euclidean_dist(gf, gf).cpu().numpy()
+    got2 = F.re_ranking(qg, qq, gg, 20, 6, 0.3)
+    # the self-distances on the diagonal are sqrt(noise) in fp32; rankings near ties may flip, so compare loosely
+    assert np.mean(np.abs(got2 - want) < 1e-3) > 0.995
+
+
+def test_jaccard_limits(rb):
+    from reidb200 import faiss_utils as F
+
+    with pytest.raises(ValueError):
+        F.compute_jaccard_distance(torch.zeros(10, 8), k1=20, print_flag=False)
