@@ -34,6 +34,12 @@ int reidb200_abi_version(void);
 /* 0 when the current device is sm_100 class with tcgen05/TMA, REIDB200_ECUDA otherwise. */
 int reidb200_check_device(void);
 
+/* Per-kernel timing for bench.py: when enabled every kernel launch of the library is bracketed by a CUDA event
+ * pair on its launch stream; profile_read sums the spans recorded under `name` (kernel names as in csrc/). */
+int reidb200_profile_enable(int on);
+int reidb200_profile_read(const char* name, int* launches, double* total_ms);
+int reidb200_profile_names(char* buf, int cap);
+
 /* ------------------------------------------------------------------------------------------
  * (1) crop + resize + normalise
  *   CV_LINEAR     modification_deepsort/feature_extractor.py:31-46  Extractor._preprocess

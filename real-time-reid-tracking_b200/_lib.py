@@ -29,6 +29,9 @@ SIGNATURES = {
     "reidb200_last_error": (C.c_char_p, []),
     "reidb200_abi_version": (_i, []),
     "reidb200_check_device": (_i, []),
+    "reidb200_profile_enable": (_i, [_i]),
+    "reidb200_profile_read": (_i, [C.c_char_p, C.POINTER(_i), C.POINTER(_d)]),
+    "reidb200_profile_names": (_i, [C.c_char_p, _i]),
     "reidb200_crop_resize_norm": (_i, [_vp, _vp, _vp, _i, _i, _i, _f3, _f3, _i, _vp, _vp]),
     "reidb200_crop_resize_norm_ws": (_i, [_vp, _vp, _vp, _i, _i, _i, _f3, _f3, _i, _vp, _vp, _sz, _vp]),
     "reidb200_resize_pil_u8": (_i, [_vp, _vp, _vp, _i, _i, _i, _vp, _vp, _sz, _vp]),
@@ -144,3 +147,23 @@ def as_f32_cuda(x, device=None) -> torch.Tensor:
     dev = device or (x.device if x.is_cuda else require_device())
     x = x.to(device=dev, dtype=torch.float32, non_blocking=True)
     return x if x.is_contiguous() else x.contiguous()
+
+
+def profile_enable(on: bool = True):
+    """Bracket every kernel launch of the library with CUDA events on its launch stream (bench.py)."""
+    check(load().reidb200_profile_enable(1 if on else 0))
+
+
+def profile_read() -> dict:
+    """{kernel name: (launches, total milliseconds)} of the spans recorded since profile_enable."""
+    lib = load()
+    buf = C.create_string_buffer(4096)
+    check(lib.reidb200_profile_names(buf, 4096))
+    out = {}
+    for name in buf.value.decode().split("\n"):
+        if not name:
+            continue
+        n, ms = C.c_int(0), C.c_double(0.0)
+        check(lib.reidb200_profile_read(name.encode(), C.byref(n), C.byref(ms)))
+        out[name] = (n.value, ms.value)
+    return out

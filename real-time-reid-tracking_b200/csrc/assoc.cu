@@ -348,12 +348,12 @@ extern "C" int reidb200_gallery_partial_fit(reidb200_gallery* g, const float* fe
     const int nb = n - b0 < g->scratch_rows ? n - b0 : g->scratch_rows;
     int32_t* dst = g->scratch;
     int32_t* after = g->scratch + g->scratch_rows;
-    pf_assign_kernel<<<ceil_div(nb, 128), 128, 0, st>>>(slot_of_row + b0, nb, g->budget, g->head, dst, after);
+    { ProfScope _ps("pf_assign_kernel", st); pf_assign_kernel<<<ceil_div(nb, 128), 128, 0, st>>>(slot_of_row + b0, nb, g->budget, g->head, dst, after); }
     RB_LAUNCH_CHECK("pf_assign_kernel");
-    pf_write_kernel<<<ceil_div(nb, 8), 256, 0, st>>>(feats + (size_t)b0 * ldf, ldf, slot_of_row + b0, dst, nb, g->budget,
-                                                    g->d, g->feats);
+    { ProfScope _ps("pf_write_kernel", st); pf_write_kernel<<<ceil_div(nb, 8), 256, 0, st>>>(feats + (size_t)b0 * ldf, ldf, slot_of_row + b0, dst, nb, g->budget,
+                                                    g->d, g->feats); }
     RB_LAUNCH_CHECK("pf_write_kernel");
-    pf_update_kernel<<<ceil_div(nb, 128), 128, 0, st>>>(slot_of_row + b0, after, nb, g->budget, g->head, g->count);
+    { ProfScope _ps("pf_update_kernel", st); pf_update_kernel<<<ceil_div(nb, 128), 128, 0, st>>>(slot_of_row + b0, after, nb, g->budget, g->head, g->count); }
     RB_LAUNCH_CHECK("pf_update_kernel");
   }
   return REIDB200_OK;
@@ -362,7 +362,7 @@ extern "C" int reidb200_gallery_partial_fit(reidb200_gallery* g, const float* fe
 extern "C" int reidb200_gallery_reset_slots(reidb200_gallery* g, const int32_t* slots, int n, void* stream) {
   if (n == 0) return REIDB200_OK;
   RB_REQUIRE(g && slots && n > 0, "gallery_reset_slots: bad argument");
-  gal_reset_kernel<<<ceil_div(n, 128), 128, 0, (cudaStream_t)stream>>>(slots, n, g->head, g->count);
+  { ProfScope _ps("gal_reset_kernel", (cudaStream_t)stream); gal_reset_kernel<<<ceil_div(n, 128), 128, 0, (cudaStream_t)stream>>>(slots, n, g->head, g->count); }
   RB_LAUNCH_CHECK("gal_reset_kernel");
   return REIDB200_OK;
 }
@@ -376,8 +376,8 @@ extern "C" int reidb200_gallery_counts(reidb200_gallery* g, int32_t* out_counts,
 
 extern "C" int reidb200_gallery_read_slot(reidb200_gallery* g, int slot, float* out_rows, void* stream) {
   RB_REQUIRE(g && out_rows && slot >= 0 && slot < g->slots, "gallery_read_slot: bad argument");
-  gal_read_kernel<<<g->budget, 128, 0, (cudaStream_t)stream>>>(g->feats, g->head, g->count, slot, g->budget, g->d,
-                                                              out_rows);
+  { ProfScope _ps("gal_read_kernel", (cudaStream_t)stream); gal_read_kernel<<<g->budget, 128, 0, (cudaStream_t)stream>>>(g->feats, g->head, g->count, slot, g->budget, g->d,
+                                                              out_rows); }
   RB_LAUNCH_CHECK("gal_read_kernel");
   return REIDB200_OK;
 }
@@ -400,7 +400,7 @@ extern "C" int reidb200_assoc_frame(reidb200_gallery* g, const float* det_feat, 
   a.trk_slot = trk_slot; a.trk_mean = trk_mean; a.trk_SI = trk_SI; a.trk_tsu = trk_tsu; a.T = T;
   a.mc_lambda = mc_lambda; a.max_dist = max_dist; a.max_iou_dist = max_iou_dist; a.iou_mode = iou_mode; a.flags = flags;
   a.out_app = out_app; a.out_raw = out_app ? out_raw : nullptr; a.out_iou = out_iou;
-  assoc_frame_kernel<<<T, AS_THREADS, 0, (cudaStream_t)stream>>>(a);
+  { ProfScope _ps("assoc_frame_kernel", (cudaStream_t)stream); assoc_frame_kernel<<<T, AS_THREADS, 0, (cudaStream_t)stream>>>(a); }
   RB_LAUNCH_CHECK("assoc_frame_kernel");
   return REIDB200_OK;
 }
@@ -423,7 +423,7 @@ extern "C" int reidb200_gating_distance(const double* x4, const double* SI, cons
   if (T == 0 || M == 0) return REIDB200_OK;
   RB_REQUIRE(x4 && SI && meas && out && T > 0 && M > 0, "gating_distance: bad argument");
   dim3 grid(ceil_div(M, 128), T);
-  gating_kernel<<<grid, 128, 0, (cudaStream_t)stream>>>(x4, SI, meas, T, M, out);
+  { ProfScope _ps("gating_kernel", (cudaStream_t)stream); gating_kernel<<<grid, 128, 0, (cudaStream_t)stream>>>(x4, SI, meas, T, M, out); }
   RB_LAUNCH_CHECK("gating_kernel");
   return REIDB200_OK;
 }
@@ -454,9 +454,9 @@ extern "C" int reidb200_cosine_distance(const float* a, int na, int64_t lda, con
   const float* ax = a; const float* bx = b;
   int64_t la = lda, lb = ldb;
   if (!normalized) {
-    normalize_rows_kernel<<<ceil_div(na, 8), 256, 0, st>>>(a, na, lda, d, an);
+    { ProfScope _ps("normalize_rows_kernel", st); normalize_rows_kernel<<<ceil_div(na, 8), 256, 0, st>>>(a, na, lda, d, an); }
     RB_LAUNCH_CHECK("normalize_rows_kernel");
-    normalize_rows_kernel<<<ceil_div(nb, 8), 256, 0, st>>>(b, nb, ldb, d, bn);
+    { ProfScope _ps("normalize_rows_kernel", st); normalize_rows_kernel<<<ceil_div(nb, 8), 256, 0, st>>>(b, nb, ldb, d, bn); }
     RB_LAUNCH_CHECK("normalize_rows_kernel");
     ax = an; bx = bn; la = d; lb = d;
   }
@@ -467,7 +467,7 @@ extern "C" int reidb200_cosine_distance(const float* a, int na, int64_t lda, con
   rc = gemm_split_launch(pa, nullptr, na, pb, nullptr, nb, d, REIDB200_DIST_DOT, out, nb, st);
   if (rc) return rc;
   const size_t n = (size_t)na * nb;
-  one_minus_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(out, n);
+  { ProfScope _ps("one_minus_kernel", st); one_minus_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(out, n); }
   RB_LAUNCH_CHECK("one_minus_kernel");
   return REIDB200_OK;
 }

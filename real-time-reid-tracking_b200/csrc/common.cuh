@@ -44,6 +44,18 @@ inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
 
 int num_sms();
 
+// RAII span: when profiling is enabled (reidb200_profile_enable) records a CUDA event pair on `st` around a launch.
+class ProfScope {
+ public:
+  ProfScope(const char* name, cudaStream_t st);
+  ~ProfScope();
+ private:
+  const char* name_;
+  cudaStream_t st_;
+  bool on_;
+  cudaEvent_t a_, b_;
+};
+
 // Bump allocator over a caller-provided workspace.
 struct Carver {
   char* base;

@@ -208,11 +208,11 @@ static int pil_run(const uint8_t* src, const int64_t* crop_off, const int32_t* c
   const int tmp_rows = (int)(ws_bytes / ((size_t)M * out_w * 3));
   RB_REQUIRE(ws != nullptr && tmp_rows >= 1, "resize_pil: workspace missing or too small");
   dim3 g1(ceil_div(tmp_rows, 16), M);
-  pil_horizontal_kernel<<<g1, 128, 0, st>>>(src, crop_off, crop_geom, out_w, tmp_rows, (uint8_t*)ws);
+  { ProfScope _ps("pil_horizontal_kernel", st); pil_horizontal_kernel<<<g1, 128, 0, st>>>(src, crop_off, crop_geom, out_w, tmp_rows, (uint8_t*)ws); }
   RB_LAUNCH_CHECK("pil_horizontal_kernel");
   dim3 g2(out_h, M);
-  pil_vertical_kernel<<<g2, 128, 0, st>>>((const uint8_t*)ws, crop_geom, out_h, out_w, tmp_rows, mean[0], mean[1],
-                                          mean[2], sd[0], sd[1], sd[2], out_u8, out_f);
+  { ProfScope _ps("pil_vertical_kernel", st); pil_vertical_kernel<<<g2, 128, 0, st>>>((const uint8_t*)ws, crop_geom, out_h, out_w, tmp_rows, mean[0], mean[1],
+                                          mean[2], sd[0], sd[1], sd[2], out_u8, out_f); }
   RB_LAUNCH_CHECK("pil_vertical_kernel");
   return REIDB200_OK;
 }
@@ -240,8 +240,8 @@ extern "C" int reidb200_crop_resize_norm_ws(const uint8_t* src, const int64_t* c
   cudaStream_t st = (cudaStream_t)stream;
   if (mode == REIDB200_RESIZE_CV_LINEAR) {
     dim3 grid(ceil_div(out_h, CV_ROWS), M);
-    crop_cv_linear_kernel<<<grid, 128, 0, st>>>(src, crop_off, crop_geom, out_h, out_w, mean_host[0], mean_host[1],
-                                                mean_host[2], std_host[0], std_host[1], std_host[2], out);
+    { ProfScope _ps("crop_cv_linear_kernel", st); crop_cv_linear_kernel<<<grid, 128, 0, st>>>(src, crop_off, crop_geom, out_h, out_w, mean_host[0], mean_host[1],
+                                                mean_host[2], std_host[0], std_host[1], std_host[2], out); }
     RB_LAUNCH_CHECK("crop_cv_linear_kernel");
     return REIDB200_OK;
   }

@@ -174,9 +174,9 @@ extern "C" int reidb200_eval_cmc_map(const float* mat, int Q, int G, int64_t ldm
   if (out_first) first = out_first;
   RB_CUDA(cudaMemsetAsync(hist, 0, (size_t)G * sizeof(int32_t), st));
   RB_CUDA(cudaMemsetAsync(status, 0, 64 * sizeof(int32_t), st));
-  eval_query_kernel<<<Q, EV_THREADS, 0, st>>>(mat, G, ldm, descending, ql, qc, gl, gc, apq, first, hist, status);
+  { ProfScope _ps("eval_query_kernel", st); eval_query_kernel<<<Q, EV_THREADS, 0, st>>>(mat, G, ldm, descending, ql, qc, gl, gc, apq, first, hist, status); }
   RB_LAUNCH_CHECK("eval_query_kernel");
-  eval_finalize_kernel<<<1, 1024, 0, st>>>(hist, apq, Q, G, out_cmc, out_ap);
+  { ProfScope _ps("eval_finalize_kernel", st); eval_finalize_kernel<<<1, 1024, 0, st>>>(hist, apq, Q, G, out_cmc, out_ap); }
   RB_LAUNCH_CHECK("eval_finalize_kernel");
   return REIDB200_OK;
 }

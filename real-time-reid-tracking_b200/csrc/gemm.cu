@@ -44,8 +44,8 @@ int pack_rows_launch(const float* x, int rows, int64_t ldx, int d, void* packed,
   if (rows == 0) return REIDB200_OK;
   const int dp = padded_dim(d);
   const int warps_per_block = 8;
-  pack_rows_kernel<<<ceil_div(rows, warps_per_block), warps_per_block * 32, 0, st>>>(
-      x, rows, ldx, d, dp, static_cast<__nv_bfloat16*>(packed), sqnorm);
+  { ProfScope _ps("pack_rows_kernel", st); pack_rows_kernel<<<ceil_div(rows, warps_per_block), warps_per_block * 32, 0, st>>>(
+      x, rows, ldx, d, dp, static_cast<__nv_bfloat16*>(packed), sqnorm); }
   RB_LAUNCH_CHECK("pack_rows_kernel");
   return REIDB200_OK;
 }
@@ -312,7 +312,7 @@ int gemm_split_launch(const void* packedA, const float* xx, int m, const void* p
   a.kind = kind; a.xx = xx; a.yy = yy; a.out = out; a.ldo = ldo;
   const long long total = (long long)a.tiles_m * a.tiles_n;
   const int grid = (int)(total < num_sms() ? total : num_sms());
-  gemm_split_tc_kernel<<<grid, GEMM_THREADS, GEMM_SMEM, st>>>(tmA, tmB, a);
+  { ProfScope _ps("gemm_split_tc_kernel", st); gemm_split_tc_kernel<<<grid, GEMM_THREADS, GEMM_SMEM, st>>>(tmA, tmB, a); }
   RB_LAUNCH_CHECK("gemm_split_tc_kernel");
   return REIDB200_OK;
 }
@@ -374,7 +374,7 @@ extern "C" int reidb200_distmat_simt(const float* x, int m, int64_t ldx, const f
   if (m == 0 || n == 0) return REIDB200_OK;
   RB_REQUIRE(x && y && out && m > 0 && n > 0 && d > 0 && kind >= 0 && kind <= 3, "distmat_simt: bad argument");
   dim3 grid(ceil_div(n, 16), ceil_div(m, 16));
-  distmat_simt_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(x, m, ldx, y, n, ldy, d, kind, out, ldo);
+  { ProfScope _ps("distmat_simt_kernel", (cudaStream_t)stream); distmat_simt_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(x, m, ldx, y, n, ldy, d, kind, out, ldo); }
   RB_LAUNCH_CHECK("distmat_simt_kernel");
   return REIDB200_OK;
 }

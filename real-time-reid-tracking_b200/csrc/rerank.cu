@@ -415,29 +415,29 @@ static int jaccard_sparse_stages(const int32_t* rank, const float* sql2, int64_t
     attr = true;
   }
   const int wpb = 8;
-  krecip_kernel<<<ceil_div(N, wpb), wpb * 32, 0, st>>>(rank, N, k1, k1, k1, w.rfull, w.rfull_cnt);
+  { ProfScope _ps("krecip_kernel(k1)", st); krecip_kernel<<<ceil_div(N, wpb), wpb * 32, 0, st>>>(rank, N, k1, k1, k1, w.rfull, w.rfull_cnt); }
   RB_LAUNCH_CHECK("krecip_kernel(k1)");
-  krecip_kernel<<<ceil_div(N, wpb), wpb * 32, 0, st>>>(rank, N, k1, d.wh, d.wh, w.rhalf, w.rhalf_cnt);
+  { ProfScope _ps("krecip_kernel(k1/2)", st); krecip_kernel<<<ceil_div(N, wpb), wpb * 32, 0, st>>>(rank, N, k1, d.wh, d.wh, w.rhalf, w.rhalf_cnt); }
   RB_LAUNCH_CHECK("krecip_kernel(k1/2)");
-  expand_v_kernel<<<N, EXP_THREADS, (size_t)d.cap1 * 16, st>>>(w.rfull, w.rfull_cnt, k1, w.rhalf, w.rhalf_cnt, d.wh, sql2,
+  { ProfScope _ps("expand_v_kernel", st); expand_v_kernel<<<N, EXP_THREADS, (size_t)d.cap1 * 16, st>>>(w.rfull, w.rfull_cnt, k1, w.rhalf, w.rhalf_cnt, d.wh, sql2,
                                                                 lds, sqnorm, N, d.cap1, use_f16, w.v1cols, w.v1vals,
-                                                                w.v1cnt);
+                                                                w.v1cnt); }
   RB_LAUNCH_CHECK("expand_v_kernel");
   if (k2 > 1) {
-    qexpand_kernel<<<N, QE_THREADS, (size_t)d.cap2 * 12, st>>>(rank, k1, k2, w.v1cols, w.v1vals, w.v1cnt, d.cap1, d.cap2,
-                                                               use_f16, w.v2cols, w.v2vals, w.v2cnt);
+    { ProfScope _ps("qexpand_kernel", st); qexpand_kernel<<<N, QE_THREADS, (size_t)d.cap2 * 12, st>>>(rank, k1, k2, w.v1cols, w.v1vals, w.v1cnt, d.cap1, d.cap2,
+                                                               use_f16, w.v2cols, w.v2vals, w.v2cnt); }
     RB_LAUNCH_CHECK("qexpand_kernel");
   }
   RB_CUDA(cudaMemsetAsync(w.colcnt, 0, (size_t)(N + 1) * sizeof(int32_t), st));
-  inv_count_kernel<<<N, 128, 0, st>>>(w.v2cols, w.v2vals, w.v2cnt, N, d.cap2, w.colcnt);
+  { ProfScope _ps("inv_count_kernel", st); inv_count_kernel<<<N, 128, 0, st>>>(w.v2cols, w.v2vals, w.v2cnt, N, d.cap2, w.colcnt); }
   RB_LAUNCH_CHECK("inv_count_kernel");
-  inv_scan_kernel<<<1, 1024, 0, st>>>(w.colcnt, N, w.colptr, w.cursor);
+  { ProfScope _ps("inv_scan_kernel", st); inv_scan_kernel<<<1, 1024, 0, st>>>(w.colcnt, N, w.colptr, w.cursor); }
   RB_LAUNCH_CHECK("inv_scan_kernel");
-  inv_fill_kernel<<<N, 128, 0, st>>>(w.v2cols, w.v2vals, w.v2cnt, N, d.cap2, w.cursor, w.inv_row, w.inv_val);
+  { ProfScope _ps("inv_fill_kernel", st); inv_fill_kernel<<<N, 128, 0, st>>>(w.v2cols, w.v2vals, w.v2cnt, N, d.cap2, w.cursor, w.inv_row, w.inv_val); }
   RB_LAUNCH_CHECK("inv_fill_kernel");
-  jaccard_rows_kernel<<<nrows, JR_THREADS, (size_t)N * sizeof(float), st>>>(
+  { ProfScope _ps("jaccard_rows_kernel", st); jaccard_rows_kernel<<<nrows, JR_THREADS, (size_t)N * sizeof(float), st>>>(
       w.v2cols, w.v2vals, w.v2cnt, d.cap2, w.colptr, w.inv_row, w.inv_val, N, row0, col0, ncols, lambda_value, sql2, lds,
-      use_f16, out, ldo);
+      use_f16, out, ldo); }
   RB_LAUNCH_CHECK("jaccard_rows_kernel");
   return REIDB200_OK;
 }
@@ -523,7 +523,7 @@ extern "C" int reidb200_k_reciprocal(const int32_t* rank, int N, int k1_cols, in
                                      void* stream) {
   RB_REQUIRE(rank && out_idx && out_cnt && N > 0 && k1_cols > 0 && k > 0, "k_reciprocal: bad argument");
   const int kc = k + 1 < k1_cols ? k + 1 : k1_cols;
-  krecip_kernel<<<ceil_div(N, 8), 256, 0, (cudaStream_t)stream>>>(rank, N, k1_cols, kc, k + 1, out_idx, out_cnt);
+  { ProfScope _ps("krecip_kernel", (cudaStream_t)stream); krecip_kernel<<<ceil_div(N, 8), 256, 0, (cudaStream_t)stream>>>(rank, N, k1_cols, kc, k + 1, out_idx, out_cnt); }
   RB_LAUNCH_CHECK("krecip_kernel");
   return REIDB200_OK;
 }

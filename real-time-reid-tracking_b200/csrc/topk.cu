@@ -199,8 +199,8 @@ int topk_rows_launch(const float* vals, int rows, int cols, int64_t ldv, const i
   if (rows == 0 || k == 0) return REIDB200_OK;
   RB_REQUIRE(k > 0 && k <= TOPK_MAX_K, "topk: k=%d outside [1,%d]", k, TOPK_MAX_K);
   RB_REQUIRE(cols >= 0 && ldv >= cols, "topk: bad cols/ld");
-  topk_rows_kernel<<<rows, TOPK_THREADS, 0, st>>>(vals, cols, ldv, cand_i, k, descending, index_base, out_d, out_i,
-                                                  idx64);
+  { ProfScope _ps("topk_rows_kernel", st); topk_rows_kernel<<<rows, TOPK_THREADS, 0, st>>>(vals, cols, ldv, cand_i, k, descending, index_base, out_d, out_i,
+                                                  idx64); }
   RB_LAUNCH_CHECK("topk_rows_kernel");
   return REIDB200_OK;
 }

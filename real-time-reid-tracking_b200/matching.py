@@ -1,0 +1,144 @@
+"""Drop-in for the StrongSORT half of yolov8_tracking/boxmot/utils/matching.py: chi2inv95 (:12-22), _pdist
+(:255-275), _cosine_distance (:278-298), _nn_cosine_distance (:321-339), NearestNeighborDistanceMetric (:342-409).
+
+The per-track sample lists live in a device-resident ring buffer (ops.Gallery); `distance` is one launch of the
+fused association kernel without the gate, returning the same float64 [T,M] matrix of float32 values.
+"""
+from __future__ import annotations
+
+import numpy as np
+import torch
+
+from . import _lib as L
+from . import ops
+
+chi2inv95 = {1: 3.8415, 2: 5.9915, 3: 7.8147, 4: 9.4877, 5: 11.070, 6: 12.592, 7: 14.067, 8: 15.507, 9: 16.919}
+
+
+def _pdist(a, b):
+    """Pair-wise squared distance, clipped at 0 (matching.py:255-275); float32 values from the distmat kernel."""
+    a, b = np.asarray(a), np.asarray(b)
+    if len(a) == 0 or len(b) == 0:
+        return np.zeros((len(a), len(b)))
+    r2 = ops.distmat(a, b, "sql2").cpu().numpy()
+    return np.clip(r2, 0.0, float(np.inf))
+
+
+def _cosine_distance(a, b, data_is_normalized=False):
+    """1 - a^.b^T, rows re-normalised unless data_is_normalized (matching.py:278-298)."""
+    out = ops.cosine_distance(a, b, data_is_normalized)
+    return out if isinstance(a, torch.Tensor) and a.is_cuda else out.cpu().numpy()
+
+
+def _nn_cosine_distance(x, y):
+    """Smallest cosine distance of every row of y to a sample in x (matching.py:321-339)."""
+    d = ops.cosine_distance(np.asarray(x, np.float32), np.asarray(y, np.float32))
+    return d.min(dim=0)[0].cpu().numpy()
+
+
+def _nn_euclidean_distance(x, y):
+    """The reference's version is broken (torch.min on an ndarray); fixed by restatement."""
+    return np.maximum(0.0, _pdist(x, y).min(axis=0))
+
+
+class NearestNeighborDistanceMetric(object):
+    """Per-target nearest-neighbour appearance metric with a device-resident gallery.
+
+    samples: dict target -> slot; the rows themselves stay on the GPU ([slots, budget, d] ring buffer created on
+    the first partial_fit, grown by doubling).  With budget=None the reference keeps every sample; here the
+    ring holds `max_unbounded` rows (documented limit)."""
+
+    def __init__(self, metric, matching_threshold, budget=None, max_tracks=512, max_unbounded=1024):
+        if metric not in ("euclidean", "cosine"):
+            raise ValueError("Invalid metric; must be either 'euclidean' or 'cosine'")
+        if metric == "euclidean":
+            raise NotImplementedError("only 'cosine' is ever used by StrongSORT (strong_sort.py:32); "
+                                      "the reference's euclidean path is broken (SURVEY F11)")
+        self.matching_threshold = matching_threshold
+        self.budget = budget
+        self._ring = int(budget) if budget is not None else int(max_unbounded)
+        self._slots_cap = int(max_tracks)
+        self._gallery = None
+        self._slot_of = {}      # target id -> slot
+        self._free = []
+
+    # -- the reference exposes `samples` as dict id -> list of rows; here: id -> stored (normalised) rows, lazily
+    @property
+    def samples(self):
+        return _SamplesView(self)
+
+    def _ensure(self, d):
+        if self._gallery is None:
+            self._gallery = ops.Gallery(self._slots_cap, self._ring, d)
+            self._free = list(range(self._slots_cap - 1, -1, -1))
+        elif self._gallery.d != d:
+            raise ValueError("feature dimension changed from %d to %d" % (self._gallery.d, d))
+
+    def _slot(self, target):
+        s = self._slot_of.get(target)
+        if s is None:
+            if not self._free:
+                raise NotImplementedError("more than %d simultaneously active tracks" % self._slots_cap)
+            s = self._free.pop()
+            self._slot_of[target] = s
+        return s
+
+    def partial_fit(self, features, targets, active_targets):
+        """Append features to their targets (last `budget` survive) and forget inactive targets (matching.py:374-389)."""
+        targets = [int(t) for t in np.asarray(targets).reshape(-1)]
+        if len(targets):
+            feats = L.as_f32_cuda(features)
+            self._ensure(feats.shape[1])
+            slots = np.array([self._slot(t) for t in targets], np.int32)
+            self._gallery.partial_fit(feats, slots)
+        active = set(int(t) for t in active_targets)
+        dead = [t for t in self._slot_of if t not in active]
+        if dead:
+            ds = np.array([self._slot_of.pop(t) for t in dead], np.int32)
+            self._gallery.reset_slots(ds)
+            self._free.extend(int(s) for s in ds)
+
+    def slots_for(self, targets):
+        return np.array([self._slot_of[int(t)] for t in np.asarray(targets).reshape(-1)], np.int32)
+
+    def distance_device(self, features, targets):
+        """f64 [T,M] CUDA tensor (no host sync)."""
+        T = len(targets)
+        feats = L.as_f32_cuda(features)
+        M = feats.shape[0]
+        if T == 0 or M == 0:
+            return torch.zeros((T, M), dtype=torch.float64, device=feats.device)
+        slots = self.slots_for(targets)
+        zeros8 = torch.zeros((T, 8), dtype=torch.float64, device=feats.device)
+        tlwh = torch.ones((M, 4), dtype=torch.float32, device=feats.device)
+        app, _, _ = ops.assoc_frame(self._gallery, feats, tlwh, slots, zeros8, None, np.ones(T, np.int32), gate=False,
+                                    want_iou=False)
+        return app
+
+    def distance(self, features, targets):
+        """np.ndarray float64 [len(targets), len(features)] (matching.py:391-409)."""
+        return self.distance_device(features, targets).cpu().numpy()
+
+
+class _SamplesView(object):
+    def __init__(self, metric):
+        self._m = metric
+
+    def __contains__(self, k):
+        return int(k) in self._m._slot_of
+
+    def __len__(self):
+        return len(self._m._slot_of)
+
+    def keys(self):
+        return self._m._slot_of.keys()
+
+    def __iter__(self):
+        return iter(self._m._slot_of)
+
+    def __getitem__(self, k):
+        """Stored rows of target k, oldest first (L2-normalised: the metric re-normalises anyway)."""
+        m = self._m
+        slot = m._slot_of[int(k)]
+        n = int(m._gallery.counts()[slot].item())
+        return list(m._gallery.read_slot(slot)[:n].cpu().numpy())
