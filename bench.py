@@ -1,0 +1,369 @@
+"""bench.py -- the reference's headline metric on B200: Q x G pairs/s of the Market1501-shaped evaluation INCLUDING
+k-reciprocal re-ranking (BASELINE.json configs[1]: 3368 query x 15913 gallery, 512-d, k1=20 k2=6 lambda=0.3), plus the
+MOT16/MOT20-shaped crop + association microseconds per frame (reported under "assoc" in the same JSON line).
+
+  python bench.py --gpus N --steps K --warmup W            (N > 1: launched under torch.distributed.run, one rank per GPU)
+  python bench.py --impl reference --steps K --warmup W    (the reference algorithm's CPU port, oracle/, on the host cores)
+
+A step = one pass of the hot path over one batch: features resident in HBM -> pack -> N x N squared-L2 tcgen05 GEMM ->
+top-k1 -> k-reciprocal sets -> sparse V -> query expansion -> inverted index -> Jaccard + lambda blend (Q x G block) ->
+CMC/mAP.  At N GPUs every rank evaluates its own Market-shaped set (independent evaluation sets: no data-path
+collective, weak scaling); the timed region is bracketed by barrier + synchronize and the maximum over ranks is used.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+import numpy as np  # noqa: E402
+import torch  # noqa: E402
+
+Q_FULL, G_FULL, D_FULL, IDS_FULL = 3368, 15913, 512, 751
+K1, K2, LAMBDA = 20, 6, 0.3
+METRIC = "QxG pairs/s incl. k-reciprocal re-rank (Market1501-shaped eval)"
+
+
+def _peaks():
+    try:
+        return json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))), "measured"
+    except Exception:
+        return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0}, "fallback"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
+
+    FIELDS = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+              "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+              "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index=0):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.FIELDS,
+                                          "--format=csv,noheader,nounits", "-lms", "50"], stdout=subprocess.PIPE,
+                                         stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._pump, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.rows.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.06)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            p = [x.strip() for x in r.split(",")]
+            if len(p) < 7:
+                continue
+            try:
+                sm.append(float(p[0])); mx.append(float(p[1]))
+            except ValueError:
+                continue
+            for n, v in zip(names, p[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# --------------------------------------------------------------------------------------------- our arm
+def _dist_env():
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    return rank, world, local
+
+
+def _timed(fn, steps, sync):
+    """CUDA-event time (ms) of `steps` calls of fn on the current stream, synchronised on both sides."""
+    sync()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        fn()
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1)
+    sync()
+    return ms
+
+
+def bench_assoc(steps, warmup):
+    """MOT16 / MOT20-shaped crop + association, microseconds per frame (device resident; and end to end)."""
+    import reidb200  # noqa: F401
+    from reidb200 import _lib as L, matching, ops, preprocess, synth, tracker
+
+    out = {}
+    dev = torch.device("cuda", torch.cuda.current_device())
+    for name, M, T in (("mot16", 30, 100), ("mot20", 200, 300)):
+        fr = synth.mot_frame(M=M, T=T, budget=100, D=512, seed=7)
+        H, W = fr["img"].shape[:2]
+        xyxy = preprocess.xywh_to_xyxy(fr["det_xywh"], W, H)
+        ok = (xyxy[:, 2] > xyxy[:, 0]) & (xyxy[:, 3] > xyxy[:, 1])
+        xyxy = xyxy[ok]
+        metric = matching.NearestNeighborDistanceMetric("cosine", 0.2, 100, max_tracks=T)
+        counts = [len(s) for s in fr["samples"]]
+        metric.partial_fit(np.concatenate(fr["samples"], 0), np.repeat(np.arange(T), counts), list(range(T)))
+        frame = torch.from_numpy(fr["img"]).to(dev)
+        off, geom = preprocess._geometry_from_xyxy(xyxy, W)
+        off_d, geom_d = torch.from_numpy(off).to(dev), torch.from_numpy(geom).to(dev)
+        crops = torch.empty((len(xyxy), 3, 256, 128), dtype=torch.float32, device=dev)
+        det_feat = torch.from_numpy(fr["det_feat"]).to(dev)
+        det_tlwh = torch.from_numpy(fr["det_tlwh"]).to(dev)
+        slots = torch.from_numpy(metric.slots_for(np.arange(T))).to(dev)
+        mean = torch.from_numpy(fr["trk_mean"]).to(dev)
+        SI = torch.from_numpy(fr["trk_SI"].reshape(T, 16)).to(dev)
+        tsu = torch.from_numpy(fr["trk_tsu"]).to(dev)
+        app = torch.empty((T, M), dtype=torch.float64, device=dev)
+        iou = torch.empty((T, M), dtype=torch.float64, device=dev)
+        lib = L.load()
+        mean3 = ops._f3((0.5, 0.5, 0.5))
+
+        def frame_step():
+            L.check(lib.reidb200_crop_resize_norm(frame.data_ptr(), off_d.data_ptr(), geom_d.data_ptr(), len(xyxy), 256, 128,
+                                                  mean3, mean3, 0, crops.data_ptr(), L.stream_ptr()))
+            L.check(lib.reidb200_assoc_frame(metric._gallery._h, det_feat.data_ptr(), det_feat.stride(0), det_tlwh.data_ptr(), M,
+                                             slots.data_ptr(), mean.data_ptr(), SI.data_ptr(), tsu.data_ptr(), T, 0.995, 0.2, 0.7,
+                                             0, 3, app.data_ptr(), None, iou.data_ptr(), L.stream_ptr()))
+
+        n = max(steps * 20, 100)
+        for _ in range(max(warmup, 3)):
+            frame_step()
+        L.profile_enable(True)
+        ms = _timed(frame_step, n, torch.cuda.synchronize)
+        prof = L.profile_read()
+        L.profile_enable(False)
+        # CUDA-graph replay of the same two launches (what a per-stream tracker loop would do)
+        g = torch.cuda.CUDAGraph()
+        s = torch.cuda.Stream()
+        s.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(s):
+            frame_step()
+            torch.cuda.synchronize()
+            with torch.cuda.graph(g, stream=s):
+                frame_step()
+        torch.cuda.synchronize()
+        ms_graph = _timed(g.replay, n, torch.cuda.synchronize)
+        # end to end through the public API: host boxes / detections / track state in, cost matrices out
+        def e2e_step():
+            c = preprocess.preprocess_frame(frame, xyxy, out=crops)
+            a, _, i = tracker.frame_costs(metric, det_feat, fr["det_tlwh"], np.arange(T), np.ones(T, bool), fr["trk_mean"],
+                                          fr["trk_SI"], fr["trk_tsu"], 0.995, 0.2, 0.7)
+            return torch.stack([a, i]).cpu()
+
+        for _ in range(3):
+            e2e_step()
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for _ in range(n):
+            e2e_step()
+        torch.cuda.synchronize()
+        e2e_us = (time.perf_counter() - t0) / n * 1e6
+        crop_us = prof["crop_cv_linear_kernel"][1] / prof["crop_cv_linear_kernel"][0] * 1e3
+        assoc_us = prof["assoc_frame_kernel"][1] / prof["assoc_frame_kernel"][0] * 1e3
+        crop_bytes = len(xyxy) * 3 * 256 * 128 * 4 + int((geom[:, 0].astype(np.int64) * geom[:, 1] * 3).sum())
+        gal_bytes = sum(counts) * 512 * 4 + M * 512 * 4 + 2 * T * M * 8
+        out[name] = {"dets": int(M), "tracks": int(T), "us_per_frame": ms / n * 1e3, "us_per_frame_cuda_graph": ms_graph / n * 1e3,
+                     "e2e_us_per_frame": e2e_us, "crop_kernel_us": crop_us, "assoc_kernel_us": assoc_us,
+                     "crop_gbs": crop_bytes / crop_us / 1e3, "assoc_gbs": gal_bytes / assoc_us / 1e3,
+                     "assoc_tflops": 2.0 * sum(counts) * M * 512 / assoc_us / 1e6}
+    return out
+
+
+# --------------------------------------------------------------------------------------------- CPU port / reference arm
+def cpu_sample(scale=4):
+    """A bounded sample of the same workload: Market-shaped set at 1/scale of the query/gallery/identity counts."""
+    import reidb200  # noqa: F401
+    from reidb200 import synth
+
+    Q, G, ids = Q_FULL // scale, G_FULL // scale, max(IDS_FULL // scale, 8)
+    return synth.market_like(Q=Q, G=G, D=D_FULL, n_ids=ids, seed=0), Q, G
+
+
+def cpu_step(d):
+    """The reference algorithm on the host: exact k-NN, compute_jaccard_distance, lambda blend, CMC/mAP (oracle port)."""
+    from oracle import reid_oracle as O
+
+    dist = O.re_ranking_from_feats(d["qf"], d["gf"], K1, K2, LAMBDA)
+    return O.evaluate_all_from_dist(dist, d["ql"], d["qc"], d["gl"], d["gc"])
+
+
+def run_reference(args):
+    rank, world, _ = _dist_env()
+    if rank != 0:
+        return
+    torch.set_num_threads(os.cpu_count() or 1)
+    d, Q, G = cpu_sample()
+    for _ in range(min(args.warmup, 1)):
+        cpu_step(d)
+    t0 = time.perf_counter()
+    steps = 0
+    for _ in range(args.steps):
+        cpu_step(d)
+        steps += 1
+        if time.perf_counter() - t0 > 240:  # keep the whole run within a few minutes
+            break
+    dt = time.perf_counter() - t0
+    v = steps * Q * G / dt
+    sample = "Market-shaped %dx%d (1/4 of every count), D=512, numpy port of the reference algorithm" % (Q, G)
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": v, "unit": "pairs/s", "n_gpus": args.gpus, "steps": steps,
+        "warmup": min(args.warmup, 1), "ms_per_step": dt / steps * 1e3, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": "market1501_rerank_k20_6_l0.3 (bounded sample %dx%d)" % (Q, G), "k1": K1, "k2": K2,
+                   "lambda": LAMBDA},
+        "cpu_baseline": {"value": v, "unit": "pairs/s", "cores": os.cpu_count(), "kind": "port", "sample": sample},
+        "e2e": {"value": v, "unit": "pairs/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }))
+
+
+def run_ours(args):
+    import reidb200  # noqa: F401
+    from reidb200 import _lib as L, evaluate, ops, synth
+
+    rank, world, local = _dist_env()
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=dev)
+    L.require_device()
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    d = synth.market_like(Q=Q_FULL, G=G_FULL, D=D_FULL, n_ids=IDS_FULL, seed=rank)
+    Q, G, N = Q_FULL, G_FULL, Q_FULL + G_FULL
+    merged_host = torch.from_numpy(np.concatenate([d["gf"], d["qf"]], 0)).pin_memory()
+    lab_host = {k: torch.from_numpy(d[k].astype(np.int32)).pin_memory() for k in ("ql", "qc", "gl", "gc")}
+    merged = merged_host.to(dev)
+    lab = {k: v.to(dev) for k, v in lab_host.items()}
+
+    def step():
+        dist_qg = ops.jaccard(merged, K1, K2, False, LAMBDA, rows=(G, Q), cols=(0, G))
+        return ops.eval_cmc_map(dist_qg, lab["ql"], lab["qc"], lab["gl"], lab["gc"], descending=False)
+
+    for _ in range(max(args.warmup, 3)):
+        cmc, ap = step()
+    barrier()
+    clocks = ClockSampler(local)
+    if rank == 0:
+        clocks.start()
+    L.profile_enable(True)
+    ms = _timed(step, args.steps, barrier)
+    prof = L.profile_read()
+    L.profile_enable(False)
+    clk = clocks.stop() if rank == 0 else None
+    t = torch.tensor([ms], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t.item())
+    value = world * args.steps * Q * G / (ms * 1e-3)
+
+    # ---- end to end through the public API: pinned host features + labels in, CMC + mAP out, every step
+    qf_h, gf_h = merged_host[G:], merged_host[:G]
+
+    def e2e_step():
+        return evaluate.evaluate_all_reranked(qf_h, lab_host["ql"], lab_host["qc"], gf_h, lab_host["gl"], lab_host["gc"], K1, K2,
+                                              LAMBDA, verbose=False)
+
+    for _ in range(2):
+        cmc_h, ap_h = e2e_step()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        cmc_h, ap_h = e2e_step()
+    torch.cuda.synchronize()
+    t = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    e2e_value = world * args.steps * Q * G / float(t.item())
+    h2d = merged_host.numel() * 4 + sum(v.numel() * 4 for v in lab_host.values())
+    d2h = G * 4 + 8
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    peaks, peak_kind = _peaks()
+    gemm_n, gemm_ms = prof.get("gemm_split_tc_kernel", (0, 0.0))
+    launches = sum(n for n, _ in prof.values())
+    share = {k: round(v[1] / ms, 4) for k, v in sorted(prof.items(), key=lambda kv: -kv[1][1])}
+    gemm_flops = 2.0 * N * N * D_FULL  # algorithmic (fp32-equivalent) flops of one launch: 2*D per pair over N x N
+    achieved = gemm_flops / (gemm_ms / max(gemm_n, 1) * 1e-3) / 1e12 if gemm_n else None
+    peak = peaks["bf16_tflops_sustained"] / 3.0  # three bf16 UMMAs per fp32-accurate product
+    line = {
+        "metric": METRIC, "value": value, "unit": "pairs/s", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+        "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+        "data": "synthetic",
+        "config": {"workload": "market1501_rerank_k20_6_l0.3", "queries": Q, "gallery": G, "dim": D_FULL, "k1": K1, "k2": K2,
+                   "lambda": LAMBDA, "parallelism": "independent evaluation sets per GPU" if world > 1 else "single GPU",
+                   "l2": "working set (1.49 GB distance matrix + 0.5 GB sparse tables per step) larger than L2"},
+        "clocks": clk,
+        "e2e": {"value": e2e_value, "unit": "pairs/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h)},
+        "gpu_launches": int(launches),
+        "roofline": {"kernel": "gemm_split_tc_kernel", "bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
+                     "frac": (achieved / peak) if achieved else None, "traffic": None,
+                     "peak_source": "%s bf16_tflops_sustained / 3 (bf16x3 split)" % peak_kind,
+                     "tensor_pipe_tflops": achieved * 3 if achieved else None},
+        "kernel_share_of_step": share,
+        "result": {"rank1": float(cmc_h[0]), "mAP": float(ap_h)},
+    }
+    if not args.no_assoc:
+        line["assoc"] = bench_assoc(args.steps, args.warmup)
+    if not args.no_cpu and world == 1:
+        dsmp, qs, gs = cpu_sample()
+        t0 = time.perf_counter()
+        cpu_step(dsmp)
+        dt = time.perf_counter() - t0
+        line["cpu_baseline"] = {"value": qs * gs / dt, "unit": "pairs/s", "cores": os.cpu_count(), "kind": "port",
+                                "sample": "Market-shaped %dx%d (1/4 of every count), one pass, numpy port of the reference" % (qs, gs)}
+    print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--no-assoc", action="store_true")
+    ap.add_argument("--no-cpu", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

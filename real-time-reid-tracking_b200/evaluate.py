@@ -115,3 +115,26 @@ def get_evaluate_result(model, dataloader_query, dataloader_gallery):
     labels_query, features_query, cams_query = get_feats(model, dataloader_query)
     labels_gallery, features_gallery, cams_gallery = get_feats(model, dataloader_gallery)
     return evaluate_all(features_query, labels_query, cams_query, features_gallery, labels_gallery, cams_gallery)
+
+
+def evaluate_all_reranked_device(qf, ql, qc, gf, gl, gc, k1=20, k2=6, lambda_value=0.3):
+    """Re-ranked evaluation, device resident: merged = cat(gallery, query) (image_reid_inference.py:270), Jaccard
+    re-ranking blended with the Euclidean distance, CMC/mAP on the re-ranked Q x G distance.  Returns CUDA tensors
+    (CMC f32[G], mAP f64[1]) without a host sync."""
+    qf = L.as_f32_cuda(qf)
+    gf = L.as_f32_cuda(gf, qf.device)
+    G, Q = gf.shape[0], qf.shape[0]
+    merged = torch.cat([gf, qf], 0)
+    dist = ops.jaccard(merged, k1, k2, False, lambda_value, rows=(G, Q), cols=(0, G))
+    return ops.eval_cmc_map(dist, _labels(ql), _labels(qc), _labels(gl), _labels(gc), descending=False)
+
+
+def evaluate_all_reranked(qf, ql, qc, gf, gl, gc, k1=20, k2=6, lambda_value=0.3, verbose=True):
+    """(CMC FloatTensor[G], mAP float) of the k-reciprocal re-ranked ranking; host arrays in, host results out."""
+    cmc, ap = evaluate_all_reranked_device(qf, ql, qc, gf, gl, gc, k1, k2, lambda_value)
+    CMC = cmc.cpu()
+    ap = float(ap.cpu()[0])
+    if verbose:
+        r = lambda k: float(CMC[k]) if CMC.numel() > k else float("nan")
+        print('Rank@1:%f Rank@5:%f Rank@10:%f mAP:%f' % (r(0), r(4), r(9), ap))
+    return CMC, ap

@@ -57,6 +57,8 @@ def preprocess_frame(frame, xyxy, size=(128, 256), norm=DEEPSORT_NORM, mode="cv_
         raise ValueError("frame must be a contiguous uint8 HxWx3 image")
     H, W = int(f.shape[0]), int(f.shape[1])
     off, geom = _geometry_from_xyxy(xyxy, W)
+    if len(off) == 0:
+        return torch.empty((0, 3, size[1], size[0]), dtype=torch.float32, device=dev)
     both = torch.from_numpy(np.concatenate([off.view(np.int32).reshape(-1, 2), geom], 1))  # one small H2D
     both = both.to(dev, non_blocking=True)
     off_d = both[:, :2].contiguous().view(torch.int64).reshape(-1)

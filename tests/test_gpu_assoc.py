@@ -31,9 +31,9 @@ def test_misc_free_functions(rb, golden):
     g = golden("assoc_misc")
     assert np.array_equal(IM.iou(g["bbox"], g["cands"]), g["iou"])      # fp64, bit-exact
     assert np.array_equal(IM.diou(g["bbox"], g["cands"]), g["diou"])
-    np.testing.assert_allclose(MT._cosine_distance(g["a"], g["b"]), g["cosine"], atol=1e-6)
+    np.testing.assert_allclose(MT._cosine_distance(g["a"], g["b"]), g["cosine"], rtol=1e-4, atol=1e-5)
     np.testing.assert_allclose(MT._pdist(g["a"], g["b"]), g["pdist"], atol=1e-4)
-    np.testing.assert_allclose(MT._nn_cosine_distance(g["a"], g["b"]), g["nn_cosine"], atol=1e-6)
+    np.testing.assert_allclose(MT._nn_cosine_distance(g["a"], g["b"]), g["nn_cosine"], rtol=1e-4, atol=1e-5)
     assert MT._pdist(np.zeros((0, 4)), g["b"][:, :4]).shape == (0, 5)
     with pytest.raises(ValueError):
         MT.NearestNeighborDistanceMetric("manhattan", 0.2, 5)

@@ -6,7 +6,7 @@ rc=0
 timeout 300 python __graft_entry__.py smoke > gpurun_out/smoke.log 2>&1; echo "smoke rc=$?" | tee -a gpurun_out/summary.txt
 for t in tests/test_gpu_dist.py tests/test_gpu_crop.py tests/test_gpu_rerank.py tests/test_gpu_assoc.py; do
   n=$(basename $t .py)
-  timeout 600 python -m pytest $t -q -m gpu -x --timeout=300 > gpurun_out/$n.log 2>&1
+  timeout 600 python -m pytest $t -q -m gpu --timeout=300 > gpurun_out/$n.log 2>&1
   r=$?; echo "$n rc=$r" | tee -a gpurun_out/summary.txt
   [ $r -ne 0 ] && rc=1
   tail -5 gpurun_out/$n.log
