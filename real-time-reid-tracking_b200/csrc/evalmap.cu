@@ -10,18 +10,32 @@
 namespace reidb200 {
 
 constexpr int EV_THREADS = 256;
-constexpr int EV_GOOD_CAP = 2048;
+constexpr int EV_GOOD_CAP = 1024;
 
 __device__ __forceinline__ uint32_t ev_key(float v, int descending) {
   const uint32_t u = float_to_ordered(v);
   return descending ? ~u : u;  // smaller key = ranked earlier
 }
 
+// Key of gallery item j as ranked for this query: junk items (label -1, or same id & same camera,
+// evaluate.py:71-72) get the largest key so that they are never counted.
+__device__ __forceinline__ uint32_t ev_masked_key(const float* row, const int32_t* gl, const int32_t* gc, int j,
+                                                  int32_t my_l, int32_t my_c, int descending) {
+  const int32_t l = __ldg(gl + j);
+  const bool junk = (l == -1) || (l == my_l && __ldg(gc + j) == my_c);
+  return junk ? 0xffffffffu : ev_key(__ldg(row + j), descending);
+}
+
+// One CTA per query.  Pass 1 stages the junk-masked keys of the whole score row in shared memory (when it
+// fits: G * 4 bytes of dynamic smem) and collects the good items; pass 2 counts, for four good items per warp at
+// a time, the non-junk items ranked before them.
+template <bool SMEM_ROW>
 __global__ void __launch_bounds__(EV_THREADS)
 eval_query_kernel(const float* __restrict__ mat, int G, int64_t ldm, int descending, const int32_t* __restrict__ ql,
                   const int32_t* __restrict__ qc, const int32_t* __restrict__ gl, const int32_t* __restrict__ gc,
                   double* __restrict__ ap_q, int32_t* __restrict__ first, int32_t* __restrict__ hist,
                   int32_t* __restrict__ status) {
+  extern __shared__ uint32_t skey[];
   __shared__ int32_t gcol[EV_GOOD_CAP];
   __shared__ uint32_t gkey[EV_GOOD_CAP];
   __shared__ int32_t gpos[EV_GOOD_CAP];
@@ -36,20 +50,31 @@ eval_query_kernel(const float* __restrict__ mat, int G, int64_t ldm, int descend
   if (tid == 0) s_ngood = 0;
   __syncthreads();
 
-  // good = same id & different camera (evaluate.py:66-70)
-  for (int j0 = 0; j0 < G; j0 += EV_THREADS) {
-    const int j = j0 + tid;
-    bool good = false;
-    if (j < G) good = (gl[j] == my_l) && (gc[j] != my_c);
-    const uint32_t ballot = __ballot_sync(0xffffffffu, good);
-    if (ballot) {
-      int base = 0;
-      if (lane == 0) base = atomicAdd(&s_ngood, __popc(ballot));
-      base = __shfl_sync(0xffffffffu, base, 0);
-      if (good) {
-        const int pos = base + __popc(ballot & ((1u << lane) - 1));
-        if (pos < EV_GOOD_CAP) { gcol[pos] = j; gkey[pos] = ev_key(row[j], descending); }
+  // good = same id & different camera (evaluate.py:66-70).  Four independent elements per thread per trip so
+  // that several loads are in flight; good items are rare, so a plain shared-memory counter collects them.
+  for (int j0 = 0; j0 < G; j0 += 4 * EV_THREADS) {
+    int32_t l[4];
+    float v[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int j = j0 + u * EV_THREADS + tid;
+      l[u] = j < G ? __ldg(gl + j) : -2;
+      v[u] = j < G ? __ldg(row + j) : 0.f;
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int j = j0 + u * EV_THREADS + tid;
+      if (j >= G) continue;
+      const uint32_t key = ev_key(v[u], descending);
+      bool junk = l[u] == -1;
+      if (l[u] == my_l) {
+        if (__ldg(gc + j) == my_c) junk = true;
+        else {
+          const int pos = atomicAdd(&s_ngood, 1);
+          if (pos < EV_GOOD_CAP) { gcol[pos] = j; gkey[pos] = key; }
+        }
       }
+      if (SMEM_ROW) skey[j] = junk ? 0xffffffffu : key;
     }
   }
   __syncthreads();
@@ -64,22 +89,31 @@ eval_query_kernel(const float* __restrict__ mat, int G, int64_t ldm, int descend
     return;
   }
 
-  // position of every good item among the non-junk items: one warp per good item
-  for (int e = warp; e < ngood; e += EV_THREADS / 32) {
-    const uint32_t key = gkey[e];
-    const int col = gcol[e];
-    int cnt = 0;
-    for (int j = lane; j < G; j += 32) {
-      const uint32_t kj = ev_key(__ldg(row + j), descending);
-      if (kj > key) continue;
-      // tie order of the reference: ascending argsort then [::-1] for scores, plain ascending for distances
-      if (kj == key && !(descending ? j > col : j < col)) continue;
-      const int32_t l = __ldg(gl + j);
-      const bool junk = (l == -1) || (l == my_l && __ldg(gc + j) == my_c);  // evaluate.py:71-72
-      cnt += !junk;
+  // position of every good item among the non-junk items: four good items per warp per sweep of the row.
+  // Tie order of the reference: ascending argsort then [::-1] for scores (higher index first), plain ascending
+  // (lower index first) for distances.
+  for (int e0 = warp * 4; e0 < ngood; e0 += (EV_THREADS / 32) * 4) {
+    uint32_t k[4];
+    int col[4], cnt[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const bool valid = e0 + u < ngood;
+      k[u] = valid ? gkey[e0 + u] : 0u;
+      col[u] = valid ? gcol[e0 + u] : -1;
+      cnt[u] = 0;
     }
-    cnt = warp_sum_i(cnt);
-    if (lane == 0) gpos[e] = cnt;
+#pragma unroll 4
+    for (int j = lane; j < G; j += 32) {
+      const uint32_t kj = SMEM_ROW ? skey[j] : ev_masked_key(row, gl, gc, j, my_l, my_c, descending);
+#pragma unroll
+      for (int u = 0; u < 4; ++u)
+        cnt[u] += (kj < k[u]) || (kj == k[u] && kj != 0xffffffffu && (descending ? j > col[u] : j < col[u]));
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int c = warp_sum_i(cnt[u]);
+      if (lane == 0 && e0 + u < ngood) gpos[e0 + u] = c;
+    }
   }
   __syncthreads();
 
@@ -136,9 +170,17 @@ eval_finalize_kernel(const int32_t* __restrict__ hist, const double* __restrict_
     if (tid == 1023) carry_s = total;
     __syncthreads();
   }
+  // mAP: the reference adds the per-query APs in query order (fp64); here 1024 contiguous chunks are summed in
+  // order and the chunk sums are added in order (same value up to ~1e-16 relative).
+  __shared__ double part[1024];
+  const int per = (Q + 1023) / 1024;
+  double acc = 0.0;
+  for (int q = tid * per; q < min(Q, (tid + 1) * per); ++q) acc += ap_q[q];
+  part[tid] = acc;
+  __syncthreads();
   if (tid == 0) {
     double ap = 0.0;
-    for (int q = 0; q < Q; ++q) ap += ap_q[q];
+    for (int t = 0; t < 1024; ++t) ap += part[t];
     *out_ap = ap / (double)Q;
   }
 }
@@ -174,7 +216,19 @@ extern "C" int reidb200_eval_cmc_map(const float* mat, int Q, int G, int64_t ldm
   if (out_first) first = out_first;
   RB_CUDA(cudaMemsetAsync(hist, 0, (size_t)G * sizeof(int32_t), st));
   RB_CUDA(cudaMemsetAsync(status, 0, 64 * sizeof(int32_t), st));
-  { ProfScope _ps("eval_query_kernel", st); eval_query_kernel<<<Q, EV_THREADS, 0, st>>>(mat, G, ldm, descending, ql, qc, gl, gc, apq, first, hist, status); }
+  const size_t row_bytes = (size_t)G * sizeof(uint32_t);
+  if (row_bytes <= 160 * 1024) {
+    static bool attr = false;
+    if (!attr) {
+      RB_CUDA(cudaFuncSetAttribute(eval_query_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
+      attr = true;
+    }
+    ProfScope _ps("eval_query_kernel", st);
+    eval_query_kernel<true><<<Q, EV_THREADS, row_bytes, st>>>(mat, G, ldm, descending, ql, qc, gl, gc, apq, first, hist, status);
+  } else {
+    ProfScope _ps("eval_query_kernel", st);
+    eval_query_kernel<false><<<Q, EV_THREADS, 0, st>>>(mat, G, ldm, descending, ql, qc, gl, gc, apq, first, hist, status);
+  }
   RB_LAUNCH_CHECK("eval_query_kernel");
   { ProfScope _ps("eval_finalize_kernel", st); eval_finalize_kernel<<<1, 1024, 0, st>>>(hist, apq, Q, G, out_cmc, out_ap); }
   RB_LAUNCH_CHECK("eval_finalize_kernel");

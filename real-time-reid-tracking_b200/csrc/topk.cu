@@ -3,7 +3,7 @@
 //
 // Selection, one CTA per row, no sorting of the row and no shared-memory atomics in the hot loop:
 //   pass 1  every thread keeps the minimum key of its strided sub-stream(s): G group minima
-//           (G = 256 or 1024 >= k).  The k-th smallest group minimum t0 is an upper bound of the k-th
+//           (G = 512 or 1024 >= k); the ordered keys are cached in shared memory when the row fits.  The k-th smallest group minimum t0 is an upper bound of the k-th
 //           smallest element (k distinct elements are <= t0) and is nearly tight because k << G.
 //   pass 2  re-read the row (L1/L2 hit) and append every element with key <= t0 to a small candidate
 //           list (warp-aggregated append).
@@ -14,9 +14,10 @@
 
 namespace reidb200 {
 
-constexpr int TOPK_THREADS = 256;
-constexpr int TOPK_CAP = 4096;   // candidate capacity (key + id in shared memory)
+constexpr int TOPK_THREADS = 512;
+constexpr int TOPK_CAP = 2048;   // candidate capacity (key + column in shared memory)
 constexpr int TOPK_MAX_K = 1024;
+constexpr int TOPK_SMEM_ROW_MAX = 36 * 1024;  // columns whose keys are cached in shared memory (144 KB)
 
 __device__ __forceinline__ uint32_t sel_key(float v, int descending) {
   const uint32_t u = float_to_ordered(v);
@@ -39,9 +40,28 @@ __device__ __forceinline__ int block_sum_int(int v, int* red) {
   return t;
 }
 
+// warp-aggregated append of (key, col) to the candidate list
+__device__ __forceinline__ void cand_append(bool take, uint32_t key, int col, int lane, int* s_count, uint32_t* ckey,
+                                            int32_t* ccol) {
+  const uint32_t ballot = __ballot_sync(0xffffffffu, take);
+  if (ballot) {
+    int base = 0;
+    if (lane == 0) base = atomicAdd(s_count, __popc(ballot));
+    base = __shfl_sync(0xffffffffu, base, 0);
+    if (take) {
+      const int pos = base + __popc(ballot & ((1u << lane) - 1));
+      if (pos < TOPK_CAP) { ckey[pos] = key; ccol[pos] = col; }
+    }
+  }
+}
+
+// SMEM_ROW: the ordered keys of the row are kept in dynamic shared memory by pass 1, so the row is read from
+// HBM exactly once; otherwise pass 2 re-reads it (L2).
+template <bool SMEM_ROW>
 __global__ void __launch_bounds__(TOPK_THREADS)
 topk_rows_kernel(const float* __restrict__ vals, int cols, int64_t ldv, const int64_t* __restrict__ cand_i, int k,
                  int descending, int64_t index_base, float* __restrict__ out_d, void* __restrict__ out_i, int idx64) {
+  extern __shared__ __align__(16) uint32_t rowkey[];
   __shared__ uint32_t ckey[TOPK_CAP];
   __shared__ int32_t ccol[TOPK_CAP];
   __shared__ uint32_t gmin[1024];
@@ -52,29 +72,37 @@ topk_rows_kernel(const float* __restrict__ vals, int cols, int64_t ldv, const in
   const int row = blockIdx.x;
   const float* v = vals + (size_t)row * ldv;
   const int64_t* ci = cand_i ? cand_i + (size_t)row * cols : nullptr;
-  const int tid = threadIdx.x;
+  const int tid = threadIdx.x, lane = tid & 31;
   const int kk = min(k, cols);
   float* od = out_d + (size_t)row * k;
 
-  // ---- pass 1: group minima
-  const int groups = (kk <= 256) ? 256 : 1024;
-  const int per_thread = groups / TOPK_THREADS;  // 1 or 4
-  uint32_t m[4] = {0xffffffffu, 0xffffffffu, 0xffffffffu, 0xffffffffu};
-  if (per_thread == 1) {
-    for (int c = tid; c < cols; c += TOPK_THREADS) m[0] = min(m[0], sel_key(__ldg(v + c), descending));
-  } else {
-    for (int c0 = 0; c0 < cols; c0 += 4 * TOPK_THREADS) {
-#pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        const int c = c0 + j * TOPK_THREADS + tid;
-        if (c < cols) m[j] = min(m[j], sel_key(__ldg(v + c), descending));
-      }
-    }
+  // ---- pass 1: group minima (128-bit loads when the row is 16-byte aligned)
+  const int groups = (kk <= TOPK_THREADS) ? TOPK_THREADS : 1024;
+  const int per_thread = groups / TOPK_THREADS;  // 1 or 2
+  const bool vec = (reinterpret_cast<uintptr_t>(v) & 15) == 0;
+  const int ncol4 = vec ? (cols >> 2) : 0;
+  const float4* v4 = reinterpret_cast<const float4*>(v);
+  uint32_t m[2] = {0xffffffffu, 0xffffffffu};
+#pragma unroll 4
+  for (int i = tid; i < ncol4; i += TOPK_THREADS) {
+    const float4 x = __ldg(v4 + i);
+    const uint32_t k0 = sel_key(x.x, descending), k1 = sel_key(x.y, descending);
+    const uint32_t k2 = sel_key(x.z, descending), k3 = sel_key(x.w, descending);
+    if (SMEM_ROW) *reinterpret_cast<uint4*>(rowkey + 4 * i) = make_uint4(k0, k1, k2, k3);
+    const int g = per_thread == 1 ? 0 : ((i / TOPK_THREADS) & 1);
+    m[g] = min(m[g], min(min(k0, k1), min(k2, k3)));
+  }
+  for (int c = ncol4 * 4 + tid; c < cols; c += TOPK_THREADS) {
+    const uint32_t kc = sel_key(__ldg(v + c), descending);
+    if (SMEM_ROW) rowkey[c] = kc;
+    const int g = per_thread == 1 ? 0 : ((c / TOPK_THREADS) & 1);
+    m[g] = min(m[g], kc);
   }
   for (int j = 0; j < per_thread; ++j) gmin[j * TOPK_THREADS + tid] = m[j];
   if (tid == 0) { s_count = 0; s_t0 = 0xffffffffu; }
   __syncthreads();
-  // k-th smallest group minimum (rank by (key, group index); exactly one group gets rank kk-1)
+  // k-th smallest group minimum (rank by (key, group index); exactly one group gets rank kk-1).  It is an upper
+  // bound of the k-th smallest element, nearly tight because k << number of groups.
   if (kk > 0) {
     for (int j = 0; j < per_thread; ++j) {
       const int g = j * TOPK_THREADS + tid;
@@ -91,36 +119,43 @@ topk_rows_kernel(const float* __restrict__ vals, int cols, int64_t ldv, const in
   uint32_t t0 = s_t0;
 
   // ---- pass 2: collect candidates <= t0
-  const int lane = tid & 31;
-  for (int c0 = 0; c0 < cols; c0 += TOPK_THREADS) {
-    const int c = c0 + tid;
-    uint32_t key = 0xffffffffu;
-    bool take = false;
-    if (c < cols) {
-      key = sel_key(__ldg(v + c), descending);
-      take = key <= t0;
+  if (SMEM_ROW) {
+    for (int c0 = 0; c0 < cols; c0 += TOPK_THREADS) {
+      const int c = c0 + tid;
+      const uint32_t key = c < cols ? rowkey[c] : 0xffffffffu;
+      cand_append(c < cols && key <= t0, key, c, lane, &s_count, ckey, ccol);
     }
-    const uint32_t ballot = __ballot_sync(0xffffffffu, take);
-    if (ballot) {
-      int base = 0;
-      if (lane == 0) base = atomicAdd(&s_count, __popc(ballot));
-      base = __shfl_sync(0xffffffffu, base, 0);
-      if (take) {
-        const int pos = base + __popc(ballot & ((1u << lane) - 1));
-        if (pos < TOPK_CAP) { ckey[pos] = key; ccol[pos] = c; }
+  } else {
+    for (int i0 = 0; i0 < ncol4; i0 += TOPK_THREADS) {
+      const int i = i0 + tid;
+      uint32_t key4[4] = {0xffffffffu, 0xffffffffu, 0xffffffffu, 0xffffffffu};
+      const bool in = i < ncol4;
+      if (in) {
+        const float4 x = __ldg(v4 + i);
+        key4[0] = sel_key(x.x, descending); key4[1] = sel_key(x.y, descending);
+        key4[2] = sel_key(x.z, descending); key4[3] = sel_key(x.w, descending);
       }
+      const bool any = in && (min(min(key4[0], key4[1]), min(key4[2], key4[3])) <= t0);
+      if (__ballot_sync(0xffffffffu, any) == 0) continue;  // warp-uniform
+#pragma unroll
+      for (int u = 0; u < 4; ++u) cand_append(in && key4[u] <= t0, key4[u], 4 * i + u, lane, &s_count, ckey, ccol);
+    }
+    for (int c0 = ncol4 * 4; c0 < cols; c0 += TOPK_THREADS) {
+      const int c = c0 + tid;
+      const uint32_t key = c < cols ? sel_key(__ldg(v + c), descending) : 0xffffffffu;
+      cand_append(c < cols && key <= t0, key, c, lane, &s_count, ckey, ccol);
     }
   }
   __syncthreads();
   int count = s_count;
 
   if (count > TOPK_CAP) {
-    // ---- fallback: exact k-th key by bisection, then ordered collection
+    // ---- fallback (heavy ties / adversarial order): exact k-th key by bisection, then ordered collection
     uint32_t lo = 0, hi = 0xffffffffu;  // invariant: count(key <= hi) >= kk, count(key <= lo-1) < kk
     while (lo < hi) {
       const uint32_t mid = lo + ((hi - lo) >> 1);
       int cnt = 0;
-      for (int c = tid; c < cols; c += TOPK_THREADS) cnt += sel_key(__ldg(v + c), descending) <= mid;
+      for (int c = tid; c < cols; c += TOPK_THREADS) cnt += (SMEM_ROW ? rowkey[c] : sel_key(__ldg(v + c), descending)) <= mid;
       cnt = block_sum_int(cnt, red);
       if (cnt >= kk) hi = mid; else lo = mid + 1;
     }
@@ -131,23 +166,15 @@ topk_rows_kernel(const float* __restrict__ vals, int cols, int64_t ldv, const in
     // strictly smaller keys (fewer than kk of them) in any order
     for (int c0 = 0; c0 < cols; c0 += TOPK_THREADS) {
       const int c = c0 + tid;
-      uint32_t key = 0xffffffffu;
-      bool take = false;
-      if (c < cols) { key = sel_key(__ldg(v + c), descending); take = key < t0; }
-      const uint32_t ballot = __ballot_sync(0xffffffffu, take);
-      if (ballot) {
-        int base = 0;
-        if (lane == 0) base = atomicAdd(&s_count, __popc(ballot));
-        base = __shfl_sync(0xffffffffu, base, 0);
-        if (take) { const int pos = base + __popc(ballot & ((1u << lane) - 1)); ckey[pos] = key; ccol[pos] = c; }
-      }
+      const uint32_t key = c < cols ? (SMEM_ROW ? rowkey[c] : sel_key(__ldg(v + c), descending)) : 0xffffffffu;
+      cand_append(c < cols && key < t0, key, c, lane, &s_count, ckey, ccol);
     }
     __syncthreads();
     int have = s_count;
     // ties == t0 in column order until kk are held (chunk by chunk, ordered prefix over the CTA)
     for (int c0 = 0; c0 < cols && have < kk; c0 += TOPK_THREADS) {
       const int c = c0 + tid;
-      const bool take = c < cols && sel_key(__ldg(v + c), descending) == t0;
+      const bool take = c < cols && (SMEM_ROW ? rowkey[c] : sel_key(__ldg(v + c), descending)) == t0;
       const uint32_t ballot = __ballot_sync(0xffffffffu, take);
       __syncthreads();
       if (lane == 0) red[tid >> 5] = __popc(ballot);
@@ -199,8 +226,21 @@ int topk_rows_launch(const float* vals, int rows, int cols, int64_t ldv, const i
   if (rows == 0 || k == 0) return REIDB200_OK;
   RB_REQUIRE(k > 0 && k <= TOPK_MAX_K, "topk: k=%d outside [1,%d]", k, TOPK_MAX_K);
   RB_REQUIRE(cols >= 0 && ldv >= cols, "topk: bad cols/ld");
-  { ProfScope _ps("topk_rows_kernel", st); topk_rows_kernel<<<rows, TOPK_THREADS, 0, st>>>(vals, cols, ldv, cand_i, k, descending, index_base, out_d, out_i,
-                                                  idx64); }
+  if (cols <= TOPK_SMEM_ROW_MAX) {
+    static bool attr = false;
+    if (!attr) {
+      RB_CUDA(cudaFuncSetAttribute(topk_rows_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                   TOPK_SMEM_ROW_MAX * 4));
+      attr = true;
+    }
+    ProfScope _ps("topk_rows_kernel", st);
+    topk_rows_kernel<true><<<rows, TOPK_THREADS, align_up((size_t)cols * 4, 16), st>>>(vals, cols, ldv, cand_i, k, descending,
+                                                                                      index_base, out_d, out_i, idx64);
+  } else {
+    ProfScope _ps("topk_rows_kernel", st);
+    topk_rows_kernel<false><<<rows, TOPK_THREADS, 0, st>>>(vals, cols, ldv, cand_i, k, descending, index_base, out_d, out_i,
+                                                          idx64);
+  }
   RB_LAUNCH_CHECK("topk_rows_kernel");
   return REIDB200_OK;
 }
