@@ -17,64 +17,50 @@ __device__ __forceinline__ uint32_t ev_key(float v, int descending) {
   return descending ? ~u : u;  // smaller key = ranked earlier
 }
 
-// Key of gallery item j as ranked for this query: junk items (label -1, or same id & same camera,
-// evaluate.py:71-72) get the largest key so that they are never counted.
-__device__ __forceinline__ uint32_t ev_masked_key(const float* row, const int32_t* gl, const int32_t* gc, int j,
-                                                  int32_t my_l, int32_t my_c, int descending) {
-  const int32_t l = __ldg(gl + j);
-  const bool junk = (l == -1) || (l == my_l && __ldg(gc + j) == my_c);
-  return junk ? 0xffffffffu : ev_key(__ldg(row + j), descending);
+// One CTA per query, one streaming pass over the score row.
+//   pass 1  collect the good items (same id, different camera: evaluate.py:66-70), rank-sort them;
+//   pass 2  every non-junk item j (junk = label -1 or same id & same camera, evaluate.py:71-72) that is ranked
+//           before the WORST good item finds, by binary search in the sorted goods, the first good item s it
+//           precedes and bumps hist[s]; position(good s) = sum_{b <= s} hist[b].
+// Tie order of the reference: ascending argsort then [::-1] for scores (higher index first), plain ascending
+// (lower index first) for distances.
+__device__ __forceinline__ bool ev_before(uint32_t ka, int ja, uint32_t kb, int jb, int descending) {
+  return ka < kb || (ka == kb && (descending ? ja > jb : ja < jb));
 }
 
-// One CTA per query.  Pass 1 stages the junk-masked keys of the whole score row in shared memory (when it
-// fits: G * 4 bytes of dynamic smem) and collects the good items; pass 2 counts, for four good items per warp at
-// a time, the non-junk items ranked before them.
-template <bool SMEM_ROW>
 __global__ void __launch_bounds__(EV_THREADS)
 eval_query_kernel(const float* __restrict__ mat, int G, int64_t ldm, int descending, const int32_t* __restrict__ ql,
                   const int32_t* __restrict__ qc, const int32_t* __restrict__ gl, const int32_t* __restrict__ gc,
                   double* __restrict__ ap_q, int32_t* __restrict__ first, int32_t* __restrict__ hist,
                   int32_t* __restrict__ status) {
-  extern __shared__ uint32_t skey[];
-  __shared__ int32_t gcol[EV_GOOD_CAP];
-  __shared__ uint32_t gkey[EV_GOOD_CAP];
-  __shared__ int32_t gpos[EV_GOOD_CAP];
+  __shared__ int32_t gcol[EV_GOOD_CAP], scol[EV_GOOD_CAP];
+  __shared__ uint32_t gkey[EV_GOOD_CAP], skey[EV_GOOD_CAP];
+  __shared__ int32_t gpos[EV_GOOD_CAP + 1];
   __shared__ int s_ngood;
   __shared__ double s_terms[EV_GOOD_CAP];
-  __shared__ int s_best;
 
   const int q = blockIdx.x;
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int tid = threadIdx.x;
   const float* row = mat + (size_t)q * ldm;
   const int32_t my_l = ql[q], my_c = qc[q];
   if (tid == 0) s_ngood = 0;
   __syncthreads();
 
-  // good = same id & different camera (evaluate.py:66-70).  Four independent elements per thread per trip so
-  // that several loads are in flight; good items are rare, so a plain shared-memory counter collects them.
+  // ---- pass 1: good items (labels only; the gallery label vectors are L2 resident across queries)
   for (int j0 = 0; j0 < G; j0 += 4 * EV_THREADS) {
     int32_t l[4];
-    float v[4];
 #pragma unroll
     for (int u = 0; u < 4; ++u) {
       const int j = j0 + u * EV_THREADS + tid;
       l[u] = j < G ? __ldg(gl + j) : -2;
-      v[u] = j < G ? __ldg(row + j) : 0.f;
     }
 #pragma unroll
     for (int u = 0; u < 4; ++u) {
       const int j = j0 + u * EV_THREADS + tid;
-      if (j >= G) continue;
-      const uint32_t key = ev_key(v[u], descending);
-      bool junk = l[u] == -1;
-      if (l[u] == my_l) {
-        if (__ldg(gc + j) == my_c) junk = true;
-        else {
-          const int pos = atomicAdd(&s_ngood, 1);
-          if (pos < EV_GOOD_CAP) { gcol[pos] = j; gkey[pos] = key; }
-        }
+      if (j < G && l[u] == my_l && __ldg(gc + j) != my_c) {
+        const int pos = atomicAdd(&s_ngood, 1);
+        if (pos < EV_GOOD_CAP) { gcol[pos] = j; gkey[pos] = ev_key(__ldg(row + j), descending); }
       }
-      if (SMEM_ROW) skey[j] = junk ? 0xffffffffu : key;
     }
   }
   __syncthreads();
@@ -88,57 +74,66 @@ eval_query_kernel(const float* __restrict__ mat, int G, int64_t ldm, int descend
     if (tid == 0) { atomicExch(status, 1); ap_q[q] = __longlong_as_double(0x7ff8000000000000LL); first[q] = -1; }
     return;
   }
+  // rank-sort the goods into ranking order; gpos doubles as the histogram
+  for (int e = tid; e < ngood; e += EV_THREADS) {
+    const uint32_t k = gkey[e];
+    const int c = gcol[e];
+    int r = 0;
+    for (int f = 0; f < ngood; ++f) r += ev_before(gkey[f], gcol[f], k, c, descending);
+    skey[r] = k;
+    scol[r] = c;
+  }
+  for (int e = tid; e <= ngood; e += EV_THREADS) gpos[e] = 0;
+  __syncthreads();
+  const uint32_t worst_k = skey[ngood - 1];
+  const int worst_c = scol[ngood - 1];
 
-  // position of every good item among the non-junk items: four good items per warp per sweep of the row.
-  // Tie order of the reference: ascending argsort then [::-1] for scores (higher index first), plain ascending
-  // (lower index first) for distances.
-  for (int e0 = warp * 4; e0 < ngood; e0 += (EV_THREADS / 32) * 4) {
-    uint32_t k[4];
-    int col[4], cnt[4];
+  // ---- pass 2: stream the row once
+  for (int j0 = 0; j0 < G; j0 += 4 * EV_THREADS) {
+    float v[4];
 #pragma unroll
     for (int u = 0; u < 4; ++u) {
-      const bool valid = e0 + u < ngood;
-      k[u] = valid ? gkey[e0 + u] : 0u;
-      col[u] = valid ? gcol[e0 + u] : -1;
-      cnt[u] = 0;
-    }
-#pragma unroll 4
-    for (int j = lane; j < G; j += 32) {
-      const uint32_t kj = SMEM_ROW ? skey[j] : ev_masked_key(row, gl, gc, j, my_l, my_c, descending);
-#pragma unroll
-      for (int u = 0; u < 4; ++u)
-        cnt[u] += (kj < k[u]) || (kj == k[u] && kj != 0xffffffffu && (descending ? j > col[u] : j < col[u]));
+      const int j = j0 + u * EV_THREADS + tid;
+      v[u] = j < G ? __ldg(row + j) : 0.f;
     }
 #pragma unroll
     for (int u = 0; u < 4; ++u) {
-      const int c = warp_sum_i(cnt[u]);
-      if (lane == 0 && e0 + u < ngood) gpos[e0 + u] = c;
+      const int j = j0 + u * EV_THREADS + tid;
+      if (j >= G) continue;
+      const uint32_t kj = ev_key(v[u], descending);
+      if (!ev_before(kj, j, worst_k, worst_c, descending)) continue;  // the common case
+      const int32_t l = __ldg(gl + j);
+      if (l == -1 || (l == my_l && __ldg(gc + j) == my_c)) continue;  // junk
+      int lo = 0, hi = ngood - 1;  // smallest s with j before good s (exists: j is before the worst good)
+      while (lo < hi) {
+        const int mid = (lo + hi) >> 1;
+        if (ev_before(kj, j, skey[mid], scol[mid], descending)) hi = mid; else lo = mid + 1;
+      }
+      atomicAdd(&gpos[lo], 1);
     }
+  }
+  __syncthreads();
+  if (tid == 0) {  // inclusive prefix: position of good s among the non-junk items
+    int run = 0;
+    for (int e = 0; e < ngood; ++e) { run += gpos[e]; gpos[e] = run; }
   }
   __syncthreads();
 
   // AP: sum over goods in ascending position of d_recall * (old_precision + precision) / 2 (evaluate.py:94-103)
   const double d_recall = 1.0 / (double)ngood;
-  for (int e = tid; e < ngood; e += EV_THREADS) {
-    const int pe = gpos[e];
-    int i = 0;  // number of goods ranked before this one (positions are distinct)
-    for (int f = 0; f < ngood; ++f) i += gpos[f] < pe;
+  for (int i = tid; i < ngood; i += EV_THREADS) {
+    const int pe = gpos[i];  // rows_good[i]
     const double precision = (double)(i + 1) * 1.0 / (double)(pe + 1);
     const double old_precision = pe != 0 ? (double)i * 1.0 / (double)pe : 1.0;
     s_terms[i] = d_recall * (old_precision + precision) / 2;
-    if (i == 0) s_best = pe;
   }
   __syncthreads();
-  double ap = 0.0;
-  int best = 0;
   if (tid == 0) {
+    double ap = 0.0;
     for (int t = 0; t < ngood; ++t) ap = ap + s_terms[t];
-    best = s_best;
-  }
-  if (tid == 0) {
     ap_q[q] = ap;
-    first[q] = best;
-    atomicAdd(hist + best, 1);
+    first[q] = gpos[0];
+    atomicAdd(hist + gpos[0], 1);
   }
 }
 
@@ -216,19 +211,7 @@ extern "C" int reidb200_eval_cmc_map(const float* mat, int Q, int G, int64_t ldm
   if (out_first) first = out_first;
   RB_CUDA(cudaMemsetAsync(hist, 0, (size_t)G * sizeof(int32_t), st));
   RB_CUDA(cudaMemsetAsync(status, 0, 64 * sizeof(int32_t), st));
-  const size_t row_bytes = (size_t)G * sizeof(uint32_t);
-  if (row_bytes <= 160 * 1024) {
-    static bool attr = false;
-    if (!attr) {
-      RB_CUDA(cudaFuncSetAttribute(eval_query_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
-      attr = true;
-    }
-    ProfScope _ps("eval_query_kernel", st);
-    eval_query_kernel<true><<<Q, EV_THREADS, row_bytes, st>>>(mat, G, ldm, descending, ql, qc, gl, gc, apq, first, hist, status);
-  } else {
-    ProfScope _ps("eval_query_kernel", st);
-    eval_query_kernel<false><<<Q, EV_THREADS, 0, st>>>(mat, G, ldm, descending, ql, qc, gl, gc, apq, first, hist, status);
-  }
+  { ProfScope _ps("eval_query_kernel", st); eval_query_kernel<<<Q, EV_THREADS, 0, st>>>(mat, G, ldm, descending, ql, qc, gl, gc, apq, first, hist, status); }
   RB_LAUNCH_CHECK("eval_query_kernel");
   { ProfScope _ps("eval_finalize_kernel", st); eval_finalize_kernel<<<1, 1024, 0, st>>>(hist, apq, Q, G, out_cmc, out_ap); }
   RB_LAUNCH_CHECK("eval_finalize_kernel");

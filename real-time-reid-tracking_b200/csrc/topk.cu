@@ -64,9 +64,7 @@ topk_rows_kernel(const float* __restrict__ vals, int cols, int64_t ldv, const in
   extern __shared__ __align__(16) uint32_t rowkey[];
   __shared__ uint32_t ckey[TOPK_CAP];
   __shared__ int32_t ccol[TOPK_CAP];
-  __shared__ uint32_t gmin[1024];
   __shared__ int red[TOPK_THREADS / 32];
-  __shared__ uint32_t s_t0;
   __shared__ int s_count;
 
   const int row = blockIdx.x;
@@ -98,29 +96,38 @@ topk_rows_kernel(const float* __restrict__ vals, int cols, int64_t ldv, const in
     const int g = per_thread == 1 ? 0 : ((c / TOPK_THREADS) & 1);
     m[g] = min(m[g], kc);
   }
-  for (int j = 0; j < per_thread; ++j) gmin[j * TOPK_THREADS + tid] = m[j];
-  if (tid == 0) { s_count = 0; s_t0 = 0xffffffffu; }
-  __syncthreads();
-  // k-th smallest group minimum (rank by (key, group index); exactly one group gets rank kk-1).  It is an upper
-  // bound of the k-th smallest element, nearly tight because k << number of groups.
+  if (tid == 0) s_count = 0;
+  // k-th smallest group minimum by bisection on the ordered key (32 barrier-counts): an upper bound of the k-th
+  // smallest element, nearly tight because k << number of groups.
+  uint32_t t0 = 0xffffffffu;
   if (kk > 0) {
-    for (int j = 0; j < per_thread; ++j) {
-      const int g = j * TOPK_THREADS + tid;
-      const uint32_t mine = m[j];
-      int rank = 0;
-      for (int o = 0; o < groups; ++o) {
-        const uint32_t other = gmin[o];
-        rank += (other < mine) || (other == mine && o < g);
-      }
-      if (rank == kk - 1) s_t0 = mine;
+    uint32_t lo = 0, hi = 0xffffffffu;
+    while (lo < hi) {
+      const uint32_t mid = lo + ((hi - lo) >> 1);
+      int c = __syncthreads_count(m[0] <= mid);
+      if (per_thread == 2) c += __syncthreads_count(m[1] <= mid);
+      if (c >= kk) hi = mid; else lo = mid + 1;
     }
+    t0 = lo;
   }
   __syncthreads();
-  uint32_t t0 = s_t0;
 
   // ---- pass 2: collect candidates <= t0
   if (SMEM_ROW) {
-    for (int c0 = 0; c0 < cols; c0 += TOPK_THREADS) {
+    const int nq4 = cols >> 2;
+    for (int i0 = 0; i0 < nq4; i0 += TOPK_THREADS) {
+      const int i = i0 + tid;
+      uint4 k4 = make_uint4(0xffffffffu, 0xffffffffu, 0xffffffffu, 0xffffffffu);
+      if (i < nq4) k4 = *reinterpret_cast<const uint4*>(rowkey + 4 * i);
+      const bool in = i < nq4;
+      const bool any = in && min(min(k4.x, k4.y), min(k4.z, k4.w)) <= t0;
+      if (__ballot_sync(0xffffffffu, any) == 0) continue;  // warp-uniform: nothing to take in these 128 columns
+      cand_append(in && k4.x <= t0, k4.x, 4 * i + 0, lane, &s_count, ckey, ccol);
+      cand_append(in && k4.y <= t0, k4.y, 4 * i + 1, lane, &s_count, ckey, ccol);
+      cand_append(in && k4.z <= t0, k4.z, 4 * i + 2, lane, &s_count, ckey, ccol);
+      cand_append(in && k4.w <= t0, k4.w, 4 * i + 3, lane, &s_count, ckey, ccol);
+    }
+    for (int c0 = nq4 * 4; c0 < cols; c0 += TOPK_THREADS) {
       const int c = c0 + tid;
       const uint32_t key = c < cols ? rowkey[c] : 0xffffffffu;
       cand_append(c < cols && key <= t0, key, c, lane, &s_count, ckey, ccol);
