@@ -11,6 +11,7 @@
 // CTA tile 128 x 256, k-block 64 (one SWIZZLE_128B atom), 2 smem stages of 96 KB
 // (Ahi, Alo, Bhi, Blo), 2 TMEM accumulator stages of 256 columns.
 #include <cuda.h>
+#include <stdlib.h>
 
 #include "gemm.cuh"
 #include "ptx.cuh"
@@ -85,6 +86,59 @@ struct GemmArgs {
   int64_t ldo;
 };
 
+
+// Epilogue of one 32-row x 256-column accumulator slab owned by one warp (TMEM lane quadrant q): thread = row.
+// Fast path (16-byte aligned rows): every thread streams its own row straight from registers with 128-bit stores
+// (a thread writes whole 128-byte lines, L2 merges them).  Slow path (odd leading dimension): transpose through a
+// padded shared-memory tile and store row-contiguous scalars.
+template <int KIND>
+__device__ __forceinline__ void epilogue_slab(const GemmArgs& a, uint32_t tmem_addr, int row0, int col_base, int lane,
+                                              float* sbuf, bool vec_ok) {
+  const int my_row = row0 + lane;
+  const float xx_mine = (KIND != REIDB200_DIST_DOT && my_row < a.m) ? __ldg(a.xx + my_row) : 0.f;
+  const int rows_here = min(32, a.m - row0);
+  if (rows_here <= 0) return;
+#pragma unroll 1
+  for (int c = 0; c < BN / 32; ++c) {
+    const int col0 = col_base + c * 32;
+    if (col0 >= a.n) break;  // warp-uniform
+    uint32_t r[32];
+    ptx::tmem_ld_32x32b_x32(tmem_addr + c * 32, r);
+    ptx::tmem_ld_wait();
+    if (vec_ok && col0 + 32 <= a.n) {
+      if (my_row < a.m) {
+        float* dst = a.out + (size_t)my_row * a.ldo + col0;
+#pragma unroll
+        for (int j = 0; j < 32; j += 4) {
+          float4 y4 = make_float4(0.f, 0.f, 0.f, 0.f);
+          if (KIND != REIDB200_DIST_DOT) y4 = __ldg(reinterpret_cast<const float4*>(a.yy + col0 + j));
+          float4 o;
+          o.x = dist_epilogue(KIND, __uint_as_float(r[j + 0]), xx_mine, y4.x);
+          o.y = dist_epilogue(KIND, __uint_as_float(r[j + 1]), xx_mine, y4.y);
+          o.z = dist_epilogue(KIND, __uint_as_float(r[j + 2]), xx_mine, y4.z);
+          o.w = dist_epilogue(KIND, __uint_as_float(r[j + 3]), xx_mine, y4.w);
+          __stcs(reinterpret_cast<float4*>(dst + j), o);
+        }
+      }
+    } else {
+#pragma unroll
+      for (int j = 0; j < 32; ++j) sbuf[lane * 33 + j] = __uint_as_float(r[j]);
+      __syncwarp();
+      const int col = col0 + lane;
+      const float yy_c = (KIND != REIDB200_DIST_DOT && col < a.n) ? __ldg(a.yy + col) : 0.f;
+#pragma unroll 8
+      for (int rr = 0; rr < 32; ++rr) {
+        const float acc = sbuf[rr * 33 + lane];
+        const float xr = __shfl_sync(0xffffffffu, xx_mine, rr);
+        if (rr < rows_here && col < a.n)
+          __stcs(a.out + (size_t)(row0 + rr) * a.ldo + col, dist_epilogue(KIND, acc, xr, yy_c));
+      }
+      __syncwarp();
+    }
+  }
+}
+
+template <int KIND>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
 gemm_split_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, GemmArgs a) {
   extern __shared__ uint8_t smem_raw[];
@@ -181,35 +235,15 @@ gemm_split_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
     // ===== epilogue warps: TMEM lane quadrant = warp % 4
     const int q = warp & 3;
     float* sbuf = epi_buf + (warp - 2) * EPI_STAGE_FLOATS;
+    const bool vec_ok = (a.ldo & 3) == 0 && (reinterpret_cast<uintptr_t>(a.out) & 15) == 0 &&
+                        (a.yy == nullptr || (reinterpret_cast<uintptr_t>(a.yy) & 15) == 0);
     int as = 0;
     uint32_t aphase = 0;
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
       const int tm = tile % a.tiles_m, tn = tile / a.tiles_m;
       ptx::mbar_wait(bar_tfull + 8 * as, aphase);
       ptx::tc_fence_after();
-      const int row0 = tm * BM + q * 32;
-      const int my_row = row0 + lane;
-      const float xx_mine = (a.xx != nullptr && my_row < a.m) ? __ldg(a.xx + my_row) : 0.f;
-      const int rows_here = min(32, a.m - row0);
-#pragma unroll 1
-      for (int c = 0; c < BN / 32; ++c) {
-        const int col0 = tn * BN + c * 32;
-        if (col0 >= a.n) break;  // warp-uniform
-        uint32_t r[32];
-        ptx::tmem_ld_32x32b_x32(tmem_base + ((uint32_t)(q * 32) << 16) + as * BN + c * 32, r);
-        ptx::tmem_ld_wait();
-#pragma unroll
-        for (int j = 0; j < 32; ++j) sbuf[lane * 33 + j] = __uint_as_float(r[j]);
-        __syncwarp();
-        const int col = col0 + lane;
-        const float yy_c = (a.yy != nullptr && col < a.n) ? __ldg(a.yy + col) : 0.f;
-        for (int rr = 0; rr < rows_here; ++rr) {
-          const float acc = sbuf[rr * 33 + lane];
-          const float xr = __shfl_sync(0xffffffffu, xx_mine, rr);
-          if (col < a.n) __stcs(a.out + (size_t)(row0 + rr) * a.ldo + col, dist_epilogue(a.kind, acc, xr, yy_c));
-        }
-        __syncwarp();
-      }
+      epilogue_slab<KIND>(a, tmem_base + ((uint32_t)(q * 32) << 16) + as * BN, tm * BM + q * 32, tn * BN, lane, sbuf, vec_ok);
       ptx::tc_fence_before();
       __syncwarp();
       if (lane == 0) ptx::mbar_arrive(bar_tempty + 8 * as);
@@ -223,6 +257,144 @@ gemm_split_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
   if (warp == 1) {
     ptx::tc_fence_after();
     ptx::tmem_dealloc(tmem_base, TMEM_COLS);
+  }
+}
+
+
+// ------------------------------------------------------------------------------------ tcgen05 kernel, CTA pairs
+// cta_group::2: a cluster of two CTAs owns a 256 x 256 output tile.  Each CTA stages its own 128 A rows and HALF of
+// the B tile (128 of the 256 rows), so a k-block costs 64 KB of L2->SMEM traffic per SM instead of 96 KB for the same
+// number of UMMA cycles; three stages fit.  The even CTA issues every UMMA (M = 256) and multicasts the commits.
+constexpr int STAGES2 = 3;
+constexpr int STAGE2_BYTES = 4 * A_BYTES;  // Ahi, Alo, Bhi(half), Blo(half): 64 KB
+constexpr size_t GEMM2_SMEM = 1024 + (size_t)STAGES2 * STAGE2_BYTES + 4 * EPI_STAGE_FLOATS * 4 + 128;
+
+template <int KIND>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GEMM_THREADS, 1)
+gemm_split_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, GemmArgs a) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  float* epi_buf = reinterpret_cast<float*>(smem + (size_t)STAGES2 * STAGE2_BYTES);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(epi_buf + 4 * EPI_STAGE_FLOATS);
+  // bars: [0,S) full, [S,2S) empty, then tmem_full[2], tmem_empty[2]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * STAGES2 + 4);
+
+  const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);
+  const int lane = threadIdx.x & 31;
+  const uint32_t rank = ptx::cluster_ctarank();
+  const bool leader = rank == 0;
+  const uint32_t bar_full = ptx::smem_u32(bars);
+  const uint32_t bar_empty = ptx::smem_u32(bars + STAGES2);
+  const uint32_t bar_tfull = ptx::smem_u32(bars + 2 * STAGES2);
+  const uint32_t bar_tempty = ptx::smem_u32(bars + 2 * STAGES2 + 2);
+  const uint32_t smem_base = ptx::smem_u32(smem);
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < STAGES2; ++s) {
+      ptx::mbar_init(bar_full + 8 * s, 1);   // the leader's arrive.expect_tx; bytes of both CTAs land here
+      ptx::mbar_init(bar_empty + 8 * s, 1);  // one multicast commit
+    }
+    for (int s = 0; s < 2; ++s) {
+      ptx::mbar_init(bar_tfull + 8 * s, 1);
+      ptx::mbar_init(bar_tempty + 8 * s, 8);  // 4 epilogue warps x 2 CTAs arrive on the leader's barrier
+    }
+    ptx::fence_barrier_init();
+    ptx::prefetch_tensormap(&tmA);
+    ptx::prefetch_tensormap(&tmB);
+  }
+  if (warp == 1) {
+    ptx::tmem_alloc_2cta(ptx::smem_u32(tmem_slot), TMEM_COLS);
+    ptx::tmem_relinquish_2cta();
+  }
+  ptx::tc_fence_before();
+  ptx::cluster_sync();  // barriers of both CTAs initialised before any remote arrive / multicast
+  ptx::tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  const int tiles_m2 = (a.tiles_m + 1) / 2;
+  const int total_tiles = tiles_m2 * a.tiles_n;
+  const int cluster_id = blockIdx.x >> 1, num_clusters = gridDim.x >> 1;
+
+  if (warp == 0) {
+    // ===== TMA producer (one thread per CTA): own A rows, own half of the B rows
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int tile = cluster_id; tile < total_tiles; tile += num_clusters) {
+        const int tm = tile % tiles_m2, tn = tile / tiles_m2;
+        const int arow = tm * 2 * BM + (int)rank * BM;
+        const int brow = tn * BN + (int)rank * (BN / 2);
+        for (int kb = 0; kb < a.num_kb; ++kb) {
+          ptx::mbar_wait(bar_empty + 8 * stage, phase ^ 1);
+          const uint32_t full = bar_full + 8 * stage;
+          const uint32_t sb = smem_base + stage * STAGE2_BYTES;
+          if (leader) ptx::mbar_arrive_expect_tx(full, 2 * STAGE2_BYTES);
+          ptx::tma_load_2d_2cta(sb, &tmA, full, kb * BK, arow);
+          ptx::tma_load_2d_2cta(sb + A_BYTES, &tmA, full, a.dp + kb * BK, arow);
+          ptx::tma_load_2d_2cta(sb + 2 * A_BYTES, &tmB, full, kb * BK, brow);
+          ptx::tma_load_2d_2cta(sb + 3 * A_BYTES, &tmB, full, a.dp + kb * BK, brow);
+          if (++stage == STAGES2) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===== MMA issuer: one thread of the even CTA
+    if (leader && lane == 0) {
+      constexpr uint32_t idesc = ptx::umma_idesc_bf16(2 * BM, BN);
+      int stage = 0, as = 0;
+      uint32_t phase = 0, aphase = 0;
+      for (int tile = cluster_id; tile < total_tiles; tile += num_clusters) {
+        ptx::mbar_wait(bar_tempty + 8 * as, aphase ^ 1);
+        ptx::tc_fence_after();
+        const uint32_t d_tmem = tmem_base + as * BN;
+        for (int kb = 0; kb < a.num_kb; ++kb) {
+          ptx::mbar_wait(bar_full + 8 * stage, phase);
+          ptx::tc_fence_after();
+          const uint32_t sb = smem_base + stage * STAGE2_BYTES;
+#pragma unroll
+          for (int kk = 0; kk < BK / 16; ++kk) {
+            const uint64_t ahi = ptx::umma_desc_k_sw128(sb + kk * 32);
+            const uint64_t alo = ptx::umma_desc_k_sw128(sb + A_BYTES + kk * 32);
+            const uint64_t bhi = ptx::umma_desc_k_sw128(sb + 2 * A_BYTES + kk * 32);
+            const uint64_t blo = ptx::umma_desc_k_sw128(sb + 3 * A_BYTES + kk * 32);
+            ptx::mma_f16_ss_2cta(d_tmem, alo, bhi, idesc, (kb | kk) != 0);
+            ptx::mma_f16_ss_2cta(d_tmem, ahi, blo, idesc, 1);
+            ptx::mma_f16_ss_2cta(d_tmem, ahi, bhi, idesc, 1);
+          }
+          ptx::mma_commit_2cta(bar_empty + 8 * stage, 3);  // frees this stage in BOTH CTAs
+          if (++stage == STAGES2) { stage = 0; phase ^= 1; }
+        }
+        ptx::mma_commit_2cta(bar_tfull + 8 * as, 3);  // accumulator complete, both CTAs
+        as ^= 1;
+        if (as == 0) aphase ^= 1;
+      }
+    }
+  } else {
+    // ===== epilogue warps (both CTAs): own 128 rows of the 256-row tile
+    const int q = warp & 3;
+    float* sbuf = epi_buf + (warp - 2) * EPI_STAGE_FLOATS;
+    const bool vec_ok = (a.ldo & 3) == 0 && (reinterpret_cast<uintptr_t>(a.out) & 15) == 0 &&
+                        (a.yy == nullptr || (reinterpret_cast<uintptr_t>(a.yy) & 15) == 0);
+    int as = 0;
+    uint32_t aphase = 0;
+    for (int tile = cluster_id; tile < total_tiles; tile += num_clusters) {
+      const int tm = tile % tiles_m2, tn = tile / tiles_m2;
+      ptx::mbar_wait(bar_tfull + 8 * as, aphase);
+      ptx::tc_fence_after();
+      epilogue_slab<KIND>(a, tmem_base + ((uint32_t)(q * 32) << 16) + as * BN, tm * 2 * BM + (int)rank * BM + q * 32, tn * BN,
+                          lane, sbuf, vec_ok);
+      ptx::tc_fence_before();
+      __syncwarp();
+      if (lane == 0) ptx::mbar_arrive_leader(bar_tempty + 8 * as);
+      as ^= 1;
+      if (as == 0) aphase ^= 1;
+    }
+  }
+
+  ptx::tc_fence_before();
+  ptx::cluster_sync();  // nobody leaves while the peer may still read this CTA's smem / signal its barriers
+  if (warp == 1) {
+    ptx::tc_fence_after();
+    ptx::tmem_dealloc_2cta(tmem_base, TMEM_COLS);
   }
 }
 
@@ -295,24 +467,42 @@ int gemm_split_launch(const void* packedA, const float* xx, int m, const void* p
   if (m == 0 || n == 0) return REIDB200_OK;
   RB_REQUIRE(kind >= 0 && kind <= 3, "distmat: unknown kind %d", kind);
   RB_REQUIRE(kind == REIDB200_DIST_DOT || (xx && yy), "distmat: row norms required for kind %d", kind);
-  static bool attr_set = false;
-  if (!attr_set) {
-    RB_CUDA(cudaFuncSetAttribute(gemm_split_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GEMM_SMEM));
-    attr_set = true;
-  }
   const int dp = padded_dim(d);
+  const bool pair = m > BM && !getenv("REIDB200_GEMM_1CTA");  // CTA pairs (cta_group::2) unless A fits one 128-row tile
   CUtensorMap tmA, tmB;
   int rc = make_operand_map(&tmA, packedA, m, dp, BM);
   if (rc) return rc;
-  rc = make_operand_map(&tmB, packedB, n, dp, BN);
+  rc = make_operand_map(&tmB, packedB, n, dp, pair ? BN / 2 : BN);
   if (rc) return rc;
   GemmArgs a;
   a.m = m; a.n = n; a.dp = dp; a.num_kb = dp / BK;
   a.tiles_m = ceil_div(m, BM); a.tiles_n = ceil_div(n, BN);
   a.kind = kind; a.xx = xx; a.yy = yy; a.out = out; a.ldo = ldo;
+  void (*k1)(CUtensorMap, CUtensorMap, GemmArgs) = nullptr;
+  void (*k2)(CUtensorMap, CUtensorMap, GemmArgs) = nullptr;
+  switch (kind) {
+    case REIDB200_DIST_EUCLID: k1 = gemm_split_tc_kernel<REIDB200_DIST_EUCLID>; k2 = gemm_split_tc2_kernel<REIDB200_DIST_EUCLID>; break;
+    case REIDB200_DIST_COSINE_HALF: k1 = gemm_split_tc_kernel<REIDB200_DIST_COSINE_HALF>; k2 = gemm_split_tc2_kernel<REIDB200_DIST_COSINE_HALF>; break;
+    case REIDB200_DIST_DOT: k1 = gemm_split_tc_kernel<REIDB200_DIST_DOT>; k2 = gemm_split_tc2_kernel<REIDB200_DIST_DOT>; break;
+    default: k1 = gemm_split_tc_kernel<REIDB200_DIST_SQL2>; k2 = gemm_split_tc2_kernel<REIDB200_DIST_SQL2>; break;
+  }
+  static bool attr_done[2][4] = {{false, false, false, false}, {false, false, false, false}};
+  if (!attr_done[pair ? 1 : 0][kind]) {
+    RB_CUDA(cudaFuncSetAttribute(pair ? (const void*)k2 : (const void*)k1, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 (int)(pair ? GEMM2_SMEM : GEMM_SMEM)));
+    attr_done[pair ? 1 : 0][kind] = true;
+  }
+  if (pair) {
+    const long long total2 = (long long)((a.tiles_m + 1) / 2) * a.tiles_n;
+    const int max_clusters = num_sms() / 2;
+    const int clusters = (int)(total2 < max_clusters ? total2 : max_clusters);
+    { ProfScope _ps("gemm_split_tc_kernel", st); k2<<<2 * clusters, GEMM_THREADS, GEMM2_SMEM, st>>>(tmA, tmB, a); }
+    RB_LAUNCH_CHECK("gemm_split_tc2_kernel");
+    return REIDB200_OK;
+  }
   const long long total = (long long)a.tiles_m * a.tiles_n;
   const int grid = (int)(total < num_sms() ? total : num_sms());
-  { ProfScope _ps("gemm_split_tc_kernel", st); gemm_split_tc_kernel<<<grid, GEMM_THREADS, GEMM_SMEM, st>>>(tmA, tmB, a); }
+  { ProfScope _ps("gemm_split_tc_kernel", st); k1<<<grid, GEMM_THREADS, GEMM_SMEM, st>>>(tmA, tmB, a); }
   RB_LAUNCH_CHECK("gemm_split_tc_kernel");
   return REIDB200_OK;
 }
