@@ -84,6 +84,11 @@ struct GemmArgs {
   const float* yy;
   float* out;
   int64_t ldo;
+  // optional per-(row, 32-column chunk) reduction of the epilogue values (min, or max when cred_max): lets the
+  // top-k selection read only the k most promising 128-byte chunks of each row instead of the whole row
+  float* cred;
+  int64_t ldcr;
+  int cred_max;
 };
 
 
@@ -108,6 +113,7 @@ __device__ __forceinline__ void epilogue_slab(const GemmArgs& a, uint32_t tmem_a
     if (vec_ok && col0 + 32 <= a.n) {
       if (my_row < a.m) {
         float* dst = a.out + (size_t)my_row * a.ldo + col0;
+        float red = 0.f;
 #pragma unroll
         for (int j = 0; j < 32; j += 4) {
           float4 y4 = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -118,9 +124,23 @@ __device__ __forceinline__ void epilogue_slab(const GemmArgs& a, uint32_t tmem_a
           o.z = dist_epilogue(KIND, __uint_as_float(r[j + 2]), xx_mine, y4.z);
           o.w = dist_epilogue(KIND, __uint_as_float(r[j + 3]), xx_mine, y4.w);
           __stcs(reinterpret_cast<float4*>(dst + j), o);
+          if (a.cred) {
+            const float lo4 = fminf(fminf(o.x, o.y), fminf(o.z, o.w)), hi4 = fmaxf(fmaxf(o.x, o.y), fmaxf(o.z, o.w));
+            red = j == 0 ? (a.cred_max ? hi4 : lo4) : (a.cred_max ? fmaxf(red, hi4) : fminf(red, lo4));
+          }
         }
+        if (a.cred) a.cred[(size_t)my_row * a.ldcr + (col0 >> 5)] = red;
       }
     } else {
+      if (a.cred && my_row < a.m) {  // ragged last chunk: reduce from the registers (thread = row) before the transpose
+        float red2 = a.cred_max ? -INFINITY : INFINITY;
+        for (int j = 0; j < 32 && col0 + j < a.n; ++j) {
+          const float yv = KIND != REIDB200_DIST_DOT ? __ldg(a.yy + col0 + j) : 0.f;
+          const float o = dist_epilogue(KIND, __uint_as_float(r[j]), xx_mine, yv);
+          red2 = a.cred_max ? fmaxf(red2, o) : fminf(red2, o);
+        }
+        a.cred[(size_t)my_row * a.ldcr + (col0 >> 5)] = red2;
+      }
 #pragma unroll
       for (int j = 0; j < 32; ++j) sbuf[lane * 33 + j] = __uint_as_float(r[j]);
       __syncwarp();
@@ -463,7 +483,8 @@ static int make_operand_map(CUtensorMap* tm, const void* packed, int rows, int d
 }
 
 int gemm_split_launch(const void* packedA, const float* xx, int m, const void* packedB, const float* yy, int n, int d,
-                      int kind, float* out, int64_t ldo, cudaStream_t st) {
+                      int kind, float* out, int64_t ldo, cudaStream_t st, float* chunk_red, int64_t ld_chunk_red,
+                      int chunk_red_max) {
   if (m == 0 || n == 0) return REIDB200_OK;
   RB_REQUIRE(kind >= 0 && kind <= 3, "distmat: unknown kind %d", kind);
   RB_REQUIRE(kind == REIDB200_DIST_DOT || (xx && yy), "distmat: row norms required for kind %d", kind);
@@ -478,6 +499,7 @@ int gemm_split_launch(const void* packedA, const float* xx, int m, const void* p
   a.m = m; a.n = n; a.dp = dp; a.num_kb = dp / BK;
   a.tiles_m = ceil_div(m, BM); a.tiles_n = ceil_div(n, BN);
   a.kind = kind; a.xx = xx; a.yy = yy; a.out = out; a.ldo = ldo;
+  a.cred = chunk_red; a.ldcr = ld_chunk_red; a.cred_max = chunk_red_max;
   void (*k1)(CUtensorMap, CUtensorMap, GemmArgs) = nullptr;
   void (*k2)(CUtensorMap, CUtensorMap, GemmArgs) = nullptr;
   switch (kind) {

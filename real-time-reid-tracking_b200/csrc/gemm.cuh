@@ -14,11 +14,16 @@ inline size_t packed_bytes(int rows, int d) { return (size_t)rows * 2 * padded_d
 int pack_rows_launch(const float* x, int rows, int64_t ldx, int d, void* packed, float* sqnorm, cudaStream_t st);
 
 // out[m,n] = epilogue(kind, A.B^T, xx, yy) with A,B packed operands.  xx/yy may be null for DOT.
+// chunk_red (optional) f32[m, ld_chunk_red]: min (max when chunk_red_max) of the outputs over every 32-column chunk,
+// consumed by topk_rows_launch to skip the chunks that cannot hold a top-k element.
 int gemm_split_launch(const void* packedA, const float* xx, int m, const void* packedB, const float* yy, int n, int d,
-                      int kind, float* out, int64_t ldo, cudaStream_t st);
+                      int kind, float* out, int64_t ldo, cudaStream_t st, float* chunk_red = nullptr,
+                      int64_t ld_chunk_red = 0, int chunk_red_max = 0);
 
 // row-wise exact top-k (topk.cu); out_i is i64 when idx64 else i32; ids = cand_i[col] or col + index_base
+// chunk_red (optional): the per-32-column reductions written by gemm_split_launch for this matrix.
 int topk_rows_launch(const float* vals, int rows, int cols, int64_t ldv, const int64_t* cand_i, int k, int descending,
-                     int64_t index_base, float* out_d, void* out_i, int idx64, cudaStream_t st);
+                     int64_t index_base, float* out_d, void* out_i, int idx64, cudaStream_t st,
+                     const float* chunk_red = nullptr, int64_t ld_chunk_red = 0);
 
 }  // namespace reidb200

@@ -455,6 +455,7 @@ extern "C" size_t reidb200_jaccard_workspace_bytes(int N, int d, int k1, int k2)
   c.take<float>((size_t)N * rd.lds);
   c.take<float>((size_t)N * k1);
   c.take<int32_t>((size_t)N * k1);
+  c.take<float>((size_t)N * ceil_div((int)rd.lds, 32));
   carve_sparse(c, N, k1, k2, rd, nullptr);
   return align_up(c.off, 256);
 }
@@ -505,13 +506,15 @@ extern "C" int reidb200_jaccard(const float* feats, int N, int64_t ldf, int d, i
   float* sql2 = c.take<float>((size_t)N * rd.lds);
   float* rank_d = c.take<float>((size_t)N * k1);
   int32_t* rank_i = c.take<int32_t>((size_t)N * k1);
+  const int ldcr = ceil_div((int)rd.lds, 32);
+  float* cred = c.take<float>((size_t)N * ldcr);
   SparseWs w;
   carve_sparse(c, N, k1, k2, rd, &w);
   rc = pack_rows_launch(feats, N, ldf, d, packed, sqn, st);
   if (rc) return rc;
-  rc = gemm_split_launch(packed, sqn, N, packed, sqn, N, d, REIDB200_DIST_SQL2, sql2, rd.lds, st);
+  rc = gemm_split_launch(packed, sqn, N, packed, sqn, N, d, REIDB200_DIST_SQL2, sql2, rd.lds, st, cred, ldcr, 0);
   if (rc) return rc;
-  rc = topk_rows_launch(sql2, N, N, rd.lds, nullptr, k1, 0, 0, rank_d, rank_i, 0, st);
+  rc = topk_rows_launch(sql2, N, N, rd.lds, nullptr, k1, 0, 0, rank_d, rank_i, 0, st, cred, ldcr);
   if (rc) return rc;
   if (rank_out) RB_CUDA(cudaMemcpyAsync(rank_out, rank_i, (size_t)N * k1 * sizeof(int32_t), cudaMemcpyDeviceToDevice, st));
   if (nrows == 0 || ncols == 0) return REIDB200_OK;

@@ -14,10 +14,10 @@
 
 namespace reidb200 {
 
-constexpr int TOPK_THREADS = 512;
 constexpr int TOPK_CAP = 2048;   // candidate capacity (key + column in shared memory)
 constexpr int TOPK_MAX_K = 1024;
 constexpr int TOPK_SMEM_ROW_MAX = 36 * 1024;  // columns whose keys are cached in shared memory (144 KB)
+constexpr int TOPK_CHUNK_MAX = 8192;          // 32-column chunks per row in the chunk-guided mode
 
 __device__ __forceinline__ uint32_t sel_key(float v, int descending) {
   const uint32_t u = float_to_ordered(v);
@@ -29,6 +29,7 @@ __device__ __forceinline__ float sel_val(uint32_t key, int descending) {
   return __uint_as_float(u);
 }
 
+template <int NT>
 __device__ __forceinline__ int block_sum_int(int v, int* red) {
   v = warp_sum_i(v);
   __syncthreads();
@@ -36,7 +37,7 @@ __device__ __forceinline__ int block_sum_int(int v, int* red) {
   __syncthreads();
   int t = 0;
 #pragma unroll
-  for (int w = 0; w < TOPK_THREADS / 32; ++w) t += red[w];
+  for (int w = 0; w < NT / 32; ++w) t += red[w];
   return t;
 }
 
@@ -55,115 +56,146 @@ __device__ __forceinline__ void cand_append(bool take, uint32_t key, int col, in
   }
 }
 
-// SMEM_ROW: the ordered keys of the row are kept in dynamic shared memory by pass 1, so the row is read from
-// HBM exactly once; otherwise pass 2 re-reads it (L2).
-template <bool SMEM_ROW>
-__global__ void __launch_bounds__(TOPK_THREADS)
+// MODE 0: two passes over the row in global memory (second pass hits L2).
+// MODE 1: the ordered keys of the row are cached in dynamic shared memory by pass 1 (row read from HBM once).
+// MODE 2: chunk-guided: the producing GEMM already reduced every 32-column chunk (min / max); the threshold is the
+//         k-th best chunk reduction and only chunks that reach it (about k of them) are read at all.
+template <int MODE, int NT>
+__global__ void __launch_bounds__(NT)
 topk_rows_kernel(const float* __restrict__ vals, int cols, int64_t ldv, const int64_t* __restrict__ cand_i, int k,
-                 int descending, int64_t index_base, float* __restrict__ out_d, void* __restrict__ out_i, int idx64) {
-  extern __shared__ __align__(16) uint32_t rowkey[];
+                 int descending, int64_t index_base, float* __restrict__ out_d, void* __restrict__ out_i, int idx64,
+                 const float* __restrict__ chunk_red, int64_t ldcr) {
+  extern __shared__ __align__(16) uint32_t rowkey[];  // MODE 1: keys of the row; MODE 2: keys of the chunk reductions
   __shared__ uint32_t ckey[TOPK_CAP];
   __shared__ int32_t ccol[TOPK_CAP];
-  __shared__ int red[TOPK_THREADS / 32];
+  __shared__ int red[NT / 32];
   __shared__ int s_count;
 
   const int row = blockIdx.x;
   const float* v = vals + (size_t)row * ldv;
   const int64_t* ci = cand_i ? cand_i + (size_t)row * cols : nullptr;
-  const int tid = threadIdx.x, lane = tid & 31;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int kk = min(k, cols);
   float* od = out_d + (size_t)row * k;
-
-  // ---- pass 1: group minima (128-bit loads when the row is 16-byte aligned)
-  const int groups = (kk <= TOPK_THREADS) ? TOPK_THREADS : 1024;
-  const int per_thread = groups / TOPK_THREADS;  // 1 or 2
   const bool vec = (reinterpret_cast<uintptr_t>(v) & 15) == 0;
   const int ncol4 = vec ? (cols >> 2) : 0;
   const float4* v4 = reinterpret_cast<const float4*>(v);
-  uint32_t m[2] = {0xffffffffu, 0xffffffffu};
-#pragma unroll 4
-  for (int i = tid; i < ncol4; i += TOPK_THREADS) {
-    const float4 x = __ldg(v4 + i);
-    const uint32_t k0 = sel_key(x.x, descending), k1 = sel_key(x.y, descending);
-    const uint32_t k2 = sel_key(x.z, descending), k3 = sel_key(x.w, descending);
-    if (SMEM_ROW) *reinterpret_cast<uint4*>(rowkey + 4 * i) = make_uint4(k0, k1, k2, k3);
-    const int g = per_thread == 1 ? 0 : ((i / TOPK_THREADS) & 1);
-    m[g] = min(m[g], min(min(k0, k1), min(k2, k3)));
-  }
-  for (int c = ncol4 * 4 + tid; c < cols; c += TOPK_THREADS) {
-    const uint32_t kc = sel_key(__ldg(v + c), descending);
-    if (SMEM_ROW) rowkey[c] = kc;
-    const int g = per_thread == 1 ? 0 : ((c / TOPK_THREADS) & 1);
-    m[g] = min(m[g], kc);
-  }
+  const int nchunks = (cols + 31) >> 5;
   if (tid == 0) s_count = 0;
-  // k-th smallest group minimum by bisection on the ordered key (32 barrier-counts): an upper bound of the k-th
-  // smallest element, nearly tight because k << number of groups.
   uint32_t t0 = 0xffffffffu;
-  if (kk > 0) {
-    uint32_t lo = 0, hi = 0xffffffffu;
-    while (lo < hi) {
-      const uint32_t mid = lo + ((hi - lo) >> 1);
-      int c = __syncthreads_count(m[0] <= mid);
-      if (per_thread == 2) c += __syncthreads_count(m[1] <= mid);
-      if (c >= kk) hi = mid; else lo = mid + 1;
-    }
-    t0 = lo;
-  }
-  __syncthreads();
 
-  // ---- pass 2: collect candidates <= t0
-  if (SMEM_ROW) {
-    const int nq4 = cols >> 2;
-    for (int i0 = 0; i0 < nq4; i0 += TOPK_THREADS) {
-      const int i = i0 + tid;
-      uint4 k4 = make_uint4(0xffffffffu, 0xffffffffu, 0xffffffffu, 0xffffffffu);
-      if (i < nq4) k4 = *reinterpret_cast<const uint4*>(rowkey + 4 * i);
-      const bool in = i < nq4;
-      const bool any = in && min(min(k4.x, k4.y), min(k4.z, k4.w)) <= t0;
-      if (__ballot_sync(0xffffffffu, any) == 0) continue;  // warp-uniform: nothing to take in these 128 columns
-      cand_append(in && k4.x <= t0, k4.x, 4 * i + 0, lane, &s_count, ckey, ccol);
-      cand_append(in && k4.y <= t0, k4.y, 4 * i + 1, lane, &s_count, ckey, ccol);
-      cand_append(in && k4.z <= t0, k4.z, 4 * i + 2, lane, &s_count, ckey, ccol);
-      cand_append(in && k4.w <= t0, k4.w, 4 * i + 3, lane, &s_count, ckey, ccol);
+  if (MODE == 2) {
+    // ---- threshold = kk-th smallest chunk reduction (an upper bound of the kk-th smallest element)
+    const float* cr = chunk_red + (size_t)row * ldcr;
+    for (int c = tid; c < nchunks; c += NT) rowkey[c] = sel_key(__ldg(cr + c), descending);
+    __syncthreads();
+    if (kk > 0 && nchunks >= kk) {
+      uint32_t lo = 0, hi = 0xffffffffu;
+      while (lo < hi) {
+        const uint32_t mid = lo + ((hi - lo) >> 1);
+        int c = 0;
+        for (int i = tid; i < nchunks; i += NT) c += rowkey[i] <= mid;
+        c = block_sum_int<NT>(c, red);
+        if (c >= kk) hi = mid; else lo = mid + 1;
+      }
+      t0 = lo;
     }
-    for (int c0 = nq4 * 4; c0 < cols; c0 += TOPK_THREADS) {
-      const int c = c0 + tid;
-      const uint32_t key = c < cols ? rowkey[c] : 0xffffffffu;
-      cand_append(c < cols && key <= t0, key, c, lane, &s_count, ckey, ccol);
+    __syncthreads();
+    // ---- read only the chunks that reach the threshold: one warp per 128-byte chunk
+    for (int c = warp; c < nchunks; c += NT / 32) {
+      if (rowkey[c] > t0) continue;  // warp-uniform
+      const int col = c * 32 + lane;
+      const uint32_t key = col < cols ? sel_key(__ldg(v + col), descending) : 0xffffffffu;
+      cand_append(col < cols && key <= t0, key, col, lane, &s_count, ckey, ccol);
     }
   } else {
-    for (int i0 = 0; i0 < ncol4; i0 += TOPK_THREADS) {
-      const int i = i0 + tid;
-      uint32_t key4[4] = {0xffffffffu, 0xffffffffu, 0xffffffffu, 0xffffffffu};
-      const bool in = i < ncol4;
-      if (in) {
-        const float4 x = __ldg(v4 + i);
-        key4[0] = sel_key(x.x, descending); key4[1] = sel_key(x.y, descending);
-        key4[2] = sel_key(x.z, descending); key4[3] = sel_key(x.w, descending);
-      }
-      const bool any = in && (min(min(key4[0], key4[1]), min(key4[2], key4[3])) <= t0);
-      if (__ballot_sync(0xffffffffu, any) == 0) continue;  // warp-uniform
-#pragma unroll
-      for (int u = 0; u < 4; ++u) cand_append(in && key4[u] <= t0, key4[u], 4 * i + u, lane, &s_count, ckey, ccol);
+    // ---- pass 1: group minima (128-bit loads when the row is 16-byte aligned)
+    const int groups = (kk <= NT) ? NT : 2 * NT;
+    const int per_thread = groups / NT;  // 1 or 2
+    uint32_t m[2] = {0xffffffffu, 0xffffffffu};
+#pragma unroll 4
+    for (int i = tid; i < ncol4; i += NT) {
+      const float4 x = __ldg(v4 + i);
+      const uint32_t k0 = sel_key(x.x, descending), k1 = sel_key(x.y, descending);
+      const uint32_t k2 = sel_key(x.z, descending), k3 = sel_key(x.w, descending);
+      if (MODE == 1) *reinterpret_cast<uint4*>(rowkey + 4 * i) = make_uint4(k0, k1, k2, k3);
+      const int g = per_thread == 1 ? 0 : ((i / NT) & 1);
+      m[g] = min(m[g], min(min(k0, k1), min(k2, k3)));
     }
-    for (int c0 = ncol4 * 4; c0 < cols; c0 += TOPK_THREADS) {
-      const int c = c0 + tid;
-      const uint32_t key = c < cols ? sel_key(__ldg(v + c), descending) : 0xffffffffu;
-      cand_append(c < cols && key <= t0, key, c, lane, &s_count, ckey, ccol);
+    for (int c = ncol4 * 4 + tid; c < cols; c += NT) {
+      const uint32_t kc = sel_key(__ldg(v + c), descending);
+      if (MODE == 1) rowkey[c] = kc;
+      const int g = per_thread == 1 ? 0 : ((c / NT) & 1);
+      m[g] = min(m[g], kc);
+    }
+    // k-th smallest group minimum by bisection on the ordered key (32 barrier-counts): an upper bound of the k-th
+    // smallest element, nearly tight because k << number of groups.
+    if (kk > 0 && kk <= groups) {
+      uint32_t lo = 0, hi = 0xffffffffu;
+      while (lo < hi) {
+        const uint32_t mid = lo + ((hi - lo) >> 1);
+        int c = __syncthreads_count(m[0] <= mid);
+        if (per_thread == 2) c += __syncthreads_count(m[1] <= mid);
+        if (c >= kk) hi = mid; else lo = mid + 1;
+      }
+      t0 = lo;
+    }
+    __syncthreads();
+
+    // ---- pass 2: collect candidates <= t0
+    if (MODE == 1) {
+      const int nq4 = cols >> 2;
+      for (int i0 = 0; i0 < nq4; i0 += NT) {
+        const int i = i0 + tid;
+        uint4 k4 = make_uint4(0xffffffffu, 0xffffffffu, 0xffffffffu, 0xffffffffu);
+        const bool in = i < nq4;
+        if (in) k4 = *reinterpret_cast<const uint4*>(rowkey + 4 * i);
+        const bool any = in && min(min(k4.x, k4.y), min(k4.z, k4.w)) <= t0;
+        if (__ballot_sync(0xffffffffu, any) == 0) continue;  // warp-uniform: nothing to take in these 128 columns
+        cand_append(in && k4.x <= t0, k4.x, 4 * i + 0, lane, &s_count, ckey, ccol);
+        cand_append(in && k4.y <= t0, k4.y, 4 * i + 1, lane, &s_count, ckey, ccol);
+        cand_append(in && k4.z <= t0, k4.z, 4 * i + 2, lane, &s_count, ckey, ccol);
+        cand_append(in && k4.w <= t0, k4.w, 4 * i + 3, lane, &s_count, ckey, ccol);
+      }
+      for (int c0 = nq4 * 4; c0 < cols; c0 += NT) {
+        const int c = c0 + tid;
+        const uint32_t key = c < cols ? rowkey[c] : 0xffffffffu;
+        cand_append(c < cols && key <= t0, key, c, lane, &s_count, ckey, ccol);
+      }
+    } else {
+      for (int i0 = 0; i0 < ncol4; i0 += NT) {
+        const int i = i0 + tid;
+        uint32_t key4[4] = {0xffffffffu, 0xffffffffu, 0xffffffffu, 0xffffffffu};
+        const bool in = i < ncol4;
+        if (in) {
+          const float4 x = __ldg(v4 + i);
+          key4[0] = sel_key(x.x, descending); key4[1] = sel_key(x.y, descending);
+          key4[2] = sel_key(x.z, descending); key4[3] = sel_key(x.w, descending);
+        }
+        const bool any = in && (min(min(key4[0], key4[1]), min(key4[2], key4[3])) <= t0);
+        if (__ballot_sync(0xffffffffu, any) == 0) continue;  // warp-uniform
+#pragma unroll
+        for (int u = 0; u < 4; ++u) cand_append(in && key4[u] <= t0, key4[u], 4 * i + u, lane, &s_count, ckey, ccol);
+      }
+      for (int c0 = ncol4 * 4; c0 < cols; c0 += NT) {
+        const int c = c0 + tid;
+        const uint32_t key = c < cols ? sel_key(__ldg(v + c), descending) : 0xffffffffu;
+        cand_append(c < cols && key <= t0, key, c, lane, &s_count, ckey, ccol);
+      }
     }
   }
   __syncthreads();
   int count = s_count;
 
   if (count > TOPK_CAP) {
-    // ---- fallback (heavy ties / adversarial order): exact k-th key by bisection, then ordered collection
+    // ---- fallback (heavy ties / adversarial order): exact k-th key by bisection over the row, ordered collection
+    auto key_at = [&](int c) -> uint32_t { return MODE == 1 ? rowkey[c] : sel_key(__ldg(v + c), descending); };
     uint32_t lo = 0, hi = 0xffffffffu;  // invariant: count(key <= hi) >= kk, count(key <= lo-1) < kk
     while (lo < hi) {
       const uint32_t mid = lo + ((hi - lo) >> 1);
       int cnt = 0;
-      for (int c = tid; c < cols; c += TOPK_THREADS) cnt += (SMEM_ROW ? rowkey[c] : sel_key(__ldg(v + c), descending)) <= mid;
-      cnt = block_sum_int(cnt, red);
+      for (int c = tid; c < cols; c += NT) cnt += key_at(c) <= mid;
+      cnt = block_sum_int<NT>(cnt, red);
       if (cnt >= kk) hi = mid; else lo = mid + 1;
     }
     t0 = lo;  // the kk-th smallest key
@@ -171,23 +203,23 @@ topk_rows_kernel(const float* __restrict__ vals, int cols, int64_t ldv, const in
     if (tid == 0) s_count = 0;
     __syncthreads();
     // strictly smaller keys (fewer than kk of them) in any order
-    for (int c0 = 0; c0 < cols; c0 += TOPK_THREADS) {
+    for (int c0 = 0; c0 < cols; c0 += NT) {
       const int c = c0 + tid;
-      const uint32_t key = c < cols ? (SMEM_ROW ? rowkey[c] : sel_key(__ldg(v + c), descending)) : 0xffffffffu;
+      const uint32_t key = c < cols ? key_at(c) : 0xffffffffu;
       cand_append(c < cols && key < t0, key, c, lane, &s_count, ckey, ccol);
     }
     __syncthreads();
     int have = s_count;
     // ties == t0 in column order until kk are held (chunk by chunk, ordered prefix over the CTA)
-    for (int c0 = 0; c0 < cols && have < kk; c0 += TOPK_THREADS) {
+    for (int c0 = 0; c0 < cols && have < kk; c0 += NT) {
       const int c = c0 + tid;
-      const bool take = c < cols && (SMEM_ROW ? rowkey[c] : sel_key(__ldg(v + c), descending)) == t0;
+      const bool take = c < cols && key_at(c) == t0;
       const uint32_t ballot = __ballot_sync(0xffffffffu, take);
       __syncthreads();
-      if (lane == 0) red[tid >> 5] = __popc(ballot);
+      if (lane == 0) red[warp] = __popc(ballot);
       __syncthreads();
       int before = 0, total = 0;
-      for (int w = 0; w < TOPK_THREADS / 32; ++w) { if (w < (tid >> 5)) before += red[w]; total += red[w]; }
+      for (int w = 0; w < NT / 32; ++w) { if (w < warp) before += red[w]; total += red[w]; }
       if (take) {
         const int pos = have + before + __popc(ballot & ((1u << lane) - 1));
         if (pos < kk) { ckey[pos] = t0; ccol[pos] = c; }
@@ -199,7 +231,7 @@ topk_rows_kernel(const float* __restrict__ vals, int cols, int64_t ldv, const in
   }
 
   // ---- finish: rank-sort candidates by (key, id) and emit the first kk
-  for (int e = tid; e < count; e += TOPK_THREADS) {
+  for (int e = tid; e < count; e += NT) {
     const uint32_t key = ckey[e];
     const int c = ccol[e];
     const int64_t id = ci ? ci[c] : (int64_t)c;
@@ -221,7 +253,7 @@ topk_rows_kernel(const float* __restrict__ vals, int cols, int64_t ldv, const in
     }
   }
   // fewer columns than k: pad like faiss (distance = +/-inf, id = -1)
-  for (int e = kk + tid; e < k; e += TOPK_THREADS) {
+  for (int e = kk + tid; e < k; e += NT) {
     od[e] = descending ? -INFINITY : INFINITY;
     if (idx64) reinterpret_cast<int64_t*>(out_i)[(size_t)row * k + e] = -1;
     else reinterpret_cast<int32_t*>(out_i)[(size_t)row * k + e] = -1;
@@ -229,24 +261,30 @@ topk_rows_kernel(const float* __restrict__ vals, int cols, int64_t ldv, const in
 }
 
 int topk_rows_launch(const float* vals, int rows, int cols, int64_t ldv, const int64_t* cand_i, int k, int descending,
-                     int64_t index_base, float* out_d, void* out_i, int idx64, cudaStream_t st) {
+                     int64_t index_base, float* out_d, void* out_i, int idx64, cudaStream_t st, const float* chunk_red,
+                     int64_t ld_chunk_red) {
   if (rows == 0 || k == 0) return REIDB200_OK;
   RB_REQUIRE(k > 0 && k <= TOPK_MAX_K, "topk: k=%d outside [1,%d]", k, TOPK_MAX_K);
   RB_REQUIRE(cols >= 0 && ldv >= cols, "topk: bad cols/ld");
-  if (cols <= TOPK_SMEM_ROW_MAX) {
+  const int nchunks = (cols + 31) / 32;
+  if (chunk_red != nullptr && nchunks >= 4 * k && nchunks <= TOPK_CHUNK_MAX) {
+    ProfScope _ps("topk_rows_kernel", st);
+    topk_rows_kernel<2, 128><<<rows, 128, align_up((size_t)nchunks * 4, 16), st>>>(
+        vals, cols, ldv, cand_i, k, descending, index_base, out_d, out_i, idx64, chunk_red, ld_chunk_red);
+  } else if (cols <= TOPK_SMEM_ROW_MAX) {
     static bool attr = false;
     if (!attr) {
-      RB_CUDA(cudaFuncSetAttribute(topk_rows_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+      RB_CUDA(cudaFuncSetAttribute(topk_rows_kernel<1, 512>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                    TOPK_SMEM_ROW_MAX * 4));
       attr = true;
     }
     ProfScope _ps("topk_rows_kernel", st);
-    topk_rows_kernel<true><<<rows, TOPK_THREADS, align_up((size_t)cols * 4, 16), st>>>(vals, cols, ldv, cand_i, k, descending,
-                                                                                      index_base, out_d, out_i, idx64);
+    topk_rows_kernel<1, 512><<<rows, 512, align_up((size_t)cols * 4, 16), st>>>(vals, cols, ldv, cand_i, k, descending,
+                                                                                index_base, out_d, out_i, idx64, nullptr, 0);
   } else {
     ProfScope _ps("topk_rows_kernel", st);
-    topk_rows_kernel<false><<<rows, TOPK_THREADS, 0, st>>>(vals, cols, ldv, cand_i, k, descending, index_base, out_d, out_i,
-                                                          idx64);
+    topk_rows_kernel<0, 512><<<rows, 512, 0, st>>>(vals, cols, ldv, cand_i, k, descending, index_base, out_d, out_i, idx64,
+                                                  nullptr, 0);
   }
   RB_LAUNCH_CHECK("topk_rows_kernel");
   return REIDB200_OK;
@@ -283,7 +321,8 @@ extern "C" size_t reidb200_knn_workspace_bytes(int nq, int nb, int d, int k) {
   c.take<float>(nq);
   c.take<char>(packed_bytes(nb, d));
   c.take<float>(nb);
-  c.take<float>((size_t)nq * chunk);
+  c.take<float>((size_t)nq * align_up((size_t)chunk, 4));
+  c.take<float>((size_t)nq * ceil_div(chunk, 32));
   if (nchunks > 1) {
     c.take<float>((size_t)nq * nchunks * k);
     c.take<int64_t>((size_t)nq * nchunks * k);
@@ -310,7 +349,10 @@ extern "C" int reidb200_knn(const float* xq, int nq, int64_t ldq, const float* x
   float* qq = c.take<float>(nq);
   char* pb = c.take<char>(packed_bytes(nb, d));
   float* bb = c.take<float>(nb);
-  float* dist = c.take<float>((size_t)nq * chunk);
+  const int64_t ldd = (int64_t)align_up((size_t)chunk, 4);  // 16-byte aligned rows: vector epilogue stores
+  float* dist = c.take<float>((size_t)nq * ldd);
+  const int ldcr = ceil_div(chunk, 32);
+  float* cred = c.take<float>((size_t)nq * ldcr);
   float* cd = nullptr;
   int64_t* cid = nullptr;
   if (nchunks > 1) {
@@ -325,13 +367,14 @@ extern "C" int reidb200_knn(const float* xq, int nq, int64_t ldq, const float* x
     const int c0 = ch * chunk;
     const int nc = min(chunk, nb - c0);
     rc = gemm_split_launch(pq, qq, nq, pb + (size_t)c0 * 2 * dp * sizeof(__nv_bfloat16), bb + c0, nc, d, metric, dist,
-                           chunk, st);
+                           ldd, st, cred, ldcr, desc);
     if (rc) return rc;
-    if (nchunks == 1) return topk_rows_launch(dist, nq, nc, chunk, nullptr, k, desc, index_base, out_d, out_i, idx64, st);
+    if (nchunks == 1)
+      return topk_rows_launch(dist, nq, nc, ldd, nullptr, k, desc, index_base, out_d, out_i, idx64, st, cred, ldcr);
     // per-chunk partial result -> slot ch of the candidate table [nq, nchunks*k] (row stride nchunks*k)
     // written through a strided view: out row stride is k, so select into a compact temp then merge below.
-    rc = topk_rows_launch(dist, nq, nc, chunk, nullptr, k, desc, index_base + c0, cd + (size_t)ch * nq * k,
-                          cid + (size_t)ch * nq * k, 1, st);
+    rc = topk_rows_launch(dist, nq, nc, ldd, nullptr, k, desc, index_base + c0, cd + (size_t)ch * nq * k,
+                          cid + (size_t)ch * nq * k, 1, st, cred, ldcr);
     if (rc) return rc;
   }
   // merge: candidate tables are [nchunks][nq][k]; gather per query through a transposing copy
@@ -339,7 +382,7 @@ extern "C" int reidb200_knn(const float* xq, int nq, int64_t ldq, const float* x
   float* md = dist;  // the distance block is free again: reuse as [nq, nchunks*k]
   int64_t* mi = reinterpret_cast<int64_t*>(dist + (size_t)nq * nchunks * k + 2);
   mi = reinterpret_cast<int64_t*>((reinterpret_cast<uintptr_t>(mi) + 7) & ~(uintptr_t)7);
-  RB_REQUIRE((size_t)nq * nchunks * k * 12 + 16 <= (size_t)nq * chunk * 4, "knn: merge buffer does not fit (k too large)");
+  RB_REQUIRE((size_t)nq * nchunks * k * 12 + 16 <= (size_t)nq * ldd * 4, "knn: merge buffer does not fit (k too large)");
   for (int ch = 0; ch < nchunks; ++ch) {
     RB_CUDA(cudaMemcpy2DAsync(md + (size_t)ch * k, (size_t)nchunks * k * 4, cd + (size_t)ch * nq * k, (size_t)k * 4,
                               (size_t)k * 4, nq, cudaMemcpyDeviceToDevice, st));
