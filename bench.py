@@ -193,6 +193,75 @@ def bench_assoc(steps, warmup):
     return out
 
 
+RETR_Q, RETR_G, RETR_D, RETR_K, RETR_PIECE = 10_000, 4_000_000, 2048, 100, 62_500
+
+
+def _gallery_piece(piece, rows, d, dev):
+    """Rows [piece*RETR_PIECE, ...) of the synthetic gallery: unit-norm N(0,I) rows, Philox-seeded by the GLOBAL piece id so
+    that the gallery (and therefore the result table) is the same at every GPU count."""
+    g = torch.Generator(device=dev)
+    g.manual_seed(1_000_003 + piece)
+    x = torch.randn((rows, d), generator=g, device=dev, dtype=torch.float32)
+    return torch.nn.functional.normalize(x, dim=1)
+
+
+def bench_retrieval(args, rank, world, dev, barrier):
+    """BASELINE.json configs[4]: 10k queries x 4M gallery x 2048-d, top-100, gallery sharded over the ranks (strong scaling):
+    resident packed shard per GPU -> tcgen05 GEMM + row-select per 2 GiB distance block -> one NCCL all-gather of the
+    per-shard (distance, id)[Q,100] tables -> merge.  Device-timed (events, max over ranks) and end to end (pinned host
+    queries in, host top-100 table out)."""
+    import reidb200  # noqa: F401
+    from reidb200 import _lib as L, shard
+
+    G = args.retrieval_gallery
+    Q, D, K = RETR_Q, RETR_D, RETR_K
+    lo, hi = shard.shard_bounds(G, world)[rank]
+    s = shard.ShardedSearcher(D, device=dev)
+    s.reserve(hi - lo)
+    r = lo
+    while r < hi:  # piecewise: the fp32 rows of a piece are dropped as soon as they are packed
+        piece, off = divmod(r, RETR_PIECE)
+        rows = _gallery_piece(piece, RETR_PIECE, D, dev)[off:min(RETR_PIECE, off + hi - r)]
+        s.append(rows)
+        r += rows.shape[0]
+    s.base = lo
+    gq = torch.Generator().manual_seed(0)
+    xq_host = torch.nn.functional.normalize(torch.randn((Q, D), generator=gq), dim=1).pin_memory()
+    xq = xq_host.to(dev)
+    steps = max(1, min(args.steps, 3))
+    Dd, Id = s.search_device(xq, K)  # warm-up (NCCL communicator, kernel attributes)
+    barrier()
+    L.profile_enable(True)
+    ms = _timed(lambda: s.search_device(xq, K), steps, barrier)
+    prof = L.profile_read()
+    L.profile_enable(False)
+    t = torch.tensor([ms], dtype=torch.float64, device=dev)
+    if world > 1:
+        import torch.distributed as dist
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t.item()) / steps
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        Dh, Ih = s.search(xq_host, K)
+    t = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    e2e_s = float(t.item()) / steps
+    gemm_n, gemm_ms = prof.get("gemm_split_tc_kernel", (0, 0.0))
+    local_flops = 2.0 * Q * (hi - lo) * D * steps
+    peaks, _ = _peaks()
+    tf = local_flops / (gemm_ms * 1e-3) / 1e12 if gemm_ms else None
+    return {"workload": "retrieval_%dq_x_%dg_d%d_top%d" % (Q, G, D, K), "scaling": "strong", "shards": world,
+            "rows_per_shard": hi - lo, "ms_per_search": ms, "pairs_per_s": Q * G / (ms * 1e-3),
+            "e2e_pairs_per_s": Q * G / e2e_s, "h2d_bytes_per_search": Q * D * 4, "d2h_bytes_per_search": Q * K * 12,
+            "allgather_bytes_per_rank": Q * K * 12 if world > 1 else 0,
+            "gemm_tflops_fp32_equiv": tf, "gemm_frac_of_peak_div3": (tf / (peaks["bf16_tflops_sustained"] / 3.0)) if tf else None,
+            "kernel_ms": {k: round(v[1] / steps, 3) for k, v in sorted(prof.items(), key=lambda kv: -kv[1][1])},
+            "launches": int(sum(n for n, _ in prof.values()) // steps),
+            "checksum": {"id_sum": int(Ih.astype(np.int64).sum()), "dist_sum": float(Dh.astype(np.float64).sum())}}
+
+
 # --------------------------------------------------------------------------------------------- CPU port / reference arm
 def cpu_sample(scale=4):
     """A bounded sample of the same workload: Market-shaped set at 1/scale of the query/gallery/identity counts."""
@@ -307,6 +376,12 @@ def run_ours(args):
     h2d = merged_host.numel() * 4 + sum(v.numel() * 4 for v in lab_host.values())
     d2h = G * 4 + 8
 
+    retrieval = None
+    if not args.no_retrieval:
+        merged = None
+        torch.cuda.empty_cache()
+        retrieval = bench_retrieval(args, rank, world, dev, barrier)
+
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -336,6 +411,8 @@ def run_ours(args):
         "kernel_share_of_step": share,
         "result": {"rank1": float(cmc_h[0]), "mAP": float(ap_h)},
     }
+    if retrieval is not None:
+        line["retrieval"] = retrieval
     if not args.no_assoc:
         line["assoc"] = bench_assoc(args.steps, args.warmup)
     if not args.no_cpu and world == 1:
@@ -358,6 +435,8 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-assoc", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-retrieval", action="store_true")
+    ap.add_argument("--retrieval-gallery", type=int, default=RETR_G)
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

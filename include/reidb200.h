@@ -110,6 +110,13 @@ size_t reidb200_knn_workspace_bytes(int nq, int nb, int d, int k);
 int reidb200_knn(const float* xq, int nq, int64_t ldq, const float* xb, int nb, int64_t ldb, int d,
                  int k, int metric, int64_t index_base, float* out_d, void* out_i, int idx64,
                  void* workspace, size_t workspace_bytes, void* stream);
+/* Same search against a gallery packed once with reidb200_pack_rows (packed_b = bf16 hi|lo planes, sqnorm_b f32[nb]):
+ * what a resident index does (GpuIndexFlatL2.add once, search many times, reid/faiss_utils.py:121-139) and what every
+ * rank of the gallery-sharded search calls on its own shard.  No fp32 copy of the gallery is needed. */
+size_t reidb200_knn_packed_workspace_bytes(int nq, int nb, int d, int k);
+int reidb200_knn_packed(const float* xq, int nq, int64_t ldq, const void* packed_b, const float* sqnorm_b, int nb,
+                        int d, int k, int metric, int64_t index_base, float* out_d, void* out_i, int idx64,
+                        void* workspace, size_t workspace_bytes, void* stream);
 /* Row-wise top-k of a materialised matrix (ascending unless descending != 0); optional explicit
  * candidate ids (cand_i, i64[rows, cols]) for merging per-shard results, else id = column +
  * index_base.  Used for the per-shard merge after the NCCL all-gather. */

@@ -43,6 +43,8 @@ SIGNATURES = {
     "reidb200_pack_rows": (_i, [_vp, _i, _i64, _i, _vp, _vp, _vp]),
     "reidb200_knn_workspace_bytes": (_sz, [_i, _i, _i, _i]),
     "reidb200_knn": (_i, [_vp, _i, _i64, _vp, _i, _i64, _i, _i, _i, _i64, _vp, _vp, _i, _vp, _sz, _vp]),
+    "reidb200_knn_packed_workspace_bytes": (_sz, [_i, _i, _i, _i]),
+    "reidb200_knn_packed": (_i, [_vp, _i, _i64, _vp, _vp, _i, _i, _i, _i, _i64, _vp, _vp, _i, _vp, _sz, _vp]),
     "reidb200_topk_rows": (_i, [_vp, _i, _i, _i64, _vp, _i, _i, _i64, _vp, _vp, _i, _vp]),
     "reidb200_eval_workspace_bytes": (_sz, [_i, _i]),
     "reidb200_eval_cmc_map": (_i, [_vp, _i, _i, _i64, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _sz, _vp]),

@@ -10,6 +10,8 @@
 //   finish  rank-sort the candidates by (key, id) and emit the first k.
 // If the candidate list overflows (heavy ties / adversarial order) the CTA falls back to an exact
 // bisection on the 32-bit ordered key.  Ties are broken by the lower id, like a stable argsort.
+#include <stdlib.h>
+
 #include "gemm.cuh"
 
 namespace reidb200 {
@@ -291,8 +293,11 @@ int topk_rows_launch(const float* vals, int rows, int cols, int64_t ldv, const i
 }
 
 // gallery columns per GEMM + select pass: distance block of at most 2^29 floats (2 GiB)
+// (REIDB200_KNN_BLOCK_FLOATS overrides the block size: lets the tests drive the multi-pass merge at small sizes)
 static int knn_chunk_cols(int nq, int nb) {
-  long long c = (1LL << 29) / (nq > 0 ? nq : 1);
+  long long block = 1LL << 29;
+  if (const char* e = getenv("REIDB200_KNN_BLOCK_FLOATS")) { const long long v = atoll(e); if (v >= 256) block = v; }
+  long long c = block / (nq > 0 ? nq : 1);
   c = c / 256 * 256;
   if (c < 256) c = 256;
   if (c > nb) c = nb;
@@ -312,21 +317,72 @@ extern "C" int reidb200_topk_rows(const float* vals, int rows, int cols, int64_t
                           (cudaStream_t)stream);
 }
 
-extern "C" size_t reidb200_knn_workspace_bytes(int nq, int nb, int d, int k) {
-  if (nq <= 0 || nb <= 0 || d <= 0 || k <= 0) return 0;
+// Shared body of knn / knn_packed: operands already packed; `c` carves the distance block, the chunk reductions and the
+// per-chunk candidate tables out of what is left of the workspace.
+static void knn_scratch_size(CarveSize& c, int nq, int nb, int k) {
   const int chunk = knn_chunk_cols(nq, nb);
   const int nchunks = ceil_div(nb, chunk);
-  CarveSize c;
-  c.take<char>(packed_bytes(nq, d));
-  c.take<float>(nq);
-  c.take<char>(packed_bytes(nb, d));
-  c.take<float>(nb);
   c.take<float>((size_t)nq * align_up((size_t)chunk, 4));
   c.take<float>((size_t)nq * ceil_div(chunk, 32));
   if (nchunks > 1) {
     c.take<float>((size_t)nq * nchunks * k);
     c.take<int64_t>((size_t)nq * nchunks * k);
   }
+}
+
+static int knn_core(const char* pq, const float* qq, int nq, const char* pb, const float* bb, int nb, int d, int k,
+                    int metric, int64_t index_base, float* out_d, void* out_i, int idx64, Carver& c, cudaStream_t st) {
+  const int chunk = knn_chunk_cols(nq, nb);
+  const int nchunks = ceil_div(nb, chunk);
+  const int dp = padded_dim(d);
+  const int desc = metric == REIDB200_DIST_DOT;
+  const int64_t ldd = (int64_t)align_up((size_t)chunk, 4);  // 16-byte aligned rows: vector epilogue stores
+  float* dist = c.take<float>((size_t)nq * ldd);
+  const int ldcr = ceil_div(chunk, 32);
+  float* cred = c.take<float>((size_t)nq * ldcr);
+  float* cd = nullptr;
+  int64_t* cid = nullptr;
+  if (nchunks > 1) {
+    cd = c.take<float>((size_t)nq * nchunks * k);
+    cid = c.take<int64_t>((size_t)nq * nchunks * k);
+  }
+  RB_REQUIRE(c.ok(), "knn: workspace too small");
+  for (int ch = 0; ch < nchunks; ++ch) {
+    const int c0 = ch * chunk;
+    const int nc = min(chunk, nb - c0);
+    int rc = gemm_split_launch(pq, qq, nq, pb + (size_t)c0 * 2 * dp * sizeof(__nv_bfloat16), bb + c0, nc, d, metric, dist,
+                               ldd, st, cred, ldcr, desc);
+    if (rc) return rc;
+    if (nchunks == 1)
+      return topk_rows_launch(dist, nq, nc, ldd, nullptr, k, desc, index_base, out_d, out_i, idx64, st, cred, ldcr);
+    // per-chunk partial result -> table ch of [nchunks][nq][k]
+    rc = topk_rows_launch(dist, nq, nc, ldd, nullptr, k, desc, index_base + c0, cd + (size_t)ch * nq * k,
+                          cid + (size_t)ch * nq * k, 1, st, cred, ldcr);
+    if (rc) return rc;
+  }
+  // merge: gather the per-chunk tables per query through transposing copies (nchunks*k candidates per query) and run
+  // one more selection with explicit ids.
+  float* md = dist;  // the distance block is free again: reuse as [nq, nchunks*k]
+  int64_t* mi = reinterpret_cast<int64_t*>(dist + (size_t)nq * nchunks * k + 2);
+  mi = reinterpret_cast<int64_t*>((reinterpret_cast<uintptr_t>(mi) + 7) & ~(uintptr_t)7);
+  RB_REQUIRE((size_t)nq * nchunks * k * 12 + 16 <= (size_t)nq * ldd * 4, "knn: merge buffer does not fit (k too large)");
+  for (int ch = 0; ch < nchunks; ++ch) {
+    RB_CUDA(cudaMemcpy2DAsync(md + (size_t)ch * k, (size_t)nchunks * k * 4, cd + (size_t)ch * nq * k, (size_t)k * 4,
+                              (size_t)k * 4, nq, cudaMemcpyDeviceToDevice, st));
+    RB_CUDA(cudaMemcpy2DAsync(mi + (size_t)ch * k, (size_t)nchunks * k * 8, cid + (size_t)ch * nq * k, (size_t)k * 8,
+                              (size_t)k * 8, nq, cudaMemcpyDeviceToDevice, st));
+  }
+  return topk_rows_launch(md, nq, nchunks * k, (int64_t)nchunks * k, mi, k, desc, 0, out_d, out_i, idx64, st);
+}
+
+extern "C" size_t reidb200_knn_workspace_bytes(int nq, int nb, int d, int k) {
+  if (nq <= 0 || nb <= 0 || d <= 0 || k <= 0) return 0;
+  CarveSize c;
+  c.take<char>(packed_bytes(nq, d));
+  c.take<float>(nq);
+  c.take<char>(packed_bytes(nb, d));
+  c.take<float>(nb);
+  knn_scratch_size(c, nq, nb, k);
   return align_up(c.off, 256);
 }
 
@@ -340,54 +396,45 @@ extern "C" int reidb200_knn(const float* xq, int nq, int64_t ldq, const float* x
   RB_REQUIRE(workspace && workspace_bytes >= reidb200_knn_workspace_bytes(nq, nb, d, k), "knn: workspace too small");
   RB_REQUIRE((reinterpret_cast<uintptr_t>(workspace) & 255) == 0, "knn: workspace must be 256-byte aligned");
   cudaStream_t st = (cudaStream_t)stream;
-  const int chunk = knn_chunk_cols(nq, nb);
-  const int nchunks = ceil_div(nb, chunk);
-  const int dp = padded_dim(d);
-  const int desc = metric == REIDB200_DIST_DOT;
   Carver c(workspace, workspace_bytes);
   char* pq = c.take<char>(packed_bytes(nq, d));
   float* qq = c.take<float>(nq);
   char* pb = c.take<char>(packed_bytes(nb, d));
   float* bb = c.take<float>(nb);
-  const int64_t ldd = (int64_t)align_up((size_t)chunk, 4);  // 16-byte aligned rows: vector epilogue stores
-  float* dist = c.take<float>((size_t)nq * ldd);
-  const int ldcr = ceil_div(chunk, 32);
-  float* cred = c.take<float>((size_t)nq * ldcr);
-  float* cd = nullptr;
-  int64_t* cid = nullptr;
-  if (nchunks > 1) {
-    cd = c.take<float>((size_t)nq * nchunks * k);
-    cid = c.take<int64_t>((size_t)nq * nchunks * k);
-  }
   int rc = pack_rows_launch(xq, nq, ldq, d, pq, qq, st);
   if (rc) return rc;
   if (xq == xb && nq == nb && ldq == ldb) { pb = pq; bb = qq; }
   else { rc = pack_rows_launch(xb, nb, ldb, d, pb, bb, st); if (rc) return rc; }
-  for (int ch = 0; ch < nchunks; ++ch) {
-    const int c0 = ch * chunk;
-    const int nc = min(chunk, nb - c0);
-    rc = gemm_split_launch(pq, qq, nq, pb + (size_t)c0 * 2 * dp * sizeof(__nv_bfloat16), bb + c0, nc, d, metric, dist,
-                           ldd, st, cred, ldcr, desc);
-    if (rc) return rc;
-    if (nchunks == 1)
-      return topk_rows_launch(dist, nq, nc, ldd, nullptr, k, desc, index_base, out_d, out_i, idx64, st, cred, ldcr);
-    // per-chunk partial result -> slot ch of the candidate table [nq, nchunks*k] (row stride nchunks*k)
-    // written through a strided view: out row stride is k, so select into a compact temp then merge below.
-    rc = topk_rows_launch(dist, nq, nc, ldd, nullptr, k, desc, index_base + c0, cd + (size_t)ch * nq * k,
-                          cid + (size_t)ch * nq * k, 1, st, cred, ldcr);
-    if (rc) return rc;
-  }
-  // merge: candidate tables are [nchunks][nq][k]; gather per query through a transposing copy
-  // (nchunks*k values per query) and run one more selection with explicit ids.
-  float* md = dist;  // the distance block is free again: reuse as [nq, nchunks*k]
-  int64_t* mi = reinterpret_cast<int64_t*>(dist + (size_t)nq * nchunks * k + 2);
-  mi = reinterpret_cast<int64_t*>((reinterpret_cast<uintptr_t>(mi) + 7) & ~(uintptr_t)7);
-  RB_REQUIRE((size_t)nq * nchunks * k * 12 + 16 <= (size_t)nq * ldd * 4, "knn: merge buffer does not fit (k too large)");
-  for (int ch = 0; ch < nchunks; ++ch) {
-    RB_CUDA(cudaMemcpy2DAsync(md + (size_t)ch * k, (size_t)nchunks * k * 4, cd + (size_t)ch * nq * k, (size_t)k * 4,
-                              (size_t)k * 4, nq, cudaMemcpyDeviceToDevice, st));
-    RB_CUDA(cudaMemcpy2DAsync(mi + (size_t)ch * k, (size_t)nchunks * k * 8, cid + (size_t)ch * nq * k, (size_t)k * 8,
-                              (size_t)k * 8, nq, cudaMemcpyDeviceToDevice, st));
-  }
-  return topk_rows_launch(md, nq, nchunks * k, (int64_t)nchunks * k, mi, k, desc, 0, out_d, out_i, idx64, st);
+  return knn_core(pq, qq, nq, pb, bb, nb, d, k, metric, index_base, out_d, out_i, idx64, c, st);
+}
+
+extern "C" size_t reidb200_knn_packed_workspace_bytes(int nq, int nb, int d, int k) {
+  if (nq <= 0 || nb <= 0 || d <= 0 || k <= 0) return 0;
+  CarveSize c;
+  c.take<char>(packed_bytes(nq, d));
+  c.take<float>(nq);
+  knn_scratch_size(c, nq, nb, k);
+  return align_up(c.off, 256);
+}
+
+extern "C" int reidb200_knn_packed(const float* xq, int nq, int64_t ldq, const void* packed_b, const float* sqnorm_b,
+                                   int nb, int d, int k, int metric, int64_t index_base, float* out_d, void* out_i,
+                                   int idx64, void* workspace, size_t workspace_bytes, void* stream) {
+  if (nq == 0) return REIDB200_OK;
+  RB_REQUIRE(xq && packed_b && sqnorm_b && out_d && out_i && nq > 0 && nb > 0 && d > 0,
+             "knn_packed: bad argument nq=%d nb=%d d=%d", nq, nb, d);
+  RB_REQUIRE(k > 0 && k <= TOPK_MAX_K, "knn_packed: k=%d outside [1,%d]", k, TOPK_MAX_K);
+  RB_REQUIRE(metric == REIDB200_DIST_SQL2 || metric == REIDB200_DIST_DOT, "knn_packed: metric must be SQL2 or DOT");
+  RB_REQUIRE(workspace && workspace_bytes >= reidb200_knn_packed_workspace_bytes(nq, nb, d, k),
+             "knn_packed: workspace too small");
+  RB_REQUIRE((reinterpret_cast<uintptr_t>(workspace) & 255) == 0 && (reinterpret_cast<uintptr_t>(packed_b) & 127) == 0,
+             "knn_packed: workspace must be 256-byte and the packed gallery 128-byte aligned");
+  cudaStream_t st = (cudaStream_t)stream;
+  Carver c(workspace, workspace_bytes);
+  char* pq = c.take<char>(packed_bytes(nq, d));
+  float* qq = c.take<float>(nq);
+  int rc = pack_rows_launch(xq, nq, ldq, d, pq, qq, st);
+  if (rc) return rc;
+  return knn_core(pq, qq, nq, static_cast<const char*>(packed_b), sqnorm_b, nb, d, k, metric, index_base, out_d, out_i,
+                  idx64, c, st);
 }

@@ -85,6 +85,51 @@ def knn(xq, xb, k, metric="sql2", index_base=0, idx64=True):
     return D, I
 
 
+def pack_rows(x, out=None, sqnorm=None):
+    """f32[rows,d] -> (packed u8 bytes of the bf16 hi|lo planes, sqnorm f32[rows]): the resident form of a gallery.
+    `out` / `sqnorm` may be slices of a larger preallocated shard so that a gallery is packed piecewise."""
+    x = _f32(x)
+    dev = L.require_device(x)
+    rows, d = x.shape
+    lib = L.load()
+    nbytes = lib.reidb200_pack_bytes(rows, d)
+    if out is None:
+        out = torch.empty(max(nbytes, 256), dtype=torch.uint8, device=dev)
+    if sqnorm is None:
+        sqnorm = torch.empty(rows, dtype=torch.float32, device=dev)
+    if rows:
+        with torch.cuda.device(dev):
+            L.check(lib.reidb200_pack_rows(x.data_ptr(), rows, x.stride(0), d, out.data_ptr(), sqnorm.data_ptr(), L.stream_ptr()))
+    return out, sqnorm
+
+
+def packed_row_bytes(d):
+    """bytes one gallery row occupies in packed form (bf16 hi + lo planes, d padded to 64)."""
+    return 2 * ((int(d) + 63) // 64 * 64) * 2
+
+
+def knn_packed(xq, packed, sqnorm, nb, d, k, metric="sql2", index_base=0, idx64=True):
+    """knn against a gallery packed once by pack_rows (resident index / one shard of a sharded gallery)."""
+    xq = _f32(xq)
+    dev = L.require_device(xq)
+    nq, dq = xq.shape
+    if dq != d:
+        raise ValueError("knn_packed: query dimension %d != gallery dimension %d" % (dq, d))
+    D = torch.empty((nq, k), dtype=torch.float32, device=dev)
+    I = torch.empty((nq, k), dtype=torch.int64 if idx64 else torch.int32, device=dev)
+    if nq == 0:
+        return D, I
+    if nb == 0:
+        raise ValueError("knn: empty database")
+    lib = L.load()
+    ws = L.workspace(lib.reidb200_knn_packed_workspace_bytes(nq, nb, d, k), dev)
+    with torch.cuda.device(dev):
+        L.check(lib.reidb200_knn_packed(xq.data_ptr(), nq, xq.stride(0), packed.data_ptr(), sqnorm.data_ptr(), int(nb), int(d),
+                                        int(k), _KIND[metric], int(index_base), D.data_ptr(), I.data_ptr(), 1 if idx64 else 0,
+                                        ws.data_ptr(), ws.numel(), L.stream_ptr()))
+    return D, I
+
+
 def topk_rows(vals, k, descending=False, cand_i=None, index_base=0, idx64=True):
     vals = _f32(vals)
     dev = L.require_device(vals)

@@ -1,0 +1,149 @@
+"""Gallery-sharded exact k-NN across the GPUs of one box, one process per GPU.
+
+Mirrors the reference's `index_init_gpu` (reid/faiss_utils.py:121-135): a faiss `IndexShards` over one
+`GpuIndexFlatL2` per GPU -- contiguous row ranges per shard, queries replicated, per-shard top-k merged.  Here every
+rank owns one shard as a RESIDENT packed operand (bf16 hi|lo planes + squared norms, packed once at add time; the fp32
+rows are not kept), runs the tcgen05 GEMM + chunk-guided row-select of libreidb200 on it (`reidb200_knn_packed`), and
+the per-shard (distance, global id)[Q,k] tables are exchanged with ONE `all_gather` (NCCL over NVLink/NVSwitch,
+Q*k*12 bytes per rank) and merged P*k -> k by the same row-select kernel with explicit candidate ids
+(`reidb200_topk_rows`).  Ties resolve to the lower global id on every rank, so all ranks return identical tables.
+
+`local_search` / `merge` are injection points for the host-logic tests (gloo, CPU tensors); the defaults are the CUDA
+kernels and raise without an sm_100 device -- there is no CPU fallback.
+"""
+from __future__ import annotations
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+from . import _lib as L
+from . import ops
+
+
+def shard_bounds(n: int, world: int):
+    """Contiguous split used by add(): shard r holds rows [lo_r, hi_r), ceil(n/world) rows each (the last ones may be
+    short or empty)."""
+    per = (n + world - 1) // world if world > 0 else n
+    return [(min(n, r * per), min(n, (r + 1) * per)) for r in range(world)]
+
+
+class ShardedSearcher:
+    def __init__(self, d, group=None, device=None, local_search=None, merge=None):
+        self.d = int(d)
+        self.group = group
+        self.distributed = dist.is_available() and dist.is_initialized()
+        self.rank = dist.get_rank(group) if self.distributed else 0
+        self.world = dist.get_world_size(group) if self.distributed else 1
+        self._custom = local_search is not None
+        self._local_search = local_search
+        self._merge = merge
+        if self._custom:
+            self.device = torch.device("cpu") if device is None else torch.device(device)
+        else:
+            self.device = device or L.require_device()
+        self.reset()
+
+    # ------------------------------------------------------------------ shard contents
+    def reset(self):
+        self.base = 0          # global id of local row 0
+        self.n_local = 0
+        self.capacity = 0
+        self._packed = None    # u8 [capacity * packed_row_bytes]
+        self._sqnorm = None    # f32 [capacity]
+        self._rows = None      # injected-search mode keeps the rows as given
+
+    @property
+    def ntotal(self):
+        """Rows over all shards (collective when distributed)."""
+        if not self.distributed:
+            return self.n_local
+        t = torch.tensor([self.n_local], dtype=torch.int64, device=self.device)
+        dist.all_reduce(t, group=self.group)
+        return int(t.item())
+
+    def reserve(self, rows):
+        """Preallocate the packed shard so a large gallery can be appended piece by piece (no 2x peak)."""
+        if self._custom:
+            return
+        rows = int(rows)
+        rb = ops.packed_row_bytes(self.d)
+        packed = torch.empty(max(rows * rb, 256), dtype=torch.uint8, device=self.device)
+        sq = torch.empty(max(rows, 1), dtype=torch.float32, device=self.device)
+        if self.n_local:
+            packed[: self.n_local * rb].copy_(self._packed[: self.n_local * rb])
+            sq[: self.n_local].copy_(self._sqnorm[: self.n_local])
+        self._packed, self._sqnorm, self.capacity = packed, sq, rows
+
+    def append(self, x):
+        """Append local rows f32[n,d] (host or device) to this rank's shard; global ids continue from base."""
+        n = int(x.shape[0])
+        if n == 0:
+            return
+        if x.shape[1] != self.d:
+            raise ValueError("append: feature dimension %d != %d" % (x.shape[1], self.d))
+        if self._custom:
+            x = torch.as_tensor(np.asarray(x, np.float32)) if not isinstance(x, torch.Tensor) else x.float()
+            self._rows = x if self._rows is None else torch.cat([self._rows, x], 0)
+            self.n_local += n
+            return
+        if self.n_local + n > self.capacity:
+            self.reserve(max(self.n_local + n, 2 * self.capacity))
+        rb = ops.packed_row_bytes(self.d)
+        lo = self.n_local
+        ops.pack_rows(L.as_f32_cuda(x, self.device), out=self._packed[lo * rb:(lo + n) * rb], sqnorm=self._sqnorm[lo:lo + n])
+        self.n_local += n
+
+    def add_shard(self, x_local, base=None):
+        """This rank's rows; `base` = global id of its first row (default: exclusive prefix sum of the shard sizes over
+        ranks, i.e. shards are numbered in rank order like IndexShards(successive_ids=True))."""
+        if self.n_local:
+            raise NotImplementedError("add_shard once after reset (contiguous shards); use append() to extend")
+        self.append(x_local)
+        if base is None:
+            base = 0
+            if self.distributed:
+                sizes = torch.zeros(self.world, dtype=torch.int64, device=self.device)
+                sizes[self.rank] = self.n_local
+                dist.all_reduce(sizes, group=self.group)
+                base = int(sizes[: self.rank].sum().item())
+        self.base = int(base)
+
+    def add(self, x):
+        """Whole gallery given on every rank (faiss `index.add(x)` on an IndexShards): keep only this rank's slice."""
+        lo, hi = shard_bounds(int(x.shape[0]), self.world)[self.rank]
+        self.add_shard(x[lo:hi], base=lo)
+
+    # ------------------------------------------------------------------ search
+    def _search_local(self, xq, k, metric):
+        if self._custom:
+            return self._local_search(xq, self._rows, k, metric, self.base)
+        return ops.knn_packed(xq, self._packed, self._sqnorm, self.n_local, self.d, k, metric, index_base=self.base, idx64=True)
+
+    def search_device(self, xq, k, metric="sql2"):
+        """(D f32[Q,k], I i64[Q,k]) identical on every rank; queries must be the same on every rank."""
+        if not self._custom:
+            xq = L.as_f32_cuda(xq, self.device)
+        nq = int(xq.shape[0])
+        pad = float("-inf") if metric == "dot" else float("inf")
+        if self.n_local:
+            Dl, Il = self._search_local(xq, k, metric)
+        else:
+            Dl = torch.full((nq, k), pad, dtype=torch.float32, device=self.device)
+            Il = torch.full((nq, k), -1, dtype=torch.int64, device=self.device)
+        if self.world == 1:
+            return Dl, Il
+        Dg = torch.empty((self.world * nq, k), dtype=torch.float32, device=self.device)
+        Ig = torch.empty((self.world * nq, k), dtype=torch.int64, device=self.device)
+        dist.all_gather_into_tensor(Dg, Dl.contiguous(), group=self.group)
+        dist.all_gather_into_tensor(Ig, Il.contiguous(), group=self.group)
+        cand_d = Dg.view(self.world, nq, k).permute(1, 0, 2).reshape(nq, self.world * k).contiguous()
+        cand_i = Ig.view(self.world, nq, k).permute(1, 0, 2).reshape(nq, self.world * k).contiguous()
+        if self._custom:
+            return self._merge(cand_d, cand_i, k, metric)
+        return ops.topk_rows(cand_d, k, descending=(metric == "dot"), cand_i=cand_i, idx64=True)
+
+    def search(self, xq, k, metric="sql2"):
+        """faiss-style host results (D f32[Q,k], I i64[Q,k]) as numpy."""
+        D, I = self.search_device(xq, k, metric)
+        return D.cpu().numpy(), I.cpu().numpy()

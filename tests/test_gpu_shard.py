@@ -1,0 +1,97 @@
+"""GPU: resident packed gallery search (reidb200_knn_packed), the multi-pass merge of knn, and the sharded searcher
+(world size 1 here; the NCCL path is exercised by tools/shard_check.py under torchrun and by bench.py --gpus N)."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import reid_oracle as O
+
+pytestmark = pytest.mark.gpu
+REL = 1e-4
+
+
+def _unit(x):
+    return (x / np.linalg.norm(x, axis=1, keepdims=True)).astype(np.float32)
+
+
+def _check(D, I, xq, xb, k):
+    Do, Io = O.knn_l2(xb, xq, k)
+    np.testing.assert_allclose(D, Do, rtol=REL, atol=2e-5)
+    bad = I != Io
+    if bad.any():
+        full = O.sql2_dist(xq, xb).astype(np.float64)
+        r, c = np.where(bad)
+        assert np.allclose(full[r, I[r, c]], full[r, Io[r, c]], rtol=REL, atol=2e-5), "non-tie index mismatch"
+    assert (np.diff(D, axis=1) >= 0).all()
+
+
+@pytest.mark.parametrize("nq,nb,d,k", [(9, 500, 48, 10), (130, 9000, 128, 100)])
+def test_knn_packed_equals_knn(rb, nq, nb, d, k):
+    from reidb200 import ops
+
+    rng = np.random.default_rng(nb)
+    xb, xq = _unit(rng.standard_normal((nb, d))), _unit(rng.standard_normal((nq, d)))
+    D0, I0 = ops.knn(xq, xb, k, "sql2", index_base=1000)
+    packed, sq = ops.pack_rows(xb)
+    D1, I1 = ops.knn_packed(xq, packed, sq, nb, d, k, "sql2", index_base=1000)
+    assert torch.equal(D0, D1) and torch.equal(I0, I1)  # same kernels, same operands: bit-identical
+    _check(D1.cpu().numpy(), I1.cpu().numpy() - 1000, xq, xb, k)
+    Dd, Id = ops.knn_packed(xq, packed, sq, nb, d, k, "dot")
+    ref = xq @ xb.T
+    order = np.argsort(-ref, axis=1, kind="stable")[:, :k]
+    np.testing.assert_allclose(Dd.cpu().numpy(), np.take_along_axis(ref, order, 1), rtol=REL, atol=2e-5)
+
+
+def test_knn_multipass_merge(rb, monkeypatch):
+    """Gallery wider than one distance block: per-block top-k tables merged by a final selection with explicit ids."""
+    from reidb200 import ops
+
+    rng = np.random.default_rng(5)
+    nq, nb, d, k = 40, 6000, 64, 50
+    xb, xq = _unit(rng.standard_normal((nb, d))), _unit(rng.standard_normal((nq, d)))
+    xb[4100] = xb[7]  # duplicate rows in different blocks: lower id first after the merge
+    xq[0] = xb[7]
+    monkeypatch.setenv("REIDB200_KNN_BLOCK_FLOATS", str(nq * 1024))  # 1024 gallery columns per pass -> 6 passes
+    D, I = ops.knn(xq, xb, k, "sql2")
+    monkeypatch.delenv("REIDB200_KNN_BLOCK_FLOATS")
+    D1, I1 = ops.knn(xq, xb, k, "sql2")
+    D, I = D.cpu().numpy(), I.cpu().numpy()
+    _check(D, I, xq, xb, k)
+    assert I[0, 0] == 7 and I[0, 1] == 4100
+    assert np.array_equal(I, I1.cpu().numpy()) and np.array_equal(D, D1.cpu().numpy())
+
+
+def test_sharded_searcher_single_rank(rb):
+    from reidb200 import shard
+
+    rng = np.random.default_rng(9)
+    nb, d, k = 5000, 96, 100
+    xb, xq = _unit(rng.standard_normal((nb, d))), _unit(rng.standard_normal((33, d)))
+    s = shard.ShardedSearcher(d)
+    s.reserve(nb)
+    for lo in range(0, nb, 1200):  # piecewise append into the preallocated packed shard
+        s.append(xb[lo:lo + 1200])
+    assert s.ntotal == nb
+    D, I = s.search(xq, k)
+    _check(D, I, xq, xb, k)
+    s.reset()
+    s.add_shard(xb[:10], base=70)
+    D, I = s.search(xq[:3], 12)
+    assert (I[:, 10:] == -1).all() and np.isinf(D[:, 10:]).all() and I[:, :10].min() == 70
+
+
+def test_faiss_index_shim(rb):
+    from reidb200 import faiss_utils as F
+
+    rng = np.random.default_rng(2)
+    xb, xq = _unit(rng.standard_normal((900, 32))), _unit(rng.standard_normal((11, 32)))
+    idx = F.index_init_gpu(1, 32)
+    idx.add(xb)
+    D, I = idx.search(xq, 5)
+    _check(D, I, xq, xb, 5)
+    D2, I2 = F.search_index_pytorch(idx, torch.from_numpy(xq).cuda(), 5)
+    assert np.array_equal(I2.cpu().numpy(), I)
+    D3, I3 = F.search_raw_array_pytorch(None, torch.from_numpy(xb).cuda(), torch.from_numpy(xq).cuda(), 5)
+    assert I3.dtype == torch.int32 and np.array_equal(I3.cpu().numpy(), I)

@@ -1,0 +1,103 @@
+"""CPU, world_size 2 over gloo: host logic of the gallery-sharded search (partitioning, global ids, all_gather layout,
+merge tie order).  The per-shard search and the merge are injected numpy stand-ins built on the oracle; the product
+defaults are the CUDA kernels (tests/test_gpu_shard.py)."""
+import os
+import socket
+import sys
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _oracle_local_search(xq, rows, k, metric, base):
+    from oracle import reid_oracle as O
+
+    kk = min(k, rows.shape[0])
+    D = np.full((xq.shape[0], k), np.inf, np.float32)
+    I = np.full((xq.shape[0], k), -1, np.int64)
+    Dk, Ik = O.knn_l2(rows.numpy(), xq.numpy(), kk)
+    D[:, :kk], I[:, :kk] = Dk, Ik + base
+    return torch.from_numpy(D), torch.from_numpy(I)
+
+
+def _oracle_merge(cand_d, cand_i, k, metric):
+    d, i = cand_d.numpy(), cand_i.numpy()
+    order = np.lexsort((i, d), axis=1)[:, :k]  # by distance, ties -> lower global id
+    return torch.from_numpy(np.take_along_axis(d, order, 1)), torch.from_numpy(np.take_along_axis(i, order, 1))
+
+
+def _worker(rank, world, port, n_gallery, out_dir):
+    sys.path.insert(0, ROOT)
+    import reidb200  # noqa: F401
+    from reidb200 import shard
+
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        rng = np.random.default_rng(0)
+        gallery = rng.standard_normal((n_gallery, 16)).astype(np.float32)
+        xq = rng.standard_normal((7, 16)).astype(np.float32)
+        if n_gallery > 5:
+            gallery[5] = gallery[n_gallery - 2]  # an exact duplicate across the two shards: tie -> lower id first
+            xq[0] = gallery[5]
+        s = shard.ShardedSearcher(16, local_search=_oracle_local_search, merge=_oracle_merge)
+        s.add(gallery)
+        assert s.ntotal == n_gallery
+        lo, hi = shard.shard_bounds(n_gallery, world)[rank]
+        assert (s.base, s.n_local) == (lo, hi - lo)
+        D, I = s.search(torch.from_numpy(xq), 4)
+        np.savez(os.path.join(out_dir, "r%d.npz" % rank), D=D, I=I)
+        # per-rank rows with implicit bases (exclusive prefix sum over ranks)
+        s2 = shard.ShardedSearcher(16, local_search=_oracle_local_search, merge=_oracle_merge)
+        s2.add_shard(gallery[lo:hi])
+        assert s2.base == lo
+        D2, I2 = s2.search(torch.from_numpy(xq), 4)
+        assert np.array_equal(I2, I) and np.array_equal(D2, D)
+    finally:
+        dist.destroy_process_group()
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+@pytest.mark.parametrize("n_gallery", [41, 3])
+def test_sharded_search_world2_gloo(tmp_path, n_gallery):
+    from oracle import reid_oracle as O
+
+    mp.spawn(_worker, args=(2, _free_port(), n_gallery, str(tmp_path)), nprocs=2, join=True)
+    r0, r1 = np.load(tmp_path / "r0.npz"), np.load(tmp_path / "r1.npz")
+    assert np.array_equal(r0["I"], r1["I"]) and np.array_equal(r0["D"], r1["D"])  # every rank returns the same table
+    rng = np.random.default_rng(0)
+    gallery = rng.standard_normal((n_gallery, 16)).astype(np.float32)
+    xq = rng.standard_normal((7, 16)).astype(np.float32)
+    if n_gallery > 5:
+        gallery[5] = gallery[n_gallery - 2]
+        xq[0] = gallery[5]
+    k = 4
+    Dw, Iw = O.knn_l2(gallery, xq, min(k, n_gallery))
+    assert np.array_equal(r0["I"][:, : Iw.shape[1]], Iw)
+    np.testing.assert_allclose(r0["D"][:, : Dw.shape[1]], Dw, rtol=1e-5, atol=1e-5)
+    if n_gallery > 5:
+        assert r0["I"][0, 0] == 5 and r0["I"][0, 1] == n_gallery - 2
+    if n_gallery < k:  # fewer rows than k: padded like faiss
+        assert (r0["I"][:, n_gallery:] == -1).all() and np.isinf(r0["D"][:, n_gallery:]).all()
+
+
+def test_shard_bounds():
+    sys.path.insert(0, ROOT)
+    import reidb200  # noqa: F401
+    from reidb200 import shard
+
+    assert shard.shard_bounds(10, 4) == [(0, 3), (3, 6), (6, 9), (9, 10)]
+    assert shard.shard_bounds(2, 4) == [(0, 1), (1, 2), (2, 2), (2, 2)]
+    assert shard.shard_bounds(0, 2) == [(0, 0), (0, 0)]
+    b = shard.shard_bounds(4_000_000, 8)
+    assert b[0] == (0, 500_000) and b[-1] == (3_500_000, 4_000_000)

@@ -1,0 +1,54 @@
+"""torchrun --nproc-per-node N tools/shard_check.py : the NCCL path of the gallery-sharded search against (a) the same
+search on ONE resident gallery (rank 0, bit-identical tables expected: same kernels, same tie rule) and (b) the CPU oracle
+on a sub-problem.  Prints one line per check; exit code 0 = all equal."""
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import numpy as np
+import torch
+import torch.distributed as dist
+
+import reidb200  # noqa: F401
+from oracle import reid_oracle as O
+from reidb200 import ops, shard
+
+rank, world, local = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1)), int(os.environ.get("LOCAL_RANK", 0))
+torch.cuda.set_device(local)
+dev = torch.device("cuda", local)
+if world > 1:
+    dist.init_process_group("nccl", device_id=dev)
+ok = True
+for nq, nb, d, k in ((64, 20_001, 128, 100), (300, 150_000, 256, 100), (17, 5, 32, 10)):
+    rng = np.random.default_rng(nb)
+    xb = rng.standard_normal((nb, d)).astype(np.float32)
+    xb /= np.linalg.norm(xb, axis=1, keepdims=True)
+    xq = rng.standard_normal((nq, d)).astype(np.float32)
+    xq /= np.linalg.norm(xq, axis=1, keepdims=True)
+    if nb > 100:
+        xb[nb - 3] = xb[11]  # duplicate rows in the first and the last shard
+        xq[0] = xb[11]
+    s = shard.ShardedSearcher(d, device=dev)
+    s.add(xb)
+    D, I = s.search(xq, k)
+    D1, I1 = ops.knn(xq, xb, k, "sql2")
+    same = np.array_equal(I, I1.cpu().numpy()) and np.array_equal(D, D1.cpu().numpy())
+    kk = min(k, nb)
+    Do, Io = O.knn_l2(xb, xq[:16], kk)
+    bad = I[:16, :kk] != Io
+    tie_ok = True
+    if bad.any():
+        full = O.sql2_dist(xq[:16], xb).astype(np.float64)
+        r, c = np.where(bad)
+        tie_ok = bool(np.allclose(full[r, I[:16, :kk][r, c]], full[r, Io[r, c]], rtol=1e-4, atol=2e-5))
+    dup_ok = nb <= 100 or (I[0, 0] == 11 and I[0, 1] == nb - 3)
+    good = same and tie_ok and dup_ok and np.allclose(D[:16, :kk], Do, rtol=1e-4, atol=2e-5)
+    ok &= bool(good)
+    if rank == 0:
+        print("shard_check world=%d nq=%d nb=%d d=%d k=%d: sharded==single %s, oracle %s, dup order %s" %
+              (world, nq, nb, d, k, same, tie_ok, dup_ok), flush=True)
+t = torch.tensor([0 if ok else 1], device=dev)
+if world > 1:
+    dist.all_reduce(t)
+    dist.destroy_process_group()
+sys.exit(int(t.item() != 0))
