@@ -194,7 +194,8 @@ int reidb200_gallery_counts(reidb200_gallery* g, int32_t* out_counts, void* stre
 int reidb200_gallery_read_slot(reidb200_gallery* g, int slot, float* out_rows, void* stream);
 
 enum { REIDB200_IOU_PLAIN = 0, REIDB200_IOU_DIOU = 1 };
-enum { REIDB200_ASSOC_CLAMP_APP = 1, REIDB200_ASSOC_CLAMP_IOU = 2, REIDB200_ASSOC_NO_GATE = 4 };
+enum { REIDB200_ASSOC_CLAMP_APP = 1, REIDB200_ASSOC_CLAMP_IOU = 2, REIDB200_ASSOC_NO_GATE = 4,
+       REIDB200_ASSOC_SIMT = 8 /* plain fp32 SIMT kernel instead of the tcgen05 one: on-device cross-check for the tests */ };
 
 /* One frame:
  *   det_feat f32[M,d]; det_tlwh f32[M,4];

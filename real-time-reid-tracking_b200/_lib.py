@@ -19,7 +19,7 @@ OK, EINVAL, ECUDA, ELIMIT = 0, -1, -2, -3
 RESIZE_CV_LINEAR, RESIZE_PIL_ANTIALIAS = 0, 1
 DIST_EUCLID, DIST_COSINE_HALF, DIST_DOT, DIST_SQL2 = 0, 1, 2, 3
 IOU_PLAIN, IOU_DIOU = 0, 1
-ASSOC_CLAMP_APP, ASSOC_CLAMP_IOU, ASSOC_NO_GATE = 1, 2, 4
+ASSOC_CLAMP_APP, ASSOC_CLAMP_IOU, ASSOC_NO_GATE, ASSOC_SIMT = 1, 2, 4, 8
 
 _vp, _i, _i64, _sz, _f, _d = C.c_void_p, C.c_int, C.c_int64, C.c_size_t, C.c_float, C.c_double
 _f3 = C.POINTER(C.c_float)

@@ -6,15 +6,20 @@
 //   iou       boxmot/trackers/strongsort/sort/iou_matching.py:9-86, modification_deepsort/iou_matching.py:5-47
 // One kernel per frame: CTA t owns track t: per-track gallery x detections cosine minimum (fp32),
 // Mahalanobis gate + blend (fp64), IoU / DIoU row (fp64).
-#include "common.cuh"
+#include "gemm.cuh"
+#include "ptx.cuh"
 
 struct reidb200_gallery {
-  int slots, budget, d;
+  int slots, budget, d, dp;
   float* feats;      // [slots, budget, d] L2-normalised rows (ring per slot)
+  __nv_bfloat16* packed;  // [slots*budget, 2*dp] the same rows as bf16 hi|lo planes: A operand of the tcgen05 frame kernel
   int32_t* count;    // [slots] valid rows
   int32_t* head;     // [slots] next write position
   int32_t* scratch;  // [2*scratch_rows] per-row destination / rows-after
   int scratch_rows;
+  __nv_bfloat16* det_packed;  // [det_cap, 2*dp] L2-normalised detection features of the current frame, hi|lo planes
+  int det_cap;
+  CUtensorMap tm_gallery;     // TMA descriptor of `packed` (box 64 x 128)
 };
 
 namespace reidb200 {
@@ -43,7 +48,8 @@ __global__ void pf_assign_kernel(const int32_t* __restrict__ slot_of_row, int n,
 // warp per row: a / ||a|| in fp32 (matching.py:294-296), written to its ring position
 __global__ void __launch_bounds__(256)
 pf_write_kernel(const float* __restrict__ feats, int64_t ldf, const int32_t* __restrict__ slot_of_row,
-                const int32_t* __restrict__ dst, int n, int budget, int d, float* __restrict__ gal) {
+                const int32_t* __restrict__ dst, int n, int budget, int d, int dp, float* __restrict__ gal,
+                __nv_bfloat16* __restrict__ packed) {
   const int i = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int lane = threadIdx.x & 31;
   if (i >= n) return;
@@ -53,8 +59,37 @@ pf_write_kernel(const float* __restrict__ feats, int64_t ldf, const int32_t* __r
   float s = 0.f;
   for (int k = lane; k < d; k += 32) { const float v = src[k]; s = fmaf(v, v, s); }
   s = sqrtf(warp_sum(s));
-  float* o = gal + ((size_t)slot_of_row[i] * budget + p) * d;
-  for (int k = lane; k < d; k += 32) o[k] = __fdiv_rn(src[k], s);
+  const size_t row = (size_t)slot_of_row[i] * budget + p;
+  float* o = gal + row * d;
+  __nv_bfloat16* hi = packed + row * 2 * dp;
+  __nv_bfloat16* lo = hi + dp;
+  for (int k = lane; k < d; k += 32) {
+    const float v = __fdiv_rn(src[k], s);
+    o[k] = v;
+    const __nv_bfloat16 h = __float2bfloat16_rn(v);
+    hi[k] = h;
+    lo[k] = __float2bfloat16_rn(v - __bfloat162float(h));
+  }
+}
+
+// warp per detection: f / ||f|| in fp32 (matching.py:294-296) split into bf16 hi|lo planes (B operand of the frame kernel)
+__global__ void __launch_bounds__(256)
+det_pack_kernel(const float* __restrict__ feats, int64_t ldf, int n, int d, int dp, __nv_bfloat16* __restrict__ packed) {
+  const int i = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (i >= n) return;
+  const float* src = feats + (size_t)i * ldf;
+  float s = 0.f;
+  for (int k = lane; k < d; k += 32) { const float v = src[k]; s = fmaf(v, v, s); }
+  s = sqrtf(warp_sum(s));
+  __nv_bfloat16* hi = packed + (size_t)i * 2 * dp;
+  __nv_bfloat16* lo = hi + dp;
+  for (int k = lane; k < dp; k += 32) {
+    const float v = k < d ? __fdiv_rn(src[k], s) : 0.f;
+    const __nv_bfloat16 h = __float2bfloat16_rn(v);
+    hi[k] = h;
+    lo[k] = __float2bfloat16_rn(v - __bfloat162float(h));
+  }
 }
 
 __global__ void pf_update_kernel(const int32_t* __restrict__ slot_of_row, const int32_t* __restrict__ after, int n,
@@ -161,7 +196,7 @@ struct AssocArgs {
 };
 
 __global__ void __launch_bounds__(AS_THREADS)
-assoc_frame_kernel(AssocArgs a) {
+assoc_frame_simt_kernel(AssocArgs a) {
   __shared__ float Gs[AS_TK][AS_TR + 4];
   __shared__ float Fs[AS_TK][AS_TD + 4];
   __shared__ float red[16][AS_TD + 1];
@@ -273,6 +308,223 @@ assoc_frame_kernel(AssocArgs a) {
   }
 }
 
+
+// ------------------------------------------------------------------------------------ fused frame kernel, tcgen05
+// Persistent, one CTA per SM, work item = (track, 256-detection tile).  The track's ring rows (<= 128 per row tile,
+// rows >= count masked) are the A operand, the frame's normalised detections the B operand, both as bf16 hi|lo planes
+// (three UMMAs per k-step: lo.hi + hi.lo + hi.hi, fp32 accumulation in TMEM).  Warp 0 = TMA producer, warp 1 = MMA
+// issuer, warps 2-5 = epilogue: TMEM -> registers (thread = gallery row), masked column maximum by a transposing
+// butterfly (31 shuffles per 32 x 32 block), then -- thread = detection -- 1 - max, Mahalanobis gate + blend + clamp and
+// the IoU / DIoU row in fp64, exactly as the SIMT kernel above does.
+constexpr int AT_BM = 128, AT_BN = 256, AT_BK = 64, AT_STAGES = 2;
+constexpr int AT_PLANE = AT_BM * AT_BK * 2;                             // 16 KB: one bf16 plane of an A stage
+constexpr int AT_STAGE_BYTES = 2 * AT_PLANE + 2 * AT_BN * AT_BK * 2;     // 96 KB (B planes sized for 256 detections)
+constexpr int AT_THREADS = 192;
+constexpr size_t AT_SMEM = 1024 + (size_t)AT_STAGES * AT_STAGE_BYTES + 2 * 4 * AT_BN * sizeof(float) + 2 * 32 * sizeof(double) + 128;
+
+// v[j] = value of column j in this lane's row  ->  returns max over the 32 lanes (rows) of column `lane`
+__device__ __forceinline__ float colmax_transpose(float (&v)[32], int lane) {
+#pragma unroll
+  for (int off = 16; off >= 1; off >>= 1) {
+    const bool up = (lane & off) != 0;
+#pragma unroll
+    for (int i = 0; i < off; ++i) {
+      const float send = up ? v[i] : v[i + off];
+      const float keep = up ? v[i + off] : v[i];
+      v[i] = fmaxf(keep, __shfl_xor_sync(0xffffffffu, send, off));
+    }
+  }
+  return v[0];
+}
+
+__global__ void __launch_bounds__(AT_THREADS, 1)
+assoc_frame_kernel(const __grid_constant__ CUtensorMap tmG, const __grid_constant__ CUtensorMap tmF, AssocArgs a, int dp,
+                   int n_dtiles, int bn_box) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  float* part = reinterpret_cast<float*>(smem + (size_t)AT_STAGES * AT_STAGE_BYTES);  // [2][4][AT_BN] per-quadrant column maxima
+  double* trk = reinterpret_cast<double*>(part + 2 * 4 * AT_BN);                       // [2][32] x4 | SI | tlwh box
+  uint64_t* bars = reinterpret_cast<uint64_t*>(trk + 2 * 32);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * AT_STAGES + 4);
+
+  const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);
+  const int lane = threadIdx.x & 31;
+  const uint32_t bar_full = ptx::smem_u32(bars);
+  const uint32_t bar_empty = ptx::smem_u32(bars + AT_STAGES);
+  const uint32_t bar_tfull = ptx::smem_u32(bars + 2 * AT_STAGES);
+  const uint32_t bar_tempty = ptx::smem_u32(bars + 2 * AT_STAGES + 2);
+  const uint32_t smem_base = ptx::smem_u32(smem);
+  const int num_kb = dp / AT_BK;
+  const uint32_t b_plane = (uint32_t)bn_box * AT_BK * 2;
+  const uint32_t stage_tx = 2 * AT_PLANE + 2 * b_plane;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < AT_STAGES; ++s) {
+      ptx::mbar_init(bar_full + 8 * s, 1);
+      ptx::mbar_init(bar_empty + 8 * s, 1);
+    }
+    for (int s = 0; s < 2; ++s) {
+      ptx::mbar_init(bar_tfull + 8 * s, 1);
+      ptx::mbar_init(bar_tempty + 8 * s, 4);
+    }
+    ptx::fence_barrier_init();
+    ptx::prefetch_tensormap(&tmG);
+    ptx::prefetch_tensormap(&tmF);
+  }
+  if (warp == 1) {
+    ptx::tmem_alloc(ptx::smem_u32(tmem_slot), 512);
+    ptx::tmem_relinquish();
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  const int total = a.T * n_dtiles;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int w = blockIdx.x; w < total; w += gridDim.x) {
+        const int t = w / n_dtiles, dt = w - t * n_dtiles;
+        const int slot = a.trk_slot[t];
+        const int cnt = slot >= 0 ? a.gcount[slot] : 0;
+        const int rts = (cnt + AT_BM - 1) / AT_BM;
+        for (int rt = 0; rt < rts; ++rt) {
+          const int arow = slot * a.budget + rt * AT_BM;
+          for (int kb = 0; kb < num_kb; ++kb) {
+            ptx::mbar_wait(bar_empty + 8 * stage, phase ^ 1);
+            const uint32_t full = bar_full + 8 * stage;
+            const uint32_t sb = smem_base + stage * AT_STAGE_BYTES;
+            ptx::mbar_arrive_expect_tx(full, stage_tx);
+            ptx::tma_load_2d(sb, &tmG, full, kb * AT_BK, arow);
+            ptx::tma_load_2d(sb + AT_PLANE, &tmG, full, dp + kb * AT_BK, arow);
+            ptx::tma_load_2d(sb + 2 * AT_PLANE, &tmF, full, kb * AT_BK, dt * AT_BN);
+            ptx::tma_load_2d(sb + 2 * AT_PLANE + b_plane, &tmF, full, dp + kb * AT_BK, dt * AT_BN);
+            if (++stage == AT_STAGES) { stage = 0; phase ^= 1; }
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      int stage = 0, as = 0;
+      uint32_t phase = 0, aphase = 0;
+      for (int w = blockIdx.x; w < total; w += gridDim.x) {
+        const int t = w / n_dtiles, dt = w - t * n_dtiles;
+        const int slot = a.trk_slot[t];
+        const int cnt = slot >= 0 ? a.gcount[slot] : 0;
+        const int rts = (cnt + AT_BM - 1) / AT_BM;
+        const int n_tile = min(bn_box, (a.M - dt * AT_BN + 15) & ~15);
+        const uint32_t idesc = ptx::umma_idesc_bf16(AT_BM, n_tile);
+        for (int rt = 0; rt < rts; ++rt) {
+          ptx::mbar_wait(bar_tempty + 8 * as, aphase ^ 1);
+          ptx::tc_fence_after();
+          const uint32_t d_tmem = tmem_base + as * AT_BN;
+          for (int kb = 0; kb < num_kb; ++kb) {
+            ptx::mbar_wait(bar_full + 8 * stage, phase);
+            ptx::tc_fence_after();
+            const uint32_t sb = smem_base + stage * AT_STAGE_BYTES;
+#pragma unroll
+            for (int kk = 0; kk < AT_BK / 16; ++kk) {
+              const uint64_t ahi = ptx::umma_desc_k_sw128(sb + kk * 32);
+              const uint64_t alo = ptx::umma_desc_k_sw128(sb + AT_PLANE + kk * 32);
+              const uint64_t bhi = ptx::umma_desc_k_sw128(sb + 2 * AT_PLANE + kk * 32);
+              const uint64_t blo = ptx::umma_desc_k_sw128(sb + 2 * AT_PLANE + b_plane + kk * 32);
+              ptx::mma_f16_ss(d_tmem, alo, bhi, idesc, (kb | kk) != 0);
+              ptx::mma_f16_ss(d_tmem, ahi, blo, idesc, 1);
+              ptx::mma_f16_ss(d_tmem, ahi, bhi, idesc, 1);
+            }
+            ptx::mma_commit(bar_empty + 8 * stage);
+            if (++stage == AT_STAGES) { stage = 0; phase ^= 1; }
+          }
+          ptx::mma_commit(bar_tfull + 8 * as);
+          as ^= 1;
+          if (as == 0) aphase ^= 1;
+        }
+      }
+    }
+  } else {
+    const int q = warp & 3;               // TMEM lane quadrant of this warp
+    const int e = threadIdx.x - 64;       // 0..127: finalize index (detection column within the tile)
+    int as = 0, it = 0;
+    uint32_t aphase = 0;
+    for (int w = blockIdx.x; w < total; w += gridDim.x, ++it) {
+      const int t = w / n_dtiles, dt = w - t * n_dtiles;
+      const int slot = a.trk_slot[t];
+      const int cnt = slot >= 0 ? a.gcount[slot] : 0;
+      const int rts = (cnt + AT_BM - 1) / AT_BM;
+      const int n_cols = min(AT_BN, a.M - dt * AT_BN);
+      float* mypart = part + ((it & 1) * 4 + q) * AT_BN;
+      double* mytrk = trk + (it & 1) * 32;
+      if (e < 4) mytrk[e] = a.trk_mean[(size_t)t * 8 + e];
+      else if (e < 20) mytrk[e] = a.trk_SI ? a.trk_SI[(size_t)t * 16 + (e - 4)] : 0.0;
+      else if (e == 20) mean_to_tlwh(a.trk_mean + (size_t)t * 8, mytrk + 20);
+      for (int rt = 0; rt < rts; ++rt) {
+        ptx::mbar_wait(bar_tfull + 8 * as, aphase);
+        ptx::tc_fence_after();
+        const bool valid = rt * AT_BM + q * 32 + lane < cnt;
+        const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + as * AT_BN;
+#pragma unroll 1
+        for (int c = 0; c * 32 < n_cols; ++c) {
+          uint32_t r[32];
+          ptx::tmem_ld_32x32b_x32(taddr + c * 32, r);
+          ptx::tmem_ld_wait();
+          float v[32];
+#pragma unroll
+          for (int j = 0; j < 32; ++j) v[j] = valid ? __uint_as_float(r[j]) : -INFINITY;
+          const float mx = colmax_transpose(v, lane);
+          float* dst = mypart + c * 32 + lane;
+          *dst = rt == 0 ? mx : fmaxf(*dst, mx);
+        }
+        ptx::tc_fence_before();
+        __syncwarp();
+        if (lane == 0) ptx::mbar_arrive(bar_tempty + 8 * as);
+        as ^= 1;
+        if (as == 0) aphase ^= 1;
+      }
+      asm volatile("bar.sync 1, 128;" ::: "memory");  // the four epilogue warps: partial maxima + track state visible
+      const bool tsu_far = a.trk_tsu[t] > 1;
+      const float* p0 = part + (it & 1) * 4 * AT_BN;
+      for (int col = e; col < n_cols; col += 128) {
+        const int m = dt * AT_BN + col;
+        const size_t o = (size_t)t * a.M + m;
+        if (a.out_app) {
+          double cost = INFTY_COST, raw = INFTY_COST;
+          if (cnt > 0) {
+            const float mx = fmaxf(fmaxf(p0[col], p0[AT_BN + col]), fmaxf(p0[2 * AT_BN + col], p0[3 * AT_BN + col]));
+            raw = (double)__fsub_rn(1.0f, mx);
+            cost = raw;
+          }
+          if (a.out_raw) a.out_raw[o] = raw;
+          if (!(a.flags & REIDB200_ASSOC_NO_GATE)) {
+            double z[4];
+            tlwh_to_xyah_f32(a.det_tlwh + (size_t)m * 4, z);
+            const double gd = maha(z, mytrk, mytrk + 4);
+            if (gd > CHI2INV95_4) cost = INFTY_COST;
+            cost = a.mc_lambda * cost + (1 - a.mc_lambda) * gd;
+          }
+          if ((a.flags & REIDB200_ASSOC_CLAMP_APP) && cost > a.max_dist) cost = a.max_dist + 1e-5;
+          a.out_app[o] = cost;
+        }
+        if (a.out_iou) {
+          double c = INFTY_COST;
+          if (!tsu_far) c = 1.0 - iou_one<float>(mytrk + 20, a.det_tlwh + (size_t)m * 4, a.iou_mode);
+          if ((a.flags & REIDB200_ASSOC_CLAMP_IOU) && c > a.max_iou_dist) c = a.max_iou_dist + 1e-5;
+          a.out_iou[o] = c;
+        }
+      }
+    }
+  }
+
+  ptx::tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    ptx::tc_fence_after();
+    ptx::tmem_dealloc(tmem_base, 512);
+  }
+}
+
 // ------------------------------------------------------------------------------------ stand-alone pieces
 template <typename CT>
 __global__ void iou_matrix_kernel(const double* __restrict__ bbox, int T, const CT* __restrict__ cand, int M, int mode,
@@ -308,17 +560,20 @@ __global__ void one_minus_kernel(float* __restrict__ x, size_t n) {
 
 }  // namespace reidb200
 
-#include "gemm.cuh"
-
 using namespace reidb200;
 
 extern "C" int reidb200_gallery_create(int slots, int budget, int d, reidb200_gallery** out) {
   RB_REQUIRE(out && slots > 0 && budget > 0 && d > 0, "gallery_create: bad argument");
   reidb200_gallery* g = new reidb200_gallery();
-  g->slots = slots; g->budget = budget; g->d = d;
-  g->feats = nullptr; g->count = nullptr; g->head = nullptr; g->scratch = nullptr;
+  g->slots = slots; g->budget = budget; g->d = d; g->dp = padded_dim(d);
+  g->feats = nullptr; g->packed = nullptr; g->count = nullptr; g->head = nullptr; g->scratch = nullptr;
+  g->det_packed = nullptr; g->det_cap = 1024;
   g->scratch_rows = slots > 1024 ? slots : 1024;
+  const size_t packed_sz = (size_t)slots * budget * 2 * g->dp * sizeof(__nv_bfloat16);
   cudaError_t e = cudaMalloc(&g->feats, (size_t)slots * budget * d * sizeof(float));
+  if (e == cudaSuccess) e = cudaMalloc(&g->packed, packed_sz);
+  if (e == cudaSuccess) e = cudaMemset(g->packed, 0, packed_sz);
+  if (e == cudaSuccess) e = cudaMalloc(&g->det_packed, (size_t)g->det_cap * 2 * g->dp * sizeof(__nv_bfloat16));
   if (e == cudaSuccess) e = cudaMalloc(&g->count, (size_t)slots * sizeof(int32_t));
   if (e == cudaSuccess) e = cudaMalloc(&g->head, (size_t)slots * sizeof(int32_t));
   if (e == cudaSuccess) e = cudaMalloc(&g->scratch, (size_t)2 * g->scratch_rows * sizeof(int32_t));
@@ -328,13 +583,15 @@ extern "C" int reidb200_gallery_create(int slots, int budget, int d, reidb200_ga
     reidb200_gallery_destroy(g);
     return cuda_fail(e, "gallery_create", __FILE__, __LINE__);
   }
+  int rc = make_operand_map(&g->tm_gallery, g->packed, slots * budget, g->dp, AT_BM);
+  if (rc) { reidb200_gallery_destroy(g); return rc; }
   *out = g;
   return REIDB200_OK;
 }
 
 extern "C" int reidb200_gallery_destroy(reidb200_gallery* g) {
   if (!g) return REIDB200_OK;
-  cudaFree(g->feats); cudaFree(g->count); cudaFree(g->head); cudaFree(g->scratch);
+  cudaFree(g->feats); cudaFree(g->packed); cudaFree(g->det_packed); cudaFree(g->count); cudaFree(g->head); cudaFree(g->scratch);
   delete g;
   return REIDB200_OK;
 }
@@ -351,7 +608,7 @@ extern "C" int reidb200_gallery_partial_fit(reidb200_gallery* g, const float* fe
     { ProfScope _ps("pf_assign_kernel", st); pf_assign_kernel<<<ceil_div(nb, 128), 128, 0, st>>>(slot_of_row + b0, nb, g->budget, g->head, dst, after); }
     RB_LAUNCH_CHECK("pf_assign_kernel");
     { ProfScope _ps("pf_write_kernel", st); pf_write_kernel<<<ceil_div(nb, 8), 256, 0, st>>>(feats + (size_t)b0 * ldf, ldf, slot_of_row + b0, dst, nb, g->budget,
-                                                    g->d, g->feats); }
+                                                    g->d, g->dp, g->feats, g->packed); }
     RB_LAUNCH_CHECK("pf_write_kernel");
     { ProfScope _ps("pf_update_kernel", st); pf_update_kernel<<<ceil_div(nb, 128), 128, 0, st>>>(slot_of_row + b0, after, nb, g->budget, g->head, g->count); }
     RB_LAUNCH_CHECK("pf_update_kernel");
@@ -400,7 +657,34 @@ extern "C" int reidb200_assoc_frame(reidb200_gallery* g, const float* det_feat, 
   a.trk_slot = trk_slot; a.trk_mean = trk_mean; a.trk_SI = trk_SI; a.trk_tsu = trk_tsu; a.T = T;
   a.mc_lambda = mc_lambda; a.max_dist = max_dist; a.max_iou_dist = max_iou_dist; a.iou_mode = iou_mode; a.flags = flags;
   a.out_app = out_app; a.out_raw = out_app ? out_raw : nullptr; a.out_iou = out_iou;
-  { ProfScope _ps("assoc_frame_kernel", (cudaStream_t)stream); assoc_frame_kernel<<<T, AS_THREADS, 0, (cudaStream_t)stream>>>(a); }
+  cudaStream_t st = (cudaStream_t)stream;
+  if (!out_app || (flags & REIDB200_ASSOC_SIMT)) {  // IoU-only frames and the fp32 cross-check of the tests
+    { ProfScope _ps("assoc_frame_simt_kernel", st); assoc_frame_simt_kernel<<<T, AS_THREADS, 0, st>>>(a); }
+    RB_LAUNCH_CHECK("assoc_frame_simt_kernel");
+    return REIDB200_OK;
+  }
+  if (M > g->det_cap) {  // grows outside the steady state only (synchronises: not capturable in a CUDA graph)
+    RB_CUDA(cudaStreamSynchronize(st));
+    cudaFree(g->det_packed);
+    g->det_packed = nullptr;
+    g->det_cap = M + M / 2;
+    RB_CUDA(cudaMalloc(&g->det_packed, (size_t)g->det_cap * 2 * g->dp * sizeof(__nv_bfloat16)));
+  }
+  { ProfScope _ps("det_pack_kernel", st); det_pack_kernel<<<ceil_div(M, 8), 256, 0, st>>>(det_feat, ldf, M, g->d, g->dp, g->det_packed); }
+  RB_LAUNCH_CHECK("det_pack_kernel");
+  const int bn_box = M >= AT_BN ? AT_BN : ((M + 15) & ~15);
+  CUtensorMap tmF;
+  int rc = make_operand_map(&tmF, g->det_packed, M, g->dp, bn_box);
+  if (rc) return rc;
+  static bool attr_done = false;
+  if (!attr_done) {
+    RB_CUDA(cudaFuncSetAttribute(assoc_frame_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)AT_SMEM));
+    attr_done = true;
+  }
+  const int n_dtiles = ceil_div(M, AT_BN);
+  const long long total = (long long)T * n_dtiles;
+  const int grid = (int)(total < num_sms() ? total : num_sms());
+  { ProfScope _ps("assoc_frame_kernel", st); assoc_frame_kernel<<<grid, AT_THREADS, AT_SMEM, st>>>(g->tm_gallery, tmF, a, g->dp, n_dtiles, bn_box); }
   RB_LAUNCH_CHECK("assoc_frame_kernel");
   return REIDB200_OK;
 }

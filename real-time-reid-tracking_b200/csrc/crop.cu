@@ -4,6 +4,8 @@
 //   PIL_ANTIALIAS: boxmot/appearance/reid_multibackend.py:58-66,210-220 (Pillow ImagingResample
 //                  8bpc two-pass fixed point, then /255 and ImageNet normalise)
 // HBM-bound: 3*out_h*out_w*4 B written + ~3*h*w B read per crop.
+#include <math.h>
+
 #include "common.cuh"
 
 namespace reidb200 {
@@ -14,11 +16,34 @@ namespace reidb200 {
 // then vertical lerp, no FMA contraction, so results are bit-identical to the numpy restatement
 // (which is itself within 1 ulp of cv2).
 constexpr int CV_ROWS = 8;
+constexpr int CV_STAGE_FLOATS = 8 * 1024;   // 32 KB of staged source rows per CTA
 
+// u8 / 255.0f correctly rounded without the IEEE division sequence: one Newton correction with an exact fma residual
+// (equal to __fdiv_rn((float)u, 255.0f) for all 256 inputs; checked exhaustively by tests/test_gpu_crop.py).
+__device__ __forceinline__ float u8_over_255(uint32_t u) {
+  const float c = 1.0f / 255.0f;
+  const float f = (float)u;
+  const float q = __fmul_rn(f, c);
+  const float r = __fmaf_rn(-q, 255.0f, f);
+  return __fmaf_rn(r, c, q);
+}
+
+struct CvNorm { float m[3], s[3], inv[3]; int pow2[3]; };
+
+__device__ __forceinline__ float cv_norm(const CvNorm& n, int c, float v) {
+  const float d = __fsub_rn(v, n.m[c]);
+  return n.pow2[c] ? __fmul_rn(d, n.inv[c]) : __fdiv_rn(d, n.s[c]);  // x / 2^k == x * 2^-k exactly
+}
+
+// CTA = (crop, CV_ROWS output rows), thread = output column.  The source rows the tile touches are staged ONCE into
+// shared memory as float(u8)/255 (aligned 32-bit global loads), so every source byte is converted once per tile instead
+// of once per tap; tiles whose source footprint exceeds the staging buffer read their taps straight from global memory.
 __global__ void __launch_bounds__(128)
 crop_cv_linear_kernel(const uint8_t* __restrict__ src, const int64_t* __restrict__ crop_off,
-                      const int32_t* __restrict__ crop_geom, int out_h, int out_w, float m0, float m1,
-                      float m2, float s0, float s1, float s2, float* __restrict__ out) {
+                      const int32_t* __restrict__ crop_geom, int out_h, int out_w, CvNorm nrm, float* __restrict__ out) {
+  extern __shared__ float staged[];
+  __shared__ int s_sy0[CV_ROWS], s_sy1[CV_ROWS];
+  __shared__ float s_b0[CV_ROWS], s_b1[CV_ROWS];
   const int crop = blockIdx.y;
   const int y_base = blockIdx.x * CV_ROWS;
   const int h = crop_geom[crop * 3 + 0], w = crop_geom[crop * 3 + 1], stride = crop_geom[crop * 3 + 2];
@@ -26,6 +51,39 @@ crop_cv_linear_kernel(const uint8_t* __restrict__ src, const int64_t* __restrict
   const double scale_x = 1.0 / ((double)out_w / (double)w);
   const double scale_y = 1.0 / ((double)out_h / (double)h);
   float* o = out + (size_t)crop * 3 * out_h * out_w;
+  const int rows_here = min(CV_ROWS, out_h - y_base);
+
+  if (threadIdx.x < CV_ROWS) {
+    const int y = min(y_base + (int)threadIdx.x, out_h - 1);
+    float fy = (float)(((double)y + 0.5) * scale_y - 0.5);
+    const int sy = (int)floorf(fy);
+    fy = __fsub_rn(fy, (float)sy);
+    s_sy0[threadIdx.x] = min(max(sy, 0), h - 1);
+    s_sy1[threadIdx.x] = min(max(sy + 1, 0), h - 1);
+    s_b1[threadIdx.x] = fy;
+    s_b0[threadIdx.x] = __fsub_rn(1.0f, fy);
+  }
+  __syncthreads();
+  const int first = s_sy0[0], last = s_sy1[rows_here - 1];
+  const int nrows = last - first + 1, w3 = w * 3;
+  const bool use_stage = (long long)nrows * w3 <= CV_STAGE_FLOATS;
+  if (use_stage) {
+    for (int r = 0; r < nrows; ++r) {
+      const uint8_t* row = base + (size_t)(first + r) * stride;
+      const int mis = (int)(reinterpret_cast<uintptr_t>(row) & 3);
+      const uint32_t* row4 = reinterpret_cast<const uint32_t*>(row - mis);
+      float* dst = staged + r * w3 - mis;
+      const int nwords = (mis + w3 + 3) >> 2;
+      for (int i = threadIdx.x; i < nwords; i += blockDim.x) {
+        const uint32_t v = __ldg(row4 + i);
+        const int k = i * 4;
+#pragma unroll
+        for (int b = 0; b < 4; ++b)
+          if (k + b >= mis && k + b < mis + w3) dst[k + b] = u8_over_255((v >> (8 * b)) & 0xffu);
+      }
+    }
+    __syncthreads();
+  }
 
   for (int x = threadIdx.x; x < out_w; x += blockDim.x) {
     float fx = (float)(((double)x + 0.5) * scale_x - 0.5);
@@ -38,28 +96,34 @@ crop_cv_linear_kernel(const uint8_t* __restrict__ src, const int64_t* __restrict
     sx1 = min(sx0 + 1, w - 1);
     const float a1 = fx, a0 = __fsub_rn(1.0f, fx);
 #pragma unroll 2
-    for (int r = 0; r < CV_ROWS; ++r) {
+    for (int r = 0; r < rows_here; ++r) {
       const int y = y_base + r;
-      if (y >= out_h) break;
-      float fy = (float)(((double)y + 0.5) * scale_y - 0.5);
-      int sy = (int)floorf(fy);
-      fy = __fsub_rn(fy, (float)sy);
-      const int sy0 = min(max(sy, 0), h - 1), sy1 = min(max(sy + 1, 0), h - 1);
-      const float b1 = fy, b0 = __fsub_rn(1.0f, fy);
-      const uint8_t* r0 = base + (size_t)sy0 * stride;
-      const uint8_t* r1 = base + (size_t)sy1 * stride;
+      const int sy0 = s_sy0[r], sy1 = s_sy1[r];
+      const float b0 = s_b0[r], b1 = s_b1[r];
+      float p[3][4];
+      if (use_stage) {
+        const float* r0 = staged + (sy0 - first) * w3;
+        const float* r1 = staged + (sy1 - first) * w3;
+#pragma unroll
+        for (int c = 0; c < 3; ++c) {
+          p[c][0] = r0[sx0 * 3 + c]; p[c][1] = r0[sx1 * 3 + c];
+          p[c][2] = r1[sx0 * 3 + c]; p[c][3] = r1[sx1 * 3 + c];
+        }
+      } else {
+        const uint8_t* r0 = base + (size_t)sy0 * stride;
+        const uint8_t* r1 = base + (size_t)sy1 * stride;
+#pragma unroll
+        for (int c = 0; c < 3; ++c) {
+          p[c][0] = u8_over_255(__ldg(r0 + sx0 * 3 + c)); p[c][1] = u8_over_255(__ldg(r0 + sx1 * 3 + c));
+          p[c][2] = u8_over_255(__ldg(r1 + sx0 * 3 + c)); p[c][3] = u8_over_255(__ldg(r1 + sx1 * 3 + c));
+        }
+      }
 #pragma unroll
       for (int c = 0; c < 3; ++c) {
-        const float p00 = __fdiv_rn((float)__ldg(r0 + sx0 * 3 + c), 255.0f);
-        const float p01 = __fdiv_rn((float)__ldg(r0 + sx1 * 3 + c), 255.0f);
-        const float p10 = __fdiv_rn((float)__ldg(r1 + sx0 * 3 + c), 255.0f);
-        const float p11 = __fdiv_rn((float)__ldg(r1 + sx1 * 3 + c), 255.0f);
-        const float h0 = __fadd_rn(__fmul_rn(p00, a0), __fmul_rn(p01, a1));
-        const float h1 = __fadd_rn(__fmul_rn(p10, a0), __fmul_rn(p11, a1));
+        const float h0 = __fadd_rn(__fmul_rn(p[c][0], a0), __fmul_rn(p[c][1], a1));
+        const float h1 = __fadd_rn(__fmul_rn(p[c][2], a0), __fmul_rn(p[c][3], a1));
         const float v = __fadd_rn(__fmul_rn(h0, b0), __fmul_rn(h1, b1));
-        const float mean = c == 0 ? m0 : (c == 1 ? m1 : m2);
-        const float sd = c == 0 ? s0 : (c == 1 ? s1 : s2);
-        __stcs(o + ((size_t)c * out_h + y) * out_w + x, __fdiv_rn(__fsub_rn(v, mean), sd));
+        __stcs(o + ((size_t)c * out_h + y) * out_w + x, cv_norm(nrm, c, v));
       }
     }
   }
@@ -240,8 +304,20 @@ extern "C" int reidb200_crop_resize_norm_ws(const uint8_t* src, const int64_t* c
   cudaStream_t st = (cudaStream_t)stream;
   if (mode == REIDB200_RESIZE_CV_LINEAR) {
     dim3 grid(ceil_div(out_h, CV_ROWS), M);
-    { ProfScope _ps("crop_cv_linear_kernel", st); crop_cv_linear_kernel<<<grid, 128, 0, st>>>(src, crop_off, crop_geom, out_h, out_w, mean_host[0], mean_host[1],
-                                                mean_host[2], std_host[0], std_host[1], std_host[2], out); }
+    CvNorm nrm;
+    for (int c = 0; c < 3; ++c) {
+      int ex = 0;
+      nrm.m[c] = mean_host[c];
+      nrm.s[c] = std_host[c];
+      nrm.pow2[c] = (frexpf(std_host[c], &ex) == 0.5f && ex > -100 && ex < 100) ? 1 : 0;  // std = 2^k: exact reciprocal
+      nrm.inv[c] = nrm.pow2[c] ? 1.0f / std_host[c] : 0.f;
+    }
+    static bool attr_done = false;
+    if (!attr_done) {
+      RB_CUDA(cudaFuncSetAttribute(crop_cv_linear_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, CV_STAGE_FLOATS * 4));
+      attr_done = true;
+    }
+    { ProfScope _ps("crop_cv_linear_kernel", st); crop_cv_linear_kernel<<<grid, 128, CV_STAGE_FLOATS * 4, st>>>(src, crop_off, crop_geom, out_h, out_w, nrm, out); }
     RB_LAUNCH_CHECK("crop_cv_linear_kernel");
     return REIDB200_OK;
   }

@@ -10,7 +10,6 @@
 // owner), warps 2-5 = epilogue (TMEM -> registers -> smem transpose -> coalesced global stores).
 // CTA tile 128 x 256, k-block 64 (one SWIZZLE_128B atom), 2 smem stages of 96 KB
 // (Ahi, Alo, Bhi, Blo), 2 TMEM accumulator stages of 256 columns.
-#include <cuda.h>
 #include <stdlib.h>
 
 #include "gemm.cuh"
@@ -462,7 +461,7 @@ static EncodeTiledFn get_encode_fn() {
 }
 
 // packed operand [rows, 2*dp] bf16, box = {64, box_rows}, 128-byte swizzle, OOB rows/cols read as zero
-static int make_operand_map(CUtensorMap* tm, const void* packed, int rows, int dp, int box_rows) {
+int make_operand_map(CUtensorMap* tm, const void* packed, int rows, int dp, int box_rows) {
   EncodeTiledFn enc = get_encode_fn();
   if (!enc) {
     set_error("cuTensorMapEncodeTiled not available from the driver");

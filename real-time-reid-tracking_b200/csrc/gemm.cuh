@@ -1,6 +1,8 @@
 // Internal interface of the split-bf16 tensor-core GEMM (gemm.cu), shared by distmat / knn /
 // jaccard / association.
 #pragma once
+#include <cuda.h>
+
 #include "common.cuh"
 
 namespace reidb200 {
@@ -19,6 +21,9 @@ int pack_rows_launch(const float* x, int rows, int64_t ldx, int d, void* packed,
 int gemm_split_launch(const void* packedA, const float* xx, int m, const void* packedB, const float* yy, int n, int d,
                       int kind, float* out, int64_t ldo, cudaStream_t st, float* chunk_red = nullptr,
                       int64_t ld_chunk_red = 0, int chunk_red_max = 0);
+
+// TMA descriptor of a packed operand [rows, 2*dp] bf16: box = {64 k-elements, box_rows}, SWIZZLE_128B, OOB reads as zero.
+int make_operand_map(CUtensorMap* tm, const void* packed, int rows, int dp, int box_rows);
 
 // row-wise exact top-k (topk.cu); out_i is i64 when idx64 else i32; ids = cand_i[col] or col + index_base
 // chunk_red (optional): the per-32-column reductions written by gemm_split_launch for this matrix.

@@ -292,8 +292,8 @@ class Gallery:
 
 def assoc_frame(gallery, det_feat, det_tlwh, trk_slot, trk_mean, trk_SI, trk_tsu, mc_lambda=0.995, max_dist=0.2,
                 max_iou_dist=0.7, iou_mode="iou", clamp_app=False, clamp_iou=False, gate=True, want_raw=False,
-                want_app=True, want_iou=True):
-    """One fused launch: (app f64[T,M] or None, raw or None, iou f64[T,M] or None), all on device."""
+                want_app=True, want_iou=True, simt=False):
+    """One fused launch (simt=True: the fp32 SIMT cross-check kernel instead of the tcgen05 one): (app f64[T,M] or None, raw or None, iou f64[T,M] or None), all on device."""
     dev = gallery.device if gallery is not None else L.require_device()
     det_tlwh = _f32(det_tlwh, dev)
     M = det_tlwh.shape[0]
@@ -313,7 +313,7 @@ def assoc_frame(gallery, det_feat, det_tlwh, trk_slot, trk_mean, trk_SI, trk_tsu
         iou = torch.empty((T, M), dtype=torch.float64, device=dev)
     if T == 0 or M == 0:
         return app, raw, iou
-    flags = (L.ASSOC_CLAMP_APP if clamp_app else 0) | (L.ASSOC_CLAMP_IOU if clamp_iou else 0) | (0 if gate else L.ASSOC_NO_GATE)
+    flags = (L.ASSOC_CLAMP_APP if clamp_app else 0) | (L.ASSOC_CLAMP_IOU if clamp_iou else 0) | (0 if gate else L.ASSOC_NO_GATE) | (L.ASSOC_SIMT if simt else 0)
     with torch.cuda.device(dev):
         L.check(L.load().reidb200_assoc_frame(gallery._h if gallery is not None else None, L.ptr(det_feat_t),
                                              det_feat_t.stride(0) if det_feat_t is not None else 0, det_tlwh.data_ptr(), M,

@@ -119,6 +119,36 @@ def test_mot_shaped_frame_vs_oracle(rb, M, T):
     assert keep1 == keep2 and len(keep1) > 0
 
 
+@pytest.mark.parametrize("M,T,budget,D", [(5, 3, 4, 24), (300, 40, 100, 96), (70, 9, 150, 512), (16, 130, 100, 64)])
+def test_tensor_core_kernel_vs_simt_vs_oracle(rb, M, T, budget, D):
+    """tcgen05 frame kernel against the fp32 SIMT kernel and the oracle: > 256 detections (detection tiles), budget > 128
+    (row tiles), feature dimension not a multiple of 64 (zero padded k-blocks), empty and unknown slots."""
+    from reidb200 import ops, synth
+
+    fr = synth.mot_frame(M=M, T=T, budget=budget, D=D, seed=M + T)
+    samples = fr["samples"]
+    gal = ops.Gallery(T + 2, budget, D)
+    keep = [t for t in range(T) if t % 7 != 3]  # some tracks never fitted: empty slot -> 1e5 rows
+    gal.partial_fit(np.concatenate([samples[t] for t in keep], 0), np.repeat(keep, [len(samples[t]) for t in keep]))
+    slots = np.arange(T, dtype=np.int32)
+    if T > 2:
+        slots[1] = -1  # track without a gallery slot
+    args = (gal, fr["det_feat"], fr["det_tlwh"], slots, fr["trk_mean"], fr["trk_SI"].reshape(T, 16), fr["trk_tsu"], 0.995, 0.2, 0.7)
+    app, raw, iou = [x.cpu().numpy() for x in ops.assoc_frame(*args, want_raw=True)]
+    app_s, raw_s, iou_s = [x.cpu().numpy() for x in ops.assoc_frame(*args, want_raw=True, simt=True)]
+    assert np.array_equal(iou, iou_s)
+    np.testing.assert_allclose(raw, raw_s, rtol=1e-4, atol=1e-5)  # north_star: distances within 1e-4 relative
+    np.testing.assert_allclose(app, app_s, rtol=1e-4, atol=1e-5)
+    assert np.array_equal(app > 1e4, app_s > 1e4)
+    empty = [t for t in range(T) if t not in keep or slots[t] < 0]
+    assert (raw[empty] == 1e5).all()
+    live = [t for t in range(T) if t in keep and slots[t] >= 0]
+    oraw = O.nn_distance_matrix([samples[t] for t in live], fr["det_feat"])
+    np.testing.assert_allclose(raw[live], oraw, rtol=1e-4, atol=1e-5)
+    oiou = O.iou_cost([O.track_to_tlwh(m[:4]) for m in fr["trk_mean"]], fr["trk_tsu"], fr["det_tlwh"])
+    assert np.array_equal(iou, oiou)
+
+
 def test_empty_inputs(rb):
     from reidb200 import iou_matching as IM, linear_assignment as LA, matching as MT, tracker as TR
 

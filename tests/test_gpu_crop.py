@@ -61,6 +61,27 @@ def test_mot_shaped_frame(rb):
     assert np.array_equal(got[sel], want)
 
 
+def test_large_small_and_odd_crops(rb):
+    """Tile footprints beyond the staging buffer (direct-tap path), 1-pixel crops, odd offsets (unaligned 32-bit staging
+    loads at every byte phase), non-power-of-two std (IEEE division path), every byte value."""
+    from reidb200 import ops, preprocess as P
+
+    rng = np.random.default_rng(11)
+    img = rng.integers(0, 256, (700, 901, 3), dtype=np.uint8)  # odd row stride: rows start at every alignment
+    img[0, :256, 0] = np.arange(256)
+    xyxy = np.array([[0, 0, 901, 700], [3, 5, 880, 650], [1, 0, 257, 1], [10, 10, 11, 400], [7, 9, 8, 10], [2, 3, 131, 259],
+                     [5, 1, 69, 129], [0, 0, 256, 2], [333, 100, 600, 699]], np.int32)
+    crops = [img[y1:y2, x1:x2] for x1, y1, x2, y2 in xyxy]
+    got = P.preprocess_frame(img, xyxy).cpu().numpy()
+    assert np.array_equal(got, O.preprocess_deepsort(crops))
+    mean, std = (0.485, 0.456, 0.406), (0.229, 0.224, 0.225)
+    off, geom = P._geometry_from_xyxy(xyxy, img.shape[1])
+    dev = torch.device("cuda")
+    got2 = ops.crop_resize_norm(torch.from_numpy(img).to(dev), torch.from_numpy(off).to(dev), torch.from_numpy(geom).to(dev),
+                                mean=mean, std=std).cpu().numpy()
+    assert np.array_equal(got2, O.preprocess_deepsort(crops, mean=mean, std=std))
+
+
 def test_empty_and_bad_crops(rb):
     from reidb200 import preprocess as P
 
