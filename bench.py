@@ -393,7 +393,7 @@ def run_ours(args):
     share = {k: round(v[1] / ms, 4) for k, v in sorted(prof.items(), key=lambda kv: -kv[1][1])}
     gemm_flops = 2.0 * N * N * D_FULL  # algorithmic (fp32-equivalent) flops of one launch: 2*D per pair over N x N
     achieved = gemm_flops / (gemm_ms / max(gemm_n, 1) * 1e-3) / 1e12 if gemm_n else None
-    peak = peaks["bf16_tflops_sustained"] / 3.0  # three bf16 UMMAs per fp32-accurate product
+    peak = peaks["bf16_tflops_sustained"] / 3.0  # three 16-bit UMMAs per fp32-accurate product
     line = {
         "metric": METRIC, "value": value, "unit": "pairs/s", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
         "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
@@ -406,7 +406,7 @@ def run_ours(args):
         "gpu_launches": int(launches),
         "roofline": {"kernel": "gemm_split_tc_kernel", "bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
                      "frac": (achieved / peak) if achieved else None, "traffic": None,
-                     "peak_source": "%s bf16_tflops_sustained / 3 (bf16x3 split)" % peak_kind,
+                     "peak_source": "%s bf16_tflops_sustained / 3 (fp16 hi|lo split: three kind::f16 UMMAs per fp32-accurate product; fp16 and bf16 run at the same rate)" % peak_kind,
                      "tensor_pipe_tflops": achieved * 3 if achieved else None},
         "kernel_share_of_step": share,
         "result": {"rank1": float(cmc_h[0]), "mAP": float(ap_h)},

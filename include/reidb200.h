@@ -73,7 +73,7 @@ int reidb200_resize_pil_u8(const uint8_t* src, const int64_t* crop_off, const in
 size_t reidb200_resize_pil_workspace_bytes(int M, int max_crop_h, int out_w);
 
 /* ------------------------------------------------------------------------------------------
- * (2) distance matrix, tcgen05 / TMA tensor-core GEMM with fp32-accurate (bf16x3 split) operands
+ * (2) distance matrix, tcgen05 / TMA tensor-core GEMM with fp32-accurate (scaled fp16 hi|lo split, 3 UMMAs) operands
  *   EUCLID       reid/losses/utils.py:21-35   euclidean_dist: sqrt(clamp(xx+yy-2xy, 1e-12))
  *   COSINE_HALF  reid/losses/utils.py:12-18   cosine_dist: (1 - xy/(|x||y|))/2
  *   DOT          reid/evaluate.py:58          score = gf . q
@@ -92,12 +92,13 @@ int reidb200_distmat(const float* x, int m, int64_t ldx, const float* y, int n, 
 int reidb200_distmat_simt(const float* x, int m, int64_t ldx, const float* y, int n, int64_t ldy,
                           int d, int kind, float* out, int64_t ldo, void* stream);
 
-/* Operand packing used by distmat/knn: f32[rows,d] -> bf16 hi|lo planes [rows, 2*dp]
- * (dp = d rounded up to 64, zero padded) and the fp32 squared row norms.  Exposed so a gallery can
- * be packed once and searched many times (every search entry point packs on the fly today). */
+/* Operand packing used by distmat/knn: f32[rows,d] -> fp16 hi|lo planes [rows, 2*dp] of the row scaled by a
+ * power of two (dp = d rounded up to 64, zero padded; 22 of fp32's 24 significand bits survive), the fp32
+ * squared norms of the unscaled rows (sqnorm f32[rows], may be NULL) and the inverse scales (iscale f32[rows]).
+ * Exposed so a gallery can be packed once and searched many times (reidb200_knn_packed). */
 size_t reidb200_pack_bytes(int rows, int d);
 int reidb200_pack_rows(const float* x, int rows, int64_t ldx, int d, void* packed, float* sqnorm,
-                       void* stream);
+                       float* iscale, void* stream);
 
 /* ------------------------------------------------------------------------------------------
  * (2b) brute-force k-NN (reid/faiss_utils.py:30-139: faiss bfKnn / GpuIndexFlatL2 / IndexFlatL2 /
@@ -110,12 +111,13 @@ size_t reidb200_knn_workspace_bytes(int nq, int nb, int d, int k);
 int reidb200_knn(const float* xq, int nq, int64_t ldq, const float* xb, int nb, int64_t ldb, int d,
                  int k, int metric, int64_t index_base, float* out_d, void* out_i, int idx64,
                  void* workspace, size_t workspace_bytes, void* stream);
-/* Same search against a gallery packed once with reidb200_pack_rows (packed_b = bf16 hi|lo planes, sqnorm_b f32[nb]):
+/* Same search against a gallery packed once with reidb200_pack_rows (packed_b = fp16 hi|lo planes, sqnorm_b and
+ * iscale_b f32[nb], 16-byte aligned):
  * what a resident index does (GpuIndexFlatL2.add once, search many times, reid/faiss_utils.py:121-139) and what every
  * rank of the gallery-sharded search calls on its own shard.  No fp32 copy of the gallery is needed. */
 size_t reidb200_knn_packed_workspace_bytes(int nq, int nb, int d, int k);
-int reidb200_knn_packed(const float* xq, int nq, int64_t ldq, const void* packed_b, const float* sqnorm_b, int nb,
-                        int d, int k, int metric, int64_t index_base, float* out_d, void* out_i, int idx64,
+int reidb200_knn_packed(const float* xq, int nq, int64_t ldq, const void* packed_b, const float* sqnorm_b,
+                        const float* iscale_b, int nb, int d, int k, int metric, int64_t index_base, float* out_d, void* out_i, int idx64,
                         void* workspace, size_t workspace_bytes, void* stream);
 /* Row-wise top-k of a materialised matrix (ascending unless descending != 0); optional explicit
  * candidate ids (cand_i, i64[rows, cols]) for merging per-shard results, else id = column +

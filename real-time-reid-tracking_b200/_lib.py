@@ -13,7 +13,7 @@ import torch
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libreidb200.so")
-ABI_VERSION = 1
+ABI_VERSION = 2
 
 OK, EINVAL, ECUDA, ELIMIT = 0, -1, -2, -3
 RESIZE_CV_LINEAR, RESIZE_PIL_ANTIALIAS = 0, 1
@@ -40,11 +40,11 @@ SIGNATURES = {
     "reidb200_distmat": (_i, [_vp, _i, _i64, _vp, _i, _i64, _i, _i, _vp, _i64, _vp, _sz, _vp]),
     "reidb200_distmat_simt": (_i, [_vp, _i, _i64, _vp, _i, _i64, _i, _i, _vp, _i64, _vp]),
     "reidb200_pack_bytes": (_sz, [_i, _i]),
-    "reidb200_pack_rows": (_i, [_vp, _i, _i64, _i, _vp, _vp, _vp]),
+    "reidb200_pack_rows": (_i, [_vp, _i, _i64, _i, _vp, _vp, _vp, _vp]),
     "reidb200_knn_workspace_bytes": (_sz, [_i, _i, _i, _i]),
     "reidb200_knn": (_i, [_vp, _i, _i64, _vp, _i, _i64, _i, _i, _i, _i64, _vp, _vp, _i, _vp, _sz, _vp]),
     "reidb200_knn_packed_workspace_bytes": (_sz, [_i, _i, _i, _i]),
-    "reidb200_knn_packed": (_i, [_vp, _i, _i64, _vp, _vp, _i, _i, _i, _i, _i64, _vp, _vp, _i, _vp, _sz, _vp]),
+    "reidb200_knn_packed": (_i, [_vp, _i, _i64, _vp, _vp, _vp, _i, _i, _i, _i, _i64, _vp, _vp, _i, _vp, _sz, _vp]),
     "reidb200_topk_rows": (_i, [_vp, _i, _i, _i64, _vp, _i, _i, _i64, _vp, _vp, _i, _vp]),
     "reidb200_eval_workspace_bytes": (_sz, [_i, _i]),
     "reidb200_eval_cmc_map": (_i, [_vp, _i, _i, _i64, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _sz, _vp]),

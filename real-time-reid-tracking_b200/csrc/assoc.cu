@@ -12,12 +12,12 @@
 struct reidb200_gallery {
   int slots, budget, d, dp;
   float* feats;      // [slots, budget, d] L2-normalised rows (ring per slot)
-  __nv_bfloat16* packed;  // [slots*budget, 2*dp] the same rows as bf16 hi|lo planes: A operand of the tcgen05 frame kernel
+  __half* packed;  // [slots*budget, 2*dp] the same rows as fp16 hi|lo planes: A operand of the tcgen05 frame kernel
   int32_t* count;    // [slots] valid rows
   int32_t* head;     // [slots] next write position
   int32_t* scratch;  // [2*scratch_rows] per-row destination / rows-after
   int scratch_rows;
-  __nv_bfloat16* det_packed;  // [det_cap, 2*dp] L2-normalised detection features of the current frame, hi|lo planes
+  __half* det_packed;  // [det_cap, 2*dp] L2-normalised detection features of the current frame, hi|lo planes
   int det_cap;
   CUtensorMap tm_gallery;     // TMA descriptor of `packed` (box 64 x 128)
 };
@@ -26,6 +26,10 @@ namespace reidb200 {
 
 constexpr double INFTY_COST = 1e5;        // sort/linear_assignment.py:9
 constexpr double CHI2INV95_4 = 9.4877;    // boxmot/utils/matching.py:12-22
+// L2-normalised rows (|v| <= 1) are scaled by 2^14 before the fp16 hi|lo split (both planes stay in fp16's normal range,
+// 22 significand bits survive); the frame kernel multiplies the accumulator by 2^-28.
+constexpr float UNIT_SCALE = 16384.0f;
+constexpr float UNIT_UNSCALE2 = 1.0f / (16384.0f * 16384.0f);
 
 // ------------------------------------------------------------------------------------ gallery
 // dst[i] = ring position of row i (or -1 when a later row of the same call overwrites it)
@@ -49,7 +53,7 @@ __global__ void pf_assign_kernel(const int32_t* __restrict__ slot_of_row, int n,
 __global__ void __launch_bounds__(256)
 pf_write_kernel(const float* __restrict__ feats, int64_t ldf, const int32_t* __restrict__ slot_of_row,
                 const int32_t* __restrict__ dst, int n, int budget, int d, int dp, float* __restrict__ gal,
-                __nv_bfloat16* __restrict__ packed) {
+                __half* __restrict__ packed) {
   const int i = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int lane = threadIdx.x & 31;
   if (i >= n) return;
@@ -61,20 +65,21 @@ pf_write_kernel(const float* __restrict__ feats, int64_t ldf, const int32_t* __r
   s = sqrtf(warp_sum(s));
   const size_t row = (size_t)slot_of_row[i] * budget + p;
   float* o = gal + row * d;
-  __nv_bfloat16* hi = packed + row * 2 * dp;
-  __nv_bfloat16* lo = hi + dp;
+  __half* hi = packed + row * 2 * dp;
+  __half* lo = hi + dp;
   for (int k = lane; k < d; k += 32) {
     const float v = __fdiv_rn(src[k], s);
     o[k] = v;
-    const __nv_bfloat16 h = __float2bfloat16_rn(v);
+    const float vs = __fmul_rn(v, UNIT_SCALE);
+    const __half h = __float2half_rn(vs);
     hi[k] = h;
-    lo[k] = __float2bfloat16_rn(v - __bfloat162float(h));
+    lo[k] = __float2half_rn(__fsub_rn(vs, __half2float(h)));
   }
 }
 
-// warp per detection: f / ||f|| in fp32 (matching.py:294-296) split into bf16 hi|lo planes (B operand of the frame kernel)
+// warp per detection: f / ||f|| in fp32 (matching.py:294-296) split into fp16 hi|lo planes (B operand of the frame kernel)
 __global__ void __launch_bounds__(256)
-det_pack_kernel(const float* __restrict__ feats, int64_t ldf, int n, int d, int dp, __nv_bfloat16* __restrict__ packed) {
+det_pack_kernel(const float* __restrict__ feats, int64_t ldf, int n, int d, int dp, __half* __restrict__ packed) {
   const int i = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int lane = threadIdx.x & 31;
   if (i >= n) return;
@@ -82,13 +87,13 @@ det_pack_kernel(const float* __restrict__ feats, int64_t ldf, int n, int d, int 
   float s = 0.f;
   for (int k = lane; k < d; k += 32) { const float v = src[k]; s = fmaf(v, v, s); }
   s = sqrtf(warp_sum(s));
-  __nv_bfloat16* hi = packed + (size_t)i * 2 * dp;
-  __nv_bfloat16* lo = hi + dp;
+  __half* hi = packed + (size_t)i * 2 * dp;
+  __half* lo = hi + dp;
   for (int k = lane; k < dp; k += 32) {
-    const float v = k < d ? __fdiv_rn(src[k], s) : 0.f;
-    const __nv_bfloat16 h = __float2bfloat16_rn(v);
+    const float v = k < d ? __fmul_rn(__fdiv_rn(src[k], s), UNIT_SCALE) : 0.f;
+    const __half h = __float2half_rn(v);
     hi[k] = h;
-    lo[k] = __float2bfloat16_rn(v - __bfloat162float(h));
+    lo[k] = __float2half_rn(__fsub_rn(v, __half2float(h)));
   }
 }
 
@@ -311,13 +316,13 @@ assoc_frame_simt_kernel(AssocArgs a) {
 
 // ------------------------------------------------------------------------------------ fused frame kernel, tcgen05
 // Persistent, one CTA per SM, work item = (track, 256-detection tile).  The track's ring rows (<= 128 per row tile,
-// rows >= count masked) are the A operand, the frame's normalised detections the B operand, both as bf16 hi|lo planes
-// (three UMMAs per k-step: lo.hi + hi.lo + hi.hi, fp32 accumulation in TMEM).  Warp 0 = TMA producer, warp 1 = MMA
+// rows >= count masked) are the A operand, the frame's normalised detections the B operand, both as fp16 hi|lo planes
+// (fp16, three UMMAs per k-step: lo.hi + hi.lo + hi.hi, fp32 accumulation in TMEM).  Warp 0 = TMA producer, warp 1 = MMA
 // issuer, warps 2-5 = epilogue: TMEM -> registers (thread = gallery row), masked column maximum by a transposing
 // butterfly (31 shuffles per 32 x 32 block), then -- thread = detection -- 1 - max, Mahalanobis gate + blend + clamp and
 // the IoU / DIoU row in fp64, exactly as the SIMT kernel above does.
 constexpr int AT_BM = 128, AT_BN = 256, AT_BK = 64, AT_STAGES = 2;
-constexpr int AT_PLANE = AT_BM * AT_BK * 2;                             // 16 KB: one bf16 plane of an A stage
+constexpr int AT_PLANE = AT_BM * AT_BK * 2;                             // 16 KB: one fp16 plane of an A stage
 constexpr int AT_STAGE_BYTES = 2 * AT_PLANE + 2 * AT_BN * AT_BK * 2;     // 96 KB (B planes sized for 256 detections)
 constexpr int AT_THREADS = 192;
 constexpr size_t AT_SMEM = 1024 + (size_t)AT_STAGES * AT_STAGE_BYTES + 2 * 4 * AT_BN * sizeof(float) + 2 * 32 * sizeof(double) + 128;
@@ -416,7 +421,7 @@ assoc_frame_kernel(const __grid_constant__ CUtensorMap tmG, const __grid_constan
         const int cnt = slot >= 0 ? a.gcount[slot] : 0;
         const int rts = (cnt + AT_BM - 1) / AT_BM;
         const int n_tile = min(bn_box, (a.M - dt * AT_BN + 15) & ~15);
-        const uint32_t idesc = ptx::umma_idesc_bf16(AT_BM, n_tile);
+        const uint32_t idesc = ptx::umma_idesc_f16(AT_BM, n_tile);
         for (int rt = 0; rt < rts; ++rt) {
           ptx::mbar_wait(bar_tempty + 8 * as, aphase ^ 1);
           ptx::tc_fence_after();
@@ -493,7 +498,7 @@ assoc_frame_kernel(const __grid_constant__ CUtensorMap tmG, const __grid_constan
           double cost = INFTY_COST, raw = INFTY_COST;
           if (cnt > 0) {
             const float mx = fmaxf(fmaxf(p0[col], p0[AT_BN + col]), fmaxf(p0[2 * AT_BN + col], p0[3 * AT_BN + col]));
-            raw = (double)__fsub_rn(1.0f, mx);
+            raw = (double)__fsub_rn(1.0f, __fmul_rn(mx, UNIT_UNSCALE2));
             cost = raw;
           }
           if (a.out_raw) a.out_raw[o] = raw;
@@ -569,11 +574,11 @@ extern "C" int reidb200_gallery_create(int slots, int budget, int d, reidb200_ga
   g->feats = nullptr; g->packed = nullptr; g->count = nullptr; g->head = nullptr; g->scratch = nullptr;
   g->det_packed = nullptr; g->det_cap = 1024;
   g->scratch_rows = slots > 1024 ? slots : 1024;
-  const size_t packed_sz = (size_t)slots * budget * 2 * g->dp * sizeof(__nv_bfloat16);
+  const size_t packed_sz = (size_t)slots * budget * 2 * g->dp * sizeof(__half);
   cudaError_t e = cudaMalloc(&g->feats, (size_t)slots * budget * d * sizeof(float));
   if (e == cudaSuccess) e = cudaMalloc(&g->packed, packed_sz);
   if (e == cudaSuccess) e = cudaMemset(g->packed, 0, packed_sz);
-  if (e == cudaSuccess) e = cudaMalloc(&g->det_packed, (size_t)g->det_cap * 2 * g->dp * sizeof(__nv_bfloat16));
+  if (e == cudaSuccess) e = cudaMalloc(&g->det_packed, (size_t)g->det_cap * 2 * g->dp * sizeof(__half));
   if (e == cudaSuccess) e = cudaMalloc(&g->count, (size_t)slots * sizeof(int32_t));
   if (e == cudaSuccess) e = cudaMalloc(&g->head, (size_t)slots * sizeof(int32_t));
   if (e == cudaSuccess) e = cudaMalloc(&g->scratch, (size_t)2 * g->scratch_rows * sizeof(int32_t));
@@ -668,7 +673,7 @@ extern "C" int reidb200_assoc_frame(reidb200_gallery* g, const float* det_feat, 
     cudaFree(g->det_packed);
     g->det_packed = nullptr;
     g->det_cap = M + M / 2;
-    RB_CUDA(cudaMalloc(&g->det_packed, (size_t)g->det_cap * 2 * g->dp * sizeof(__nv_bfloat16)));
+    RB_CUDA(cudaMalloc(&g->det_packed, (size_t)g->det_cap * 2 * g->dp * sizeof(__half)));
   }
   { ProfScope _ps("det_pack_kernel", st); det_pack_kernel<<<ceil_div(M, 8), 256, 0, st>>>(det_feat, ldf, M, g->d, g->dp, g->det_packed); }
   RB_LAUNCH_CHECK("det_pack_kernel");
@@ -719,6 +724,8 @@ extern "C" size_t reidb200_cosine_distance_workspace_bytes(int na, int nb, int d
   c.take<float>((size_t)nb * d);
   c.take<char>(packed_bytes(na, d));
   c.take<char>(packed_bytes(nb, d));
+  c.take<float>(na);
+  c.take<float>(nb);
   return align_up(c.off, 256);
 }
 
@@ -735,6 +742,8 @@ extern "C" int reidb200_cosine_distance(const float* a, int na, int64_t lda, con
   float* bn = c.take<float>((size_t)nb * d);
   char* pa = c.take<char>(packed_bytes(na, d));
   char* pb = c.take<char>(packed_bytes(nb, d));
+  float* isa = c.take<float>(na);
+  float* isb = c.take<float>(nb);
   const float* ax = a; const float* bx = b;
   int64_t la = lda, lb = ldb;
   if (!normalized) {
@@ -744,11 +753,11 @@ extern "C" int reidb200_cosine_distance(const float* a, int na, int64_t lda, con
     RB_LAUNCH_CHECK("normalize_rows_kernel");
     ax = an; bx = bn; la = d; lb = d;
   }
-  int rc = pack_rows_launch(ax, na, la, d, pa, nullptr, st);
+  int rc = pack_rows_launch(ax, na, la, d, pa, nullptr, isa, st);
   if (rc) return rc;
-  rc = pack_rows_launch(bx, nb, lb, d, pb, nullptr, st);
+  rc = pack_rows_launch(bx, nb, lb, d, pb, nullptr, isb, st);
   if (rc) return rc;
-  rc = gemm_split_launch(pa, nullptr, na, pb, nullptr, nb, d, REIDB200_DIST_DOT, out, nb, st);
+  rc = gemm_split_launch(pa, nullptr, isa, na, pb, nullptr, isb, nb, d, REIDB200_DIST_DOT, out, nb, st);
   if (rc) return rc;
   const size_t n = (size_t)na * nb;
   { ProfScope _ps("one_minus_kernel", st); one_minus_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(out, n); }

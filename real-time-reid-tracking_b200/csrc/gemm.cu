@@ -1,8 +1,12 @@
 // (2) Distance matrix as a tcgen05 / TMA tensor-core GEMM with fp32-accurate operands.
 //
-// Every fp32 operand row is split into two bf16 planes, x = hi + lo (|x - hi - lo| <= 2^-17 |x|), and
-// each 64-wide k-block issues three UMMAs into one fp32 TMEM accumulator:
-//        acc += Ahi.Bhi^T + Ahi.Blo^T + Alo.Bhi^T            (the dropped lo.lo term is ~2^-18 relative)
+// Every fp32 operand row is scaled by a power of two (its largest magnitude lands in [2^14, 2^15): exact, and it keeps
+// both planes in fp16's normal range) and split into two fp16 planes, s.x = hi + lo with |s.x - hi - lo| <= 2^-22 |s.x|
+// (fp16 carries 11 significand bits, so the pair carries 22 of fp32's 24).  Each 64-wide k-block issues three UMMAs
+// (kind::f16, fp32 accumulation in TMEM) into one accumulator:
+//        acc += Alo.Bhi^T + Ahi.Blo^T + Ahi.Bhi^T            (the dropped lo.lo term is ~2^-22 relative)
+// and the epilogue multiplies by the two inverse row scales (exact).  A bf16 split at the same cost would leave
+// 2^-18 per element -- 16x more error than this and 64x more than fp32.
 // Epilogues restate reid/losses/utils.py:12-35 (euclidean_dist, cosine_dist), reid/evaluate.py:58
 // (dot score) and faiss METRIC_L2 (reid/faiss_utils.py:97-111).
 //
@@ -14,38 +18,52 @@
 
 #include "gemm.cuh"
 #include "ptx.cuh"
+#include <math.h>
 
 namespace reidb200 {
 
 // ------------------------------------------------------------------------------------ packing
 __global__ void __launch_bounds__(256)
-pack_rows_kernel(const float* __restrict__ x, int rows, int64_t ldx, int d, int dp,
-                 __nv_bfloat16* __restrict__ packed, float* __restrict__ sqnorm) {
+pack_rows_kernel(const float* __restrict__ x, int rows, int64_t ldx, int d, int dp, __half* __restrict__ packed,
+                 float* __restrict__ sqnorm, float* __restrict__ iscale) {
   const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int lane = threadIdx.x & 31;
   if (warp >= rows) return;
   const float* src = x + (size_t)warp * ldx;
-  __nv_bfloat16* hi = packed + (size_t)warp * 2 * dp;
-  __nv_bfloat16* lo = hi + dp;
-  float s = 0.f;
-  for (int k = lane; k < dp; k += 32) {
-    const float v = k < d ? __ldg(src + k) : 0.f;
-    const __nv_bfloat16 h = __float2bfloat16_rn(v);
-    const __nv_bfloat16 l = __float2bfloat16_rn(v - __bfloat162float(h));
-    hi[k] = h;
-    lo[k] = l;
+  float s = 0.f, mx = 0.f;
+  for (int k = lane; k < d; k += 32) {
+    const float v = __ldg(src + k);
     s = fmaf(v, v, s);
+    mx = fmaxf(mx, fabsf(v));
   }
   s = warp_sum(s);
-  if (lane == 0 && sqnorm) sqnorm[warp] = s;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+  // scale = 2^(14 - floor(log2 max)): the row maximum lands in [2^14, 2^15); exponent clamped so the scale stays finite
+  int e = 0;
+  if (mx > 0.f && mx <= 3.0e38f) e = min(max(14 - ilogbf(mx), -100), 100);
+  const float scale = ldexpf(1.0f, e);
+  __half* hi = packed + (size_t)warp * 2 * dp;
+  __half* lo = hi + dp;
+  for (int k = lane; k < dp; k += 32) {
+    const float v = k < d ? __fmul_rn(__ldg(src + k), scale) : 0.f;
+    const __half h = __float2half_rn(v);
+    hi[k] = h;
+    lo[k] = __float2half_rn(__fsub_rn(v, __half2float(h)));
+  }
+  if (lane == 0) {
+    if (sqnorm) sqnorm[warp] = s;
+    iscale[warp] = ldexpf(1.0f, -e);
+  }
 }
 
-int pack_rows_launch(const float* x, int rows, int64_t ldx, int d, void* packed, float* sqnorm, cudaStream_t st) {
+int pack_rows_launch(const float* x, int rows, int64_t ldx, int d, void* packed, float* sqnorm, float* iscale,
+                     cudaStream_t st) {
   if (rows == 0) return REIDB200_OK;
   const int dp = padded_dim(d);
   const int warps_per_block = 8;
   { ProfScope _ps("pack_rows_kernel", st); pack_rows_kernel<<<ceil_div(rows, warps_per_block), warps_per_block * 32, 0, st>>>(
-      x, rows, ldx, d, dp, static_cast<__nv_bfloat16*>(packed), sqnorm); }
+      x, rows, ldx, d, dp, static_cast<__half*>(packed), sqnorm, iscale); }
   RB_LAUNCH_CHECK("pack_rows_kernel");
   return REIDB200_OK;
 }
@@ -81,6 +99,8 @@ struct GemmArgs {
   int m, n, dp, num_kb, tiles_m, tiles_n, kind;
   const float* xx;
   const float* yy;
+  const float* isa;  // inverse power-of-two scale of every A row / B row (pack_rows_kernel)
+  const float* isb;
   float* out;
   int64_t ldo;
   // optional per-(row, 32-column chunk) reduction of the epilogue values (min, or max when cred_max): lets the
@@ -100,6 +120,7 @@ __device__ __forceinline__ void epilogue_slab(const GemmArgs& a, uint32_t tmem_a
                                               float* sbuf, bool vec_ok) {
   const int my_row = row0 + lane;
   const float xx_mine = (KIND != REIDB200_DIST_DOT && my_row < a.m) ? __ldg(a.xx + my_row) : 0.f;
+  const float ia_mine = my_row < a.m ? __ldg(a.isa + my_row) : 0.f;
   const int rows_here = min(32, a.m - row0);
   if (rows_here <= 0) return;
 #pragma unroll 1
@@ -117,11 +138,12 @@ __device__ __forceinline__ void epilogue_slab(const GemmArgs& a, uint32_t tmem_a
         for (int j = 0; j < 32; j += 4) {
           float4 y4 = make_float4(0.f, 0.f, 0.f, 0.f);
           if (KIND != REIDB200_DIST_DOT) y4 = __ldg(reinterpret_cast<const float4*>(a.yy + col0 + j));
+          const float4 s4 = __ldg(reinterpret_cast<const float4*>(a.isb + col0 + j));
           float4 o;
-          o.x = dist_epilogue(KIND, __uint_as_float(r[j + 0]), xx_mine, y4.x);
-          o.y = dist_epilogue(KIND, __uint_as_float(r[j + 1]), xx_mine, y4.y);
-          o.z = dist_epilogue(KIND, __uint_as_float(r[j + 2]), xx_mine, y4.z);
-          o.w = dist_epilogue(KIND, __uint_as_float(r[j + 3]), xx_mine, y4.w);
+          o.x = dist_epilogue(KIND, __fmul_rn(__fmul_rn(__uint_as_float(r[j + 0]), ia_mine), s4.x), xx_mine, y4.x);
+          o.y = dist_epilogue(KIND, __fmul_rn(__fmul_rn(__uint_as_float(r[j + 1]), ia_mine), s4.y), xx_mine, y4.y);
+          o.z = dist_epilogue(KIND, __fmul_rn(__fmul_rn(__uint_as_float(r[j + 2]), ia_mine), s4.z), xx_mine, y4.z);
+          o.w = dist_epilogue(KIND, __fmul_rn(__fmul_rn(__uint_as_float(r[j + 3]), ia_mine), s4.w), xx_mine, y4.w);
           __stcs(reinterpret_cast<float4*>(dst + j), o);
           if (a.cred) {
             const float lo4 = fminf(fminf(o.x, o.y), fminf(o.z, o.w)), hi4 = fmaxf(fmaxf(o.x, o.y), fmaxf(o.z, o.w));
@@ -135,7 +157,7 @@ __device__ __forceinline__ void epilogue_slab(const GemmArgs& a, uint32_t tmem_a
         float red2 = a.cred_max ? -INFINITY : INFINITY;
         for (int j = 0; j < 32 && col0 + j < a.n; ++j) {
           const float yv = KIND != REIDB200_DIST_DOT ? __ldg(a.yy + col0 + j) : 0.f;
-          const float o = dist_epilogue(KIND, __uint_as_float(r[j]), xx_mine, yv);
+          const float o = dist_epilogue(KIND, __fmul_rn(__fmul_rn(__uint_as_float(r[j]), ia_mine), __ldg(a.isb + col0 + j)), xx_mine, yv);
           red2 = a.cred_max ? fmaxf(red2, o) : fminf(red2, o);
         }
         a.cred[(size_t)my_row * a.ldcr + (col0 >> 5)] = red2;
@@ -145,10 +167,12 @@ __device__ __forceinline__ void epilogue_slab(const GemmArgs& a, uint32_t tmem_a
       __syncwarp();
       const int col = col0 + lane;
       const float yy_c = (KIND != REIDB200_DIST_DOT && col < a.n) ? __ldg(a.yy + col) : 0.f;
+      const float ib_c = col < a.n ? __ldg(a.isb + col) : 0.f;
 #pragma unroll 8
       for (int rr = 0; rr < 32; ++rr) {
-        const float acc = sbuf[rr * 33 + lane];
         const float xr = __shfl_sync(0xffffffffu, xx_mine, rr);
+        const float ir = __shfl_sync(0xffffffffu, ia_mine, rr);
+        const float acc = __fmul_rn(__fmul_rn(sbuf[rr * 33 + lane], ir), ib_c);
         if (rr < rows_here && col < a.n)
           __stcs(a.out + (size_t)(row0 + rr) * a.ldo + col, dist_epilogue(KIND, acc, xr, yy_c));
       }
@@ -221,7 +245,7 @@ gemm_split_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
   } else if (warp == 1) {
     // ===== MMA issuer (one thread issues every UMMA and every commit)
     if (lane == 0) {
-      constexpr uint32_t idesc = ptx::umma_idesc_bf16(BM, BN);
+      constexpr uint32_t idesc = ptx::umma_idesc_f16(BM, BN);
       int stage = 0, as = 0;
       uint32_t phase = 0, aphase = 0;
       for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
@@ -255,7 +279,8 @@ gemm_split_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
     const int q = warp & 3;
     float* sbuf = epi_buf + (warp - 2) * EPI_STAGE_FLOATS;
     const bool vec_ok = (a.ldo & 3) == 0 && (reinterpret_cast<uintptr_t>(a.out) & 15) == 0 &&
-                        (a.yy == nullptr || (reinterpret_cast<uintptr_t>(a.yy) & 15) == 0);
+                        (a.yy == nullptr || (reinterpret_cast<uintptr_t>(a.yy) & 15) == 0) &&
+                        (reinterpret_cast<uintptr_t>(a.isb) & 15) == 0;
     int as = 0;
     uint32_t aphase = 0;
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
@@ -358,7 +383,7 @@ gemm_split_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
   } else if (warp == 1) {
     // ===== MMA issuer: one thread of the even CTA
     if (leader && lane == 0) {
-      constexpr uint32_t idesc = ptx::umma_idesc_bf16(2 * BM, BN);
+      constexpr uint32_t idesc = ptx::umma_idesc_f16(2 * BM, BN);
       int stage = 0, as = 0;
       uint32_t phase = 0, aphase = 0;
       for (int tile = cluster_id; tile < total_tiles; tile += num_clusters) {
@@ -392,7 +417,8 @@ gemm_split_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
     const int q = warp & 3;
     float* sbuf = epi_buf + (warp - 2) * EPI_STAGE_FLOATS;
     const bool vec_ok = (a.ldo & 3) == 0 && (reinterpret_cast<uintptr_t>(a.out) & 15) == 0 &&
-                        (a.yy == nullptr || (reinterpret_cast<uintptr_t>(a.yy) & 15) == 0);
+                        (a.yy == nullptr || (reinterpret_cast<uintptr_t>(a.yy) & 15) == 0) &&
+                        (reinterpret_cast<uintptr_t>(a.isb) & 15) == 0;
     int as = 0;
     uint32_t aphase = 0;
     for (int tile = cluster_id; tile < total_tiles; tile += num_clusters) {
@@ -460,7 +486,7 @@ static EncodeTiledFn get_encode_fn() {
   return fn;
 }
 
-// packed operand [rows, 2*dp] bf16, box = {64, box_rows}, 128-byte swizzle, OOB rows/cols read as zero
+// packed operand [rows, 2*dp] fp16, box = {64, box_rows}, 128-byte swizzle, OOB rows/cols read as zero
 int make_operand_map(CUtensorMap* tm, const void* packed, int rows, int dp, int box_rows) {
   EncodeTiledFn enc = get_encode_fn();
   if (!enc) {
@@ -468,10 +494,10 @@ int make_operand_map(CUtensorMap* tm, const void* packed, int rows, int dp, int 
     return REIDB200_ECUDA;
   }
   cuuint64_t gdim[2] = {(cuuint64_t)2 * dp, (cuuint64_t)rows};
-  cuuint64_t gstride[1] = {(cuuint64_t)2 * dp * sizeof(__nv_bfloat16)};
+  cuuint64_t gstride[1] = {(cuuint64_t)2 * dp * sizeof(__half)};
   cuuint32_t box[2] = {(cuuint32_t)BK, (cuuint32_t)box_rows};
   cuuint32_t estr[2] = {1, 1};
-  CUresult r = enc(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(packed), gdim, gstride, box, estr,
+  CUresult r = enc(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, const_cast<void*>(packed), gdim, gstride, box, estr,
                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) {
@@ -481,10 +507,11 @@ int make_operand_map(CUtensorMap* tm, const void* packed, int rows, int dp, int 
   return REIDB200_OK;
 }
 
-int gemm_split_launch(const void* packedA, const float* xx, int m, const void* packedB, const float* yy, int n, int d,
-                      int kind, float* out, int64_t ldo, cudaStream_t st, float* chunk_red, int64_t ld_chunk_red,
-                      int chunk_red_max) {
+int gemm_split_launch(const void* packedA, const float* xx, const float* isa, int m, const void* packedB, const float* yy,
+                      const float* isb, int n, int d, int kind, float* out, int64_t ldo, cudaStream_t st, float* chunk_red,
+                      int64_t ld_chunk_red, int chunk_red_max) {
   if (m == 0 || n == 0) return REIDB200_OK;
+  RB_REQUIRE(isa && isb, "distmat: operand scales missing");
   RB_REQUIRE(kind >= 0 && kind <= 3, "distmat: unknown kind %d", kind);
   RB_REQUIRE(kind == REIDB200_DIST_DOT || (xx && yy), "distmat: row norms required for kind %d", kind);
   const int dp = padded_dim(d);
@@ -497,7 +524,7 @@ int gemm_split_launch(const void* packedA, const float* xx, int m, const void* p
   GemmArgs a;
   a.m = m; a.n = n; a.dp = dp; a.num_kb = dp / BK;
   a.tiles_m = ceil_div(m, BM); a.tiles_n = ceil_div(n, BN);
-  a.kind = kind; a.xx = xx; a.yy = yy; a.out = out; a.ldo = ldo;
+  a.kind = kind; a.xx = xx; a.yy = yy; a.isa = isa; a.isb = isb; a.out = out; a.ldo = ldo;
   a.cred = chunk_red; a.ldcr = ld_chunk_red; a.cred_max = chunk_red_max;
   void (*k1)(CUtensorMap, CUtensorMap, GemmArgs) = nullptr;
   void (*k2)(CUtensorMap, CUtensorMap, GemmArgs) = nullptr;
@@ -538,20 +565,20 @@ extern "C" size_t reidb200_pack_bytes(int rows, int d) {
 }
 
 extern "C" int reidb200_pack_rows(const float* x, int rows, int64_t ldx, int d, void* packed, float* sqnorm,
-                                  void* stream) {
+                                  float* iscale, void* stream) {
   if (rows == 0) return REIDB200_OK;
-  RB_REQUIRE(x && packed && rows > 0 && d > 0 && ldx >= d, "pack_rows: bad argument");
+  RB_REQUIRE(x && packed && iscale && rows > 0 && d > 0 && ldx >= d, "pack_rows: bad argument");
   RB_REQUIRE((reinterpret_cast<uintptr_t>(packed) & 15) == 0, "pack_rows: packed buffer must be 16-byte aligned");
-  return pack_rows_launch(x, rows, ldx, d, packed, sqnorm, (cudaStream_t)stream);
+  return pack_rows_launch(x, rows, ldx, d, packed, sqnorm, iscale, (cudaStream_t)stream);
 }
 
 extern "C" size_t reidb200_distmat_workspace_bytes(int m, int n, int d) {
   if (m <= 0 || n <= 0 || d <= 0) return 0;
   CarveSize c;
   c.take<char>(packed_bytes(m, d));
-  c.take<float>(m);
+  c.take<float>(2 * align_up((size_t)m, 4));
   c.take<char>(packed_bytes(n, d));
-  c.take<float>(n);
+  c.take<float>(2 * align_up((size_t)n, 4));
   return align_up(c.off, 256);
 }
 
@@ -565,19 +592,22 @@ extern "C" int reidb200_distmat(const float* x, int m, int64_t ldx, const float*
   cudaStream_t st = (cudaStream_t)stream;
   Carver c(workspace, workspace_bytes);
   void* pa = c.take<char>(packed_bytes(m, d));
-  float* xx = c.take<float>(m);
+  float* xx = c.take<float>(2 * align_up((size_t)m, 4));
   void* pb = c.take<char>(packed_bytes(n, d));
-  float* yy = c.take<float>(n);
-  int rc = pack_rows_launch(x, m, ldx, d, pa, xx, st);
+  float* yy = c.take<float>(2 * align_up((size_t)n, 4));
+  float* isa = xx + align_up((size_t)m, 4);  // 16-byte aligned halves: the epilogue loads float4s of yy and isb
+  float* isb = yy + align_up((size_t)n, 4);
+  int rc = pack_rows_launch(x, m, ldx, d, pa, xx, isa, st);
   if (rc) return rc;
   if (x == y && m == n && ldx == ldy) {
     pb = pa;
     yy = xx;
+    isb = isa;
   } else {
-    rc = pack_rows_launch(y, n, ldy, d, pb, yy, st);
+    rc = pack_rows_launch(y, n, ldy, d, pb, yy, isb, st);
     if (rc) return rc;
   }
-  return gemm_split_launch(pa, xx, m, pb, yy, n, d, kind, out, ldo, st);
+  return gemm_split_launch(pa, xx, isa, m, pb, yy, isb, n, d, kind, out, ldo, st);
 }
 
 extern "C" int reidb200_distmat_simt(const float* x, int m, int64_t ldx, const float* y, int n, int64_t ldy, int d,

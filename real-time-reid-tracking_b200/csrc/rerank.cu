@@ -452,6 +452,7 @@ extern "C" size_t reidb200_jaccard_workspace_bytes(int N, int d, int k1, int k2)
   NullCarver c;
   c.take<char>(packed_bytes(N, d));
   c.take<float>(N);
+  c.take<float>(N);
   c.take<float>((size_t)N * rd.lds);
   c.take<float>((size_t)N * k1);
   c.take<int32_t>((size_t)N * k1);
@@ -503,6 +504,7 @@ extern "C" int reidb200_jaccard(const float* feats, int N, int64_t ldf, int d, i
   Carver c(workspace, workspace_bytes);
   char* packed = c.take<char>(packed_bytes(N, d));
   float* sqn = c.take<float>(N);
+  float* isc = c.take<float>(N);
   float* sql2 = c.take<float>((size_t)N * rd.lds);
   float* rank_d = c.take<float>((size_t)N * k1);
   int32_t* rank_i = c.take<int32_t>((size_t)N * k1);
@@ -510,9 +512,9 @@ extern "C" int reidb200_jaccard(const float* feats, int N, int64_t ldf, int d, i
   float* cred = c.take<float>((size_t)N * ldcr);
   SparseWs w;
   carve_sparse(c, N, k1, k2, rd, &w);
-  rc = pack_rows_launch(feats, N, ldf, d, packed, sqn, st);
+  rc = pack_rows_launch(feats, N, ldf, d, packed, sqn, isc, st);
   if (rc) return rc;
-  rc = gemm_split_launch(packed, sqn, N, packed, sqn, N, d, REIDB200_DIST_SQL2, sql2, rd.lds, st, cred, ldcr, 0);
+  rc = gemm_split_launch(packed, sqn, isc, N, packed, sqn, isc, N, d, REIDB200_DIST_SQL2, sql2, rd.lds, st, cred, ldcr, 0);
   if (rc) return rc;
   rc = topk_rows_launch(sql2, N, N, rd.lds, nullptr, k1, 0, 0, rank_d, rank_i, 0, st, cred, ldcr);
   if (rc) return rc;

@@ -330,8 +330,8 @@ static void knn_scratch_size(CarveSize& c, int nq, int nb, int k) {
   }
 }
 
-static int knn_core(const char* pq, const float* qq, int nq, const char* pb, const float* bb, int nb, int d, int k,
-                    int metric, int64_t index_base, float* out_d, void* out_i, int idx64, Carver& c, cudaStream_t st) {
+static int knn_core(const char* pq, const float* qq, const float* isq, int nq, const char* pb, const float* bb,
+                    const float* isb, int nb, int d, int k, int metric, int64_t index_base, float* out_d, void* out_i, int idx64, Carver& c, cudaStream_t st) {
   const int chunk = knn_chunk_cols(nq, nb);
   const int nchunks = ceil_div(nb, chunk);
   const int dp = padded_dim(d);
@@ -350,8 +350,8 @@ static int knn_core(const char* pq, const float* qq, int nq, const char* pb, con
   for (int ch = 0; ch < nchunks; ++ch) {
     const int c0 = ch * chunk;
     const int nc = min(chunk, nb - c0);
-    int rc = gemm_split_launch(pq, qq, nq, pb + (size_t)c0 * 2 * dp * sizeof(__nv_bfloat16), bb + c0, nc, d, metric, dist,
-                               ldd, st, cred, ldcr, desc);
+    int rc = gemm_split_launch(pq, qq, isq, nq, pb + (size_t)c0 * 2 * dp * sizeof(__half), bb + c0, isb + c0, nc, d, metric,
+                               dist, ldd, st, cred, ldcr, desc);
     if (rc) return rc;
     if (nchunks == 1)
       return topk_rows_launch(dist, nq, nc, ldd, nullptr, k, desc, index_base, out_d, out_i, idx64, st, cred, ldcr);
@@ -380,7 +380,9 @@ extern "C" size_t reidb200_knn_workspace_bytes(int nq, int nb, int d, int k) {
   CarveSize c;
   c.take<char>(packed_bytes(nq, d));
   c.take<float>(nq);
+  c.take<float>(nq);
   c.take<char>(packed_bytes(nb, d));
+  c.take<float>(nb);
   c.take<float>(nb);
   knn_scratch_size(c, nq, nb, k);
   return align_up(c.off, 256);
@@ -399,13 +401,15 @@ extern "C" int reidb200_knn(const float* xq, int nq, int64_t ldq, const float* x
   Carver c(workspace, workspace_bytes);
   char* pq = c.take<char>(packed_bytes(nq, d));
   float* qq = c.take<float>(nq);
+  float* isq = c.take<float>(nq);
   char* pb = c.take<char>(packed_bytes(nb, d));
   float* bb = c.take<float>(nb);
-  int rc = pack_rows_launch(xq, nq, ldq, d, pq, qq, st);
+  float* isb = c.take<float>(nb);
+  int rc = pack_rows_launch(xq, nq, ldq, d, pq, qq, isq, st);
   if (rc) return rc;
-  if (xq == xb && nq == nb && ldq == ldb) { pb = pq; bb = qq; }
-  else { rc = pack_rows_launch(xb, nb, ldb, d, pb, bb, st); if (rc) return rc; }
-  return knn_core(pq, qq, nq, pb, bb, nb, d, k, metric, index_base, out_d, out_i, idx64, c, st);
+  if (xq == xb && nq == nb && ldq == ldb) { pb = pq; bb = qq; isb = isq; }
+  else { rc = pack_rows_launch(xb, nb, ldb, d, pb, bb, isb, st); if (rc) return rc; }
+  return knn_core(pq, qq, isq, nq, pb, bb, isb, nb, d, k, metric, index_base, out_d, out_i, idx64, c, st);
 }
 
 extern "C" size_t reidb200_knn_packed_workspace_bytes(int nq, int nb, int d, int k) {
@@ -413,15 +417,16 @@ extern "C" size_t reidb200_knn_packed_workspace_bytes(int nq, int nb, int d, int
   CarveSize c;
   c.take<char>(packed_bytes(nq, d));
   c.take<float>(nq);
+  c.take<float>(nq);
   knn_scratch_size(c, nq, nb, k);
   return align_up(c.off, 256);
 }
 
 extern "C" int reidb200_knn_packed(const float* xq, int nq, int64_t ldq, const void* packed_b, const float* sqnorm_b,
-                                   int nb, int d, int k, int metric, int64_t index_base, float* out_d, void* out_i,
+                                   const float* iscale_b, int nb, int d, int k, int metric, int64_t index_base, float* out_d, void* out_i,
                                    int idx64, void* workspace, size_t workspace_bytes, void* stream) {
   if (nq == 0) return REIDB200_OK;
-  RB_REQUIRE(xq && packed_b && sqnorm_b && out_d && out_i && nq > 0 && nb > 0 && d > 0,
+  RB_REQUIRE(xq && packed_b && sqnorm_b && iscale_b && out_d && out_i && nq > 0 && nb > 0 && d > 0,
              "knn_packed: bad argument nq=%d nb=%d d=%d", nq, nb, d);
   RB_REQUIRE(k > 0 && k <= TOPK_MAX_K, "knn_packed: k=%d outside [1,%d]", k, TOPK_MAX_K);
   RB_REQUIRE(metric == REIDB200_DIST_SQL2 || metric == REIDB200_DIST_DOT, "knn_packed: metric must be SQL2 or DOT");
@@ -429,12 +434,15 @@ extern "C" int reidb200_knn_packed(const float* xq, int nq, int64_t ldq, const v
              "knn_packed: workspace too small");
   RB_REQUIRE((reinterpret_cast<uintptr_t>(workspace) & 255) == 0 && (reinterpret_cast<uintptr_t>(packed_b) & 127) == 0,
              "knn_packed: workspace must be 256-byte and the packed gallery 128-byte aligned");
+  RB_REQUIRE(((reinterpret_cast<uintptr_t>(sqnorm_b) | reinterpret_cast<uintptr_t>(iscale_b)) & 15) == 0,
+             "knn_packed: sqnorm_b / iscale_b must be 16-byte aligned");
   cudaStream_t st = (cudaStream_t)stream;
   Carver c(workspace, workspace_bytes);
   char* pq = c.take<char>(packed_bytes(nq, d));
   float* qq = c.take<float>(nq);
-  int rc = pack_rows_launch(xq, nq, ldq, d, pq, qq, st);
+  float* isq = c.take<float>(nq);
+  int rc = pack_rows_launch(xq, nq, ldq, d, pq, qq, isq, st);
   if (rc) return rc;
-  return knn_core(pq, qq, nq, static_cast<const char*>(packed_b), sqnorm_b, nb, d, k, metric, index_base, out_d, out_i,
-                  idx64, c, st);
+  return knn_core(pq, qq, isq, nq, static_cast<const char*>(packed_b), sqnorm_b, iscale_b, nb, d, k, metric, index_base,
+                  out_d, out_i, idx64, c, st);
 }

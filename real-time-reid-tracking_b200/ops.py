@@ -85,9 +85,9 @@ def knn(xq, xb, k, metric="sql2", index_base=0, idx64=True):
     return D, I
 
 
-def pack_rows(x, out=None, sqnorm=None):
-    """f32[rows,d] -> (packed u8 bytes of the bf16 hi|lo planes, sqnorm f32[rows]): the resident form of a gallery.
-    `out` / `sqnorm` may be slices of a larger preallocated shard so that a gallery is packed piecewise."""
+def pack_rows(x, out=None, sqnorm=None, iscale=None):
+    """f32[rows,d] -> (packed u8 bytes of the scaled fp16 hi|lo planes, sqnorm f32[rows], iscale f32[rows]): the resident
+    form of a gallery.  `out` / `sqnorm` / `iscale` may be slices of a larger preallocated shard (piecewise packing)."""
     x = _f32(x)
     dev = L.require_device(x)
     rows, d = x.shape
@@ -97,18 +97,21 @@ def pack_rows(x, out=None, sqnorm=None):
         out = torch.empty(max(nbytes, 256), dtype=torch.uint8, device=dev)
     if sqnorm is None:
         sqnorm = torch.empty(rows, dtype=torch.float32, device=dev)
+    if iscale is None:
+        iscale = torch.empty(rows, dtype=torch.float32, device=dev)
     if rows:
         with torch.cuda.device(dev):
-            L.check(lib.reidb200_pack_rows(x.data_ptr(), rows, x.stride(0), d, out.data_ptr(), sqnorm.data_ptr(), L.stream_ptr()))
-    return out, sqnorm
+            L.check(lib.reidb200_pack_rows(x.data_ptr(), rows, x.stride(0), d, out.data_ptr(), sqnorm.data_ptr(),
+                                           iscale.data_ptr(), L.stream_ptr()))
+    return out, sqnorm, iscale
 
 
 def packed_row_bytes(d):
-    """bytes one gallery row occupies in packed form (bf16 hi + lo planes, d padded to 64)."""
+    """bytes one gallery row occupies in packed form (fp16 hi + lo planes, d padded to 64)."""
     return 2 * ((int(d) + 63) // 64 * 64) * 2
 
 
-def knn_packed(xq, packed, sqnorm, nb, d, k, metric="sql2", index_base=0, idx64=True):
+def knn_packed(xq, packed, sqnorm, iscale, nb, d, k, metric="sql2", index_base=0, idx64=True):
     """knn against a gallery packed once by pack_rows (resident index / one shard of a sharded gallery)."""
     xq = _f32(xq)
     dev = L.require_device(xq)
@@ -124,7 +127,8 @@ def knn_packed(xq, packed, sqnorm, nb, d, k, metric="sql2", index_base=0, idx64=
     lib = L.load()
     ws = L.workspace(lib.reidb200_knn_packed_workspace_bytes(nq, nb, d, k), dev)
     with torch.cuda.device(dev):
-        L.check(lib.reidb200_knn_packed(xq.data_ptr(), nq, xq.stride(0), packed.data_ptr(), sqnorm.data_ptr(), int(nb), int(d),
+        L.check(lib.reidb200_knn_packed(xq.data_ptr(), nq, xq.stride(0), packed.data_ptr(), sqnorm.data_ptr(), iscale.data_ptr(), int(nb),
+                                        int(d),
                                         int(k), _KIND[metric], int(index_base), D.data_ptr(), I.data_ptr(), 1 if idx64 else 0,
                                         ws.data_ptr(), ws.numel(), L.stream_ptr()))
     return D, I

@@ -2,7 +2,7 @@
 
 Mirrors the reference's `index_init_gpu` (reid/faiss_utils.py:121-135): a faiss `IndexShards` over one
 `GpuIndexFlatL2` per GPU -- contiguous row ranges per shard, queries replicated, per-shard top-k merged.  Here every
-rank owns one shard as a RESIDENT packed operand (bf16 hi|lo planes + squared norms, packed once at add time; the fp32
+rank owns one shard as a RESIDENT packed operand (scaled fp16 hi|lo planes + squared norms, packed once at add time; the fp32
 rows are not kept), runs the tcgen05 GEMM + chunk-guided row-select of libreidb200 on it (`reidb200_knn_packed`), and
 the per-shard (distance, global id)[Q,k] tables are exchanged with ONE `all_gather` (NCCL over NVLink/NVSwitch,
 Q*k*12 bytes per rank) and merged P*k -> k by the same row-select kernel with explicit candidate ids
@@ -51,6 +51,7 @@ class ShardedSearcher:
         self.capacity = 0
         self._packed = None    # u8 [capacity * packed_row_bytes]
         self._sqnorm = None    # f32 [capacity]
+        self._iscale = None    # f32 [capacity] inverse power-of-two row scales of the packed planes
         self._rows = None      # injected-search mode keeps the rows as given
 
     @property
@@ -70,10 +71,12 @@ class ShardedSearcher:
         rb = ops.packed_row_bytes(self.d)
         packed = torch.empty(max(rows * rb, 256), dtype=torch.uint8, device=self.device)
         sq = torch.empty(max(rows, 1), dtype=torch.float32, device=self.device)
+        isc = torch.empty(max(rows, 1), dtype=torch.float32, device=self.device)
         if self.n_local:
             packed[: self.n_local * rb].copy_(self._packed[: self.n_local * rb])
             sq[: self.n_local].copy_(self._sqnorm[: self.n_local])
-        self._packed, self._sqnorm, self.capacity = packed, sq, rows
+            isc[: self.n_local].copy_(self._iscale[: self.n_local])
+        self._packed, self._sqnorm, self._iscale, self.capacity = packed, sq, isc, rows
 
     def append(self, x):
         """Append local rows f32[n,d] (host or device) to this rank's shard; global ids continue from base."""
@@ -91,7 +94,8 @@ class ShardedSearcher:
             self.reserve(max(self.n_local + n, 2 * self.capacity))
         rb = ops.packed_row_bytes(self.d)
         lo = self.n_local
-        ops.pack_rows(L.as_f32_cuda(x, self.device), out=self._packed[lo * rb:(lo + n) * rb], sqnorm=self._sqnorm[lo:lo + n])
+        ops.pack_rows(L.as_f32_cuda(x, self.device), out=self._packed[lo * rb:(lo + n) * rb], sqnorm=self._sqnorm[lo:lo + n],
+                      iscale=self._iscale[lo:lo + n])
         self.n_local += n
 
     def add_shard(self, x_local, base=None):
@@ -118,7 +122,7 @@ class ShardedSearcher:
     def _search_local(self, xq, k, metric):
         if self._custom:
             return self._local_search(xq, self._rows, k, metric, self.base)
-        return ops.knn_packed(xq, self._packed, self._sqnorm, self.n_local, self.d, k, metric, index_base=self.base, idx64=True)
+        return ops.knn_packed(xq, self._packed, self._sqnorm, self._iscale, self.n_local, self.d, k, metric, index_base=self.base, idx64=True)
 
     def search_device(self, xq, k, metric="sql2"):
         """(D f32[Q,k], I i64[Q,k]) identical on every rank; queries must be the same on every rank."""

@@ -64,6 +64,31 @@ def test_distmat_unit_features_ranking(rb):
         assert np.allclose(ref[r, a[r, c]], ref[r, b[r, c]], rtol=REL)
 
 
+def test_distmat_accuracy_is_fp32_class(rb):
+    """The scaled fp16 hi|lo split keeps 22 significand bits per operand, so the operand error is ~2^-22 relative; what is
+    left is the tensor core's own fp32 accumulation, which truncates: every UMMA loses < 1 ulp of the RUNNING sum, i.e. a
+    few 1e-7 for small dot products and up to ~3 * (d/16) * 2^-25 for |dot| ~ |x||y| (near duplicates)."""
+    from reidb200 import ops
+
+    rng = np.random.default_rng(3)
+    x, y = _unit(rng.standard_normal((300, 512))), _unit(rng.standard_normal((700, 512)))
+    y[:50] = _unit(x[:50] + 1e-3 * rng.standard_normal((50, 512)))  # near duplicates: dot ~ 1
+    truth = x.astype(np.float64) @ y.astype(np.float64).T
+    got = ops.distmat(x, y, "dot").cpu().numpy()
+    err = np.abs(got - truth)
+    assert err[np.abs(truth) < 0.5].max() <= 3e-7, err[np.abs(truth) < 0.5].max()
+    assert err.max() <= 3 * (512 / 16) * 2.0 ** -25 * 2.5, err.max()  # 7.2e-6: truncating accumulation at |dot| ~ 1
+    sx = (10.0 ** rng.uniform(-3, 3, (300, 1))).astype(np.float32)
+    sy = (10.0 ** rng.uniform(-3, 3, (700, 1))).astype(np.float32)
+    xs, ys = x * sx, y * sy
+    truth = xs.astype(np.float64) @ ys.astype(np.float64).T
+    got = ops.distmat(xs, ys, "dot").cpu().numpy()
+    scale = np.linalg.norm(xs, axis=1)[:, None] * np.linalg.norm(ys, axis=1)[None, :]
+    assert (np.abs(got - truth) <= (3e-7 + 7.2e-6 * np.abs(truth) / scale) * scale).all()
+    z = np.zeros((3, 512), np.float32)  # all-zero rows: scale falls back to 1, distances stay finite
+    assert np.array_equal(ops.distmat(z, y[:5], "dot").cpu().numpy(), np.zeros((3, 5), np.float32))
+
+
 def test_distmat_errors(rb):
     from reidb200 import ops
 

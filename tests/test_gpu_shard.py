@@ -34,11 +34,11 @@ def test_knn_packed_equals_knn(rb, nq, nb, d, k):
     rng = np.random.default_rng(nb)
     xb, xq = _unit(rng.standard_normal((nb, d))), _unit(rng.standard_normal((nq, d)))
     D0, I0 = ops.knn(xq, xb, k, "sql2", index_base=1000)
-    packed, sq = ops.pack_rows(xb)
-    D1, I1 = ops.knn_packed(xq, packed, sq, nb, d, k, "sql2", index_base=1000)
+    packed, sq, isc = ops.pack_rows(xb)
+    D1, I1 = ops.knn_packed(xq, packed, sq, isc, nb, d, k, "sql2", index_base=1000)
     assert torch.equal(D0, D1) and torch.equal(I0, I1)  # same kernels, same operands: bit-identical
     _check(D1.cpu().numpy(), I1.cpu().numpy() - 1000, xq, xb, k)
-    Dd, Id = ops.knn_packed(xq, packed, sq, nb, d, k, "dot")
+    Dd, Id = ops.knn_packed(xq, packed, sq, isc, nb, d, k, "dot")
     ref = xq @ xb.T
     order = np.argsort(-ref, axis=1, kind="stable")[:, :k]
     np.testing.assert_allclose(Dd.cpu().numpy(), np.take_along_axis(ref, order, 1), rtol=REL, atol=2e-5)
