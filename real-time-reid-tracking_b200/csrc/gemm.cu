@@ -15,6 +15,7 @@
 // CTA tile 128 x 256, k-block 64 (one SWIZZLE_128B atom), 2 smem stages of 96 KB
 // (Ahi, Alo, Bhi, Blo), 2 TMEM accumulator stages of 256 columns.
 #include <stdlib.h>
+#include <string.h>
 
 #include "gemm.cuh"
 #include "ptx.cuh"
@@ -90,7 +91,7 @@ constexpr int STAGES = 2;
 constexpr int A_BYTES = BM * BK * 2;                      // 16 KB
 constexpr int B_BYTES = BN * BK * 2;                      // 32 KB
 constexpr int STAGE_BYTES = 2 * A_BYTES + 2 * B_BYTES;    // 96 KB
-constexpr int EPI_STAGE_FLOATS = 32 * 33;                 // per epilogue warp
+constexpr int EPI_STAGE_FLOATS = 2 * 32 * 32;             // per epilogue warp: two 32 x 32 fp32 output boxes (TMA store source)
 constexpr int GEMM_THREADS = 192;
 constexpr int TMEM_COLS = 512;
 constexpr size_t GEMM_SMEM = 1024 + (size_t)STAGES * STAGE_BYTES + 4 * EPI_STAGE_FLOATS * 4 + 128;
@@ -108,16 +109,18 @@ struct GemmArgs {
   float* cred;
   int64_t ldcr;
   int cred_max;
+  int tma_out;  // the output tensor map is valid (16-byte aligned rows): epilogue stores through the TMA engine
 };
 
 
 // Epilogue of one 32-row x 256-column accumulator slab owned by one warp (TMEM lane quadrant q): thread = row.
-// Fast path (16-byte aligned rows): every thread streams its own row straight from registers with 128-bit stores
-// (a thread writes whole 128-byte lines, L2 merges them).  Slow path (odd leading dimension): transpose through a
-// padded shared-memory tile and store row-contiguous scalars.
+// Fast path (16-byte aligned rows): the warp stages each 32 x 32 box in shared memory (128-byte rows, 16-byte chunks
+// XOR-swizzled by row & 7: four conflict-free wavefronts per 512-byte store) and one lane hands it to the TMA store
+// engine, which clips the ragged matrix edges; two boxes per warp are in flight.  Slow path (odd leading dimension):
+// transpose through a padded shared-memory tile and store row-contiguous scalars.
 template <int KIND>
-__device__ __forceinline__ void epilogue_slab(const GemmArgs& a, uint32_t tmem_addr, int row0, int col_base, int lane,
-                                              float* sbuf, bool vec_ok) {
+__device__ __forceinline__ void epilogue_slab(const GemmArgs& a, const CUtensorMap* tmO, uint32_t tmem_addr, int row0,
+                                              int col_base, int lane, float* sbuf, bool vec_ok, int& box) {
   const int my_row = row0 + lane;
   const float xx_mine = (KIND != REIDB200_DIST_DOT && my_row < a.m) ? __ldg(a.xx + my_row) : 0.f;
   const float ia_mine = my_row < a.m ? __ldg(a.isa + my_row) : 0.f;
@@ -130,35 +133,65 @@ __device__ __forceinline__ void epilogue_slab(const GemmArgs& a, uint32_t tmem_a
     uint32_t r[32];
     ptx::tmem_ld_32x32b_x32(tmem_addr + c * 32, r);
     ptx::tmem_ld_wait();
-    if (vec_ok && col0 + 32 <= a.n) {
-      if (my_row < a.m) {
-        float* dst = a.out + (size_t)my_row * a.ldo + col0;
-        float red = 0.f;
+    if (vec_ok) {
+      float* sb = sbuf + box * 1024;
+      if (lane == 0) ptx::bulk_wait_read<1>();  // the store issued two boxes ago has finished reading this buffer
+      __syncwarp();
+      const bool full = col0 + 32 <= a.n;
+      float red = a.cred_max ? -INFINITY : INFINITY;
 #pragma unroll
-        for (int j = 0; j < 32; j += 4) {
-          float4 y4 = make_float4(0.f, 0.f, 0.f, 0.f);
+      for (int j = 0; j < 32; j += 4) {
+        float4 y4 = make_float4(0.f, 0.f, 0.f, 0.f), s4;
+        if (full) {
           if (KIND != REIDB200_DIST_DOT) y4 = __ldg(reinterpret_cast<const float4*>(a.yy + col0 + j));
-          const float4 s4 = __ldg(reinterpret_cast<const float4*>(a.isb + col0 + j));
-          float4 o;
-          o.x = dist_epilogue(KIND, __fmul_rn(__fmul_rn(__uint_as_float(r[j + 0]), ia_mine), s4.x), xx_mine, y4.x);
-          o.y = dist_epilogue(KIND, __fmul_rn(__fmul_rn(__uint_as_float(r[j + 1]), ia_mine), s4.y), xx_mine, y4.y);
-          o.z = dist_epilogue(KIND, __fmul_rn(__fmul_rn(__uint_as_float(r[j + 2]), ia_mine), s4.z), xx_mine, y4.z);
-          o.w = dist_epilogue(KIND, __fmul_rn(__fmul_rn(__uint_as_float(r[j + 3]), ia_mine), s4.w), xx_mine, y4.w);
-          __stcs(reinterpret_cast<float4*>(dst + j), o);
-          if (a.cred) {
+          s4 = __ldg(reinterpret_cast<const float4*>(a.isb + col0 + j));
+        } else {  // ragged last chunk: scalar, guarded loads (the store itself is clipped by the TMA engine)
+          float yv[4] = {0.f, 0.f, 0.f, 0.f}, sv[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+          for (int u = 0; u < 4; ++u)
+            if (col0 + j + u < a.n) {
+              if (KIND != REIDB200_DIST_DOT) yv[u] = __ldg(a.yy + col0 + j + u);
+              sv[u] = __ldg(a.isb + col0 + j + u);
+            }
+          y4 = make_float4(yv[0], yv[1], yv[2], yv[3]);
+          s4 = make_float4(sv[0], sv[1], sv[2], sv[3]);
+        }
+        float4 o;
+        o.x = dist_epilogue(KIND, __fmul_rn(__fmul_rn(__uint_as_float(r[j + 0]), ia_mine), s4.x), xx_mine, y4.x);
+        o.y = dist_epilogue(KIND, __fmul_rn(__fmul_rn(__uint_as_float(r[j + 1]), ia_mine), s4.y), xx_mine, y4.y);
+        o.z = dist_epilogue(KIND, __fmul_rn(__fmul_rn(__uint_as_float(r[j + 2]), ia_mine), s4.z), xx_mine, y4.z);
+        o.w = dist_epilogue(KIND, __fmul_rn(__fmul_rn(__uint_as_float(r[j + 3]), ia_mine), s4.w), xx_mine, y4.w);
+        *reinterpret_cast<float4*>(sb + lane * 32 + (((j >> 2) ^ (lane & 7)) << 2)) = o;
+        if (a.cred) {
+          if (full) {
             const float lo4 = fminf(fminf(o.x, o.y), fminf(o.z, o.w)), hi4 = fmaxf(fmaxf(o.x, o.y), fmaxf(o.z, o.w));
-            red = j == 0 ? (a.cred_max ? hi4 : lo4) : (a.cred_max ? fmaxf(red, hi4) : fminf(red, lo4));
+            red = a.cred_max ? fmaxf(red, hi4) : fminf(red, lo4);
+          } else {
+            const float ov[4] = {o.x, o.y, o.z, o.w};
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
+              if (col0 + j + u < a.n) red = a.cred_max ? fmaxf(red, ov[u]) : fminf(red, ov[u]);
           }
         }
-        if (a.cred) a.cred[(size_t)my_row * a.ldcr + (col0 >> 5)] = red;
       }
+      if (a.cred && my_row < a.m) a.cred[(size_t)my_row * a.ldcr + (col0 >> 5)] = red;
+      ptx::fence_proxy_async();
+      __syncwarp();
+      if (lane == 0) {
+        ptx::tma_store_2d(tmO, ptx::smem_u32(sb), col0, row0);
+        ptx::bulk_commit();
+      }
+      box ^= 1;
     } else {
-      if (a.cred && my_row < a.m) {  // ragged last chunk: reduce from the registers (thread = row) before the transpose
+      if (a.cred && my_row < a.m) {  // reduce from the registers (thread = row) before the transpose
         float red2 = a.cred_max ? -INFINITY : INFINITY;
-        for (int j = 0; j < 32 && col0 + j < a.n; ++j) {
-          const float yv = KIND != REIDB200_DIST_DOT ? __ldg(a.yy + col0 + j) : 0.f;
-          const float o = dist_epilogue(KIND, __fmul_rn(__fmul_rn(__uint_as_float(r[j]), ia_mine), __ldg(a.isb + col0 + j)), xx_mine, yv);
-          red2 = a.cred_max ? fmaxf(red2, o) : fminf(red2, o);
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {  // fully unrolled: r[] must stay in registers
+          if (col0 + j < a.n) {
+            const float yv = KIND != REIDB200_DIST_DOT ? __ldg(a.yy + col0 + j) : 0.f;
+            const float o = dist_epilogue(KIND, __fmul_rn(__fmul_rn(__uint_as_float(r[j]), ia_mine), __ldg(a.isb + col0 + j)), xx_mine, yv);
+            red2 = a.cred_max ? fmaxf(red2, o) : fminf(red2, o);
+          }
         }
         a.cred[(size_t)my_row * a.ldcr + (col0 >> 5)] = red2;
       }
@@ -183,7 +216,8 @@ __device__ __forceinline__ void epilogue_slab(const GemmArgs& a, uint32_t tmem_a
 
 template <int KIND>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
-gemm_split_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, GemmArgs a) {
+gemm_split_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                     const __grid_constant__ CUtensorMap tmO, GemmArgs a) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   float* epi_buf = reinterpret_cast<float*>(smem + (size_t)STAGES * STAGE_BYTES);
@@ -278,22 +312,22 @@ gemm_split_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
     // ===== epilogue warps: TMEM lane quadrant = warp % 4
     const int q = warp & 3;
     float* sbuf = epi_buf + (warp - 2) * EPI_STAGE_FLOATS;
-    const bool vec_ok = (a.ldo & 3) == 0 && (reinterpret_cast<uintptr_t>(a.out) & 15) == 0 &&
-                        (a.yy == nullptr || (reinterpret_cast<uintptr_t>(a.yy) & 15) == 0) &&
-                        (reinterpret_cast<uintptr_t>(a.isb) & 15) == 0;
-    int as = 0;
+    const bool vec_ok = a.tma_out != 0;
+    int as = 0, box = 0;
     uint32_t aphase = 0;
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
       const int tm = tile % a.tiles_m, tn = tile / a.tiles_m;
       ptx::mbar_wait(bar_tfull + 8 * as, aphase);
       ptx::tc_fence_after();
-      epilogue_slab<KIND>(a, tmem_base + ((uint32_t)(q * 32) << 16) + as * BN, tm * BM + q * 32, tn * BN, lane, sbuf, vec_ok);
+      epilogue_slab<KIND>(a, &tmO, tmem_base + ((uint32_t)(q * 32) << 16) + as * BN, tm * BM + q * 32, tn * BN, lane, sbuf,
+                          vec_ok, box);
       ptx::tc_fence_before();
       __syncwarp();
       if (lane == 0) ptx::mbar_arrive(bar_tempty + 8 * as);
       as ^= 1;
       if (as == 0) aphase ^= 1;
     }
+    if (lane == 0) ptx::bulk_wait<0>();  // every TMA store of this warp has been performed
   }
 
   ptx::tc_fence_before();
@@ -315,7 +349,8 @@ constexpr size_t GEMM2_SMEM = 1024 + (size_t)STAGES2 * STAGE2_BYTES + 4 * EPI_ST
 
 template <int KIND>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GEMM_THREADS, 1)
-gemm_split_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, GemmArgs a) {
+gemm_split_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                      const __grid_constant__ CUtensorMap tmO, GemmArgs a) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   float* epi_buf = reinterpret_cast<float*>(smem + (size_t)STAGES2 * STAGE2_BYTES);
@@ -416,23 +451,22 @@ gemm_split_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
     // ===== epilogue warps (both CTAs): own 128 rows of the 256-row tile
     const int q = warp & 3;
     float* sbuf = epi_buf + (warp - 2) * EPI_STAGE_FLOATS;
-    const bool vec_ok = (a.ldo & 3) == 0 && (reinterpret_cast<uintptr_t>(a.out) & 15) == 0 &&
-                        (a.yy == nullptr || (reinterpret_cast<uintptr_t>(a.yy) & 15) == 0) &&
-                        (reinterpret_cast<uintptr_t>(a.isb) & 15) == 0;
-    int as = 0;
+    const bool vec_ok = a.tma_out != 0;
+    int as = 0, box = 0;
     uint32_t aphase = 0;
     for (int tile = cluster_id; tile < total_tiles; tile += num_clusters) {
       const int tm = tile % tiles_m2, tn = tile / tiles_m2;
       ptx::mbar_wait(bar_tfull + 8 * as, aphase);
       ptx::tc_fence_after();
-      epilogue_slab<KIND>(a, tmem_base + ((uint32_t)(q * 32) << 16) + as * BN, tm * 2 * BM + (int)rank * BM + q * 32, tn * BN,
-                          lane, sbuf, vec_ok);
+      epilogue_slab<KIND>(a, &tmO, tmem_base + ((uint32_t)(q * 32) << 16) + as * BN, tm * 2 * BM + (int)rank * BM + q * 32,
+                          tn * BN, lane, sbuf, vec_ok, box);
       ptx::tc_fence_before();
       __syncwarp();
       if (lane == 0) ptx::mbar_arrive_leader(bar_tempty + 8 * as);
       as ^= 1;
       if (as == 0) aphase ^= 1;
     }
+    if (lane == 0) ptx::bulk_wait<0>();  // every TMA store of this warp has been performed
   }
 
   ptx::tc_fence_before();
@@ -507,6 +541,26 @@ int make_operand_map(CUtensorMap* tm, const void* packed, int rows, int dp, int 
   return REIDB200_OK;
 }
 
+// output matrix f32[m, n] with row stride ldo (elements): box = 32 x 32, SWIZZLE_128B (128-byte box rows)
+static int make_output_map(CUtensorMap* tm, float* out, int m, int n, int64_t ldo) {
+  EncodeTiledFn enc = get_encode_fn();
+  if (!enc) {
+    set_error("cuTensorMapEncodeTiled not available from the driver");
+    return REIDB200_ECUDA;
+  }
+  cuuint64_t gdim[2] = {(cuuint64_t)n, (cuuint64_t)m};
+  cuuint64_t gstride[1] = {(cuuint64_t)ldo * sizeof(float)};
+  cuuint32_t box[2] = {32, 32};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = enc(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, out, gdim, gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                   CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    set_error("cuTensorMapEncodeTiled (output) failed (%d) m=%d n=%d ldo=%lld", (int)r, m, n, (long long)ldo);
+    return REIDB200_ECUDA;
+  }
+  return REIDB200_OK;
+}
+
 int gemm_split_launch(const void* packedA, const float* xx, const float* isa, int m, const void* packedB, const float* yy,
                       const float* isb, int n, int d, int kind, float* out, int64_t ldo, cudaStream_t st, float* chunk_red,
                       int64_t ld_chunk_red, int chunk_red_max) {
@@ -526,8 +580,16 @@ int gemm_split_launch(const void* packedA, const float* xx, const float* isa, in
   a.tiles_m = ceil_div(m, BM); a.tiles_n = ceil_div(n, BN);
   a.kind = kind; a.xx = xx; a.yy = yy; a.isa = isa; a.isb = isb; a.out = out; a.ldo = ldo;
   a.cred = chunk_red; a.ldcr = ld_chunk_red; a.cred_max = chunk_red_max;
-  void (*k1)(CUtensorMap, CUtensorMap, GemmArgs) = nullptr;
-  void (*k2)(CUtensorMap, CUtensorMap, GemmArgs) = nullptr;
+  CUtensorMap tmO;
+  memset(&tmO, 0, sizeof(tmO));
+  a.tma_out = (ldo & 3) == 0 && (reinterpret_cast<uintptr_t>(out) & 15) == 0 &&
+              (yy == nullptr || (reinterpret_cast<uintptr_t>(yy) & 15) == 0) && (reinterpret_cast<uintptr_t>(isb) & 15) == 0;
+  if (a.tma_out) {
+    rc = make_output_map(&tmO, out, m, n, ldo);
+    if (rc) return rc;
+  }
+  void (*k1)(CUtensorMap, CUtensorMap, CUtensorMap, GemmArgs) = nullptr;
+  void (*k2)(CUtensorMap, CUtensorMap, CUtensorMap, GemmArgs) = nullptr;
   switch (kind) {
     case REIDB200_DIST_EUCLID: k1 = gemm_split_tc_kernel<REIDB200_DIST_EUCLID>; k2 = gemm_split_tc2_kernel<REIDB200_DIST_EUCLID>; break;
     case REIDB200_DIST_COSINE_HALF: k1 = gemm_split_tc_kernel<REIDB200_DIST_COSINE_HALF>; k2 = gemm_split_tc2_kernel<REIDB200_DIST_COSINE_HALF>; break;
@@ -544,13 +606,13 @@ int gemm_split_launch(const void* packedA, const float* xx, const float* isa, in
     const long long total2 = (long long)((a.tiles_m + 1) / 2) * a.tiles_n;
     const int max_clusters = num_sms() / 2;
     const int clusters = (int)(total2 < max_clusters ? total2 : max_clusters);
-    { ProfScope _ps("gemm_split_tc_kernel", st); k2<<<2 * clusters, GEMM_THREADS, GEMM2_SMEM, st>>>(tmA, tmB, a); }
+    { ProfScope _ps("gemm_split_tc_kernel", st); k2<<<2 * clusters, GEMM_THREADS, GEMM2_SMEM, st>>>(tmA, tmB, tmO, a); }
     RB_LAUNCH_CHECK("gemm_split_tc2_kernel");
     return REIDB200_OK;
   }
   const long long total = (long long)a.tiles_m * a.tiles_n;
   const int grid = (int)(total < num_sms() ? total : num_sms());
-  { ProfScope _ps("gemm_split_tc_kernel", st); k1<<<grid, GEMM_THREADS, GEMM_SMEM, st>>>(tmA, tmB, a); }
+  { ProfScope _ps("gemm_split_tc_kernel", st); k1<<<grid, GEMM_THREADS, GEMM_SMEM, st>>>(tmA, tmB, tmO, a); }
   RB_LAUNCH_CHECK("gemm_split_tc_kernel");
   return REIDB200_OK;
 }
