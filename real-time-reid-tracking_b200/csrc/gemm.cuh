@@ -28,9 +28,10 @@ int gemm_split_launch(const void* packedA, const float* xx, const float* isa, in
 int make_operand_map(CUtensorMap* tm, const void* packed, int rows, int dp, int box_rows);
 
 // row-wise exact top-k (topk.cu); out_i is i64 when idx64 else i32; ids = cand_i[col] or col + index_base
-// chunk_red (optional): the per-32-column reductions written by gemm_split_launch for this matrix.
+// chunk_red (optional): the per-32-column reductions written by gemm_split_launch for this matrix (consumed: rows the
+// warp-per-row selection hands to the exact kernel are flagged in it).
 int topk_rows_launch(const float* vals, int rows, int cols, int64_t ldv, const int64_t* cand_i, int k, int descending,
                      int64_t index_base, float* out_d, void* out_i, int idx64, cudaStream_t st,
-                     const float* chunk_red = nullptr, int64_t ld_chunk_red = 0);
+                     float* chunk_red = nullptr, int64_t ld_chunk_red = 0);
 
 }  // namespace reidb200

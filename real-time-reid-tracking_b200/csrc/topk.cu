@@ -19,7 +19,8 @@ namespace reidb200 {
 constexpr int TOPK_CAP = 2048;   // candidate capacity (key + column in shared memory)
 constexpr int TOPK_MAX_K = 1024;
 constexpr int TOPK_SMEM_ROW_MAX = 36 * 1024;  // columns whose keys are cached in shared memory (144 KB)
-constexpr int TOPK_CHUNK_MAX = 8192;          // 32-column chunks per row in the chunk-guided mode
+constexpr uint32_t TOPK_REDO_FLAG = 0x7fc0deadu;  // NaN payload written over a row's first chunk reduction: "redo this row"
+constexpr int TW_CAP = 512;                       // candidates per warp in the chunk-guided kernel
 
 __device__ __forceinline__ uint32_t sel_key(float v, int descending) {
   const uint32_t u = float_to_ordered(v);
@@ -60,20 +61,18 @@ __device__ __forceinline__ void cand_append(bool take, uint32_t key, int col, in
 
 // MODE 0: two passes over the row in global memory (second pass hits L2).
 // MODE 1: the ordered keys of the row are cached in dynamic shared memory by pass 1 (row read from HBM once).
-// MODE 2: chunk-guided: the producing GEMM already reduced every 32-column chunk (min / max); the threshold is the
-//         k-th best chunk reduction and only chunks that reach it (about k of them) are read at all.
+// (The chunk-guided selection over GEMM outputs is topk_chunk_warp_kernel below; rows it could not finish are flagged
+//  in their chunk-reduction row and redone here: `flag_rows` != null makes every other CTA exit at once.)
 template <int MODE, int NT>
-__global__ void __launch_bounds__(NT)
-topk_rows_kernel(const float* __restrict__ vals, int cols, int64_t ldv, const int64_t* __restrict__ cand_i, int k,
-                 int descending, int64_t index_base, float* __restrict__ out_d, void* __restrict__ out_i, int idx64,
-                 const float* __restrict__ chunk_red, int64_t ldcr) {
-  extern __shared__ __align__(16) uint32_t rowkey[];  // MODE 1: keys of the row; MODE 2: keys of the chunk reductions
+__device__ __forceinline__ void topk_row_body(const int row, const float* __restrict__ vals, int cols, int64_t ldv,
+                                              const int64_t* __restrict__ cand_i, int k, int descending, int64_t index_base,
+                                              float* __restrict__ out_d, void* __restrict__ out_i, int idx64) {
+  extern __shared__ __align__(16) uint32_t rowkey[];  // MODE 1: keys of the row
   __shared__ uint32_t ckey[TOPK_CAP];
   __shared__ int32_t ccol[TOPK_CAP];
   __shared__ int red[NT / 32];
   __shared__ int s_count;
 
-  const int row = blockIdx.x;
   const float* v = vals + (size_t)row * ldv;
   const int64_t* ci = cand_i ? cand_i + (size_t)row * cols : nullptr;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -82,35 +81,10 @@ topk_rows_kernel(const float* __restrict__ vals, int cols, int64_t ldv, const in
   const bool vec = (reinterpret_cast<uintptr_t>(v) & 15) == 0;
   const int ncol4 = vec ? (cols >> 2) : 0;
   const float4* v4 = reinterpret_cast<const float4*>(v);
-  const int nchunks = (cols + 31) >> 5;
   if (tid == 0) s_count = 0;
   uint32_t t0 = 0xffffffffu;
 
-  if (MODE == 2) {
-    // ---- threshold = kk-th smallest chunk reduction (an upper bound of the kk-th smallest element)
-    const float* cr = chunk_red + (size_t)row * ldcr;
-    for (int c = tid; c < nchunks; c += NT) rowkey[c] = sel_key(__ldg(cr + c), descending);
-    __syncthreads();
-    if (kk > 0 && nchunks >= kk) {
-      uint32_t lo = 0, hi = 0xffffffffu;
-      while (lo < hi) {
-        const uint32_t mid = lo + ((hi - lo) >> 1);
-        int c = 0;
-        for (int i = tid; i < nchunks; i += NT) c += rowkey[i] <= mid;
-        c = block_sum_int<NT>(c, red);
-        if (c >= kk) hi = mid; else lo = mid + 1;
-      }
-      t0 = lo;
-    }
-    __syncthreads();
-    // ---- read only the chunks that reach the threshold: one warp per 128-byte chunk
-    for (int c = warp; c < nchunks; c += NT / 32) {
-      if (rowkey[c] > t0) continue;  // warp-uniform
-      const int col = c * 32 + lane;
-      const uint32_t key = col < cols ? sel_key(__ldg(v + col), descending) : 0xffffffffu;
-      cand_append(col < cols && key <= t0, key, col, lane, &s_count, ckey, ccol);
-    }
-  } else {
+  {
     // ---- pass 1: group minima (128-bit loads when the row is 16-byte aligned)
     const int groups = (kk <= NT) ? NT : 2 * NT;
     const int per_thread = groups / NT;  // 1 or 2
@@ -262,31 +236,151 @@ topk_rows_kernel(const float* __restrict__ vals, int cols, int64_t ldv, const in
   }
 }
 
+
+template <int MODE, int NT>
+__global__ void __launch_bounds__(NT)
+topk_rows_kernel(const float* __restrict__ vals, int cols, int64_t ldv, const int64_t* __restrict__ cand_i, int k,
+                 int descending, int64_t index_base, float* __restrict__ out_d, void* __restrict__ out_i, int idx64) {
+  topk_row_body<MODE, NT>(blockIdx.x, vals, cols, ldv, cand_i, k, descending, index_base, out_d, out_i, idx64);
+}
+
+// Redo of the rows the chunk-guided kernel flagged (first chunk reduction overwritten with TOPK_REDO_FLAG): a small
+// persistent grid scans the flags; normally no row is flagged and the kernel ends after one pass over them.
+template <int NT>
+__global__ void __launch_bounds__(NT)
+topk_rows_redo_kernel(const float* __restrict__ vals, int rows, int cols, int64_t ldv, int k, int descending,
+                      int64_t index_base, float* __restrict__ out_d, void* __restrict__ out_i, int idx64,
+                      const float* __restrict__ flag_rows, int64_t ldcr) {
+  for (int row = blockIdx.x; row < rows; row += gridDim.x) {
+    if (__float_as_uint(__ldg(flag_rows + (size_t)row * ldcr)) != TOPK_REDO_FLAG) continue;  // CTA-uniform
+    topk_row_body<0, NT>(row, vals, cols, ldv, nullptr, k, descending, index_base, out_d, out_i, idx64);
+    __syncthreads();
+  }
+}
+
+// Chunk-guided selection, one WARP per row: the producing GEMM already reduced every 32-column chunk of the row (min, or
+// max for descending).  Lane-local minima of 32*S interleaved groups of chunk keys give, by a register-only bisection, an
+// upper bound t0 of the k-th smallest element (k distinct elements are <= the k-th smallest group minimum); only chunks
+// whose reduction reaches t0 (about k..2k of them) are read from the matrix, 128 bytes each, and their elements <= t0
+// become candidates (warp-ballot compaction, no atomics, no block barriers).  A rank sort of the candidates by
+// (key, column) emits the k best; ties -> lower column.  Rows with more than TW_CAP candidates (massive ties) are
+// flagged and redone by the exact CTA-per-row kernel.
+template <int S>
+__global__ void __launch_bounds__(128)
+topk_chunk_warp_kernel(const float* __restrict__ vals, int rows, int cols, int64_t ldv, int k, int descending,
+                       int64_t index_base, float* __restrict__ out_d, void* __restrict__ out_i, int idx64,
+                       float* __restrict__ chunk_red, int64_t ldcr) {
+  __shared__ uint32_t ckey[4][TW_CAP];
+  __shared__ int32_t ccol[4][TW_CAP];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int row = blockIdx.x * 4 + warp;
+  if (row >= rows) return;
+  const float* v = vals + (size_t)row * ldv;
+  float* cr = chunk_red + (size_t)row * ldcr;
+  const int nchunks = (cols + 31) >> 5;
+  const int kk = min(k, cols);
+
+  uint32_t m[S];
+#pragma unroll
+  for (int s = 0; s < S; ++s) m[s] = 0xffffffffu;
+  for (int c0 = 0; c0 < nchunks; c0 += 32 * S) {
+#pragma unroll
+    for (int s = 0; s < S; ++s) {
+      const int c = c0 + s * 32 + lane;
+      if (c < nchunks) m[s] = min(m[s], sel_key(__ldg(cr + c), descending));
+    }
+  }
+  uint32_t lo = 0, hi = 0xffffffffu;
+  while (lo < hi) {
+    const uint32_t mid = lo + ((hi - lo) >> 1);
+    int cnt = 0;
+#pragma unroll
+    for (int s = 0; s < S; ++s) cnt += m[s] <= mid;
+    cnt = __reduce_add_sync(0xffffffffu, cnt);
+    if (cnt >= kk) hi = mid; else lo = mid + 1;
+  }
+  const uint32_t t0 = lo;
+
+  int count = 0;
+  uint32_t* mk = ckey[warp];
+  int32_t* mc = ccol[warp];
+  for (int c0 = 0; c0 < nchunks; c0 += 32) {
+    const int c = c0 + lane;
+    const bool q = c < nchunks && sel_key(__ldg(cr + c), descending) <= t0;
+    uint32_t todo = __ballot_sync(0xffffffffu, q);
+    while (todo) {
+      const int b = __ffs(todo) - 1;
+      todo &= todo - 1;
+      const int col = (c0 + b) * 32 + lane;
+      const uint32_t key = col < cols ? sel_key(__ldg(v + col), descending) : 0xffffffffu;
+      const bool take = col < cols && key <= t0;
+      const uint32_t tb = __ballot_sync(0xffffffffu, take);
+      const int pos = count + __popc(tb & ((1u << lane) - 1));
+      if (take && pos < TW_CAP) { mk[pos] = key; mc[pos] = col; }
+      count += __popc(tb);
+    }
+  }
+  if (count > TW_CAP) {  // hand the row to the exact CTA-per-row kernel
+    if (lane == 0) cr[0] = __uint_as_float(TOPK_REDO_FLAG);
+    return;
+  }
+  __syncwarp();
+  float* od = out_d + (size_t)row * k;
+  for (int e = lane; e < count; e += 32) {
+    const uint32_t key = mk[e];
+    const int col = mc[e];
+    int rank = 0;
+    for (int o = 0; o < count; ++o) {
+      const uint32_t ok = mk[o];
+      rank += (ok < key) || (ok == key && mc[o] < col);
+    }
+    if (rank < kk) {
+      od[rank] = sel_val(key, descending);
+      const int64_t gid = (int64_t)col + index_base;
+      if (idx64) reinterpret_cast<int64_t*>(out_i)[(size_t)row * k + rank] = gid;
+      else reinterpret_cast<int32_t*>(out_i)[(size_t)row * k + rank] = (int32_t)gid;
+    }
+  }
+  for (int e = kk + lane; e < k; e += 32) {
+    od[e] = descending ? -INFINITY : INFINITY;
+    if (idx64) reinterpret_cast<int64_t*>(out_i)[(size_t)row * k + e] = -1;
+    else reinterpret_cast<int32_t*>(out_i)[(size_t)row * k + e] = -1;
+  }
+}
+
 int topk_rows_launch(const float* vals, int rows, int cols, int64_t ldv, const int64_t* cand_i, int k, int descending,
-                     int64_t index_base, float* out_d, void* out_i, int idx64, cudaStream_t st, const float* chunk_red,
+                     int64_t index_base, float* out_d, void* out_i, int idx64, cudaStream_t st, float* chunk_red,
                      int64_t ld_chunk_red) {
   if (rows == 0 || k == 0) return REIDB200_OK;
   RB_REQUIRE(k > 0 && k <= TOPK_MAX_K, "topk: k=%d outside [1,%d]", k, TOPK_MAX_K);
   RB_REQUIRE(cols >= 0 && ldv >= cols, "topk: bad cols/ld");
   const int nchunks = (cols + 31) / 32;
-  if (chunk_red != nullptr && nchunks >= 4 * k && nchunks <= TOPK_CHUNK_MAX) {
-    ProfScope _ps("topk_rows_kernel", st);
-    topk_rows_kernel<2, 128><<<rows, 128, align_up((size_t)nchunks * 4, 16), st>>>(
-        vals, cols, ldv, cand_i, k, descending, index_base, out_d, out_i, idx64, chunk_red, ld_chunk_red);
-  } else if (cols <= TOPK_SMEM_ROW_MAX) {
-    static bool attr = false;
-    if (!attr) {
-      RB_CUDA(cudaFuncSetAttribute(topk_rows_kernel<1, 512>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                   TOPK_SMEM_ROW_MAX * 4));
-      attr = true;
+  static bool attr = false;
+  if (!attr) {
+    RB_CUDA(cudaFuncSetAttribute(topk_rows_kernel<1, 512>, cudaFuncAttributeMaxDynamicSharedMemorySize, TOPK_SMEM_ROW_MAX * 4));
+    attr = true;
+  }
+  if (chunk_red != nullptr && cand_i == nullptr && nchunks >= 4 * k && nchunks >= 64 && k <= 128) {
+    // groups = 32*S >= 2k lane-local minima (S = 2, 4 or 8)
+    const int grid = ceil_div(rows, 4);
+    {
+      ProfScope _ps("topk_rows_kernel", st);
+      if (k <= 32) topk_chunk_warp_kernel<2><<<grid, 128, 0, st>>>(vals, rows, cols, ldv, k, descending, index_base, out_d, out_i, idx64, chunk_red, ld_chunk_red);
+      else if (k <= 64) topk_chunk_warp_kernel<4><<<grid, 128, 0, st>>>(vals, rows, cols, ldv, k, descending, index_base, out_d, out_i, idx64, chunk_red, ld_chunk_red);
+      else topk_chunk_warp_kernel<8><<<grid, 128, 0, st>>>(vals, rows, cols, ldv, k, descending, index_base, out_d, out_i, idx64, chunk_red, ld_chunk_red);
     }
+    RB_LAUNCH_CHECK("topk_chunk_warp_kernel");
+    // rows the warp kernel flagged (candidate overflow: massive ties) are redone exactly
+    ProfScope _ps2("topk_rows_redo_kernel", st);
+    topk_rows_redo_kernel<512><<<min(rows, 2 * num_sms()), 512, 0, st>>>(vals, rows, cols, ldv, k, descending, index_base, out_d,
+                                                                       out_i, idx64, chunk_red, ld_chunk_red);
+  } else if (cols <= TOPK_SMEM_ROW_MAX) {
     ProfScope _ps("topk_rows_kernel", st);
     topk_rows_kernel<1, 512><<<rows, 512, align_up((size_t)cols * 4, 16), st>>>(vals, cols, ldv, cand_i, k, descending,
-                                                                                index_base, out_d, out_i, idx64, nullptr, 0);
+                                                                                index_base, out_d, out_i, idx64);
   } else {
     ProfScope _ps("topk_rows_kernel", st);
-    topk_rows_kernel<0, 512><<<rows, 512, 0, st>>>(vals, cols, ldv, cand_i, k, descending, index_base, out_d, out_i, idx64,
-                                                  nullptr, 0);
+    topk_rows_kernel<0, 512><<<rows, 512, 0, st>>>(vals, cols, ldv, cand_i, k, descending, index_base, out_d, out_i, idx64);
   }
   RB_LAUNCH_CHECK("topk_rows_kernel");
   return REIDB200_OK;

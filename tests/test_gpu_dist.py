@@ -124,6 +124,29 @@ def test_knn_vs_oracle(rb, nq, nb, d, k):
     assert (np.diff(D, axis=1) >= 0).all()
 
 
+def test_knn_chunk_guided_overflow_redo(rb):
+    """Thousands of exact ties overflow the warp kernel's candidate buffer: those rows are redone by the exact kernel and
+    still come out lowest-index first; ordinary rows of the same launch are unaffected."""
+    from reidb200 import ops
+
+    rng = np.random.default_rng(12)
+    nb, d, k = 8000, 64, 10
+    xb = _unit(rng.standard_normal((nb, d)))
+    xb[1000:4000] = xb[1000]
+    xq = _unit(rng.standard_normal((6, d)))
+    xq[0] = xb[1000]
+    xq[3] = xb[2500]
+    for metric in ("sql2", "dot"):
+        D, I = ops.knn(xq, xb, k, metric)
+        D, I = D.cpu().numpy(), I.cpu().numpy()
+        assert np.array_equal(I[0], np.arange(1000, 1000 + k)) and np.array_equal(I[3], np.arange(1000, 1000 + k))
+        full = O.sql2_dist(xq, xb) if metric == "sql2" else -(xq @ xb.T)
+        Io = np.argsort(full, axis=1, kind="stable")[:, :k]
+        bad = I != Io
+        r, c = np.where(bad)
+        assert np.allclose(full[r, I[r, c]], full[r, Io[r, c]], rtol=REL, atol=2e-5)
+
+
 def test_knn_golden_rank(rb, golden):
     from reidb200 import ops
 
