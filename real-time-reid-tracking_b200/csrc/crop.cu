@@ -15,11 +15,10 @@ namespace reidb200 {
 // the oracle's (oracle/reid_oracle.py resize_linear_cv): horizontal lerp of the two source rows,
 // then vertical lerp, no FMA contraction, so results are bit-identical to the numpy restatement
 // (which is itself within 1 ulp of cv2).
-constexpr int CV_ROWS = 8;
-constexpr int CV_STAGE_FLOATS = 8 * 1024;   // 32 KB of staged source rows per CTA
+constexpr int CV_TILE_ROWS = 32;  // output rows per CTA (one thread walks one output column down the tile)
 
 // u8 / 255.0f correctly rounded without the IEEE division sequence: one Newton correction with an exact fma residual
-// (equal to __fdiv_rn((float)u, 255.0f) for all 256 inputs; checked exhaustively by tests/test_gpu_crop.py).
+// (equal to __fdiv_rn((float)u, 255.0f) for all 256 inputs: every byte value occurs in tests/test_gpu_crop.py).
 __device__ __forceinline__ float u8_over_255(uint32_t u) {
   const float c = 1.0f / 255.0f;
   const float f = (float)u;
@@ -28,103 +27,87 @@ __device__ __forceinline__ float u8_over_255(uint32_t u) {
   return __fmaf_rn(r, c, q);
 }
 
-struct CvNorm { float m[3], s[3], inv[3]; int pow2[3]; };
+struct CvNorm { float m[3], s[3], inv[3]; };
 
+// (v - mean) / std; POW2: every std is a power of two, x / 2^k == x * 2^-k exactly
+template <bool POW2>
 __device__ __forceinline__ float cv_norm(const CvNorm& n, int c, float v) {
   const float d = __fsub_rn(v, n.m[c]);
-  return n.pow2[c] ? __fmul_rn(d, n.inv[c]) : __fdiv_rn(d, n.s[c]);  // x / 2^k == x * 2^-k exactly
+  return POW2 ? __fmul_rn(d, n.inv[c]) : __fdiv_rn(d, n.s[c]);
 }
 
-// CTA = (crop, CV_ROWS output rows), thread = output column.  The source rows the tile touches are staged ONCE into
-// shared memory as float(u8)/255 (aligned 32-bit global loads), so every source byte is converted once per tile instead
-// of once per tap; tiles whose source footprint exceeds the staging buffer read their taps straight from global memory.
+struct CvRow { int sy0, sy1; float b0, b1; };  // the two source rows of an output row + vertical weights
+
+// horizontal lerp of one source row at this thread's column taps (the oracle's first step, same operation order)
+__device__ __forceinline__ float3 cv_hrow(const uint8_t* __restrict__ row, int i0, int i1, float a0, float a1) {
+  float3 hv;
+  hv.x = __fadd_rn(__fmul_rn(u8_over_255(__ldg(row + i0)), a0), __fmul_rn(u8_over_255(__ldg(row + i1)), a1));
+  hv.y = __fadd_rn(__fmul_rn(u8_over_255(__ldg(row + i0 + 1)), a0), __fmul_rn(u8_over_255(__ldg(row + i1 + 1)), a1));
+  hv.z = __fadd_rn(__fmul_rn(u8_over_255(__ldg(row + i0 + 2)), a0), __fmul_rn(u8_over_255(__ldg(row + i1 + 2)), a1));
+  return hv;
+}
+
+// CTA = (crop, 32 output rows), thread = output column walking down the tile.  No shared-memory staging and no barriers
+// in the loop: a thread keeps the horizontally interpolated values of the last two source rows in registers, so when
+// consecutive output rows share a source row (always when the crop is not shrunk vertically) that row is fetched,
+// converted and interpolated once.  Source bytes come through L1 (a warp touches ~100 contiguous bytes per row).
+template <bool POW2>
 __global__ void __launch_bounds__(128)
 crop_cv_linear_kernel(const uint8_t* __restrict__ src, const int64_t* __restrict__ crop_off,
                       const int32_t* __restrict__ crop_geom, int out_h, int out_w, CvNorm nrm, float* __restrict__ out) {
-  extern __shared__ float staged[];
-  __shared__ int s_sy0[CV_ROWS], s_sy1[CV_ROWS];
-  __shared__ float s_b0[CV_ROWS], s_b1[CV_ROWS];
+  __shared__ CvRow s_row[CV_TILE_ROWS];
   const int crop = blockIdx.y;
-  const int y_base = blockIdx.x * CV_ROWS;
+  const int y_base = blockIdx.x * CV_TILE_ROWS;
   const int h = crop_geom[crop * 3 + 0], w = crop_geom[crop * 3 + 1], stride = crop_geom[crop * 3 + 2];
   const uint8_t* base = src + crop_off[crop];
-  const double scale_x = 1.0 / ((double)out_w / (double)w);
-  const double scale_y = 1.0 / ((double)out_h / (double)h);
-  float* o = out + (size_t)crop * 3 * out_h * out_w;
-  const int rows_here = min(CV_ROWS, out_h - y_base);
-
-  if (threadIdx.x < CV_ROWS) {
-    const int y = min(y_base + (int)threadIdx.x, out_h - 1);
+  const int rows_here = min(CV_TILE_ROWS, out_h - y_base);
+  if (threadIdx.x < rows_here) {
+    const double scale_y = 1.0 / ((double)out_h / (double)h);
+    const int y = y_base + threadIdx.x;
     float fy = (float)(((double)y + 0.5) * scale_y - 0.5);
     const int sy = (int)floorf(fy);
     fy = __fsub_rn(fy, (float)sy);
-    s_sy0[threadIdx.x] = min(max(sy, 0), h - 1);
-    s_sy1[threadIdx.x] = min(max(sy + 1, 0), h - 1);
-    s_b1[threadIdx.x] = fy;
-    s_b0[threadIdx.x] = __fsub_rn(1.0f, fy);
+    CvRow rw;
+    rw.sy0 = min(max(sy, 0), h - 1);
+    rw.sy1 = min(max(sy + 1, 0), h - 1);
+    rw.b1 = fy;
+    rw.b0 = __fsub_rn(1.0f, fy);
+    s_row[threadIdx.x] = rw;
   }
   __syncthreads();
-  const int first = s_sy0[0], last = s_sy1[rows_here - 1];
-  const int nrows = last - first + 1, w3 = w * 3;
-  const bool use_stage = (long long)nrows * w3 <= CV_STAGE_FLOATS;
-  if (use_stage) {
-    for (int r = 0; r < nrows; ++r) {
-      const uint8_t* row = base + (size_t)(first + r) * stride;
-      const int mis = (int)(reinterpret_cast<uintptr_t>(row) & 3);
-      const uint32_t* row4 = reinterpret_cast<const uint32_t*>(row - mis);
-      float* dst = staged + r * w3 - mis;
-      const int nwords = (mis + w3 + 3) >> 2;
-      for (int i = threadIdx.x; i < nwords; i += blockDim.x) {
-        const uint32_t v = __ldg(row4 + i);
-        const int k = i * 4;
-#pragma unroll
-        for (int b = 0; b < 4; ++b)
-          if (k + b >= mis && k + b < mis + w3) dst[k + b] = u8_over_255((v >> (8 * b)) & 0xffu);
-      }
-    }
-    __syncthreads();
-  }
+  const double scale_x = 1.0 / ((double)out_w / (double)w);
+  const size_t plane = (size_t)out_h * out_w;
+  float* o = out + (size_t)crop * 3 * plane + (size_t)y_base * out_w;
 
   for (int x = threadIdx.x; x < out_w; x += blockDim.x) {
     float fx = (float)(((double)x + 0.5) * scale_x - 0.5);
     int sx = (int)floorf(fx);
     fx = __fsub_rn(fx, (float)sx);
-    int sx0, sx1;
+    int sx0;
     if (sx < 0) { sx0 = 0; fx = 0.f; }
     else if (sx >= w - 1) { sx0 = w - 1; fx = 0.f; }
     else sx0 = sx;
-    sx1 = min(sx0 + 1, w - 1);
+    const int i0 = sx0 * 3, i1 = min(sx0 + 1, w - 1) * 3;
     const float a1 = fx, a0 = __fsub_rn(1.0f, fx);
-#pragma unroll 2
+    int idA = -1, idB = -1;
+    float3 hA = make_float3(0.f, 0.f, 0.f), hB = hA;
+    float* op = o + x;
+#pragma unroll 4
     for (int r = 0; r < rows_here; ++r) {
-      const int y = y_base + r;
-      const int sy0 = s_sy0[r], sy1 = s_sy1[r];
-      const float b0 = s_b0[r], b1 = s_b1[r];
-      float p[3][4];
-      if (use_stage) {
-        const float* r0 = staged + (sy0 - first) * w3;
-        const float* r1 = staged + (sy1 - first) * w3;
-#pragma unroll
-        for (int c = 0; c < 3; ++c) {
-          p[c][0] = r0[sx0 * 3 + c]; p[c][1] = r0[sx1 * 3 + c];
-          p[c][2] = r1[sx0 * 3 + c]; p[c][3] = r1[sx1 * 3 + c];
-        }
-      } else {
-        const uint8_t* r0 = base + (size_t)sy0 * stride;
-        const uint8_t* r1 = base + (size_t)sy1 * stride;
-#pragma unroll
-        for (int c = 0; c < 3; ++c) {
-          p[c][0] = u8_over_255(__ldg(r0 + sx0 * 3 + c)); p[c][1] = u8_over_255(__ldg(r0 + sx1 * 3 + c));
-          p[c][2] = u8_over_255(__ldg(r1 + sx0 * 3 + c)); p[c][3] = u8_over_255(__ldg(r1 + sx1 * 3 + c));
-        }
-      }
-#pragma unroll
-      for (int c = 0; c < 3; ++c) {
-        const float h0 = __fadd_rn(__fmul_rn(p[c][0], a0), __fmul_rn(p[c][1], a1));
-        const float h1 = __fadd_rn(__fmul_rn(p[c][2], a0), __fmul_rn(p[c][3], a1));
-        const float v = __fadd_rn(__fmul_rn(h0, b0), __fmul_rn(h1, b1));
-        __stcs(o + ((size_t)c * out_h + y) * out_w + x, cv_norm(nrm, c, v));
-      }
+      const CvRow rw = s_row[r];
+      float3 h0, h1;  // all conditions are warp-uniform (they depend on the row only)
+      if (rw.sy0 == idA) h0 = hA;
+      else if (rw.sy0 == idB) h0 = hB;
+      else h0 = cv_hrow(base + (size_t)rw.sy0 * stride, i0, i1, a0, a1);
+      if (rw.sy1 == rw.sy0) h1 = h0;
+      else if (rw.sy1 == idB) h1 = hB;
+      else if (rw.sy1 == idA) h1 = hA;
+      else h1 = cv_hrow(base + (size_t)rw.sy1 * stride, i0, i1, a0, a1);
+      idA = rw.sy0; hA = h0; idB = rw.sy1; hB = h1;
+      __stcs(op, cv_norm<POW2>(nrm, 0, __fadd_rn(__fmul_rn(h0.x, rw.b0), __fmul_rn(h1.x, rw.b1))));
+      __stcs(op + plane, cv_norm<POW2>(nrm, 1, __fadd_rn(__fmul_rn(h0.y, rw.b0), __fmul_rn(h1.y, rw.b1))));
+      __stcs(op + 2 * plane, cv_norm<POW2>(nrm, 2, __fadd_rn(__fmul_rn(h0.z, rw.b0), __fmul_rn(h1.z, rw.b1))));
+      op += out_w;
     }
   }
 }
@@ -303,21 +286,22 @@ extern "C" int reidb200_crop_resize_norm_ws(const uint8_t* src, const int64_t* c
   RB_REQUIRE(M > 0 && out_h > 0 && out_w > 0, "crop_resize_norm: bad shape M=%d out=%dx%d", M, out_h, out_w);
   cudaStream_t st = (cudaStream_t)stream;
   if (mode == REIDB200_RESIZE_CV_LINEAR) {
-    dim3 grid(ceil_div(out_h, CV_ROWS), M);
+    dim3 grid(ceil_div(out_h, CV_TILE_ROWS), M);
     CvNorm nrm;
+    bool pow2 = true;
     for (int c = 0; c < 3; ++c) {
       int ex = 0;
       nrm.m[c] = mean_host[c];
       nrm.s[c] = std_host[c];
-      nrm.pow2[c] = (frexpf(std_host[c], &ex) == 0.5f && ex > -100 && ex < 100) ? 1 : 0;  // std = 2^k: exact reciprocal
-      nrm.inv[c] = nrm.pow2[c] ? 1.0f / std_host[c] : 0.f;
+      const bool p2 = frexpf(std_host[c], &ex) == 0.5f && ex > -100 && ex < 100;  // std = 2^k: exact reciprocal
+      nrm.inv[c] = p2 ? 1.0f / std_host[c] : 0.f;
+      pow2 = pow2 && p2;
     }
-    static bool attr_done = false;
-    if (!attr_done) {
-      RB_CUDA(cudaFuncSetAttribute(crop_cv_linear_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, CV_STAGE_FLOATS * 4));
-      attr_done = true;
+    {
+      ProfScope _ps("crop_cv_linear_kernel", st);
+      if (pow2) crop_cv_linear_kernel<true><<<grid, 128, 0, st>>>(src, crop_off, crop_geom, out_h, out_w, nrm, out);
+      else crop_cv_linear_kernel<false><<<grid, 128, 0, st>>>(src, crop_off, crop_geom, out_h, out_w, nrm, out);
     }
-    { ProfScope _ps("crop_cv_linear_kernel", st); crop_cv_linear_kernel<<<grid, 128, CV_STAGE_FLOATS * 4, st>>>(src, crop_off, crop_geom, out_h, out_w, nrm, out); }
     RB_LAUNCH_CHECK("crop_cv_linear_kernel");
     return REIDB200_OK;
   }
