@@ -92,6 +92,11 @@ crop_cv_linear_kernel(const uint8_t* __restrict__ src, const int64_t* __restrict
     int idA = -1, idB = -1;
     float3 hA = make_float3(0.f, 0.f, 0.f), hB = hA;
     float* op = o + x;
+    // pull every source line this column will touch into L1 up front (independent requests: full memory parallelism);
+    // the dependent load -> convert -> lerp chains of the loop below then run at L1 latency
+    asm volatile("prefetch.global.L1 [%0];" ::"l"(base + (size_t)s_row[0].sy0 * stride + i0));
+    for (int r = 0; r < rows_here; ++r)
+      asm volatile("prefetch.global.L1 [%0];" ::"l"(base + (size_t)s_row[r].sy1 * stride + i1 + 2));
 #pragma unroll 4
     for (int r = 0; r < rows_here; ++r) {
       const CvRow rw = s_row[r];
