@@ -110,7 +110,36 @@ struct GemmArgs {
   int64_t ldcr;
   int cred_max;
   int tma_out;  // the output tensor map is valid (16-byte aligned rows): epilogue stores through the TMA engine
+  int symmetric;  // A == B (self distances): only tiles with tn >= tm are computed, each also stored transposed
 };
+
+// tile index -> (tm, tn) of the CTA-pair kernel.  Symmetric mode enumerates the upper triangle column by column:
+// tile = tn (tn + 1) / 2 + tm, tm <= tn.
+__device__ __forceinline__ void pair_tile_coords(int tile, int tiles_m2, int symmetric, int& tm, int& tn) {
+  if (!symmetric) { tm = tile % tiles_m2; tn = tile / tiles_m2; return; }
+  int b = (int)((sqrtf(8.0f * (float)tile + 1.0f) - 1.0f) * 0.5f);
+  while ((b + 1) * (b + 2) / 2 <= tile) ++b;
+  while (b * (b + 1) / 2 > tile) --b;
+  tn = b;
+  tm = tile - b * (b + 1) / 2;
+}
+
+// v[j] = value of column j in this lane's row -> reduction (min, or max) over the 32 lanes (rows) of column `lane`
+template <bool MAX>
+__device__ __forceinline__ float colred_transpose(float (&v)[32], int lane) {
+#pragma unroll
+  for (int off = 16; off >= 1; off >>= 1) {
+    const bool up = (lane & off) != 0;
+#pragma unroll
+    for (int i = 0; i < off; ++i) {
+      const float send = up ? v[i] : v[i + off];
+      const float keep = up ? v[i + off] : v[i];
+      const float got = __shfl_xor_sync(0xffffffffu, send, off);
+      v[i] = MAX ? fmaxf(keep, got) : fminf(keep, got);
+    }
+  }
+  return v[0];
+}
 
 
 // Epilogue of one 32-row x 256-column accumulator slab owned by one warp (TMEM lane quadrant q): thread = row.
@@ -120,7 +149,8 @@ struct GemmArgs {
 // transpose through a padded shared-memory tile and store row-contiguous scalars.
 template <int KIND>
 __device__ __forceinline__ void epilogue_slab(const GemmArgs& a, const CUtensorMap* tmO, uint32_t tmem_addr, int row0,
-                                              int col_base, int lane, float* sbuf, bool vec_ok, int& box) {
+                                              int col_base, int lane, float* sbuf, bool vec_ok, int& box,
+                                              bool sym_t = false) {
   const int my_row = row0 + lane;
   const float xx_mine = (KIND != REIDB200_DIST_DOT && my_row < a.m) ? __ldg(a.xx + my_row) : 0.f;
   const float ia_mine = my_row < a.m ? __ldg(a.isa + my_row) : 0.f;
@@ -162,6 +192,10 @@ __device__ __forceinline__ void epilogue_slab(const GemmArgs& a, const CUtensorM
         o.z = dist_epilogue(KIND, __fmul_rn(__fmul_rn(__uint_as_float(r[j + 2]), ia_mine), s4.z), xx_mine, y4.z);
         o.w = dist_epilogue(KIND, __fmul_rn(__fmul_rn(__uint_as_float(r[j + 3]), ia_mine), s4.w), xx_mine, y4.w);
         *reinterpret_cast<float4*>(sb + lane * 32 + (((j >> 2) ^ (lane & 7)) << 2)) = o;
+        if (sym_t) {  // keep the outputs: the block is stored a second time, transposed
+          r[j + 0] = __float_as_uint(o.x); r[j + 1] = __float_as_uint(o.y);
+          r[j + 2] = __float_as_uint(o.z); r[j + 3] = __float_as_uint(o.w);
+        }
         if (a.cred) {
           if (full) {
             const float lo4 = fminf(fminf(o.x, o.y), fminf(o.z, o.w)), hi4 = fmaxf(fmaxf(o.x, o.y), fmaxf(o.z, o.w));
@@ -182,6 +216,30 @@ __device__ __forceinline__ void epilogue_slab(const GemmArgs& a, const CUtensorM
         ptx::bulk_commit();
       }
       box ^= 1;
+      if (sym_t) {
+        // mirror block out[col0 + j, row0 + lane]: box row j = this block's column j (lanes write 32 consecutive floats
+        // of a box row: conflict-free), clipped by the TMA engine like the direct one
+        float* st = sbuf + box * 1024;
+        if (lane == 0) ptx::bulk_wait_read<1>();
+        __syncwarp();
+#pragma unroll
+        for (int j = 0; j < 32; ++j) st[j * 32 + ((((lane >> 2) ^ (j & 7)) << 2) | (lane & 3))] = __uint_as_float(r[j]);
+        if (a.cred) {  // chunk reduction of the mirror rows: over this warp's 32 rows, per column
+          float v[32];
+          const float pad = a.cred_max ? -INFINITY : INFINITY;
+#pragma unroll
+          for (int j = 0; j < 32; ++j) v[j] = my_row < a.m ? __uint_as_float(r[j]) : pad;
+          const float red_t = a.cred_max ? colred_transpose<true>(v, lane) : colred_transpose<false>(v, lane);
+          if (col0 + lane < a.n) a.cred[(size_t)(col0 + lane) * a.ldcr + (row0 >> 5)] = red_t;
+        }
+        ptx::fence_proxy_async();
+        __syncwarp();
+        if (lane == 0) {
+          ptx::tma_store_2d(tmO, ptx::smem_u32(st), row0, col0);
+          ptx::bulk_commit();
+        }
+        box ^= 1;
+      }
     } else {
       if (a.cred && my_row < a.m) {  // reduce from the registers (thread = row) before the transpose
         float red2 = a.cred_max ? -INFINITY : INFINITY;
@@ -390,7 +448,7 @@ gemm_split_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
   ptx::tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
   const int tiles_m2 = (a.tiles_m + 1) / 2;
-  const int total_tiles = tiles_m2 * a.tiles_n;
+  const int total_tiles = a.symmetric ? tiles_m2 * (tiles_m2 + 1) / 2 : tiles_m2 * a.tiles_n;
   const int cluster_id = blockIdx.x >> 1, num_clusters = gridDim.x >> 1;
 
   if (warp == 0) {
@@ -399,7 +457,8 @@ gemm_split_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
       int stage = 0;
       uint32_t phase = 0;
       for (int tile = cluster_id; tile < total_tiles; tile += num_clusters) {
-        const int tm = tile % tiles_m2, tn = tile / tiles_m2;
+        int tm, tn;
+        pair_tile_coords(tile, tiles_m2, a.symmetric, tm, tn);
         const int arow = tm * 2 * BM + (int)rank * BM;
         const int brow = tn * BN + (int)rank * (BN / 2);
         for (int kb = 0; kb < a.num_kb; ++kb) {
@@ -455,11 +514,12 @@ gemm_split_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
     int as = 0, box = 0;
     uint32_t aphase = 0;
     for (int tile = cluster_id; tile < total_tiles; tile += num_clusters) {
-      const int tm = tile % tiles_m2, tn = tile / tiles_m2;
+      int tm, tn;
+      pair_tile_coords(tile, tiles_m2, a.symmetric, tm, tn);
       ptx::mbar_wait(bar_tfull + 8 * as, aphase);
       ptx::tc_fence_after();
       epilogue_slab<KIND>(a, &tmO, tmem_base + ((uint32_t)(q * 32) << 16) + as * BN, tm * 2 * BM + (int)rank * BM + q * 32,
-                          tn * BN, lane, sbuf, vec_ok, box);
+                          tn * BN, lane, sbuf, vec_ok, box, a.symmetric && tn != tm);
       ptx::tc_fence_before();
       __syncwarp();
       if (lane == 0) ptx::mbar_arrive_leader(bar_tempty + 8 * as);
@@ -588,6 +648,8 @@ int gemm_split_launch(const void* packedA, const float* xx, const float* isa, in
     rc = make_output_map(&tmO, out, m, n, ldo);
     if (rc) return rc;
   }
+  // self distances: compute the upper triangle of 256 x 256 tiles only and store every off-diagonal tile twice
+  a.symmetric = pair && a.tma_out && packedA == packedB && m == n && xx == yy && isa == isb && !getenv("REIDB200_GEMM_NOSYM");
   void (*k1)(CUtensorMap, CUtensorMap, CUtensorMap, GemmArgs) = nullptr;
   void (*k2)(CUtensorMap, CUtensorMap, CUtensorMap, GemmArgs) = nullptr;
   switch (kind) {
@@ -603,7 +665,8 @@ int gemm_split_launch(const void* packedA, const float* xx, const float* isa, in
     attr_done[pair ? 1 : 0][kind] = true;
   }
   if (pair) {
-    const long long total2 = (long long)((a.tiles_m + 1) / 2) * a.tiles_n;
+    const long long tm2 = (a.tiles_m + 1) / 2;
+    const long long total2 = a.symmetric ? tm2 * (tm2 + 1) / 2 : tm2 * a.tiles_n;
     const int max_clusters = num_sms() / 2;
     const int clusters = (int)(total2 < max_clusters ? total2 : max_clusters);
     { ProfScope _ps("gemm_split_tc_kernel", st); k2<<<2 * clusters, GEMM_THREADS, GEMM2_SMEM, st>>>(tmA, tmB, tmO, a); }

@@ -251,10 +251,20 @@ __global__ void __launch_bounds__(NT)
 topk_rows_redo_kernel(const float* __restrict__ vals, int rows, int cols, int64_t ldv, int k, int descending,
                       int64_t index_base, float* __restrict__ out_d, void* __restrict__ out_i, int idx64,
                       const float* __restrict__ flag_rows, int64_t ldcr) {
-  for (int row = blockIdx.x; row < rows; row += gridDim.x) {
-    if (__float_as_uint(__ldg(flag_rows + (size_t)row * ldcr)) != TOPK_REDO_FLAG) continue;  // CTA-uniform
-    topk_row_body<0, NT>(row, vals, cols, ldv, nullptr, k, descending, index_base, out_d, out_i, idx64);
+  // every thread checks one row per pass (a contiguous block of NT rows per CTA); flagged rows are queued in shared memory
+  __shared__ int todo[NT];
+  __shared__ int ntodo;
+  for (int base = blockIdx.x * NT; base < rows; base += gridDim.x * NT) {
+    if (threadIdx.x == 0) ntodo = 0;
     __syncthreads();
+    const int row = base + threadIdx.x;
+    if (row < rows && __float_as_uint(__ldg(flag_rows + (size_t)row * ldcr)) == TOPK_REDO_FLAG) todo[atomicAdd(&ntodo, 1)] = row;
+    __syncthreads();
+    const int n = ntodo;
+    for (int i = 0; i < n; ++i) {
+      topk_row_body<0, NT>(todo[i], vals, cols, ldv, nullptr, k, descending, index_base, out_d, out_i, idx64);
+      __syncthreads();
+    }
   }
 }
 
@@ -372,7 +382,7 @@ int topk_rows_launch(const float* vals, int rows, int cols, int64_t ldv, const i
     RB_LAUNCH_CHECK("topk_chunk_warp_kernel");
     // rows the warp kernel flagged (candidate overflow: massive ties) are redone exactly
     ProfScope _ps2("topk_rows_redo_kernel", st);
-    topk_rows_redo_kernel<512><<<min(rows, 2 * num_sms()), 512, 0, st>>>(vals, rows, cols, ldv, k, descending, index_base, out_d,
+    topk_rows_redo_kernel<512><<<min(ceil_div(rows, 512), 2 * num_sms()), 512, 0, st>>>(vals, rows, cols, ldv, k, descending, index_base, out_d,
                                                                        out_i, idx64, chunk_red, ld_chunk_red);
   } else if (cols <= TOPK_SMEM_ROW_MAX) {
     ProfScope _ps("topk_rows_kernel", st);

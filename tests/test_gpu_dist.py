@@ -89,6 +89,42 @@ def test_distmat_accuracy_is_fp32_class(rb):
     assert np.array_equal(ops.distmat(z, y[:5], "dot").cpu().numpy(), np.zeros((3, 5), np.float32))
 
 
+@pytest.mark.parametrize("n,d", [(700, 64), (1100, 512), (257, 100)])
+def test_self_distance_symmetric_mode(rb, n, d, monkeypatch):
+    """x vs x: only the upper triangle of 256x256 tiles is computed, off-diagonal tiles are stored twice (mirror through a
+    transposed shared-memory box).  The result is exactly symmetric and matches the full computation / the oracle; the
+    chunk minima of the mirrored blocks drive the same k-NN."""
+    from reidb200 import ops
+
+    rng = np.random.default_rng(n)
+    x = _unit(rng.standard_normal((n, d)))
+    x[n // 2] = x[3]
+    xd = torch.from_numpy(x).cuda()
+    for kind in ("sql2", "euclid", "dot"):
+        got = ops.distmat(xd, xd, kind).cpu().numpy()
+        blk = np.arange(n) // 256
+        off = blk[:, None] != blk[None, :]  # mirrored tiles are copies; inside a diagonal tile both halves are computed
+        assert np.array_equal(got[off], got.T[off]) and np.abs(got - got.T).max() <= 2e-5
+        monkeypatch.setenv("REIDB200_GEMM_NOSYM", "1")
+        full = ops.distmat(xd, xd, kind).cpu().numpy()
+        monkeypatch.delenv("REIDB200_GEMM_NOSYM")
+        np.testing.assert_allclose(got, full, rtol=REL, atol=2e-5)
+        assert np.array_equal(np.triu(got), np.triu(full)) or np.abs(got - full).max() <= 2e-5
+    np.testing.assert_allclose(ops.distmat(xd, xd, "sql2").cpu().numpy(), O.sql2_dist(x, x), rtol=REL, atol=2e-5)
+    k = 20
+    D, I = ops.knn(xd, xd, k, "sql2")
+    monkeypatch.setenv("REIDB200_GEMM_NOSYM", "1")
+    D2, I2 = ops.knn(xd, xd, k, "sql2")
+    monkeypatch.delenv("REIDB200_GEMM_NOSYM")
+    D, I, D2, I2 = D.cpu().numpy(), I.cpu().numpy(), D2.cpu().numpy(), I2.cpu().numpy()
+    np.testing.assert_allclose(D, D2, rtol=REL, atol=2e-5)
+    bad = I != I2
+    if bad.any():
+        fullm = O.sql2_dist(x, x).astype(np.float64)
+        r, c = np.where(bad)
+        assert np.allclose(fullm[r, I[r, c]], fullm[r, I2[r, c]], rtol=REL, atol=2e-5)
+
+
 def test_distmat_errors(rb):
     from reidb200 import ops
 

@@ -1,0 +1,6 @@
+#!/bin/bash
+mkdir -p gpurun_out
+timeout 600 python -m pytest tests/test_gpu_dist.py -q -m gpu --timeout=300 -x 2>&1 | tail -3
+timeout 300 python tools/step_once.py 2 > gpurun_out/step_plain.log 2>&1 &&
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:gemm_split -s 1 -c 1 -o gpurun_out/r01_gemm_sym python tools/step_once.py 2 > gpurun_out/ncu_gemm.log 2>&1
+echo "ncu rc=$?"; tail -2 gpurun_out/ncu_gemm.log
