@@ -391,7 +391,13 @@ def run_ours(args):
     gemm_n, gemm_ms = prof.get("gemm_split_tc_kernel", (0, 0.0))
     launches = sum(n for n, _ in prof.values())
     share = {k: round(v[1] / ms, 4) for k, v in sorted(prof.items(), key=lambda kv: -kv[1][1])}
-    gemm_flops = 2.0 * N * N * D_FULL  # algorithmic (fp32-equivalent) flops of one launch: 2*D per pair over N x N
+    # algorithmic (fp32-equivalent) flops of one launch: 2*D per UNORDERED pair -- the self-distance matrix is symmetric
+    # and the kernel computes only its upper triangle of tiles (each off-diagonal tile is stored twice)
+    gemm_flops = 2.0 * D_FULL * (N * (N + 1) / 2.0)
+    try:  # dram__bytes_read.sum + dram__bytes_write.sum of this kernel from the committed ncu --set full capture
+        traffic = json.load(open(os.path.join(ROOT, "profiles", "gemm_traffic.json")))["dram_bytes_per_launch"]
+    except Exception:
+        traffic = None
     achieved = gemm_flops / (gemm_ms / max(gemm_n, 1) * 1e-3) / 1e12 if gemm_n else None
     peak = peaks["bf16_tflops_sustained"] / 3.0  # three 16-bit UMMAs per fp32-accurate product
     line = {
@@ -405,8 +411,9 @@ def run_ours(args):
         "e2e": {"value": e2e_value, "unit": "pairs/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h)},
         "gpu_launches": int(launches),
         "roofline": {"kernel": "gemm_split_tc_kernel", "bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
-                     "frac": (achieved / peak) if achieved else None, "traffic": None,
+                     "frac": (achieved / peak) if achieved else None, "traffic": traffic,
                      "peak_source": "%s bf16_tflops_sustained / 3 (fp16 hi|lo split: three kind::f16 UMMAs per fp32-accurate product; fp16 and bf16 run at the same rate)" % peak_kind,
+                     "units_per_launch": "N(N+1)/2 = %d unordered pairs x 2*D flop" % (N * (N + 1) // 2),
                      "tensor_pipe_tflops": achieved * 3 if achieved else None},
         "kernel_share_of_step": share,
         "result": {"rank1": float(cmc_h[0]), "mAP": float(ap_h)},

@@ -91,10 +91,13 @@ constexpr int STAGES = 2;
 constexpr int A_BYTES = BM * BK * 2;                      // 16 KB
 constexpr int B_BYTES = BN * BK * 2;                      // 32 KB
 constexpr int STAGE_BYTES = 2 * A_BYTES + 2 * B_BYTES;    // 96 KB
-constexpr int EPI_STAGE_FLOATS = 2 * 32 * 32;             // per epilogue warp: two 32 x 32 fp32 output boxes (TMA store source)
-constexpr int GEMM_THREADS = 192;
+constexpr int EPI_WARPS = 8;                              // two per TMEM lane quadrant (SM sub-partition)
+constexpr int EPI_STAGE_FLOATS = 32 * 32;                 // per epilogue warp: one 32 x 32 fp32 output box (TMA store source)
+constexpr int GEMM_THREADS = 64 + 32 * EPI_WARPS;         // TMA producer warp, MMA warp, epilogue warps
 constexpr int TMEM_COLS = 512;
-constexpr size_t GEMM_SMEM = 1024 + (size_t)STAGES * STAGE_BYTES + 4 * EPI_STAGE_FLOATS * 4 + 128;
+constexpr int EPI_YW_FLOATS = EPI_WARPS * 64;             // per epilogue warp: column norms | column scale factors of a chunk
+// dynamic shared memory is declared 1024-byte aligned (SWIZZLE_128B operand tiles); the kernels trap if it is not
+constexpr size_t GEMM_SMEM = (size_t)STAGES * STAGE_BYTES + EPI_WARPS * EPI_STAGE_FLOATS * 4 + EPI_YW_FLOATS * 4 + 128;
 
 struct GemmArgs {
   int m, n, dp, num_kb, tiles_m, tiles_n, kind;
@@ -111,6 +114,7 @@ struct GemmArgs {
   int cred_max;
   int tma_out;  // the output tensor map is valid (16-byte aligned rows): epilogue stores through the TMA engine
   int symmetric;  // A == B (self distances): only tiles with tn >= tm are computed, each also stored transposed
+  int debug;      // timing experiments only (REIDB200_GEMM_DEBUG): 1 = no mirror store, 2 = no stores, 4 = no epilogue
 };
 
 // tile index -> (tm, tn) of the CTA-pair kernel.  Symmetric mode enumerates the upper triangle column by column:
@@ -142,131 +146,147 @@ __device__ __forceinline__ float colred_transpose(float (&v)[32], int lane) {
 }
 
 
-// Epilogue of one 32-row x 256-column accumulator slab owned by one warp (TMEM lane quadrant q): thread = row.
-// Fast path (16-byte aligned rows): the warp stages each 32 x 32 box in shared memory (128-byte rows, 16-byte chunks
-// XOR-swizzled by row & 7: four conflict-free wavefronts per 512-byte store) and one lane hands it to the TMA store
-// engine, which clips the ragged matrix edges; two boxes per warp are in flight.  Slow path (odd leading dimension):
-// transpose through a padded shared-memory tile and store row-contiguous scalars.
+// value of one output element from the raw accumulator r.  Operands were scaled by powers of two (ia = inverse row
+// scale, s = inverse column scale), so every scaling is exact and the fused form rounds like the plain one:
+// fma(-2, r ia s, xx + yy) == fma(r ia, -2 s, xx + yy).  sv = -2 s for the two L2 kinds, s otherwise (epi_colscale).
 template <int KIND>
-__device__ __forceinline__ void epilogue_slab(const GemmArgs& a, const CUtensorMap* tmO, uint32_t tmem_addr, int row0,
-                                              int col_base, int lane, float* sbuf, bool vec_ok, int& box,
-                                              bool sym_t = false) {
+__device__ __forceinline__ float epi_colscale(float s) {
+  return (KIND == REIDB200_DIST_SQL2 || KIND == REIDB200_DIST_EUCLID) ? __fmul_rn(-2.0f, s) : s;
+}
+template <int KIND>
+__device__ __forceinline__ float epi_value(float r, float ia, float sv, float xx, float yy) {
+  const float ra = __fmul_rn(r, ia);
+  if (KIND == REIDB200_DIST_SQL2) return fmaf(ra, sv, __fadd_rn(xx, yy));
+  if (KIND == REIDB200_DIST_EUCLID) return sqrtf(fmaxf(fmaf(ra, sv, __fadd_rn(xx, yy)), 1e-12f));
+  return dist_epilogue(KIND, __fmul_rn(ra, sv), xx, yy);
+}
+
+// Epilogue of the accumulator columns owned by one warp: TMEM lane quadrant q = warp % 4 (thread = row), and every
+// second 32-column chunk of the 256-column tile (two warps share a quadrant: chunks c0, c0 + 2, ...), so that each
+// SM sub-partition has two epilogue warps to hide each other's latencies.
+// Fast path (16-byte aligned rows): the warp turns the chunk into output values in registers, stages the 32 x 32 box
+// in shared memory (128-byte rows, 16-byte pieces XOR-swizzled by row & 7: four conflict-free wavefronts per 512-byte
+// store) and one lane hands it to the TMA store engine, which clips the ragged matrix edges.  Slow path (odd leading
+// dimension): transpose through the same shared-memory tile and store row-contiguous scalars.
+// Latency hiding: the column norms / scales of the warp's next chunk and its accumulator columns (tcgen05.ld) are
+// requested while the current chunk is processed; the first chunk's norms are requested BEFORE the wait on the
+// accumulator-full barrier; the wait for the staging buffer (previous TMA store has read it) comes after the math.
+// `yw` = 64 floats of shared memory private to this warp (column norms | column scale factors of the current chunk,
+// read back as broadcast 128-bit loads).
+template <int KIND>
+__device__ __forceinline__ void epilogue_slab(const GemmArgs& a, const CUtensorMap* tmO, uint32_t bar_full, uint32_t parity,
+                                              uint32_t tmem_addr, int row0, int col_base, int c_first, int lane, float* sb,
+                                              float* yw, bool vec_ok, bool sym_t = false) {
   const int my_row = row0 + lane;
-  const float xx_mine = (KIND != REIDB200_DIST_DOT && my_row < a.m) ? __ldg(a.xx + my_row) : 0.f;
-  const float ia_mine = my_row < a.m ? __ldg(a.isa + my_row) : 0.f;
   const int rows_here = min(32, a.m - row0);
-  if (rows_here <= 0) return;
+  const int nch = rows_here <= 0 ? 0 : min(BN / 32, (a.n - col_base + 31) >> 5);  // warp-uniform
+  float xx_mine = 0.f, ia_mine = 0.f, yn = 0.f, sn = 0.f;
+  if (c_first < nch) {
+    if (my_row < a.m) {
+      if (KIND != REIDB200_DIST_DOT) xx_mine = __ldg(a.xx + my_row);
+      ia_mine = __ldg(a.isa + my_row);
+    }
+    if (col_base + c_first * 32 + lane < a.n) {
+      if (KIND != REIDB200_DIST_DOT) yn = __ldg(a.yy + col_base + c_first * 32 + lane);
+      sn = __ldg(a.isb + col_base + c_first * 32 + lane);
+    }
+  }
+  ptx::mbar_wait(bar_full, parity);
+  ptx::tc_fence_after();
+  if (c_first >= nch || (a.debug & 4)) return;
+  if (a.debug & 1) sym_t = false;
+  if (a.debug & 2) vec_ok = false;
+  const bool want_red = a.cred != nullptr;
+  const bool red_max = a.cred_max != 0;
+  uint32_t rn[32];
+  ptx::tmem_ld_32x32b_x32(tmem_addr + c_first * 32, rn);
 #pragma unroll 1
-  for (int c = 0; c < BN / 32; ++c) {
+  for (int c = c_first; c < nch; c += 2) {
     const int col0 = col_base + c * 32;
-    if (col0 >= a.n) break;  // warp-uniform
-    uint32_t r[32];
-    ptx::tmem_ld_32x32b_x32(tmem_addr + c * 32, r);
-    ptx::tmem_ld_wait();
-    if (vec_ok) {
-      float* sb = sbuf + box * 1024;
-      if (lane == 0) ptx::bulk_wait_read<1>();  // the store issued two boxes ago has finished reading this buffer
-      __syncwarp();
-      const bool full = col0 + 32 <= a.n;
-      float red = a.cred_max ? -INFINITY : INFINITY;
+    yw[lane] = yn;
+    yw[32 + lane] = epi_colscale<KIND>(sn);
+    float o[32];
+    ptx::tmem_ld_wait(rn);
 #pragma unroll
-      for (int j = 0; j < 32; j += 4) {
-        float4 y4 = make_float4(0.f, 0.f, 0.f, 0.f), s4;
-        if (full) {
-          if (KIND != REIDB200_DIST_DOT) y4 = __ldg(reinterpret_cast<const float4*>(a.yy + col0 + j));
-          s4 = __ldg(reinterpret_cast<const float4*>(a.isb + col0 + j));
-        } else {  // ragged last chunk: scalar, guarded loads (the store itself is clipped by the TMA engine)
-          float yv[4] = {0.f, 0.f, 0.f, 0.f}, sv[4] = {0.f, 0.f, 0.f, 0.f};
-#pragma unroll
-          for (int u = 0; u < 4; ++u)
-            if (col0 + j + u < a.n) {
-              if (KIND != REIDB200_DIST_DOT) yv[u] = __ldg(a.yy + col0 + j + u);
-              sv[u] = __ldg(a.isb + col0 + j + u);
-            }
-          y4 = make_float4(yv[0], yv[1], yv[2], yv[3]);
-          s4 = make_float4(sv[0], sv[1], sv[2], sv[3]);
-        }
-        float4 o;
-        o.x = dist_epilogue(KIND, __fmul_rn(__fmul_rn(__uint_as_float(r[j + 0]), ia_mine), s4.x), xx_mine, y4.x);
-        o.y = dist_epilogue(KIND, __fmul_rn(__fmul_rn(__uint_as_float(r[j + 1]), ia_mine), s4.y), xx_mine, y4.y);
-        o.z = dist_epilogue(KIND, __fmul_rn(__fmul_rn(__uint_as_float(r[j + 2]), ia_mine), s4.z), xx_mine, y4.z);
-        o.w = dist_epilogue(KIND, __fmul_rn(__fmul_rn(__uint_as_float(r[j + 3]), ia_mine), s4.w), xx_mine, y4.w);
-        *reinterpret_cast<float4*>(sb + lane * 32 + (((j >> 2) ^ (lane & 7)) << 2)) = o;
-        if (sym_t) {  // keep the outputs: the block is stored a second time, transposed
-          r[j + 0] = __float_as_uint(o.x); r[j + 1] = __float_as_uint(o.y);
-          r[j + 2] = __float_as_uint(o.z); r[j + 3] = __float_as_uint(o.w);
-        }
-        if (a.cred) {
-          if (full) {
-            const float lo4 = fminf(fminf(o.x, o.y), fminf(o.z, o.w)), hi4 = fmaxf(fmaxf(o.x, o.y), fmaxf(o.z, o.w));
-            red = a.cred_max ? fmaxf(red, hi4) : fminf(red, lo4);
-          } else {
-            const float ov[4] = {o.x, o.y, o.z, o.w};
-#pragma unroll
-            for (int u = 0; u < 4; ++u)
-              if (col0 + j + u < a.n) red = a.cred_max ? fmaxf(red, ov[u]) : fminf(red, ov[u]);
-          }
-        }
+    for (int j = 0; j < 32; ++j) o[j] = __uint_as_float(rn[j]);
+    if (c + 2 < nch) {
+      ptx::tmem_ld_32x32b_x32(tmem_addr + (c + 2) * 32, rn);
+      yn = 0.f; sn = 0.f;
+      if (col0 + 64 + lane < a.n) {
+        if (KIND != REIDB200_DIST_DOT) yn = __ldg(a.yy + col0 + 64 + lane);
+        sn = __ldg(a.isb + col0 + 64 + lane);
       }
-      if (a.cred && my_row < a.m) a.cred[(size_t)my_row * a.ldcr + (col0 >> 5)] = red;
+    }
+    __syncwarp();
+    const bool full = col0 + 32 <= a.n;
+    // ---- math: raw accumulators -> output values, in registers (thread = row); row reduction over the chunk
+    float red = red_max ? -INFINITY : INFINITY;
+#pragma unroll
+    for (int j = 0; j < 32; j += 4) {
+      const float4 y4 = *reinterpret_cast<const float4*>(yw + j);  // broadcast reads (zero beyond column n)
+      const float4 s4 = *reinterpret_cast<const float4*>(yw + 32 + j);
+      o[j + 0] = epi_value<KIND>(o[j + 0], ia_mine, s4.x, xx_mine, y4.x);
+      o[j + 1] = epi_value<KIND>(o[j + 1], ia_mine, s4.y, xx_mine, y4.y);
+      o[j + 2] = epi_value<KIND>(o[j + 2], ia_mine, s4.z, xx_mine, y4.z);
+      o[j + 3] = epi_value<KIND>(o[j + 3], ia_mine, s4.w, xx_mine, y4.w);
+    }
+    if (full) {
+#pragma unroll
+      for (int j = 0; j < 32; ++j) red = red_max ? fmaxf(red, o[j]) : fminf(red, o[j]);
+    } else {
+#pragma unroll
+      for (int j = 0; j < 32; ++j)
+        if (col0 + j < a.n) red = red_max ? fmaxf(red, o[j]) : fminf(red, o[j]);
+    }
+    if (want_red && my_row < a.m) a.cred[(size_t)my_row * a.ldcr + (col0 >> 5)] = red;
+    if (vec_ok) {
+      // ---- direct box: wait until the previous TMA store has read the staging buffer, stage, store
+      if (lane == 0) ptx::bulk_wait_read<0>();
+      __syncwarp();
+#pragma unroll
+      for (int j = 0; j < 32; j += 4)
+        *reinterpret_cast<float4*>(sb + lane * 32 + (((j >> 2) ^ (lane & 7)) << 2)) = make_float4(o[j], o[j + 1], o[j + 2], o[j + 3]);
       ptx::fence_proxy_async();
       __syncwarp();
       if (lane == 0) {
         ptx::tma_store_2d(tmO, ptx::smem_u32(sb), col0, row0);
         ptx::bulk_commit();
       }
-      box ^= 1;
       if (sym_t) {
-        // mirror block out[col0 + j, row0 + lane]: box row j = this block's column j (lanes write 32 consecutive floats
-        // of a box row: conflict-free), clipped by the TMA engine like the direct one
-        float* st = sbuf + box * 1024;
-        if (lane == 0) ptx::bulk_wait_read<1>();
-        __syncwarp();
+        // ---- mirror block out[col0 + j, row0 + lane], straight from the registers: for every column j the warp
+        // writes 32 consecutive floats of mirror row col0 + j (one coalesced 128-byte store; no staging buffer, so
+        // nothing to wait for).  Its chunk reduction (mirror row = column col0 + lane, over this warp's rows) reads
+        // the column back from the staged direct box, which the TMA engine is reading concurrently.
+        if (want_red) {
+          float red_t = red_max ? -INFINITY : INFINITY;
 #pragma unroll
-        for (int j = 0; j < 32; ++j) st[j * 32 + ((((lane >> 2) ^ (j & 7)) << 2) | (lane & 3))] = __uint_as_float(r[j]);
-        if (a.cred) {  // chunk reduction of the mirror rows: over this warp's 32 rows, per column
-          float v[32];
-          const float pad = a.cred_max ? -INFINITY : INFINITY;
-#pragma unroll
-          for (int j = 0; j < 32; ++j) v[j] = my_row < a.m ? __uint_as_float(r[j]) : pad;
-          const float red_t = a.cred_max ? colred_transpose<true>(v, lane) : colred_transpose<false>(v, lane);
+          for (int rr = 0; rr < 32; ++rr) {
+            const float v = sb[rr * 32 + ((((lane >> 2) ^ (rr & 7)) << 2) | (lane & 3))];
+            if (rr < rows_here) red_t = red_max ? fmaxf(red_t, v) : fminf(red_t, v);
+          }
           if (col0 + lane < a.n) a.cred[(size_t)(col0 + lane) * a.ldcr + (row0 >> 5)] = red_t;
         }
-        ptx::fence_proxy_async();
-        __syncwarp();
-        if (lane == 0) {
-          ptx::tma_store_2d(tmO, ptx::smem_u32(st), row0, col0);
-          ptx::bulk_commit();
-        }
-        box ^= 1;
-      }
-    } else {
-      if (a.cred && my_row < a.m) {  // reduce from the registers (thread = row) before the transpose
-        float red2 = a.cred_max ? -INFINITY : INFINITY;
+        if (my_row < a.m) {
+          float* mp = a.out + (size_t)col0 * a.ldo + my_row;
+          if (full) {
 #pragma unroll
-        for (int j = 0; j < 32; ++j) {  // fully unrolled: r[] must stay in registers
-          if (col0 + j < a.n) {
-            const float yv = KIND != REIDB200_DIST_DOT ? __ldg(a.yy + col0 + j) : 0.f;
-            const float o = dist_epilogue(KIND, __fmul_rn(__fmul_rn(__uint_as_float(r[j]), ia_mine), __ldg(a.isb + col0 + j)), xx_mine, yv);
-            red2 = a.cred_max ? fmaxf(red2, o) : fminf(red2, o);
+            for (int j = 0; j < 32; ++j) mp[(size_t)j * a.ldo] = o[j];
+          } else {
+#pragma unroll
+            for (int j = 0; j < 32; ++j)
+              if (col0 + j < a.n) mp[(size_t)j * a.ldo] = o[j];
           }
         }
-        a.cred[(size_t)my_row * a.ldcr + (col0 >> 5)] = red2;
       }
+    } else {
+      // ---- slow path: transpose through shared memory (XOR-swizzled columns), row-contiguous scalar stores
 #pragma unroll
-      for (int j = 0; j < 32; ++j) sbuf[lane * 33 + j] = __uint_as_float(r[j]);
+      for (int j = 0; j < 32; ++j) sb[lane * 32 + (j ^ lane)] = o[j];
       __syncwarp();
       const int col = col0 + lane;
-      const float yy_c = (KIND != REIDB200_DIST_DOT && col < a.n) ? __ldg(a.yy + col) : 0.f;
-      const float ib_c = col < a.n ? __ldg(a.isb + col) : 0.f;
 #pragma unroll 8
-      for (int rr = 0; rr < 32; ++rr) {
-        const float xr = __shfl_sync(0xffffffffu, xx_mine, rr);
-        const float ir = __shfl_sync(0xffffffffu, ia_mine, rr);
-        const float acc = __fmul_rn(__fmul_rn(sbuf[rr * 33 + lane], ir), ib_c);
-        if (rr < rows_here && col < a.n)
-          __stcs(a.out + (size_t)(row0 + rr) * a.ldo + col, dist_epilogue(KIND, acc, xr, yy_c));
-      }
+      for (int rr = 0; rr < 32; ++rr)
+        if (rr < rows_here && col < a.n && !(a.debug & 2)) __stcs(a.out + (size_t)(row0 + rr) * a.ldo + col, sb[rr * 32 + (lane ^ rr)]);
       __syncwarp();
     }
   }
@@ -276,10 +296,11 @@ template <int KIND>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
 gemm_split_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                      const __grid_constant__ CUtensorMap tmO, GemmArgs a) {
-  extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  extern __shared__ __align__(1024) uint8_t smem[];
+  if ((ptx::smem_u32(smem) & 1023u) != 0) __trap();
   float* epi_buf = reinterpret_cast<float*>(smem + (size_t)STAGES * STAGE_BYTES);
-  uint64_t* bars = reinterpret_cast<uint64_t*>(epi_buf + 4 * EPI_STAGE_FLOATS);
+  float* yw_buf = epi_buf + EPI_WARPS * EPI_STAGE_FLOATS;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(yw_buf + EPI_YW_FLOATS);
   // bars: [0,STAGES) full, [STAGES,2*STAGES) empty, then tmem_full[2], tmem_empty[2]
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * STAGES + 4);
 
@@ -298,7 +319,7 @@ gemm_split_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
     }
     for (int s = 0; s < 2; ++s) {
       ptx::mbar_init(bar_tfull + 8 * s, 1);
-      ptx::mbar_init(bar_tempty + 8 * s, 4);  // one arrival per epilogue warp
+      ptx::mbar_init(bar_tempty + 8 * s, EPI_WARPS);  // one arrival per epilogue warp
     }
     ptx::fence_barrier_init();
     ptx::prefetch_tensormap(&tmA);
@@ -371,14 +392,13 @@ gemm_split_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
     const int q = warp & 3;
     float* sbuf = epi_buf + (warp - 2) * EPI_STAGE_FLOATS;
     const bool vec_ok = a.tma_out != 0;
-    int as = 0, box = 0;
+    const int c_first = (warp - 2) >> 2;  // the two warps of a quadrant interleave the 32-column chunks
+    int as = 0;
     uint32_t aphase = 0;
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
       const int tm = tile % a.tiles_m, tn = tile / a.tiles_m;
-      ptx::mbar_wait(bar_tfull + 8 * as, aphase);
-      ptx::tc_fence_after();
-      epilogue_slab<KIND>(a, &tmO, tmem_base + ((uint32_t)(q * 32) << 16) + as * BN, tm * BM + q * 32, tn * BN, lane, sbuf,
-                          vec_ok, box);
+      epilogue_slab<KIND>(a, &tmO, bar_tfull + 8 * as, aphase, tmem_base + ((uint32_t)(q * 32) << 16) + as * BN,
+                          tm * BM + q * 32, tn * BN, c_first, lane, sbuf, yw_buf + (warp - 2) * 64, vec_ok);
       ptx::tc_fence_before();
       __syncwarp();
       if (lane == 0) ptx::mbar_arrive(bar_tempty + 8 * as);
@@ -403,16 +423,18 @@ gemm_split_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
 // number of UMMA cycles; three stages fit.  The even CTA issues every UMMA (M = 256) and multicasts the commits.
 constexpr int STAGES2 = 3;
 constexpr int STAGE2_BYTES = 4 * A_BYTES;  // Ahi, Alo, Bhi(half), Blo(half): 64 KB
-constexpr size_t GEMM2_SMEM = 1024 + (size_t)STAGES2 * STAGE2_BYTES + 4 * EPI_STAGE_FLOATS * 4 + 128;
+constexpr size_t GEMM2_SMEM = (size_t)STAGES2 * STAGE2_BYTES + EPI_WARPS * EPI_STAGE_FLOATS * 4 + EPI_YW_FLOATS * 4 + 128;
+static_assert(GEMM_SMEM <= 232448 && GEMM2_SMEM <= 232448, "shared memory budget (227 KB per CTA)");
 
 template <int KIND>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GEMM_THREADS, 1)
 gemm_split_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                       const __grid_constant__ CUtensorMap tmO, GemmArgs a) {
-  extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  extern __shared__ __align__(1024) uint8_t smem[];
+  if ((ptx::smem_u32(smem) & 1023u) != 0) __trap();
   float* epi_buf = reinterpret_cast<float*>(smem + (size_t)STAGES2 * STAGE2_BYTES);
-  uint64_t* bars = reinterpret_cast<uint64_t*>(epi_buf + 4 * EPI_STAGE_FLOATS);
+  float* yw_buf = epi_buf + EPI_WARPS * EPI_STAGE_FLOATS;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(yw_buf + EPI_YW_FLOATS);
   // bars: [0,S) full, [S,2S) empty, then tmem_full[2], tmem_empty[2]
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * STAGES2 + 4);
 
@@ -433,7 +455,7 @@ gemm_split_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
     }
     for (int s = 0; s < 2; ++s) {
       ptx::mbar_init(bar_tfull + 8 * s, 1);
-      ptx::mbar_init(bar_tempty + 8 * s, 8);  // 4 epilogue warps x 2 CTAs arrive on the leader's barrier
+      ptx::mbar_init(bar_tempty + 8 * s, 2 * EPI_WARPS);  // epilogue warps of both CTAs arrive on the leader's barrier
     }
     ptx::fence_barrier_init();
     ptx::prefetch_tensormap(&tmA);
@@ -511,15 +533,15 @@ gemm_split_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
     const int q = warp & 3;
     float* sbuf = epi_buf + (warp - 2) * EPI_STAGE_FLOATS;
     const bool vec_ok = a.tma_out != 0;
-    int as = 0, box = 0;
+    const int c_first = (warp - 2) >> 2;  // the two warps of a quadrant interleave the 32-column chunks
+    int as = 0;
     uint32_t aphase = 0;
     for (int tile = cluster_id; tile < total_tiles; tile += num_clusters) {
       int tm, tn;
       pair_tile_coords(tile, tiles_m2, a.symmetric, tm, tn);
-      ptx::mbar_wait(bar_tfull + 8 * as, aphase);
-      ptx::tc_fence_after();
-      epilogue_slab<KIND>(a, &tmO, tmem_base + ((uint32_t)(q * 32) << 16) + as * BN, tm * 2 * BM + (int)rank * BM + q * 32,
-                          tn * BN, lane, sbuf, vec_ok, box, a.symmetric && tn != tm);
+      epilogue_slab<KIND>(a, &tmO, bar_tfull + 8 * as, aphase, tmem_base + ((uint32_t)(q * 32) << 16) + as * BN,
+                          tm * 2 * BM + (int)rank * BM + q * 32, tn * BN, c_first, lane, sbuf, yw_buf + (warp - 2) * 64,
+                          vec_ok, a.symmetric && tn != tm);
       ptx::tc_fence_before();
       __syncwarp();
       if (lane == 0) ptx::mbar_arrive_leader(bar_tempty + 8 * as);
@@ -649,6 +671,7 @@ int gemm_split_launch(const void* packedA, const float* xx, const float* isa, in
     if (rc) return rc;
   }
   // self distances: compute the upper triangle of 256 x 256 tiles only and store every off-diagonal tile twice
+  a.debug = getenv("REIDB200_GEMM_DEBUG") ? atoi(getenv("REIDB200_GEMM_DEBUG")) : 0;
   a.symmetric = pair && a.tma_out && packedA == packedB && m == n && xx == yy && isa == isb && !getenv("REIDB200_GEMM_NOSYM");
   void (*k1)(CUtensorMap, CUtensorMap, CUtensorMap, GemmArgs) = nullptr;
   void (*k2)(CUtensorMap, CUtensorMap, CUtensorMap, GemmArgs) = nullptr;

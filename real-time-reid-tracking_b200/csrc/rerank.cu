@@ -354,7 +354,7 @@ static RerankDims rerank_dims(int N, int k1, int k2) {
   d.wh = d.half + 1 < k1 ? d.half + 1 : k1;
   d.cap1 = k1 + k1 * d.wh;
   d.cap2 = k2 > 1 ? k2 * d.cap1 : d.cap1;
-  d.lds = (int64_t)align_up((size_t)N, 4);
+  d.lds = (int64_t)align_up((size_t)N, 32);  // 128-byte aligned rows: every 32 x 32 output box of the GEMM covers whole cache lines
   return d;
 }
 
