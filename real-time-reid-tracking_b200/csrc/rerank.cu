@@ -69,78 +69,86 @@ __device__ int block_exclusive_scan(int* data, int n, int* warp_tot) {
   return total;
 }
 
-// One CTA per row i.  Dynamic smem: L[cap] S[cap] flag[cap] (ints) + val[cap] (floats).
+// One CTA per row i.  Dynamic smem: K[P] flag[P] (ints) + val[P] (floats), P = cap rounded up to a power of two.
+// The candidate lists are staged uncompacted in K -- slot t < k1 holds R(i,k1)[t], slot k1 + t*wh + a holds
+// R(c_t,k1/2)[a] -- with INT_MAX in every unused slot; rejected candidates (2/3 rule) are overwritten with
+// INT_MAX, one bitonic sort of the next power of two above the used extent puts the keys in np.unique's
+// order, and neighbour comparison + a scan drops the duplicates.  (np.unique is a sort; the sorted unique
+// set does not depend on how it is obtained.)
+constexpr int EXP_MAX_K1 = 128;
+
 __global__ void __launch_bounds__(EXP_THREADS)
 expand_v_kernel(const int32_t* __restrict__ rfull, const int32_t* __restrict__ rfull_cnt, int wf,
                 const int32_t* __restrict__ rhalf, const int32_t* __restrict__ rhalf_cnt, int wh,
-                const float* __restrict__ sql2, int64_t lds, const float* __restrict__ sqnorm, int N, int cap,
+                const float* __restrict__ sql2, int64_t lds, const float* __restrict__ sqnorm, int N, int cap, int P,
                 int use_f16, int32_t* __restrict__ vcols, float* __restrict__ vvals, int32_t* __restrict__ vcnt) {
   extern __shared__ int sm_i[];
-  int* L = sm_i;
-  int* S = L + cap;
-  int* flag = S + cap;
-  float* val = reinterpret_cast<float*>(flag + cap);
-  __shared__ int s_off[129];
+  int* K = sm_i;
+  int* flag = K + P;
+  float* val = reinterpret_cast<float*>(flag + P);
+  __shared__ int s_nc[EXP_MAX_K1], s_inter[EXP_MAX_K1];
   __shared__ int warp_tot[EXP_THREADS / 32];
   __shared__ float s_red[EXP_THREADS / 32];
+  constexpr int SENT = 0x7fffffff;
 
   const int i = blockIdx.x;
   const int tid = threadIdx.x;
   const int nb = rfull_cnt[i];
   const int32_t* base = rfull + (size_t)i * wf;
-
-  // 2/3 rule against the UNEXPANDED R(i,k1) (faiss_utils.py:192-197)
-  for (int t = tid; t < nb; t += EXP_THREADS) {
-    const int c = base[t];
-    const int nc = rhalf_cnt[c];
-    const int32_t* rc = rhalf + (size_t)c * wh;
-    int inter = 0;
-    for (int a = 0; a < nc; ++a) {
-      const int x = rc[a];
-      for (int b = 0; b < nb; ++b) inter += (base[b] == x);
+  const int used = wf + nb * wh;  // slots [0, used) may hold keys
+  int Pn = 32;
+  while (Pn < used) Pn <<= 1;     // <= P
+  for (int t = tid; t < Pn; t += EXP_THREADS) K[t] = SENT;
+  if (tid < nb) { s_nc[tid] = rhalf_cnt[base[tid]]; s_inter[tid] = 0; }
+  __syncthreads();
+  for (int t = tid; t < nb; t += EXP_THREADS) K[t] = base[t];
+  for (int e = tid; e < nb * wh; e += EXP_THREADS) {
+    const int t = e / wh, a = e - t * wh;
+    if (a < s_nc[t]) K[wf + e] = rhalf[(size_t)base[t] * wh + a];
+  }
+  __syncthreads();
+  // 2/3 rule against the UNEXPANDED R(i,k1) (faiss_utils.py:192-197): inter_t = #(R(c_t,k1/2) & R(i,k1))
+  for (int e = tid; e < nb * wh; e += EXP_THREADS) {
+    const int t = e / wh;
+    const int x = K[wf + e];
+    if (x != SENT) {
+      int hit = 0;
+      for (int b2 = 0; b2 < nb; ++b2) hit += (K[b2] == x);
+      if (hit) atomicAdd(s_inter + t, hit);
     }
-    s_off[t] = ((double)inter > (2.0 / 3.0) * (double)nc) ? nc : 0;
   }
   __syncthreads();
-  if (tid == 0) {
-    int run = nb;
-    for (int t = 0; t < nb; ++t) { const int v = s_off[t]; s_off[t] = run; run += v; }
-    s_off[nb] = run;
+  for (int e = tid; e < nb * wh; e += EXP_THREADS) {
+    const int t = e / wh;
+    if (!((double)s_inter[t] > (2.0 / 3.0) * (double)s_nc[t])) K[wf + e] = SENT;
   }
   __syncthreads();
-  const int n = s_off[nb];
-  for (int t = tid; t < nb; t += EXP_THREADS) L[t] = base[t];
-  for (int t = 0; t < nb; ++t) {
-    const int o = s_off[t], len = s_off[t + 1] - o;
-    const int32_t* rc = rhalf + (size_t)base[t] * wh;
-    for (int a = tid; a < len; a += EXP_THREADS) L[o + a] = rc[a];
-  }
-  __syncthreads();
-  // np.unique: sort ascending, drop duplicates (rank sort; n <= cap is small)
-  for (int e = tid; e < n; e += EXP_THREADS) {
-    const int x = L[e];
-    int r = 0, dup = 0;
-    for (int o = 0; o < n; ++o) {
-      const int y = L[o];
-      r += (y < x) || (y == x && o < e);
-      dup |= (y == x && o < e);
+  // bitonic sort of K[0, Pn), ascending (INT_MAX padding ends up last)
+  for (int k = 2; k <= Pn; k <<= 1) {
+    for (int j = k >> 1; j > 0; j >>= 1) {
+      for (int idx = tid; idx < (Pn >> 1); idx += EXP_THREADS) {
+        const int i1 = ((idx & ~(j - 1)) << 1) | (idx & (j - 1));
+        const int i2 = i1 + j;
+        const int x = K[i1], y = K[i2];
+        const bool up = (i1 & k) == 0;
+        if ((x > y) == up) { K[i1] = y; K[i2] = x; }
+      }
+      __syncthreads();
     }
-    S[r] = x;
-    flag[r] = dup ? 0 : 1;
   }
+  for (int r = tid; r < Pn; r += EXP_THREADS) flag[r] = (K[r] != SENT && (r == 0 || K[r - 1] != K[r])) ? 1 : 0;
   __syncthreads();
-  const int nu = block_exclusive_scan(flag, n, warp_tot);  // flag[r] -> output slot of S[r]
-  // S[r] is unique iff it differs from S[r-1]
+  const int nu = block_exclusive_scan(flag, Pn, warp_tot);  // flag[r] -> output slot of K[r]
   float lmax = -INFINITY;
   const float xi = sqnorm[i];
-  for (int r = tid; r < n; r += EXP_THREADS) {
-    const int c = S[r];
-    if (r == 0 || S[r - 1] != c) {
+  for (int r = tid; r < Pn; r += EXP_THREADS) {
+    const int c = K[r];
+    if (c != SENT && (r == 0 || K[r - 1] != c)) {
       // dist = 2 - 2 x_i.x_c (faiss_utils.py:201-204), with x_i.x_c = (|x_i|^2 + |x_c|^2 - sql2)/2
       const float dot = 0.5f * ((xi + sqnorm[c]) - sql2[(size_t)i * lds + c]);
       const float nd = -(2.0f - 2.0f * dot);
       val[flag[r]] = nd;
-      L[flag[r]] = c;
+      vcols[(size_t)i * cap + flag[r]] = c;
       lmax = fmaxf(lmax, nd);
     }
   }
@@ -169,7 +177,6 @@ expand_v_kernel(const int32_t* __restrict__ rfull, const int32_t* __restrict__ r
   for (int u = tid; u < nu; u += EXP_THREADS) {
     float v = __fdiv_rn(val[u], gsum);
     if (use_f16) v = __half2float(__float2half_rn(v));
-    vcols[(size_t)i * cap + u] = L[u];
     vvals[(size_t)i * cap + u] = v;
   }
   if (tid == 0) vcnt[i] = nu;
@@ -306,39 +313,116 @@ __global__ void inv_fill_kernel(const int32_t* __restrict__ cols, const float* _
 // One CTA per output row i: acc[r] = sum_j min(V[i,j], V[r,j]) over the inverted lists of the
 // non-zeros of row i (faiss_utils.py:223-234), staged in shared memory (N floats), then the whole
 // dense row 1 - t/(2-t) (clamped at 0, :236-240) is written once, coalesced.
+// The scatter is flattened: the row's non-zeros and the extents of their inverted lists are staged in
+// shared memory first (one dependent-load chain per CTA instead of one per entry), an exclusive scan of
+// the list lengths turns (entry, position) into one index space, and every thread walks that space with
+// a stride of the CTA size, several independent loads in flight.
+// The accumulator is 2.30 fixed point (sums of minima of softmax weights lie in [0, 1]; every term is rounded to
+// a multiple of 2^-30, the sum itself is exact): shared-memory integer atomics are native -- fp32 ones are
+// compare-and-swap loops that serialise on the few hundred hot rows of a cluster -- and the result no longer
+// depends on the order in which the atomics land.
+// Dynamic smem: acc[N4] | e_val[cap] | e_beg[cap] (ints) | e_off[cap + 1] (ints), N4 = N rounded up to 4.
 constexpr int JR_THREADS = 512;
+constexpr int JR_PF = 32;                        // squared-L2 values prefetched per thread (covers 16384 columns)
+constexpr float JR_FIX = 1073741824.0f;          // 2^30
+constexpr float JR_UNFIX = 1.0f / 1073741824.0f;
 
-__global__ void __launch_bounds__(JR_THREADS)
+__device__ __forceinline__ float jaccard_value(float t, int use_f16) {
+  if (t == 0.f) return 1.0f;  // 1 - 0 / 2, exactly
+  if (use_f16) t = __half2float(__float2half_rn(t));
+  const float jd = __fsub_rn(1.0f, __fdiv_rn(t, __fsub_rn(2.0f, t)));
+  return jd < 0.f ? 0.f : jd;
+}
+
+__global__ void __launch_bounds__(JR_THREADS, 2)
 jaccard_rows_kernel(const int32_t* __restrict__ qcols, const float* __restrict__ qvals, const int32_t* __restrict__ qcnt,
                     int cap, const int32_t* __restrict__ colptr, const int32_t* __restrict__ inv_row,
                     const float* __restrict__ inv_val, int N, int row0, int col0, int ncols, float lambda_value,
                     const float* __restrict__ sql2, int64_t lds, int use_f16, void* __restrict__ out, int64_t ldo) {
-  extern __shared__ float acc[];
+  extern __shared__ __align__(16) float acc[];
+  const int N4 = (N + 3) & ~3;
+  unsigned int* acci = reinterpret_cast<unsigned int*>(acc);
+  float* e_val = acc + N4;
+  int* e_beg = reinterpret_cast<int*>(e_val + cap);
+  int* e_off = e_beg + cap;
+  __shared__ int warp_tot[JR_THREADS / 32];
   const int i = row0 + blockIdx.x;
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  for (int r = tid; r < N; r += JR_THREADS) acc[r] = 0.f;
-  __syncthreads();
+  const int tid = threadIdx.x;
+  // lambda blend: this row's slice of the squared-L2 matrix is requested NOW (JR_PF independent loads per thread,
+  // the whole 64 KB slice of a Market-sized row in flight at once) and consumed after the scatter
+  const bool blend = lambda_value > 0.f;
+  const float* srow = sql2 + (size_t)i * lds + col0;
+  float pre[JR_PF];
+  if (blend) {
+#pragma unroll
+    for (int k = 0; k < JR_PF; ++k) {
+      const int c = tid + k * JR_THREADS;
+      pre[k] = c < ncols ? __ldcs(srow + c) : 0.f;
+    }
+  }
+  for (int r = tid; r < N4 / 4; r += JR_THREADS) reinterpret_cast<float4*>(acc)[r] = make_float4(0.f, 0.f, 0.f, 0.f);
   const int n = qcnt[i];
-  for (int t = warp; t < n; t += JR_THREADS / 32) {
+  for (int t = tid; t < n; t += JR_THREADS) {
     const float v = qvals[(size_t)i * cap + t];
-    if (v == 0.f) continue;
     const int j = qcols[(size_t)i * cap + t];
     const int b = colptr[j], e = colptr[j + 1];
-    for (int p = b + lane; p < e; p += 32) atomicAdd(acc + inv_row[p], fminf(v, inv_val[p]));
+    e_val[t] = v;
+    e_beg[t] = b;
+    e_off[t] = v == 0.f ? 0 : e - b;
+  }
+  __syncthreads();
+  const int total = block_exclusive_scan(e_off, n, warp_tot);  // e_off[t] = first flat index of entry t
+  if (tid == 0) e_off[n] = total;
+  __syncthreads();
+  {
+    int t = 0;
+    constexpr int U = 4;
+    for (int w0 = tid; w0 < total; w0 += U * JR_THREADS) {
+      int rr[U];
+      float vv[U], mv[U];
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const int w = w0 + u * JR_THREADS;
+        rr[u] = -1;
+        if (w < total) {
+          while (w >= e_off[t + 1]) ++t;  // entries with an empty list are skipped (equal offsets)
+          const int p = e_beg[t] + (w - e_off[t]);
+          rr[u] = __ldg(inv_row + p);
+          vv[u] = __ldg(inv_val + p);
+          mv[u] = e_val[t];
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < U; ++u)
+        if (rr[u] >= 0) atomicAdd(acci + rr[u], __float2uint_rn(__fmul_rn(fminf(mv[u], vv[u]), JR_FIX)));
+    }
+  }
+  __syncthreads();
+  for (int r = tid; r < N4 / 4; r += JR_THREADS) {  // fixed point -> fp32, in place
+    const uint4 a4 = reinterpret_cast<const uint4*>(acci)[r];
+    if ((a4.x | a4.y | a4.z | a4.w) != 0u)
+      reinterpret_cast<float4*>(acc)[r] = make_float4(__fmul_rn(__uint2float_rn(a4.x), JR_UNFIX), __fmul_rn(__uint2float_rn(a4.y), JR_UNFIX),
+                                                      __fmul_rn(__uint2float_rn(a4.z), JR_UNFIX), __fmul_rn(__uint2float_rn(a4.w), JR_UNFIX));
   }
   __syncthreads();
   const float one_m_l = 1.0f - lambda_value;
-  for (int c = tid; c < ncols; c += JR_THREADS) {
-    float t = acc[col0 + c];
-    if (use_f16) t = __half2float(__float2half_rn(t));
-    float jd = __fsub_rn(1.0f, __fdiv_rn(t, __fsub_rn(2.0f, t)));
-    if (jd < 0.f) jd = 0.f;
-    if (lambda_value > 0.f) {
-      const float orig = sqrtf(fmaxf(sql2[(size_t)i * lds + col0 + c], 1e-12f));
-      jd = __fadd_rn(__fmul_rn(jd, one_m_l), __fmul_rn(orig, lambda_value));
+  float* orow = reinterpret_cast<float*>(out) + (size_t)blockIdx.x * ldo;
+  __half* hrow = reinterpret_cast<__half*>(out) + (size_t)blockIdx.x * ldo;
+#pragma unroll
+  for (int k = 0; k < JR_PF; ++k) {
+    const int c = tid + k * JR_THREADS;
+    if (c < ncols) {
+      float jd = jaccard_value(acc[col0 + c], use_f16);
+      if (blend) jd = __fadd_rn(__fmul_rn(jd, one_m_l), __fmul_rn(sqrtf(fmaxf(pre[k], 1e-12f)), lambda_value));
+      if (use_f16) hrow[c] = __float2half_rn(jd);
+      else __stcs(orow + c, jd);
     }
-    if (use_f16) reinterpret_cast<__half*>(out)[(size_t)blockIdx.x * ldo + c] = __float2half_rn(jd);
-    else __stcs(reinterpret_cast<float*>(out) + (size_t)blockIdx.x * ldo + c, jd);
+  }
+  for (int c = tid + JR_PF * JR_THREADS; c < ncols; c += JR_THREADS) {  // rows wider than JR_PF * JR_THREADS columns
+    float jd = jaccard_value(acc[col0 + c], use_f16);
+    if (blend) jd = __fadd_rn(__fmul_rn(jd, one_m_l), __fmul_rn(sqrtf(fmaxf(__ldcs(srow + c), 1e-12f)), lambda_value));
+    if (use_f16) hrow[c] = __float2half_rn(jd);
+    else __stcs(orow + c, jd);
   }
 }
 
@@ -397,21 +481,23 @@ struct NullCarver {  // size-only twin of Carver
 static int rerank_check(int N, int k1, int k2, const RerankDims& d) {
   RB_REQUIRE(k1 >= 1 && k1 <= 128 && k1 < N, "jaccard: need 1 <= k1 <= 128 and k1 < N (k1=%d, N=%d)", k1, N);
   RB_REQUIRE(k2 >= 1 && k2 <= QE_MAX_K2 && k2 <= k1, "jaccard: need 1 <= k2 <= min(k1,%d) (k2=%d)", QE_MAX_K2, k2);
-  if (d.cap1 > 4096 || d.cap2 > 8192 || (size_t)N * 4 > 220 * 1024) {
-    set_error("jaccard: size outside this build's limits (N=%d <= 56320, cap1=%d <= 4096, cap2=%d <= 8192)", N, d.cap1, d.cap2);
+  if (d.cap1 > 4096 || d.cap2 > 8192 || (size_t)((N + 3) & ~3) * 4 + (size_t)d.cap2 * 12 + 16 > 232448 - 256) {
+    set_error("jaccard: size outside this build's limits (4 N + 12 cap2 <= 227 KB of shared memory: N=%d, cap1=%d <= 4096, cap2=%d <= 8192)", N, d.cap1, d.cap2);
     return REIDB200_ELIMIT;
   }
   return REIDB200_OK;
 }
+
+static size_t jaccard_rows_smem(int N, int cap) { return (size_t)((N + 3) & ~3) * 4 + (size_t)cap * 12 + 16; }
 
 static int jaccard_sparse_stages(const int32_t* rank, const float* sql2, int64_t lds, const float* sqnorm, int N, int k1,
                                  int k2, int use_f16, float lambda_value, int row0, int nrows, int col0, int ncols,
                                  void* out, int64_t ldo, const RerankDims& d, const SparseWs& w, cudaStream_t st) {
   static bool attr = false;
   if (!attr) {
-    RB_CUDA(cudaFuncSetAttribute(expand_v_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 4096 * 16));
+    RB_CUDA(cudaFuncSetAttribute(expand_v_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 4096 * 12));
     RB_CUDA(cudaFuncSetAttribute(qexpand_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 8192 * 12));
-    RB_CUDA(cudaFuncSetAttribute(jaccard_rows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
+    RB_CUDA(cudaFuncSetAttribute(jaccard_rows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448 - 256));
     attr = true;
   }
   const int wpb = 8;
@@ -419,8 +505,10 @@ static int jaccard_sparse_stages(const int32_t* rank, const float* sql2, int64_t
   RB_LAUNCH_CHECK("krecip_kernel(k1)");
   { ProfScope _ps("krecip_kernel(k1/2)", st); krecip_kernel<<<ceil_div(N, wpb), wpb * 32, 0, st>>>(rank, N, k1, d.wh, d.wh, w.rhalf, w.rhalf_cnt); }
   RB_LAUNCH_CHECK("krecip_kernel(k1/2)");
-  { ProfScope _ps("expand_v_kernel", st); expand_v_kernel<<<N, EXP_THREADS, (size_t)d.cap1 * 16, st>>>(w.rfull, w.rfull_cnt, k1, w.rhalf, w.rhalf_cnt, d.wh, sql2,
-                                                                lds, sqnorm, N, d.cap1, use_f16, w.v1cols, w.v1vals,
+  int expP = 32;
+  while (expP < d.cap1) expP <<= 1;
+  { ProfScope _ps("expand_v_kernel", st); expand_v_kernel<<<N, EXP_THREADS, (size_t)expP * 12, st>>>(w.rfull, w.rfull_cnt, k1, w.rhalf, w.rhalf_cnt, d.wh, sql2,
+                                                                lds, sqnorm, N, d.cap1, expP, use_f16, w.v1cols, w.v1vals,
                                                                 w.v1cnt); }
   RB_LAUNCH_CHECK("expand_v_kernel");
   if (k2 > 1) {
@@ -435,7 +523,8 @@ static int jaccard_sparse_stages(const int32_t* rank, const float* sql2, int64_t
   RB_LAUNCH_CHECK("inv_scan_kernel");
   { ProfScope _ps("inv_fill_kernel", st); inv_fill_kernel<<<N, 128, 0, st>>>(w.v2cols, w.v2vals, w.v2cnt, N, d.cap2, w.cursor, w.inv_row, w.inv_val); }
   RB_LAUNCH_CHECK("inv_fill_kernel");
-  { ProfScope _ps("jaccard_rows_kernel", st); jaccard_rows_kernel<<<nrows, JR_THREADS, (size_t)N * sizeof(float), st>>>(
+  const int jr_cap = k2 > 1 ? d.cap2 : d.cap1;
+  { ProfScope _ps("jaccard_rows_kernel", st); jaccard_rows_kernel<<<nrows, JR_THREADS, jaccard_rows_smem(N, jr_cap), st>>>(
       w.v2cols, w.v2vals, w.v2cnt, d.cap2, w.colptr, w.inv_row, w.inv_val, N, row0, col0, ncols, lambda_value, sql2, lds,
       use_f16, out, ldo); }
   RB_LAUNCH_CHECK("jaccard_rows_kernel");
