@@ -98,4 +98,30 @@ __device__ __forceinline__ uint32_t float_to_ordered(float f) {
   return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
 }
 
+// Exclusive scan of in[0..n) by ONE CTA of 1024 threads through shared memory: coalesced loads into buf[0..n), every
+// thread scans a contiguous chunk (odd chunk length: conflict-free banks), one block-wide scan of the chunk totals.
+// Afterwards buf[r] = sum of in[0..r); returns the total.  wsum = 32 ints of shared memory.  Ends with a barrier.
+__device__ __forceinline__ int cta_exclusive_scan_smem(const int32_t* __restrict__ in, int n, int* buf, int* wsum) {
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  for (int r = tid; r < n; r += 1024) buf[r] = in[r];
+  __syncthreads();
+  const int per = ((n + 1023) / 1024) | 1;
+  const int b = min(n, tid * per), e = min(n, b + per);
+  int tot = 0;
+  for (int r = b; r < e; ++r) tot += buf[r];
+  int incl = tot;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const int v = __shfl_up_sync(0xffffffffu, incl, o);
+    if (lane >= o) incl += v;
+  }
+  if (lane == 31) wsum[warp] = incl;
+  __syncthreads();
+  int run = incl - tot, total = 0;
+  for (int w = 0; w < 32; ++w) { if (w < warp) run += wsum[w]; total += wsum[w]; }
+  for (int r = b; r < e; ++r) { const int v = buf[r]; buf[r] = run; run += v; }
+  __syncthreads();
+  return total;
+}
+
 }  // namespace reidb200

@@ -11,6 +11,7 @@ namespace reidb200 {
 
 constexpr int EV_THREADS = 256;
 constexpr int EV_GOOD_CAP = 1024;
+constexpr int EV_UNROLL = 16;  // row values in flight per thread in the streaming pass (4 CTAs x 16 KB per SM)
 
 __device__ __forceinline__ uint32_t ev_key(float v, int descending) {
   const uint32_t u = float_to_ordered(v);
@@ -28,7 +29,7 @@ __device__ __forceinline__ bool ev_before(uint32_t ka, int ja, uint32_t kb, int 
   return ka < kb || (ka == kb && (descending ? ja > jb : ja < jb));
 }
 
-__global__ void __launch_bounds__(EV_THREADS)
+__global__ void __launch_bounds__(EV_THREADS, 4)
 eval_query_kernel(const float* __restrict__ mat, int G, int64_t ldm, int descending, const int32_t* __restrict__ ql,
                   const int32_t* __restrict__ qc, const int32_t* __restrict__ gl, const int32_t* __restrict__ gc,
                   double* __restrict__ ap_q, int32_t* __restrict__ first, int32_t* __restrict__ hist,
@@ -47,15 +48,15 @@ eval_query_kernel(const float* __restrict__ mat, int G, int64_t ldm, int descend
   __syncthreads();
 
   // ---- pass 1: good items (labels only; the gallery label vectors are L2 resident across queries)
-  for (int j0 = 0; j0 < G; j0 += 4 * EV_THREADS) {
-    int32_t l[4];
+  for (int j0 = 0; j0 < G; j0 += 8 * EV_THREADS) {
+    int32_t l[8];
 #pragma unroll
-    for (int u = 0; u < 4; ++u) {
+    for (int u = 0; u < 8; ++u) {
       const int j = j0 + u * EV_THREADS + tid;
       l[u] = j < G ? __ldg(gl + j) : -2;
     }
 #pragma unroll
-    for (int u = 0; u < 4; ++u) {
+    for (int u = 0; u < 8; ++u) {
       const int j = j0 + u * EV_THREADS + tid;
       if (j < G && l[u] == my_l && __ldg(gc + j) != my_c) {
         const int pos = atomicAdd(&s_ngood, 1);
@@ -89,15 +90,15 @@ eval_query_kernel(const float* __restrict__ mat, int G, int64_t ldm, int descend
   const int worst_c = scol[ngood - 1];
 
   // ---- pass 2: stream the row once
-  for (int j0 = 0; j0 < G; j0 += 4 * EV_THREADS) {
-    float v[4];
+  for (int j0 = 0; j0 < G; j0 += EV_UNROLL * EV_THREADS) {
+    float v[EV_UNROLL];
 #pragma unroll
-    for (int u = 0; u < 4; ++u) {
+    for (int u = 0; u < EV_UNROLL; ++u) {
       const int j = j0 + u * EV_THREADS + tid;
-      v[u] = j < G ? __ldg(row + j) : 0.f;
+      v[u] = j < G ? __ldcs(row + j) : 0.f;
     }
 #pragma unroll
-    for (int u = 0; u < 4; ++u) {
+    for (int u = 0; u < EV_UNROLL; ++u) {
       const int j = j0 + u * EV_THREADS + tid;
       if (j >= G) continue;
       const uint32_t kj = ev_key(v[u], descending);
@@ -138,45 +139,35 @@ eval_query_kernel(const float* __restrict__ mat, int G, int64_t ldm, int descend
 }
 
 // CMC[r] = float(#queries with first hit <= r) / Q ; mAP = (sum_q ap_q in query order) / Q
+// Single CTA; dynamic smem: G + 1 ints (cta_exclusive_scan_smem).
 __global__ void __launch_bounds__(1024)
 eval_finalize_kernel(const int32_t* __restrict__ hist, const double* __restrict__ ap_q, int Q, int G,
                      float* __restrict__ out_cmc, double* __restrict__ out_ap) {
+  extern __shared__ int sbuf[];
   __shared__ int wsum[32];
-  __shared__ int carry_s;
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  if (tid == 0) carry_s = 0;
-  __syncthreads();
-  for (int r0 = 0; r0 < G; r0 += 1024) {
-    const int r = r0 + tid;
-    int v = r < G ? hist[r] : 0;
-    // inclusive scan inside the warp
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-      const int n = __shfl_up_sync(0xffffffffu, v, o);
-      if (lane >= o) v += n;
-    }
-    if (lane == 31) wsum[warp] = v;
-    __syncthreads();
-    int before = carry_s;
-    for (int w = 0; w < warp; ++w) before += wsum[w];
-    const int total = v + before;
-    if (r < G) out_cmc[r] = __fdiv_rn((float)total, (float)Q);
-    __syncthreads();
-    if (tid == 1023) carry_s = total;
-    __syncthreads();
-  }
-  // mAP: the reference adds the per-query APs in query order (fp64); here 1024 contiguous chunks are summed in
-  // order and the chunk sums are added in order (same value up to ~1e-16 relative).
   __shared__ double part[1024];
-  const int per = (Q + 1023) / 1024;
+  const int tid = threadIdx.x;
+  // mAP partial sums: the reference adds the per-query APs in query order (fp64); here 1024 contiguous chunks are
+  // summed in order and the chunk sums are added in order (same value up to ~1e-16 relative).
+  const int perq = (Q + 1023) / 1024;
   double acc = 0.0;
-  for (int q = tid * per; q < min(Q, (tid + 1) * per); ++q) acc += ap_q[q];
+  for (int q = tid * perq; q < min(Q, (tid + 1) * perq); ++q) acc += ap_q[q];
   part[tid] = acc;
+  const int total = cta_exclusive_scan_smem(hist, G, sbuf, wsum);
+  if (tid == 0) sbuf[G] = total;
   __syncthreads();
-  if (tid == 0) {
-    double ap = 0.0;
-    for (int t = 0; t < 1024; ++t) ap += part[t];
-    *out_ap = ap / (double)Q;
+  for (int r = tid; r < G; r += 1024) out_cmc[r] = __fdiv_rn((float)sbuf[r + 1], (float)Q);  // inclusive prefix
+  if (tid < 32) {  // 32 chunk sums per lane, in order, then the 32 lane sums in order
+    double a2 = 0.0;
+    for (int t = 0; t < 32; ++t) a2 += part[tid * 32 + t];
+    __syncwarp();
+    part[tid] = a2;
+    __syncwarp();
+    if (tid == 0) {
+      double ap = 0.0;
+      for (int t = 0; t < 32; ++t) ap += part[t];
+      *out_ap = ap / (double)Q;
+    }
   }
 }
 
@@ -211,9 +202,15 @@ extern "C" int reidb200_eval_cmc_map(const float* mat, int Q, int G, int64_t ldm
   if (out_first) first = out_first;
   RB_CUDA(cudaMemsetAsync(hist, 0, (size_t)G * sizeof(int32_t), st));
   RB_CUDA(cudaMemsetAsync(status, 0, 64 * sizeof(int32_t), st));
+  static bool attr = false;
+  if (!attr) {
+    RB_CUDA(cudaFuncSetAttribute(eval_finalize_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    attr = true;
+  }
+  RB_REQUIRE((size_t)(G + 1) * sizeof(int) <= 200 * 1024, "eval_cmc_map: gallery larger than this build's limit (G=%d <= 51199)", G);
   { ProfScope _ps("eval_query_kernel", st); eval_query_kernel<<<Q, EV_THREADS, 0, st>>>(mat, G, ldm, descending, ql, qc, gl, gc, apq, first, hist, status); }
   RB_LAUNCH_CHECK("eval_query_kernel");
-  { ProfScope _ps("eval_finalize_kernel", st); eval_finalize_kernel<<<1, 1024, 0, st>>>(hist, apq, Q, G, out_cmc, out_ap); }
+  { ProfScope _ps("eval_finalize_kernel", st); eval_finalize_kernel<<<1, 1024, (size_t)(G + 1) * sizeof(int), st>>>(hist, apq, Q, G, out_cmc, out_ap); }
   RB_LAUNCH_CHECK("eval_finalize_kernel");
   return REIDB200_OK;
 }

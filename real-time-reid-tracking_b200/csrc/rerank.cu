@@ -265,33 +265,14 @@ __global__ void inv_count_kernel(const int32_t* __restrict__ cols, const float* 
     if (vals[(size_t)i * cap + t] != 0.f) atomicAdd(colcnt + cols[(size_t)i * cap + t], 1);
 }
 
-// colptr[0..N] = exclusive scan of colcnt; cursor = copy of colptr.  Single CTA.
+// colptr[0..N] = exclusive scan of colcnt; cursor = copy of colptr.  Single CTA; dynamic smem: N ints.
 __global__ void __launch_bounds__(1024)
 inv_scan_kernel(const int32_t* __restrict__ colcnt, int N, int32_t* __restrict__ colptr, int32_t* __restrict__ cursor) {
+  extern __shared__ int sm_i[];
   __shared__ int wsum[32];
-  __shared__ int carry_s;
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  if (tid == 0) carry_s = 0;
-  __syncthreads();
-  for (int r0 = 0; r0 < N; r0 += 1024) {
-    const int r = r0 + tid;
-    const int x = r < N ? colcnt[r] : 0;
-    int v = x;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-      const int nb = __shfl_up_sync(0xffffffffu, v, o);
-      if (lane >= o) v += nb;
-    }
-    if (lane == 31) wsum[warp] = v;
-    __syncthreads();
-    int before = carry_s;
-    for (int w = 0; w < warp; ++w) before += wsum[w];
-    if (r < N) { colptr[r] = before + v - x; cursor[r] = before + v - x; }
-    __syncthreads();
-    if (tid == 1023) carry_s = before + v;
-    __syncthreads();
-  }
-  if (tid == 0) colptr[N] = carry_s;
+  const int total = cta_exclusive_scan_smem(colcnt, N, sm_i, wsum);
+  for (int r = threadIdx.x; r < N; r += 1024) { const int v = sm_i[r]; colptr[r] = v; cursor[r] = v; }
+  if (threadIdx.x == 0) colptr[N] = total;
 }
 
 __global__ void inv_fill_kernel(const int32_t* __restrict__ cols, const float* __restrict__ vals,
@@ -497,6 +478,7 @@ static int jaccard_sparse_stages(const int32_t* rank, const float* sql2, int64_t
   if (!attr) {
     RB_CUDA(cudaFuncSetAttribute(expand_v_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 4096 * 12));
     RB_CUDA(cudaFuncSetAttribute(qexpand_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 8192 * 12));
+    RB_CUDA(cudaFuncSetAttribute(inv_scan_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448 - 256));
     RB_CUDA(cudaFuncSetAttribute(jaccard_rows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448 - 256));
     attr = true;
   }
@@ -519,7 +501,7 @@ static int jaccard_sparse_stages(const int32_t* rank, const float* sql2, int64_t
   RB_CUDA(cudaMemsetAsync(w.colcnt, 0, (size_t)(N + 1) * sizeof(int32_t), st));
   { ProfScope _ps("inv_count_kernel", st); inv_count_kernel<<<N, 128, 0, st>>>(w.v2cols, w.v2vals, w.v2cnt, N, d.cap2, w.colcnt); }
   RB_LAUNCH_CHECK("inv_count_kernel");
-  { ProfScope _ps("inv_scan_kernel", st); inv_scan_kernel<<<1, 1024, 0, st>>>(w.colcnt, N, w.colptr, w.cursor); }
+  { ProfScope _ps("inv_scan_kernel", st); inv_scan_kernel<<<1, 1024, (size_t)N * sizeof(int), st>>>(w.colcnt, N, w.colptr, w.cursor); }
   RB_LAUNCH_CHECK("inv_scan_kernel");
   { ProfScope _ps("inv_fill_kernel", st); inv_fill_kernel<<<N, 128, 0, st>>>(w.v2cols, w.v2vals, w.v2cnt, N, d.cap2, w.cursor, w.inv_row, w.inv_val); }
   RB_LAUNCH_CHECK("inv_fill_kernel");
