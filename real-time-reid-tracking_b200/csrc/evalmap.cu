@@ -48,22 +48,31 @@ eval_query_kernel(const float* __restrict__ mat, int G, int64_t ldm, int descend
   __syncthreads();
 
   // ---- pass 1: good items (labels only; the gallery label vectors are L2 resident across queries)
-  for (int j0 = 0; j0 < G; j0 += 8 * EV_THREADS) {
-    int32_t l[8];
+  auto good_candidate = [&](int j) {  // label matches: good unless same camera
+    if (__ldg(gc + j) != my_c) {
+      const int pos = atomicAdd(&s_ngood, 1);
+      if (pos < EV_GOOD_CAP) { gcol[pos] = j; gkey[pos] = ev_key(__ldg(row + j), descending); }
+    }
+  };
+  const int G4 = (reinterpret_cast<uintptr_t>(gl) & 15) == 0 ? G >> 2 : 0;  // 128-bit label loads when aligned
+  for (int j0 = 0; j0 < G4; j0 += 4 * EV_THREADS) {
+    int4 l[4];
 #pragma unroll
-    for (int u = 0; u < 8; ++u) {
-      const int j = j0 + u * EV_THREADS + tid;
-      l[u] = j < G ? __ldg(gl + j) : -2;
+    for (int u = 0; u < 4; ++u) {
+      const int j4 = j0 + u * EV_THREADS + tid;
+      l[u] = j4 < G4 ? __ldg(reinterpret_cast<const int4*>(gl) + j4) : make_int4(-2, -2, -2, -2);
     }
 #pragma unroll
-    for (int u = 0; u < 8; ++u) {
-      const int j = j0 + u * EV_THREADS + tid;
-      if (j < G && l[u] == my_l && __ldg(gc + j) != my_c) {
-        const int pos = atomicAdd(&s_ngood, 1);
-        if (pos < EV_GOOD_CAP) { gcol[pos] = j; gkey[pos] = ev_key(__ldg(row + j), descending); }
-      }
+    for (int u = 0; u < 4; ++u) {
+      const int j = 4 * (j0 + u * EV_THREADS + tid);
+      if (l[u].x == my_l) good_candidate(j);
+      if (l[u].y == my_l) good_candidate(j + 1);
+      if (l[u].z == my_l) good_candidate(j + 2);
+      if (l[u].w == my_l) good_candidate(j + 3);
     }
   }
+  for (int j = 4 * G4 + tid; j < G; j += EV_THREADS)
+    if (__ldg(gl + j) == my_l) good_candidate(j);
   __syncthreads();
   const int ngood = s_ngood;
   if (ngood == 0) {  // the cmc[0] == -1 sentinel: query skipped (evaluate.py:43-45,80-82)
@@ -88,6 +97,10 @@ eval_query_kernel(const float* __restrict__ mat, int G, int64_t ldm, int descend
   __syncthreads();
   const uint32_t worst_k = skey[ngood - 1];
   const int worst_c = scol[ngood - 1];
+  // float value of the worst good item: a plain float comparison against it is a cheap superset test of "ranked
+  // before the worst good" (the key order refines the float order: -0 < +0, index tie-breaks)
+  const uint32_t worst_o = descending ? ~worst_k : worst_k;
+  const float worst_v = __uint_as_float((worst_o & 0x80000000u) ? (worst_o & 0x7fffffffu) : ~worst_o);
 
   // ---- pass 2: stream the row once
   for (int j0 = 0; j0 < G; j0 += EV_UNROLL * EV_THREADS) {
@@ -101,8 +114,9 @@ eval_query_kernel(const float* __restrict__ mat, int G, int64_t ldm, int descend
     for (int u = 0; u < EV_UNROLL; ++u) {
       const int j = j0 + u * EV_THREADS + tid;
       if (j >= G) continue;
+      if (descending ? !(v[u] >= worst_v) : !(v[u] <= worst_v)) continue;  // the common case
       const uint32_t kj = ev_key(v[u], descending);
-      if (!ev_before(kj, j, worst_k, worst_c, descending)) continue;  // the common case
+      if (!ev_before(kj, j, worst_k, worst_c, descending)) continue;
       const int32_t l = __ldg(gl + j);
       if (l == -1 || (l == my_l && __ldg(gc + j) == my_c)) continue;  // junk
       int lo = 0, hi = ngood - 1;  // smallest s with j before good s (exists: j is before the worst good)

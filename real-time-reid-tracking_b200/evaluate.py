@@ -117,16 +117,103 @@ def get_evaluate_result(model, dataloader_query, dataloader_gallery):
     return evaluate_all(features_query, labels_query, cams_query, features_gallery, labels_gallery, cams_gallery)
 
 
-def evaluate_all_reranked_device(qf, ql, qc, gf, gl, gc, k1=20, k2=6, lambda_value=0.3):
+def _merge_into(merged, gf, qf):
+    """merged[:G] = gf, merged[G:] = qf without a torch.cat temporary: host inputs are copied straight into place."""
+    G = gf.shape[0]
+    for dst, src in ((merged[:G], gf), (merged[G:], qf)):
+        if not isinstance(src, torch.Tensor):
+            src = torch.from_numpy(np.ascontiguousarray(np.asarray(src, dtype=np.float32)))
+        dst.copy_(src, non_blocking=True)
+    return merged
+
+
+def evaluate_all_reranked_device(qf, ql, qc, gf, gl, gc, k1=20, k2=6, lambda_value=0.3, merged=None):
     """Re-ranked evaluation, device resident: merged = cat(gallery, query) (image_reid_inference.py:270), Jaccard
     re-ranking blended with the Euclidean distance, CMC/mAP on the re-ranked Q x G distance.  Returns CUDA tensors
-    (CMC f32[G], mAP f64[1]) without a host sync."""
-    qf = L.as_f32_cuda(qf)
-    gf = L.as_f32_cuda(gf, qf.device)
-    G, Q = gf.shape[0], qf.shape[0]
-    merged = torch.cat([gf, qf], 0)
+    (CMC f32[G], mAP f64[1]) without a host sync.  `merged` = optional preallocated f32[G+Q, D] device buffer."""
+    G, Q, D = int(gf.shape[0]), int(qf.shape[0]), int(qf.shape[1])
+    if merged is None:
+        dev = qf.device if isinstance(qf, torch.Tensor) and qf.is_cuda else L.require_device()
+        merged = torch.empty((G + Q, D), dtype=torch.float32, device=dev)
+    _merge_into(merged, gf, qf)
     dist = ops.jaccard(merged, k1, k2, False, lambda_value, rows=(G, Q), cols=(0, G))
     return ops.eval_cmc_map(dist, _labels(ql), _labels(qc), _labels(gl), _labels(gc), descending=False)
+
+
+class RerankedEvalStream:
+    """Back-to-back re-ranked evaluations of many (query, gallery) sets with the copies hidden: the host->device copy
+    of set i+1 runs on a copy stream while set i is computed, results come back through pinned buffers.
+
+        ev = RerankedEvalStream(depth=2)
+        t0 = ev.submit(qf, ql, qc, gf, gl, gc)        # returns at once
+        t1 = ev.submit(...)                            # its H2D overlaps the kernels of t0
+        CMC, ap = ev.result(t0)                        # same values as evaluate_all_reranked
+
+    One evaluation is the unit the reference computes in image_reid_inference.py:270-315; this class only schedules
+    several of them (CUDA streams + events, no threads)."""
+
+    def __init__(self, depth=2, device=None):
+        self.dev = device or L.require_device()
+        self.depth = max(1, int(depth))
+        self.copy_stream = torch.cuda.Stream(self.dev)
+        self.compute_stream = torch.cuda.Stream(self.dev)
+        self.slots = [dict(busy=None, free=None) for _ in range(self.depth)]
+        self.n = 0
+
+    def _buffers(self, slot, Q, G, D):
+        key = (Q, G, D)
+        if slot.get("key") != key:
+            with torch.cuda.device(self.dev):
+                slot["merged"] = torch.empty((G + Q, D), dtype=torch.float32, device=self.dev)
+                slot["lab"] = torch.empty(2 * (Q + G), dtype=torch.int32, device=self.dev)
+                slot["cmc_h"] = torch.empty(G, dtype=torch.float32).pin_memory()
+                slot["ap_h"] = torch.empty(1, dtype=torch.float64).pin_memory()
+            slot["key"] = key
+        return slot
+
+    def submit(self, qf, ql, qc, gf, gl, gc, k1=20, k2=6, lambda_value=0.3):
+        G, Q, D = int(gf.shape[0]), int(qf.shape[0]), int(qf.shape[1])
+        ticket = self.n
+        slot = self.slots[ticket % self.depth]
+        if slot["busy"] is not None:  # the slot's previous evaluation must have been collected or at least finished
+            slot["busy"].synchronize()
+        self._buffers(slot, Q, G, D)
+        lab = slot["lab"]
+        with torch.cuda.stream(self.copy_stream):
+            if slot["free"] is not None:
+                self.copy_stream.wait_event(slot["free"])  # kernels of the slot's previous occupant are done
+            _merge_into(slot["merged"], gf, qf)
+            off = 0
+            views = []
+            for v, n in ((ql, Q), (qc, Q), (gl, G), (gc, G)):
+                t = _labels(v)
+                if t.dtype != torch.int32:
+                    t = t.to(torch.int32)
+                lab[off:off + n].copy_(t, non_blocking=True)
+                views.append(lab[off:off + n])
+                off += n
+            ready = torch.cuda.Event()
+            ready.record(self.copy_stream)
+        with torch.cuda.stream(self.compute_stream):
+            self.compute_stream.wait_event(ready)
+            dist = ops.jaccard(slot["merged"], k1, k2, False, lambda_value, rows=(G, Q), cols=(0, G))
+            cmc, ap = ops.eval_cmc_map(dist, views[0], views[1], views[2], views[3], descending=False)
+            free = torch.cuda.Event()
+            free.record(self.compute_stream)
+            slot["cmc_h"].copy_(cmc, non_blocking=True)
+            slot["ap_h"].copy_(ap, non_blocking=True)
+            done = torch.cuda.Event()
+            done.record(self.compute_stream)
+        slot["free"], slot["busy"], slot["ticket"] = free, done, ticket
+        self.n += 1
+        return ticket
+
+    def result(self, ticket):
+        slot = self.slots[ticket % self.depth]
+        if slot.get("ticket") != ticket:
+            raise ValueError("RerankedEvalStream.result: ticket %d is no longer held (depth=%d)" % (ticket, self.depth))
+        slot["busy"].synchronize()
+        return slot["cmc_h"].clone(), float(slot["ap_h"][0])
 
 
 def evaluate_all_reranked(qf, ql, qc, gf, gl, gc, k1=20, k2=6, lambda_value=0.3, verbose=True):

@@ -65,3 +65,28 @@ def test_jaccard_limits(rb):
 
     with pytest.raises(ValueError):
         F.compute_jaccard_distance(torch.zeros(10, 8), k1=20, print_flag=False)
+
+
+def test_reranked_eval_stream_matches_sync(rb):
+    """The pipelined evaluator (copies of set i+1 under the kernels of set i) returns what the synchronous call does,
+    for sets of different shapes sharing its slots, and both agree with the oracle."""
+    from reidb200 import evaluate as E, synth
+
+    sets = [synth.market_like(Q=60 + 20 * s, G=400 + 50 * s, D=64, n_ids=30, seed=10 + s) for s in range(5)]
+    keys = ("qf", "ql", "qc", "gf", "gl", "gc")
+    ev = E.RerankedEvalStream(depth=2)
+    tickets, got = [], {}
+    for i, d in enumerate(sets):
+        tickets.append(ev.submit(*[d[k] for k in keys], 20, 6, 0.3))
+        if i >= 1:
+            got[i - 1] = ev.result(tickets[i - 1])
+    got[len(sets) - 1] = ev.result(tickets[-1])
+    with pytest.raises(ValueError):
+        ev.result(tickets[0])  # its slot has been reused
+    for i, d in enumerate(sets):
+        cmc, ap = E.evaluate_all_reranked(*[d[k] for k in keys], 20, 6, 0.3, verbose=False)
+        assert torch.equal(cmc, got[i][0]) and ap == got[i][1]
+        dist = O.re_ranking_from_feats(d["qf"], d["gf"], 20, 6, 0.3)
+        ocmc, oap = O.evaluate_all_from_dist(dist, d["ql"], d["qc"], d["gl"], d["gc"])
+        # re-ranked distances agree to ~1e-6; a near-tie may swap two neighbours, so compare the reductions loosely
+        assert np.abs(cmc.numpy() - np.asarray(ocmc)).max() <= 2.0 / len(d["ql"]) + 1e-6 and abs(ap - oap) <= 2e-3
