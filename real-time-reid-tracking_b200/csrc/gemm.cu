@@ -114,6 +114,10 @@ struct GemmArgs {
   int cred_max;
   int tma_out;  // the output tensor map is valid (16-byte aligned rows): epilogue stores through the TMA engine
   int symmetric;  // A == B (self distances): only tiles with tn >= tm are computed, each also stored transposed
+  // box-major output (the re-ranking workspace): the matrix is stored as 32 x 32 boxes of 4 KB, box (rb, cb) at float
+  // offset (rb * blocked + cb) * 1024, row-major inside; blocked = boxes per box row (0 = plain row-major).  Every
+  // epilogue store is then one contiguous 4 KB piece of DRAM instead of 32 pieces of 128 B a row stride apart.
+  int blocked;
   int debug;      // timing experiments only (REIDB200_GEMM_DEBUG): 1 = no mirror store, 2 = no stores, 4 = no epilogue
 };
 
@@ -231,8 +235,15 @@ __device__ __forceinline__ void epilogue_slab(const GemmArgs& a, const CUtensorM
       o[j + 3] = epi_value<KIND>(o[j + 3], ia_mine, s4.w, xx_mine, y4.w);
     }
     if (full) {
+      float t[16];
 #pragma unroll
-      for (int j = 0; j < 32; ++j) red = red_max ? fmaxf(red, o[j]) : fminf(red, o[j]);
+      for (int j = 0; j < 16; ++j) t[j] = red_max ? fmaxf(o[j], o[j + 16]) : fminf(o[j], o[j + 16]);
+#pragma unroll
+      for (int w = 8; w >= 1; w >>= 1) {
+#pragma unroll
+        for (int j = 0; j < w; ++j) t[j] = red_max ? fmaxf(t[j], t[j + w]) : fminf(t[j], t[j + w]);
+      }
+      red = t[0];
     } else {
 #pragma unroll
       for (int j = 0; j < 32; ++j)
@@ -249,7 +260,8 @@ __device__ __forceinline__ void epilogue_slab(const GemmArgs& a, const CUtensorM
       ptx::fence_proxy_async();
       __syncwarp();
       if (lane == 0) {
-        ptx::tma_store_2d(tmO, ptx::smem_u32(sb), col0, row0);
+        if (a.blocked) ptx::tma_store_2d(tmO, ptx::smem_u32(sb), 0, ((row0 >> 5) * a.blocked + (col0 >> 5)) * 32);
+        else ptx::tma_store_2d(tmO, ptx::smem_u32(sb), col0, row0);
         ptx::bulk_commit();
       }
       if (sym_t) {
@@ -258,15 +270,27 @@ __device__ __forceinline__ void epilogue_slab(const GemmArgs& a, const CUtensorM
         // nothing to wait for).  Its chunk reduction (mirror row = column col0 + lane, over this warp's rows) reads
         // the column back from the staged direct box, which the TMA engine is reading concurrently.
         if (want_red) {
-          float red_t = red_max ? -INFINITY : INFINITY;
+          float v[32];
 #pragma unroll
-          for (int rr = 0; rr < 32; ++rr) {
-            const float v = sb[rr * 32 + ((((lane >> 2) ^ (rr & 7)) << 2) | (lane & 3))];
-            if (rr < rows_here) red_t = red_max ? fmaxf(red_t, v) : fminf(red_t, v);
+          for (int rr = 0; rr < 32; ++rr) v[rr] = sb[rr * 32 + ((((lane >> 2) ^ (rr & 7)) << 2) | (lane & 3))];
+          if (rows_here < 32) {  // ragged last row block (warp-uniform): rows beyond m do not take part
+            const float pad = red_max ? -INFINITY : INFINITY;
+#pragma unroll
+            for (int rr = 0; rr < 32; ++rr) v[rr] = rr < rows_here ? v[rr] : pad;
           }
+#pragma unroll
+          for (int w = 16; w >= 1; w >>= 1) {
+#pragma unroll
+            for (int rr = 0; rr < w; ++rr) v[rr] = red_max ? fmaxf(v[rr], v[rr + w]) : fminf(v[rr], v[rr + w]);
+          }
+          const float red_t = v[0];
           if (col0 + lane < a.n) a.cred[(size_t)(col0 + lane) * a.ldcr + (row0 >> 5)] = red_t;
         }
-        if (my_row < a.m) {
+        if (a.blocked) {  // box (col0 / 32, row0 / 32), padded to whole boxes: no edge guards
+          float* mp = a.out + ((size_t)(col0 >> 5) * a.blocked + (row0 >> 5)) * 1024 + lane;
+#pragma unroll
+          for (int j = 0; j < 32; ++j) mp[j * 32] = o[j];
+        } else if (my_row < a.m) {
           float* mp = a.out + (size_t)col0 * a.ldo + my_row;
           if (full) {
 #pragma unroll
@@ -645,7 +669,7 @@ static int make_output_map(CUtensorMap* tm, float* out, int m, int n, int64_t ld
 
 int gemm_split_launch(const void* packedA, const float* xx, const float* isa, int m, const void* packedB, const float* yy,
                       const float* isb, int n, int d, int kind, float* out, int64_t ldo, cudaStream_t st, float* chunk_red,
-                      int64_t ld_chunk_red, int chunk_red_max) {
+                      int64_t ld_chunk_red, int chunk_red_max, int blocked) {
   if (m == 0 || n == 0) return REIDB200_OK;
   RB_REQUIRE(isa && isb, "distmat: operand scales missing");
   RB_REQUIRE(kind >= 0 && kind <= 3, "distmat: unknown kind %d", kind);
@@ -666,7 +690,12 @@ int gemm_split_launch(const void* packedA, const float* xx, const float* isa, in
   memset(&tmO, 0, sizeof(tmO));
   a.tma_out = (ldo & 3) == 0 && (reinterpret_cast<uintptr_t>(out) & 15) == 0 &&
               (yy == nullptr || (reinterpret_cast<uintptr_t>(yy) & 15) == 0) && (reinterpret_cast<uintptr_t>(isb) & 15) == 0;
-  if (a.tma_out) {
+  a.blocked = blocked ? ceil_div(n, 32) : 0;
+  if (blocked) {
+    RB_REQUIRE(a.tma_out, "distmat: the box-major layout needs 16-byte aligned buffers");
+    rc = make_output_map(&tmO, out, ceil_div(m, 32) * a.blocked * 32, 32, 32);  // a tall matrix of 128-byte rows
+    if (rc) return rc;
+  } else if (a.tma_out) {
     rc = make_output_map(&tmO, out, m, n, ldo);
     if (rc) return rc;
   }

@@ -22,7 +22,7 @@ int pack_rows_launch(const float* x, int rows, int64_t ldx, int d, void* packed,
 // consumed by topk_rows_launch to skip the chunks that cannot hold a top-k element.
 int gemm_split_launch(const void* packedA, const float* xx, const float* isa, int m, const void* packedB, const float* yy,
                       const float* isb, int n, int d, int kind, float* out, int64_t ldo, cudaStream_t st,
-                      float* chunk_red = nullptr, int64_t ld_chunk_red = 0, int chunk_red_max = 0);
+                      float* chunk_red = nullptr, int64_t ld_chunk_red = 0, int chunk_red_max = 0, int blocked = 0);
 
 // TMA descriptor of a packed operand [rows, 2*dp] fp16: box = {64 k-elements, box_rows}, SWIZZLE_128B, OOB reads as zero.
 int make_operand_map(CUtensorMap* tm, const void* packed, int rows, int dp, int box_rows);
