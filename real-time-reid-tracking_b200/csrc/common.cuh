@@ -98,6 +98,56 @@ __device__ __forceinline__ uint32_t float_to_ordered(float f) {
   return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
 }
 
+// Bitonic sort of 32*S keys held by one warp, ascending, element e = lane*S + s (S consecutive elements per lane, S a
+// power of two), with an optional 32-bit payload.  Compare-exchanges at distance < S stay inside a lane (registers);
+// larger distances are one shuffle per element.  Everything unrolls: k[] and v[] stay in registers.
+template <int S, bool HAS_VAL>
+__device__ __forceinline__ void warp_bitonic_sort(uint32_t (&k)[S], uint32_t (&v)[S], int lane) {
+#pragma unroll
+  for (int kk = 2; kk <= 32 * S; kk <<= 1) {
+#pragma unroll
+    for (int j = kk >> 1; j > 0; j >>= 1) {
+      if (j >= S) {
+        const int lj = j / S;
+        const bool lower = (lane & lj) == 0;
+#pragma unroll
+        for (int s = 0; s < S; ++s) {
+          const bool up = ((lane * S + s) & kk) == 0;
+          const uint32_t ok = __shfl_xor_sync(0xffffffffu, k[s], lj);
+          uint32_t ov = 0;
+          if (HAS_VAL) ov = __shfl_xor_sync(0xffffffffu, v[s], lj);
+          const bool take = (lower == up) ? (ok < k[s]) : (ok > k[s]);
+          if (take) { k[s] = ok; if (HAS_VAL) v[s] = ov; }
+        }
+      } else {
+#pragma unroll
+        for (int s = 0; s < S; ++s) {
+          if ((s & j) == 0) {
+            const bool up = ((lane * S + s) & kk) == 0;
+            const uint32_t a = k[s], b = k[s | j];
+            if ((a > b) == up) {
+              k[s] = b; k[s | j] = a;
+              if (HAS_VAL) { const uint32_t t = v[s]; v[s] = v[s | j]; v[s | j] = t; }
+            }
+          }
+        }
+      }
+    }
+  }
+}
+
+// exclusive prefix of x over the lanes of a warp; total returned through `total`
+__device__ __forceinline__ int warp_exclusive_scan(int x, int lane, int& total) {
+  int incl = x;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const int n = __shfl_up_sync(0xffffffffu, incl, o);
+    if (lane >= o) incl += n;
+  }
+  total = __shfl_sync(0xffffffffu, incl, 31);
+  return incl - x;
+}
+
 // Exclusive scan of in[0..n) by ONE CTA of 1024 threads through shared memory: coalesced loads into buf[0..n), every
 // thread scans a contiguous chunk (odd chunk length: conflict-free banks), one block-wide scan of the chunk totals.
 // Afterwards buf[r] = sum of in[0..r); returns the total.  wsum = 32 ints of shared memory.  Ends with a barrier.

@@ -43,6 +43,43 @@ krecip_kernel(const int32_t* __restrict__ rank, int N, int k1_cols, int kc, int 
   if (lane == 0) out_cnt[i] = cnt;
 }
 
+// R(i,k1) and R(i,k1/2) in one pass over the neighbour rows (kh = min(k1/2 + 1, k1_cols) <= kc): the half list keeps
+// the forward neighbours f < kh whose first kh backward neighbours contain i.
+__global__ void __launch_bounds__(256)
+krecip_both_kernel(const int32_t* __restrict__ rank, int N, int k1_cols, int kc, int kh, int32_t* __restrict__ full_idx,
+                   int32_t* __restrict__ full_cnt, int32_t* __restrict__ half_idx, int32_t* __restrict__ half_cnt) {
+  const int i = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (i >= N) return;
+  int cnt = 0, cnth = 0;
+  for (int f0 = 0; f0 < kc; f0 += 32) {
+    const int f = f0 + lane;
+    bool keep = false, keeph = false;
+    int c = -1;
+    if (f < kc) {
+      c = rank[(size_t)i * k1_cols + f];
+      if (c >= 0 && c < N) {
+        const int32_t* b = rank + (size_t)c * k1_cols;
+        for (int t = 0; t < kc; ++t) {
+          const bool m = b[t] == i;
+          keep |= m;
+          keeph |= m && t < kh;
+        }
+        keeph = keeph && f < kh;
+      }
+    }
+    const uint32_t ballot = __ballot_sync(0xffffffffu, keep), balloth = __ballot_sync(0xffffffffu, keeph);
+    const uint32_t below = (1u << lane) - 1;
+    if (keep) full_idx[(size_t)i * kc + cnt + __popc(ballot & below)] = c;
+    if (keeph) half_idx[(size_t)i * kh + cnth + __popc(balloth & below)] = c;
+    cnt += __popc(ballot);
+    cnth += __popc(balloth);
+  }
+  for (int t = cnt + lane; t < kc; t += 32) full_idx[(size_t)i * kc + t] = -1;
+  for (int t = cnth + lane; t < kh; t += 32) half_idx[(size_t)i * kh + t] = -1;
+  if (lane == 0) { full_cnt[i] = cnt; half_cnt[i] = cnth; }
+}
+
 // ------------------------------------------------------------------------------------ D4
 constexpr int EXP_THREADS = 128;
 
@@ -182,6 +219,115 @@ expand_v_kernel(const int32_t* __restrict__ rfull, const int32_t* __restrict__ r
   if (tid == 0) vcnt[i] = nu;
 }
 
+// Warp-per-row variant for the common small case (k1 <= 32 and k1 + k1 * wh <= 256 candidate slots, e.g. k1 = 20):
+// same slots, same 2/3 rule, but the 256 keys live in registers (8 per lane), the sort is warp_bitonic_sort (no
+// block barriers) and the duplicate removal is a neighbour comparison + a warp scan.
+constexpr int EXW_WARPS = 4;
+
+__global__ void __launch_bounds__(EXW_WARPS * 32)
+expand_v_warp_kernel(const int32_t* __restrict__ rfull, const int32_t* __restrict__ rfull_cnt, int wf,
+                     const int32_t* __restrict__ rhalf, const int32_t* __restrict__ rhalf_cnt, int wh,
+                     const float* __restrict__ sql2, int64_t lds, const float* __restrict__ sqnorm, int N, int cap,
+                     int use_f16, int32_t* __restrict__ vcols, float* __restrict__ vvals, int32_t* __restrict__ vcnt) {
+  __shared__ int s_base[EXW_WARPS][32], s_nc[EXW_WARPS][32], s_inter[EXW_WARPS][32];
+  constexpr uint32_t SENT = 0x7fffffffu;
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  const int i = blockIdx.x * EXW_WARPS + w;
+  if (i >= N) return;  // whole warps leave; the kernel has no block-wide barrier
+  const int nb = rfull_cnt[i];
+  int b_mine = -1, nc_mine = 0;
+  if (lane < nb) {
+    b_mine = rfull[(size_t)i * wf + lane];
+    nc_mine = rhalf_cnt[b_mine];
+  }
+  s_base[w][lane] = b_mine;
+  s_nc[w][lane] = nc_mine;
+  s_inter[w][lane] = 0;
+  __syncwarp();
+  const uint32_t inv_wh = (65536u + (uint32_t)wh - 1u) / (uint32_t)wh;  // q / wh == (q * inv_wh) >> 16 for q < 256
+  uint32_t k[8], nov[8];
+  int tl[8];
+#pragma unroll
+  for (int s = 0; s < 8; ++s) {
+    const int e = lane * 8 + s;
+    uint32_t key = SENT;
+    int t = -1;
+    if (e < wf) {
+      if (e < nb) key = (uint32_t)s_base[w][e];
+    } else {
+      const uint32_t q = (uint32_t)(e - wf);
+      const int tt = (int)((q * inv_wh) >> 16);
+      const int a = (int)q - tt * wh;
+      if (tt < nb && a < s_nc[w][tt]) {
+        key = (uint32_t)rhalf[(size_t)s_base[w][tt] * wh + a];
+        t = tt;
+      }
+    }
+    k[s] = key;
+    tl[s] = t;
+  }
+  // 2/3 rule against the UNEXPANDED R(i,k1) (faiss_utils.py:192-197): inter_t = #(R(c_t,k1/2) & R(i,k1))
+  int hit[8];
+#pragma unroll
+  for (int s = 0; s < 8; ++s) hit[s] = 0;
+  for (int b2 = 0; b2 < nb; ++b2) {
+    const uint32_t bv = (uint32_t)s_base[w][b2];
+#pragma unroll
+    for (int s = 0; s < 8; ++s) hit[s] += (k[s] == bv);
+  }
+#pragma unroll
+  for (int s = 0; s < 8; ++s)
+    if (tl[s] >= 0 && hit[s]) atomicAdd(&s_inter[w][tl[s]], hit[s]);
+  __syncwarp();
+#pragma unroll
+  for (int s = 0; s < 8; ++s)
+    if (tl[s] >= 0 && !((double)s_inter[w][tl[s]] > (2.0 / 3.0) * (double)s_nc[w][tl[s]])) k[s] = SENT;
+  warp_bitonic_sort<8, false>(k, nov, lane);
+  // unique keys (np.unique order), their output slots
+  const uint32_t last_prev = __shfl_up_sync(0xffffffffu, k[7], 1);
+  bool head[8];
+  int cnt = 0;
+#pragma unroll
+  for (int s = 0; s < 8; ++s) {
+    const uint32_t prev = s == 0 ? last_prev : k[s - 1];
+    head[s] = k[s] != SENT && ((lane == 0 && s == 0) || prev != k[s]);
+    cnt += head[s] ? 1 : 0;
+  }
+  int nu;
+  int slot = warp_exclusive_scan(cnt, lane, nu);
+  const float xi = sqnorm[i];
+  float nd[8];
+  float lmax = -INFINITY;
+#pragma unroll
+  for (int s = 0; s < 8; ++s) {
+    nd[s] = -INFINITY;
+    if (head[s]) {
+      // dist = 2 - 2 x_i.x_c (faiss_utils.py:201-204), with x_i.x_c = (|x_i|^2 + |x_c|^2 - sql2)/2
+      const int c = (int)k[s];
+      const float dot = 0.5f * ((xi + sqnorm[c]) - sql2[(size_t)i * lds + c]);
+      nd[s] = -(2.0f - 2.0f * dot);
+      lmax = fmaxf(lmax, nd[s]);
+    }
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) lmax = fmaxf(lmax, __shfl_xor_sync(0xffffffffu, lmax, o));
+  float lsum = 0.f;
+#pragma unroll
+  for (int s = 0; s < 8; ++s)
+    if (head[s]) { nd[s] = expf(nd[s] - lmax); lsum += nd[s]; }
+  const float gsum = warp_sum(lsum);
+#pragma unroll
+  for (int s = 0; s < 8; ++s)
+    if (head[s]) {
+      float v = __fdiv_rn(nd[s], gsum);
+      if (use_f16) v = __half2float(__float2half_rn(v));
+      vcols[(size_t)i * cap + slot] = (int32_t)k[s];
+      vvals[(size_t)i * cap + slot] = v;
+      ++slot;
+    }
+  if (lane == 0) vcnt[i] = nu;
+}
+
 // ------------------------------------------------------------------------------------ D5
 // V_qe[i] = mean(V[rank[i,:k2]], axis=0) (faiss_utils.py:209-214): merge of k2 sorted sparse rows.
 // Sums run in neighbour order j = 0..k2-1 like the reference's row-by-row reduction (zeros are exact
@@ -192,15 +338,22 @@ constexpr int QE_MAX_K2 = 32;
 __global__ void __launch_bounds__(QE_THREADS)
 qexpand_kernel(const int32_t* __restrict__ rank, int k1_cols, int k2, const int32_t* __restrict__ vcols,
                const float* __restrict__ vvals, const int32_t* __restrict__ vcnt, int cap1, int cap2, int use_f16,
-               int32_t* __restrict__ qcols, float* __restrict__ qvals, int32_t* __restrict__ qcnt) {
+               int32_t* __restrict__ qcols, float* __restrict__ qvals, int32_t* __restrict__ qcnt,
+               const int32_t* __restrict__ row_list, const int32_t* __restrict__ row_list_len, int N,
+               int32_t* __restrict__ colcnt) {
   extern __shared__ int sm_i[];
+  // rows: all of them, or (after qexpand_warp_kernel) the listed ones it left behind
+  const int nrows = row_list ? *row_list_len : N;
+  for (int idx = blockIdx.x; idx < nrows; idx += gridDim.x) {
+  const int i = row_list ? row_list[idx] : idx;
+  __syncthreads();  // shared memory of the previous row is free
   int* mcol = sm_i;
   int* head = mcol + cap2;
   float* mval = reinterpret_cast<float*>(head + cap2);
   __shared__ int s_row[QE_MAX_K2], s_len[QE_MAX_K2], s_off[QE_MAX_K2 + 1];
   __shared__ int warp_tot[QE_THREADS / 32];
 
-  const int i = blockIdx.x, tid = threadIdx.x;
+  const int tid = threadIdx.x;
   if (tid < k2) {
     const int r = rank[(size_t)i * k1_cols + tid];
     s_row[tid] = r;
@@ -251,9 +404,93 @@ qexpand_kernel(const int32_t* __restrict__ rank, int k1_cols, int k2, const int3
       const int slot = head[p];
       qcols[(size_t)i * cap2 + slot] = c;
       qvals[(size_t)i * cap2 + slot] = v;
+      if (colcnt && v != 0.f) atomicAdd(colcnt + c, 1);  // D6 column counts, fused
     }
   }
   if (tid == 0) qcnt[i] = nu;
+  }
+}
+
+// Warp-per-row variant for rows whose k2 lists hold at most 256 entries in total (the common case): the entries are
+// keyed (column, neighbour j), sorted by warp_bitonic_sort with their weights as payload, staged in shared memory,
+// and every run of equal columns is summed in neighbour order by its first element.  Rows with more entries are
+// appended to long_list and left to qexpand_kernel.
+constexpr int QEW_WARPS = 4;
+
+__global__ void __launch_bounds__(QEW_WARPS * 32)
+qexpand_warp_kernel(const int32_t* __restrict__ rank, int k1_cols, int k2, const int32_t* __restrict__ vcols,
+                    const float* __restrict__ vvals, const int32_t* __restrict__ vcnt, int N, int cap1, int cap2,
+                    int use_f16, int32_t* __restrict__ qcols, float* __restrict__ qvals, int32_t* __restrict__ qcnt,
+                    int32_t* __restrict__ colcnt, int32_t* __restrict__ long_list, int32_t* __restrict__ long_len) {
+  __shared__ int s_row[QEW_WARPS][32], s_off[QEW_WARPS][33];
+  __shared__ uint32_t s_key[QEW_WARPS][256];
+  __shared__ float s_val[QEW_WARPS][256];
+  constexpr uint32_t SENT = 0xffffffffu;
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  const int i = blockIdx.x * QEW_WARPS + w;
+  if (i >= N) return;  // whole warps leave; the kernel has no block-wide barrier
+  int r = -1, len = 0;
+  if (lane < k2) {
+    r = rank[(size_t)i * k1_cols + lane];
+    len = vcnt[r];
+  }
+  int n;
+  const int off = warp_exclusive_scan(len, lane, n);
+  if (n > 256) {
+    if (lane == 0) long_list[atomicAdd(long_len, 1)] = i;
+    return;
+  }
+  s_row[w][lane] = r;
+  s_off[w][lane] = off;  // lanes >= k2 hold n
+  if (lane == 31) s_off[w][32] = n;
+  __syncwarp();
+  uint32_t k[8], v[8];
+#pragma unroll
+  for (int s = 0; s < 8; ++s) {
+    const int e = lane * 8 + s;
+    k[s] = SENT;
+    v[s] = 0u;
+    if (e < n) {
+      int j = 0;
+      while (e >= s_off[w][j + 1]) ++j;
+      const size_t src = (size_t)s_row[w][j] * cap1 + (e - s_off[w][j]);
+      k[s] = ((uint32_t)vcols[src] << 5) | (uint32_t)j;
+      v[s] = __float_as_uint(vvals[src]);
+    }
+  }
+  warp_bitonic_sort<8, true>(k, v, lane);
+#pragma unroll
+  for (int s = 0; s < 8; ++s) {
+    s_key[w][lane * 8 + s] = k[s];
+    s_val[w][lane * 8 + s] = __uint_as_float(v[s]);
+  }
+  __syncwarp();
+  const uint32_t last_prev = __shfl_up_sync(0xffffffffu, k[7], 1);
+  bool head[8];
+  int cnt = 0;
+#pragma unroll
+  for (int s = 0; s < 8; ++s) {
+    const uint32_t prev = s == 0 ? last_prev : k[s - 1];
+    head[s] = k[s] != SENT && ((lane == 0 && s == 0) || (prev >> 5) != (k[s] >> 5));
+    cnt += head[s] ? 1 : 0;
+  }
+  int nu;
+  int slot = warp_exclusive_scan(cnt, lane, nu);
+#pragma unroll
+  for (int s = 0; s < 8; ++s)
+    if (head[s]) {
+      const int e = lane * 8 + s;
+      const uint32_t c = k[s] >> 5;
+      float sum = __uint_as_float(v[s]);
+      for (int t = e + 1; t < n && (s_key[w][t] >> 5) == c; ++t) sum = __fadd_rn(sum, s_val[w][t]);
+      float val = __fdiv_rn(sum, (float)k2);
+      if (use_f16) val = __half2float(__float2half_rn(val));
+      qcols[(size_t)i * cap2 + slot] = (int32_t)c;
+      qvals[(size_t)i * cap2 + slot] = val;
+      if (colcnt && val != 0.f) atomicAdd(colcnt + c, 1);  // D6 column counts, fused
+      ++slot;
+    }
+  if (lane == 0) qcnt[i] = nu;
 }
 
 // ------------------------------------------------------------------------------------ D6
@@ -445,7 +682,7 @@ static void carve_sparse(C& c, int N, int k1, int k2, const RerankDims& d, Spars
   } else {
     t.v2cols = t.v1cols; t.v2vals = t.v1vals; t.v2cnt = t.v1cnt;
   }
-  t.colcnt = c.template take<int32_t>(N + 1);
+  t.colcnt = c.template take<int32_t>(N + 2);  // [N + 1] = number of rows left to the CTA-wide qexpand kernel
   t.colptr = c.template take<int32_t>(N + 1);
   t.cursor = c.template take<int32_t>(N + 1);
   t.inv_row = c.template take<int32_t>((size_t)N * d.cap2);
@@ -483,24 +720,34 @@ static int jaccard_sparse_stages(const int32_t* rank, const float* sql2, int64_t
     attr = true;
   }
   const int wpb = 8;
-  { ProfScope _ps("krecip_kernel(k1)", st); krecip_kernel<<<ceil_div(N, wpb), wpb * 32, 0, st>>>(rank, N, k1, k1, k1, w.rfull, w.rfull_cnt); }
-  RB_LAUNCH_CHECK("krecip_kernel(k1)");
-  { ProfScope _ps("krecip_kernel(k1/2)", st); krecip_kernel<<<ceil_div(N, wpb), wpb * 32, 0, st>>>(rank, N, k1, d.wh, d.wh, w.rhalf, w.rhalf_cnt); }
-  RB_LAUNCH_CHECK("krecip_kernel(k1/2)");
-  int expP = 32;
-  while (expP < d.cap1) expP <<= 1;
-  { ProfScope _ps("expand_v_kernel", st); expand_v_kernel<<<N, EXP_THREADS, (size_t)expP * 12, st>>>(w.rfull, w.rfull_cnt, k1, w.rhalf, w.rhalf_cnt, d.wh, sql2,
-                                                                lds, sqnorm, N, d.cap1, expP, use_f16, w.v1cols, w.v1vals,
-                                                                w.v1cnt); }
-  RB_LAUNCH_CHECK("expand_v_kernel");
-  if (k2 > 1) {
-    { ProfScope _ps("qexpand_kernel", st); qexpand_kernel<<<N, QE_THREADS, (size_t)d.cap2 * 12, st>>>(rank, k1, k2, w.v1cols, w.v1vals, w.v1cnt, d.cap1, d.cap2,
-                                                               use_f16, w.v2cols, w.v2vals, w.v2cnt); }
-    RB_LAUNCH_CHECK("qexpand_kernel");
+  { ProfScope _ps("krecip_kernel", st); krecip_both_kernel<<<ceil_div(N, wpb), wpb * 32, 0, st>>>(rank, N, k1, k1, d.wh, w.rfull, w.rfull_cnt, w.rhalf, w.rhalf_cnt); }
+  RB_LAUNCH_CHECK("krecip_both_kernel");
+  if (k1 <= 32 && k1 + k1 * d.wh <= 256) {
+    { ProfScope _ps("expand_v_kernel", st); expand_v_warp_kernel<<<ceil_div(N, EXW_WARPS), EXW_WARPS * 32, 0, st>>>(
+        w.rfull, w.rfull_cnt, k1, w.rhalf, w.rhalf_cnt, d.wh, sql2, lds, sqnorm, N, d.cap1, use_f16, w.v1cols, w.v1vals, w.v1cnt); }
+  } else {
+    int expP = 32;
+    while (expP < d.cap1) expP <<= 1;
+    { ProfScope _ps("expand_v_kernel", st); expand_v_kernel<<<N, EXP_THREADS, (size_t)expP * 12, st>>>(w.rfull, w.rfull_cnt, k1, w.rhalf, w.rhalf_cnt, d.wh, sql2,
+                                                                  lds, sqnorm, N, d.cap1, expP, use_f16, w.v1cols, w.v1vals,
+                                                                  w.v1cnt); }
   }
-  RB_CUDA(cudaMemsetAsync(w.colcnt, 0, (size_t)(N + 1) * sizeof(int32_t), st));
-  { ProfScope _ps("inv_count_kernel", st); inv_count_kernel<<<N, 128, 0, st>>>(w.v2cols, w.v2vals, w.v2cnt, N, d.cap2, w.colcnt); }
-  RB_LAUNCH_CHECK("inv_count_kernel");
+  RB_LAUNCH_CHECK("expand_v_kernel");
+  RB_CUDA(cudaMemsetAsync(w.colcnt, 0, (size_t)(N + 2) * sizeof(int32_t), st));
+  if (k2 > 1) {
+    // D5 + the column counts of D6: warp kernel first, the CTA kernel picks up the rows it marked as too long
+    { ProfScope _ps("qexpand_kernel", st); qexpand_warp_kernel<<<ceil_div(N, QEW_WARPS), QEW_WARPS * 32, 0, st>>>(
+        rank, k1, k2, w.v1cols, w.v1vals, w.v1cnt, N, d.cap1, d.cap2, use_f16, w.v2cols, w.v2vals, w.v2cnt, w.colcnt,
+        w.cursor, w.colcnt + N + 1); }  // the cursor array is free until inv_scan_kernel: it holds the long-row list
+    RB_LAUNCH_CHECK("qexpand_warp_kernel");
+    { ProfScope _ps("qexpand_kernel(long rows)", st); qexpand_kernel<<<min(N, 2 * num_sms()), QE_THREADS, (size_t)d.cap2 * 12, st>>>(
+        rank, k1, k2, w.v1cols, w.v1vals, w.v1cnt, d.cap1, d.cap2, use_f16, w.v2cols, w.v2vals, w.v2cnt, w.cursor, w.colcnt + N + 1, N,
+        w.colcnt); }
+    RB_LAUNCH_CHECK("qexpand_kernel");
+  } else {
+    { ProfScope _ps("inv_count_kernel", st); inv_count_kernel<<<N, 128, 0, st>>>(w.v2cols, w.v2vals, w.v2cnt, N, d.cap2, w.colcnt); }
+    RB_LAUNCH_CHECK("inv_count_kernel");
+  }
   { ProfScope _ps("inv_scan_kernel", st); inv_scan_kernel<<<1, 1024, (size_t)N * sizeof(int), st>>>(w.colcnt, N, w.colptr, w.cursor); }
   RB_LAUNCH_CHECK("inv_scan_kernel");
   { ProfScope _ps("inv_fill_kernel", st); inv_fill_kernel<<<N, 128, 0, st>>>(w.v2cols, w.v2vals, w.v2cnt, N, d.cap2, w.cursor, w.inv_row, w.inv_val); }

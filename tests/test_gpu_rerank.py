@@ -90,3 +90,16 @@ def test_reranked_eval_stream_matches_sync(rb):
         ocmc, oap = O.evaluate_all_from_dist(dist, d["ql"], d["qc"], d["gl"], d["gc"])
         # re-ranked distances agree to ~1e-6; a near-tie may swap two neighbours, so compare the reductions loosely
         assert np.abs(cmc.numpy() - np.asarray(ocmc)).max() <= 2.0 / len(d["ql"]) + 1e-6 and abs(ap - oap) <= 2e-3
+
+
+@pytest.mark.parametrize("k1,k2", [(30, 10), (40, 1), (8, 4)])
+def test_jaccard_other_k_vs_oracle(rb, k1, k2):
+    """k1 / k2 outside the warp-kernel fast paths (more than 256 candidate slots per row, long merged lists) and a
+    tiny k1 go through the CTA kernels; all of them must agree with the oracle."""
+    from reidb200 import faiss_utils as F, synth
+
+    d = synth.market_like(Q=120, G=680, D=64, n_ids=25, seed=21)
+    feats = np.concatenate([d["gf"], d["qf"]], 0)
+    J = F.compute_jaccard_distance(torch.from_numpy(feats), k1=k1, k2=k2, print_flag=False)
+    Jo = O.compute_jaccard_distance(feats, k1=k1, k2=k2)
+    np.testing.assert_allclose(J, Jo, atol=5e-6)
