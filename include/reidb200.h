@@ -232,6 +232,25 @@ int reidb200_cosine_distance(const float* a, int na, int64_t lda, const float* b
                              int d, int normalized, float* out, void* workspace,
                              size_t workspace_bytes, void* stream);
 
+/* ------------------------------------------------------------------------------------------
+ * N2: pairwise box costs of the other boxmot trackers.
+ *   modes 0-3  iou_batch / giou_batch / diou_batch / ciou_batch of xyxy boxes, computed and returned in the
+ *              inputs' dtype (float32 or float64)      replaces boxmot/utils/iou.py:4-164
+ *   mode 4     bbox_ious: the "+1" pixel IoU on float32 tlbr boxes -> float32
+ *   mode 5     iou_distance = 1 - bbox_ious                                replaces boxmot/utils/matching.py:71-114,216-248
+ * boxes_a [n,4], boxes_b [k,4], out [n,k] (row-major, dense). */
+enum {
+  REIDB200_BOX_IOU = 0, REIDB200_BOX_GIOU = 1, REIDB200_BOX_DIOU = 2, REIDB200_BOX_CIOU = 3,
+  REIDB200_BOX_PLUS_ONE = 4, REIDB200_BOX_IOU_DISTANCE = 5
+};
+int reidb200_box_pairs(const void* boxes_a, int n, const void* boxes_b, int k, int is_f64, int mode, void* out,
+                       void* stream);
+/*   fuse_score (det_scores != NULL): out f64[n,k] = 1 - (1 - cost) * score[col]
+ *   fuse_iou   (tlbr_a, tlbr_b != NULL): out (cost's dtype) = 1 - (1 - cost) * (1 + iou_sim) / 2, iou_sim from bbox_ious
+ *   cost f32 or f64 [n,k]                                                  replaces boxmot/utils/matching.py:189-213 */
+int reidb200_fuse_cost(const void* cost, int cost_is_f64, int n, int k, const double* det_scores,
+                       const float* tlbr_a, const float* tlbr_b, void* out, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

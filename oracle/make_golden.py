@@ -290,10 +290,66 @@ def gold_assoc():
           cosine=np.asarray(cd), pdist=np.asarray(pd), nn_cosine=np.asarray(nn))
 
 
+# ---------------------------------------------------------------- N2 box-pair costs of the other boxmot trackers
+def gold_boxpairs():
+    IO = ref_import.load_file_pkg("boxmot.utils.iou")
+    MT = ref_import.load_file_pkg("boxmot.utils.matching")
+    rng = np.random.default_rng(3)
+
+    def boxes(n):
+        xy = rng.uniform(0, 1500, (n, 2))
+        wh = rng.uniform(5, 300, (n, 2))
+        return np.concatenate([xy, xy + wh], 1)
+
+    a64, b64 = boxes(23), boxes(31)
+    b64[3] = a64[2]            # identical pair: IoU 1, CIoU's alpha = 0/0 (NaN in the reference too)
+    b64[4, :2] += 5000.0       # far away: no overlap
+    b64[4, 2:] += 5000.0
+    out = {"a64": a64, "b64": b64}
+    for dt, tag in ((np.float64, "64"), (np.float32, "32")):
+        a, b = a64.astype(dt), b64.astype(dt)
+        for mode, fn in (("iou", IO.iou_batch), ("giou", IO.giou_batch), ("diou", IO.diou_batch), ("ciou", IO.ciou_batch)):
+            with np.errstate(invalid="ignore"):
+                want = fn(a, b)
+                got = O.box_pairs(a, b, mode)
+            assert want.dtype == dt and np.array_equal(want, got, equal_nan=True), (mode, tag)
+            out["%s_%s" % (mode, tag)] = want
+    a32, b32 = a64.astype(np.float32), b64.astype(np.float32)
+    want = MT.bbox_ious(a32, b32)
+    assert np.array_equal(want, O.bbox_ious(a32, b32))
+    out["plus_one"] = want
+    want = MT.iou_distance(list(a32), list(b32))
+    assert want.dtype == np.float32 and np.array_equal(want, O.iou_distance(a32, b32))
+    out["iou_distance"] = want
+
+    class Obj:
+        def __init__(self, tlbr, score=1.0, feat=None):
+            self.tlbr, self.score, self.curr_feat, self.smooth_feat = tlbr, score, feat, feat
+
+    scores = rng.uniform(0.1, 1.0, 31)
+    ft, fd = rng.standard_normal((23, 32)).astype(np.float32), rng.standard_normal((31, 32)).astype(np.float32)
+    trk = [Obj(a32[i], 1.0, ft[i]) for i in range(23)]
+    det = [Obj(b32[i], float(scores[i]), fd[i]) for i in range(31)]
+    want = MT.fuse_score(MT.iou_distance(trk, det), det)
+    assert want.dtype == np.float64 and np.array_equal(want, O.fuse_score(out["iou_distance"], scores))
+    out["fuse_score"] = want
+    emb = MT.embedding_distance(trk, det)
+    np.testing.assert_allclose(O.embedding_distance(ft, fd), emb, rtol=0, atol=1e-12)
+    out["embedding"] = emb
+    want = MT.fuse_iou(emb, trk, det)
+    assert want.dtype == np.float64 and np.array_equal(want, O.fuse_iou(emb, a32, b32))
+    out["fuse_iou64"] = want
+    emb32 = emb.astype(np.float32)
+    want = MT.fuse_iou(emb32, trk, det)
+    assert want.dtype == np.float32 and np.array_equal(want, O.fuse_iou(emb32, a32, b32))
+    out["fuse_iou32"] = want
+    _save("boxpairs", scores=scores, feat_t=ft, feat_d=fd, **out)
+
+
 def main():
     assert ref_import.available(), "/root/reference not present: fixtures can only be (re)generated in the build container"
     ref_import.install()
-    for fn in (gold_dist, gold_eval, gold_jaccard, gold_preprocess, gold_assoc):
+    for fn in (gold_dist, gold_eval, gold_jaccard, gold_preprocess, gold_assoc, gold_boxpairs):
         print(fn.__name__)
         fn()
     print("oracle pinned against the reference; fixtures in tests/golden/")

@@ -602,3 +602,100 @@ def match_frame(fr, max_dist, max_iou_dist, mc_lambda):
         ic = np.zeros((len(cand), len(um_d)))
     m_b, um_b, um_d = min_cost_matching_from_cost(ic, max_iou_dist, cand, um_d)
     return m_a + m_b, list(set(um_a + um_b)), um_d
+
+
+# --------------------------------------------------------------------------
+# N2  the other boxmot cost families: pairwise box overlaps of
+# boxmot/utils/iou.py:4-164 (xyxy boxes, arithmetic in the inputs' dtype), the
+# "+1" pixel IoU of boxmot/utils/matching.py:216-248 (float32 inputs), and the
+# score / IoU fusions of matching.py:189-213.
+# --------------------------------------------------------------------------
+def _pair_terms(b1, b2):
+    """Broadcast views (N,1) x (1,K) of the corners plus the overlap area and plain IoU."""
+    a = np.asarray(b1)[:, None, :]
+    b = np.asarray(b2)[None, :, :]
+    iw = np.maximum(0.0, np.minimum(a[..., 2], b[..., 2]) - np.maximum(a[..., 0], b[..., 0]))
+    ih = np.maximum(0.0, np.minimum(a[..., 3], b[..., 3]) - np.maximum(a[..., 1], b[..., 1]))
+    inter = iw * ih
+    union = (a[..., 2] - a[..., 0]) * (a[..., 3] - a[..., 1]) + (b[..., 2] - b[..., 0]) * (b[..., 3] - b[..., 1]) - inter
+    return a, b, inter, inter / union
+
+
+def box_pairs(b1, b2, mode: str = "iou"):
+    """iou_batch / giou_batch / diou_batch / ciou_batch (boxmot/utils/iou.py:4-23, 26-59, 62-102, 105-164):
+    [N,K] matrix; giou/diou/ciou are rescaled to (0,1) by (x + 1) / 2 like the reference."""
+    a, b, inter, iou = _pair_terms(b1, b2)
+    if mode == "iou":
+        return iou
+    ex1, ey1 = np.minimum(a[..., 0], b[..., 0]), np.minimum(a[..., 1], b[..., 1])
+    ex2, ey2 = np.maximum(a[..., 2], b[..., 2]), np.maximum(a[..., 3], b[..., 3])
+    if mode == "giou":
+        enclose = (ex2 - ex1) * (ey2 - ey1)
+        return (iou - (enclose - inter) / enclose + 1.0) / 2.0
+    cx1, cy1 = (a[..., 0] + a[..., 2]) / 2.0, (a[..., 1] + a[..., 3]) / 2.0
+    cx2, cy2 = (b[..., 0] + b[..., 2]) / 2.0, (b[..., 1] + b[..., 3]) / 2.0
+    inner = (cx1 - cx2) ** 2 + (cy1 - cy2) ** 2
+    outer = (ex2 - ex1) ** 2 + (ey2 - ey1) ** 2
+    if mode == "diou":
+        return (iou - inner / outer + 1) / 2.0
+    if mode == "ciou":
+        w1, h1 = a[..., 2] - a[..., 0], a[..., 3] - a[..., 1] + 1.0
+        w2, h2 = b[..., 2] - b[..., 0], b[..., 3] - b[..., 1] + 1.0
+        at = np.arctan(w2 / h2) - np.arctan(w1 / h1)
+        v = (4 / (np.pi ** 2)) * (at ** 2)
+        alpha = v / ((1 - iou) + v)
+        return (iou - inner / outer - alpha * v + 1) / 2.0
+    raise ValueError(mode)
+
+
+def bbox_ious(boxes, query_boxes):
+    """The '+1' pixel-inclusive IoU of boxmot/utils/matching.py:216-248 on float32 tlbr boxes: widths/heights and the
+    overlap are float32, the union is promoted to float64 by `float(...)`, the quotient is stored as float32."""
+    bx = np.asarray(boxes, np.float32)
+    qb = np.asarray(query_boxes, np.float32)
+    one = np.float32(1)
+    a = bx[:, None, :]
+    q = qb[None, :, :]
+    iw = np.minimum(a[..., 2], q[..., 2]) - np.maximum(a[..., 0], q[..., 0]) + one
+    ih = np.minimum(a[..., 3], q[..., 3]) - np.maximum(a[..., 1], q[..., 1]) + one
+    qa = (q[..., 2] - q[..., 0] + one) * (q[..., 3] - q[..., 1] + one)
+    ba = (a[..., 2] - a[..., 0] + one) * (a[..., 3] - a[..., 1] + one)
+    inter = iw * ih                                   # float32
+    ua = ((ba + qa) - inter).astype(np.float64)       # float32 arithmetic, then float(...)
+    out = np.zeros(inter.shape, np.float32)
+    ok = (iw > 0) & (ih > 0)
+    out[ok] = (inter.astype(np.float64)[ok] / ua[ok]).astype(np.float32)
+    return out
+
+
+def iou_distance(atlbrs, btlbrs):
+    """1 - bbox_ious (matching.py:71-114), float32; empty inputs give an empty float32 matrix."""
+    if len(atlbrs) == 0 or len(btlbrs) == 0:
+        return np.zeros((len(atlbrs), len(btlbrs)), np.float32)
+    return 1 - bbox_ious(atlbrs, btlbrs)
+
+
+def fuse_score(cost, det_scores):
+    """matching.py:203-213: 1 - (1 - cost) * score, float64 through the float64 score vector."""
+    if np.asarray(cost).size == 0:
+        return cost
+    return 1 - (1 - np.asarray(cost)) * np.asarray(det_scores, np.float64)[None, :]
+
+
+def fuse_iou(cost, atlbrs, btlbrs):
+    """matching.py:189-200: 1 - (1 - cost) * (1 + iou_sim) / 2 (the score factor is commented out in the reference)."""
+    if np.asarray(cost).size == 0:
+        return cost
+    iou_sim = 1 - iou_distance(atlbrs, btlbrs)
+    return 1 - (1 - np.asarray(cost)) * (1 + iou_sim) / 2
+
+
+def embedding_distance(track_feats, det_feats):
+    """matching.py:138-160 with metric='cosine': max(0, 1 - u.v / (|u| |v|)) in float64 on float32 inputs
+    (scipy.spatial.distance.cdist promotes to double)."""
+    t = np.asarray(track_feats, np.float32).astype(np.float64)
+    d = np.asarray(det_feats, np.float32).astype(np.float64)
+    if t.size == 0 or d.size == 0:
+        return np.zeros((len(t), len(d)), np.float32)
+    sim = (t @ d.T) / (np.linalg.norm(t, axis=1)[:, None] * np.linalg.norm(d, axis=1)[None, :])
+    return np.maximum(0.0, 1.0 - sim)

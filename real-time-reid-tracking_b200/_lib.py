@@ -19,6 +19,7 @@ OK, EINVAL, ECUDA, ELIMIT = 0, -1, -2, -3
 RESIZE_CV_LINEAR, RESIZE_PIL_ANTIALIAS = 0, 1
 DIST_EUCLID, DIST_COSINE_HALF, DIST_DOT, DIST_SQL2 = 0, 1, 2, 3
 IOU_PLAIN, IOU_DIOU = 0, 1
+BOX_MODES = {"iou": 0, "giou": 1, "diou": 2, "ciou": 3, "plus_one": 4, "iou_distance": 5}
 ASSOC_CLAMP_APP, ASSOC_CLAMP_IOU, ASSOC_NO_GATE, ASSOC_SIMT = 1, 2, 4, 8
 
 _vp, _i, _i64, _sz, _f, _d = C.c_void_p, C.c_int, C.c_int64, C.c_size_t, C.c_float, C.c_double
@@ -63,6 +64,8 @@ SIGNATURES = {
     "reidb200_gating_distance": (_i, [_vp, _vp, _vp, _i, _i, _vp, _vp]),
     "reidb200_cosine_distance_workspace_bytes": (_sz, [_i, _i, _i]),
     "reidb200_cosine_distance": (_i, [_vp, _i, _i64, _vp, _i, _i64, _i, _i, _vp, _vp, _sz, _vp]),
+    "reidb200_box_pairs": (_i, [_vp, _i, _vp, _i, _i, _i, _vp, _vp]),
+    "reidb200_fuse_cost": (_i, [_vp, _i, _i, _i, _vp, _vp, _vp, _vp, _vp]),
 }
 
 _lib = None

@@ -1,5 +1,7 @@
-"""Drop-in for the StrongSORT half of yolov8_tracking/boxmot/utils/matching.py: chi2inv95 (:12-22), _pdist
-(:255-275), _cosine_distance (:278-298), _nn_cosine_distance (:321-339), NearestNeighborDistanceMetric (:342-409).
+"""Drop-in for yolov8_tracking/boxmot/utils/matching.py.  StrongSORT half: chi2inv95 (:12-22), _pdist (:255-275),
+_cosine_distance (:278-298), _nn_cosine_distance (:321-339), NearestNeighborDistanceMetric (:342-409).  ByteTrack /
+BoT-SORT half: ious (:71-88), iou_distance (:91-112), embedding_distance (:138-160), fuse_iou (:189-200),
+fuse_score (:203-213), bbox_ious (:216-248) on csrc/boxpairs.cu.
 
 The per-track sample lists live in a device-resident ring buffer (ops.Gallery); `distance` is one launch of the
 fused association kernel without the gate, returning the same float64 [T,M] matrix of float32 values.
@@ -39,6 +41,71 @@ def _nn_cosine_distance(x, y):
 def _nn_euclidean_distance(x, y):
     """The reference's version is broken (torch.min on an ndarray); fixed by restatement."""
     return np.maximum(0.0, _pdist(x, y).min(axis=0))
+
+
+def bbox_ious(boxes, query_boxes):
+    """'+1' pixel IoU of float32 tlbr boxes, [N,K] float32 (matching.py:216-248; a Python double loop there)."""
+    return ops.box_pairs(np.asarray(boxes, np.float32), np.asarray(query_boxes, np.float32), "plus_one").cpu().numpy()
+
+
+def ious(atlbrs, btlbrs):
+    """matching.py:71-88: float32 [len(a), len(b)]; empty inputs give an empty matrix without a launch."""
+    out = np.zeros((len(atlbrs), len(btlbrs)), dtype=np.float32)
+    if out.size == 0:
+        return out
+    return bbox_ious(np.ascontiguousarray(atlbrs, dtype=np.float32), np.ascontiguousarray(btlbrs, dtype=np.float32))
+
+
+def _tlbrs(tracks):
+    if len(tracks) > 0 and isinstance(tracks[0], np.ndarray):
+        return tracks
+    return [t.tlbr for t in tracks]
+
+
+def iou_distance(atracks, btracks):
+    """1 - IoU of the tracks' tlbr boxes (or of plain box arrays), matching.py:91-112."""
+    if (len(atracks) > 0 and isinstance(atracks[0], np.ndarray)) or (len(btracks) > 0 and isinstance(btracks[0], np.ndarray)):
+        atlbrs, btlbrs = atracks, btracks
+    else:
+        atlbrs, btlbrs = [t.tlbr for t in atracks], [t.tlbr for t in btracks]
+    if len(atlbrs) == 0 or len(btlbrs) == 0:
+        return 1 - np.zeros((len(atlbrs), len(btlbrs)), dtype=np.float32)
+    return ops.box_pairs(np.ascontiguousarray(atlbrs, dtype=np.float32), np.ascontiguousarray(btlbrs, dtype=np.float32),
+                         "iou_distance").cpu().numpy()
+
+
+def embedding_distance(tracks, detections, metric="cosine"):
+    """max(0, cosine distance) of the tracks' smooth_feat to the detections' curr_feat (matching.py:138-160).  The
+    reference goes through scipy's float64 cdist; here the product runs on the fp32-accurate tensor-core path
+    (|difference| <= 1e-6) and the matrix comes back as float64 like cdist's."""
+    cost = np.zeros((len(tracks), len(detections)), dtype=np.float32)
+    if cost.size == 0:
+        return cost
+    if metric != "cosine":
+        raise ValueError("embedding_distance: only the cosine metric is used by the reference trackers")
+    det = np.asarray([t.curr_feat for t in detections], dtype=np.float32)
+    trk = np.asarray([t.smooth_feat for t in tracks], dtype=np.float32)
+    d = ops.cosine_distance(trk, det).cpu().numpy().astype(np.float64)
+    return np.maximum(0.0, d)
+
+
+def fuse_iou(cost_matrix, tracks, detections):
+    """1 - (1 - cost) * (1 + iou_sim) / 2 (matching.py:189-200)."""
+    cost_matrix = np.asarray(cost_matrix)
+    if cost_matrix.size == 0:
+        return cost_matrix
+    a = np.ascontiguousarray(_tlbrs(tracks), dtype=np.float32)
+    b = np.ascontiguousarray(_tlbrs(detections), dtype=np.float32)
+    return ops.fuse_cost(cost_matrix, tlbr_a=a, tlbr_b=b).cpu().numpy()
+
+
+def fuse_score(cost_matrix, detections):
+    """1 - (1 - cost) * det.score (matching.py:203-213), float64."""
+    cost_matrix = np.asarray(cost_matrix)
+    if cost_matrix.size == 0:
+        return cost_matrix
+    scores = np.array([d.score for d in detections]) if len(detections) and hasattr(detections[0], "score") else np.asarray(detections)
+    return ops.fuse_cost(cost_matrix, det_scores=scores).cpu().numpy()
 
 
 class NearestNeighborDistanceMetric(object):

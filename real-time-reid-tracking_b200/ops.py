@@ -343,6 +343,55 @@ def iou_matrix(bbox_tlwh, cand_tlwh, mode="iou"):
     return out
 
 
+def _boxes(x, dtype, dev):
+    t = torch.as_tensor(np.ascontiguousarray(np.asarray(x.detach().cpu() if isinstance(x, torch.Tensor) else x, dtype=dtype)))
+    return t.reshape(-1, 4).to(dev)
+
+
+def box_pairs(boxes_a, boxes_b, mode="iou", dtype=None):
+    """Pairwise xyxy box metric [N,K] on device: iou / giou / diou / ciou (input dtype, float32 or float64), plus_one
+    (bbox_ious) and iou_distance (float32).  boxmot/utils/iou.py:4-164, boxmot/utils/matching.py:71-114,216-248."""
+    dev = L.require_device()
+    if mode in ("plus_one", "iou_distance"):
+        dtype = np.float32
+    elif dtype is None:
+        dtype = np.float32 if np.asarray(boxes_a).dtype == np.float32 and np.asarray(boxes_b).dtype == np.float32 else np.float64
+    a, b = _boxes(boxes_a, dtype, dev), _boxes(boxes_b, dtype, dev)
+    out = torch.empty((a.shape[0], b.shape[0]), dtype=torch.float32 if dtype == np.float32 else torch.float64, device=dev)
+    if a.shape[0] and b.shape[0]:
+        with torch.cuda.device(dev):
+            L.check(L.load().reidb200_box_pairs(a.data_ptr(), a.shape[0], b.data_ptr(), b.shape[0], 0 if dtype == np.float32 else 1,
+                                               L.BOX_MODES[mode], out.data_ptr(), L.stream_ptr()))
+    return out
+
+
+def fuse_cost(cost, det_scores=None, tlbr_a=None, tlbr_b=None):
+    """fuse_score (det_scores given -> f64) or fuse_iou (both box sets given -> cost's dtype); matching.py:189-213."""
+    dev = L.require_device()
+    c = torch.as_tensor(cost)
+    if c.dtype not in (torch.float32, torch.float64):
+        c = c.to(torch.float64)
+    c = c.to(dev).contiguous()
+    n, k = c.shape
+    is64 = c.dtype == torch.float64
+    sc = a = b = None
+    if det_scores is not None:
+        sc = torch.as_tensor(np.asarray(det_scores, dtype=np.float64)).reshape(-1).to(dev)
+        if sc.numel() != k:
+            raise ValueError("fuse_score: one score per detection (column) expected")
+        out = torch.empty((n, k), dtype=torch.float64, device=dev)
+    else:
+        a, b = _boxes(tlbr_a, np.float32, dev), _boxes(tlbr_b, np.float32, dev)
+        if a.shape[0] != n or b.shape[0] != k:
+            raise ValueError("fuse_iou: box sets do not match the cost matrix")
+        out = torch.empty((n, k), dtype=c.dtype, device=dev)
+    if n and k:
+        with torch.cuda.device(dev):
+            L.check(L.load().reidb200_fuse_cost(c.data_ptr(), 1 if is64 else 0, n, k, L.ptr(sc), L.ptr(a), L.ptr(b), out.data_ptr(),
+                                               L.stream_ptr()))
+    return out
+
+
 def gating_distance(x4, SI, meas):
     dev = L.require_device()
     x4 = torch.as_tensor(np.asarray(x4, dtype=np.float64)).reshape(-1, 4).to(dev)

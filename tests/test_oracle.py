@@ -98,3 +98,22 @@ def test_assoc_sequence(golden):
         assert sorted(ud) == fr["unmatched_dets"].tolist()
         n += len(m)
     assert n > 20
+
+
+def test_boxpairs_n2(golden):
+    """N2: the oracle's pairwise box costs against the reference's iou.py / matching.py outputs (bit-exact)."""
+    g = golden("boxpairs")
+    for tag, dt in (("64", np.float64), ("32", np.float32)):
+        a, b = g["a64"].astype(dt), g["b64"].astype(dt)
+        for mode in ("iou", "giou", "diou", "ciou"):
+            with np.errstate(invalid="ignore"):
+                got = O.box_pairs(a, b, mode)
+            assert got.dtype == dt and np.array_equal(got, g["%s_%s" % (mode, tag)], equal_nan=True), (mode, tag)
+    a32, b32 = g["a64"].astype(np.float32), g["b64"].astype(np.float32)
+    assert np.array_equal(O.bbox_ious(a32, b32), g["plus_one"])
+    assert np.array_equal(O.iou_distance(a32, b32), g["iou_distance"])
+    assert np.array_equal(O.fuse_score(g["iou_distance"], g["scores"]), g["fuse_score"])
+    assert np.array_equal(O.fuse_iou(g["embedding"], a32, b32), g["fuse_iou64"])
+    assert np.array_equal(O.fuse_iou(g["embedding"].astype(np.float32), a32, b32), g["fuse_iou32"])
+    np.testing.assert_allclose(O.embedding_distance(g["feat_t"], g["feat_d"]), g["embedding"], atol=1e-12)
+    assert O.iou_distance(np.zeros((0, 4)), b32).shape == (0, 31)
