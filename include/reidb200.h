@@ -251,6 +251,14 @@ int reidb200_box_pairs(const void* boxes_a, int n, const void* boxes_b, int k, i
 int reidb200_fuse_cost(const void* cost, int cost_is_f64, int n, int k, const double* det_scores,
                        const float* tlbr_a, const float* tlbr_b, void* out, void* stream);
 
+/*   OC-SORT / DeepOCSORT association cost, one launch per frame: out_iou f64[D,T] = iou_batch(detections, trackers),
+ *   out_angle f64[D,T] = the velocity-direction-consistency term (valid * (pi/2 - |acos|) / pi * vdc_weight * score).
+ *   detections f64[D,5] (x1,y1,x2,y2,score), trackers f64[T,5], velocities f64[T,2] (dy,dx), previous_obs f64[T,5]
+ *   (score < 0 = no previous observation)                replaces boxmot/utils/association.py:6-16,107-140 */
+int reidb200_ocsort_cost(const double* detections, int D, const double* trackers, int T, const double* velocities,
+                         const double* previous_obs, double vdc_weight, double* out_iou, double* out_angle,
+                         void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -346,10 +346,46 @@ def gold_boxpairs():
     _save("boxpairs", scores=scores, feat_t=ft, feat_d=fd, **out)
 
 
+def gold_ocsort():
+    """OC-SORT associate: the reference's own iou_matrix / final_cost, captured at its linear_assignment call."""
+    A = ref_import.load_file_pkg("boxmot.utils.association")
+    from scipy.optimize import linear_sum_assignment
+
+    rng = np.random.default_rng(5)
+    T, D = 17, 21
+    xy, wh = rng.uniform(0, 900, (T, 2)), rng.uniform(20, 200, (T, 2))
+    trk = np.concatenate([xy, xy + wh, np.zeros((T, 1))], 1)
+    perm = rng.permutation(T)
+    det = np.concatenate([trk[perm, :4] + rng.normal(0, 6, (T, 4)), rng.uniform(0.3, 1, (T, 1))], 1)
+    xy, wh = rng.uniform(0, 900, (D - T, 2)), rng.uniform(20, 200, (D - T, 2))
+    det = np.concatenate([det, np.concatenate([xy, xy + wh, rng.uniform(0.3, 1, (D - T, 1))], 1)], 0)
+    det[1, :4] = trk[perm[0], :4] + 3.0   # two detections on one track: the Hungarian branch is taken
+    vel = rng.normal(0, 1, (T, 2))
+    vel /= np.linalg.norm(vel, axis=1, keepdims=True)
+    vel[3] = 0.0
+    prev = np.concatenate([trk[:, :4] - rng.normal(0, 10, (T, 4)), np.ones((T, 1))], 1)
+    prev[[2, 9]] = -1.0                   # no previous observation
+    captured = {}
+
+    def capture(cost):
+        captured["cost"] = np.array(cost)
+        x, y = linear_sum_assignment(cost)
+        return np.array(list(zip(x, y)))
+
+    A.linear_assignment = capture
+    m, ud, ut = A.associate(det, trk, 0.3, vel, prev, 0.2)
+    assert "cost" in captured, "fixture must take the assignment branch"
+    iou, ang = O.ocsort_cost(det, trk, vel, prev, 0.2)
+    Y, X = A.speed_direction_batch(det, prev)
+    np.testing.assert_allclose(-(iou + ang), captured["cost"], rtol=0, atol=1e-15)
+    _save("ocsort", det=det, trk=trk, vel=vel, prev=prev, vdc=np.float64(0.2), final_cost=captured["cost"], matches=m,
+          unmatched_dets=np.asarray(ud), unmatched_trks=np.asarray(ut), Y=Y, X=X)
+
+
 def main():
     assert ref_import.available(), "/root/reference not present: fixtures can only be (re)generated in the build container"
     ref_import.install()
-    for fn in (gold_dist, gold_eval, gold_jaccard, gold_preprocess, gold_assoc, gold_boxpairs):
+    for fn in (gold_dist, gold_eval, gold_jaccard, gold_preprocess, gold_assoc, gold_boxpairs, gold_ocsort):
         print(fn.__name__)
         fn()
     print("oracle pinned against the reference; fixtures in tests/golden/")

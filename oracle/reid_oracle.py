@@ -699,3 +699,22 @@ def embedding_distance(track_feats, det_feats):
         return np.zeros((len(t), len(d)), np.float32)
     sim = (t @ d.T) / (np.linalg.norm(t, axis=1)[:, None] * np.linalg.norm(d, axis=1)[None, :])
     return np.maximum(0.0, 1.0 - sim)
+
+
+def ocsort_cost(detections, trackers, velocities, previous_obs, vdc_weight):
+    """(iou_matrix [D,T], angle_diff_cost [D,T]) of OC-SORT's associate (boxmot/utils/association.py:6-16 and
+    :122-140), float64: the two terms of final_cost = -(iou + angle [+ emb])."""
+    det = np.asarray(detections, np.float64)
+    trk = np.asarray(trackers, np.float64)
+    vel = np.asarray(velocities, np.float64)
+    prev = np.asarray(previous_obs, np.float64)
+    cx1, cy1 = (det[:, 0] + det[:, 2]) / 2.0, (det[:, 1] + det[:, 3]) / 2.0          # [D]
+    cx2, cy2 = (prev[:, 0] + prev[:, 2])[:, None] / 2.0, (prev[:, 1] + prev[:, 3])[:, None] / 2.0  # [T,1]
+    dx, dy = cx1 - cx2, cy1 - cy2                                                       # [T,D]
+    norm = np.sqrt(dx ** 2 + dy ** 2) + 1e-6
+    dx, dy = dx / norm, dy / norm
+    cosang = np.clip(vel[:, 1:2] * dx + vel[:, 0:1] * dy, -1, 1)
+    diff = (np.pi / 2.0 - np.abs(np.arccos(cosang))) / np.pi
+    valid = np.where(prev[:, 4] < 0, 0.0, 1.0)[:, None]
+    angle = (((valid * diff) * vdc_weight).T) * det[:, -1][:, None]
+    return box_pairs(det[:, :4], trk[:, :4], "iou"), angle

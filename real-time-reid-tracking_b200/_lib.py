@@ -66,6 +66,7 @@ SIGNATURES = {
     "reidb200_cosine_distance": (_i, [_vp, _i, _i64, _vp, _i, _i64, _i, _i, _vp, _vp, _sz, _vp]),
     "reidb200_box_pairs": (_i, [_vp, _i, _vp, _i, _i, _i, _vp, _vp]),
     "reidb200_fuse_cost": (_i, [_vp, _i, _i, _i, _vp, _vp, _vp, _vp, _vp]),
+    "reidb200_ocsort_cost": (_i, [_vp, _i, _vp, _i, _vp, _vp, _d, _vp, _vp, _vp]),
 }
 
 _lib = None

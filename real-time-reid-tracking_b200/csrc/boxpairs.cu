@@ -108,6 +108,35 @@ fuse_kernel(const T* __restrict__ cost, int n, int k, const double* __restrict__
   }
 }
 
+// OC-SORT / DeepOCSORT association cost (boxmot/utils/association.py:6-16 speed_direction_batch, :107-140 associate):
+//   iou[d,t]   = iou_batch(detections, trackers)
+//   angle[d,t] = valid[t] * (pi/2 - |acos(clip(vx[t]*X + vy[t]*Y, -1, 1))|) / pi * vdc_weight * score[d]
+// with (Y, X) the unit direction from the track's previous observation centre to the detection centre.  float64.
+__global__ void __launch_bounds__(256)
+ocsort_cost_kernel(const double* __restrict__ det, int D, const double* __restrict__ trk, int T,
+                   const double* __restrict__ vel, const double* __restrict__ prev, double vdc_weight,
+                   double* __restrict__ out_iou, double* __restrict__ out_angle) {
+  const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= (long long)D * T) return;
+  const int d = (int)(idx / T), t = (int)(idx - (long long)d * T);
+  Box4<double> a, b;
+  a.x1 = det[5 * d + 0]; a.y1 = det[5 * d + 1]; a.x2 = det[5 * d + 2]; a.y2 = det[5 * d + 3];
+  b.x1 = trk[5 * t + 0]; b.y1 = trk[5 * t + 1]; b.x2 = trk[5 * t + 2]; b.y2 = trk[5 * t + 3];
+  out_iou[idx] = pair_value<double>(a, b, REIDB200_BOX_IOU);
+  const double cx1 = (a.x1 + a.x2) / 2.0, cy1 = (a.y1 + a.y2) / 2.0;
+  const double cx2 = (prev[5 * t + 0] + prev[5 * t + 2]) / 2.0, cy2 = (prev[5 * t + 1] + prev[5 * t + 3]) / 2.0;
+  double dx = cx1 - cx2, dy = cy1 - cy2;
+  const double norm = sqrt(dx * dx + dy * dy) + 1e-6;
+  dx = dx / norm;
+  dy = dy / norm;
+  // velocities[:, 0] pairs with Y (= dy), velocities[:, 1] with X (= dx)
+  double c = vel[2 * t + 1] * dx + vel[2 * t + 0] * dy;
+  c = c < -1.0 ? -1.0 : (c > 1.0 ? 1.0 : c);
+  const double diff = (1.5707963267948966 - fabs(acos(c))) / 3.141592653589793;
+  const double valid = prev[5 * t + 4] < 0.0 ? 0.0 : 1.0;
+  out_angle[idx] = ((valid * diff) * vdc_weight) * det[5 * d + 4];
+}
+
 }  // namespace reidb200
 
 using namespace reidb200;
@@ -154,5 +183,19 @@ extern "C" int reidb200_fuse_cost(const void* cost, int cost_is_f64, int n, int 
     { ProfScope _ps("fuse_kernel", st); fuse_kernel<float><<<grid, 256, 0, st>>>(static_cast<const float*>(cost), n, k, det_scores, tlbr_a, tlbr_b, out); }
   }
   RB_LAUNCH_CHECK("fuse_kernel");
+  return REIDB200_OK;
+}
+
+extern "C" int reidb200_ocsort_cost(const double* detections, int D, const double* trackers, int T, const double* velocities,
+                                    const double* previous_obs, double vdc_weight, double* out_iou, double* out_angle,
+                                    void* stream) {
+  if (D == 0 || T == 0) return REIDB200_OK;
+  RB_REQUIRE(detections && trackers && velocities && previous_obs && out_iou && out_angle && D > 0 && T > 0,
+             "ocsort_cost: bad argument");
+  cudaStream_t st = (cudaStream_t)stream;
+  const long long total = (long long)D * T;
+  { ProfScope _ps("ocsort_cost_kernel", st); ocsort_cost_kernel<<<(int)((total + 255) / 256), 256, 0, st>>>(
+      detections, D, trackers, T, velocities, previous_obs, vdc_weight, out_iou, out_angle); }
+  RB_LAUNCH_CHECK("ocsort_cost_kernel");
   return REIDB200_OK;
 }

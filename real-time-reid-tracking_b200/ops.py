@@ -392,6 +392,23 @@ def fuse_cost(cost, det_scores=None, tlbr_a=None, tlbr_b=None):
     return out
 
 
+def ocsort_cost(detections, trackers, velocities, previous_obs, vdc_weight):
+    """(iou f64[D,T], angle_diff_cost f64[D,T]) device tensors of OC-SORT's associate (association.py:107-140)."""
+    dev = L.require_device()
+    f = lambda x, w: torch.as_tensor(np.ascontiguousarray(np.asarray(x, dtype=np.float64))).reshape(-1, w).to(dev)
+    det, trk, vel, prev = f(detections, 5), f(trackers, 5), f(velocities, 2), f(previous_obs, 5)
+    D, T = det.shape[0], trk.shape[0]
+    if vel.shape[0] != T or prev.shape[0] != T:
+        raise ValueError("ocsort_cost: one velocity and one previous observation per tracker expected")
+    iou = torch.empty((D, T), dtype=torch.float64, device=dev)
+    ang = torch.empty((D, T), dtype=torch.float64, device=dev)
+    if D and T:
+        with torch.cuda.device(dev):
+            L.check(L.load().reidb200_ocsort_cost(det.data_ptr(), D, trk.data_ptr(), T, vel.data_ptr(), prev.data_ptr(),
+                                                 float(vdc_weight), iou.data_ptr(), ang.data_ptr(), L.stream_ptr()))
+    return iou, ang
+
+
 def gating_distance(x4, SI, meas):
     dev = L.require_device()
     x4 = torch.as_tensor(np.asarray(x4, dtype=np.float64)).reshape(-1, 4).to(dev)

@@ -80,3 +80,22 @@ def test_mot20_size_vs_oracle(rb):
     assert np.array_equal(M.iou_distance(list(a32), list(b32)), O.iou_distance(a32, b32))
     sc = rng.uniform(0, 1, 200)
     assert np.array_equal(M.fuse_score(O.iou_distance(a32, b32), sc), O.fuse_score(O.iou_distance(a32, b32), sc))
+
+
+def test_ocsort_associate_golden(rb, golden):
+    """OC-SORT associate: the fused IoU + velocity-direction cost equals the reference's final_cost (captured at its
+    linear_assignment call) and the matches / unmatched sets equal the reference's."""
+    from reidb200 import association as A
+
+    g = golden("ocsort")
+    iou, ang = A.associate_costs(g["det"], g["trk"], g["vel"], g["prev"], float(g["vdc"]))
+    np.testing.assert_allclose(-(iou + ang), g["final_cost"], rtol=0, atol=1e-14)  # acos is a library function on both sides
+    oi, oa = O.ocsort_cost(g["det"], g["trk"], g["vel"], g["prev"], float(g["vdc"]))
+    assert np.array_equal(iou, oi)
+    m, ud, ut = A.associate(g["det"], g["trk"], 0.3, g["vel"], g["prev"], float(g["vdc"]))
+    assert np.array_equal(m, g["matches"])
+    assert np.array_equal(np.asarray(ud), g["unmatched_dets"]) and np.array_equal(np.asarray(ut), g["unmatched_trks"])
+    Y, X = A.speed_direction_batch(g["det"], g["prev"])
+    assert np.array_equal(Y, g["Y"]) and np.array_equal(X, g["X"])
+    m0, ud0, ut0 = A.associate(g["det"], np.zeros((0, 5)), 0.3, np.zeros((0, 2)), np.zeros((0, 5)), 0.2)
+    assert m0.shape == (0, 2) and len(ud0) == len(g["det"])

@@ -117,3 +117,9 @@ def test_boxpairs_n2(golden):
     assert np.array_equal(O.fuse_iou(g["embedding"].astype(np.float32), a32, b32), g["fuse_iou32"])
     np.testing.assert_allclose(O.embedding_distance(g["feat_t"], g["feat_d"]), g["embedding"], atol=1e-12)
     assert O.iou_distance(np.zeros((0, 4)), b32).shape == (0, 31)
+
+
+def test_ocsort_cost_n2(golden):
+    g = golden("ocsort")
+    iou, ang = O.ocsort_cost(g["det"], g["trk"], g["vel"], g["prev"], float(g["vdc"]))
+    np.testing.assert_allclose(-(iou + ang), g["final_cost"], rtol=0, atol=1e-15)
