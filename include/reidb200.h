@@ -259,6 +259,21 @@ int reidb200_ocsort_cost(const double* detections, int D, const double* trackers
                          const double* previous_obs, double vdc_weight, double* out_iou, double* out_angle,
                          void* stream);
 
+/* ------------------------------------------------------------------------------------------
+ * N3: StrongSORT's Kalman filter for many tracks at once, device resident.
+ * State arrays (caller-owned, indexed by track slot): x f64[slots,8], P f64[slots,64], SI f64[slots,16]; x and SI feed
+ * reidb200_assoc_frame (trk_mean / trk_SI) without leaving the device.  `slots` i32[n] lists the tracks touched;
+ * measurements f64[n,4] are xyah (Detection.to_xyah() values promoted to double), confidences f64[n] or NULL (= 0).
+ *   initiate  replaces StrongSortKalmanFilterAdapter.initiate (strongsort_kf_adapter.py:25-58); SI := 0
+ *   predict   replaces .predict (:60-94) + KalmanFilter.predict (kalman_filter.py:340-379); slots may be NULL (= 0..n-1)
+ *   update    replaces .update (:96-135) + KalmanFilter.update (kalman_filter.py:486-575), writes SI */
+int reidb200_kf_initiate(double* x, double* P, double* SI, const int32_t* slots, const double* measurements, int n,
+                         double w_pos, double w_vel, void* stream);
+int reidb200_kf_predict(double* x, double* P, const int32_t* slots, int n, double dt, double w_pos, double w_vel,
+                        void* stream);
+int reidb200_kf_update(double* x, double* P, double* SI, const int32_t* slots, const double* measurements,
+                       const double* confidences, int n, double w_pos, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

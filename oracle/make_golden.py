@@ -382,10 +382,52 @@ def gold_ocsort():
           unmatched_dets=np.asarray(ud), unmatched_trks=np.asarray(ut), Y=Y, X=X)
 
 
+def gold_kalman():
+    """N3: StrongSortKalmanFilterAdapter driven like Track does (one object per track): initiate, then per frame
+    predict and, for matched tracks, update with a float32 xyah measurement and a confidence."""
+    KA = ref_import.load_file_pkg("boxmot.motion.adapters.strongsort_kf_adapter")
+    rng = np.random.default_rng(17)
+    T, frames = 9, 7
+    z0 = np.stack([rng.uniform(100, 1500, T), rng.uniform(100, 900, T), rng.uniform(0.3, 0.6, T), rng.uniform(60, 300, T)], 1)
+    kfs, state = [], []
+    for t in range(T):
+        kf = KA.StrongSortKalmanFilterAdapter()
+        x, P = kf.initiate(z0[t].copy())
+        kfs.append(kf)
+        state.append([x.copy(), P.copy(), kf.SI.copy()])
+        ox, oP, oSI = O.kf_initiate(z0[t])
+        assert np.array_equal(ox, x) and np.array_equal(oP, P) and np.array_equal(oSI, kf.SI)
+    matched = rng.uniform(size=(frames, T)) < 0.7
+    matched[0, 0] = False
+    meas = np.zeros((frames, T, 4), np.float32)
+    conf = rng.uniform(0.3, 0.95, (frames, T))
+    xs, Ps, SIs = [], [], []
+    for f in range(frames):
+        for t in range(T):
+            x, P = kfs[t].predict(state[t][0], state[t][1])
+            ox, oP = O.kf_predict(state[t][0], state[t][1])
+            np.testing.assert_allclose(ox, x, rtol=1e-13, atol=0)
+            np.testing.assert_allclose(oP, P, rtol=1e-12, atol=1e-12)
+            state[t][0], state[t][1] = x.copy(), P.copy()
+            if matched[f, t]:
+                z = (x[:4] + rng.normal(0, [4, 4, 0.01, 4])).astype(np.float32)
+                meas[f, t] = z
+                ox, oP, oSI = O.kf_update(state[t][0], state[t][1], z, conf[f, t])
+                x, P = kfs[t].update(state[t][0], state[t][1], z, conf[f, t])
+                np.testing.assert_allclose(ox, x, rtol=1e-11, atol=1e-9)
+                np.testing.assert_allclose(oP, P, rtol=1e-9, atol=1e-9)
+                np.testing.assert_allclose(oSI, kfs[t].SI, rtol=1e-9, atol=1e-12)
+                state[t] = [x.copy(), P.copy(), kfs[t].SI.copy()]
+        xs.append(np.stack([s[0] for s in state]))
+        Ps.append(np.stack([s[1] for s in state]))
+        SIs.append(np.stack([s[2] for s in state]))
+    _save("kalman", z0=z0, matched=matched, meas=meas, conf=conf, x=np.stack(xs), P=np.stack(Ps), SI=np.stack(SIs))
+
+
 def main():
     assert ref_import.available(), "/root/reference not present: fixtures can only be (re)generated in the build container"
     ref_import.install()
-    for fn in (gold_dist, gold_eval, gold_jaccard, gold_preprocess, gold_assoc, gold_boxpairs, gold_ocsort):
+    for fn in (gold_dist, gold_eval, gold_jaccard, gold_preprocess, gold_assoc, gold_boxpairs, gold_ocsort, gold_kalman):
         print(fn.__name__)
         fn()
     print("oracle pinned against the reference; fixtures in tests/golden/")

@@ -718,3 +718,39 @@ def ocsort_cost(detections, trackers, velocities, previous_obs, vdc_weight):
     valid = np.where(prev[:, 4] < 0, 0.0, 1.0)[:, None]
     angle = (((valid * diff) * vdc_weight).T) * det[:, -1][:, None]
     return box_pairs(det[:, :4], trk[:, :4], "iou"), angle
+
+
+# --------------------------------------------------------------------------
+# N3  StrongSORT's Kalman filter (boxmot/motion/adapters/strongsort_kf_adapter.py:25-135 on
+# boxmot/motion/kalman_filter.py:340-379, 486-575), one track at a time, numpy float64.
+# --------------------------------------------------------------------------
+KF_W_POS, KF_W_VEL = 1.0 / 20, 1.0 / 160
+
+
+def kf_initiate(measurement):
+    m = np.asarray(measurement, np.float64)
+    std = [2 * KF_W_POS * m[0], 2 * KF_W_POS * m[1], 1 * m[2], 2 * KF_W_POS * m[3],
+           10 * KF_W_VEL * m[0], 10 * KF_W_VEL * m[1], 0.1 * m[2], 10 * KF_W_VEL * m[3]]
+    return np.r_[m, np.zeros(4)], np.diag(np.square(std)), np.zeros((4, 4))
+
+
+def kf_predict(x, P, dt=1.0):
+    F = np.eye(8)
+    for i in range(4):
+        F[i, 4 + i] = dt
+    std = [KF_W_POS * x[0], KF_W_POS * x[1], 1 * x[2], KF_W_POS * x[3], KF_W_VEL * x[0], KF_W_VEL * x[1], 0.1 * x[2], KF_W_VEL * x[3]]
+    Q = np.diag(np.square(std))
+    return F @ x, (F @ P) @ F.T + Q
+
+
+def kf_update(x, P, z, confidence=0.0):
+    """Returns (x, P, SI): SI is the inverse innovation covariance the NEXT frames gate with."""
+    H = np.eye(4, 8)
+    std = [(1 - confidence) * s for s in (KF_W_POS * x[3], KF_W_POS * x[3], 1e-1, KF_W_POS * x[3])]
+    R = np.diag(np.square(std))
+    y = np.asarray(z, np.float64) - H @ x
+    PHT = P @ H.T
+    SI = np.linalg.inv(H @ PHT + R)
+    K = PHT @ SI
+    A = np.eye(8) - K @ H
+    return x + K @ y, (A @ P) @ A.T + (K @ R) @ K.T, SI

@@ -67,6 +67,9 @@ SIGNATURES = {
     "reidb200_box_pairs": (_i, [_vp, _i, _vp, _i, _i, _i, _vp, _vp]),
     "reidb200_fuse_cost": (_i, [_vp, _i, _i, _i, _vp, _vp, _vp, _vp, _vp]),
     "reidb200_ocsort_cost": (_i, [_vp, _i, _vp, _i, _vp, _vp, _d, _vp, _vp, _vp]),
+    "reidb200_kf_initiate": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _d, _d, _vp]),
+    "reidb200_kf_predict": (_i, [_vp, _vp, _vp, _i, _d, _d, _d, _vp]),
+    "reidb200_kf_update": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _i, _d, _vp]),
 }
 
 _lib = None

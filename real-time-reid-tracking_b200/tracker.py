@@ -23,8 +23,10 @@ def frame_costs(metric, det_feat, det_tlwh, trk_ids, trk_confirmed, trk_mean, tr
     if metric._gallery is None:  # nothing fitted yet (no confirmed track can exist): allocate an empty gallery
         metric._ensure(int(np.asarray(det_feat).shape[1]))
     gallery = metric._gallery
-    return ops.assoc_frame(gallery, det_feat, det_tlwh, slots, np.asarray(trk_mean, np.float64).reshape(T, 8),
-                           np.asarray(trk_SI, np.float64).reshape(T, 16), np.asarray(trk_tsu, np.int32), mc_lambda,
+    # track state: host arrays, or device tensors straight from kalman.BatchedStrongSortKF.gate_state (no H2D)
+    as64 = lambda a, w: a.reshape(T, w) if isinstance(a, torch.Tensor) else np.asarray(a, np.float64).reshape(T, w)
+    return ops.assoc_frame(gallery, det_feat, det_tlwh, slots, as64(trk_mean, 8), as64(trk_SI, 16),
+                           trk_tsu if isinstance(trk_tsu, torch.Tensor) else np.asarray(trk_tsu, np.int32), mc_lambda,
                            max_dist, max_iou_dist, iou_mode, clamp_app=clamp, clamp_iou=clamp, want_raw=want_raw)
 
 

@@ -123,3 +123,18 @@ def test_ocsort_cost_n2(golden):
     g = golden("ocsort")
     iou, ang = O.ocsort_cost(g["det"], g["trk"], g["vel"], g["prev"], float(g["vdc"]))
     np.testing.assert_allclose(-(iou + ang), g["final_cost"], rtol=0, atol=1e-15)
+
+
+def test_kalman_n3(golden):
+    """N3: the oracle's Kalman steps replay the reference adapter's recorded sequence."""
+    g = golden("kalman")
+    T = g["z0"].shape[0]
+    st = [list(O.kf_initiate(g["z0"][t])) for t in range(T)]
+    for f in range(g["matched"].shape[0]):
+        for t in range(T):
+            st[t][0], st[t][1] = O.kf_predict(st[t][0], st[t][1])
+            if g["matched"][f, t]:
+                st[t] = list(O.kf_update(st[t][0], st[t][1], g["meas"][f, t], g["conf"][f, t]))
+        np.testing.assert_allclose(np.stack([s[0] for s in st]), g["x"][f], rtol=1e-10, atol=1e-8)
+        np.testing.assert_allclose(np.stack([s[1] for s in st]), g["P"][f], rtol=1e-8, atol=1e-8)
+        np.testing.assert_allclose(np.stack([s[2] for s in st]), g["SI"][f], rtol=1e-8, atol=1e-12)
