@@ -193,6 +193,76 @@ def bench_assoc(steps, warmup):
     return out
 
 
+def bench_next_rows(steps):
+    """N2 / N3 rows at MOT20 size (300 tracks x 200 detections): kernel microseconds from CUDA events on the
+    launch stream, and the same call of the numpy oracle on the host beside it."""
+    import reidb200  # noqa: F401
+    from oracle import reid_oracle as O
+    from reidb200 import _lib as L, ops
+    from reidb200.kalman import BatchedStrongSortKF
+
+    rng = np.random.default_rng(3)
+    T, M = 300, 200
+    xy, wh = rng.uniform(0, 1800, (T + M, 2)), rng.uniform(8, 260, (T + M, 2))
+    bx = np.concatenate([xy, xy + wh], 1)
+    a, b = bx[:T], bx[T:]
+    dev = torch.device("cuda", torch.cuda.current_device())
+    a_d, b_d = torch.from_numpy(a).to(dev), torch.from_numpy(b).to(dev)
+    out = torch.empty((T, M), dtype=torch.float64, device=dev)
+    lib = L.load()
+    n = max(20 * steps, 100)
+    res = {"tracks": T, "dets": M}
+
+    def kernel_us(fn, name):
+        for _ in range(3):
+            fn()
+        L.profile_enable(True)
+        _timed(fn, n, torch.cuda.synchronize)
+        prof = L.profile_read()
+        L.profile_enable(False)
+        return prof[name][1] / prof[name][0] * 1e3
+
+    def host_us(fn, reps=5):
+        fn()
+        t0 = time.perf_counter()
+        for _ in range(reps):
+            fn()
+        return (time.perf_counter() - t0) / reps * 1e6
+
+    for mode in ("iou", "giou", "diou", "ciou"):
+        res["box_pairs_%s_us" % mode] = kernel_us(lambda: L.check(lib.reidb200_box_pairs(
+            a_d.data_ptr(), T, b_d.data_ptr(), M, 1, L.BOX_MODES[mode], out.data_ptr(), L.stream_ptr())), "box_pairs_kernel")
+    res["box_pairs_ciou_numpy_us"] = host_us(lambda: O.box_pairs(a, b, "ciou"))
+    det = np.concatenate([b, rng.uniform(0.3, 1, (M, 1))], 1)
+    trk = np.concatenate([a, np.zeros((T, 1))], 1)
+    vel = rng.normal(0, 1, (T, 2))
+    prev = np.concatenate([a - 5.0, np.ones((T, 1))], 1)
+    d_d, t_d, v_d, p_d = (torch.from_numpy(x).to(dev) for x in (det, trk, vel, prev))
+    o1, o2 = torch.empty((M, T), dtype=torch.float64, device=dev), torch.empty((M, T), dtype=torch.float64, device=dev)
+    res["ocsort_cost_us"] = kernel_us(lambda: L.check(lib.reidb200_ocsort_cost(
+        d_d.data_ptr(), M, t_d.data_ptr(), T, v_d.data_ptr(), p_d.data_ptr(), 0.2, o1.data_ptr(), o2.data_ptr(), L.stream_ptr())),
+        "ocsort_cost_kernel")
+    res["ocsort_cost_numpy_us"] = host_us(lambda: O.ocsort_cost(det, trk, vel, prev, 0.2))
+    z = np.stack([rng.uniform(0, 1900, T), rng.uniform(0, 1000, T), rng.uniform(0.2, 0.7, T), rng.uniform(40, 400, T)], 1)
+    kf = BatchedStrongSortKF(max_tracks=T)
+    slots = torch.arange(T, dtype=torch.int32, device=dev)
+    z_d, c_d = torch.from_numpy(z).to(dev), torch.full((T,), 0.5, dtype=torch.float64, device=dev)
+    kf.initiate(slots, z_d)
+    res["kf_predict_us"] = kernel_us(lambda: kf.predict(slots), "kf_predict_kernel")
+    kf.initiate(slots, z_d)
+    kf.predict(slots)
+    res["kf_update_us"] = kernel_us(lambda: kf.update(slots, z_d, c_d), "kf_update_kernel")
+    st = [O.kf_initiate(z[t]) for t in range(T)]
+
+    def host_kf():
+        for t in range(T):
+            x, P = O.kf_predict(st[t][0], st[t][1])
+            O.kf_update(x, P, z[t], 0.5)
+
+    res["kf_predict_update_numpy_us"] = host_us(host_kf, 2)
+    return res
+
+
 RETR_Q, RETR_G, RETR_D, RETR_K, RETR_PIECE = 10_000, 4_000_000, 2048, 100, 62_500
 
 
@@ -448,6 +518,7 @@ def run_ours(args):
         line["retrieval"] = retrieval
     if not args.no_assoc:
         line["assoc"] = bench_assoc(args.steps, args.warmup)
+        line["next_rows"] = bench_next_rows(args.steps)
     if not args.no_cpu and world == 1:
         dsmp, qs, gs = cpu_sample()
         t0 = time.perf_counter()
