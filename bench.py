@@ -172,7 +172,7 @@ def bench_assoc(steps, warmup):
             c = preprocess.preprocess_frame(frame, xyxy, out=crops)
             a, _, i = tracker.frame_costs(metric, det_feat, fr["det_tlwh"], np.arange(T), np.ones(T, bool), fr["trk_mean"],
                                           fr["trk_SI"], fr["trk_tsu"], 0.995, 0.2, 0.7)
-            return torch.stack([a, i]).cpu()
+            return tracker.costs_to_host(a, i)  # one D2H of both cost matrices, as tracker.match_arrays does
 
         for _ in range(3):
             e2e_step()

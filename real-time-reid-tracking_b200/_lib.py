@@ -134,7 +134,13 @@ def require_device(t: torch.Tensor = None) -> torch.device:
     return dev
 
 
+_raw_stream = getattr(torch._C, "_cuda_getCurrentRawStream", None)
+
+
 def stream_ptr() -> int:
+    """cudaStream_t of torch's current stream on the current device (the raw getter skips building a Stream object)."""
+    if _raw_stream is not None:
+        return _raw_stream(torch.cuda.current_device())
     return torch.cuda.current_stream().cuda_stream
 
 
@@ -145,6 +151,63 @@ def ptr(t) -> int:
 def workspace(nbytes: int, device) -> torch.Tensor:
     """256-byte aligned scratch (torch's caching allocator hands out 512-byte aligned blocks)."""
     return torch.empty(max(int(nbytes), 256), dtype=torch.uint8, device=device)
+
+
+class HostStaging:
+    """Small per-call host arrays -> device in ONE copy: the arrays are laid out back to back (8-byte aligned) in a
+    pinned buffer, copied with a single asynchronous H2D, and returned as typed views of the device mirror.  Two
+    buffer pairs alternate, so the views handed out by one call stay valid until the call after the next (a frame's
+    inputs are consumed by the kernels launched right after).  An event per pair guards the pinned memory against
+    being rewritten while its previous copy is still in flight."""
+
+    def __init__(self, device):
+        self.dev = device
+        self.slot = 0
+        self.pairs = [dict(cap=0, host=None, dev=None, ev=None) for _ in range(2)]
+
+    def upload(self, arrays):
+        import numpy as np
+
+        sizes = [(a.nbytes + 7) & ~7 for a in arrays]
+        total = max(sum(sizes), 8)
+        pr = self.pairs[self.slot]
+        self.slot ^= 1
+        if pr["cap"] < total:
+            cap = max(4096, 1 << (total - 1).bit_length())
+            pr["host"] = torch.empty(cap, dtype=torch.uint8).pin_memory()
+            pr["dev"] = torch.empty(cap, dtype=torch.uint8, device=self.dev)
+            pr["cap"], pr["ev"], pr["sig"] = cap, None, None
+        if pr["ev"] is not None:
+            pr["ev"].synchronize()
+        sig = tuple((a.dtype.str, a.shape) for a in arrays)
+        if pr.get("sig") != sig:  # typed host / device views of this layout, rebuilt only when the shapes change
+            hv = pr["host"].numpy()
+            off, hviews, dviews = 0, [], []
+            for a, sz in zip(arrays, sizes):
+                hviews.append(hv[off:off + a.nbytes].view(a.dtype).reshape(a.shape))
+                dviews.append(pr["dev"][off:off + a.nbytes].view(_TORCH_OF[a.dtype.str]).reshape(a.shape))
+                off += sz
+            pr["sig"], pr["hviews"], pr["dviews"], pr["bytes"] = sig, hviews, dviews, off
+            pr["src"], pr["dst"] = pr["host"][:off], pr["dev"][:off]
+        for h, a in zip(pr["hviews"], arrays):
+            h[...] = a
+        views, off = pr["dviews"], pr["bytes"]
+        pr["dst"].copy_(pr["src"], non_blocking=True)
+        if pr["ev"] is None:
+            pr["ev"] = torch.cuda.Event()
+        pr["ev"].record()
+        return views
+
+
+_TORCH_OF = {"<f8": torch.float64, "<f4": torch.float32, "<i4": torch.int32, "<i8": torch.int64, "|u1": torch.uint8}
+_staging = {}
+
+
+def staging(device) -> HostStaging:
+    key = (device.type, device.index)
+    if key not in _staging:
+        _staging[key] = HostStaging(device)
+    return _staging[key]
 
 
 def as_f32_cuda(x, device=None) -> torch.Tensor:

@@ -260,7 +260,7 @@ class Gallery:
         self._h = h
 
     def close(self):
-        if getattr(self, "_h", None):
+        if getattr(self, "_h", None) and L is not None:  # (module globals are gone at interpreter shutdown)
             L.load().reidb200_gallery_destroy(self._h)
             self._h = None
 
@@ -296,7 +296,7 @@ class Gallery:
 
 def assoc_frame(gallery, det_feat, det_tlwh, trk_slot, trk_mean, trk_SI, trk_tsu, mc_lambda=0.995, max_dist=0.2,
                 max_iou_dist=0.7, iou_mode="iou", clamp_app=False, clamp_iou=False, gate=True, want_raw=False,
-                want_app=True, want_iou=True, simt=False):
+                want_app=True, want_iou=True, simt=False, out_app=None, out_iou=None):
     """One fused launch (simt=True: the fp32 SIMT cross-check kernel instead of the tcgen05 one): (app f64[T,M] or None, raw or None, iou f64[T,M] or None), all on device."""
     dev = gallery.device if gallery is not None else L.require_device()
     det_tlwh = _f32(det_tlwh, dev)
@@ -311,10 +311,10 @@ def assoc_frame(gallery, det_feat, det_tlwh, trk_slot, trk_mean, trk_SI, trk_tsu
         det_feat_t = _f32(det_feat, dev)
         slot_t = _i32(trk_slot, dev)
         si_t = torch.as_tensor(trk_SI).to(device=dev, dtype=torch.float64).contiguous()
-        app = torch.empty((T, M), dtype=torch.float64, device=dev)
+        app = out_app if out_app is not None else torch.empty((T, M), dtype=torch.float64, device=dev)
         raw = torch.empty((T, M), dtype=torch.float64, device=dev) if want_raw else None
     if want_iou:
-        iou = torch.empty((T, M), dtype=torch.float64, device=dev)
+        iou = out_iou if out_iou is not None else torch.empty((T, M), dtype=torch.float64, device=dev)
     if T == 0 or M == 0:
         return app, raw, iou
     flags = (L.ASSOC_CLAMP_APP if clamp_app else 0) | (L.ASSOC_CLAMP_IOU if clamp_iou else 0) | (0 if gate else L.ASSOC_NO_GATE) | (L.ASSOC_SIMT if simt else 0)

@@ -59,10 +59,7 @@ def preprocess_frame(frame, xyxy, size=(128, 256), norm=DEEPSORT_NORM, mode="cv_
     off, geom = _geometry_from_xyxy(xyxy, W)
     if len(off) == 0:
         return torch.empty((0, 3, size[1], size[0]), dtype=torch.float32, device=dev)
-    both = torch.from_numpy(np.concatenate([off.view(np.int32).reshape(-1, 2), geom], 1))  # one small H2D
-    both = both.to(dev, non_blocking=True)
-    off_d = both[:, :2].contiguous().view(torch.int64).reshape(-1)
-    geom_d = both[:, 2:].contiguous()
+    off_d, geom_d = L.staging(dev).upload([off, geom])  # one pinned H2D for both tables
     return ops.crop_resize_norm(f.reshape(-1), off_d, geom_d, size[1], size[0], norm[0], norm[1], mode, out=out)
 
 

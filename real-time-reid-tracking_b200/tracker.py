@@ -7,6 +7,7 @@ from __future__ import annotations
 import numpy as np
 import torch
 
+from . import _lib as L
 from . import ops
 from .linear_assignment import _solve, track_gate_state
 
@@ -16,18 +17,55 @@ def frame_costs(metric, det_feat, det_tlwh, trk_ids, trk_confirmed, trk_mean, tr
     """Device matrices (app f64[T,M], raw or None, iou f64[T,M]); rows of unconfirmed tracks carry 1e5 in `app`."""
     T = len(trk_ids)
     max_dist = metric.matching_threshold if max_dist is None else max_dist
-    slots = np.full(T, -1, np.int32)
-    for r in range(T):
-        if trk_confirmed[r] and int(trk_ids[r]) in metric.samples:
-            slots[r] = metric._slot_of[int(trk_ids[r])]
+    slot_of = metric._slot_of  # id -> ring-buffer slot of every target that has samples
+    slots = np.fromiter((slot_of.get(int(i), -1) if c else -1 for i, c in zip(trk_ids, trk_confirmed)), np.int32, T)
     if metric._gallery is None:  # nothing fitted yet (no confirmed track can exist): allocate an empty gallery
         metric._ensure(int(np.asarray(det_feat).shape[1]))
     gallery = metric._gallery
-    # track state: host arrays, or device tensors straight from kalman.BatchedStrongSortKF.gate_state (no H2D)
-    as64 = lambda a, w: a.reshape(T, w) if isinstance(a, torch.Tensor) else np.asarray(a, np.float64).reshape(T, w)
-    return ops.assoc_frame(gallery, det_feat, det_tlwh, slots, as64(trk_mean, 8), as64(trk_SI, 16),
-                           trk_tsu if isinstance(trk_tsu, torch.Tensor) else np.asarray(trk_tsu, np.int32), mc_lambda,
-                           max_dist, max_iou_dist, iou_mode, clamp_app=clamp, clamp_iou=clamp, want_raw=want_raw)
+    dev = gallery.device
+    # per-frame host state goes up in ONE pinned copy; device tensors (kalman.BatchedStrongSortKF.gate_state) pass through
+    host = {}
+    if not isinstance(trk_mean, torch.Tensor):
+        host["mean"] = np.ascontiguousarray(np.asarray(trk_mean, np.float64).reshape(T, 8))
+    if not isinstance(trk_SI, torch.Tensor):
+        host["SI"] = np.ascontiguousarray(np.asarray(trk_SI, np.float64).reshape(T, 16))
+    if not isinstance(det_tlwh, torch.Tensor):
+        host["tlwh"] = np.ascontiguousarray(np.asarray(det_tlwh, np.float32).reshape(-1, 4))
+    if not isinstance(trk_tsu, torch.Tensor):
+        host["tsu"] = np.ascontiguousarray(np.asarray(trk_tsu, np.int32).reshape(T))
+    host["slots"] = slots
+    up = dict(zip(host.keys(), L.staging(dev).upload(list(host.values()))))
+    mean_d = up.get("mean", trk_mean.reshape(T, 8) if isinstance(trk_mean, torch.Tensor) else None)
+    SI_d = up.get("SI", trk_SI.reshape(T, 16) if isinstance(trk_SI, torch.Tensor) else None)
+    M = int(up["tlwh"].shape[0]) if "tlwh" in up else int(det_tlwh.shape[0])
+    out = torch.empty((2, T, M), dtype=torch.float64, device=dev)  # app | iou in one buffer: one D2H for the host solve
+    return ops.assoc_frame(gallery, det_feat, up.get("tlwh", det_tlwh), up["slots"], mean_d, SI_d, up.get("tsu", trk_tsu),
+                           mc_lambda, max_dist, max_iou_dist, iou_mode, clamp_app=clamp, clamp_iou=clamp, want_raw=want_raw,
+                           out_app=out[0], out_iou=out[1])
+
+
+_host_out = {"bufs": [None, None], "turn": 0}
+
+
+def costs_to_host(app, iou):
+    """(app, iou) numpy float64 with ONE device->host copy into pinned memory when both are the halves of
+    frame_costs' buffer.  The arrays are views of one of two alternating pinned buffers: they stay valid until the
+    call after the next (a frame's costs are consumed by that frame's assignment)."""
+    base = app._base
+    if (base is not None and base is iou._base and base.dim() == 3 and base.shape[0] == 2
+            and app.data_ptr() == base.data_ptr() and iou.data_ptr() == base.data_ptr() + app.numel() * 8):
+        k = _host_out["turn"]
+        _host_out["turn"] = k ^ 1
+        buf = _host_out["bufs"][k]
+        if buf is None or buf.numel() < base.numel():
+            buf = torch.empty(max(base.numel(), 1 << 16), dtype=torch.float64).pin_memory()
+            _host_out["bufs"][k] = buf
+        h = buf[:base.numel()].view(base.shape)
+        h.copy_(base, non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+        h = h.numpy()
+        return h[0], h[1]
+    return app.cpu().numpy(), iou.cpu().numpy()
 
 
 def match_arrays(metric, det_feat, det_tlwh, trk_ids, trk_confirmed, trk_mean, trk_SI, trk_tsu, mc_lambda, max_iou_dist,
@@ -41,8 +79,7 @@ def match_arrays(metric, det_feat, det_tlwh, trk_ids, trk_confirmed, trk_mean, t
     if T and M:
         app, _, iou = frame_costs(metric, det_feat, det_tlwh, trk_ids, trk_confirmed, trk_mean, trk_SI, trk_tsu, mc_lambda,
                                   max_dist, max_iou_dist, iou_mode)
-        both = torch.stack([app, iou]).cpu().numpy()  # one D2H
-        app, iou = both[0], both[1]
+        app, iou = costs_to_host(app, iou)  # one D2H
     # stage A: confirmed tracks x all detections, appearance cost (matching_cascade, single level)
     if len(confirmed) == 0 or M == 0:
         m_a, um_d = [], dets
