@@ -404,7 +404,10 @@ def run_ours(args):
     merged = merged_host.to(dev)
     lab = {k: v.to(dev) for k, v in lab_host.items()}
 
-    def step():
+    def step():  # fused: the CTA that produces a query's re-ranked row reduces it to AP / first hit at once
+        return ops.rerank_eval(merged, G, lab["ql"], lab["qc"], lab["gl"], lab["gc"], K1, K2, LAMBDA)
+
+    def step_materialised():  # the same evaluation with the re-ranked Q x G matrix written and re-read (two calls)
         dist_qg = ops.jaccard(merged, K1, K2, False, LAMBDA, rows=(G, Q), cols=(0, G))
         return ops.eval_cmc_map(dist_qg, lab["ql"], lab["qc"], lab["gl"], lab["gc"], descending=False)
 
@@ -414,8 +417,11 @@ def run_ours(args):
     clocks = ClockSampler(local)
     if rank == 0:
         clocks.start()
+    ms = _timed(step, args.steps, barrier)  # the headline: K steps, nothing but the product's launches on the stream
+    # a second pass of K steps with every kernel bracketed by CUDA events on its launch stream (kernel shares, the
+    # roofline kernel's launch time, the launch count); the event pairs cost a few per cent, hence the separate pass
     L.profile_enable(True)
-    ms = _timed(step, args.steps, barrier)
+    ms_prof = _timed(step, args.steps, barrier)
     prof = L.profile_read()
     L.profile_enable(False)
     clk = clocks.stop() if rank == 0 else None
@@ -424,6 +430,9 @@ def run_ours(args):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms = float(t.item())
     value = world * args.steps * Q * G / (ms * 1e-3)
+    cmc_m, ap_m = step_materialised()
+    assert torch.equal(cmc_m, cmc) and torch.equal(ap_m, ap), "fused and materialised evaluations differ"
+    ms_mat = _timed(step_materialised, args.steps, barrier) / args.steps
 
     # ---- end to end through the public API: pinned host features + labels in, CMC + mAP out, every step
     qf_h, gf_h = merged_host[G:], merged_host[:G]
@@ -484,7 +493,7 @@ def run_ours(args):
     peaks, peak_kind = _peaks()
     gemm_n, gemm_ms = prof.get("gemm_split_tc_kernel", (0, 0.0))
     launches = sum(n for n, _ in prof.values())
-    share = {k: round(v[1] / ms, 4) for k, v in sorted(prof.items(), key=lambda kv: -kv[1][1])}
+    share = {k: round(v[1] / ms_prof, 4) for k, v in sorted(prof.items(), key=lambda kv: -kv[1][1])}
     # algorithmic (fp32-equivalent) flops of one launch: 2*D per UNORDERED pair -- the self-distance matrix is symmetric
     # and the kernel computes only its upper triangle of tiles (each off-diagonal tile is stored twice)
     gemm_flops = 2.0 * D_FULL * (N * (N + 1) / 2.0)
@@ -500,7 +509,9 @@ def run_ours(args):
         "data": "synthetic",
         "config": {"workload": "market1501_rerank_k20_6_l0.3", "queries": Q, "gallery": G, "dim": D_FULL, "k1": K1, "k2": K2,
                    "lambda": LAMBDA, "parallelism": "independent evaluation sets per GPU" if world > 1 else "single GPU",
-                   "l2": "working set (1.49 GB distance matrix + 0.5 GB sparse tables per step) larger than L2"},
+                   "l2": "working set (1.49 GB distance matrix + 0.5 GB sparse tables per step) larger than L2",
+                   "evaluation": "fused into the re-rank kernel (ops.rerank_eval); ms_per_step_materialised = jaccard + eval_cmc_map"},
+        "ms_per_step_materialised": ms_mat, "ms_per_step_with_kernel_events": ms_prof / args.steps,
         "clocks": clk,
         "e2e": {"value": e2e_value, "unit": "pairs/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
                 "mode": "evaluate.RerankedEvalStream(depth=2): H2D of set i+1 overlaps the kernels of set i",

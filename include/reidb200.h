@@ -232,6 +232,17 @@ int reidb200_cosine_distance(const float* a, int na, int64_t lda, const float* b
                              int d, int normalized, float* out, void* workspace,
                              size_t workspace_bytes, void* stream);
 
+/* Re-ranked evaluation in one call (stages 3 + 4 fused): feats f32[G+Q, d] = gallery rows first, then query rows
+ * (the merged set of image_reid_inference.py:270); the Q x G block of the lambda-blended Jaccard distance is reduced
+ * to CMC f32[G] / mAP f64[1] by the CTA that produces each query row, so the re-ranked matrix is not re-read and, with
+ * out_dist == NULL, never written.  G <= 16384 (wider galleries: reidb200_jaccard + reidb200_eval_cmc_map).
+ * replaces reid/faiss_utils.py:149-244 followed by reid/evaluate.py:33-105 on the re-ranked distance. */
+size_t reidb200_rerank_eval_workspace_bytes(int N, int d, int k1, int k2, int Q, int G);
+int reidb200_rerank_eval(const float* feats, int G, int Q, int64_t ldf, int d, int k1, int k2, float lambda_value,
+                         const int32_t* ql, const int32_t* qc, const int32_t* gl, const int32_t* gc,
+                         float* out_dist, int64_t ldo, float* out_cmc, double* out_ap, void* workspace,
+                         size_t workspace_bytes, void* stream);
+
 /* ------------------------------------------------------------------------------------------
  * N2: pairwise box costs of the other boxmot trackers.
  *   modes 0-3  iou_batch / giou_batch / diou_batch / ciou_batch of xyxy boxes, computed and returned in the

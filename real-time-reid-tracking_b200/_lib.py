@@ -64,6 +64,8 @@ SIGNATURES = {
     "reidb200_gating_distance": (_i, [_vp, _vp, _vp, _i, _i, _vp, _vp]),
     "reidb200_cosine_distance_workspace_bytes": (_sz, [_i, _i, _i]),
     "reidb200_cosine_distance": (_i, [_vp, _i, _i64, _vp, _i, _i64, _i, _i, _vp, _vp, _sz, _vp]),
+    "reidb200_rerank_eval_workspace_bytes": (_sz, [_i, _i, _i, _i, _i, _i]),
+    "reidb200_rerank_eval": (_i, [_vp, _i, _i, _i64, _i, _i, _i, _f, _vp, _vp, _vp, _vp, _vp, _i64, _vp, _vp, _vp, _sz, _vp]),
     "reidb200_box_pairs": (_i, [_vp, _i, _vp, _i, _i, _i, _vp, _vp]),
     "reidb200_fuse_cost": (_i, [_vp, _i, _i, _i, _vp, _vp, _vp, _vp, _vp]),
     "reidb200_ocsort_cost": (_i, [_vp, _i, _vp, _i, _vp, _vp, _d, _vp, _vp, _vp]),

@@ -5,18 +5,12 @@
 // so each query needs only |good| counting passes over its score row.  AP is accumulated in the
 // reference's order (ascending rows_good, fp64) and the per-query APs are summed in query order, so
 // the mAP is bit-identical to the reference whenever the rankings are.
-#include "common.cuh"
+#include "evalmap.cuh"
 
 namespace reidb200 {
 
 constexpr int EV_THREADS = 256;
-constexpr int EV_GOOD_CAP = 1024;
 constexpr int EV_UNROLL = 16;  // row values in flight per thread in the streaming pass (4 CTAs x 16 KB per SM)
-
-__device__ __forceinline__ uint32_t ev_key(float v, int descending) {
-  const uint32_t u = float_to_ordered(v);
-  return descending ? ~u : u;  // smaller key = ranked earlier
-}
 
 // One CTA per query, one streaming pass over the score row.
 //   pass 1  collect the good items (same id, different camera: evaluate.py:66-70), rank-sort them;
@@ -25,10 +19,6 @@ __device__ __forceinline__ uint32_t ev_key(float v, int descending) {
 //           precedes and bumps hist[s]; position(good s) = sum_{b <= s} hist[b].
 // Tie order of the reference: ascending argsort then [::-1] for scores (higher index first), plain ascending
 // (lower index first) for distances.
-__device__ __forceinline__ bool ev_before(uint32_t ka, int ja, uint32_t kb, int jb, int descending) {
-  return ka < kb || (ka == kb && (descending ? ja > jb : ja < jb));
-}
-
 __global__ void __launch_bounds__(EV_THREADS, 4)
 eval_query_kernel(const float* __restrict__ mat, int G, int64_t ldm, int descending, const int32_t* __restrict__ ql,
                   const int32_t* __restrict__ qc, const int32_t* __restrict__ gl, const int32_t* __restrict__ gc,
@@ -185,6 +175,19 @@ eval_finalize_kernel(const int32_t* __restrict__ hist, const double* __restrict_
   }
 }
 
+int eval_finalize_launch(const int32_t* hist, const double* ap_q, int Q, int G, float* out_cmc, double* out_ap,
+                         cudaStream_t st) {
+  static bool attr = false;
+  if (!attr) {
+    RB_CUDA(cudaFuncSetAttribute(eval_finalize_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    attr = true;
+  }
+  RB_REQUIRE((size_t)(G + 1) * sizeof(int) <= 200 * 1024, "eval_cmc_map: gallery larger than this build's limit (G=%d <= 51199)", G);
+  { ProfScope _ps("eval_finalize_kernel", st); eval_finalize_kernel<<<1, 1024, (size_t)(G + 1) * sizeof(int), st>>>(hist, ap_q, Q, G, out_cmc, out_ap); }
+  RB_LAUNCH_CHECK("eval_finalize_kernel");
+  return REIDB200_OK;
+}
+
 }  // namespace reidb200
 
 using namespace reidb200;
@@ -216,15 +219,7 @@ extern "C" int reidb200_eval_cmc_map(const float* mat, int Q, int G, int64_t ldm
   if (out_first) first = out_first;
   RB_CUDA(cudaMemsetAsync(hist, 0, (size_t)G * sizeof(int32_t), st));
   RB_CUDA(cudaMemsetAsync(status, 0, 64 * sizeof(int32_t), st));
-  static bool attr = false;
-  if (!attr) {
-    RB_CUDA(cudaFuncSetAttribute(eval_finalize_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-    attr = true;
-  }
-  RB_REQUIRE((size_t)(G + 1) * sizeof(int) <= 200 * 1024, "eval_cmc_map: gallery larger than this build's limit (G=%d <= 51199)", G);
   { ProfScope _ps("eval_query_kernel", st); eval_query_kernel<<<Q, EV_THREADS, 0, st>>>(mat, G, ldm, descending, ql, qc, gl, gc, apq, first, hist, status); }
   RB_LAUNCH_CHECK("eval_query_kernel");
-  { ProfScope _ps("eval_finalize_kernel", st); eval_finalize_kernel<<<1, 1024, (size_t)(G + 1) * sizeof(int), st>>>(hist, apq, Q, G, out_cmc, out_ap); }
-  RB_LAUNCH_CHECK("eval_finalize_kernel");
-  return REIDB200_OK;
+  return eval_finalize_launch(hist, apq, Q, G, out_cmc, out_ap, st);
 }

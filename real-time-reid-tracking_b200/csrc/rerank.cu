@@ -10,6 +10,7 @@
 //   D7  Jaccard: min-sum over shared columns, 1 - t/(2-t)     jaccard_rows_kernel (CTA / output row,
 //       dense accumulator staged in shared memory, coalesced dense row written once)
 //   D8  optional lambda blend with the Euclidean distance (north_star; not in the reference)
+#include "evalmap.cuh"
 #include "gemm.cuh"
 
 namespace reidb200 {
@@ -540,23 +541,40 @@ __global__ void inv_fill_kernel(const int32_t* __restrict__ cols, const float* _
 // compare-and-swap loops that serialise on the few hundred hot rows of a cluster -- and the result no longer
 // depends on the order in which the atomics land.
 // Dynamic smem: acc[N4] | e_val[cap] | e_beg[cap] (ints) | e_off[cap + 1] (ints), N4 = N rounded up to 4.
+// Optional fused evaluation (D8 -> B4-B6): when the output block is the Q x G block of a re-ranked evaluation, the CTA
+// that has just produced query row q still holds it in registers and reduces it to the query's AP / first hit right
+// away (eval_row_in_registers, evalmap.cuh) -- the re-ranked matrix is then neither re-read nor, if `out` is null,
+// written at all (2 x 214 MB of HBM traffic at Market size).
+struct EvalFuse {
+  const int32_t *ql, *qc, *gl, *gc;
+  double* ap_q;
+  int32_t *first, *hist, *status;
+  int enabled;
+};
+
 constexpr int JR_THREADS = 512;
 constexpr int JR_PF = 32;                        // squared-L2 values prefetched per thread (covers 16384 columns)
 constexpr float JR_FIX = 1073741824.0f;          // 2^30
 constexpr float JR_UNFIX = 1.0f / 1073741824.0f;
 
-__device__ __forceinline__ float jaccard_value(float t, int use_f16) {
-  if (t == 0.f) return 1.0f;  // 1 - 0 / 2, exactly
+// 1 - t / (2 - t), clamped at 0 (faiss_utils.py:236-240).  Almost every entry of a row has t == 0 (no shared
+// neighbour): that case is exactly 1 and stays inline, the division lives out of line (the output loop is unrolled).
+static __device__ __noinline__ float jaccard_nonzero(float t, int use_f16) {
   if (use_f16) t = __half2float(__float2half_rn(t));
   const float jd = __fsub_rn(1.0f, __fdiv_rn(t, __fsub_rn(2.0f, t)));
   return jd < 0.f ? 0.f : jd;
+}
+
+__device__ __forceinline__ float jaccard_value(float t, int use_f16) {
+  return t == 0.f ? 1.0f : jaccard_nonzero(t, use_f16);
 }
 
 __global__ void __launch_bounds__(JR_THREADS, 2)
 jaccard_rows_kernel(const int32_t* __restrict__ qcols, const float* __restrict__ qvals, const int32_t* __restrict__ qcnt,
                     int cap, const int32_t* __restrict__ colptr, const int32_t* __restrict__ inv_row,
                     const float* __restrict__ inv_val, int N, int row0, int col0, int ncols, float lambda_value,
-                    const float* __restrict__ sql2, int64_t lds, int use_f16, void* __restrict__ out, int64_t ldo) {
+                    const float* __restrict__ sql2, int64_t lds, int use_f16, void* __restrict__ out, int64_t ldo,
+                    EvalFuse ev) {
   extern __shared__ __align__(16) float acc[];
   const int N4 = (N + 3) & ~3;
   unsigned int* acci = reinterpret_cast<unsigned int*>(acc);
@@ -632,8 +650,11 @@ jaccard_rows_kernel(const int32_t* __restrict__ qcols, const float* __restrict__
     if (c < ncols) {
       float jd = jaccard_value(acc[col0 + c], use_f16);
       if (blend) jd = __fadd_rn(__fmul_rn(jd, one_m_l), __fmul_rn(sqrtf(fmaxf(pre[k], 1e-12f)), lambda_value));
-      if (use_f16) hrow[c] = __float2half_rn(jd);
-      else __stcs(orow + c, jd);
+      pre[k] = jd;  // the row stays in registers for the fused evaluation
+      if (out) {
+        if (use_f16) hrow[c] = __float2half_rn(jd);
+        else __stcs(orow + c, jd);
+      }
     }
   }
   for (int c = tid + JR_PF * JR_THREADS; c < ncols; c += JR_THREADS) {  // rows wider than JR_PF * JR_THREADS columns
@@ -641,6 +662,11 @@ jaccard_rows_kernel(const int32_t* __restrict__ qcols, const float* __restrict__
     if (blend) jd = __fadd_rn(__fmul_rn(jd, one_m_l), __fmul_rn(sqrtf(fmaxf(__ldcs(srow + c), 1e-12f)), lambda_value));
     if (use_f16) hrow[c] = __float2half_rn(jd);
     else __stcs(orow + c, jd);
+  }
+  if (ev.enabled) {  // host side guarantees ncols <= JR_PF * JR_THREADS, fp32 output, shared memory >= EvalScratch
+    __syncthreads();  // the accumulator is dead: its shared memory becomes the evaluation scratch
+    eval_row_in_registers<JR_THREADS, JR_PF>(pre, ncols, (int)blockIdx.x, 0, ev.ql, ev.qc, ev.gl, ev.gc, ev.ap_q, ev.first,
+                                             ev.hist, ev.status, reinterpret_cast<EvalScratch*>(acc));
   }
 }
 
@@ -710,7 +736,8 @@ static size_t jaccard_rows_smem(int N, int cap) { return (size_t)((N + 3) & ~3) 
 
 static int jaccard_sparse_stages(const int32_t* rank, const float* sql2, int64_t lds, const float* sqnorm, int N, int k1,
                                  int k2, int use_f16, float lambda_value, int row0, int nrows, int col0, int ncols,
-                                 void* out, int64_t ldo, const RerankDims& d, const SparseWs& w, cudaStream_t st) {
+                                 void* out, int64_t ldo, const RerankDims& d, const SparseWs& w, cudaStream_t st,
+                                 const EvalFuse* ev = nullptr) {
   static bool attr = false;
   if (!attr) {
     RB_CUDA(cudaFuncSetAttribute(expand_v_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 4096 * 12));
@@ -753,9 +780,17 @@ static int jaccard_sparse_stages(const int32_t* rank, const float* sql2, int64_t
   { ProfScope _ps("inv_fill_kernel", st); inv_fill_kernel<<<N, 128, 0, st>>>(w.v2cols, w.v2vals, w.v2cnt, N, d.cap2, w.cursor, w.inv_row, w.inv_val); }
   RB_LAUNCH_CHECK("inv_fill_kernel");
   const int jr_cap = k2 > 1 ? d.cap2 : d.cap1;
-  { ProfScope _ps("jaccard_rows_kernel", st); jaccard_rows_kernel<<<nrows, JR_THREADS, jaccard_rows_smem(N, jr_cap), st>>>(
+  EvalFuse evf;
+  memset(&evf, 0, sizeof(evf));
+  size_t jr_smem = jaccard_rows_smem(N, jr_cap);
+  if (ev) {
+    evf = *ev;
+    evf.enabled = 1;
+    if (jr_smem < sizeof(EvalScratch) + 16) jr_smem = sizeof(EvalScratch) + 16;
+  }
+  { ProfScope _ps("jaccard_rows_kernel", st); jaccard_rows_kernel<<<nrows, JR_THREADS, jr_smem, st>>>(
       w.v2cols, w.v2vals, w.v2cnt, d.cap2, w.colptr, w.inv_row, w.inv_val, N, row0, col0, ncols, lambda_value, sql2, lds,
-      use_f16, out, ldo); }
+      use_f16, out, ldo, evf); }
   RB_LAUNCH_CHECK("jaccard_rows_kernel");
   return REIDB200_OK;
 }
@@ -849,4 +884,68 @@ extern "C" int reidb200_k_reciprocal(const int32_t* rank, int N, int k1_cols, in
   { ProfScope _ps("krecip_kernel", (cudaStream_t)stream); krecip_kernel<<<ceil_div(N, 8), 256, 0, (cudaStream_t)stream>>>(rank, N, k1_cols, kc, k + 1, out_idx, out_cnt); }
   RB_LAUNCH_CHECK("krecip_kernel");
   return REIDB200_OK;
+}
+
+// Re-ranked evaluation in one call: merged = [gallery (G rows); query (Q rows)], Jaccard re-ranking blended with the
+// Euclidean distance on the Q x G block, CMC / mAP reduced by the CTA that produces each query row (EvalFuse).
+// out_dist may be null: the re-ranked matrix is then never written.
+extern "C" size_t reidb200_rerank_eval_workspace_bytes(int N, int d, int k1, int k2, int Q, int G) {
+  if (N <= 0 || d <= 0 || k1 <= 0 || k2 <= 0 || Q <= 0 || G <= 0) return 0;
+  CarveSize c;
+  c.take<char>(reidb200_jaccard_workspace_bytes(N, d, k1, k2));
+  c.take<int32_t>(G);   // first-hit histogram
+  c.take<double>(Q);    // per-query AP
+  c.take<int32_t>(Q);   // first hit
+  c.take<int32_t>(64);  // status
+  return align_up(c.off, 256);
+}
+
+extern "C" int reidb200_rerank_eval(const float* feats, int G, int Q, int64_t ldf, int d, int k1, int k2, float lambda_value,
+                                    const int32_t* ql, const int32_t* qc, const int32_t* gl, const int32_t* gc,
+                                    float* out_dist, int64_t ldo, float* out_cmc, double* out_ap, void* workspace,
+                                    size_t workspace_bytes, void* stream) {
+  RB_REQUIRE(feats && ql && qc && gl && gc && out_cmc && out_ap && G > 0 && Q > 0 && d > 0 && ldf >= d,
+             "rerank_eval: bad argument");
+  RB_REQUIRE(G <= JR_PF * JR_THREADS, "rerank_eval: the fused evaluation holds at most %d gallery columns per query row (G=%d); "
+             "use reidb200_jaccard + reidb200_eval_cmc_map", JR_PF * JR_THREADS, G);
+  RB_REQUIRE(out_dist == nullptr || ldo >= G, "rerank_eval: ldo too small");
+  const int N = G + Q;
+  RB_REQUIRE(workspace && workspace_bytes >= reidb200_rerank_eval_workspace_bytes(N, d, k1, k2, Q, G), "rerank_eval: workspace too small");
+  RB_REQUIRE((reinterpret_cast<uintptr_t>(workspace) & 255) == 0, "rerank_eval: workspace must be 256-byte aligned");
+  const RerankDims rd = rerank_dims(N, k1, k2);
+  int rc = rerank_check(N, k1, k2, rd);
+  if (rc) return rc;
+  cudaStream_t st = (cudaStream_t)stream;
+  Carver c0(workspace, workspace_bytes);
+  const size_t jbytes = reidb200_jaccard_workspace_bytes(N, d, k1, k2);
+  char* jws = c0.take<char>(jbytes);
+  EvalFuse ev;
+  ev.ql = ql; ev.qc = qc; ev.gl = gl; ev.gc = gc;
+  ev.hist = c0.take<int32_t>(G);
+  ev.ap_q = c0.take<double>(Q);
+  ev.first = c0.take<int32_t>(Q);
+  ev.status = c0.take<int32_t>(64);
+  ev.enabled = 1;
+  RB_CUDA(cudaMemsetAsync(ev.hist, 0, (size_t)G * sizeof(int32_t), st));
+  RB_CUDA(cudaMemsetAsync(ev.status, 0, 64 * sizeof(int32_t), st));
+  Carver c(jws, jbytes);
+  char* packed = c.take<char>(packed_bytes(N, d));
+  float* sqn = c.take<float>(N);
+  float* isc = c.take<float>(N);
+  float* sql2 = c.take<float>((size_t)N * rd.lds);
+  float* rank_d = c.take<float>((size_t)N * k1);
+  int32_t* rank_i = c.take<int32_t>((size_t)N * k1);
+  const int ldcr = ceil_div((int)rd.lds, 32);
+  float* cred = c.take<float>((size_t)N * ldcr);
+  SparseWs w;
+  carve_sparse(c, N, k1, k2, rd, &w);
+  rc = pack_rows_launch(feats, N, ldf, d, packed, sqn, isc, st);
+  if (rc) return rc;
+  rc = gemm_split_launch(packed, sqn, isc, N, packed, sqn, isc, N, d, REIDB200_DIST_SQL2, sql2, rd.lds, st, cred, ldcr, 0, 0);
+  if (rc) return rc;
+  rc = topk_rows_launch(sql2, N, N, rd.lds, nullptr, k1, 0, 0, rank_d, rank_i, 0, st, cred, ldcr);
+  if (rc) return rc;
+  rc = jaccard_sparse_stages(rank_i, sql2, rd.lds, sqn, N, k1, k2, 0, lambda_value, G, Q, 0, G, out_dist, ldo, rd, w, st, &ev);
+  if (rc) return rc;
+  return eval_finalize_launch(ev.hist, ev.ap_q, Q, G, out_cmc, out_ap, st);
 }

@@ -136,8 +136,7 @@ def evaluate_all_reranked_device(qf, ql, qc, gf, gl, gc, k1=20, k2=6, lambda_val
         dev = qf.device if isinstance(qf, torch.Tensor) and qf.is_cuda else L.require_device()
         merged = torch.empty((G + Q, D), dtype=torch.float32, device=dev)
     _merge_into(merged, gf, qf)
-    dist = ops.jaccard(merged, k1, k2, False, lambda_value, rows=(G, Q), cols=(0, G))
-    return ops.eval_cmc_map(dist, _labels(ql), _labels(qc), _labels(gl), _labels(gc), descending=False)
+    return ops.rerank_eval(merged, G, _labels(ql), _labels(qc), _labels(gl), _labels(gc), k1, k2, lambda_value)
 
 
 class RerankedEvalStream:
@@ -196,8 +195,7 @@ class RerankedEvalStream:
             ready.record(self.copy_stream)
         with torch.cuda.stream(self.compute_stream):
             self.compute_stream.wait_event(ready)
-            dist = ops.jaccard(slot["merged"], k1, k2, False, lambda_value, rows=(G, Q), cols=(0, G))
-            cmc, ap = ops.eval_cmc_map(dist, views[0], views[1], views[2], views[3], descending=False)
+            cmc, ap = ops.rerank_eval(slot["merged"], G, views[0], views[1], views[2], views[3], k1, k2, lambda_value)
             free = torch.cuda.Event()
             free.record(self.compute_stream)
             slot["cmc_h"].copy_(cmc, non_blocking=True)

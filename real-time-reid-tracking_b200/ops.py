@@ -247,6 +247,38 @@ def resize_pil_u8(src, crop_off, crop_geom, max_h, out_h=256, out_w=128):
     return out
 
 
+RERANK_EVAL_MAX_G = 16384  # gallery columns one CTA of the fused kernel keeps in registers (JR_PF * JR_THREADS)
+
+
+def rerank_eval(merged, G, ql, qc, gl, gc, k1=20, k2=6, lambda_value=0.3, want_dist=False):
+    """Fused re-ranked evaluation of merged = [gallery (G rows); query]: (cmc f32[G], ap f64[1][, dist f32[Q,G]]) on
+    device.  Same values as jaccard(rows=(G,Q), cols=(0,G), lambda) followed by eval_cmc_map(descending=False); the
+    re-ranked matrix is only materialised when want_dist."""
+    merged = _f32(merged)
+    dev = L.require_device(merged)
+    N, d = merged.shape
+    Q = N - int(G)
+    if Q <= 0 or G <= 0:
+        raise ValueError("rerank_eval: empty query or gallery set")
+    if G > RERANK_EVAL_MAX_G:
+        dist = jaccard(merged, k1, k2, False, lambda_value, rows=(G, Q), cols=(0, G))
+        cmc, ap = eval_cmc_map(dist, ql, qc, gl, gc, descending=False)
+        return (cmc, ap, dist) if want_dist else (cmc, ap)
+    ql, qc, gl, gc = _i32(ql, dev), _i32(qc, dev), _i32(gl, dev), _i32(gc, dev)
+    if ql.numel() != Q or qc.numel() != Q or gl.numel() != G or gc.numel() != G:
+        raise ValueError("label / camera vectors do not match the query / gallery sets")
+    lib = L.load()
+    cmc = torch.empty(G, dtype=torch.float32, device=dev)
+    ap = torch.empty(1, dtype=torch.float64, device=dev)
+    dist = torch.empty((Q, G), dtype=torch.float32, device=dev) if want_dist else None
+    ws = L.workspace(lib.reidb200_rerank_eval_workspace_bytes(N, d, k1, k2, Q, G), dev)
+    with torch.cuda.device(dev):
+        L.check(lib.reidb200_rerank_eval(merged.data_ptr(), int(G), Q, merged.stride(0), d, k1, k2, float(lambda_value), ql.data_ptr(),
+                                         qc.data_ptr(), gl.data_ptr(), gc.data_ptr(), L.ptr(dist), G, cmc.data_ptr(), ap.data_ptr(),
+                                         ws.data_ptr(), ws.numel(), L.stream_ptr()))
+    return (cmc, ap, dist) if want_dist else (cmc, ap)
+
+
 # ----------------------------------------------------------------------------------------- association
 class Gallery:
     """Device-resident per-track feature ring buffer [slots, budget, d] (NearestNeighborDistanceMetric.samples)."""

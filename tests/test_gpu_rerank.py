@@ -103,3 +103,23 @@ def test_jaccard_other_k_vs_oracle(rb, k1, k2):
     J = F.compute_jaccard_distance(torch.from_numpy(feats), k1=k1, k2=k2, print_flag=False)
     Jo = O.compute_jaccard_distance(feats, k1=k1, k2=k2)
     np.testing.assert_allclose(J, Jo, atol=5e-6)
+
+
+@pytest.mark.parametrize("lam", [0.3, 0.0])
+def test_fused_rerank_eval_equals_two_calls(rb, lam):
+    """ops.rerank_eval (evaluation fused into the re-rank kernel) gives the CMC / mAP of jaccard + eval_cmc_map bit for
+    bit, and the matrix it optionally writes is the one jaccard writes."""
+    from reidb200 import ops, synth
+
+    d = synth.market_like(Q=130, G=700, D=64, n_ids=35, seed=31)
+    d["gl"][::17] = -1                      # junk gallery rows
+    d["ql"][5] = 10 ** 6                    # a query without any good match: the -1 sentinel path
+    merged = torch.from_numpy(np.concatenate([d["gf"], d["qf"]], 0)).cuda()
+    G, Q = 700, 130
+    lab = [torch.from_numpy(d[k].astype(np.int32)).cuda() for k in ("ql", "qc", "gl", "gc")]
+    dist = ops.jaccard(merged, 20, 6, False, lam, rows=(G, Q), cols=(0, G))
+    cmc2, ap2 = ops.eval_cmc_map(dist, *lab, descending=False)
+    cmc1, ap1, dist1 = ops.rerank_eval(merged, G, *lab, 20, 6, lam, want_dist=True)
+    assert torch.equal(dist1, dist) and torch.equal(cmc1, cmc2) and torch.equal(ap1, ap2)
+    cmc0, ap0 = ops.rerank_eval(merged, G, *lab, 20, 6, lam)
+    assert torch.equal(cmc0, cmc2) and torch.equal(ap0, ap2)
