@@ -103,6 +103,8 @@ __device__ __forceinline__ uint32_t float_to_ordered(float f) {
 // larger distances are one shuffle per element.  Everything unrolls: k[] and v[] stay in registers.
 template <int S, bool HAS_VAL>
 __device__ __forceinline__ void warp_bitonic_sort(uint32_t (&k)[S], uint32_t (&v)[S], int lane) {
+  // every compare-exchange is written as selects (no branches: the compiler otherwise emits a divergent-branch
+  // sequence per exchange, which tripled the instruction count of the sort)
 #pragma unroll
   for (int kk = 2; kk <= 32 * S; kk <<= 1) {
 #pragma unroll
@@ -113,11 +115,17 @@ __device__ __forceinline__ void warp_bitonic_sort(uint32_t (&k)[S], uint32_t (&v
 #pragma unroll
         for (int s = 0; s < S; ++s) {
           const bool up = ((lane * S + s) & kk) == 0;
-          const uint32_t ok = __shfl_xor_sync(0xffffffffu, k[s], lj);
-          uint32_t ov = 0;
-          if (HAS_VAL) ov = __shfl_xor_sync(0xffffffffu, v[s], lj);
-          const bool take = (lower == up) ? (ok < k[s]) : (ok > k[s]);
-          if (take) { k[s] = ok; if (HAS_VAL) v[s] = ov; }
+          const bool keep_min = lower == up;
+          const uint32_t mine = k[s];
+          const uint32_t ok = __shfl_xor_sync(0xffffffffu, mine, lj);
+          if (HAS_VAL) {
+            const uint32_t ov = __shfl_xor_sync(0xffffffffu, v[s], lj);
+            const bool take = keep_min ? (ok < mine) : (ok > mine);
+            k[s] = take ? ok : mine;
+            v[s] = take ? ov : v[s];
+          } else {
+            k[s] = keep_min ? min(mine, ok) : max(mine, ok);
+          }
         }
       } else {
 #pragma unroll
@@ -125,9 +133,17 @@ __device__ __forceinline__ void warp_bitonic_sort(uint32_t (&k)[S], uint32_t (&v
           if ((s & j) == 0) {
             const bool up = ((lane * S + s) & kk) == 0;
             const uint32_t a = k[s], b = k[s | j];
-            if ((a > b) == up) {
-              k[s] = b; k[s | j] = a;
-              if (HAS_VAL) { const uint32_t t = v[s]; v[s] = v[s | j]; v[s | j] = t; }
+            if (HAS_VAL) {
+              const bool sw = (a > b) == up;
+              const uint32_t va = v[s], vb = v[s | j];
+              k[s] = sw ? b : a;
+              k[s | j] = sw ? a : b;
+              v[s] = sw ? vb : va;
+              v[s | j] = sw ? va : vb;
+            } else {
+              const uint32_t lo = min(a, b), hi = max(a, b);
+              k[s] = up ? lo : hi;
+              k[s | j] = up ? hi : lo;
             }
           }
         }

@@ -413,8 +413,8 @@ qexpand_kernel(const int32_t* __restrict__ rank, int k1_cols, int k2, const int3
 }
 
 // Warp-per-row variant for rows whose k2 lists hold at most 256 entries in total (the common case): the entries are
-// keyed (column, neighbour j), sorted by warp_bitonic_sort with their weights as payload, staged in shared memory,
-// and every run of equal columns is summed in neighbour order by its first element.  Rows with more entries are
+// keyed (column, position in the concatenated lists), sorted by warp_bitonic_sort, and every run of equal columns is
+// summed in neighbour order by its first element, the weights read from shared memory through the key's low bits.  Rows with more entries are
 // appended to long_list and left to qexpand_kernel.
 constexpr int QEW_WARPS = 4;
 
@@ -445,26 +445,24 @@ qexpand_warp_kernel(const int32_t* __restrict__ rank, int k1_cols, int k2, const
   s_off[w][lane] = off;  // lanes >= k2 hold n
   if (lane == 31) s_off[w][32] = n;
   __syncwarp();
-  uint32_t k[8], v[8];
+  // key = (column << 8) | element index e: e grows with the neighbour index j, so sorting the keys alone orders every
+  // column's entries by neighbour; the weights stay in shared memory at their original positions (no payload)
+  uint32_t k[8], nov[8];
 #pragma unroll
   for (int s = 0; s < 8; ++s) {
     const int e = lane * 8 + s;
     k[s] = SENT;
-    v[s] = 0u;
     if (e < n) {
       int j = 0;
       while (e >= s_off[w][j + 1]) ++j;
       const size_t src = (size_t)s_row[w][j] * cap1 + (e - s_off[w][j]);
-      k[s] = ((uint32_t)vcols[src] << 5) | (uint32_t)j;
-      v[s] = __float_as_uint(vvals[src]);
+      k[s] = ((uint32_t)vcols[src] << 8) | (uint32_t)e;
+      s_val[w][e] = vvals[src];
     }
   }
-  warp_bitonic_sort<8, true>(k, v, lane);
+  warp_bitonic_sort<8, false>(k, nov, lane);
 #pragma unroll
-  for (int s = 0; s < 8; ++s) {
-    s_key[w][lane * 8 + s] = k[s];
-    s_val[w][lane * 8 + s] = __uint_as_float(v[s]);
-  }
+  for (int s = 0; s < 8; ++s) s_key[w][lane * 8 + s] = k[s];
   __syncwarp();
   const uint32_t last_prev = __shfl_up_sync(0xffffffffu, k[7], 1);
   bool head[8];
@@ -472,7 +470,7 @@ qexpand_warp_kernel(const int32_t* __restrict__ rank, int k1_cols, int k2, const
 #pragma unroll
   for (int s = 0; s < 8; ++s) {
     const uint32_t prev = s == 0 ? last_prev : k[s - 1];
-    head[s] = k[s] != SENT && ((lane == 0 && s == 0) || (prev >> 5) != (k[s] >> 5));
+    head[s] = k[s] != SENT && ((lane == 0 && s == 0) || (prev >> 8) != (k[s] >> 8));
     cnt += head[s] ? 1 : 0;
   }
   int nu;
@@ -481,9 +479,9 @@ qexpand_warp_kernel(const int32_t* __restrict__ rank, int k1_cols, int k2, const
   for (int s = 0; s < 8; ++s)
     if (head[s]) {
       const int e = lane * 8 + s;
-      const uint32_t c = k[s] >> 5;
-      float sum = __uint_as_float(v[s]);
-      for (int t = e + 1; t < n && (s_key[w][t] >> 5) == c; ++t) sum = __fadd_rn(sum, s_val[w][t]);
+      const uint32_t c = k[s] >> 8;
+      float sum = s_val[w][k[s] & 255u];
+      for (int t = e + 1; t < n && (s_key[w][t] >> 8) == c; ++t) sum = __fadd_rn(sum, s_val[w][s_key[w][t] & 255u]);
       float val = __fdiv_rn(sum, (float)k2);
       if (use_f16) val = __half2float(__float2half_rn(val));
       qcols[(size_t)i * cap2 + slot] = (int32_t)c;
