@@ -865,7 +865,7 @@ extern "C" int reidb200_jaccard(const float* feats, int N, int64_t ldf, int d, i
   carve_sparse(c, N, k1, k2, rd, &w);
   rc = pack_rows_launch(feats, N, ldf, d, packed, sqn, isc, st);
   if (rc) return rc;
-  rc = gemm_split_launch(packed, sqn, isc, N, packed, sqn, isc, N, d, REIDB200_DIST_SQL2, sql2, rd.lds, st, cred, ldcr, 0, getenv("REIDB200_BLOCKED_EXP") ? 1 : 0);
+  rc = gemm_split_launch(packed, sqn, isc, N, packed, sqn, isc, N, d, REIDB200_DIST_SQL2, sql2, rd.lds, st, cred, ldcr, 0, 0);
   if (rc) return rc;
   rc = topk_rows_launch(sql2, N, N, rd.lds, nullptr, k1, 0, 0, rank_d, rank_i, 0, st, cred, ldcr);
   if (rc) return rc;
