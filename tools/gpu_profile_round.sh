@@ -6,4 +6,4 @@ timeout 300 python __graft_entry__.py smoke > gpurun_out/smoke.log 2>&1; echo "s
 timeout 900 python bench.py --impl reference --steps 2 --warmup 1 > gpurun_out/bench_ref.json 2> gpurun_out/bench_ref.err; echo "ref rc=$?"
 timeout 1200 python bench.py > gpurun_out/bench_full.json 2> gpurun_out/bench_full.err; echo "bench rc=$?"; tail -3 gpurun_out/bench_full.err
 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/launches_bench.csv python bench.py --steps 2 --warmup 3 --no-cpu --no-retrieval --no-assoc > gpurun_out/ncu_launch.log 2>&1; echo "launch list rc=$?"
-timeout 900 ncu --set full --clock-control none --import-source on -s 14 -c 14 -f -o gpurun_out/r01_step_full_b python tools/step_once.py 2 > gpurun_out/ncu_step.log 2>&1; echo "ncu step rc=$?"
+timeout 900 ncu --set full --clock-control none --import-source on -s 12 -c 12 -f -o gpurun_out/r01_step_full_c python tools/step_once_fused.py 2 > gpurun_out/ncu_step.log 2>&1; echo "ncu step rc=$?"
