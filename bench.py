@@ -404,8 +404,15 @@ def run_ours(args):
     merged = merged_host.to(dev)
     lab = {k: v.to(dev) for k, v in lab_host.items()}
 
-    def step():  # fused: the CTA that produces a query's re-ranked row reduces it to AP / first hit at once
+    def step_launches():  # fused: the CTA that produces a query's re-ranked row reduces it to AP / first hit at once
         return ops.rerank_eval(merged, G, lab["ql"], lab["qc"], lab["gl"], lab["gc"], K1, K2, LAMBDA)
+
+    # the same call captured once as a CUDA graph (ops.RerankEvalPlan): what evaluate.evaluate_all_reranked replays
+    plan = ops.RerankEvalPlan(G, Q, D_FULL, K1, K2, LAMBDA, dev)
+    plan.merged.copy_(merged)
+    for dst, k in ((plan.ql, "ql"), (plan.qc, "qc"), (plan.gl, "gl"), (plan.gc, "gc")):
+        dst.copy_(lab[k])
+    step = plan.run
 
     def step_materialised():  # the same evaluation with the re-ranked Q x G matrix written and re-read (two calls)
         dist_qg = ops.jaccard(merged, K1, K2, False, LAMBDA, rows=(G, Q), cols=(0, G))
@@ -420,8 +427,11 @@ def run_ours(args):
     ms = _timed(step, args.steps, barrier)  # the headline: K steps, nothing but the product's launches on the stream
     # a second pass of K steps with every kernel bracketed by CUDA events on its launch stream (kernel shares, the
     # roofline kernel's launch time, the launch count); the event pairs cost a few per cent, hence the separate pass
+    cmc_l, ap_l = step_launches()
+    assert torch.equal(cmc_l, cmc) and torch.equal(ap_l, ap), "graph replay and plain launches differ"
+    ms_launch = _timed(step_launches, args.steps, barrier)  # the same kernels launched one by one (no graph)
     L.profile_enable(True)
-    ms_prof = _timed(step, args.steps, barrier)
+    ms_prof = _timed(step_launches, args.steps, barrier)
     prof = L.profile_read()
     L.profile_enable(False)
     clk = clocks.stop() if rank == 0 else None
@@ -510,7 +520,9 @@ def run_ours(args):
         "config": {"workload": "market1501_rerank_k20_6_l0.3", "queries": Q, "gallery": G, "dim": D_FULL, "k1": K1, "k2": K2,
                    "lambda": LAMBDA, "parallelism": "independent evaluation sets per GPU" if world > 1 else "single GPU",
                    "l2": "working set (1.49 GB distance matrix + 0.5 GB sparse tables per step) larger than L2",
-                   "evaluation": "fused into the re-rank kernel (ops.rerank_eval); ms_per_step_materialised = jaccard + eval_cmc_map"},
+                   "evaluation": "fused into the re-rank kernel (ops.rerank_eval); ms_per_step_materialised = jaccard + eval_cmc_map",
+                   "launch": "one CUDA graph replay per step (ops.RerankEvalPlan); ms_per_step_stream_launches = the same kernels launched one by one"},
+        "ms_per_step_stream_launches": ms_launch / args.steps,
         "ms_per_step_materialised": ms_mat, "ms_per_step_with_kernel_events": ms_prof / args.steps,
         "clocks": clk,
         "e2e": {"value": e2e_value, "unit": "pairs/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),

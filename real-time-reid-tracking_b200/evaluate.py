@@ -127,13 +127,48 @@ def _merge_into(merged, gf, qf):
     return merged
 
 
+_plan = {}  # the most recent shape's captured evaluation (RerankEvalPlan), reused by back-to-back calls
+
+
+def release_plans():
+    """Drop the cached CUDA graph and its buffers (workspace of about 4 * N^2 bytes)."""
+    _plan.clear()
+
+
+def _copy_labels(lab, Q, G, ql, qc, gl, gc):
+    off, views = 0, []
+    for v, n in ((ql, Q), (qc, Q), (gl, G), (gc, G)):  # the order of RerankEvalPlan.lab
+        t = _labels(v)
+        if t.numel() != n:
+            raise ValueError("label / camera vectors do not match the query / gallery sets")
+        if t.dtype != torch.int32:
+            t = t.to(torch.int32)
+        lab[off:off + n].copy_(t, non_blocking=True)
+        views.append(lab[off:off + n])
+        off += n
+    return views
+
+
 def evaluate_all_reranked_device(qf, ql, qc, gf, gl, gc, k1=20, k2=6, lambda_value=0.3, merged=None):
     """Re-ranked evaluation, device resident: merged = cat(gallery, query) (image_reid_inference.py:270), Jaccard
     re-ranking blended with the Euclidean distance, CMC/mAP on the re-ranked Q x G distance.  Returns CUDA tensors
-    (CMC f32[G], mAP f64[1]) without a host sync.  `merged` = optional preallocated f32[G+Q, D] device buffer."""
+    (CMC f32[G], mAP f64[1]) without a host sync.  With `merged` (a preallocated f32[G+Q, D] device buffer) the kernels
+    are launched one by one; without it the call replays the CUDA graph cached for its shape (ops.RerankEvalPlan)."""
     G, Q, D = int(gf.shape[0]), int(qf.shape[0]), int(qf.shape[1])
+    dev = qf.device if isinstance(qf, torch.Tensor) and qf.is_cuda else L.require_device()
+    if merged is None and 0 < G <= ops.RERANK_EVAL_MAX_G and Q > 0:
+        key = (dev, G, Q, D, int(k1), int(k2), float(lambda_value))
+        plan = _plan.get(key)
+        if plan is None:
+            _plan.clear()
+            with torch.cuda.device(dev):
+                plan = _plan[key] = ops.RerankEvalPlan(G, Q, D, k1, k2, lambda_value, dev)
+        with torch.cuda.device(dev):
+            _merge_into(plan.merged, gf, qf)
+            _copy_labels(plan.lab, Q, G, ql, qc, gl, gc)
+            cmc, ap = plan.run()
+            return cmc.clone(), ap.clone()
     if merged is None:
-        dev = qf.device if isinstance(qf, torch.Tensor) and qf.is_cuda else L.require_device()
         merged = torch.empty((G + Q, D), dtype=torch.float32, device=dev)
     _merge_into(merged, gf, qf)
     return ops.rerank_eval(merged, G, _labels(ql), _labels(qc), _labels(gl), _labels(gc), k1, k2, lambda_value)
@@ -159,12 +194,17 @@ class RerankedEvalStream:
         self.slots = [dict(busy=None, free=None) for _ in range(self.depth)]
         self.n = 0
 
-    def _buffers(self, slot, Q, G, D):
-        key = (Q, G, D)
+    def _buffers(self, slot, Q, G, D, k1, k2, lambda_value):
+        key = (Q, G, D, int(k1), int(k2), float(lambda_value))
         if slot.get("key") != key:
             with torch.cuda.device(self.dev):
-                slot["merged"] = torch.empty((G + Q, D), dtype=torch.float32, device=self.dev)
-                slot["lab"] = torch.empty(2 * (Q + G), dtype=torch.int32, device=self.dev)
+                # a captured CUDA graph per slot when the fused kernel covers the gallery, plain launches otherwise
+                slot["plan"] = ops.RerankEvalPlan(G, Q, D, k1, k2, lambda_value, self.dev) if G <= ops.RERANK_EVAL_MAX_G else None
+                if slot["plan"] is not None:
+                    slot["merged"], slot["lab"] = slot["plan"].merged, slot["plan"].lab
+                else:
+                    slot["merged"] = torch.empty((G + Q, D), dtype=torch.float32, device=self.dev)
+                    slot["lab"] = torch.empty(2 * (Q + G), dtype=torch.int32, device=self.dev)
                 slot["cmc_h"] = torch.empty(G, dtype=torch.float32).pin_memory()
                 slot["ap_h"] = torch.empty(1, dtype=torch.float64).pin_memory()
             slot["key"] = key
@@ -176,26 +216,21 @@ class RerankedEvalStream:
         slot = self.slots[ticket % self.depth]
         if slot["busy"] is not None:  # the slot's previous evaluation must have been collected or at least finished
             slot["busy"].synchronize()
-        self._buffers(slot, Q, G, D)
+        self._buffers(slot, Q, G, D, k1, k2, lambda_value)
         lab = slot["lab"]
         with torch.cuda.stream(self.copy_stream):
             if slot["free"] is not None:
                 self.copy_stream.wait_event(slot["free"])  # kernels of the slot's previous occupant are done
             _merge_into(slot["merged"], gf, qf)
-            off = 0
-            views = []
-            for v, n in ((ql, Q), (qc, Q), (gl, G), (gc, G)):
-                t = _labels(v)
-                if t.dtype != torch.int32:
-                    t = t.to(torch.int32)
-                lab[off:off + n].copy_(t, non_blocking=True)
-                views.append(lab[off:off + n])
-                off += n
+            views = _copy_labels(lab, Q, G, ql, qc, gl, gc)
             ready = torch.cuda.Event()
             ready.record(self.copy_stream)
         with torch.cuda.stream(self.compute_stream):
             self.compute_stream.wait_event(ready)
-            cmc, ap = ops.rerank_eval(slot["merged"], G, views[0], views[1], views[2], views[3], k1, k2, lambda_value)
+            if slot["plan"] is not None:
+                cmc, ap = slot["plan"].run()
+            else:
+                cmc, ap = ops.rerank_eval(slot["merged"], G, views[0], views[1], views[2], views[3], k1, k2, lambda_value)
             free = torch.cuda.Event()
             free.record(self.compute_stream)
             slot["cmc_h"].copy_(cmc, non_blocking=True)

@@ -279,6 +279,51 @@ def rerank_eval(merged, G, ql, qc, gl, gc, k1=20, k2=6, lambda_value=0.3, want_d
     return (cmc, ap, dist) if want_dist else (cmc, ap)
 
 
+class RerankEvalPlan:
+    """One fused re-ranked evaluation at a fixed shape, captured once as a CUDA graph and replayed: the ~12 kernel
+    launches and memsets of reidb200_rerank_eval cost one graph launch, and every buffer (features, labels, workspace,
+    results) is owned by the plan.  Fill `merged` ([gallery; query] rows) and `ql/qc/gl/gc` (views of one int32 buffer),
+    then run(); `cmc` / `ap` hold the result of the latest replay on the stream run() was called on.  Same values as
+    rerank_eval on the same inputs (the same kernels run)."""
+
+    def __init__(self, G, Q, D, k1=20, k2=6, lambda_value=0.3, device=None):
+        G, Q, D = int(G), int(Q), int(D)
+        if Q <= 0 or G <= 0:
+            raise ValueError("RerankEvalPlan: empty query or gallery set")
+        if G > RERANK_EVAL_MAX_G:
+            raise ValueError("RerankEvalPlan: G = %d exceeds the fused kernel's %d gallery columns" % (G, RERANK_EVAL_MAX_G))
+        self.dev = dev = device or L.require_device()
+        self.G, self.Q, self.D, self.k1, self.k2, self.lambda_value = G, Q, D, int(k1), int(k2), float(lambda_value)
+        lib = L.load()
+        N = G + Q
+        with torch.cuda.device(dev):
+            self.merged = torch.empty((N, D), dtype=torch.float32, device=dev).normal_()
+            self.lab = torch.zeros(2 * N, dtype=torch.int32, device=dev)
+            self.ql, self.qc, self.gl, self.gc = self.lab[:Q], self.lab[Q:2 * Q], self.lab[2 * Q:2 * Q + G], self.lab[2 * Q + G:]
+            self.cmc = torch.empty(G, dtype=torch.float32, device=dev)
+            self.ap = torch.empty(1, dtype=torch.float64, device=dev)
+            self._ws = L.workspace(lib.reidb200_rerank_eval_workspace_bytes(N, D, self.k1, self.k2, Q, G), dev)
+            # first call outside the capture (one-time kernel attributes), on well-formed random rows
+            side = torch.cuda.Stream(dev)
+            side.wait_stream(torch.cuda.current_stream(dev))
+            with torch.cuda.stream(side):
+                self._launch()
+            side.synchronize()
+            self.graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(self.graph, stream=side):
+                self._launch()
+
+    def _launch(self):
+        L.check(L.load().reidb200_rerank_eval(self.merged.data_ptr(), self.G, self.Q, self.merged.stride(0), self.D, self.k1,
+                                              self.k2, self.lambda_value, self.ql.data_ptr(), self.qc.data_ptr(),
+                                              self.gl.data_ptr(), self.gc.data_ptr(), 0, self.G, self.cmc.data_ptr(),
+                                              self.ap.data_ptr(), self._ws.data_ptr(), self._ws.numel(), L.stream_ptr()))
+
+    def run(self):
+        self.graph.replay()
+        return self.cmc, self.ap
+
+
 # ----------------------------------------------------------------------------------------- association
 class Gallery:
     """Device-resident per-track feature ring buffer [slots, budget, d] (NearestNeighborDistanceMetric.samples)."""

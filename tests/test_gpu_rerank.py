@@ -123,3 +123,29 @@ def test_fused_rerank_eval_equals_two_calls(rb, lam):
     assert torch.equal(dist1, dist) and torch.equal(cmc1, cmc2) and torch.equal(ap1, ap2)
     cmc0, ap0 = ops.rerank_eval(merged, G, *lab, 20, 6, lam)
     assert torch.equal(cmc0, cmc2) and torch.equal(ap0, ap2)
+
+
+def test_rerank_eval_plan_replays_the_same_evaluation(rb):
+    """ops.RerankEvalPlan (the evaluation captured as one CUDA graph) returns what the plain launches return, replay
+    after replay with new inputs in its buffers; evaluate_all_reranked reuses the cached plan for a repeated shape."""
+    from reidb200 import evaluate as E, ops, synth
+
+    G, Q = 640, 110
+    plan = ops.RerankEvalPlan(G, Q, 64, 20, 6, 0.3)
+    for seed in (41, 42, 43):
+        d = synth.market_like(Q=Q, G=G, D=64, n_ids=30, seed=seed)
+        merged = torch.from_numpy(np.concatenate([d["gf"], d["qf"]], 0)).cuda()
+        lab = [torch.from_numpy(d[k].astype(np.int32)).cuda() for k in ("ql", "qc", "gl", "gc")]
+        plan.merged.copy_(merged)
+        for dst, src in zip((plan.ql, plan.qc, plan.gl, plan.gc), lab):
+            dst.copy_(src)
+        cmc_g, ap_g = [t.clone() for t in plan.run()]
+        cmc, ap = ops.rerank_eval(merged, G, *lab, 20, 6, 0.3)
+        assert torch.equal(cmc_g, cmc) and torch.equal(ap_g, ap)
+        keys = ("qf", "ql", "qc", "gf", "gl", "gc")
+        cmc_h, ap_h = E.evaluate_all_reranked(*[d[k] for k in keys], 20, 6, 0.3, verbose=False)
+        assert torch.equal(cmc_h, cmc.cpu()) and ap_h == float(ap.cpu()[0])
+    assert len(E._plan) == 1
+    E.release_plans()
+    with pytest.raises(ValueError):
+        ops.RerankEvalPlan(ops.RERANK_EVAL_MAX_G + 1, 4, 64)
