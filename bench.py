@@ -263,6 +263,44 @@ def bench_next_rows(steps):
     return res
 
 
+def bench_posttricks(merged, k1, k2, steps):
+    """N4 row at the Market-shaped merged set: DBSCAN / clamp + add on the device-resident N x N Jaccard matrix
+    (ms, CUDA events on the launch stream) with sklearn's DBSCAN on a bounded host sample beside it."""
+    import reidb200  # noqa: F401
+    from reidb200 import _lib as L, ops
+
+    N = merged.shape[0]
+    J = ops.jaccard(merged, k1, k2)
+    res = {"N": int(N), "matrix_bytes": int(N) * int(N) * 4}
+    n = max(steps, 5)
+    for _ in range(2):
+        labels, ncl, core = ops.dbscan_precomputed(J, 0.5, 7)
+    L.profile_enable(True)
+    ms = _timed(lambda: ops.dbscan_precomputed(J, 0.5, 7), n, torch.cuda.synchronize)
+    prof = L.profile_read()
+    L.profile_enable(False)
+    res["dbscan_ms"] = ms / n
+    res["dbscan_kernel_ms"] = {k: v[1] / v[0] for k, v in prof.items()}
+    deg = prof.get("dbscan_degree_kernel")
+    if deg:
+        res["dbscan_degree_read_GBps"] = res["matrix_bytes"] / (deg[1] / deg[0] * 1e-3) / 1e9
+    res["dbscan_clusters"], res["dbscan_core"], res["dbscan_noise"] = int(ncl.item()), int(core.sum().item()), int((labels == -1).sum().item())
+    other = torch.rand((N, N), dtype=torch.float32, device=J.device)
+    res["clamp_add_ms"] = _timed(lambda: ops.clamp_add_(J, other), n, torch.cuda.synchronize) / n
+    res["clamp_add_GBps"] = 3 * res["matrix_bytes"] / (res["clamp_add_ms"] * 1e-3) / 1e9
+    try:
+        from sklearn.cluster import DBSCAN
+        S = 4000
+        Jh = ops.jaccard(merged[:S].contiguous(), k1, k2).cpu().numpy()
+        t0 = time.perf_counter()
+        DBSCAN(eps=0.5, min_samples=7, metric="precomputed", n_jobs=-1).fit_predict(Jh)
+        res["sklearn_dbscan_ms_sample"] = (time.perf_counter() - t0) * 1e3
+        res["sklearn_sample"] = "%d x %d sub-matrix on the host cores (the reference's call, n_jobs=-1)" % (S, S)
+    except ImportError:
+        res["sklearn_dbscan_ms_sample"] = None
+    return res
+
+
 RETR_Q, RETR_G, RETR_D, RETR_K, RETR_PIECE = 10_000, 4_000_000, 2048, 100, 62_500
 
 
@@ -489,6 +527,7 @@ def run_ours(args):
     h2d = merged_host.numel() * 4 + sum(v.numel() * 4 for v in lab_host.values())
     d2h = G * 4 + 8
 
+    posttricks = bench_posttricks(merged, K1, K2, args.steps) if (rank == 0 and not args.no_assoc) else None
     retrieval = None
     if not args.no_retrieval:
         merged = None
@@ -542,6 +581,7 @@ def run_ours(args):
     if not args.no_assoc:
         line["assoc"] = bench_assoc(args.steps, args.warmup)
         line["next_rows"] = bench_next_rows(args.steps)
+        line["next_rows"]["n4"] = posttricks
     if not args.no_cpu and world == 1:
         dsmp, qs, gs = cpu_sample()
         t0 = time.perf_counter()

@@ -285,6 +285,31 @@ int reidb200_kf_predict(double* x, double* P, const int32_t* slots, int n, doubl
 int reidb200_kf_update(double* x, double* P, double* SI, const int32_t* slots, const double* measurements,
                        const double* confidences, int n, double w_pos, void* stream);
 
+/* ------------------------------------------------------------------------------------------
+ * N4: the steps around compute_jaccard_distance in reid/image_reid_inference.py, on the device-resident
+ * N x N matrix and embeddings.
+ *   tta_merge_normalize  out = F.normalize((a + b) / 2, dim=1) (image_reid_inference.py:252-253, 268-269); b may be NULL
+ *                        (plain row normalisation)
+ *   clamp_add            dist[dist < 0] = 0 ; dist += other (:287-290); other may be NULL
+ *   dbscan_precomputed   sklearn.cluster.DBSCAN(eps, min_samples, metric="precomputed").fit_predict(dist) (:291-301) on a
+ *                        symmetric f32[N, N] matrix: labels i32[N] (-1 = noise, clusters numbered by their lowest core
+ *                        index as sklearn's search does), n_clusters i32[1] (device, may be NULL), core_out i32[N] 0/1
+ *                        (may be NULL).  N <= 57984 (one CTA numbers the clusters).
+ *   smooth_groups        smooth_tracklets (reid/inference_utils.py:19-27): rows order[seg_start[g] .. seg_start[g+1]) of
+ *                        emb become emb * keep + mean(rows) * avg_w (reference: 0.1 / 0.9) */
+int reidb200_tta_merge_normalize(const float* a, size_t lda, const float* b, size_t ldb, int rows, int D, float* out,
+                                 size_t ldo, void* stream);
+int reidb200_clamp_add(float* dist, int rows, int cols, size_t ld, const float* other, size_t ldo, void* stream);
+size_t reidb200_dbscan_workspace_bytes(int N);
+int reidb200_dbscan_precomputed(const float* dist, int N, size_t ld, float eps, int min_samples, int32_t* labels,
+                                int32_t* n_clusters, int32_t* core_out, void* ws, size_t ws_bytes, void* stream);
+int reidb200_smooth_groups(float* emb, int D, size_t lde, const int32_t* order, const int32_t* seg_start, int n_groups,
+                           float keep, float avg_w, void* stream);
+/* out = x - column mean(x), mean_out f32[D] optional: the centring step of diminish_camera_bias
+ * (reid/inference_utils.py:9-10); its Gram matrix and projection go through reidb200_distmat(kind DOT). */
+int reidb200_center_columns(const float* x, int rows, int D, size_t ldx, float* out, size_t ldo, float* mean_out,
+                            void* stream);
+
 #ifdef __cplusplus
 }
 #endif

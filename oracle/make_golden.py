@@ -424,10 +424,63 @@ def gold_kalman():
     _save("kalman", z0=z0, matched=matched, meas=meas, conf=conf, x=np.stack(xs), P=np.stack(Ps), SI=np.stack(SIs))
 
 
+def gold_posttricks():
+    """N4: flip-TTA merge, clamp + attribute distance add, sklearn's DBSCAN on the precomputed Jaccard matrix,
+    smooth_tracklets and diminish_camera_bias, each produced by the reference's own code / dependency."""
+    import torch.nn.functional as TF
+    from sklearn.cluster import DBSCAN
+    IU = ref_import.load_file("ref_inference_utils", "reid/inference_utils.py")
+    U = ref_import.load_file("ref_losses_utils", "reid/losses/utils.py")
+    rng = np.random.default_rng(17)
+    N, D, n_ids = 420, 32, 28
+    cent = rng.standard_normal((n_ids, D)).astype(np.float32)
+    ids = rng.integers(0, n_ids, N)
+    spread = np.where(rng.random(N) < 0.15, 1.4, 0.35).astype(np.float32)[:, None]  # some outliers: noise / border points
+    e1 = (cent[ids] + spread * rng.standard_normal((N, D))).astype(np.float32)
+    e2 = (e1 + 0.05 * rng.standard_normal((N, D))).astype(np.float32)
+    merged = TF.normalize((torch.from_numpy(e1) + torch.from_numpy(e2)) / 2.0, dim=1)
+    np.testing.assert_allclose(O.tta_merge_normalize(e1, e2), merged.numpy(), rtol=0, atol=2e-7)
+    cams = rng.integers(0, 4, N)
+    unbiased = IU.diminish_camera_bias(merged.clone(), torch.from_numpy(cams).float())
+    np.testing.assert_allclose(O.diminish_camera_bias(merged.numpy(), cams), unbiased.numpy(), rtol=0, atol=2e-5)
+    feats = unbiased.numpy()
+    J = O.compute_jaccard_distance(feats, 20, 6)  # (pinned against the reference in gold_jaccard)
+    attrs = TF.normalize(torch.from_numpy(rng.integers(1, 3, (n_ids, 30)).astype(np.float32)[ids]), dim=1)
+    attr_dist = U.euclidean_dist(attrs, attrs).numpy()
+    out = {}
+    for tag, eps, ms, other in (("plain", 0.5, 7, None), ("attr", 0.62, 5, attr_dist), ("tight", 0.3, 3, None)):
+        d = J.copy()
+        d[d < 0] = 0.
+        if other is not None:
+            d += other
+        np.testing.assert_array_equal(O.clamp_add(J, other), d)
+        cm = DBSCAN(eps=eps, min_samples=ms, metric="precomputed", n_jobs=-1)
+        lab = cm.fit_predict(d)
+        core = np.zeros(N, bool)
+        core[cm.core_sample_indices_] = True
+        olab, ocore = O.dbscan_precomputed(d, eps, ms)
+        assert np.array_equal(olab, lab) and np.array_equal(ocore, core), tag
+        border = (lab != -1) & ~core
+        print("  dbscan %-5s clusters %d noise %d border %d" % (tag, lab.max() + 1, (lab == -1).sum(), border.sum()))
+        assert (lab == -1).any() and lab.max() >= 3
+        out["lab_" + tag], out["core_" + tag] = lab.astype(np.int64), core
+        out["eps_" + tag], out["ms_" + tag] = np.float64(eps), np.int32(ms)
+    assert ((out["lab_plain"] != -1) & ~out["core_plain"]).any() or ((out["lab_attr"] != -1) & ~out["core_attr"]).any()
+    lab = out["lab_plain"]
+    seqs = rng.integers(0, 5, N)
+    num_labels = int(lab.max()) + 1
+    merged_seqs = torch.from_numpy(seqs * num_labels + lab)
+    valid = lab != -1
+    smooth = IU.smooth_tracklets(unbiased.clone(), merged_seqs, valid)
+    np.testing.assert_allclose(O.smooth_tracklets(feats, merged_seqs.numpy(), valid), smooth.numpy(), rtol=0, atol=2e-7)
+    _save("posttricks", e1=e1, e2=e2, merged=merged.numpy(), cams=cams.astype(np.int32), unbiased=feats, J=J,
+          attr_dist=attr_dist, merged_seqs=merged_seqs.numpy().astype(np.int64), smooth=smooth.numpy(), **out)
+
+
 def main():
     assert ref_import.available(), "/root/reference not present: fixtures can only be (re)generated in the build container"
     ref_import.install()
-    for fn in (gold_dist, gold_eval, gold_jaccard, gold_preprocess, gold_assoc, gold_boxpairs, gold_ocsort, gold_kalman):
+    for fn in (gold_dist, gold_eval, gold_jaccard, gold_preprocess, gold_assoc, gold_boxpairs, gold_ocsort, gold_kalman, gold_posttricks):
         print(fn.__name__)
         fn()
     print("oracle pinned against the reference; fixtures in tests/golden/")

@@ -754,3 +754,92 @@ def kf_update(x, P, z, confidence=0.0):
     K = PHT @ SI
     A = np.eye(8) - K @ H
     return x + K @ y, (A @ P) @ A.T + (K @ R) @ K.T, SI
+
+
+# ------------------------------------------------------------------------------------------
+# N4: the steps around compute_jaccard_distance in reid/image_reid_inference.py
+# ------------------------------------------------------------------------------------------
+def tta_merge_normalize(e1: np.ndarray, e2: np.ndarray) -> np.ndarray:
+    """(e1 + e2) / 2.0 then F.normalize(dim=1) = x / max(||x||_2, 1e-12) (image_reid_inference.py:252-253, 268-269)."""
+    v = (np.asarray(e1, np.float32) + np.asarray(e2, np.float32)) / np.float32(2.0)
+    nrm = np.sqrt((v * v).sum(1, dtype=np.float32, keepdims=True)).astype(np.float32)
+    return (v / np.maximum(nrm, np.float32(1e-12))).astype(np.float32)
+
+
+def clamp_add(dists: np.ndarray, other: np.ndarray = None) -> np.ndarray:
+    """dists[dists < 0] = 0 ; dists += attribute_dist (image_reid_inference.py:287-290), float32."""
+    d = np.array(dists, dtype=np.float32, copy=True)
+    d[d < 0] = 0.0
+    if other is not None:
+        d += np.asarray(other, np.float32)
+    return d
+
+
+def dbscan_precomputed(dists: np.ndarray, eps: float, min_samples: int):
+    """sklearn.cluster.DBSCAN(eps, min_samples, metric="precomputed").fit_predict(dists) (image_reid_inference.py:291-301).
+    scikit-learn is a dependency of the reference (requirements.txt:11, unpinned; 1.9.0 in this image) and is not
+    vendored; this restates its published algorithm: cluster/_dbscan.py (neighbourhoods = radius_neighbors(radius=eps)
+    on the dense matrix = np.where(row <= eps), the python float eps compared in the row's float32; core = size >=
+    min_samples, self included) and cluster/_dbscan_inner.pyx (for i ascending: an unlabelled core point seeds a new
+    label and a depth-first search labels every unlabelled neighbour, pushing the core ones).
+    Returns (labels int64[N], core bool[N])."""
+    d = np.asarray(dists)
+    N = d.shape[0]
+    radius = d.dtype.type(eps)
+    neigh = [np.where(d[i] <= radius)[0] for i in range(N)]
+    core = np.array([len(n) >= min_samples for n in neigh], dtype=bool)
+    labels = np.full(N, -1, dtype=np.int64)
+    label_num = 0
+    for i in range(N):
+        if labels[i] != -1 or not core[i]:
+            continue
+        stack = []
+        v = i
+        while True:
+            if labels[v] == -1:
+                labels[v] = label_num
+                if core[v]:
+                    for w in neigh[v]:
+                        if labels[w] == -1:
+                            stack.append(int(w))
+            if not stack:
+                break
+            v = stack.pop()
+        label_num += 1
+    return labels, core
+
+
+def smooth_tracklets(embeddings: np.ndarray, seqs: np.ndarray, indices_valid: np.ndarray) -> np.ndarray:
+    """reid/inference_utils.py:19-27: per unique sequence id, the valid rows become row * 0.1 + mean(valid rows) * 0.9
+    (float32); a sequence id without valid rows is left alone (the reference's bare except)."""
+    e = np.array(embeddings, dtype=np.float32, copy=True)
+    seqs = np.asarray(seqs)
+    valid = np.asarray(indices_valid, dtype=bool)
+    for j in np.unique(seqs):
+        idx = np.logical_and(seqs == j, valid)
+        if not idx.any():
+            continue
+        cur = e[idx]
+        avg = (cur.sum(0, dtype=np.float32) / np.float32(cur.shape[0])).astype(np.float32)
+        e[idx] = cur * np.float32(0.1) + avg[None, :] * np.float32(0.9)
+    return e
+
+
+def diminish_camera_bias(embeddings: np.ndarray, cams: np.ndarray, la: float = 0.05) -> np.ndarray:
+    """reid/inference_utils.py:5-16: per camera i in 0..max(cams): the rows of the camera lose their mean, are multiplied
+    by P^T with P = inverse(X^T X + n * la * I) built from the rows BEFORE centring (the reference takes its copy
+    first), and are renormalised to unit length.  float32 like the reference; the inverse in float64 then rounded."""
+    e = np.array(embeddings, dtype=np.float32, copy=True)
+    cams = np.asarray(cams).astype(np.int64)
+    D = e.shape[1]
+    for i in range(int(cams.max()) + 1):
+        m = cams == i
+        cur = e[m].copy()
+        n = cur.shape[0]
+        bias = (cur.sum(0, dtype=np.float32) / np.float32(n)).astype(np.float32) if n else np.zeros(D, np.float32)
+        A = (cur.T @ cur + np.float32(n * la) * np.eye(D, dtype=np.float32)).astype(np.float32)
+        P = np.linalg.inv(A.astype(np.float64)).astype(np.float32)
+        y = ((cur - bias[None, :]) @ P.T).astype(np.float32)
+        nrm = np.sqrt((y * y).sum(1, dtype=np.float32, keepdims=True))
+        e[m] = y / nrm
+    return e

@@ -72,6 +72,12 @@ SIGNATURES = {
     "reidb200_kf_initiate": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _d, _d, _vp]),
     "reidb200_kf_predict": (_i, [_vp, _vp, _vp, _i, _d, _d, _d, _vp]),
     "reidb200_kf_update": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _i, _d, _vp]),
+    "reidb200_tta_merge_normalize": (_i, [_vp, _sz, _vp, _sz, _i, _i, _vp, _sz, _vp]),
+    "reidb200_clamp_add": (_i, [_vp, _i, _i, _sz, _vp, _sz, _vp]),
+    "reidb200_dbscan_workspace_bytes": (_sz, [_i]),
+    "reidb200_dbscan_precomputed": (_i, [_vp, _i, _sz, _f, _i, _vp, _vp, _vp, _vp, _sz, _vp]),
+    "reidb200_smooth_groups": (_i, [_vp, _i, _sz, _vp, _vp, _i, _f, _f, _vp]),
+    "reidb200_center_columns": (_i, [_vp, _i, _i, _sz, _vp, _sz, _vp, _vp]),
 }
 
 _lib = None

@@ -540,3 +540,87 @@ def jaccard_from_sql2(sql2, k1=20, k2=6, use_float16=False, lambda_value=0.0, ro
                                                1 if use_float16 else 0, float(lambda_value), row0, nrows, col0, ncols,
                                                out.data_ptr(), out.stride(0), ws.data_ptr(), ws.numel(), L.stream_ptr()))
     return (out, rank) if want_rank else out
+
+
+# ----------------------------------------------------------------------------------------- N4: around the Jaccard matrix
+def tta_merge_normalize(a, b=None, out=None):
+    """F.normalize((a + b) / 2, dim=1) (b None: plain row normalisation), f32[rows, D] on device."""
+    a = _f32(a)
+    dev = L.require_device(a)
+    b = _f32(b, dev) if b is not None else None
+    if b is not None and b.shape != a.shape:
+        raise ValueError("tta_merge_normalize: shapes differ")
+    rows, D = a.shape
+    if out is None:
+        out = torch.empty((rows, D), dtype=torch.float32, device=dev)
+    with torch.cuda.device(dev):
+        L.check(L.load().reidb200_tta_merge_normalize(a.data_ptr(), a.stride(0), L.ptr(b), b.stride(0) if b is not None else 0,
+                                                      rows, D, out.data_ptr(), out.stride(0), L.stream_ptr()))
+    return out
+
+
+def _rows_f32_cuda(t, what):
+    if not (isinstance(t, torch.Tensor) and t.is_cuda and t.dtype == torch.float32 and t.dim() == 2 and t.stride(1) == 1):
+        raise ValueError("%s: a float32 CUDA matrix with unit column stride is required (it is modified / read in place)" % what)
+    return t
+
+
+def clamp_add_(dist, other=None):
+    """In place on the device matrix: dist[dist < 0] = 0, then dist += other (f32[rows, cols], optional)."""
+    _rows_f32_cuda(dist, "clamp_add_")
+    dev = dist.device
+    if other is not None:
+        other = _f32(other, dev)
+        if other.shape != dist.shape:
+            raise ValueError("clamp_add_: shapes differ")
+    rows, cols = dist.shape
+    with torch.cuda.device(dev):
+        L.check(L.load().reidb200_clamp_add(dist.data_ptr(), rows, cols, dist.stride(0), L.ptr(other),
+                                            other.stride(0) if other is not None else 0, L.stream_ptr()))
+    return dist
+
+
+def dbscan_precomputed(dist, eps, min_samples):
+    """sklearn's DBSCAN on a symmetric precomputed f32[N, N] device matrix (rows may be padded: stride(0) >= N):
+    (labels i32[N] with -1 = noise, n_clusters i32[1], core i32[N] 0/1), all on device, no host sync."""
+    _rows_f32_cuda(dist, "dbscan_precomputed")
+    N = dist.shape[0]
+    if dist.shape[1] != N:
+        raise ValueError("dbscan_precomputed: the distance matrix must be square")
+    dev = dist.device
+    labels = torch.empty(N, dtype=torch.int32, device=dev)
+    ncl = torch.zeros(1, dtype=torch.int32, device=dev)
+    core = torch.empty(N, dtype=torch.int32, device=dev)
+    if N:
+        lib = L.load()
+        ws = L.workspace(lib.reidb200_dbscan_workspace_bytes(N), dev)
+        with torch.cuda.device(dev):
+            L.check(lib.reidb200_dbscan_precomputed(dist.data_ptr(), N, dist.stride(0), float(eps), int(min_samples), labels.data_ptr(),
+                                                    ncl.data_ptr(), core.data_ptr(), ws.data_ptr(), ws.numel(), L.stream_ptr()))
+    return labels, ncl, core
+
+
+def smooth_groups_(emb, order, seg_start, keep=0.1, avg_w=0.9):
+    """In place: rows order[seg_start[g] : seg_start[g+1]] of emb become emb * keep + mean(those rows) * avg_w."""
+    _rows_f32_cuda(emb, "smooth_groups_")
+    dev = emb.device
+    order, seg_start = _i32(order, dev), _i32(seg_start, dev)
+    n_groups = seg_start.numel() - 1
+    if n_groups > 0:
+        with torch.cuda.device(dev):
+            L.check(L.load().reidb200_smooth_groups(emb.data_ptr(), emb.shape[1], emb.stride(0), order.data_ptr(), seg_start.data_ptr(),
+                                                   n_groups, float(keep), float(avg_w), L.stream_ptr()))
+    return emb
+
+
+def center_columns(x, want_mean=False):
+    """x - x.mean(dim=0) (f32[rows, D] on device); optionally also the mean."""
+    x = _f32(x)
+    dev = L.require_device(x)
+    rows, D = x.shape
+    out = torch.empty((rows, D), dtype=torch.float32, device=dev)
+    mean = torch.empty(D, dtype=torch.float32, device=dev) if want_mean else None
+    with torch.cuda.device(dev):
+        L.check(L.load().reidb200_center_columns(x.data_ptr(), rows, D, x.stride(0), out.data_ptr(), out.stride(0), L.ptr(mean),
+                                                 L.stream_ptr()))
+    return (out, mean) if want_mean else out

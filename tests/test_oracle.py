@@ -138,3 +138,17 @@ def test_kalman_n3(golden):
         np.testing.assert_allclose(np.stack([s[0] for s in st]), g["x"][f], rtol=1e-10, atol=1e-8)
         np.testing.assert_allclose(np.stack([s[1] for s in st]), g["P"][f], rtol=1e-8, atol=1e-8)
         np.testing.assert_allclose(np.stack([s[2] for s in st]), g["SI"][f], rtol=1e-8, atol=1e-12)
+
+
+def test_posttricks_n4(golden):
+    """N4: the oracle's flip-TTA merge, camera-bias removal, clamp + attribute add, DBSCAN and tracklet smoothing replay
+    what the reference's own functions (and its sklearn dependency) produced."""
+    g = golden("posttricks")
+    np.testing.assert_allclose(O.tta_merge_normalize(g["e1"], g["e2"]), g["merged"], rtol=0, atol=2e-7)
+    np.testing.assert_allclose(O.diminish_camera_bias(g["merged"], g["cams"]), g["unbiased"], rtol=0, atol=2e-5)
+    for tag, other in (("plain", None), ("attr", g["attr_dist"]), ("tight", None)):
+        d = O.clamp_add(g["J"], other)
+        lab, core = O.dbscan_precomputed(d, float(g["eps_" + tag]), int(g["ms_" + tag]))
+        assert np.array_equal(lab, g["lab_" + tag]) and np.array_equal(core, g["core_" + tag])
+    valid = g["lab_plain"] != -1
+    np.testing.assert_allclose(O.smooth_tracklets(g["unbiased"], g["merged_seqs"], valid), g["smooth"], rtol=0, atol=2e-7)
