@@ -8,59 +8,107 @@
 // included, compared in float32), core = |neighbourhood| >= min_samples, clusters = connected components of the core
 // points numbered by their lowest core index (sklearn seeds its depth-first search at ascending i), a border point
 // takes the lowest-numbered cluster that has a core point in its neighbourhood (the first search that reaches it),
-// everything else is noise (-1).  The matrix is read row by row (HBM bound): once for the degrees, then the lower
-// triangle of the core rows for the unions and the rows of the non-core points for the border labels.  d is taken as
-// symmetric (the Jaccard matrix is, bit for bit): row i stands for column i.
+// everything else is noise (-1).  The matrix is read once, row by row (HBM bound): the degree pass keeps each row's
+// neighbour list (up to 64 entries; longer rows are scanned again), the union and border passes walk the lists.  d is
+// taken as symmetric (the Jaccard matrix is, bit for bit): row i stands for column i.
 #include "common.cuh"
 
 namespace reidb200 {
 
-// Calls hit(j) for every j in [0, n) with p[j] <= eps (COUNT_ONLY: hit(number of such j), possibly in several calls).  A warp walks the row with four float4 loads in flight per lane;
+// Calls hit(j) for every j in [0, n) with p[j] <= eps.  A warp walks the row with eight float4 loads in flight per lane;
 // rows need not be 16-byte aligned (N is odd at Market size): the first few elements up to the next 16-byte boundary
 // and the last few are read as scalars.  Hits are rare, so a lane gathers them in a bit mask and serves them in one place.
-template <bool COUNT_ONLY = false, typename F>
+template <typename F>
 __device__ __forceinline__ void row_hits(const float* __restrict__ p, int n, float eps, int lane, F hit) {
   int head = (int)(((16u - (uint32_t)((uintptr_t)p & 15u)) & 15u) >> 2);
   head = head < n ? head : n;
-  if (lane < head && p[lane] <= eps) hit(COUNT_ONLY ? 1 : lane);
+  if (lane < head && p[lane] <= eps) hit(lane);
   const float* q = p + head;  // 16-byte aligned
   const int n4 = (n - head) & ~3;
-  for (int c0 = lane * 4; c0 < n4; c0 += 512) {
+  for (int c0 = lane * 4; c0 < n4; c0 += 1024) {
+    float4 v[8];
+#pragma unroll
+    for (int u = 0; u < 8; ++u) {
+      const int c = c0 + u * 128;
+      v[u] = c < n4 ? __ldcs(reinterpret_cast<const float4*>(q + c)) : make_float4(INFINITY, INFINITY, INFINITY, INFINITY);
+    }
+    uint32_t m = 0;
+#pragma unroll
+    for (int u = 0; u < 8; ++u)
+      m |= ((v[u].x <= eps ? 1u : 0u) | (v[u].y <= eps ? 2u : 0u) | (v[u].z <= eps ? 4u : 0u) | (v[u].w <= eps ? 8u : 0u)) << (4 * u);
+    while (m) {
+      const int b = __ffs(m) - 1;
+      m &= m - 1;
+      hit(head + c0 + (b >> 2) * 128 + (b & 3));
+    }
+  }
+  for (int c = head + n4 + lane; c < n; c += 32)
+    if (p[c] <= eps) hit(c);
+}
+
+// Hits of a row are kept (up to DB_CAP per row, any order) so that the later passes need not read the matrix again;
+// a row with more hits than that is simply scanned again where it is needed.
+constexpr int DB_CAP = 64;
+
+// One CTA per row (its 256 threads stream the row: consecutive warps read consecutive 512-byte pieces).
+__global__ void __launch_bounds__(256)
+dbscan_degree_kernel(const float* __restrict__ d, int N, size_t ld, float eps, int min_samples, int32_t* __restrict__ core,
+                     int32_t* __restrict__ parent, int32_t* __restrict__ degree, int32_t* __restrict__ hits) {
+  __shared__ int s_cnt;
+  const int row = blockIdx.x, tid = threadIdx.x;
+  if (tid == 0) s_cnt = 0;
+  __syncthreads();
+  int32_t* h = hits + (size_t)row * DB_CAP;
+  const float* p = d + (size_t)row * ld;
+  auto hit = [&](int j) {
+    const int pos = atomicAdd(&s_cnt, 1);
+    if (pos < DB_CAP) h[pos] = j;
+  };
+  int head = (int)(((16u - (uint32_t)((uintptr_t)p & 15u)) & 15u) >> 2);
+  head = head < N ? head : N;
+  if (tid < head && p[tid] <= eps) hit(tid);
+  const float* q = p + head;  // 16-byte aligned
+  const int n4 = (N - head) & ~3;
+  for (int c0 = tid * 4; c0 < n4; c0 += 4096) {
     float4 v[4];
 #pragma unroll
     for (int u = 0; u < 4; ++u) {
-      const int c = c0 + u * 128;
+      const int c = c0 + u * 1024;
       v[u] = c < n4 ? __ldcs(reinterpret_cast<const float4*>(q + c)) : make_float4(INFINITY, INFINITY, INFINITY, INFINITY);
     }
     uint32_t m = 0;
 #pragma unroll
     for (int u = 0; u < 4; ++u)
       m |= ((v[u].x <= eps ? 1u : 0u) | (v[u].y <= eps ? 2u : 0u) | (v[u].z <= eps ? 4u : 0u) | (v[u].w <= eps ? 8u : 0u)) << (4 * u);
-    if (COUNT_ONLY) {
-      hit(__popc(m));
-    } else {
-      while (m) {
-        const int b = __ffs(m) - 1;
-        m &= m - 1;
-        hit(head + c0 + (b >> 2) * 128 + (b & 3));
-      }
+    while (m) {
+      const int b = __ffs(m) - 1;
+      m &= m - 1;
+      hit(head + c0 + (b >> 2) * 1024 + (b & 3));
     }
   }
-  for (int c = head + n4 + lane; c < n; c += 32)
-    if (p[c] <= eps) hit(COUNT_ONLY ? 1 : c);
-}
-
-__global__ void __launch_bounds__(256)
-dbscan_degree_kernel(const float* __restrict__ d, int N, size_t ld, float eps, int min_samples, int32_t* __restrict__ core,
-                     int32_t* __restrict__ parent) {
-  const int row = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
-  if (row >= N) return;
-  int cnt = 0;
-  row_hits<true>(d + (size_t)row * ld, N, eps, lane, [&](int k) { cnt += k; });
-  cnt = __reduce_add_sync(0xffffffffu, cnt);
-  if (lane == 0) {
+  for (int c = head + n4 + tid; c < N; c += 256)
+    if (p[c] <= eps) hit(c);
+  __syncthreads();
+  if (tid == 0) {
+    const int cnt = s_cnt;
+    degree[row] = cnt;
     core[row] = cnt >= min_samples ? 1 : 0;
     parent[row] = row;
+  }
+}
+
+// Calls hit(j) for the row's neighbours j < limit: from the stored list, or from the matrix when the list overflowed.
+template <typename F>
+__device__ __forceinline__ void row_neighbours(const float* __restrict__ d, size_t ld, int row, int limit, float eps, int lane,
+                                               const int32_t* __restrict__ degree, const int32_t* __restrict__ hits, F hit) {
+  const int cnt = degree[row];
+  if (cnt <= DB_CAP) {
+    for (int e = lane; e < cnt; e += 32) {
+      const int j = hits[(size_t)row * DB_CAP + e];
+      if (j < limit) hit(j);
+    }
+  } else {
+    row_hits(d + (size_t)row * ld, limit, eps, lane, hit);
   }
 }
 
@@ -89,10 +137,11 @@ __device__ __noinline__ void uf_unite(int32_t* parent, int a, int b) {
 }
 
 __global__ void __launch_bounds__(256)
-dbscan_link_kernel(const float* __restrict__ d, int N, size_t ld, float eps, const int32_t* __restrict__ core, int32_t* parent) {
+dbscan_link_kernel(const float* __restrict__ d, int N, size_t ld, float eps, const int32_t* __restrict__ core, int32_t* parent,
+                   const int32_t* __restrict__ degree, const int32_t* __restrict__ hits) {
   const int row = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
   if (row >= N || !core[row]) return;
-  row_hits(d + (size_t)row * ld, row, eps, lane, [&](int j) {  // lower triangle: every core pair once
+  row_neighbours(d, ld, row, row, eps, lane, degree, hits, [&](int j) {  // lower triangle: every core pair once
     if (core[j]) uf_unite(parent, row, j);
   });
 }
@@ -114,12 +163,12 @@ dbscan_number_kernel(int N, const int32_t* __restrict__ core, int32_t* parent, i
 
 __global__ void __launch_bounds__(256)
 dbscan_border_kernel(const float* __restrict__ d, int N, size_t ld, float eps, const int32_t* __restrict__ core,
-                     int32_t* labels) {
+                     int32_t* labels, const int32_t* __restrict__ degree, const int32_t* __restrict__ hits) {
   const int row = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
   if (row >= N || core[row]) return;
   int best = INT_MAX;
   // labels of core points are final (written by the previous kernel); only non-core rows are written here
-  row_hits(d + (size_t)row * ld, N, eps, lane, [&](int j) {
+  row_neighbours(d, ld, row, N, eps, lane, degree, hits, [&](int j) {
     if (core[j]) best = min(best, *(volatile int32_t*)(labels + j));
   });
   best = __reduce_min_sync(0xffffffffu, best);
@@ -233,7 +282,7 @@ center_columns_kernel(const float* __restrict__ x, int rows, int D, size_t ldx, 
 
 using namespace reidb200;
 
-extern "C" size_t reidb200_dbscan_workspace_bytes(int N) { return (size_t)(N > 0 ? N : 0) * 3 * sizeof(int32_t) + 256; }
+extern "C" size_t reidb200_dbscan_workspace_bytes(int N) { return (size_t)(N > 0 ? N : 0) * (4 + DB_CAP) * sizeof(int32_t) + 256; }
 
 extern "C" int reidb200_dbscan_precomputed(const float* dist, int N, size_t ld, float eps, int min_samples, int32_t* labels,
                                            int32_t* n_clusters, int32_t* core_out, void* ws, size_t ws_bytes, void* stream) {
@@ -246,15 +295,17 @@ extern "C" int reidb200_dbscan_precomputed(const float* dist, int N, size_t ld, 
   int32_t* core = core_out ? core_out : (int32_t*)ws;
   int32_t* parent = (int32_t*)ws + N;
   int32_t* flags = (int32_t*)ws + 2 * (size_t)N;
+  int32_t* degree = (int32_t*)ws + 3 * (size_t)N;
+  int32_t* hits = (int32_t*)ws + 4 * (size_t)N;
   const int grid = (N + 7) / 8;
   {
     ProfScope _ps("dbscan_degree_kernel", st);
-    dbscan_degree_kernel<<<grid, 256, 0, st>>>(dist, N, ld, eps, min_samples, core, parent);
+    dbscan_degree_kernel<<<N, 256, 0, st>>>(dist, N, ld, eps, min_samples, core, parent, degree, hits);
   }
   RB_LAUNCH_CHECK("dbscan_degree_kernel");
   {
     ProfScope _ps("dbscan_link_kernel", st);
-    dbscan_link_kernel<<<grid, 256, 0, st>>>(dist, N, ld, eps, core, parent);
+    dbscan_link_kernel<<<grid, 256, 0, st>>>(dist, N, ld, eps, core, parent, degree, hits);
   }
   RB_LAUNCH_CHECK("dbscan_link_kernel");
   {
@@ -269,7 +320,7 @@ extern "C" int reidb200_dbscan_precomputed(const float* dist, int N, size_t ld, 
   RB_LAUNCH_CHECK("dbscan_number_kernel");
   {
     ProfScope _ps("dbscan_border_kernel", st);
-    dbscan_border_kernel<<<grid, 256, 0, st>>>(dist, N, ld, eps, core, labels);
+    dbscan_border_kernel<<<grid, 256, 0, st>>>(dist, N, ld, eps, core, labels, degree, hits);
   }
   RB_LAUNCH_CHECK("dbscan_border_kernel");
   return REIDB200_OK;

@@ -59,3 +59,38 @@ def smooth_tracklets(embeddings, seqs, indices_valid):
     if e.data_ptr() != embeddings.data_ptr():
         embeddings.copy_(e)
     return embeddings
+
+
+def cluster_smooth_evaluate(gallery_embeddings, query_embeddings, gallery_labels, query_labels, gallery_cams, query_cams,
+                            gallery_seqs, query_seqs, eps=0.5, min_samples=7, attribute_dist=None, camera_bias=True,
+                            k1=20, k2=6):
+    """The experimental inference path of reid/image_reid_inference.py:246-315 as one device-resident pipeline:
+    flip-TTA merge of the (plain, flipped) embedding pairs -> cat(gallery, query) -> diminish_camera_bias ->
+    compute_jaccard_distance -> clamp + attribute distance -> DBSCAN -> smooth_tracklets -> evaluate_all.
+    `*_embeddings` = a pair (plain, flipped) or a single already merged tensor.  Returns (CMC FloatTensor[G], mAP float,
+    pseudo_labels i64 ndarray); the N x N matrix never leaves the device."""
+    from . import evaluate
+
+    dev = L.require_device()
+
+    def merge(e):
+        if isinstance(e, (tuple, list)):
+            return ops.tta_merge_normalize(torch.as_tensor(e[0]).to(dev), torch.as_tensor(e[1]).to(dev))
+        return torch.as_tensor(e).to(device=dev, dtype=torch.float32)
+
+    g, q = merge(gallery_embeddings), merge(query_embeddings)
+    G = g.shape[0]
+    merged = torch.cat((g, q), dim=0)
+    cat = lambda a, b: torch.cat((torch.as_tensor(a).reshape(-1), torch.as_tensor(b).reshape(-1))).to(dev)
+    merged_cams, merged_seqs = cat(gallery_cams, query_cams), cat(gallery_seqs, query_seqs)
+    if camera_bias:
+        merged = diminish_camera_bias(merged, merged_cams)
+    dists = ops.jaccard(merged, k1, k2)
+    ops.clamp_add_(dists, attribute_dist)
+    pseudo, ncl, _ = ops.dbscan_precomputed(dists, eps, min_samples)
+    del dists
+    num_labels = int(ncl.item())
+    merged_seqs = merged_seqs.to(torch.int64) * num_labels + pseudo.to(torch.int64)  # image_reid_inference.py:305
+    merged = smooth_tracklets(merged, merged_seqs, pseudo != -1)
+    CMC, ap = evaluate.evaluate_all(merged[G:], query_labels, query_cams, merged[:G], gallery_labels, gallery_cams)
+    return CMC, ap, pseudo.cpu().numpy().astype(np.int64)

@@ -110,9 +110,22 @@ def test_dbscan_edges(rb):
     assert int(ncl.item()) == 0 and bool((labels == -1).all()) and int(core.sum()) == 0
     labels, ncl, core = ops.dbscan_precomputed(torch.zeros((50, 50), device="cuda"), 0.5, 50)
     assert int(ncl.item()) == 1 and bool((labels == 0).all()) and int(core.sum()) == 50
+    labels, ncl, core = ops.dbscan_precomputed(torch.zeros((333, 333), device="cuda"), 0.5, 5)  # overflowing lists
+    assert int(ncl.item()) == 1 and bool((labels == 0).all()) and int(core.sum()) == 333
     # min_samples = 1: every point is core, singletons are clusters numbered by index
     labels, ncl, _ = ops.dbscan_precomputed(far, 0.5, 1)
     assert labels.cpu().tolist() == list(range(50)) and int(ncl.item()) == 50
+    # rows with more neighbours than the kernel's per-row list holds (64): the union and border passes scan them again
+    n = 260
+    d = np.ones((n, n), dtype=np.float32)
+    d[:130, :130] = 0.1          # 130 mutually close points: core for min_samples = 120
+    d[200, :100] = d[:100, 200] = 0.2   # 101 neighbours (self included): a border point with an overflowing list
+    d[196:206, 196:206] = np.minimum(d[196:206, 196:206], 0.3)  # ten close points (incl. 200): too few to be core
+    np.fill_diagonal(d, 0.0)
+    labels, ncl, core = ops.dbscan_precomputed(torch.from_numpy(d).cuda(), 0.5, 120)
+    olab, ocore = O.dbscan_precomputed(d, 0.5, 120)
+    assert np.array_equal(labels.cpu().numpy().astype(np.int64), olab) and np.array_equal(core.cpu().numpy().astype(bool), ocore)
+    assert int(ncl.item()) == 1 and olab[200] == 0 and not ocore[200] and olab[150] == -1 and olab[198] == -1 and ocore[:130].all()
     labels, ncl, _ = ops.dbscan_precomputed(torch.zeros((0, 0), device="cuda"), 0.5, 3)
     assert labels.numel() == 0
     with pytest.raises(ValueError):
@@ -156,3 +169,29 @@ def test_center_columns_and_larger_bias_vs_oracle(rb):
     cams = rng.integers(0, 6, 1500)
     got = IU.diminish_camera_bias(torch.from_numpy(f.copy()).cuda(), torch.from_numpy(cams).cuda()).cpu().numpy()
     np.testing.assert_allclose(got, O.diminish_camera_bias(f, cams), rtol=0, atol=2e-5)
+
+
+def test_cluster_smooth_evaluate_pipeline_vs_oracle(rb):
+    """image_reid_inference.py:246-315 end to end on the device against the same chain of oracle functions."""
+    from reidb200 import inference_utils as IU, synth
+
+    d = synth.market_like(Q=90, G=510, D=64, n_ids=30, seed=77)
+    rng = np.random.default_rng(78)
+    flip = lambda e: (e + 0.03 * rng.standard_normal(e.shape)).astype(np.float32)
+    g2, q2 = flip(d["gf"]), flip(d["qf"])
+    gseq, qseq = rng.integers(0, 4, 510), rng.integers(0, 4, 90)
+    attr = rng.integers(1, 3, (30, 30)).astype(np.float32)
+    ids = np.concatenate([d["gl"], d["ql"]]) % 30
+    a = attr[ids] / np.linalg.norm(attr[ids], axis=1, keepdims=True)
+    attr_dist = O.euclidean_dist(a.astype(np.float32), a.astype(np.float32))
+    CMC, ap, pseudo = IU.cluster_smooth_evaluate((d["gf"], g2), (d["qf"], q2), d["gl"], d["ql"], d["gc"], d["qc"], gseq, qseq,
+                                                 eps=0.6, min_samples=5, attribute_dist=attr_dist)
+    merged = np.concatenate([O.tta_merge_normalize(d["gf"], g2), O.tta_merge_normalize(d["qf"], q2)], 0)
+    merged = O.diminish_camera_bias(merged, np.concatenate([d["gc"], d["qc"]]))
+    dists = O.clamp_add(O.compute_jaccard_distance(merged, 20, 6), attr_dist)
+    olab, _ = O.dbscan_precomputed(dists, 0.6, 5)
+    assert np.array_equal(pseudo, olab)
+    seqs = np.concatenate([gseq, qseq]) * (olab.max() + 1) + olab
+    sm = O.smooth_tracklets(merged, seqs, olab != -1)
+    oCMC, oap = O.evaluate_all(sm[510:], d["ql"], d["qc"], sm[:510], d["gl"], d["gc"])
+    assert np.abs(CMC.numpy() - np.asarray(oCMC)).max() <= 1.0 / 90 + 1e-6 and abs(ap - oap) <= 2e-3
