@@ -210,6 +210,27 @@ clamp_add_kernel(float* __restrict__ dist, int rows, int cols, size_t ld, const 
   }
 }
 
+// the same over fully contiguous matrices, as one flat array (rows of odd length are not 16-byte aligned one by one)
+__global__ void __launch_bounds__(256)
+clamp_add_flat_kernel(float* __restrict__ dist, const float* __restrict__ other, size_t n4, size_t n) {
+  const size_t stride = (size_t)gridDim.x * 256;
+  for (size_t i = (size_t)blockIdx.x * 256 + threadIdx.x; i < n4; i += stride) {
+    float4 v = reinterpret_cast<float4*>(dist)[i];
+    v.x = v.x < 0.f ? 0.f : v.x; v.y = v.y < 0.f ? 0.f : v.y; v.z = v.z < 0.f ? 0.f : v.z; v.w = v.w < 0.f ? 0.f : v.w;
+    if (other) {
+      const float4 o = __ldcs(reinterpret_cast<const float4*>(other) + i);
+      v.x = v.x + o.x; v.y = v.y + o.y; v.z = v.z + o.z; v.w = v.w + o.w;
+    }
+    reinterpret_cast<float4*>(dist)[i] = v;
+  }
+  if (blockIdx.x == 0)
+    for (size_t e = n4 * 4 + threadIdx.x; e < n; e += 256) {
+      float v = dist[e];
+      v = v < 0.f ? 0.f : v;
+      dist[e] = other ? v + other[e] : v;
+    }
+}
+
 // out[r] = normalize((a[r] + b[r]) / 2): one warp per row, x / max(||x||_2, 1e-12) as F.normalize
 __global__ void __launch_bounds__(256)
 tta_merge_normalize_kernel(const float* __restrict__ a, size_t lda, const float* __restrict__ b, size_t ldb, int rows, int D,
@@ -331,6 +352,14 @@ extern "C" int reidb200_clamp_add(float* dist, int rows, int cols, size_t ld, co
   RB_REQUIRE(dist && rows > 0 && cols > 0 && ld >= (size_t)cols && (!other || ldo >= (size_t)cols), "clamp_add: bad argument");
   RB_REQUIRE(rows <= 65535 * 1024, "clamp_add: too many rows");
   cudaStream_t st = (cudaStream_t)stream;
+  if (ld == (size_t)cols && (!other || ldo == (size_t)cols) && (uintptr_t)dist % 16 == 0 && (!other || (uintptr_t)other % 16 == 0)) {
+    const size_t n = (size_t)rows * cols, n4 = n / 4;
+    const size_t want = (n4 + 255) / 256;
+    const int grid = (int)(want < (size_t)num_sms() * 16 ? (want ? want : 1) : (size_t)num_sms() * 16);
+    { ProfScope _ps("clamp_add_kernel", st); clamp_add_flat_kernel<<<grid, 256, 0, st>>>(dist, other, n4, n); }
+    RB_LAUNCH_CHECK("clamp_add_kernel");
+    return REIDB200_OK;
+  }
   const int vec = (ld % 4 == 0) && ((uintptr_t)dist % 16 == 0) && (!other || ((ldo % 4 == 0) && ((uintptr_t)other % 16 == 0)));
   // grid.y is limited to 65535 rows per launch
   for (int r0 = 0; r0 < rows; r0 += 65535) {

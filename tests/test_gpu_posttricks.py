@@ -29,6 +29,10 @@ def test_tta_merge_and_clamp_add_golden(rb, golden):
     view.copy_(torch.from_numpy(a))
     ops.clamp_add_(view, torch.from_numpy(b))
     assert np.array_equal(view.cpu().numpy(), O.clamp_add(a, b)) and float(buf[:, 37:].abs().sum()) == 0.0
+    # contiguous with an odd element count: the flat float4 path and its scalar tail
+    flat = ops.clamp_add_(torch.from_numpy(a).cuda(), torch.from_numpy(b).cuda())
+    assert np.array_equal(flat.cpu().numpy(), O.clamp_add(a, b))
+    assert np.array_equal(ops.clamp_add_(torch.from_numpy(a).cuda()).cpu().numpy(), O.clamp_add(a))
 
 
 @pytest.mark.parametrize("tag", ["plain", "attr", "tight"])
