@@ -182,6 +182,26 @@ def bench_assoc(steps, warmup):
             e2e_step()
         torch.cuda.synchronize()
         e2e_us = (time.perf_counter() - t0) / n * 1e6
+        # the whole Tracker._match from host arrays (costs + both assignment stages): Hungarian on the host (scipy, the
+        # reference's solver) against the device assignment (N1)
+        conf = np.arange(T) % 7 != 0
+        margs = (metric, det_feat, fr["det_tlwh"], np.arange(T), conf, fr["trk_mean"], fr["trk_SI"], fr["trk_tsu"], 0.995, 0.7, 0.2)
+        match_us = {}
+        for tag, dl in (("host_lap", False), ("device_lap", True)):
+            for _ in range(3):
+                res = tracker.match_arrays(*margs, device_lap=dl)
+            t0 = time.perf_counter()
+            for _ in range(n):
+                res = tracker.match_arrays(*margs, device_lap=dl)
+            match_us[tag] = (time.perf_counter() - t0) / n * 1e6
+            match_us[tag + "_matches"] = len(res[0])
+        L.profile_enable(True)
+        for _ in range(20):
+            tracker.match_arrays(*margs, device_lap=True)
+        torch.cuda.synchronize()
+        lp = L.profile_read()
+        L.profile_enable(False)
+        match_us["lap_kernels_us"] = sum(lp[k][1] for k in ("lap_components_kernel", "lap_solve_kernel") if k in lp) / 20 * 1e3
         crop_us = prof["crop_cv_linear_kernel"][1] / prof["crop_cv_linear_kernel"][0] * 1e3
         assoc_us = prof["assoc_frame_kernel"][1] / prof["assoc_frame_kernel"][0] * 1e3
         crop_bytes = len(xyxy) * 3 * 256 * 128 * 4 + int((geom[:, 0].astype(np.int64) * geom[:, 1] * 3).sum())
@@ -189,7 +209,7 @@ def bench_assoc(steps, warmup):
         out[name] = {"dets": int(M), "tracks": int(T), "us_per_frame": ms / n * 1e3, "us_per_frame_cuda_graph": ms_graph / n * 1e3,
                      "e2e_us_per_frame": e2e_us, "crop_kernel_us": crop_us, "assoc_kernel_us": assoc_us,
                      "crop_gbs": crop_bytes / crop_us / 1e3, "assoc_gbs": gal_bytes / assoc_us / 1e3,
-                     "assoc_tflops": 2.0 * sum(counts) * M * 512 / assoc_us / 1e6}
+                     "assoc_tflops": 2.0 * sum(counts) * M * 512 / assoc_us / 1e6, "match_e2e_us": match_us}
     return out
 
 

@@ -310,6 +310,20 @@ int reidb200_smooth_groups(float* emb, int D, size_t lde, const int32_t* order, 
 int reidb200_center_columns(const float* x, int rows, int D, size_t ldx, float* out, size_t ldo, float* mean_out,
                             void* stream);
 
+/* ------------------------------------------------------------------------------------------
+ * N1: min_cost_matching's assignment on the device-resident cost matrix
+ * (boxmot/trackers/strongsort/sort/linear_assignment.py:58-77: clamp to max_distance + 1e-5,
+ * scipy.optimize.linear_sum_assignment, pairs above max_distance dropped).
+ * cost f64[T, M] (row stride ld); the solve takes the rows row_cand[0..nrc) whose match_col_of_row entry is still -1 and
+ * the columns whose det_matched entry is still 0, and records its matches in both arrays (match_col_of_row[row] = col,
+ * det_matched[col] = 1), so that the stages of Tracker._match chain on the device.  The admissible entries
+ * (cost <= max_distance) split into connected components, each solved by one warp with scipy's shortest-augmenting-path
+ * algorithm in float64: the same matches as scipy whenever the optimum is unique.  status i32[1] (device) is set to 1 if a
+ * solve could not finish (non-finite costs).  At most 2048 rows / columns per solve. */
+size_t reidb200_lap_workspace_bytes(int T, int M);
+int reidb200_lap_gated(const double* cost, int T, int M, size_t ld, const int32_t* row_cand, int nrc, double max_distance,
+                       int32_t* match_col_of_row, int32_t* det_matched, int32_t* status, void* ws, size_t ws_bytes, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -78,6 +78,8 @@ SIGNATURES = {
     "reidb200_dbscan_precomputed": (_i, [_vp, _i, _sz, _f, _i, _vp, _vp, _vp, _vp, _sz, _vp]),
     "reidb200_smooth_groups": (_i, [_vp, _i, _sz, _vp, _vp, _i, _f, _f, _vp]),
     "reidb200_center_columns": (_i, [_vp, _i, _i, _sz, _vp, _sz, _vp, _vp]),
+    "reidb200_lap_workspace_bytes": (_sz, [_i, _i]),
+    "reidb200_lap_gated": (_i, [_vp, _i, _i, _sz, _vp, _i, _d, _vp, _vp, _vp, _vp, _sz, _vp]),
 }
 
 _lib = None

@@ -12,7 +12,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OBJ = os.path.join(HERE, "csrc", "_obj")
 LIB = os.path.join(HERE, "libreidb200.so")
-SOURCES = ["core.cu", "crop.cu", "gemm.cu", "topk.cu", "evalmap.cu", "rerank.cu", "assoc.cu", "boxpairs.cu", "kalman.cu", "cluster.cu"]
+SOURCES = ["core.cu", "crop.cu", "gemm.cu", "topk.cu", "evalmap.cu", "rerank.cu", "assoc.cu", "boxpairs.cu", "kalman.cu", "cluster.cu", "lap.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17", "-fmad=false",
               "-Xcompiler", "-fPIC"]
 

@@ -624,3 +624,27 @@ def center_columns(x, want_mean=False):
         L.check(L.load().reidb200_center_columns(x.data_ptr(), rows, D, x.stride(0), out.data_ptr(), out.stride(0), L.ptr(mean),
                                                  L.stream_ptr()))
     return (out, mean) if want_mean else out
+
+
+# ----------------------------------------------------------------------------------------- N1: assignment on device
+def lap_gated(cost, row_cand, max_distance, match_col_of_row, det_matched, status=None):
+    """One min_cost_matching solve on the device cost matrix f64[T, M]: rows `row_cand` (i32, device) that are still
+    unmatched x columns still unmatched; matches are recorded in match_col_of_row i32[T] / det_matched i32[M] in place.
+    Returns the status tensor (i32[1], non-zero if a solve met non-finite costs); no host sync."""
+    if not (isinstance(cost, torch.Tensor) and cost.is_cuda and cost.dtype == torch.float64 and cost.dim() == 2 and cost.stride(1) == 1):
+        raise ValueError("lap_gated: a float64 CUDA matrix with unit column stride is required")
+    dev = cost.device
+    T, M = cost.shape
+    row_cand = _i32(row_cand, dev)
+    if status is None:
+        status = torch.zeros(1, dtype=torch.int32, device=dev)
+    if match_col_of_row.numel() != T or det_matched.numel() != M or match_col_of_row.dtype != torch.int32 or det_matched.dtype != torch.int32:
+        raise ValueError("lap_gated: match_col_of_row i32[T] and det_matched i32[M] are required")
+    if T and M and row_cand.numel():
+        lib = L.load()
+        ws = L.workspace(lib.reidb200_lap_workspace_bytes(T, M), dev)
+        with torch.cuda.device(dev):
+            L.check(lib.reidb200_lap_gated(cost.data_ptr(), T, M, cost.stride(0), row_cand.data_ptr(), row_cand.numel(),
+                                           float(max_distance), match_col_of_row.data_ptr(), det_matched.data_ptr(), status.data_ptr(),
+                                           ws.data_ptr(), ws.numel(), L.stream_ptr()))
+    return status

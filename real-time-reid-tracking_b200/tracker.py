@@ -69,8 +69,11 @@ def costs_to_host(app, iou):
 
 
 def match_arrays(metric, det_feat, det_tlwh, trk_ids, trk_confirmed, trk_mean, trk_SI, trk_tsu, mc_lambda, max_iou_dist,
-                 max_dist=None, iou_mode="iou"):
-    """(matches [(track_row, det_idx)], unmatched_tracks, unmatched_detections) exactly as Tracker._match returns them."""
+                 max_dist=None, iou_mode="iou", device_lap=False):
+    """(matches [(track_row, det_idx)], unmatched_tracks, unmatched_detections) exactly as Tracker._match returns them.
+    device_lap=True solves both assignment stages on the device too: the same matches whenever scipy's
+    optimum is unique, unmatched detections listed in ascending order (scipy's pairing of gated leftovers, which orders
+    the reference's list, is not reproduced)."""
     T, M = len(trk_ids), len(det_tlwh)
     max_dist = metric.matching_threshold if max_dist is None else max_dist
     confirmed = [i for i in range(T) if trk_confirmed[i]]
@@ -79,6 +82,8 @@ def match_arrays(metric, det_feat, det_tlwh, trk_ids, trk_confirmed, trk_mean, t
     if T and M:
         app, _, iou = frame_costs(metric, det_feat, det_tlwh, trk_ids, trk_confirmed, trk_mean, trk_SI, trk_tsu, mc_lambda,
                                   max_dist, max_iou_dist, iou_mode)
+        if device_lap:
+            return _match_on_device(app, iou, confirmed, unconfirmed, trk_tsu, max_dist, max_iou_dist)
         app, iou = costs_to_host(app, iou)  # one D2H
     # stage A: confirmed tracks x all detections, appearance cost (matching_cascade, single level)
     if len(confirmed) == 0 or M == 0:
@@ -94,6 +99,45 @@ def match_arrays(metric, det_feat, det_tlwh, trk_ids, trk_confirmed, trk_mean, t
     else:
         m_b, um_b, um_d = _solve(np.ascontiguousarray(iou[np.ix_(cand, um_d)]), max_iou_dist, cand, um_d)
     return m_a + m_b, list(set(um_a + um_b)), um_d
+
+
+_lap_host = {}
+
+
+def _match_on_device(app, iou, confirmed, unconfirmed, trk_tsu, max_dist, max_iou_dist):
+    """Both stages of Tracker._match (tracker.py:175-233) chained on the device: stage A over the confirmed rows of the
+    appearance matrix, stage B over the IoU matrix for the unconfirmed rows and the confirmed rows with
+    time_since_update == 1 that stage A left unmatched (the kernel filters rows / columns matched so far).  One small
+    H2D (the two row lists) and one D2H (2T + M + 1 ints) per frame."""
+    dev = app.device
+    T, M = app.shape
+    cand_b = unconfirmed + [k for k in confirmed if trk_tsu[k] == 1]
+    rows_a, rows_b = L.staging(dev).upload([np.asarray(confirmed, np.int32), np.asarray(cand_b, np.int32)])
+    state = torch.empty(2 * T + M + 1, dtype=torch.int32, device=dev)
+    state[:T] = -1
+    state[T:T + M + 1] = 0
+    match, det_m, status, match_a = state[:T], state[T:T + M], state[T + M:T + M + 1], state[T + M + 1:]
+    if confirmed:
+        ops.lap_gated(app, rows_a, max_dist, match, det_m, status)
+    match_a.copy_(match)
+    if cand_b:
+        ops.lap_gated(iou, rows_b, max_iou_dist, match, det_m, status)
+    key = (dev.index, state.numel())
+    host = _lap_host.get(key)
+    if host is None:
+        _lap_host.clear()
+        host = _lap_host[key] = torch.empty(state.numel(), dtype=torch.int32).pin_memory()
+    host.copy_(state, non_blocking=True)
+    torch.cuda.current_stream(dev).synchronize()
+    h = host.numpy()
+    if h[T + M]:
+        raise L.Reidb200Error("device assignment met non-finite costs")
+    mt, mt_a = h[:T], h[T + M + 1:]
+    m_a = [(k, int(mt_a[k])) for k in confirmed if mt_a[k] >= 0]
+    m_b = [(k, int(mt[k])) for k in cand_b if mt[k] >= 0 and mt_a[k] < 0]
+    um_t = [k for k in range(T) if mt[k] < 0]
+    um_d = [j for j in range(M) if h[T + j] == 0]
+    return m_a + m_b, list(set(um_t)), um_d
 
 
 def match(metric, tracks, detections, mc_lambda, max_iou_dist):
