@@ -3,16 +3,17 @@ reference runs it (linear_assignment.py:58-77: clamp, solve, drop pairs above ma
 import numpy as np
 import pytest
 import torch
-from scipy.optimize import linear_sum_assignment
+
+from oracle import reid_oracle as O
 
 pytestmark = pytest.mark.gpu
 
 
 def _reference_matches(cost, max_distance):
-    c = cost.copy()
-    c[c > max_distance] = max_distance + 1e-5
-    rows, cols = linear_sum_assignment(c)
-    return sorted((int(r), int(k)) for r, k in zip(rows, cols) if c[r, k] <= max_distance)
+    """The oracle's restatement of min_cost_matching (clamp, scipy's solve, post-filter; pinned by assoc_seq.npz)."""
+    T, M = cost.shape
+    matches, _, _ = O.min_cost_matching_from_cost(cost, max_distance, range(T), range(M))
+    return sorted((int(r), int(k)) for r, k in matches)
 
 
 def _device_matches(cost, max_distance, row_cand=None, match=None, det=None):
