@@ -111,16 +111,20 @@ def _match_on_device(app, iou, confirmed, unconfirmed, trk_tsu, max_dist, max_io
     H2D (the two row lists) and one D2H (2T + M + 1 ints) per frame."""
     dev = app.device
     T, M = app.shape
-    cand_b = unconfirmed + [k for k in confirmed if trk_tsu[k] == 1]
-    rows_a, rows_b = L.staging(dev).upload([np.asarray(confirmed, np.int32), np.asarray(cand_b, np.int32)])
-    state = torch.empty(2 * T + M + 1, dtype=torch.int32, device=dev)
-    state[:T] = -1
-    state[T:T + M + 1] = 0
+    tsu = np.asarray(trk_tsu)
+    conf_a = np.asarray(confirmed, np.int32)
+    cand_b = np.concatenate([np.asarray(unconfirmed, np.int32), conf_a[tsu[conf_a] == 1] if conf_a.size else conf_a]).astype(np.int32)
+    init = _lap_init.get((T, M))
+    if init is None:
+        _lap_init.clear()
+        init = _lap_init[(T, M)] = np.concatenate([np.full(T, -1, np.int32), np.zeros(M + 1 + T, np.int32)])
+    # row lists and the initial state (match = -1, det_matched = 0, status = 0, match after stage A) in one H2D
+    rows_a, rows_b, state = L.staging(dev).upload([conf_a, cand_b, init])
     match, det_m, status, match_a = state[:T], state[T:T + M], state[T + M:T + M + 1], state[T + M + 1:]
-    if confirmed:
+    if conf_a.size:
         ops.lap_gated(app, rows_a, max_dist, match, det_m, status)
     match_a.copy_(match)
-    if cand_b:
+    if cand_b.size:
         ops.lap_gated(iou, rows_b, max_iou_dist, match, det_m, status)
     key = (dev.index, state.numel())
     host = _lap_host.get(key)
@@ -133,11 +137,13 @@ def _match_on_device(app, iou, confirmed, unconfirmed, trk_tsu, max_dist, max_io
     if h[T + M]:
         raise L.Reidb200Error("device assignment met non-finite costs")
     mt, mt_a = h[:T], h[T + M + 1:]
-    m_a = [(k, int(mt_a[k])) for k in confirmed if mt_a[k] >= 0]
-    m_b = [(k, int(mt[k])) for k in cand_b if mt[k] >= 0 and mt_a[k] < 0]
-    um_t = [k for k in range(T) if mt[k] < 0]
-    um_d = [j for j in range(M) if h[T + j] == 0]
-    return m_a + m_b, list(set(um_t)), um_d
+    ra = conf_a[mt_a[conf_a] >= 0] if conf_a.size else conf_a
+    rb = cand_b[(mt[cand_b] >= 0) & (mt_a[cand_b] < 0)] if cand_b.size else cand_b
+    matches = list(zip(ra.tolist(), mt_a[ra].tolist())) + list(zip(rb.tolist(), mt[rb].tolist()))
+    return matches, np.nonzero(mt < 0)[0].tolist(), np.nonzero(h[T:T + M] == 0)[0].tolist()
+
+
+_lap_init = {}
 
 
 def match(metric, tracks, detections, mc_lambda, max_iou_dist):
