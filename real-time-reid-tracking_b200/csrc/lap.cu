@@ -39,7 +39,7 @@ __global__ void __launch_bounds__(1024)
 lap_components_kernel(const double* __restrict__ cost, size_t ld, const int32_t* __restrict__ row_cand, int nrc, int M,
                       double max_distance, const int32_t* __restrict__ match_col_of_row, const int32_t* __restrict__ det_matched,
                       int32_t* __restrict__ rows_sorted, int32_t* __restrict__ cols_sorted, int32_t* __restrict__ comps,
-                      int32_t* __restrict__ info) {
+                      int32_t* __restrict__ info, int debug_stop) {
   extern __shared__ int sm[];
   __shared__ int wsum[32];
   __shared__ int s_ncomp;
@@ -65,46 +65,63 @@ lap_components_kernel(const double* __restrict__ cost, size_t ld, const int32_t*
   const int n = nr + nc;
   for (int k = tid; k < n; k += 1024) parent[k] = k;
   __syncthreads();
+  if (debug_stop == 1) { if (tid == 0) info[0] = 0; return; }  // (REIDB200_LAP_DEBUG: timing only)
   if (nr > 0 && nc > 0) {
-    for (int e = tid; e < nr * nc; e += 1024) {
-      const int a = e / nc, b = e - a * nc;
-      if (cost[(size_t)ar[a] * ld + ac[b]] <= max_distance) sm_unite(parent, a, nr + b);
+    // a warp takes two rows at a time, its lanes stride the columns: sixteen loads in flight per lane, no index division
+    const int wp = tid >> 5, lane = tid & 31;
+    for (int a0 = wp; a0 < nr; a0 += 64) {
+      const int a1 = a0 + 32;
+      const double* r0 = cost + (size_t)ar[a0] * ld;
+      const double* r1 = a1 < nr ? cost + (size_t)ar[a1] * ld : r0;
+      for (int b0 = 0; b0 < nc; b0 += 256) {
+        double c0[8], c1[8];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          const int b = b0 + k * 32 + lane;
+          const int col = b < nc ? ac[b] : 0;
+          c0[k] = b < nc ? r0[col] : INFINITY;
+          c1[k] = (b < nc && a1 < nr) ? r1[col] : INFINITY;
+        }
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          const int b = b0 + k * 32 + lane;
+          if (c0[k] <= max_distance) sm_unite(parent, a0, nr + b);
+          if (c1[k] <= max_distance) sm_unite(parent, a1, nr + b);
+        }
+      }
     }
   }
   __syncthreads();
+  if (debug_stop == 2) { if (tid == 0) info[0] = 0; return; }
   for (int k = tid; k < n; k += 1024) root[k] = sm_find(parent, k);
   __syncthreads();
-  // rows and columns in (component root, index) order; a component with a row is led by its lowest row
-  for (int a = tid; a < nr; a += 1024) {
-    const int ra = root[a];
-    int rank = 0, cnt = 0;
-    for (int o = 0; o < nr; ++o) {
-      const int r2 = root[o];
-      rank += (r2 < ra || (r2 == ra && o < a)) ? 1 : 0;
-      cnt += r2 == ra ? 1 : 0;
-    }
-    rows_sorted[rank] = ar[a];
-    if (ra == a) {
-      int before = 0, ncols = 0;
-      for (int b = 0; b < nc; ++b) {
-        const int r2 = root[nr + b];
-        before += r2 < ra ? 1 : 0;
-        ncols += r2 == ra ? 1 : 0;
-      }
-      if (ncols > 0) {
-        const int k = atomicAdd(&s_ncomp, 1);
-        comps[4 * k] = rank; comps[4 * k + 1] = cnt; comps[4 * k + 2] = before; comps[4 * k + 3] = ncols;
-      }
-    }
-  }
-  for (int b = tid; b < nc; b += 1024) {
-    const int rb = root[nr + b];
+  // rows and columns in (component root, index) order through one unique key per node; a component with a row is led
+  // by its lowest row (rows carry the lower node numbers)
+  int* key = parent;  // (the union-find forest is no longer needed)
+  for (int k = tid; k < n; k += 1024) key[k] = root[k] * 4096 + (k < nr ? k : k - nr);
+  __syncthreads();
+  for (int k = tid; k < n; k += 1024) {
+    const int mine = key[k];
     int rank = 0;
-    for (int o = 0; o < nc; ++o) {
-      const int r2 = root[nr + o];
-      rank += (r2 < rb || (r2 == rb && o < b)) ? 1 : 0;
+    if (k < nr) {
+      for (int o = 0; o < nr; ++o) rank += key[o] < mine ? 1 : 0;
+      rows_sorted[rank] = ar[k];
+      if (root[k] == k) {  // leader: sizes of its component and the columns sorted before it
+        int cnt = 0, before = 0, ncols = 0;
+        for (int o = 0; o < nr; ++o) cnt += root[o] == k ? 1 : 0;
+        for (int o = nr; o < n; ++o) {
+          before += root[o] < k ? 1 : 0;
+          ncols += root[o] == k ? 1 : 0;
+        }
+        if (ncols > 0) {
+          const int c = atomicAdd(&s_ncomp, 1);
+          comps[4 * c] = rank; comps[4 * c + 1] = cnt; comps[4 * c + 2] = before; comps[4 * c + 3] = ncols;
+        }
+      }
+    } else {
+      for (int o = nr; o < n; ++o) rank += key[o] < mine ? 1 : 0;
+      cols_sorted[rank] = ac[k - nr];
     }
-    cols_sorted[rank] = ac[b];
   }
   __syncthreads();
   if (tid == 0) { info[0] = s_ncomp; info[1] = nr; info[2] = nc; }
@@ -115,11 +132,76 @@ struct LapWork {
   int32_t *path, *a4b, *b4a, *SR, *SC;  // each T + M
 };
 
-__global__ void __launch_bounds__(256)
+// Warp arg-min over (value, free column preferred, lower column index): the order scipy's scan resolves equal costs in.
+__device__ __forceinline__ void lap_argmin(double& best, int& best_free, int& best_b) {
+#pragma unroll
+  for (int o = 16; o; o >>= 1) {
+    const double ob = __shfl_xor_sync(0xffffffffu, best, o);
+    const int obb = __shfl_xor_sync(0xffffffffu, best_b, o), of = __shfl_xor_sync(0xffffffffu, best_free, o);
+    if (ob < best || (ob == best && (of > best_free || (of == best_free && obb < best_b)))) { best = ob; best_b = obb; best_free = of; }
+  }
+}
+
+constexpr int LAP_SOLVE_WARPS = 4;
+
+// A component of at most 32 x 32: the clamped sub-matrix sits in shared memory, lane b owns column b (dual v, shortest
+// path cost, path, owner) and lane a owns row a (dual u, assigned column) in registers; the same arithmetic in the same
+// order as the general path below.  cs = this warp's 32 x 33 doubles.
+__device__ __forceinline__ void lap_solve_small(double* cs, int na, int nb, int lane, double max_distance, int& b4a_out,
+                                                bool& admissible_out) {
+  double u_a = 0.0, v_b = 0.0;
+  int b4a_a = -1, a4b_b = -1;
+  for (int cur = 0; cur < na; ++cur) {
+    double sp_b = INFINITY;
+    int path_b = -1;
+    bool SC_b = false, SR_a = false;
+    int sink = -1, i = cur;
+    double min_val = 0.0;
+    while (sink < 0) {
+      if (lane == i) SR_a = true;
+      const double ui = __shfl_sync(0xffffffffu, u_a, i);
+      double best = INFINITY;
+      int best_b = INT_MAX, best_free = 0;
+      if (lane < nb && !SC_b) {
+        const double r = min_val + cs[i * 33 + lane] - ui - v_b;
+        if (r < sp_b) { sp_b = r; path_b = i; }
+        best = sp_b; best_b = lane; best_free = a4b_b < 0 ? 1 : 0;
+      }
+      lap_argmin(best, best_free, best_b);
+      if (best_b == INT_MAX) {  // cannot happen with the clamped (finite) costs; never spin
+        b4a_out = -1;
+        admissible_out = false;
+        return;
+      }
+      min_val = best;
+      if (lane == best_b) SC_b = true;
+      const int owner = __shfl_sync(0xffffffffu, a4b_b, best_b);
+      if (owner < 0) sink = best_b; else i = owner;
+    }
+    const double sp_of_mine = __shfl_sync(0xffffffffu, sp_b, b4a_a < 0 ? 0 : b4a_a);
+    if (lane == cur) u_a = u_a + min_val;
+    else if (SR_a) u_a = u_a + (min_val - sp_of_mine);
+    if (SC_b) v_b = v_b - (min_val - sp_b);
+    int j = sink;
+    for (int hop = 0; hop <= na; ++hop) {  // augment along the path back to cur
+      const int a = __shfl_sync(0xffffffffu, path_b, j);
+      if (lane == j) a4b_b = a;
+      const int t = __shfl_sync(0xffffffffu, b4a_a, a);
+      if (lane == a) b4a_a = j;
+      j = t;
+      if (a == cur) break;
+    }
+  }
+  b4a_out = b4a_a;
+  admissible_out = lane < na && cs[lane * 33 + (b4a_a < 0 ? 0 : b4a_a)] <= max_distance;
+}
+
+__global__ void __launch_bounds__(32 * LAP_SOLVE_WARPS)
 lap_solve_kernel(const double* __restrict__ cost, size_t ld, double max_distance, const int32_t* __restrict__ rows_sorted,
                  const int32_t* __restrict__ cols_sorted, const int32_t* __restrict__ comps, const int32_t* __restrict__ info,
                  LapWork w, int32_t* __restrict__ match_col_of_row, int32_t* __restrict__ det_matched, int32_t* __restrict__ status) {
-  const int comp = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+  __shared__ double s_cost[LAP_SOLVE_WARPS][32 * 33];
+  const int comp = blockIdx.x * LAP_SOLVE_WARPS + (threadIdx.x >> 5), lane = threadIdx.x & 31;
   if (comp >= info[0]) return;
   const int row_off = comps[4 * comp], nrows = comps[4 * comp + 1], col_off = comps[4 * comp + 2], ncols = comps[4 * comp + 3];
   const int32_t* R = rows_sorted + row_off;
@@ -137,6 +219,21 @@ lap_solve_kernel(const double* __restrict__ cost, size_t ld, double max_distance
     const double x = tr ? cost[(size_t)B[b] * ld + A[a]] : cost[(size_t)A[a] * ld + B[b]];
     return x <= max_distance ? x : gated;
   };
+  if (nb <= 32) {  // the usual size: registers + shared memory
+    double* cs = s_cost[threadIdx.x >> 5];
+    for (int a = 0; a < na; ++a)
+      if (lane < nb) cs[a * 33 + lane] = cst(a, lane);
+    __syncwarp();
+    int b4a_a;
+    bool ok;
+    lap_solve_small(cs, na, nb, lane, max_distance, b4a_a, ok);
+    if (ok) {
+      const int row = tr ? B[b4a_a] : A[lane], col = tr ? A[lane] : B[b4a_a];
+      match_col_of_row[row] = col;
+      det_matched[col] = 1;
+    }
+    return;
+  }
   const int base = row_off + col_off;
   double* u = w.u + base;
   double* v = w.v + base;
@@ -164,12 +261,7 @@ lap_solve_kernel(const double* __restrict__ cost, size_t ld, double max_distance
         const int fr = a4b[b] < 0 ? 1 : 0;  // scipy prefers an unassigned column among equal costs
         if (s < best || (s == best && (fr > best_free || (fr == best_free && b < best_b)))) { best = s; best_b = b; best_free = fr; }
       }
-#pragma unroll
-      for (int o = 16; o; o >>= 1) {
-        const double ob = __shfl_xor_sync(0xffffffffu, best, o);
-        const int obb = __shfl_xor_sync(0xffffffffu, best_b, o), of = __shfl_xor_sync(0xffffffffu, best_free, o);
-        if (ob < best || (ob == best && (of > best_free || (of == best_free && obb < best_b)))) { best = ob; best_b = obb; best_free = of; }
-      }
+      lap_argmin(best, best_free, best_b);
       if (best_b == INT_MAX || ++guard > nb) {  // cannot happen with finite costs; never spin
         if (lane == 0) atomicExch(status, 1);
         return;
@@ -247,16 +339,17 @@ extern "C" int reidb200_lap_gated(const double* cost, int T, int M, size_t ld, c
                                  (int)(((size_t)3 * 2 * LAP_MAX_SIDE + LAP_MAX_SIDE) * sizeof(int))));
     attr = true;
   }
+  static const int debug_stop = getenv("REIDB200_LAP_DEBUG") ? atoi(getenv("REIDB200_LAP_DEBUG")) : 0;  // timing experiments only
   {
     ProfScope _ps("lap_components_kernel", st);
     lap_components_kernel<<<1, 1024, smem, st>>>(cost, ld, row_cand, nrc, M, max_distance, match_col_of_row, det_matched, rows_sorted,
-                                                 cols_sorted, comps, info);
+                                                 cols_sorted, comps, info, debug_stop);
   }
   RB_LAUNCH_CHECK("lap_components_kernel");
   const int max_comps = nrc < M ? nrc : M;
   {
     ProfScope _ps("lap_solve_kernel", st);
-    lap_solve_kernel<<<(max_comps + 7) / 8, 256, 0, st>>>(cost, ld, max_distance, rows_sorted, cols_sorted, comps, info, w,
+    lap_solve_kernel<<<(max_comps + LAP_SOLVE_WARPS - 1) / LAP_SOLVE_WARPS, 32 * LAP_SOLVE_WARPS, 0, st>>>(cost, ld, max_distance, rows_sorted, cols_sorted, comps, info, w,
                                                           match_col_of_row, det_matched, status);
   }
   RB_LAUNCH_CHECK("lap_solve_kernel");
