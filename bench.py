@@ -390,6 +390,32 @@ def bench_retrieval(args, rank, world, dev, barrier):
             "checksum": {"id_sum": int(Ih.astype(np.int64).sum()), "dist_sum": float(Dh.astype(np.float64).sum())}}
 
 
+def bench_eval_c1(args, rank, world, dev, barrier, d0):
+    """BASELINE.json configs[0]: Market-shaped evaluate_all WITHOUT re-ranking (3368 x 15913 x 512-d score GEMM + CMC/mAP
+    counting kernel), the queries split over the ranks and one NCCL all-reduce of the CMC counts + AP sum
+    (shard.evaluate_all_sharded).  Strong scaling: the same set on every rank.  Device-timed, max over ranks."""
+    from reidb200 import shard, synth
+
+    d = d0 if d0 is not None else synth.market_like(Q=Q_FULL, G=G_FULL, D=D_FULL, n_ids=IDS_FULL, seed=0)
+    a = [torch.from_numpy(d[k]).to(dev) for k in ("qf", "ql", "qc", "gf", "gl", "gc")]
+    a[1], a[2], a[4], a[5] = (x.to(torch.int32) for x in (a[1], a[2], a[4], a[5]))
+    fn = lambda: shard.evaluate_all_sharded(*a, device=dev)
+    for _ in range(3):
+        cmc, ap = fn()
+    barrier()
+    steps = max(args.steps, 5)
+    ms = _timed(fn, steps, barrier)
+    t = torch.tensor([ms], dtype=torch.float64, device=dev)
+    if world > 1:
+        import torch.distributed as dist
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t.item()) / steps
+    return {"workload": "market1501_eval_no_rerank (configs[0])", "scaling": "strong", "query_shards": world,
+            "ms_per_eval": ms, "pairs_per_s": Q_FULL * G_FULL / (ms * 1e-3),
+            "allreduce_bytes": (G_FULL + 1) * 8 if world > 1 else 0,
+            "result": {"rank1": float(cmc[0]), "mAP": float(ap)}}
+
+
 # --------------------------------------------------------------------------------------------- CPU port / reference arm
 def cpu_sample(scale=4):
     """A bounded sample of the same workload: Market-shaped set at 1/scale of the query/gallery/identity counts."""
@@ -558,6 +584,7 @@ def run_ours(args):
     h2d = merged_host.numel() * 4 + sum(v.numel() * 4 for v in lab_host.values())
     d2h = G * 4 + 8
 
+    eval_c1 = bench_eval_c1(args, rank, world, dev, barrier, d if rank == 0 else None)
     posttricks = bench_posttricks(merged, K1, K2, args.steps) if (rank == 0 and not args.no_assoc) else None
     retrieval = None
     if not args.no_retrieval:
@@ -607,6 +634,7 @@ def run_ours(args):
         "kernel_share_of_step": share,
         "result": {"rank1": float(cmc_h[0]), "mAP": float(ap_h)},
     }
+    line["eval_c1"] = eval_c1
     if retrieval is not None:
         line["retrieval"] = retrieval
     if not args.no_assoc:

@@ -42,6 +42,23 @@ def evaluate_all(qf, ql, qc, gf, gl, gc):
     return CMC, ap
 
 
+def evaluate_all_sharded(qf, ql, qc, gf, gl, gc, group=None, verbose=True):
+    """`evaluate_all` with the queries split over the ranks of `group` (one process per GPU, gallery replicated) and
+    ONE NCCL all-reduce of the CMC counts + AP sum (shard.evaluate_all_sharded); same return value on every rank."""
+    from . import shard
+
+    cmc, ap = shard.evaluate_all_sharded(qf, ql, qc, gf, gl, gc, group=group)
+    CMC, ap = cmc.cpu(), float(ap.cpu())
+    if ap != ap:
+        raise L.Reidb200Error("evaluate_all: a query has more good matches than this build holds (2048)")
+    if verbose and shard.dist.is_initialized() and shard.dist.get_rank(group) != 0:
+        verbose = False
+    if verbose:
+        r = lambda k: float(CMC[k]) if CMC.numel() > k else float("nan")
+        print('Rank@1:%f Rank@5:%f Rank@10:%f mAP:%f' % (r(0), r(4), r(9), ap))
+    return CMC, ap
+
+
 def evaluate_dist(dist, ql, qc, gl, gc):
     """Same reduction on a precomputed Q x G DISTANCE matrix (ascending = better), e.g. a re-ranked one."""
     cmc, ap = ops.eval_cmc_map(dist, _labels(ql), _labels(qc), _labels(gl), _labels(gc), descending=False)

@@ -151,3 +151,57 @@ class ShardedSearcher:
         """faiss-style host results (D f32[Q,k], I i64[Q,k]) as numpy."""
         D, I = self.search_device(xq, k, metric)
         return D.cpu().numpy(), I.cpu().numpy()
+
+
+# --------------------------------------------------------------------------------------------- query-sharded CMC / mAP
+def _eval_queries_cuda(qf, ql, qc, gf, gl, gc):
+    """Per-query (ap f64[q], first-hit rank i32[q]) of a query slice on this rank's GPU: tcgen05 score GEMM + the
+    counting kernel of csrc/evalmap.cu (ap 0 / first -1 for a query with no valid match, like evaluate.py:41-43)."""
+    score = ops.distmat(qf, gf, "dot")
+    _, _, ap_q, first = ops.eval_cmc_map(score, ql, qc, gl, gc, descending=True, per_query=True)
+    return ap_q, first
+
+
+def evaluate_all_sharded(qf, ql, qc, gf, gl, gc, group=None, device=None, local_eval=None):
+    """`evaluate_all` (reid/evaluate.py:33-52) with the QUERIES split over the ranks (queries are
+    independent).  Every rank holds the gallery, evaluates queries [lo_r, hi_r) of `shard_bounds(Q, world)` and
+    contributes (#queries whose first hit is at rank <= r, for every r) and its sum of APs; ONE all-reduce(sum) of
+    f64[G+1] (counts are exact in f64) gives every rank the same `(CMC f32[G], mAP f64)`, divided by ALL Q queries as
+    the reference does.  Counts are integers, so CMC is bit-identical to the single-GPU call; the AP sum differs from
+    it by the summation order only (<= 1e-15).
+
+    `local_eval(qf, ql, qc, gf, gl, gc) -> (ap_q f64[q], first i32[q])` is the injection point of the gloo host-logic
+    test; the default is the CUDA path and raises without an sm_100 device."""
+    distributed = dist.is_available() and dist.is_initialized()
+    rank = dist.get_rank(group) if distributed else 0
+    world = dist.get_world_size(group) if distributed else 1
+    custom = local_eval is not None
+    if custom:
+        dev = torch.device("cpu") if device is None else torch.device(device)
+        as_f = lambda x: torch.as_tensor(np.asarray(x, np.float32) if not isinstance(x, torch.Tensor) else x).to(dev)
+    else:
+        dev = device or L.require_device()
+        as_f = lambda x: L.as_f32_cuda(x, dev)
+    lab = lambda x: (x if isinstance(x, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(np.asarray(x)))).reshape(-1)
+    qf, gf = as_f(qf), as_f(gf)
+    ql, qc, gl, gc = lab(ql), lab(qc), lab(gl), lab(gc)
+    Q, G = int(qf.shape[0]), int(gf.shape[0])
+    if Q == 0 or G == 0:
+        raise ValueError("evaluate_all: empty query or gallery set")
+    if ql.numel() != Q or qc.numel() != Q or gl.numel() != G or gc.numel() != G:
+        raise ValueError("label / camera vectors do not match the feature matrices")
+    lo, hi = shard_bounds(Q, world)[rank]
+    part = torch.zeros(G + 1, dtype=torch.float64, device=dev)
+    if hi > lo:
+        ap_q, first = (local_eval if custom else _eval_queries_cuda)(qf[lo:hi], ql[lo:hi], qc[lo:hi], gf, gl, gc)
+        ap_q, first = ap_q.to(dev), first.to(dev).long()
+        hit = first >= 0
+        hist = torch.bincount(first[hit], minlength=G)[:G]
+        part[:G] = torch.cumsum(hist, 0).to(torch.float64)
+        part[G] = ap_q.sum()
+    if world > 1:
+        dist.all_reduce(part, op=dist.ReduceOp.SUM, group=group)
+    # tensor / tensor: an IEEE division like the finalize kernel's (torch turns `/ python_scalar` into `* (1/Q)`)
+    cmc = part[:G].to(torch.float32) / torch.full((1,), float(Q), dtype=torch.float32, device=dev)
+    ap = part[G] / Q
+    return cmc, ap

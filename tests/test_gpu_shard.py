@@ -95,3 +95,19 @@ def test_faiss_index_shim(rb):
     assert np.array_equal(I2.cpu().numpy(), I)
     D3, I3 = F.search_raw_array_pytorch(None, torch.from_numpy(xb).cuda(), torch.from_numpy(xq).cuda(), 5)
     assert I3.dtype == torch.int32 and np.array_equal(I3.cpu().numpy(), I)
+
+
+def test_sharded_evaluate_all_single_rank(rb):
+    """Query-sharded evaluate_all at world size 1 == the single call (bit for bit) and the oracle (CMC/mAP 1e-6)."""
+    from reidb200 import evaluate, shard, synth
+
+    d = synth.market_like(Q=150, G=700, D=64, seed=4, orphan_frac=0.05)
+    qf, ql, qc, gf, gl, gc = (d[k] for k in ('qf', 'ql', 'qc', 'gf', 'gl', 'gc'))
+    cmc, ap = shard.evaluate_all_sharded(qf, ql, qc, gf, gl, gc)
+    cmc1, ap1 = evaluate.evaluate_all_device(qf, ql, qc, gf, gl, gc)
+    assert torch.equal(cmc, cmc1) and abs(float(ap) - float(ap1[0])) < 1e-14
+    cmco, apo = O.evaluate_all(qf, ql, qc, gf, gl, gc)
+    np.testing.assert_allclose(cmc.cpu().numpy(), cmco, atol=1e-6)
+    assert abs(float(ap) - apo) < 1e-6
+    CMC, ap2 = evaluate.evaluate_all_sharded(qf, ql, qc, gf, gl, gc, verbose=False)
+    assert isinstance(CMC, torch.FloatTensor) and ap2 == float(ap)

@@ -101,3 +101,61 @@ def test_shard_bounds():
     assert shard.shard_bounds(0, 2) == [(0, 0), (0, 0)]
     b = shard.shard_bounds(4_000_000, 8)
     assert b[0] == (0, 500_000) and b[-1] == (3_500_000, 4_000_000)
+
+
+# ------------------------------------------------------------------ query-sharded evaluate_all (CMC/mAP row)
+def _oracle_local_eval(qf, ql, qc, gf, gl, gc):
+    from oracle import reid_oracle as O
+
+    n = qf.shape[0]
+    ap = np.zeros(n, np.float64)
+    first = np.full(n, -1, np.int32)
+    for i in range(n):
+        ap_i, cmc_i = O.evaluate(qf[i].numpy(), int(ql[i]), int(qc[i]), gf.numpy(), gl.numpy(), gc.numpy())
+        if cmc_i[0] == -1:
+            continue
+        ap[i], first[i] = ap_i, int(np.argmax(cmc_i))
+    return torch.from_numpy(ap), torch.from_numpy(first)
+
+
+def _eval_case(Q, G, seed=3):
+    rng = np.random.default_rng(seed)
+    gl = rng.integers(0, 9, G)
+    gl[rng.random(G) < 0.15] = -1
+    gc = rng.integers(0, 3, G)
+    ql, qc = rng.integers(0, 9, Q), rng.integers(0, 3, Q)
+    if Q > 2:
+        ql[2] = 77  # a query without any valid match: skipped in the sums, still counted in the divisor
+    unit = lambda a: (a / np.linalg.norm(a, axis=1, keepdims=True)).astype(np.float32)
+    cent = rng.standard_normal((100, 24))
+    gf = unit(cent[gl] + 0.8 * rng.standard_normal((G, 24)))
+    qf = unit(cent[ql] + 0.8 * rng.standard_normal((Q, 24)))
+    return qf, ql, qc, gf, gl, gc
+
+
+def _eval_worker(rank, world, port, Q, out_dir):
+    sys.path.insert(0, ROOT)
+    import reidb200  # noqa: F401
+    from reidb200 import shard
+
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        qf, ql, qc, gf, gl, gc = _eval_case(Q, 60)
+        cmc, ap = shard.evaluate_all_sharded(qf, ql, qc, gf, gl, gc, local_eval=_oracle_local_eval)
+        np.savez(os.path.join(out_dir, "e%d.npz" % rank), cmc=cmc.numpy(), ap=float(ap))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("Q", [11, 1])
+def test_sharded_evaluate_all_world2_gloo(tmp_path, Q):
+    from oracle import reid_oracle as O
+
+    mp.spawn(_eval_worker, args=(2, _free_port(), Q, str(tmp_path)), nprocs=2, join=True)
+    r0, r1 = np.load(tmp_path / "e0.npz"), np.load(tmp_path / "e1.npz")
+    assert np.array_equal(r0["cmc"], r1["cmc"]) and r0["ap"] == r1["ap"]  # same answer on every rank
+    qf, ql, qc, gf, gl, gc = _eval_case(Q, 60)
+    cmc, ap = O.evaluate_all(qf, ql, qc, gf, gl, gc)
+    assert np.array_equal(r0["cmc"], cmc)  # integer counts / Q: exact
+    assert abs(float(r0["ap"]) - ap) < 1e-12

@@ -47,6 +47,19 @@ for nq, nb, d, k in ((64, 20_001, 128, 100), (300, 150_000, 256, 100), (17, 5, 3
     if rank == 0:
         print("shard_check world=%d nq=%d nb=%d d=%d k=%d: sharded==single %s, oracle %s, dup order %s" %
               (world, nq, nb, d, k, same, tie_ok, dup_ok), flush=True)
+# query-sharded evaluate_all (one all-reduce of CMC counts + AP sum) against the single-GPU call
+from reidb200 import evaluate, synth
+
+for Q, G, D in ((3368, 15913, 512), (5, 40, 32), (1, 9, 16)):
+    m = synth.market_like(Q=Q, G=G, D=D, seed=Q)
+    a = [m[k] for k in ("qf", "ql", "qc", "gf", "gl", "gc")]
+    cmc, ap = shard.evaluate_all_sharded(*a, device=dev)
+    cmc1, ap1 = evaluate.evaluate_all_device(*[torch.from_numpy(x).to(dev) for x in a])
+    same = bool(torch.equal(cmc, cmc1)) and abs(float(ap) - float(ap1[0])) < 1e-12
+    ok &= same
+    if rank == 0:
+        print("shard_check world=%d evaluate_all Q=%d G=%d: query-sharded == single %s (rank1 %.6f mAP %.6f)" %
+              (world, Q, G, same, float(cmc[0]), float(ap)), flush=True)
 t = torch.tensor([0 if ok else 1], device=dev)
 if world > 1:
     dist.all_reduce(t)
