@@ -155,11 +155,13 @@ class ShardedSearcher:
 
 # --------------------------------------------------------------------------------------------- query-sharded CMC / mAP
 def _eval_queries_cuda(qf, ql, qc, gf, gl, gc):
-    """Per-query (ap f64[q], first-hit rank i32[q]) of a query slice on this rank's GPU: tcgen05 score GEMM + the
-    counting kernel of csrc/evalmap.cu (ap 0 / first -1 for a query with no valid match, like evaluate.py:41-43)."""
+    """Cumulative first-hit counts f64[G] and AP sum f64[] of a query slice on this rank's GPU: tcgen05 score GEMM + the
+    counting kernel of csrc/evalmap.cu (a query with no valid match adds nothing, like evaluate.py:41-43).  The kernel
+    returns float(count) / float(q); count <= 2^24 so round(cmc * q) restores the integer exactly -- no extra pass, no
+    host sync."""
     score = ops.distmat(qf, gf, "dot")
-    _, _, ap_q, first = ops.eval_cmc_map(score, ql, qc, gl, gc, descending=True, per_query=True)
-    return ap_q, first
+    cmc, _, ap_q, _ = ops.eval_cmc_map(score, ql, qc, gl, gc, descending=True, per_query=True)
+    return torch.round(cmc.to(torch.float64) * float(qf.shape[0])), ap_q.sum()
 
 
 def evaluate_all_sharded(qf, ql, qc, gf, gl, gc, group=None, device=None, local_eval=None):
@@ -192,13 +194,14 @@ def evaluate_all_sharded(qf, ql, qc, gf, gl, gc, group=None, device=None, local_
         raise ValueError("label / camera vectors do not match the feature matrices")
     lo, hi = shard_bounds(Q, world)[rank]
     part = torch.zeros(G + 1, dtype=torch.float64, device=dev)
-    if hi > lo:
-        ap_q, first = (local_eval if custom else _eval_queries_cuda)(qf[lo:hi], ql[lo:hi], qc[lo:hi], gf, gl, gc)
-        ap_q, first = ap_q.to(dev), first.to(dev).long()
-        hit = first >= 0
-        hist = torch.bincount(first[hit], minlength=G)[:G]
+    if hi > lo and custom:
+        ap_q, first = local_eval(qf[lo:hi], ql[lo:hi], qc[lo:hi], gf, gl, gc)
+        first = first.to(dev).long()
+        hist = torch.bincount(first[first >= 0], minlength=G)[:G]
         part[:G] = torch.cumsum(hist, 0).to(torch.float64)
-        part[G] = ap_q.sum()
+        part[G] = ap_q.to(dev).sum()
+    elif hi > lo:
+        part[:G], part[G] = _eval_queries_cuda(qf[lo:hi], ql[lo:hi], qc[lo:hi], gf, gl, gc)
     if world > 1:
         dist.all_reduce(part, op=dist.ReduceOp.SUM, group=group)
     # tensor / tensor: an IEEE division like the finalize kernel's (torch turns `/ python_scalar` into `* (1/Q)`)
