@@ -1,4 +1,4 @@
-"""torchrun --nproc-per-node N tools/shard_check.py : the NCCL path of the gallery-sharded search against (a) the same
+"""torchrun --nproc-per-node N tests/nccl_shard_check.py : the NCCL path of the gallery-sharded search against (a) the same
 search on ONE resident gallery (rank 0, bit-identical tables expected: same kernels, same tie rule) and (b) the CPU oracle
 on a sub-problem.  Prints one line per check; exit code 0 = all equal."""
 import os

@@ -1,5 +1,5 @@
 """GPU: resident packed gallery search (reidb200_knn_packed), the multi-pass merge of knn, and the sharded searcher
-(world size 1 here; the NCCL path is exercised by tools/shard_check.py under torchrun and by bench.py --gpus N)."""
+(world size 1 here; the NCCL path is exercised by tests/nccl_shard_check.py under torchrun and by bench.py --gpus N)."""
 import os
 
 import numpy as np
