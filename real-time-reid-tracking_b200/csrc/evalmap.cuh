@@ -49,21 +49,17 @@ static __device__ __noinline__ void ev_count_before(EvalScratch* sc, int ngood, 
   atomicAdd(&sc->gpos[lo], 1);
 }
 
-// One query whose G row values live in registers: thread tid holds column tid + k * NT in val[k], k < PF (G <= NT * PF).
-// Same two passes as eval_query_kernel: (1) good items = same id & other camera, rank-sorted; (2) every non-junk column
-// ranked before the worst good item bumps the histogram slot of the first good item it precedes.  All NT threads of
-// the CTA must call it (block barriers inside).  Writes ap_q[q], first[q], hist[first hit]; sets *status on overflow.
+// Label pass of the register-resident evaluation, separated so that the caller can run it EARLY (it needs the labels
+// only, not the row values: in the fused re-rank kernel it sits under the latency of the kernel's first global loads
+// instead of adding four dependent L2 round trips to the tail).  Bit k of the result = column tid + k * NT is a good
+// item of query q (same id, different camera: evaluate.py:66-70).
 template <int NT, int PF>
-__device__ __forceinline__ void eval_row_in_registers(const float (&val)[PF], int G, int q, int descending,
-                                                      const int32_t* __restrict__ ql, const int32_t* __restrict__ qc,
-                                                      const int32_t* __restrict__ gl, const int32_t* __restrict__ gc,
-                                                      double* __restrict__ ap_q, int32_t* __restrict__ first,
-                                                      int32_t* __restrict__ hist, int32_t* __restrict__ status,
-                                                      EvalScratch* sc) {
+__device__ __forceinline__ uint32_t eval_good_mask(int G, int q, const int32_t* __restrict__ ql, const int32_t* __restrict__ qc,
+                                                   const int32_t* __restrict__ gl, const int32_t* __restrict__ gc) {
+  static_assert(PF <= 32, "one mask bit per register value");
   const int tid = threadIdx.x;
   const int32_t my_l = ql[q], my_c = qc[q];
-  if (tid == 0) sc->ngood = 0;
-  __syncthreads();
+  uint32_t mask = 0;
 #pragma unroll
   for (int k0 = 0; k0 < PF; k0 += 8) {  // labels in batches of eight loads (the label vectors are L2 resident)
     int32_t lab[8];
@@ -75,9 +71,41 @@ __device__ __forceinline__ void eval_row_in_registers(const float (&val)[PF], in
 #pragma unroll
     for (int u = 0; u < 8; ++u) {
       const int j = tid + (k0 + u) * NT;
-      if (k0 + u < PF && j < G && lab[u] == my_l && __ldg(gc + j) != my_c)  // good: same id, different camera
-        ev_add_good(sc, j, ev_key(val[k0 + u], descending));
+      if (k0 + u < PF && j < G && lab[u] == my_l && __ldg(gc + j) != my_c) mask |= 1u << (k0 + u);
     }
+  }
+  return mask;
+}
+
+// One query whose G row values live in registers: thread tid holds column tid + k * NT in val[k], k < PF (G <= NT * PF);
+// goodmask = eval_good_mask<NT, PF>() of the same query.
+// LAZY values: bit k of donemask says val[k] is the final ranking value; a clear bit says val[k] is still a RAW value
+// r with final = finish(r), finish monotone non-decreasing (distances, descending == 0 only).  Raw values are finished
+// only where the ranking needs them: the good items, and the columns with r <= raw_bound(worst good value), where
+// raw_bound(w) >= every r with finish(r) <= w (a superset test -- the exact comparison follows on the finished value,
+// so the result is identical to finishing everything first).  Pass donemask = ~0u when all values are final.
+// Same two passes as eval_query_kernel: (1) good items = same id & other camera, rank-sorted; (2) every non-junk column
+// ranked before the worst good item bumps the histogram slot of the first good item it precedes.  All NT threads of
+// the CTA must call it (block barriers inside).  Writes ap_q[q], first[q], hist[first hit]; sets *status on overflow.
+template <int NT, int PF, class Finish, class RawBound>
+__device__ __forceinline__ void eval_row_in_registers(float (&val)[PF], uint32_t donemask, uint32_t goodmask, Finish finish,
+                                                      RawBound raw_bound, int G, int q, int descending,
+                                                      const int32_t* __restrict__ ql, const int32_t* __restrict__ qc,
+                                                      const int32_t* __restrict__ gl, const int32_t* __restrict__ gc,
+                                                      double* __restrict__ ap_q, int32_t* __restrict__ first,
+                                                      int32_t* __restrict__ hist, int32_t* __restrict__ status,
+                                                      EvalScratch* sc) {
+  const int tid = threadIdx.x;
+  const int32_t my_l = ql[q], my_c = qc[q];
+  if (tid == 0) sc->ngood = 0;
+  __syncthreads();
+  if (goodmask) {  // a handful of threads per CTA
+#pragma unroll
+    for (int k = 0; k < PF; ++k)
+      if ((goodmask >> k) & 1u) {
+        if (!((donemask >> k) & 1u)) { val[k] = finish(val[k]); donemask |= 1u << k; }
+        ev_add_good(sc, tid + k * NT, ev_key(val[k], descending));
+      }
   }
   __syncthreads();
   const int ngood = sc->ngood;
@@ -102,12 +130,19 @@ __device__ __forceinline__ void eval_row_in_registers(const float (&val)[PF], in
   const uint32_t worst_k = sc->skey[ngood - 1];
   const uint32_t worst_o = descending ? ~worst_k : worst_k;
   const float worst_v = __uint_as_float((worst_o & 0x80000000u) ? (worst_o & 0x7fffffffu) : ~worst_o);
+  const float raw_t = raw_bound(worst_v);
+  const int kfull = G / NT;  // iterations in which every thread has a column
 #pragma unroll
   for (int k = 0; k < PF; ++k) {
     const int j = tid + k * NT;
-    if (j >= G) continue;
-    if (descending ? !(val[k] >= worst_v) : !(val[k] <= worst_v)) continue;  // cheap superset test, the common case
-    ev_count_before(sc, ngood, ev_key(val[k], descending), j, descending, my_l, my_c, gl, gc);
+    if (k >= kfull && j >= G) continue;
+    float v = val[k];
+    if (!((donemask >> k) & 1u)) {
+      if (!(v <= raw_t)) continue;  // the common case: a raw value that cannot be ranked before the worst good item
+      v = finish(v);
+    }
+    if (descending ? !(v >= worst_v) : !(v <= worst_v)) continue;  // cheap superset test
+    ev_count_before(sc, ngood, ev_key(v, descending), j, descending, my_l, my_c, gl, gc);
   }
   __syncthreads();
   if (tid == 0) {  // inclusive prefix: position of good s among the non-junk items

@@ -563,6 +563,11 @@ static __device__ __noinline__ float jaccard_nonzero(float t, int use_f16) {
   return jd < 0.f ? 0.f : jd;
 }
 
+// lambda blend of one entry (D8): jd * (1 - lambda) + sqrt(max(d2, 1e-12)) * lambda, every operation rounded on its own
+static __device__ __noinline__ float jr_blend_value(float jd, float d2, float one_m_l, float lambda_value) {
+  return __fadd_rn(__fmul_rn(jd, one_m_l), __fmul_rn(sqrtf(fmaxf(d2, 1e-12f)), lambda_value));
+}
+
 __device__ __forceinline__ float jaccard_value(float t, int use_f16) {
   return t == 0.f ? 1.0f : jaccard_nonzero(t, use_f16);
 }
@@ -596,6 +601,9 @@ jaccard_rows_kernel(const int32_t* __restrict__ qcols, const float* __restrict__
   }
   for (int r = tid; r < N4 / 4; r += JR_THREADS) reinterpret_cast<float4*>(acc)[r] = make_float4(0.f, 0.f, 0.f, 0.f);
   const int n = qcnt[i];
+  // fused evaluation: which of this thread's columns are good items of the query (labels only -- done here, under the
+  // latency of the loads above and below, the row values arrive at the end)
+  const uint32_t goodmask = ev.enabled ? eval_good_mask<JR_THREADS, JR_PF>(ncols, (int)blockIdx.x, ev.ql, ev.qc, ev.gl, ev.gc) : 0u;
   for (int t = tid; t < n; t += JR_THREADS) {
     const float v = qvals[(size_t)i * cap + t];
     const int j = qcols[(size_t)i * cap + t];
@@ -642,6 +650,39 @@ jaccard_rows_kernel(const int32_t* __restrict__ qcols, const float* __restrict__
   const float one_m_l = 1.0f - lambda_value;
   float* orow = reinterpret_cast<float*>(out) + (size_t)blockIdx.x * ldo;
   __half* hrow = reinterpret_cast<__half*>(out) + (size_t)blockIdx.x * ldo;
+  if (ev.enabled && blend && !out && !use_f16) {
+    // The fused-evaluation path (nothing stored, fp32, blended).  Almost every entry of a row has no shared neighbour
+    // (t == 0, Jaccard distance exactly 1): its final value (1 - lambda) + lambda * sqrt(d2) is monotone in the
+    // squared distance the thread already holds, so the evaluation finishes it LAZILY -- only for the good items and
+    // for the entries whose d2 is below a bound derived from the worst good item (eval_row_in_registers).  Entries
+    // with shared neighbours are finished here, before the accumulator's shared memory becomes the scratch.
+    const float* arow = acc + col0 + tid;
+    const int kfull = ncols / JR_THREADS;  // iterations in which every thread has a column
+    uint32_t donemask = 0;
+#pragma unroll
+    for (int k = 0; k < JR_PF; ++k) {
+      if (k < kfull || tid + k * JR_THREADS < ncols) {
+        const float t = arow[k * JR_THREADS];
+        if (t != 0.f) {
+          pre[k] = jr_blend_value(jaccard_nonzero(t, 0), pre[k], one_m_l, lambda_value);
+          donemask |= 1u << k;
+        }
+      }
+    }
+    __syncthreads();  // the accumulator is dead: its shared memory becomes the evaluation scratch
+    auto finish = [&](float d2) { return jr_blend_value(1.0f, d2, one_m_l, lambda_value); };
+    // finish(d2) <= w  =>  lambda * sqrt(d2) <= w - (1 - lambda) + a few ulp of w; the slack below is 5 x that
+    auto raw_bound = [&](float w) {
+      const float sb = __fdiv_rn(__fadd_rn(__fsub_rn(w, one_m_l), __fmul_rn(fabsf(w), 1e-6f)), lambda_value);
+      if (!(sb >= 0.f)) return __int_as_float(0xff800000);  // -inf: no entry without shared neighbours can be that close
+      const float s1 = __fmul_rn(sb, 1.00001f);
+      return fmaxf(__fmul_rn(__fmul_rn(s1, s1), 1.0001f), 1.1e-12f);  // >= the 1e-12 clamp of negative d2
+    };
+    eval_row_in_registers<JR_THREADS, JR_PF>(pre, donemask, goodmask, finish, raw_bound, ncols, (int)blockIdx.x, 0, ev.ql, ev.qc,
+                                             ev.gl, ev.gc, ev.ap_q, ev.first, ev.hist, ev.status,
+                                             reinterpret_cast<EvalScratch*>(acc));
+    return;
+  } else {
 #pragma unroll
   for (int k = 0; k < JR_PF; ++k) {
     const int c = tid + k * JR_THREADS;
@@ -655,6 +696,7 @@ jaccard_rows_kernel(const int32_t* __restrict__ qcols, const float* __restrict__
       }
     }
   }
+  }
   for (int c = tid + JR_PF * JR_THREADS; c < ncols; c += JR_THREADS) {  // rows wider than JR_PF * JR_THREADS columns
     float jd = jaccard_value(acc[col0 + c], use_f16);
     if (blend) jd = __fadd_rn(__fmul_rn(jd, one_m_l), __fmul_rn(sqrtf(fmaxf(__ldcs(srow + c), 1e-12f)), lambda_value));
@@ -663,8 +705,9 @@ jaccard_rows_kernel(const int32_t* __restrict__ qcols, const float* __restrict__
   }
   if (ev.enabled) {  // host side guarantees ncols <= JR_PF * JR_THREADS, fp32 output, shared memory >= EvalScratch
     __syncthreads();  // the accumulator is dead: its shared memory becomes the evaluation scratch
-    eval_row_in_registers<JR_THREADS, JR_PF>(pre, ncols, (int)blockIdx.x, 0, ev.ql, ev.qc, ev.gl, ev.gc, ev.ap_q, ev.first,
-                                             ev.hist, ev.status, reinterpret_cast<EvalScratch*>(acc));
+    eval_row_in_registers<JR_THREADS, JR_PF>(pre, ~0u, goodmask, [](float v) { return v; }, [](float w) { return w; }, ncols,
+                                             (int)blockIdx.x, 0, ev.ql, ev.qc, ev.gl, ev.gc, ev.ap_q, ev.first, ev.hist, ev.status,
+                                             reinterpret_cast<EvalScratch*>(acc));
   }
 }
 
