@@ -145,6 +145,34 @@ __device__ __forceinline__ void eval_row_in_registers(float (&val)[PF], uint32_t
     ev_count_before(sc, ngood, ev_key(v, descending), j, descending, my_l, my_c, gl, gc);
   }
   __syncthreads();
+  if (ngood <= 32) {
+    // the usual case (a Market query has ~17 good items): prefix, AP terms and the ordered sum stay inside warp 0 --
+    // shuffles instead of two more block barriers and two serial loops through shared memory; same operations in
+    // the same order as the general path below
+    if (tid < 32) {
+      int pe = tid < ngood ? sc->gpos[tid] : 0;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {  // inclusive prefix: position of good s among the non-junk items
+        const int up = __shfl_up_sync(0xffffffffu, pe, o);
+        if (tid >= o) pe += up;
+      }
+      const double d_recall = 1.0 / (double)ngood;
+      double term = 0.0;
+      if (tid < ngood) {
+        const double precision = (double)(tid + 1) * 1.0 / (double)(pe + 1);
+        const double old_precision = pe != 0 ? (double)tid * 1.0 / (double)pe : 1.0;
+        term = d_recall * (old_precision + precision) / 2;
+      }
+      double ap = 0.0;
+      for (int t = 0; t < ngood; ++t) ap = ap + __shfl_sync(0xffffffffu, term, t);
+      if (tid == 0) {
+        ap_q[q] = ap;
+        first[q] = pe;
+        atomicAdd(hist + pe, 1);
+      }
+    }
+    return;
+  }
   if (tid == 0) {  // inclusive prefix: position of good s among the non-junk items
     int run = 0;
     for (int e = 0; e < ngood; ++e) { run += sc->gpos[e]; sc->gpos[e] = run; }

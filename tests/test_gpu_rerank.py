@@ -105,13 +105,14 @@ def test_jaccard_other_k_vs_oracle(rb, k1, k2):
     np.testing.assert_allclose(J, Jo, atol=5e-6)
 
 
+@pytest.mark.parametrize("n_ids", [35, 8])  # ~16 good items per query (warp-level AP tail) and ~70 (general tail)
 @pytest.mark.parametrize("lam", [0.3, 0.0])
-def test_fused_rerank_eval_equals_two_calls(rb, lam):
+def test_fused_rerank_eval_equals_two_calls(rb, lam, n_ids):
     """ops.rerank_eval (evaluation fused into the re-rank kernel) gives the CMC / mAP of jaccard + eval_cmc_map bit for
     bit, and the matrix it optionally writes is the one jaccard writes."""
     from reidb200 import ops, synth
 
-    d = synth.market_like(Q=130, G=700, D=64, n_ids=35, seed=31)
+    d = synth.market_like(Q=130, G=700, D=64, n_ids=n_ids, seed=31)
     d["gl"][::17] = -1                      # junk gallery rows
     d["ql"][5] = 10 ** 6                    # a query without any good match: the -1 sentinel path
     merged = torch.from_numpy(np.concatenate([d["gf"], d["qf"]], 0)).cuda()
