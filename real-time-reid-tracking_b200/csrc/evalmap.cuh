@@ -49,17 +49,55 @@ static __device__ __noinline__ void ev_count_before(EvalScratch* sc, int ngood, 
   atomicAdd(&sc->gpos[lo], 1);
 }
 
+// Which column of the row sits in register k of thread tid.  VEC == 1: column tid + k * NT (consecutive threads hold
+// consecutive columns).  VEC == 4: the thread holds groups of four consecutive columns, group g = k / 4 starting at
+// 4 * (tid + g * NT) -- the row, the labels and the accumulator are then read with 128-bit accesses.
+template <int NT, int VEC>
+__device__ __forceinline__ int ev_col(int tid, int k) {
+  return VEC == 1 ? tid + k * NT : VEC * (tid + (k / VEC) * NT) + (k % VEC);
+}
+
 // Label pass of the register-resident evaluation, separated so that the caller can run it EARLY (it needs the labels
 // only, not the row values: in the fused re-rank kernel it sits under the latency of the kernel's first global loads
 // instead of adding four dependent L2 round trips to the tail).  Bit k of the result = column tid + k * NT is a good
 // item of query q (same id, different camera: evaluate.py:66-70).
-template <int NT, int PF>
+template <int NT, int PF, int VEC = 1>
 __device__ __forceinline__ uint32_t eval_good_mask(int G, int q, const int32_t* __restrict__ ql, const int32_t* __restrict__ qc,
                                                    const int32_t* __restrict__ gl, const int32_t* __restrict__ gc) {
   static_assert(PF <= 32, "one mask bit per register value");
+  static_assert(VEC == 1 || (VEC == 4 && PF % 4 == 0), "VEC is 1 or 4");
   const int tid = threadIdx.x;
   const int32_t my_l = ql[q], my_c = qc[q];
   uint32_t mask = 0;
+  if (VEC == 4) {  // gl must be 16-byte aligned (the caller checks)
+    constexpr int GB = 2;  // groups per batch: the caller's row values already fill half of the register file
+#pragma unroll
+    for (int g0 = 0; g0 < PF / 4; g0 += GB) {
+      int4 lab[GB];
+#pragma unroll
+      for (int u = 0; u < GB; ++u) {
+        const int j0 = 4 * (tid + (g0 + u) * NT);
+        if (j0 + 3 < G) {
+          lab[u] = __ldg(reinterpret_cast<const int4*>(gl + j0));
+        } else {  // the group that straddles the end of the label vector
+          lab[u].x = j0 < G ? __ldg(gl + j0) : -2;
+          lab[u].y = j0 + 1 < G ? __ldg(gl + j0 + 1) : -2;
+          lab[u].z = j0 + 2 < G ? __ldg(gl + j0 + 2) : -2;
+          lab[u].w = -2;
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < GB; ++u) {
+        const int g = g0 + u;
+        const int j0 = 4 * (tid + g * NT);
+        if (lab[u].x == my_l && j0 < G && __ldg(gc + j0) != my_c) mask |= 1u << (4 * g);
+        if (lab[u].y == my_l && j0 + 1 < G && __ldg(gc + j0 + 1) != my_c) mask |= 1u << (4 * g + 1);
+        if (lab[u].z == my_l && j0 + 2 < G && __ldg(gc + j0 + 2) != my_c) mask |= 1u << (4 * g + 2);
+        if (lab[u].w == my_l && j0 + 3 < G && __ldg(gc + j0 + 3) != my_c) mask |= 1u << (4 * g + 3);
+      }
+    }
+    return mask;
+  }
 #pragma unroll
   for (int k0 = 0; k0 < PF; k0 += 8) {  // labels in batches of eight loads (the label vectors are L2 resident)
     int32_t lab[8];
@@ -77,7 +115,8 @@ __device__ __forceinline__ uint32_t eval_good_mask(int G, int q, const int32_t* 
   return mask;
 }
 
-// One query whose G row values live in registers: thread tid holds column tid + k * NT in val[k], k < PF (G <= NT * PF);
+// One query whose G row values live in registers: thread tid holds column ev_col<NT, VEC>(tid, k) in val[k], k < PF
+// (G <= NT * PF);
 // goodmask = eval_good_mask<NT, PF>() of the same query.
 // LAZY values: bit k of donemask says val[k] is the final ranking value; a clear bit says val[k] is still a RAW value
 // r with final = finish(r), finish monotone non-decreasing (distances, descending == 0 only).  Raw values are finished
@@ -87,7 +126,7 @@ __device__ __forceinline__ uint32_t eval_good_mask(int G, int q, const int32_t* 
 // Same two passes as eval_query_kernel: (1) good items = same id & other camera, rank-sorted; (2) every non-junk column
 // ranked before the worst good item bumps the histogram slot of the first good item it precedes.  All NT threads of
 // the CTA must call it (block barriers inside).  Writes ap_q[q], first[q], hist[first hit]; sets *status on overflow.
-template <int NT, int PF, class Finish, class RawBound>
+template <int NT, int PF, int VEC, class Finish, class RawBound>
 __device__ __forceinline__ void eval_row_in_registers(float (&val)[PF], uint32_t donemask, uint32_t goodmask, Finish finish,
                                                       RawBound raw_bound, int G, int q, int descending,
                                                       const int32_t* __restrict__ ql, const int32_t* __restrict__ qc,
@@ -104,7 +143,7 @@ __device__ __forceinline__ void eval_row_in_registers(float (&val)[PF], uint32_t
     for (int k = 0; k < PF; ++k)
       if ((goodmask >> k) & 1u) {
         if (!((donemask >> k) & 1u)) { val[k] = finish(val[k]); donemask |= 1u << k; }
-        ev_add_good(sc, tid + k * NT, ev_key(val[k], descending));
+        ev_add_good(sc, ev_col<NT, VEC>(tid, k), ev_key(val[k], descending));
       }
   }
   __syncthreads();
@@ -131,10 +170,10 @@ __device__ __forceinline__ void eval_row_in_registers(float (&val)[PF], uint32_t
   const uint32_t worst_o = descending ? ~worst_k : worst_k;
   const float worst_v = __uint_as_float((worst_o & 0x80000000u) ? (worst_o & 0x7fffffffu) : ~worst_o);
   const float raw_t = raw_bound(worst_v);
-  const int kfull = G / NT;  // iterations in which every thread has a column
+  const int kfull = (G / (NT * VEC)) * VEC;  // leading registers that hold a valid column in every thread
 #pragma unroll
   for (int k = 0; k < PF; ++k) {
-    const int j = tid + k * NT;
+    const int j = ev_col<NT, VEC>(tid, k);
     if (k >= kfull && j >= G) continue;
     float v = val[k];
     if (!((donemask >> k) & 1u)) {

@@ -592,7 +592,19 @@ jaccard_rows_kernel(const int32_t* __restrict__ qcols, const float* __restrict__
   const bool blend = lambda_value > 0.f;
   const float* srow = sql2 + (size_t)i * lds + col0;
   float pre[JR_PF];
-  if (blend) {
+  // fused-evaluation path (nothing stored, fp32, blended): the thread holds groups of FOUR consecutive columns, so the
+  // distance slice, the gallery labels and the accumulator are read with 128-bit accesses (ev_col<.., 4>)
+  const bool fast = ev.enabled && blend && !out && !use_f16 && (col0 & 3) == 0 && (lds & 3) == 0 &&
+                    ((reinterpret_cast<uintptr_t>(sql2) | reinterpret_cast<uintptr_t>(ev.gl)) & 15) == 0;
+  if (fast) {
+#pragma unroll
+    for (int g = 0; g < JR_PF / 4; ++g) {
+      const int c0 = 4 * (tid + g * JR_THREADS);
+      // a group that straddles ncols still lies inside the row's allocation (lds >= N rounded up to 32 columns)
+      const float4 v = c0 < ncols ? __ldcs(reinterpret_cast<const float4*>(srow + c0)) : make_float4(0.f, 0.f, 0.f, 0.f);
+      pre[4 * g] = v.x; pre[4 * g + 1] = v.y; pre[4 * g + 2] = v.z; pre[4 * g + 3] = v.w;
+    }
+  } else if (blend) {
 #pragma unroll
     for (int k = 0; k < JR_PF; ++k) {
       const int c = tid + k * JR_THREADS;
@@ -603,7 +615,9 @@ jaccard_rows_kernel(const int32_t* __restrict__ qcols, const float* __restrict__
   const int n = qcnt[i];
   // fused evaluation: which of this thread's columns are good items of the query (labels only -- done here, under the
   // latency of the loads above and below, the row values arrive at the end)
-  const uint32_t goodmask = ev.enabled ? eval_good_mask<JR_THREADS, JR_PF>(ncols, (int)blockIdx.x, ev.ql, ev.qc, ev.gl, ev.gc) : 0u;
+  const uint32_t goodmask = !ev.enabled ? 0u
+                            : fast ? eval_good_mask<JR_THREADS, JR_PF, 4>(ncols, (int)blockIdx.x, ev.ql, ev.qc, ev.gl, ev.gc)
+                                   : eval_good_mask<JR_THREADS, JR_PF, 1>(ncols, (int)blockIdx.x, ev.ql, ev.qc, ev.gl, ev.gc);
   for (int t = tid; t < n; t += JR_THREADS) {
     const float v = qvals[(size_t)i * cap + t];
     const int j = qcols[(size_t)i * cap + t];
@@ -650,22 +664,26 @@ jaccard_rows_kernel(const int32_t* __restrict__ qcols, const float* __restrict__
   const float one_m_l = 1.0f - lambda_value;
   float* orow = reinterpret_cast<float*>(out) + (size_t)blockIdx.x * ldo;
   __half* hrow = reinterpret_cast<__half*>(out) + (size_t)blockIdx.x * ldo;
-  if (ev.enabled && blend && !out && !use_f16) {
-    // The fused-evaluation path (nothing stored, fp32, blended).  Almost every entry of a row has no shared neighbour
-    // (t == 0, Jaccard distance exactly 1): its final value (1 - lambda) + lambda * sqrt(d2) is monotone in the
-    // squared distance the thread already holds, so the evaluation finishes it LAZILY -- only for the good items and
-    // for the entries whose d2 is below a bound derived from the worst good item (eval_row_in_registers).  Entries
-    // with shared neighbours are finished here, before the accumulator's shared memory becomes the scratch.
-    const float* arow = acc + col0 + tid;
-    const int kfull = ncols / JR_THREADS;  // iterations in which every thread has a column
+  if (fast) {
+    // Almost every entry of a row has no shared neighbour (t == 0, Jaccard distance exactly 1): its final value
+    // (1 - lambda) + lambda * sqrt(d2) is monotone in the squared distance the thread already holds, so the
+    // evaluation finishes it LAZILY -- only for the good items and for the entries whose d2 is below a bound derived
+    // from the worst good item (eval_row_in_registers).  Entries with shared neighbours are finished here, before the
+    // accumulator's shared memory becomes the scratch.
+    const float* arow = acc + col0;
     uint32_t donemask = 0;
 #pragma unroll
-    for (int k = 0; k < JR_PF; ++k) {
-      if (k < kfull || tid + k * JR_THREADS < ncols) {
-        const float t = arow[k * JR_THREADS];
-        if (t != 0.f) {
-          pre[k] = jr_blend_value(jaccard_nonzero(t, 0), pre[k], one_m_l, lambda_value);
-          donemask |= 1u << k;
+    for (int g = 0; g < JR_PF / 4; ++g) {
+      const int c0 = 4 * (tid + g * JR_THREADS);
+      if (c0 < ncols) {  // acc holds N rounded up to 4 entries: the straddling group stays in bounds
+        const float4 t4 = *reinterpret_cast<const float4*>(arow + c0);
+        const float tt[4] = {t4.x, t4.y, t4.z, t4.w};
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          if (tt[u] != 0.f && c0 + u < ncols) {
+            pre[4 * g + u] = jr_blend_value(jaccard_nonzero(tt[u], 0), pre[4 * g + u], one_m_l, lambda_value);
+            donemask |= 1u << (4 * g + u);
+          }
         }
       }
     }
@@ -678,7 +696,7 @@ jaccard_rows_kernel(const int32_t* __restrict__ qcols, const float* __restrict__
       const float s1 = __fmul_rn(sb, 1.00001f);
       return fmaxf(__fmul_rn(__fmul_rn(s1, s1), 1.0001f), 1.1e-12f);  // >= the 1e-12 clamp of negative d2
     };
-    eval_row_in_registers<JR_THREADS, JR_PF>(pre, donemask, goodmask, finish, raw_bound, ncols, (int)blockIdx.x, 0, ev.ql, ev.qc,
+    eval_row_in_registers<JR_THREADS, JR_PF, 4>(pre, donemask, goodmask, finish, raw_bound, ncols, (int)blockIdx.x, 0, ev.ql, ev.qc,
                                              ev.gl, ev.gc, ev.ap_q, ev.first, ev.hist, ev.status,
                                              reinterpret_cast<EvalScratch*>(acc));
     return;
@@ -705,7 +723,7 @@ jaccard_rows_kernel(const int32_t* __restrict__ qcols, const float* __restrict__
   }
   if (ev.enabled) {  // host side guarantees ncols <= JR_PF * JR_THREADS, fp32 output, shared memory >= EvalScratch
     __syncthreads();  // the accumulator is dead: its shared memory becomes the evaluation scratch
-    eval_row_in_registers<JR_THREADS, JR_PF>(pre, ~0u, goodmask, [](float v) { return v; }, [](float w) { return w; }, ncols,
+    eval_row_in_registers<JR_THREADS, JR_PF, 1>(pre, ~0u, goodmask, [](float v) { return v; }, [](float w) { return w; }, ncols,
                                              (int)blockIdx.x, 0, ev.ql, ev.qc, ev.gl, ev.gc, ev.ap_q, ev.first, ev.hist, ev.status,
                                              reinterpret_cast<EvalScratch*>(acc));
   }

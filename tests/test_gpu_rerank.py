@@ -112,11 +112,11 @@ def test_fused_rerank_eval_equals_two_calls(rb, lam, n_ids):
     bit, and the matrix it optionally writes is the one jaccard writes."""
     from reidb200 import ops, synth
 
-    d = synth.market_like(Q=130, G=700, D=64, n_ids=n_ids, seed=31)
+    G, Q = (700 if n_ids == 35 else 701), 130  # 701: the last group of four columns straddles the end of the row
+    d = synth.market_like(Q=Q, G=G, D=64, n_ids=n_ids, seed=31)
     d["gl"][::17] = -1                      # junk gallery rows
     d["ql"][5] = 10 ** 6                    # a query without any good match: the -1 sentinel path
     merged = torch.from_numpy(np.concatenate([d["gf"], d["qf"]], 0)).cuda()
-    G, Q = 700, 130
     lab = [torch.from_numpy(d[k].astype(np.int32)).cuda() for k in ("ql", "qc", "gl", "gc")]
     dist = ops.jaccard(merged, 20, 6, False, lam, rows=(G, Q), cols=(0, G))
     cmc2, ap2 = ops.eval_cmc_map(dist, *lab, descending=False)
