@@ -654,13 +654,14 @@ jaccard_rows_kernel(const int32_t* __restrict__ qcols, const float* __restrict__
     }
   }
   __syncthreads();
+  if (!fast)  // the fused path converts the few non-zero sums where it reads them
   for (int r = tid; r < N4 / 4; r += JR_THREADS) {  // fixed point -> fp32, in place
     const uint4 a4 = reinterpret_cast<const uint4*>(acci)[r];
     if ((a4.x | a4.y | a4.z | a4.w) != 0u)
       reinterpret_cast<float4*>(acc)[r] = make_float4(__fmul_rn(__uint2float_rn(a4.x), JR_UNFIX), __fmul_rn(__uint2float_rn(a4.y), JR_UNFIX),
                                                       __fmul_rn(__uint2float_rn(a4.z), JR_UNFIX), __fmul_rn(__uint2float_rn(a4.w), JR_UNFIX));
   }
-  __syncthreads();
+  if (!fast) __syncthreads();  // `fast` is uniform over the CTA
   const float one_m_l = 1.0f - lambda_value;
   float* orow = reinterpret_cast<float*>(out) + (size_t)blockIdx.x * ldo;
   __half* hrow = reinterpret_cast<__half*>(out) + (size_t)blockIdx.x * ldo;
@@ -670,18 +671,19 @@ jaccard_rows_kernel(const int32_t* __restrict__ qcols, const float* __restrict__
     // evaluation finishes it LAZILY -- only for the good items and for the entries whose d2 is below a bound derived
     // from the worst good item (eval_row_in_registers).  Entries with shared neighbours are finished here, before the
     // accumulator's shared memory becomes the scratch.
-    const float* arow = acc + col0;
+    const unsigned int* arow = acci + col0;
     uint32_t donemask = 0;
 #pragma unroll
     for (int g = 0; g < JR_PF / 4; ++g) {
       const int c0 = 4 * (tid + g * JR_THREADS);
       if (c0 < ncols) {  // acc holds N rounded up to 4 entries: the straddling group stays in bounds
-        const float4 t4 = *reinterpret_cast<const float4*>(arow + c0);
-        const float tt[4] = {t4.x, t4.y, t4.z, t4.w};
+        const uint4 a4 = *reinterpret_cast<const uint4*>(arow + c0);  // still 2.30 fixed point (no conversion pass here)
+        const unsigned int aa[4] = {a4.x, a4.y, a4.z, a4.w};
 #pragma unroll
         for (int u = 0; u < 4; ++u) {
-          if (tt[u] != 0.f && c0 + u < ncols) {
-            pre[4 * g + u] = jr_blend_value(jaccard_nonzero(tt[u], 0), pre[4 * g + u], one_m_l, lambda_value);
+          if (aa[u] != 0u && c0 + u < ncols) {
+            const float t = __fmul_rn(__uint2float_rn(aa[u]), JR_UNFIX);
+            pre[4 * g + u] = jr_blend_value(jaccard_nonzero(t, 0), pre[4 * g + u], one_m_l, lambda_value);
             donemask |= 1u << (4 * g + u);
           }
         }
