@@ -184,6 +184,10 @@ typedef struct reidb200_gallery reidb200_gallery;
 
 int reidb200_gallery_create(int slots, int budget, int d, reidb200_gallery** out);
 int reidb200_gallery_destroy(reidb200_gallery* g);
+/* Grow a gallery (more slots and / or a longer ring per slot; never shrinks), contents preserved bit for bit: the
+ * reference's sample store is unbounded (budget=None keeps every sample, any number of targets, matching.py:363-389).
+ * Synchronises `stream`. */
+int reidb200_gallery_resize(reidb200_gallery* g, int new_slots, int new_budget, void* stream);
 /* Append n feature rows f32[n,d]; row i goes to slot slot_of_row[i] (i32[n], device).  Rows for one
  * slot are appended in row order; only the last `budget` survive (matching.py:385-386). */
 int reidb200_gallery_partial_fit(reidb200_gallery* g, const float* feats, int64_t ldf,
@@ -242,6 +246,12 @@ int reidb200_rerank_eval(const float* feats, int G, int Q, int64_t ldf, int d, i
                          const int32_t* ql, const int32_t* qc, const int32_t* gl, const int32_t* gc,
                          float* out_dist, int64_t ldo, float* out_cmc, double* out_ap, void* workspace,
                          size_t workspace_bytes, void* stream);
+/* Same, also returning what reid/evaluate.py:55-75 evaluate() returns per query: out_ap_q f64[Q] (0 for a skipped query)
+ * and out_first i32[Q] (first-hit rank in the junk-free ranking, -1 = the cmc[0] == -1 sentinel); either may be NULL. */
+int reidb200_rerank_eval_pq(const float* feats, int G, int Q, int64_t ldf, int d, int k1, int k2, float lambda_value,
+                            const int32_t* ql, const int32_t* qc, const int32_t* gl, const int32_t* gc,
+                            float* out_dist, int64_t ldo, float* out_cmc, double* out_ap, double* out_ap_q,
+                            int32_t* out_first, void* workspace, size_t workspace_bytes, void* stream);
 
 /* ------------------------------------------------------------------------------------------
  * N2: pairwise box costs of the other boxmot trackers.

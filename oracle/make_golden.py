@@ -55,12 +55,49 @@ def gold_dist():
 
 
 # ---------------------------------------------------------------- B3-B6 evaluation
+def ranked_eval(E, dist, ql, qc, gl, gc):
+    """Reference compute_mAP (reid/evaluate.py:78-105) over every row of a DISTANCE matrix (ascending, stable argsort)
+    with the reference's good / junk rule (:66-72).  Returns (CMC f32[G] / Q, mAP, per-query AP, first-hit rank (-1 = no
+    valid match), margin) -- margin[i] = smallest relative gap between a good item and a non-good neighbour in query i's
+    junk-free ranking: where it is below the distance tolerance, a swap of the two is a tie, not an error."""
+    nq, ng = dist.shape
+    CMC = torch.IntTensor(ng).zero_()
+    ap_sum = 0.0
+    aps = np.zeros(nq)
+    first = np.full(nq, -1, np.int32)
+    margin = np.full(nq, np.inf)
+    for i in range(nq):
+        index = np.argsort(dist[i], kind="stable")
+        query_index = np.argwhere(gl == ql[i])
+        camera_index = np.argwhere(gc == qc[i])
+        good_index = np.setdiff1d(query_index, camera_index, assume_unique=True)
+        junk_index1 = np.argwhere(gl == -1)
+        junk_index2 = np.intersect1d(query_index, camera_index)
+        junk_index = np.append(junk_index2, junk_index1)
+        ap, cmc = E.compute_mAP(index, good_index, junk_index)
+        if cmc[0] == -1:
+            continue
+        CMC = CMC + cmc
+        ap_sum += ap
+        aps[i] = ap
+        first[i] = int(np.argmax(cmc.numpy()))
+        keep = index[np.isin(index, junk_index, invert=True)]
+        dv = dist[i][keep].astype(np.float64)
+        isg = np.isin(keep, good_index)
+        edge = isg[1:] != isg[:-1]
+        if edge.any():
+            margin[i] = ((dv[1:] - dv[:-1])[edge] / np.maximum(np.abs(dv[1:][edge]), 1e-12)).min()
+    return (CMC.float() / nq).numpy(), ap_sum / nq, aps, first, margin
+
+
 def gold_eval():
+    """HARD synthetic data (synth.hard_noise): first hits spread over many ranks, CMC is a curve, APs take many values --
+    a kernel that mis-ranks anything but the top item fails against this fixture."""
     E = ref_import.load_file("ref_evaluate", "reid/evaluate.py")
     sys.path.insert(0, os.path.join(ROOT, "real-time-reid-tracking_b200"))
     import synth  # noqa
 
-    d = synth.market_like(Q=60, G=500, D=32, n_ids=40, seed=3, orphan_frac=0.05)
+    d = synth.market_like(Q=90, G=600, D=32, n_ids=150, seed=3, orphan_frac=0.05, noise=1.2)
     t = {k: torch.from_numpy(v) for k, v in d.items()}
     import contextlib, io
     with contextlib.redirect_stdout(io.StringIO()):
@@ -76,7 +113,44 @@ def gold_eval():
         c = c.numpy()
         aps.append(float(a))
         first.append(-1 if c[0] == -1 else int(np.argmax(c)))
-    _save("eval", **d, cmc=cmc, ap=np.float64(ap), ap_per_query=np.array(aps), first_hit=np.array(first, np.int32))
+    first = np.array(first, np.int32)
+    assert first.max() >= 5 and len(np.unique(first)) >= 5 and (first < 0).any(), "fixture too easy: %s" % np.bincount(first[first >= 0])
+    assert len(np.unique(np.round(aps, 9))) > 40 and cmc[0] < 0.9 < cmc[-1]
+    print("  eval: rank-1 %.4f rank-5 %.4f mAP %.4f, first hits up to rank %d" % (cmc[0], cmc[4], ap, first.max()))
+    _save("eval", **d, cmc=cmc, ap=np.float64(ap), ap_per_query=np.array(aps), first_hit=first)
+
+
+def gold_rerank_eval():
+    """Re-ranked evaluation at a size the GPU tests compare entry by entry: the reference's compute_jaccard_distance on
+    merged = cat(gallery, query) (image_reid_inference.py:270), blended with the reference's euclidean_dist (the blend
+    itself is the north_star addition), ranked and reduced by the reference's compute_mAP."""
+    E = ref_import.load_file("ref_evaluate", "reid/evaluate.py")
+    F = ref_import.load_file("ref_faiss_utils", "reid/faiss_utils.py")
+    U = ref_import.load_file("ref_losses_utils", "reid/losses/utils.py")
+    sys.path.insert(0, os.path.join(ROOT, "real-time-reid-tracking_b200"))
+    import synth  # noqa
+
+    Q, G, lam = 160, 900, 0.3
+    d = synth.market_like(Q=Q, G=G, D=64, n_ids=150, seed=8, orphan_frac=0.04, noise=1.4)
+    t = {k: torch.from_numpy(v) for k, v in d.items()}
+    merged = torch.cat([t["gf"], t["qf"]], 0)
+    out = dict(d)
+    for tag, k1, k2 in (("k20_6", 20, 6), ("k12_3", 12, 3)):
+        J = F.compute_jaccard_distance(merged, k1=k1, k2=k2, print_flag=False, search_option=3)
+        Jo = O.compute_jaccard_distance(merged.numpy(), k1, k2)
+        np.testing.assert_allclose(Jo, J, rtol=0, atol=2e-6)
+        orig = U.euclidean_dist(t["qf"], t["gf"]).numpy()
+        dist = (J[G:, :G] * np.float32(1.0 - lam) + orig * np.float32(lam)).astype(np.float32)
+        np.testing.assert_allclose(O.re_ranking_from_feats(d["qf"], d["gf"], k1, k2, lam), dist, rtol=0, atol=2e-6)
+        cmc, mAP, aps, first, margin = ranked_eval(E, dist, d["ql"], d["qc"], d["gl"], d["gc"])
+        ocmc, oap = O.evaluate_all_from_dist(dist, d["ql"], d["qc"], d["gl"], d["gc"])
+        assert np.array_equal(ocmc, cmc) and abs(oap - mAP) < 1e-12
+        assert first.max() >= 3 and cmc[0] < 0.995, "re-ranked fixture too easy"
+        print("  rerank_eval %s: rank-1 %.4f mAP %.4f, first hits up to rank %d, %d queries with margin < 1e-5"
+              % (tag, cmc[0], mAP, first.max(), (margin < 1e-5).sum()))
+        out.update({"dist_" + tag: dist, "cmc_" + tag: cmc, "map_" + tag: np.float64(mAP), "ap_q_" + tag: aps,
+                    "first_" + tag: first, "margin_" + tag: margin})
+    _save("rerank_eval", lambda_value=np.float64(lam), **out)
 
 
 # ---------------------------------------------------------------- D1-D7 Jaccard re-ranking
@@ -480,7 +554,7 @@ def gold_posttricks():
 def main():
     assert ref_import.available(), "/root/reference not present: fixtures can only be (re)generated in the build container"
     ref_import.install()
-    for fn in (gold_dist, gold_eval, gold_jaccard, gold_preprocess, gold_assoc, gold_boxpairs, gold_ocsort, gold_kalman, gold_posttricks):
+    for fn in (gold_dist, gold_eval, gold_rerank_eval, gold_jaccard, gold_preprocess, gold_assoc, gold_boxpairs, gold_ocsort, gold_kalman, gold_posttricks):
         print(fn.__name__)
         fn()
     print("oracle pinned against the reference; fixtures in tests/golden/")

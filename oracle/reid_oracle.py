@@ -273,6 +273,25 @@ def evaluate_all_from_dist(dist, ql, qc, gl, gc):
     return CMC.astype(np.float32) / np.float32(Q), ap / Q
 
 
+def evaluate_per_query_from_dist(dist, ql, qc, gl, gc):
+    """Per-query (AP f64[Q], first-hit rank i32[Q] with -1 = the cmc[0] == -1 sentinel) of a DISTANCE matrix: what
+    reid/evaluate.py:55-75 evaluate() returns for each query, on the ranking evaluate_all_from_dist uses."""
+    Q = dist.shape[0]
+    gl = np.asarray(gl)
+    gc = np.asarray(gc)
+    aps = np.zeros(Q)
+    first = np.full(Q, -1, np.int32)
+    for i in range(Q):
+        index = np.argsort(dist[i], kind="stable")
+        good, junk = _good_junk(ql[i], qc[i], gl, gc)
+        ap_i, cmc_i = compute_mAP(index, good, junk)
+        if cmc_i[0] == -1:
+            continue
+        aps[i] = ap_i
+        first[i] = int(np.argmax(cmc_i))
+    return aps, first
+
+
 # --------------------------------------------------------------------------
 # A1/A2  crop + cv2-style bilinear resize + normalise
 # (modification_deepsort/feature_extractor.py:24-46; strong_sort.py:115-121,149-159)

@@ -13,7 +13,7 @@ import torch
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libreidb200.so")
-ABI_VERSION = 2
+ABI_VERSION = 3
 
 OK, EINVAL, ECUDA, ELIMIT = 0, -1, -2, -3
 RESIZE_CV_LINEAR, RESIZE_PIL_ANTIALIAS = 0, 1
@@ -55,6 +55,7 @@ SIGNATURES = {
     "reidb200_k_reciprocal": (_i, [_vp, _i, _i, _i, _vp, _vp, _vp]),
     "reidb200_gallery_create": (_i, [_i, _i, _i, C.POINTER(_vp)]),
     "reidb200_gallery_destroy": (_i, [_vp]),
+    "reidb200_gallery_resize": (_i, [_vp, _i, _i, _vp]),
     "reidb200_gallery_partial_fit": (_i, [_vp, _vp, _i64, _vp, _i, _vp]),
     "reidb200_gallery_reset_slots": (_i, [_vp, _vp, _i, _vp]),
     "reidb200_gallery_counts": (_i, [_vp, _vp, _vp]),
@@ -66,6 +67,7 @@ SIGNATURES = {
     "reidb200_cosine_distance": (_i, [_vp, _i, _i64, _vp, _i, _i64, _i, _i, _vp, _vp, _sz, _vp]),
     "reidb200_rerank_eval_workspace_bytes": (_sz, [_i, _i, _i, _i, _i, _i]),
     "reidb200_rerank_eval": (_i, [_vp, _i, _i, _i64, _i, _i, _i, _f, _vp, _vp, _vp, _vp, _vp, _i64, _vp, _vp, _vp, _sz, _vp]),
+    "reidb200_rerank_eval_pq": (_i, [_vp, _i, _i, _i64, _i, _i, _i, _f, _vp, _vp, _vp, _vp, _vp, _i64, _vp, _vp, _vp, _vp, _vp, _sz, _vp]),
     "reidb200_box_pairs": (_i, [_vp, _i, _vp, _i, _i, _i, _vp, _vp]),
     "reidb200_fuse_cost": (_i, [_vp, _i, _i, _i, _vp, _vp, _vp, _vp, _vp]),
     "reidb200_ocsort_cost": (_i, [_vp, _i, _vp, _i, _vp, _vp, _d, _vp, _vp, _vp]),

@@ -127,6 +127,23 @@ __global__ void gal_read_kernel(const float* __restrict__ gal, const int32_t* __
   }
 }
 
+// copy of one gallery into a larger one (more slots and / or a longer ring): the rows of every slot move, oldest first,
+// to ring positions 0..count-1 of the new layout (head = count mod new budget), bit for bit
+__global__ void gal_resize_kernel(const float* __restrict__ src, const __half* __restrict__ src_packed,
+                                  const int32_t* __restrict__ src_head, const int32_t* __restrict__ src_count, int old_budget,
+                                  int new_budget, int d, int dp, float* __restrict__ dst, __half* __restrict__ dst_packed,
+                                  int32_t* __restrict__ dst_head, int32_t* __restrict__ dst_count) {
+  const int slot = blockIdx.x;
+  const int c = src_count[slot], h = src_head[slot];
+  for (int r = blockIdx.y; r < c; r += gridDim.y) {
+    const size_t from = (size_t)slot * old_budget + ((h - c + r) % old_budget + old_budget) % old_budget;
+    const size_t to = (size_t)slot * new_budget + r;
+    for (int k = threadIdx.x; k < d; k += blockDim.x) dst[to * d + k] = src[from * d + k];
+    for (int k = threadIdx.x; k < 2 * dp; k += blockDim.x) dst_packed[to * 2 * dp + k] = src_packed[from * 2 * dp + k];
+  }
+  if (blockIdx.y == 0 && threadIdx.x == 0) { dst_count[slot] = c; dst_head[slot] = c % new_budget; }
+}
+
 // ------------------------------------------------------------------------------------ box / gate math
 // Detection.to_xyah in float32 (sort/detection.py:42-50), promoted to double by z - Hx
 __device__ __forceinline__ void tlwh_to_xyah_f32(const float* t, double z[4]) {
@@ -594,6 +611,38 @@ extern "C" int reidb200_gallery_create(int slots, int budget, int d, reidb200_ga
   return REIDB200_OK;
 }
 
+// Grow a gallery in place (the handle stays valid): more slots and / or a longer ring per slot, contents preserved bit
+// for bit (NearestNeighborDistanceMetric is unbounded in the reference: budget=None keeps every sample and any number of
+// targets, boxmot/utils/matching.py:363-389).  Synchronises `stream`; not capturable in a CUDA graph.
+extern "C" int reidb200_gallery_resize(reidb200_gallery* g, int new_slots, int new_budget, void* stream) {
+  RB_REQUIRE(g && new_slots >= g->slots && new_budget >= g->budget, "gallery_resize: a gallery can only grow");
+  if (new_slots == g->slots && new_budget == g->budget) return REIDB200_OK;
+  cudaStream_t st = (cudaStream_t)stream;
+  float* feats = nullptr; __half* packed = nullptr; int32_t *count = nullptr, *head = nullptr, *scratch = nullptr;
+  const size_t packed_sz = (size_t)new_slots * new_budget * 2 * g->dp * sizeof(__half);
+  const int scratch_rows = new_slots > 1024 ? new_slots : 1024;
+  cudaError_t e = cudaMalloc(&feats, (size_t)new_slots * new_budget * g->d * sizeof(float));
+  if (e == cudaSuccess) e = cudaMalloc(&packed, packed_sz);
+  if (e == cudaSuccess) e = cudaMemsetAsync(packed, 0, packed_sz, st);
+  if (e == cudaSuccess) e = cudaMalloc(&count, (size_t)new_slots * sizeof(int32_t));
+  if (e == cudaSuccess) e = cudaMalloc(&head, (size_t)new_slots * sizeof(int32_t));
+  if (e == cudaSuccess) e = cudaMalloc(&scratch, (size_t)2 * scratch_rows * sizeof(int32_t));
+  if (e == cudaSuccess) e = cudaMemsetAsync(count, 0, (size_t)new_slots * sizeof(int32_t), st);
+  if (e == cudaSuccess) e = cudaMemsetAsync(head, 0, (size_t)new_slots * sizeof(int32_t), st);
+  if (e != cudaSuccess) {
+    cudaFree(feats); cudaFree(packed); cudaFree(count); cudaFree(head); cudaFree(scratch);
+    return cuda_fail(e, "gallery_resize", __FILE__, __LINE__);
+  }
+  gal_resize_kernel<<<dim3(g->slots, g->budget < 16 ? g->budget : 16), 128, 0, st>>>(g->feats, g->packed, g->head, g->count, g->budget,
+                                                                                  new_budget, g->d, g->dp, feats, packed, head, count);
+  RB_LAUNCH_CHECK("gal_resize_kernel");
+  RB_CUDA(cudaStreamSynchronize(st));
+  cudaFree(g->feats); cudaFree(g->packed); cudaFree(g->count); cudaFree(g->head); cudaFree(g->scratch);
+  g->feats = feats; g->packed = packed; g->count = count; g->head = head; g->scratch = scratch;
+  g->slots = new_slots; g->budget = new_budget; g->scratch_rows = scratch_rows;
+  return make_operand_map(&g->tm_gallery, g->packed, new_slots * new_budget, g->dp, AT_BM);
+}
+
 extern "C" int reidb200_gallery_destroy(reidb200_gallery* g) {
   if (!g) return REIDB200_OK;
   cudaFree(g->feats); cudaFree(g->packed); cudaFree(g->det_packed); cudaFree(g->count); cudaFree(g->head); cudaFree(g->scratch);
@@ -681,10 +730,9 @@ extern "C" int reidb200_assoc_frame(reidb200_gallery* g, const float* det_feat, 
   CUtensorMap tmF;
   int rc = make_operand_map(&tmF, g->det_packed, M, g->dp, bn_box);
   if (rc) return rc;
-  static bool attr_done = false;
-  if (!attr_done) {
+  static DeviceOnce attr_done;
+  if (attr_done.pending()) {
     RB_CUDA(cudaFuncSetAttribute(assoc_frame_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)AT_SMEM));
-    attr_done = true;
   }
   const int n_dtiles = ceil_div(M, AT_BN);
   const long long total = (long long)T * n_dtiles;

@@ -330,10 +330,9 @@ extern "C" int reidb200_dbscan_precomputed(const float* dist, int N, size_t ld, 
   }
   RB_LAUNCH_CHECK("dbscan_link_kernel");
   {
-    static bool attr = false;
-    if (!attr) {
+    static DeviceOnce attr;
+    if (attr.pending()) {
       RB_CUDA(cudaFuncSetAttribute(dbscan_number_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448 - 256));
-      attr = true;
     }
     ProfScope _ps("dbscan_number_kernel", st);
     dbscan_number_kernel<<<1, 1024, (size_t)N * 4, st>>>(N, core, parent, flags, labels, n_clusters);

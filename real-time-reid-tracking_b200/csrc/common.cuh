@@ -44,6 +44,19 @@ inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
 
 int num_sms();
 
+// cudaFuncSetAttribute (dynamic shared memory opt-in) is a PER-DEVICE setting: one flag per (call site, device), so a
+// process that touches a second GPU (faiss_utils.index_init_gpu(ngpus > 1)) opts in there too.
+struct DeviceOnce {
+  bool done[64] = {};
+  bool pending() {
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return true;
+    if (done[dev]) return false;
+    done[dev] = true;
+    return true;
+  }
+};
+
 // RAII span: when profiling is enabled (reidb200_profile_enable) records a CUDA event pair on `st` around a launch.
 class ProfScope {
  public:

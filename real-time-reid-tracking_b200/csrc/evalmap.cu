@@ -177,10 +177,9 @@ eval_finalize_kernel(const int32_t* __restrict__ hist, const double* __restrict_
 
 int eval_finalize_launch(const int32_t* hist, const double* ap_q, int Q, int G, float* out_cmc, double* out_ap,
                          cudaStream_t st) {
-  static bool attr = false;
-  if (!attr) {
+  static DeviceOnce attr;
+  if (attr.pending()) {
     RB_CUDA(cudaFuncSetAttribute(eval_finalize_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-    attr = true;
   }
   RB_REQUIRE((size_t)(G + 1) * sizeof(int) <= 200 * 1024, "eval_cmc_map: gallery larger than this build's limit (G=%d <= 51199)", G);
   { ProfScope _ps("eval_finalize_kernel", st); eval_finalize_kernel<<<1, 1024, (size_t)(G + 1) * sizeof(int), st>>>(hist, ap_q, Q, G, out_cmc, out_ap); }

@@ -710,11 +710,10 @@ int gemm_split_launch(const void* packedA, const float* xx, const float* isa, in
     case REIDB200_DIST_DOT: k1 = gemm_split_tc_kernel<REIDB200_DIST_DOT>; k2 = gemm_split_tc2_kernel<REIDB200_DIST_DOT>; break;
     default: k1 = gemm_split_tc_kernel<REIDB200_DIST_SQL2>; k2 = gemm_split_tc2_kernel<REIDB200_DIST_SQL2>; break;
   }
-  static bool attr_done[2][4] = {{false, false, false, false}, {false, false, false, false}};
-  if (!attr_done[pair ? 1 : 0][kind]) {
+  static DeviceOnce attr_done[2][4];
+  if (attr_done[pair ? 1 : 0][kind].pending()) {
     RB_CUDA(cudaFuncSetAttribute(pair ? (const void*)k2 : (const void*)k1, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  (int)(pair ? GEMM2_SMEM : GEMM_SMEM)));
-    attr_done[pair ? 1 : 0][kind] = true;
   }
   if (pair) {
     const long long tm2 = (a.tiles_m + 1) / 2;

@@ -333,11 +333,10 @@ extern "C" int reidb200_lap_gated(const double* cost, int T, int M, size_t ld, c
   w.path = (int32_t*)take(n * 4); w.a4b = (int32_t*)take(n * 4); w.b4a = (int32_t*)take(n * 4);
   w.SR = (int32_t*)take(n * 4); w.SC = (int32_t*)take(n * 4);
   const size_t smem = ((size_t)3 * (nrc + M) + (size_t)(nrc > M ? nrc : M)) * sizeof(int);
-  static bool attr = false;
-  if (!attr) {
+  static DeviceOnce attr;
+  if (attr.pending()) {
     RB_CUDA(cudaFuncSetAttribute(lap_components_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  (int)(((size_t)3 * 2 * LAP_MAX_SIDE + LAP_MAX_SIDE) * sizeof(int))));
-    attr = true;
   }
   static const int debug_stop = getenv("REIDB200_LAP_DEBUG") ? atoi(getenv("REIDB200_LAP_DEBUG")) : 0;  // timing experiments only
   {

@@ -799,13 +799,12 @@ static int jaccard_sparse_stages(const int32_t* rank, const float* sql2, int64_t
                                  int k2, int use_f16, float lambda_value, int row0, int nrows, int col0, int ncols,
                                  void* out, int64_t ldo, const RerankDims& d, const SparseWs& w, cudaStream_t st,
                                  const EvalFuse* ev = nullptr) {
-  static bool attr = false;
-  if (!attr) {
+  static DeviceOnce attr;
+  if (attr.pending()) {
     RB_CUDA(cudaFuncSetAttribute(expand_v_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 4096 * 12));
     RB_CUDA(cudaFuncSetAttribute(qexpand_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 8192 * 12));
     RB_CUDA(cudaFuncSetAttribute(inv_scan_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448 - 256));
     RB_CUDA(cudaFuncSetAttribute(jaccard_rows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448 - 256));
-    attr = true;
   }
   const int wpb = 8;
   { ProfScope _ps("krecip_kernel", st); krecip_both_kernel<<<ceil_div(N, wpb), wpb * 32, 0, st>>>(rank, N, k1, k1, d.wh, w.rfull, w.rfull_cnt, w.rhalf, w.rhalf_cnt); }
@@ -961,10 +960,10 @@ extern "C" size_t reidb200_rerank_eval_workspace_bytes(int N, int d, int k1, int
   return align_up(c.off, 256);
 }
 
-extern "C" int reidb200_rerank_eval(const float* feats, int G, int Q, int64_t ldf, int d, int k1, int k2, float lambda_value,
-                                    const int32_t* ql, const int32_t* qc, const int32_t* gl, const int32_t* gc,
-                                    float* out_dist, int64_t ldo, float* out_cmc, double* out_ap, void* workspace,
-                                    size_t workspace_bytes, void* stream) {
+static int rerank_eval_impl(const float* feats, int G, int Q, int64_t ldf, int d, int k1, int k2, float lambda_value,
+                            const int32_t* ql, const int32_t* qc, const int32_t* gl, const int32_t* gc,
+                            float* out_dist, int64_t ldo, float* out_cmc, double* out_ap, double* out_ap_q,
+                            int32_t* out_first, void* workspace, size_t workspace_bytes, void* stream) {
   RB_REQUIRE(feats && ql && qc && gl && gc && out_cmc && out_ap && G > 0 && Q > 0 && d > 0 && ldf >= d,
              "rerank_eval: bad argument");
   RB_REQUIRE(G <= JR_PF * JR_THREADS, "rerank_eval: the fused evaluation holds at most %d gallery columns per query row (G=%d); "
@@ -987,6 +986,8 @@ extern "C" int reidb200_rerank_eval(const float* feats, int G, int Q, int64_t ld
   ev.first = c0.take<int32_t>(Q);
   ev.status = c0.take<int32_t>(64);
   ev.enabled = 1;
+  if (out_ap_q) ev.ap_q = out_ap_q;
+  if (out_first) ev.first = out_first;
   RB_CUDA(cudaMemsetAsync(ev.hist, 0, (size_t)G * sizeof(int32_t), st));
   RB_CUDA(cudaMemsetAsync(ev.status, 0, 64 * sizeof(int32_t), st));
   Carver c(jws, jbytes);
@@ -1009,4 +1010,20 @@ extern "C" int reidb200_rerank_eval(const float* feats, int G, int Q, int64_t ld
   rc = jaccard_sparse_stages(rank_i, sql2, rd.lds, sqn, N, k1, k2, 0, lambda_value, G, Q, 0, G, out_dist, ldo, rd, w, st, &ev);
   if (rc) return rc;
   return eval_finalize_launch(ev.hist, ev.ap_q, Q, G, out_cmc, out_ap, st);
+}
+
+extern "C" int reidb200_rerank_eval(const float* feats, int G, int Q, int64_t ldf, int d, int k1, int k2, float lambda_value,
+                                    const int32_t* ql, const int32_t* qc, const int32_t* gl, const int32_t* gc,
+                                    float* out_dist, int64_t ldo, float* out_cmc, double* out_ap, void* workspace,
+                                    size_t workspace_bytes, void* stream) {
+  return rerank_eval_impl(feats, G, Q, ldf, d, k1, k2, lambda_value, ql, qc, gl, gc, out_dist, ldo, out_cmc, out_ap, nullptr,
+                          nullptr, workspace, workspace_bytes, stream);
+}
+
+extern "C" int reidb200_rerank_eval_pq(const float* feats, int G, int Q, int64_t ldf, int d, int k1, int k2, float lambda_value,
+                                       const int32_t* ql, const int32_t* qc, const int32_t* gl, const int32_t* gc,
+                                       float* out_dist, int64_t ldo, float* out_cmc, double* out_ap, double* out_ap_q,
+                                       int32_t* out_first, void* workspace, size_t workspace_bytes, void* stream) {
+  return rerank_eval_impl(feats, G, Q, ldf, d, k1, k2, lambda_value, ql, qc, gl, gc, out_dist, ldo, out_cmc, out_ap, out_ap_q,
+                          out_first, workspace, workspace_bytes, stream);
 }

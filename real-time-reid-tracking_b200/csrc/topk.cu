@@ -365,10 +365,9 @@ int topk_rows_launch(const float* vals, int rows, int cols, int64_t ldv, const i
   RB_REQUIRE(k > 0 && k <= TOPK_MAX_K, "topk: k=%d outside [1,%d]", k, TOPK_MAX_K);
   RB_REQUIRE(cols >= 0 && ldv >= cols, "topk: bad cols/ld");
   const int nchunks = (cols + 31) / 32;
-  static bool attr = false;
-  if (!attr) {
+  static DeviceOnce attr;
+  if (attr.pending()) {
     RB_CUDA(cudaFuncSetAttribute(topk_rows_kernel<1, 512>, cudaFuncAttributeMaxDynamicSharedMemorySize, TOPK_SMEM_ROW_MAX * 4));
-    attr = true;
   }
   if (chunk_red != nullptr && cand_i == nullptr && nchunks >= 4 * k && nchunks >= 64 && k <= 128) {
     // groups = 32*S >= 2k lane-local minima (S = 2, 4 or 8)

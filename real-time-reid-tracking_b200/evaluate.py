@@ -20,6 +20,14 @@ def _labels(x):
     return torch.from_numpy(np.ascontiguousarray(np.asarray(x))).reshape(-1)
 
 
+def _check_ap(ap, what):
+    """The counting kernels hold at most EV_GOOD_CAP = 1024 good matches per query (csrc/evalmap.cuh); a query with more
+    poisons the AP sum with NaN (and sets the device status word).  Every host-returning entry point turns that into an error."""
+    if ap != ap:
+        raise L.Reidb200Error("%s: a query has more good gallery matches than this build holds (1024)" % what)
+    return ap
+
+
 def evaluate_all_device(qf, ql, qc, gf, gl, gc):
     """Device-resident variant: returns (CMC f32[G], mAP f64[1]) CUDA tensors, no host sync."""
     qf = L.as_f32_cuda(qf)
@@ -34,9 +42,7 @@ def evaluate_all(qf, ql, qc, gf, gl, gc):
     """(CMC FloatTensor[G] averaged over ALL Q queries, mAP float); prints Rank@1/5/10 + mAP like the reference."""
     cmc, ap = evaluate_all_device(qf, ql, qc, gf, gl, gc)
     CMC = cmc.cpu()
-    ap = float(ap.cpu()[0])
-    if ap != ap:
-        raise L.Reidb200Error("evaluate_all: a query has more good matches than this build holds (2048)")
+    ap = _check_ap(float(ap.cpu()[0]), "evaluate_all")
     r = lambda k: float(CMC[k]) if CMC.numel() > k else float("nan")
     print('Rank@1:%f Rank@5:%f Rank@10:%f mAP:%f' % (r(0), r(4), r(9), ap))
     return CMC, ap
@@ -48,9 +54,7 @@ def evaluate_all_sharded(qf, ql, qc, gf, gl, gc, group=None, verbose=True):
     from . import shard
 
     cmc, ap = shard.evaluate_all_sharded(qf, ql, qc, gf, gl, gc, group=group)
-    CMC, ap = cmc.cpu(), float(ap.cpu())
-    if ap != ap:
-        raise L.Reidb200Error("evaluate_all: a query has more good matches than this build holds (2048)")
+    CMC, ap = cmc.cpu(), _check_ap(float(ap.cpu()), "evaluate_all_sharded")
     if verbose and shard.dist.is_initialized() and shard.dist.get_rank(group) != 0:
         verbose = False
     if verbose:
@@ -62,7 +66,7 @@ def evaluate_all_sharded(qf, ql, qc, gf, gl, gc, group=None, verbose=True):
 def evaluate_dist(dist, ql, qc, gl, gc):
     """Same reduction on a precomputed Q x G DISTANCE matrix (ascending = better), e.g. a re-ranked one."""
     cmc, ap = ops.eval_cmc_map(dist, _labels(ql), _labels(qc), _labels(gl), _labels(gc), descending=False)
-    return cmc.cpu(), float(ap.cpu()[0])
+    return cmc.cpu(), _check_ap(float(ap.cpu()[0]), "evaluate_dist")
 
 
 def evaluate(qf, ql, qc, gf, gl, gc):
@@ -263,14 +267,14 @@ class RerankedEvalStream:
         if slot.get("ticket") != ticket:
             raise ValueError("RerankedEvalStream.result: ticket %d is no longer held (depth=%d)" % (ticket, self.depth))
         slot["busy"].synchronize()
-        return slot["cmc_h"].clone(), float(slot["ap_h"][0])
+        return slot["cmc_h"].clone(), _check_ap(float(slot["ap_h"][0]), "RerankedEvalStream.result")
 
 
 def evaluate_all_reranked(qf, ql, qc, gf, gl, gc, k1=20, k2=6, lambda_value=0.3, verbose=True):
     """(CMC FloatTensor[G], mAP float) of the k-reciprocal re-ranked ranking; host arrays in, host results out."""
     cmc, ap = evaluate_all_reranked_device(qf, ql, qc, gf, gl, gc, k1, k2, lambda_value)
     CMC = cmc.cpu()
-    ap = float(ap.cpu()[0])
+    ap = _check_ap(float(ap.cpu()[0]), "evaluate_all_reranked")
     if verbose:
         r = lambda k: float(CMC[k]) if CMC.numel() > k else float("nan")
         print('Rank@1:%f Rank@5:%f Rank@10:%f mAP:%f' % (r(0), r(4), r(9), ap))

@@ -127,7 +127,8 @@ class FlatL2Index:
 
 class ShardedFlatL2Index:
     """faiss.IndexShards over one GpuIndexFlatL2 per GPU (faiss_utils.py:121-135), driven from ONE process:
-    rows are split contiguously over `ngpus` devices, every shard runs the fused GEMM + top-k on its own
+    every add() splits its rows contiguously over the `ngpus` devices and may be called repeatedly (ids keep counting up
+    in call order, as IndexShards(successive_ids) numbers them); every shard runs the fused GEMM + top-k on its own
     stream, the per-shard (distance, global id) lists are merged by the row-select kernel on device 0.
     (The one-process-per-GPU variant with an NCCL all-gather is reidb200.shard.ShardedSearcher.)"""
 
@@ -138,44 +139,52 @@ class ShardedFlatL2Index:
         self.ngpus = max(1, min(int(ngpus) if ngpus else avail, avail))
         self.d = int(d)
         self.shards = [FlatL2Index(d, torch.device("cuda", i)) for i in range(self.ngpus)]
-        self._bases = [0] * self.ngpus
+        self._ids = [None] * self.ngpus  # global id of every row a shard holds (i64, on the shard's device)
+        self._n = 0
 
     @property
     def ntotal(self):
-        return sum(s.ntotal for s in self.shards)
+        return self._n
 
     def reset(self):
         for s in self.shards:
             s.reset()
-        self._bases = [0] * self.ngpus
+        self._ids = [None] * self.ngpus
+        self._n = 0
 
     def add(self, x):
-        if self.ntotal:
-            raise NotImplementedError("ShardedFlatL2Index: add once after reset (contiguous shards)")
         x = np.asarray(x, np.float32) if not isinstance(x, torch.Tensor) else x
+        assert x.shape[1] == self.d
         n = x.shape[0]
         per = (n + self.ngpus - 1) // self.ngpus
         for i, s in enumerate(self.shards):
             lo, hi = min(n, i * per), min(n, (i + 1) * per)
-            self._bases[i] = lo
             if hi > lo:
                 s.add(x[lo:hi])
+                ids = torch.arange(self._n + lo, self._n + hi, dtype=torch.int64, device=s.device)
+                self._ids[i] = ids if self._ids[i] is None else torch.cat([self._ids[i], ids])
+        self._n += n
 
     def search_device(self, x, k):
         parts_d, parts_i = [], []
         dev0 = self.shards[0].device
-        for s, base in zip(self.shards, self._bases):
+        for s, ids in zip(self.shards, self._ids):
             if s.ntotal == 0:
                 continue
             with torch.cuda.device(s.device):
-                D, I = s.search_device(x, k, index_base=base)
+                D, I = s.search_device(x, k)
+                valid = I >= 0  # fewer rows than k on this shard: faiss pads with -1
+                I = torch.where(valid, ids[I.clamp(min=0)], I)
             parts_d.append(D.to(dev0, non_blocking=True))
             parts_i.append(I.to(dev0, non_blocking=True))
         for s in self.shards:
             torch.cuda.synchronize(s.device)
+        if not parts_d:
+            raise ValueError("search on an empty index")
         if len(parts_d) == 1:
             return parts_d[0], parts_i[0]
-        return ops.topk_rows(torch.cat(parts_d, 1), k, descending=False, cand_i=torch.cat(parts_i, 1), idx64=True)
+        with torch.cuda.device(dev0):
+            return ops.topk_rows(torch.cat(parts_d, 1), k, descending=False, cand_i=torch.cat(parts_i, 1), idx64=True)
 
     def search(self, x, k):
         D, I = self.search_device(x, k)

@@ -26,14 +26,26 @@ class _StandInBackbone(torch.nn.Module):
 
 
 class Extractor(object):
-    def __init__(self, model_path=None, use_cuda=True, net=None):
+    def __init__(self, model_path=None, use_cuda=True, net=None, standin=False):
+        """`net`: the embedding backbone (a torch module).  The reference builds SEDense18_IBN from a module that does not
+        exist in its tree, so the backbone has to come from the caller; `model_path` (a checkpoint with a
+        "net_dict" or a plain state dict) is loaded into it STRICTLY.  Without `net` the call raises -- silently returning
+        embeddings of random weights is not a drop-in -- unless standin=True asks for the random-init 512-d stand-in
+        (tests / benchmarks only: backbone weights are outside the kernel scope)."""
         self.device = "cuda" if use_cuda else "cpu"
         if not use_cuda or not torch.cuda.is_available():
             raise RuntimeError("reidb200 Extractor needs a CUDA device (no CPU fallback)")
-        self.net = net if net is not None else _StandInBackbone()
-        if model_path is not None and net is None:
+        if net is None:
+            if not standin:
+                raise ValueError("Extractor: pass the embedding backbone as `net` (the reference's SEDense18_IBN import is "
+                                 "broken, SURVEY F10); standin=True builds a random-init stand-in for tests")
+            if model_path is not None:
+                raise ValueError("Extractor: a checkpoint cannot be loaded into the random-init stand-in backbone")
+            net = _StandInBackbone()
+        self.net = net
+        if model_path is not None:
             state = torch.load(model_path, map_location="cpu")
-            self.net.load_state_dict(state.get("net_dict", state) if isinstance(state, dict) else state, strict=False)
+            self.net.load_state_dict(state.get("net_dict", state) if isinstance(state, dict) else state, strict=True)
         self.net.to(self.device).eval()
         self.size = (128, 256)                       # (w, h), feature_extractor.py:24
         self.norm = P.DEEPSORT_NORM                  # Normalize([.5]*3, [.5]*3), :27-29

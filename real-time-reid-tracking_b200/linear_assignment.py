@@ -71,13 +71,18 @@ def track_gate_state(track):
 def gate_cost_matrix(cost_matrix, tracks, detections, track_indices, detection_indices, mc_lambda,
                      gated_cost=INFTY_COST, only_position=False):
     """In place AND returned: cost[row, gd > chi2inv95] = gated_cost; cost[row] = l*cost[row] + (1-l)*gd."""
-    if only_position:
-        raise NotImplementedError("only_position gating is never used by StrongSORT")
+    gating_dim = 2 if only_position else 4
+    gating_threshold = chi2inv95[gating_dim]
     T, M = len(track_indices), len(detection_indices)
+    measurements = np.asarray([detections[i].to_xyah() for i in detection_indices])
+    if only_position and T:
+        # the reference forwards the flag to track.kf.gating_distance (linear_assignment.py:188-190), whose
+        # only_position branch cannot run: reshape_z / the 2x2 product raise ValueError for every input
+        # (strongsort_kf_adapter.py:160-168, "Needs to be tested!").  Same exception here, through the adapter.
+        from .strongsort_kf_adapter import StrongSortKalmanFilterAdapter
+        StrongSortKalmanFilterAdapter._only_position_error(measurements)
     if T == 0 or M == 0:
         return cost_matrix
-    gating_threshold = chi2inv95[4]
-    measurements = np.asarray([detections[i].to_xyah() for i in detection_indices])
     x4 = np.zeros((T, 4))
     SI = np.zeros((T, 16))
     for row, track_idx in enumerate(track_indices):

@@ -109,25 +109,30 @@ def fuse_score(cost_matrix, detections):
 
 
 class NearestNeighborDistanceMetric(object):
-    """Per-target nearest-neighbour appearance metric with a device-resident gallery.
+    """Per-target nearest-neighbour appearance metric with a device-resident gallery (matching.py:342-409).
 
-    samples: dict target -> slot; the rows themselves stay on the GPU ([slots, budget, d] ring buffer created on
-    the first partial_fit, grown by doubling).  With budget=None the reference keeps every sample; here the
-    ring holds `max_unbounded` rows (documented limit)."""
+    samples: dict target -> slot; the rows themselves stay on the GPU in a [slots, ring, d] ring buffer created on the
+    first partial_fit.  Like the reference's dict of lists the store is unbounded: the slot table doubles when more than
+    `max_tracks` targets are alive, and with budget=None (keep every sample) the ring doubles whenever a target would
+    outgrow it (ops.Gallery.resize: contents move bit for bit).  `max_tracks` / `max_unbounded` are only the initial sizes.
 
-    def __init__(self, metric, matching_threshold, budget=None, max_tracks=512, max_unbounded=1024):
+    metric="euclidean": the reference's helper is broken (torch.min on an ndarray raises TypeError at the first
+    distance() call); here it is fixed by restatement -- the smallest SQUARED distance to a stored sample,
+    clipped at 0, samples kept unnormalised -- on the distmat kernel, off the fused association path."""
+
+    def __init__(self, metric, matching_threshold, budget=None, max_tracks=512, max_unbounded=128):
         if metric not in ("euclidean", "cosine"):
             raise ValueError("Invalid metric; must be either 'euclidean' or 'cosine'")
-        if metric == "euclidean":
-            raise NotImplementedError("only 'cosine' is ever used by StrongSORT (strong_sort.py:32); "
-                                      "the reference's euclidean path is broken (SURVEY F11)")
+        self.metric_name = metric
         self.matching_threshold = matching_threshold
         self.budget = budget
         self._ring = int(budget) if budget is not None else int(max_unbounded)
         self._slots_cap = int(max_tracks)
         self._gallery = None
         self._slot_of = {}      # target id -> slot
+        self._rows_of = {}      # target id -> rows held (host mirror of the device counts: no sync needed to grow)
         self._free = []
+        self._raw = {}          # euclidean only: target id -> f32[n, d] device rows, oldest first
 
     # -- the reference exposes `samples` as dict id -> list of rows; here: id -> stored (normalised) rows, lazily
     @property
@@ -144,24 +149,48 @@ class NearestNeighborDistanceMetric(object):
     def _slot(self, target):
         s = self._slot_of.get(target)
         if s is None:
-            if not self._free:
-                raise NotImplementedError("more than %d simultaneously active tracks" % self._slots_cap)
+            if not self._free:  # more live targets than slots: double the table (the reference's dict has no limit)
+                old = self._slots_cap
+                self._slots_cap = 2 * old
+                self._gallery.resize(slots=self._slots_cap)
+                self._free = list(range(self._slots_cap - 1, old - 1, -1))
             s = self._free.pop()
             self._slot_of[target] = s
+            self._rows_of[target] = 0
         return s
 
     def partial_fit(self, features, targets, active_targets):
         """Append features to their targets (last `budget` survive) and forget inactive targets (matching.py:374-389)."""
         targets = [int(t) for t in np.asarray(targets).reshape(-1)]
+        active = set(int(t) for t in active_targets)
+        if self.metric_name == "euclidean":
+            feats = L.as_f32_cuda(features) if len(targets) else None
+            for i, t in enumerate(targets):
+                rows = feats[i:i + 1] if t not in self._raw else torch.cat([self._raw[t], feats[i:i + 1]], 0)
+                self._raw[t] = rows[-self.budget:] if self.budget is not None else rows
+            self._raw = {int(k): self._raw[int(k)] for k in active_targets}  # (KeyError for an unknown target, like the reference)
+            return
         if len(targets):
             feats = L.as_f32_cuda(features)
             self._ensure(feats.shape[1])
             slots = np.array([self._slot(t) for t in targets], np.int32)
+            need = 0
+            for t in targets:
+                self._rows_of[t] += 1
+                need = max(need, self._rows_of[t])
+            if self.budget is None and need > self._ring:  # keep every sample: grow the ring instead of dropping rows
+                while self._ring < need:
+                    self._ring *= 2
+                self._gallery.resize(budget=self._ring)
+            elif self.budget is not None:
+                for t in set(targets):
+                    self._rows_of[t] = min(self._rows_of[t], self._ring)
             self._gallery.partial_fit(feats, slots)
-        active = set(int(t) for t in active_targets)
         dead = [t for t in self._slot_of if t not in active]
         if dead:
             ds = np.array([self._slot_of.pop(t) for t in dead], np.int32)
+            for t in dead:
+                self._rows_of.pop(t, None)
             self._gallery.reset_slots(ds)
             self._free.extend(int(s) for s in ds)
 
@@ -175,6 +204,11 @@ class NearestNeighborDistanceMetric(object):
         M = feats.shape[0]
         if T == 0 or M == 0:
             return torch.zeros((T, M), dtype=torch.float64, device=feats.device)
+        if self.metric_name == "euclidean":
+            out = torch.empty((T, M), dtype=torch.float64, device=feats.device)
+            for i, t in enumerate(targets):
+                out[i] = ops.distmat(self._raw[int(t)], feats, "sql2").clamp_(min=0.0).min(dim=0)[0]
+            return out
         slots = self.slots_for(targets)
         zeros8 = torch.zeros((T, 8), dtype=torch.float64, device=feats.device)
         tlwh = torch.ones((M, 4), dtype=torch.float32, device=feats.device)
@@ -191,21 +225,26 @@ class _SamplesView(object):
     def __init__(self, metric):
         self._m = metric
 
+    def _ids(self):
+        return self._m._raw if self._m.metric_name == "euclidean" else self._m._slot_of
+
     def __contains__(self, k):
-        return int(k) in self._m._slot_of
+        return int(k) in self._ids()
 
     def __len__(self):
-        return len(self._m._slot_of)
+        return len(self._ids())
 
     def keys(self):
-        return self._m._slot_of.keys()
+        return self._ids().keys()
 
     def __iter__(self):
-        return iter(self._m._slot_of)
+        return iter(self._ids())
 
     def __getitem__(self, k):
         """Stored rows of target k, oldest first (L2-normalised: the metric re-normalises anyway)."""
         m = self._m
+        if m.metric_name == "euclidean":
+            return list(m._raw[int(k)].cpu().numpy())
         slot = m._slot_of[int(k)]
         n = int(m._gallery.counts()[slot].item())
         return list(m._gallery.read_slot(slot)[:n].cpu().numpy())

@@ -250,10 +250,11 @@ def resize_pil_u8(src, crop_off, crop_geom, max_h, out_h=256, out_w=128):
 RERANK_EVAL_MAX_G = 16384  # gallery columns one CTA of the fused kernel keeps in registers (JR_PF * JR_THREADS)
 
 
-def rerank_eval(merged, G, ql, qc, gl, gc, k1=20, k2=6, lambda_value=0.3, want_dist=False):
-    """Fused re-ranked evaluation of merged = [gallery (G rows); query]: (cmc f32[G], ap f64[1][, dist f32[Q,G]]) on
-    device.  Same values as jaccard(rows=(G,Q), cols=(0,G), lambda) followed by eval_cmc_map(descending=False); the
-    re-ranked matrix is only materialised when want_dist."""
+def rerank_eval(merged, G, ql, qc, gl, gc, k1=20, k2=6, lambda_value=0.3, want_dist=False, per_query=False):
+    """Fused re-ranked evaluation of merged = [gallery (G rows); query]: (cmc f32[G], ap f64[1][, dist f32[Q,G]][, ap_q
+    f64[Q], first i32[Q]]) on device.  Same values as jaccard(rows=(G,Q), cols=(0,G), lambda) followed by
+    eval_cmc_map(descending=False); the re-ranked matrix is only materialised when want_dist; per_query adds what the
+    reference's evaluate() returns for every query (AP, first-hit rank with -1 = no valid gallery match)."""
     merged = _f32(merged)
     dev = L.require_device(merged)
     N, d = merged.shape
@@ -262,8 +263,8 @@ def rerank_eval(merged, G, ql, qc, gl, gc, k1=20, k2=6, lambda_value=0.3, want_d
         raise ValueError("rerank_eval: empty query or gallery set")
     if G > RERANK_EVAL_MAX_G:
         dist = jaccard(merged, k1, k2, False, lambda_value, rows=(G, Q), cols=(0, G))
-        cmc, ap = eval_cmc_map(dist, ql, qc, gl, gc, descending=False)
-        return (cmc, ap, dist) if want_dist else (cmc, ap)
+        res = eval_cmc_map(dist, ql, qc, gl, gc, descending=False, per_query=per_query)
+        return (res[0], res[1]) + ((dist,) if want_dist else ()) + tuple(res[2:])
     ql, qc, gl, gc = _i32(ql, dev), _i32(qc, dev), _i32(gl, dev), _i32(gc, dev)
     if ql.numel() != Q or qc.numel() != Q or gl.numel() != G or gc.numel() != G:
         raise ValueError("label / camera vectors do not match the query / gallery sets")
@@ -271,12 +272,14 @@ def rerank_eval(merged, G, ql, qc, gl, gc, k1=20, k2=6, lambda_value=0.3, want_d
     cmc = torch.empty(G, dtype=torch.float32, device=dev)
     ap = torch.empty(1, dtype=torch.float64, device=dev)
     dist = torch.empty((Q, G), dtype=torch.float32, device=dev) if want_dist else None
+    ap_q = torch.empty(Q, dtype=torch.float64, device=dev) if per_query else None
+    first = torch.empty(Q, dtype=torch.int32, device=dev) if per_query else None
     ws = L.workspace(lib.reidb200_rerank_eval_workspace_bytes(N, d, k1, k2, Q, G), dev)
     with torch.cuda.device(dev):
-        L.check(lib.reidb200_rerank_eval(merged.data_ptr(), int(G), Q, merged.stride(0), d, k1, k2, float(lambda_value), ql.data_ptr(),
-                                         qc.data_ptr(), gl.data_ptr(), gc.data_ptr(), L.ptr(dist), G, cmc.data_ptr(), ap.data_ptr(),
-                                         ws.data_ptr(), ws.numel(), L.stream_ptr()))
-    return (cmc, ap, dist) if want_dist else (cmc, ap)
+        L.check(lib.reidb200_rerank_eval_pq(merged.data_ptr(), int(G), Q, merged.stride(0), d, k1, k2, float(lambda_value), ql.data_ptr(),
+                                            qc.data_ptr(), gl.data_ptr(), gc.data_ptr(), L.ptr(dist), G, cmc.data_ptr(), ap.data_ptr(),
+                                            L.ptr(ap_q), L.ptr(first), ws.data_ptr(), ws.numel(), L.stream_ptr()))
+    return (cmc, ap) + ((dist,) if want_dist else ()) + ((ap_q, first) if per_query else ())
 
 
 class RerankEvalPlan:
@@ -342,6 +345,14 @@ class Gallery:
             self._h = None
 
     __del__ = close
+
+    def resize(self, slots=None, budget=None):
+        """Grow in place (more slots and / or a longer ring per slot); stored rows keep their bits and their order."""
+        slots = self.slots if slots is None else int(slots)
+        budget = self.budget if budget is None else int(budget)
+        with torch.cuda.device(self.device):
+            L.check(L.load().reidb200_gallery_resize(self._h, slots, budget, L.stream_ptr()))
+        self.slots, self.budget = slots, budget
 
     def partial_fit(self, feats, slot_of_row):
         feats = _f32(feats, self.device)
@@ -581,7 +592,8 @@ def clamp_add_(dist, other=None):
 
 
 def dbscan_precomputed(dist, eps, min_samples):
-    """sklearn's DBSCAN on a symmetric precomputed f32[N, N] device matrix (rows may be padded: stride(0) >= N):
+    """sklearn's DBSCAN on a SYMMETRIC precomputed f32[N, N] device matrix (rows may be padded: stride(0) >= N; the union
+    pass reads the lower triangle only, so d[i, j] must equal d[j, i] -- cluster.DBSCAN.fit checks a sample of pairs):
     (labels i32[N] with -1 = noise, n_clusters i32[1], core i32[N] 0/1), all on device, no host sync."""
     _rows_f32_cuda(dist, "dbscan_precomputed")
     N = dist.shape[0]

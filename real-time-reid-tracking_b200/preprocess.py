@@ -33,8 +33,16 @@ def xywh_to_xyxy(boxes_xywh, width, height):
     return np.stack([x1, y1, x2, y2], 1).astype(np.int32)
 
 
-def _geometry_from_xyxy(xyxy, width):
+def _geometry_from_xyxy(xyxy, width, height=None):
     xyxy = np.asarray(xyxy, np.int64).reshape(-1, 4)
+    if height is not None and len(xyxy):
+        # numpy's img[y1:y2, x1:x2] clips silently at the frame border (negative starts aside); a box that leaves the
+        # frame would make the kernel read neighbouring rows or past the buffer, so it is clipped the same way here
+        xyxy = xyxy.copy()
+        if (xyxy[:, :2] < 0).any():
+            raise ValueError("crop box with a negative origin (StrongSORT._xywh_to_xyxy clamps at 0)")
+        xyxy[:, 2] = np.minimum(xyxy[:, 2], width)
+        xyxy[:, 3] = np.minimum(xyxy[:, 3], height)
     w = xyxy[:, 2] - xyxy[:, 0]
     h = xyxy[:, 3] - xyxy[:, 1]
     if len(xyxy) and (w.min() <= 0 or h.min() <= 0):
@@ -56,7 +64,7 @@ def preprocess_frame(frame, xyxy, size=(128, 256), norm=DEEPSORT_NORM, mode="cv_
     if f.dtype != torch.uint8 or f.dim() != 3 or f.shape[2] != 3 or not f.is_contiguous():
         raise ValueError("frame must be a contiguous uint8 HxWx3 image")
     H, W = int(f.shape[0]), int(f.shape[1])
-    off, geom = _geometry_from_xyxy(xyxy, W)
+    off, geom = _geometry_from_xyxy(xyxy, W, H)
     if len(off) == 0:
         return torch.empty((0, 3, size[1], size[0]), dtype=torch.float32, device=dev)
     off_d, geom_d = L.staging(dev).upload([off, geom])  # one pinned H2D for both tables

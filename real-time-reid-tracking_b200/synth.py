@@ -12,14 +12,24 @@ def _unit(x):
     return (x / np.linalg.norm(x, axis=1, keepdims=True)).astype(np.float32)
 
 
+def hard_noise(D):
+    """Noise level at which a same-id pair sits about 3 sigma above the different-id cosines of D-dimensional
+    features (2.5 at D = 512): plain rank-1 ~ 0.9-0.95, mAP ~ 0.5-0.85, first hits spread over many ranks --
+    Market-like difficulty instead of the trivially separable default (noise = 0.6: every AP is 0 or 1)."""
+    return float(np.sqrt(max(np.sqrt(float(D)) / 3.1 - 1.0, 0.25)))
+
+
 def market_like(Q=3368, G=15913, D=512, n_ids=751, n_cams=6, seed=0, noise=0.6,
                 junk_frac=0.18, orphan_frac=0.01):
     """Returns dict(qf,ql,qc,gf,gl,gc): fp32 L2-normalised features, int64 labels/cams.
+    noise = 0.6 is SURVEY 8d's recipe (easy: rank-1 == mAP); noise = "hard" uses hard_noise(D).
 
     Gallery: ids 0..n_ids-1 plus label -1 distractors (junk_frac of G).  Every query has at
     least one cross-camera gallery match, except ~orphan_frac of them whose id is absent
     from the gallery (exercises the -1 sentinel of reid/evaluate.py:80-82).
     """
+    if noise == "hard":
+        noise = hard_noise(D)
     rng = np.random.default_rng(seed)
     n_ids = max(2, min(n_ids, max(2, G // 4)))
     cent = rng.standard_normal((n_ids + 1, D)).astype(np.float32)

@@ -1,0 +1,96 @@
+"""GPU parity of the evaluation on HARD data (first hits spread over many ranks, APs take many values), query by query
+against the reference's own outputs (tests/golden/eval.npz, rerank_eval.npz: oracle/make_golden.py).  A kernel that
+mis-ranks anything but the top item fails here.  Comparison rule (tests/_ties.py): every query's AP / first hit must be
+the reference's unless a good item and a non-good item are closer than the distance tolerance, where the reference's value
+must lie between the best and worst arrangement of the tie."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import reid_oracle as O
+import _ties as T
+
+pytestmark = pytest.mark.gpu
+KEYS = ("qf", "ql", "qc", "gf", "gl", "gc")
+
+
+def test_plain_eval_every_query_vs_reference(rb, golden):
+    """evaluate_all / evaluate on the hard fixture: CMC and mAP within 1e-6, every query's AP and first-hit rank equal to
+    the reference's evaluate() (reid/evaluate.py:55-105)."""
+    from reidb200 import evaluate as E, ops
+
+    g = golden("eval")
+    t = {k: torch.from_numpy(g[k]) for k in KEYS}
+    assert g["first_hit"].max() >= 5 and g["cmc"][0] < 0.9  # the fixture is a curve, not a constant
+    cmc, ap = E.evaluate_all(*[t[k] for k in KEYS])
+    np.testing.assert_allclose(cmc.numpy(), g["cmc"], atol=1e-6)
+    assert abs(ap - float(g["ap"])) < 1e-6
+    score = ops.distmat(t["qf"], t["gf"], "dot")
+    _, _, ap_q, first = ops.eval_cmc_map(score, g["ql"], g["qc"], g["gl"], g["gc"], descending=True, per_query=True)
+    ap_q, first = ap_q.cpu().numpy(), first.cpu().numpy()
+    loose, _ = T.check_per_query(-score.cpu().numpy(), g["ql"], g["qc"], g["gl"], g["gc"], g["ap_per_query"], g["first_hit"],
+                                 ap_q, first, rel_tol=0.0, abs_tol=2e-7)
+    assert loose <= 2
+    tight = np.abs(ap_q - g["ap_per_query"]) < 1e-9
+    assert tight.sum() >= len(ap_q) - loose and (first == g["first_hit"]).sum() >= len(first) - loose
+    for i in (0, 7, int(np.argmax(g["first_hit"])), int(np.argmin(g["first_hit"]))):  # the reference-named per-query entry
+        a, c = E.evaluate(t["qf"][i], t["ql"][i], t["qc"][i], t["gf"], t["gl"], t["gc"])
+        if g["first_hit"][i] < 0:
+            assert c[0] == -1 and a == 0
+        else:
+            assert abs(a - g["ap_per_query"][i]) < 1e-9 and int(np.argmax(c.numpy())) == g["first_hit"][i]
+            assert c.sum() == len(c) - g["first_hit"][i]
+
+
+@pytest.mark.parametrize("tag,k1,k2", [("k20_6", 20, 6), ("k12_3", 12, 3)])
+def test_reranked_eval_every_query_vs_reference(rb, golden, tag, k1, k2):
+    """Fused re-ranked evaluation against the reference-generated fixture: the Q x G matrix entry by entry, every query's
+    AP / first hit, CMC and mAP at 1e-6 (plus the width of the tie intervals, if any)."""
+    from reidb200 import evaluate as E, ops
+
+    g = golden("rerank_eval")
+    G, Q = g["gf"].shape[0], g["qf"].shape[0]
+    lam = float(g["lambda_value"])
+    merged = torch.from_numpy(np.concatenate([g["gf"], g["qf"]], 0)).cuda()
+    cmc, ap, dist, ap_q, first = ops.rerank_eval(merged, G, g["ql"], g["qc"], g["gl"], g["gc"], k1, k2, lam, want_dist=True,
+                                                 per_query=True)
+    dist, ap_q, first = dist.cpu().numpy(), ap_q.cpu().numpy(), first.cpu().numpy()
+    want = g["dist_" + tag]
+    np.testing.assert_allclose(dist, want, rtol=0, atol=5e-6)
+    loose, width = T.check_per_query(dist, g["ql"], g["qc"], g["gl"], g["gc"], g["ap_q_" + tag], g["first_" + tag], ap_q, first,
+                                     rel_tol=0.0, abs_tol=1e-5)
+    assert loose <= (g["margin_" + tag] < 2e-5).sum() + 2
+    exact = (np.abs(ap_q - g["ap_q_" + tag]) < 1e-9) & (first == g["first_" + tag])
+    assert exact.sum() >= Q - loose, "%d queries differ, %d have near-ties" % (Q - exact.sum(), loose)
+    assert abs(float(ap[0]) - float(g["map_" + tag])) <= 1e-6 + width / Q
+    assert np.abs(cmc.cpu().numpy() - g["cmc_" + tag]).max() <= 1e-6 + loose / Q
+    if loose == 0:
+        assert np.abs(cmc.cpu().numpy() - g["cmc_" + tag]).max() <= 1e-6 and abs(float(ap[0]) - float(g["map_" + tag])) <= 1e-6
+    # the user-facing call returns the same reduction
+    if (k1, k2) == (20, 6):
+        cmc_h, ap_h = E.evaluate_all_reranked(*[g[k] for k in KEYS], k1, k2, lam, verbose=False)
+        assert torch.equal(cmc_h, cmc.cpu()) and ap_h == float(ap[0])
+
+
+def test_eval_hard_market_shape_vs_oracle(rb):
+    """A larger hard set (oracle instead of fixture): plain and re-ranked, per query."""
+    from reidb200 import evaluate as E, ops, synth
+
+    d = synth.market_like(Q=300, G=4000, D=128, n_ids=700, seed=2, orphan_frac=0.03, noise=1.9)
+    cmc, ap = E.evaluate_all(*[torch.from_numpy(d[k]) for k in KEYS])
+    ocmc, oap = O.evaluate_all(*[d[k] for k in KEYS])
+    assert ocmc[0] < 0.9 and np.unique(ocmc).size > 20
+    np.testing.assert_allclose(cmc.numpy(), ocmc, atol=1e-6)
+    assert abs(ap - oap) < 1e-6
+    G, Q = 4000, 300
+    merged = torch.from_numpy(np.concatenate([d["gf"], d["qf"]], 0)).cuda()
+    cmc, ap, dist, ap_q, first = ops.rerank_eval(merged, G, d["ql"], d["qc"], d["gl"], d["gc"], 20, 6, 0.3, want_dist=True,
+                                                 per_query=True)
+    odist = O.re_ranking_from_feats(d["qf"], d["gf"], 20, 6, 0.3)
+    np.testing.assert_allclose(dist.cpu().numpy(), odist, rtol=0, atol=5e-6)
+    oap_q, ofirst = O.evaluate_per_query_from_dist(odist, d["ql"], d["qc"], d["gl"], d["gc"])
+    loose, width = T.check_per_query(dist.cpu().numpy(), d["ql"], d["qc"], d["gl"], d["gc"], oap_q, ofirst, ap_q.cpu().numpy(),
+                                     first.cpu().numpy(), rel_tol=0.0, abs_tol=1e-5)
+    ocmc, oap = O.evaluate_all_from_dist(odist, d["ql"], d["qc"], d["gl"], d["gc"])
+    assert abs(float(ap[0]) - oap) <= 1e-6 + width / Q and np.abs(cmc.cpu().numpy() - ocmc).max() <= 1e-6 + loose / Q
+    assert loose <= 12

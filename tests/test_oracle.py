@@ -3,6 +3,7 @@ produced by running the reference's own code (reid/evaluate.py, reid/faiss_utils
 reid/losses/utils.py, boxmot matching / linear_assignment / iou_matching / KF adapter,
 modification_deepsort feature_extractor + iou_matching)."""
 import numpy as np
+import pytest
 
 from oracle import reid_oracle as O
 
@@ -152,3 +153,46 @@ def test_posttricks_n4(golden):
         assert np.array_equal(lab, g["lab_" + tag]) and np.array_equal(core, g["core_" + tag])
     valid = g["lab_plain"] != -1
     np.testing.assert_allclose(O.smooth_tracklets(g["unbiased"], g["merged_seqs"], valid), g["smooth"], rtol=0, atol=2e-7)
+
+
+def test_hard_eval_fixture_is_a_curve_and_oracle_matches(golden):
+    """eval.npz is generated on hard data: first hits spread over ranks, many AP values; the oracle reproduces the reference."""
+    g = golden("eval")
+    assert g["first_hit"].max() >= 5 and len(np.unique(g["first_hit"])) >= 5 and g["cmc"][0] < 0.9 < g["cmc"][-1]
+    cmc, ap = O.evaluate_all(g["qf"], g["ql"], g["qc"], g["gf"], g["gl"], g["gc"])
+    assert np.array_equal(cmc, g["cmc"]) and abs(ap - float(g["ap"])) < 1e-12
+    for i in range(0, len(g["ql"]), 7):
+        a, c = O.evaluate(g["qf"][i], g["ql"][i], g["qc"][i], g["gf"], g["gl"], g["gc"])
+        f = -1 if c[0] == -1 else int(np.argmax(c))
+        assert f == g["first_hit"][i] and abs(a - g["ap_per_query"][i]) < 1e-12
+
+
+@pytest.mark.parametrize("tag,k1,k2", [("k20_6", 20, 6), ("k12_3", 12, 3)])
+def test_rerank_eval_fixture_vs_oracle_and_tie_helper(golden, tag, k1, k2):
+    """rerank_eval.npz (reference Jaccard + blend + compute_mAP): the oracle's restatement agrees, and the tie-aware
+    interval helper of the GPU tests collapses to the reference's AP / first hit when the tolerance is zero."""
+    import _ties as T
+
+    g = golden("rerank_eval")
+    dist = g["dist_" + tag]
+    od = O.re_ranking_from_feats(g["qf"], g["gf"], k1, k2, float(g["lambda_value"]))
+    np.testing.assert_allclose(od, dist, rtol=0, atol=2e-6)
+    ap_q, first = O.evaluate_per_query_from_dist(dist, g["ql"], g["qc"], g["gl"], g["gc"])
+    assert np.array_equal(first, g["first_" + tag]) and np.abs(ap_q - g["ap_q_" + tag]).max() < 1e-12
+    assert g["first_" + tag].max() >= 3
+    loose, width = T.check_per_query(dist, g["ql"], g["qc"], g["gl"], g["gc"], g["ap_q_" + tag], g["first_" + tag], rel_tol=0.0)
+    assert width < 1e-9  # only exact ties (none expected) widen an interval at zero tolerance
+    loose2, width2 = T.check_per_query(dist, g["ql"], g["qc"], g["gl"], g["gc"], g["ap_q_" + tag], g["first_" + tag], abs_tol=1e-3)
+    assert loose2 > loose and width2 > width  # a coarse tolerance does open intervals
+
+
+def test_market_full_fixture_present_and_consistent(golden):
+    """The full-size configs[0] / configs[1] fixture (oracle/make_golden_fullsize.py): shapes, ranges, and the hard-data
+    property the GPU test relies on (first hits beyond rank 0, CMC a curve)."""
+    g = golden("market_full")
+    assert g["rr_ap_q"].shape == (3368,) and g["rr_cmc"].shape == (15913,) and g["dist_vals"].shape[1] == 15913
+    assert g["plain_first"].max() >= 10 and g["rr_first"].max() >= 3 and g["plain_cmc"][0] < 0.95
+    assert 0.5 < float(g["rr_map"]) < 0.99 and float(g["plain_map"]) < float(g["rr_map"])
+    assert abs(g["rr_ap_q"].sum() / 3368 - float(g["rr_map"])) < 1e-12
+    assert np.all(np.diff(g["rr_cmc"]) >= 0) and np.all(np.diff(g["rank_dist"], axis=1) >= 0)
+    assert np.array_equal(g["rank_vals"][:, 0], g["rank_rows"])  # self first
