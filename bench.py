@@ -167,21 +167,38 @@ def bench_assoc(steps, warmup):
                 frame_step()
         torch.cuda.synchronize()
         ms_graph = _timed(g.replay, n, torch.cuda.synchronize)
-        # end to end through the public API: host boxes / detections / track state in, cost matrices out
+        # end to end through the public API: host boxes / detections / track state in, cost matrices out (host numpy).
+        # tracker.FrameContext = two C calls per frame (one pinned H2D each, one D2H of both matrices, no Python marshalling)
+        fc = tracker.FrameContext(metric, max_dets=256, max_tracks=512)
+        xyxy32 = np.ascontiguousarray(xyxy, dtype=np.int32)
+        ids, conf_all = np.arange(T), np.ones(T, bool)
+        slots_h = metric.slots_for(ids)
+        SI16 = np.ascontiguousarray(fr["trk_SI"].reshape(T, 16))
+
         def e2e_step():
+            fc.crops(frame, xyxy32, out=crops)
+            return fc.costs(det_feat, fr["det_tlwh"], ids, conf_all, fr["trk_mean"], SI16, fr["trk_tsu"], 0.995, 0.2, 0.7, slots=slots_h)
+
+        def e2e_step_py():  # round 1's path: per-frame Python marshalling (tracker.frame_costs + costs_to_host)
             c = preprocess.preprocess_frame(frame, xyxy, out=crops)
             a, _, i = tracker.frame_costs(metric, det_feat, fr["det_tlwh"], np.arange(T), np.ones(T, bool), fr["trk_mean"],
                                           fr["trk_SI"], fr["trk_tsu"], 0.995, 0.2, 0.7)
             return tracker.costs_to_host(a, i)  # one D2H of both cost matrices, as tracker.match_arrays does
 
-        for _ in range(3):
-            e2e_step()
-        torch.cuda.synchronize()
-        t0 = time.perf_counter()
-        for _ in range(n):
-            e2e_step()
-        torch.cuda.synchronize()
-        e2e_us = (time.perf_counter() - t0) / n * 1e6
+        a_fc, i_fc = e2e_step()
+        a_py, i_py = e2e_step_py()
+        assert np.array_equal(a_fc, a_py) and np.array_equal(i_fc, i_py), "FrameContext and frame_costs differ"
+        e2e = {}
+        for tag, fn in (("ctx", e2e_step), ("py", e2e_step_py)):
+            for _ in range(3):
+                fn()
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            for _ in range(n):
+                fn()
+            torch.cuda.synchronize()
+            e2e[tag] = (time.perf_counter() - t0) / n * 1e6
+        e2e_us = e2e["ctx"]
         # the whole Tracker._match from host arrays (costs + both assignment stages): Hungarian on the host (scipy, the
         # reference's solver) against the device assignment (N1)
         conf = np.arange(T) % 7 != 0
@@ -207,7 +224,9 @@ def bench_assoc(steps, warmup):
         crop_bytes = len(xyxy) * 3 * 256 * 128 * 4 + int((geom[:, 0].astype(np.int64) * geom[:, 1] * 3).sum())
         gal_bytes = sum(counts) * 512 * 4 + M * 512 * 4 + 2 * T * M * 8
         out[name] = {"dets": int(M), "tracks": int(T), "us_per_frame": ms / n * 1e3, "us_per_frame_cuda_graph": ms_graph / n * 1e3,
-                     "e2e_us_per_frame": e2e_us, "crop_kernel_us": crop_us, "assoc_kernel_us": assoc_us,
+                     "e2e_us_per_frame": e2e_us, "e2e_us_per_frame_python_marshalling": e2e["py"],
+                     "e2e_h2d_bytes": int(len(xyxy) * 20 + M * 16 + T * 200), "e2e_d2h_bytes": int(2 * T * M * 8),
+                     "crop_kernel_us": crop_us, "assoc_kernel_us": assoc_us,
                      "crop_gbs": crop_bytes / crop_us / 1e3, "assoc_gbs": gal_bytes / assoc_us / 1e3,
                      "assoc_tflops": 2.0 * sum(counts) * M * 512 / assoc_us / 1e6, "match_e2e_us": match_us}
     return out
@@ -390,13 +409,18 @@ def bench_retrieval(args, rank, world, dev, barrier):
             "checksum": {"id_sum": int(Ih.astype(np.int64).sum()), "dist_sum": float(Dh.astype(np.float64).sum())}}
 
 
+def bench_rerank_sharded(args, rank, world, dev, barrier):
+    """(e3) one re-ranked evaluation split over the ranks -- filled in once shard.rerank_eval_sharded exists."""
+    return None
+
+
 def bench_eval_c1(args, rank, world, dev, barrier, d0):
     """BASELINE.json configs[0]: Market-shaped evaluate_all WITHOUT re-ranking (3368 x 15913 x 512-d score GEMM + CMC/mAP
     counting kernel), the queries split over the ranks and one NCCL all-reduce of the CMC counts + AP sum
     (shard.evaluate_all_sharded).  Strong scaling: the same set on every rank.  Device-timed, max over ranks."""
     from reidb200 import shard, synth
 
-    d = d0 if d0 is not None else synth.market_like(Q=Q_FULL, G=G_FULL, D=D_FULL, n_ids=IDS_FULL, seed=0)
+    d = d0 if d0 is not None else market_set(0, hard=True)
     a = [torch.from_numpy(d[k]).to(dev) for k in ("qf", "ql", "qc", "gf", "gl", "gc")]
     a[1], a[2], a[4], a[5] = (x.to(torch.int32) for x in (a[1], a[2], a[4], a[5]))
     fn = lambda: shard.evaluate_all_sharded(*a, device=dev)
@@ -417,13 +441,15 @@ def bench_eval_c1(args, rank, world, dev, barrier, d0):
 
 
 # --------------------------------------------------------------------------------------------- CPU port / reference arm
-def cpu_sample(scale=4):
-    """A bounded sample of the same workload: Market-shaped set at 1/scale of the query/gallery/identity counts."""
+HARD_NOISE = 2.5   # Market-like difficulty (plain rank-1 ~ 0.87-0.95, mAP ~ 0.45-0.63); SURVEY 8d's recipe is noise = 0.6
+
+
+def market_set(seed, hard=True):
+    """BASELINE.json configs[0] / configs[1] input at FULL size: 3368 x 15913 x 512-d, 751 ids + junk, 6 cameras."""
     import reidb200  # noqa: F401
     from reidb200 import synth
 
-    Q, G, ids = Q_FULL // scale, G_FULL // scale, max(IDS_FULL // scale, 8)
-    return synth.market_like(Q=Q, G=G, D=D_FULL, n_ids=ids, seed=0), Q, G
+    return synth.market_like(Q=Q_FULL, G=G_FULL, D=D_FULL, n_ids=IDS_FULL, seed=seed, noise=HARD_NOISE if hard else 0.6)
 
 
 def cpu_step(d):
@@ -434,33 +460,136 @@ def cpu_step(d):
     return O.evaluate_all_from_dist(dist, d["ql"], d["qc"], d["gl"], d["gc"])
 
 
+def _threads(n):
+    """Context manager limiting BLAS / OpenMP threads (the tracking scripts pin them to 1, track_yolov5.py:5-9)."""
+    try:
+        from threadpoolctl import threadpool_limits
+        return threadpool_limits(limits=n)
+    except Exception:
+        import contextlib
+        return contextlib.nullcontext()
+
+
+def cpu_frame_us(M, T, threads, frames=12):
+    """C3 / C4 on the host the way the reference runs a frame (sort/tracker.py:175-233): Extractor._preprocess of the M
+    crops (cv2.resize when OpenCV is importable, else the oracle's restatement), NearestNeighborDistanceMetric.distance,
+    gate_cost_matrix, iou_cost; the two Hungarian solves timed separately.  Median microseconds over `frames` frames."""
+    from oracle import reid_oracle as O
+    from reidb200 import preprocess, synth
+    from scipy.optimize import linear_sum_assignment
+
+    try:
+        import cv2
+        cv2.setNumThreads(threads if threads > 0 else -1)
+    except Exception:
+        cv2 = None
+    fr = synth.mot_frame(M=M, T=T, budget=100, D=512, seed=7)
+    H, W = fr["img"].shape[:2]
+    xyxy = preprocess.xywh_to_xyxy(fr["det_xywh"], W, H)
+    xyxy = xyxy[(xyxy[:, 2] > xyxy[:, 0]) & (xyxy[:, 3] > xyxy[:, 1])]
+    crops = [fr["img"][b[1]:b[3], b[0]:b[2]] for b in xyxy]
+    meas = O.tlwh_to_xyah_f32(fr["det_tlwh"])
+    trk_tlwh = [O.track_to_tlwh(m[:4]) for m in fr["trk_mean"]]
+    t_pre, t_cost, t_lap = [], [], []
+
+    def pre():
+        if cv2 is None:
+            return O.preprocess_deepsort(crops)
+        out = []
+        for c in crops:  # feature_extractor.py:31-46
+            im = cv2.resize(c.astype(np.float32) / 255., (128, 256))
+            out.append(((im.transpose(2, 0, 1) - 0.5) / 0.5)[None])
+        return np.concatenate(out, 0).astype(np.float32)
+
+    with _threads(threads if threads > 0 else None):
+        for f in range(frames + 1):
+            t0 = time.perf_counter()
+            pre()
+            t1 = time.perf_counter()
+            raw = O.nn_distance_matrix(fr["samples"], fr["det_feat"])
+            app = O.gate_cost_matrix(raw, fr["trk_mean"][:, :4], fr["trk_SI"], meas, 0.995)
+            iou = O.iou_cost(trk_tlwh, fr["trk_tsu"], fr["det_tlwh"])
+            t2 = time.perf_counter()
+            linear_sum_assignment(O.clamp_cost(app, 0.2))
+            linear_sum_assignment(O.clamp_cost(iou, 0.7))
+            t3 = time.perf_counter()
+            if f:  # first frame = warm-up
+                t_pre.append(t1 - t0); t_cost.append(t2 - t1); t_lap.append(t3 - t2)
+    med = lambda v: float(np.median(v) * 1e6)
+    return {"crop_us": med(t_pre), "cost_us": med(t_cost), "crop_plus_cost_us": med(np.add(t_pre, t_cost)), "hungarian_us": med(t_lap),
+            "frames": frames, "crop_impl": "cv2.resize" if cv2 is not None else "numpy restatement"}
+
+
+def cpu_rows(d_hard):
+    """the host-side numbers that sit next to the GPU ones (numpy port of the reference, this box's
+    cores): C1 evaluate_all, C3 / C4 per frame at 1 thread (as the tracking scripts pin) and all cores, C5 exact top-100
+    over a 64 k sub-gallery extrapolated linearly to 4 M rows."""
+    from oracle import reid_oracle as O
+
+    cores = os.cpu_count() or 1
+    out = {"cores": cores, "kind": "port"}
+    keys = ("qf", "ql", "qc", "gf", "gl", "gc")
+    for tag, n in (("1_thread", 1), ("all_cores", 0)):
+        with _threads(n if n else None):
+            t0 = time.perf_counter()
+            cmc, ap = O.evaluate_all(*[d_hard[k] for k in keys])
+            dt = time.perf_counter() - t0
+        out.setdefault("c1_evaluate_all", {})[tag] = {"seconds": dt, "pairs_per_s": Q_FULL * G_FULL / dt}
+        out["c1_evaluate_all"]["result"] = {"rank1": float(cmc[0]), "mAP": float(ap)}
+        out.setdefault("c3_mot16_frame", {})[tag] = cpu_frame_us(30, 100, n)
+        out.setdefault("c4_mot20_frame", {})[tag] = cpu_frame_us(200, 300, n, frames=8)
+    rng = np.random.default_rng(0)
+    sub = 65536
+    xb = rng.standard_normal((sub, RETR_D), dtype=np.float32)
+    xq = rng.standard_normal((RETR_Q, RETR_D), dtype=np.float32)
+    t0 = time.perf_counter()
+    O.knn_l2(xb, xq, RETR_K)
+    dt = time.perf_counter() - t0
+    out["c5_retrieval"] = {"sub_gallery": sub, "seconds_sub": dt, "seconds_4M_extrapolated": dt * RETR_G / sub,
+                           "pairs_per_s": RETR_Q * sub / dt, "note": "10 k x 64 k x 2048 exact top-100 on all cores, extrapolated linearly in G"}
+    return out
+
+
 def run_reference(args):
+    """The reference's own CPU algorithm for configs[1] at FULL size on the hard data (the numpy port: the Python reference
+    cannot travel to the GPU box).  One step = one whole re-ranked evaluation (about a minute); the run stops after the
+    requested steps or ~4 minutes, whichever comes first, and reports the steps it did."""
     rank, world, _ = _dist_env()
     if rank != 0:
         return
     torch.set_num_threads(os.cpu_count() or 1)
-    d, Q, G = cpu_sample()
-    for _ in range(min(args.warmup, 1)):
-        cpu_step(d)
+    d = market_set(0, hard=True)
+    Q, G = Q_FULL, G_FULL
     t0 = time.perf_counter()
     steps = 0
-    for _ in range(args.steps):
-        cpu_step(d)
+    res = None
+    for _ in range(max(args.steps, 1)):
+        res = cpu_step(d)
         steps += 1
-        if time.perf_counter() - t0 > 240:  # keep the whole run within a few minutes
+        if time.perf_counter() - t0 > 170:  # keep the whole run within a few minutes
             break
     dt = time.perf_counter() - t0
     v = steps * Q * G / dt
-    sample = "Market-shaped %dx%d (1/4 of every count), D=512, numpy port of the reference algorithm" % (Q, G)
+    sample = "FULL configs[1]: Market-shaped %dx%d, D=512, hard data (noise %.1f), numpy port of the reference algorithm" % (Q, G, HARD_NOISE)
     print(json.dumps({
         "impl": "reference", "metric": METRIC, "value": v, "unit": "pairs/s", "n_gpus": args.gpus, "steps": steps,
-        "warmup": min(args.warmup, 1), "ms_per_step": dt / steps * 1e3, "higher_is_better": True, "scaling": "weak",
+        "warmup": 0, "ms_per_step": dt / steps * 1e3, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": "market1501_rerank_k20_6_l0.3 (bounded sample %dx%d)" % (Q, G), "k1": K1, "k2": K2,
-                   "lambda": LAMBDA},
+        "config": _config(1),
         "cpu_baseline": {"value": v, "unit": "pairs/s", "cores": os.cpu_count(), "kind": "port", "sample": sample},
         "e2e": {"value": v, "unit": "pairs/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "result": {"rank1": float(res[0][0]), "mAP": float(res[1])},
+        "note": "steps / warmup requested: %d / %d; a step is a whole full-size evaluation (~1 min), so the run is cut at ~3 min" % (args.steps, args.warmup),
     }))
+
+
+def _config(world):
+    return {"workload": "market1501_rerank_k20_6_l0.3_hard (configs[1]; noise %.1f: Market-like difficulty)" % HARD_NOISE,
+            "queries": Q_FULL, "gallery": G_FULL, "dim": D_FULL, "k1": K1, "k2": K2, "lambda": LAMBDA,
+            "parallelism": "independent evaluation sets per GPU" if world > 1 else "single GPU",
+            "l2": "working set (N x N distance work + 0.5 GB sparse tables per step) larger than L2",
+            "evaluation": "fused into the re-rank kernel (ops.rerank_eval); ms_per_step_materialised = jaccard + eval_cmc_map",
+            "launch": "one CUDA graph replay per step (ops.RerankEvalPlan); ms_per_step_stream_launches = the same kernels launched one by one"}
 
 
 def run_ours(args):
@@ -492,7 +621,7 @@ def run_ours(args):
             dist.barrier()
         torch.cuda.synchronize()
 
-    d = synth.market_like(Q=Q_FULL, G=G_FULL, D=D_FULL, n_ids=IDS_FULL, seed=rank)
+    d = market_set(rank, hard=True)
     Q, G, N = Q_FULL, G_FULL, Q_FULL + G_FULL
     merged_host = torch.from_numpy(np.concatenate([d["gf"], d["qf"]], 0)).pin_memory()
     lab_host = {k: torch.from_numpy(d[k].astype(np.int32)).pin_memory() for k in ("ql", "qc", "gl", "gc")}
@@ -584,11 +713,29 @@ def run_ours(args):
     h2d = merged_host.numel() * 4 + sum(v.numel() * 4 for v in lab_host.values())
     d2h = G * 4 + 8
 
+    # ---- the same step on SURVEY 8d's recipe (noise 0.6: trivially separable, round 1's headline data) for continuity
+    d_easy = market_set(rank, hard=False)
+    plan.merged.copy_(torch.from_numpy(np.concatenate([d_easy["gf"], d_easy["qf"]], 0)))
+    for dst, k in ((plan.ql, "ql"), (plan.qc, "qc"), (plan.gl, "gl"), (plan.gc, "gc")):
+        dst.copy_(torch.from_numpy(d_easy[k].astype(np.int32)))
+    for _ in range(3):
+        cmc_e, ap_e = step()
+    ms_easy = _timed(step, args.steps, barrier)
+    t = torch.tensor([ms_easy], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_easy = float(t.item())
+    easy = {"workload": "market1501_rerank_k20_6_l0.3 on SURVEY 8d's recipe (noise 0.6)", "ms_per_step": ms_easy / args.steps,
+            "value": world * args.steps * Q * G / (ms_easy * 1e-3), "result": {"rank1": float(cmc_e[0]), "mAP": float(ap_e[0])}}
+    del d_easy
+
     eval_c1 = bench_eval_c1(args, rank, world, dev, barrier, d if rank == 0 else None)
+    rerank_sharded = bench_rerank_sharded(args, rank, world, dev, barrier) if not args.no_sharded_rerank else None
     posttricks = bench_posttricks(merged, K1, K2, args.steps) if (rank == 0 and not args.no_assoc) else None
     retrieval = None
     if not args.no_retrieval:
         merged = None
+        plan = None
         torch.cuda.empty_cache()
         retrieval = bench_retrieval(args, rank, world, dev, barrier)
 
@@ -602,7 +749,7 @@ def run_ours(args):
     launches = sum(n for n, _ in prof.values())
     share = {k: round(v[1] / ms_prof, 4) for k, v in sorted(prof.items(), key=lambda kv: -kv[1][1])}
     # algorithmic (fp32-equivalent) flops of one launch: 2*D per UNORDERED pair -- the self-distance matrix is symmetric
-    # and the kernel computes only its upper triangle of tiles (each off-diagonal tile is stored twice)
+    # and the kernel computes only its upper triangle of tiles
     gemm_flops = 2.0 * D_FULL * (N * (N + 1) / 2.0)
     try:  # dram__bytes_read.sum + dram__bytes_write.sum of this kernel from the committed ncu --set full capture
         traffic = json.load(open(os.path.join(ROOT, "profiles", "gemm_traffic.json")))["dram_bytes_per_launch"]
@@ -614,11 +761,11 @@ def run_ours(args):
         "metric": METRIC, "value": value, "unit": "pairs/s", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
         "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
         "data": "synthetic",
-        "config": {"workload": "market1501_rerank_k20_6_l0.3", "queries": Q, "gallery": G, "dim": D_FULL, "k1": K1, "k2": K2,
-                   "lambda": LAMBDA, "parallelism": "independent evaluation sets per GPU" if world > 1 else "single GPU",
-                   "l2": "working set (1.49 GB distance matrix + 0.5 GB sparse tables per step) larger than L2",
-                   "evaluation": "fused into the re-rank kernel (ops.rerank_eval); ms_per_step_materialised = jaccard + eval_cmc_map",
-                   "launch": "one CUDA graph replay per step (ops.RerankEvalPlan); ms_per_step_stream_launches = the same kernels launched one by one"},
+        # compact per-N numbers first (a long line may be cut at its tail): strong-scaling rows with a data-path collective
+        "retrieval_ms_per_search": retrieval["ms_per_search"] if retrieval else None,
+        "rerank_sharded_ms": rerank_sharded["ms_per_eval"] if rerank_sharded else None,
+        "config": _config(world),
+        "survey_recipe": easy,
         "ms_per_step_stream_launches": ms_launch / args.steps,
         "ms_per_step_materialised": ms_mat, "ms_per_step_with_kernel_events": ms_prof / args.steps,
         "clocks": clk,
@@ -634,6 +781,8 @@ def run_ours(args):
         "kernel_share_of_step": share,
         "result": {"rank1": float(cmc_h[0]), "mAP": float(ap_h)},
     }
+    if rerank_sharded is not None:
+        line["rerank_sharded"] = rerank_sharded
     line["eval_c1"] = eval_c1
     if retrieval is not None:
         line["retrieval"] = retrieval
@@ -642,12 +791,14 @@ def run_ours(args):
         line["next_rows"] = bench_next_rows(args.steps)
         line["next_rows"]["n4"] = posttricks
     if not args.no_cpu and world == 1:
-        dsmp, qs, gs = cpu_sample()
         t0 = time.perf_counter()
-        cpu_step(dsmp)
+        res = cpu_step(d)  # FULL configs[1] on the same hard data, one pass (about a minute)
         dt = time.perf_counter() - t0
-        line["cpu_baseline"] = {"value": qs * gs / dt, "unit": "pairs/s", "cores": os.cpu_count(), "kind": "port",
-                                "sample": "Market-shaped %dx%d (1/4 of every count), one pass, numpy port of the reference" % (qs, gs)}
+        line["cpu_baseline"] = {"value": Q * G / dt, "unit": "pairs/s", "cores": os.cpu_count(), "kind": "port", "seconds": dt,
+                                "sample": "FULL configs[1] (%dx%d, D=512, hard data), one pass, numpy port of the reference" % (Q, G),
+                                "result": {"rank1": float(res[0][0]), "mAP": float(res[1])}}
+        if not args.no_cpu_rows:
+            line["cpu_rows"] = cpu_rows(d)
     print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
@@ -662,6 +813,8 @@ def main():
     ap.add_argument("--no-assoc", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-retrieval", action="store_true")
+    ap.add_argument("--no-cpu-rows", action="store_true", help="skip the C1 / C3 / C4 / C5 host baselines (BASELINE.md section 2)")
+    ap.add_argument("--no-sharded-rerank", action="store_true")
     ap.add_argument("--retrieval-gallery", type=int, default=RETR_G)
     args = ap.parse_args()
     if args.impl == "reference":

@@ -221,6 +221,29 @@ int reidb200_assoc_frame(reidb200_gallery* g, const float* det_feat, int64_t ldf
                          double mc_lambda, double max_dist, double max_iou_dist, int iou_mode,
                          int flags, double* out_app, double* out_raw, double* out_iou, void* stream);
 
+/* ------------------------------------------------------------------------------------------
+ * One tracking frame FROM HOST ARRAYS in two calls (crops before the backbone, costs after it), the way the reference's
+ * per-frame code hands over its data (strong_sort.py:149-159 _get_features; sort/tracker.py:175-233 _match): plain host
+ * pointers in, each call ONE pinned host->device copy of the small per-frame tables + the kernels; frame_costs ends with
+ * ONE device->host copy of both float64 cost matrices into pinned memory and a stream synchronisation, and returns
+ * pointers into that pinned result (valid until the call after the next).  No per-frame allocation.
+ *   frame      u8[H,W,3] on the DEVICE (where the detector left it); xyxy_host i32[n,4] crop boxes img[y1:y2, x1:x2]
+ *              (slice ends are clipped at the frame border as numpy does; an empty crop is REIDB200_EINVAL)
+ *   det_feat   f32[M,d] on the DEVICE (the backbone's output); everything else is host memory:
+ *   det_tlwh_host f32[M,4], trk_slot_host i32[T], trk_mean_host f64[T,8], trk_SI_host f64[T,16], trk_tsu_host i32[T]
+ * out_app_host / out_iou_host receive f64[T,M] (row-major) as reidb200_assoc_frame defines them. */
+typedef struct reidb200_frame reidb200_frame;
+int reidb200_frame_create(reidb200_gallery* g, int max_dets, int max_tracks, reidb200_frame** out);
+int reidb200_frame_destroy(reidb200_frame* f);
+int reidb200_frame_crops(reidb200_frame* f, const uint8_t* frame, int H, int W, const int32_t* xyxy_host, int n,
+                         int out_h, int out_w, const float mean_host[3], const float std_host[3], float* out,
+                         void* stream);
+int reidb200_frame_costs(reidb200_frame* f, const float* det_feat, int64_t ldf, const float* det_tlwh_host, int M,
+                         const int32_t* trk_slot_host, const double* trk_mean_host, const double* trk_SI_host,
+                         const int32_t* trk_tsu_host, int T, double mc_lambda, double max_dist, double max_iou_dist,
+                         int iou_mode, int flags, const double** out_app_host, const double** out_iou_host,
+                         void* stream);
+
 /* Stand-alone pieces of the same kernel family (the reference's free functions):
  *   iou / DIoU of T boxes (f64 tlwh) against M candidates (f32 or f64 tlwh) -> f64[T,M] */
 int reidb200_iou_matrix(const double* bbox_tlwh, int T, const void* cand_tlwh, int cand_is_f64, int M,

@@ -13,7 +13,7 @@ import torch
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libreidb200.so")
-ABI_VERSION = 3
+ABI_VERSION = 4
 
 OK, EINVAL, ECUDA, ELIMIT = 0, -1, -2, -3
 RESIZE_CV_LINEAR, RESIZE_PIL_ANTIALIAS = 0, 1
@@ -61,6 +61,10 @@ SIGNATURES = {
     "reidb200_gallery_counts": (_i, [_vp, _vp, _vp]),
     "reidb200_gallery_read_slot": (_i, [_vp, _i, _vp, _vp]),
     "reidb200_assoc_frame": (_i, [_vp, _vp, _i64, _vp, _i, _vp, _vp, _vp, _vp, _i, _d, _d, _d, _i, _i, _vp, _vp, _vp, _vp]),
+    "reidb200_frame_create": (_i, [_vp, _i, _i, C.POINTER(_vp)]),
+    "reidb200_frame_destroy": (_i, [_vp]),
+    "reidb200_frame_crops": (_i, [_vp, _vp, _i, _i, _vp, _i, _i, _i, _f3, _f3, _vp, _vp]),
+    "reidb200_frame_costs": (_i, [_vp, _vp, _i64, _vp, _i, _vp, _vp, _vp, _vp, _i, _d, _d, _d, _i, _i, C.POINTER(_vp), C.POINTER(_vp), _vp]),
     "reidb200_iou_matrix": (_i, [_vp, _i, _vp, _i, _i, _i, _vp, _vp]),
     "reidb200_gating_distance": (_i, [_vp, _vp, _vp, _i, _i, _vp, _vp]),
     "reidb200_cosine_distance_workspace_bytes": (_sz, [_i, _i, _i]),

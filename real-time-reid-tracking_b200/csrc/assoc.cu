@@ -6,6 +6,9 @@
 //   iou       boxmot/trackers/strongsort/sort/iou_matching.py:9-86, modification_deepsort/iou_matching.py:5-47
 // One kernel per frame: CTA t owns track t: per-track gallery x detections cosine minimum (fp32),
 // Mahalanobis gate + blend (fp64), IoU / DIoU row (fp64).
+#include <stdlib.h>
+#include <string.h>
+
 #include "gemm.cuh"
 #include "ptx.cuh"
 
@@ -20,6 +23,9 @@ struct reidb200_gallery {
   __half* det_packed;  // [det_cap, 2*dp] L2-normalised detection features of the current frame, hi|lo planes
   int det_cap;
   CUtensorMap tm_gallery;     // TMA descriptor of `packed` (box 64 x 128)
+  CUtensorMap tm_rows[4];     // the same tensor with boxes of 16 / 32 / 64 / 128 rows: count-aware loads of a track's rows
+  int32_t* sched;             // frame schedule written by assoc_schedule (tracks packed into 128-row tiles by 32-row quadrants)
+  int sched_cap;              // tracks the schedule buffer holds
 };
 
 namespace reidb200 {
@@ -547,6 +553,297 @@ assoc_frame_kernel(const __grid_constant__ CUtensorMap tmG, const __grid_constan
   }
 }
 
+// ------------------------------------------------------------------------------------ fused frame kernel, packed tiles
+// Second form of the tcgen05 frame kernel, for rings of at most 128 rows (StrongSORT's nn_budget is 100): a frame's tracks
+// are PACKED into 128-row A tiles by 32-row quadrants (a track with `count` rows takes ceil(count / 32) consecutive
+// quadrants = TMEM lane quadrants = epilogue warps), and only ceil16(count) rows of every track are fetched -- TMA boxes
+// of 16 / 32 / 64 / 128 rows written at the track's row offset inside the stage; the MMA still runs M = 128 over whatever
+// the untouched rows hold, and those accumulator rows are masked.  Against one track per tile this halves the tiles (and
+// with them the re-streaming of the detection operand from L2) and reads the ring's valid rows only: DRAM traffic ~ sum of
+// count x 2 KB instead of the whole [slots, budget] ring.
+// Schedule (device side, assoc_schedule_kernel, one warp): sched[0] = tiles in total, sched[1] = tiles with rows;
+// sched[4 + 4 * tile + q] = track row index of quadrant q (or -1).  Tiles >= sched[1] list the tracks WITHOUT rows
+// (unknown slot / empty ring: every cost is 1e5 before the gate), four per tile, no MMA.
+constexpr int A2_STAGES = 2;
+constexpr size_t A2_SMEM = 1024 + (size_t)A2_STAGES * AT_STAGE_BYTES + 2 * 4 * AT_BN * sizeof(float) + 2 * 4 * 32 * sizeof(double) + 128;
+
+__global__ void __launch_bounds__(32)
+assoc_schedule_kernel(const int32_t* __restrict__ trk_slot, const int32_t* __restrict__ gcount, int T, int32_t* __restrict__ sched) {
+  // One warp.  32 tracks at a time: every lane fetches its track's row count (the two dependent loads of all 32 tracks are
+  // in flight together), three ballots hand the 32 quadrant counts (0..4) to lane 0 as bit planes, and lane 0 runs the
+  // packing state machine on registers only; pass 2 appends the tracks without rows, four per tile.
+  const int lane = threadIdx.x;
+  int32_t* seg = sched + 4;
+  int tile = 0, q = 0;
+  for (int pass = 0; pass < 2; ++pass) {
+    for (int base = 0; base < T; base += 32) {
+      const int t = base + lane;
+      int nq = 0;
+      bool empty = false;
+      if (t < T) {
+        const int slot = trk_slot ? trk_slot[t] : -1;
+        const int cnt = slot >= 0 ? gcount[slot] : 0;
+        nq = min((cnt + 31) >> 5, 4);
+        empty = cnt <= 0;
+      }
+      const uint32_t b0 = __ballot_sync(0xffffffffu, nq & 1), b1 = __ballot_sync(0xffffffffu, nq & 2),
+                     b2 = __ballot_sync(0xffffffffu, nq & 4), be = __ballot_sync(0xffffffffu, empty);
+      if (lane == 0) {
+        const int n = min(32, T - base);
+        for (int i = 0; i < n; ++i) {
+          if (pass == 0) {
+            const int k = ((b0 >> i) & 1) | (((b1 >> i) & 1) << 1) | (((b2 >> i) & 1) << 2);
+            if (k == 0) continue;
+            if (q + k > 4) {
+              for (; q < 4; ++q) seg[tile * 4 + q] = -1;
+              ++tile; q = 0;
+            }
+            for (int j = 0; j < k; ++j) seg[tile * 4 + q + j] = base + i;
+            q += k;
+            if (q == 4) { ++tile; q = 0; }
+          } else if ((be >> i) & 1) {
+            seg[tile * 4 + q] = base + i;
+            if (++q == 4) { ++tile; q = 0; }
+          }
+        }
+      }
+    }
+    if (lane == 0) {
+      if (q > 0) {
+        for (; q < 4; ++q) seg[tile * 4 + q] = -1;
+        ++tile; q = 0;
+      }
+      if (pass == 0) sched[1] = tile;
+      else sched[0] = tile;
+    }
+  }
+}
+
+struct RowMaps { CUtensorMap m[4]; };  // boxes of 16, 32, 64, 128 rows
+
+__global__ void __launch_bounds__(AT_THREADS, 1)
+assoc_frame2_kernel(const __grid_constant__ RowMaps tmR, const __grid_constant__ CUtensorMap tmF, AssocArgs a, int dp,
+                    int n_dtiles, int bn_box, const int32_t* __restrict__ sched) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  float* part = reinterpret_cast<float*>(smem + (size_t)A2_STAGES * AT_STAGE_BYTES);  // [2][4][AT_BN] per-quadrant column maxima
+  double* trk = reinterpret_cast<double*>(part + 2 * 4 * AT_BN);                       // [2][4][32] x4 | SI | tlwh box per segment
+  uint64_t* bars = reinterpret_cast<uint64_t*>(trk + 2 * 4 * 32);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * A2_STAGES + 4);
+
+  const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);
+  const int lane = threadIdx.x & 31;
+  const uint32_t bar_full = ptx::smem_u32(bars);
+  const uint32_t bar_empty = ptx::smem_u32(bars + A2_STAGES);
+  const uint32_t bar_tfull = ptx::smem_u32(bars + 2 * A2_STAGES);
+  const uint32_t bar_tempty = ptx::smem_u32(bars + 2 * A2_STAGES + 2);
+  const uint32_t smem_base = ptx::smem_u32(smem);
+  const int num_kb = dp / AT_BK;
+  const uint32_t b_plane = (uint32_t)bn_box * AT_BK * 2;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < A2_STAGES; ++s) {
+      ptx::mbar_init(bar_full + 8 * s, 1);
+      ptx::mbar_init(bar_empty + 8 * s, 1);
+    }
+    for (int s = 0; s < 2; ++s) {
+      ptx::mbar_init(bar_tfull + 8 * s, 1);
+      ptx::mbar_init(bar_tempty + 8 * s, 4);
+    }
+    ptx::fence_barrier_init();
+#pragma unroll
+    for (int i = 0; i < 4; ++i) ptx::prefetch_tensormap(&tmR.m[i]);
+    ptx::prefetch_tensormap(&tmF);
+  }
+  if (warp == 1) {
+    ptx::tmem_alloc(ptx::smem_u32(tmem_slot), 512);
+    ptx::tmem_relinquish();
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  const int n_tiles = sched[0], n_real = sched[1];
+  const int32_t* seg = sched + 4;
+  const int total = n_tiles * n_dtiles;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int w = blockIdx.x; w < total; w += gridDim.x) {
+        const int tile = w / n_dtiles, dt = w - tile * n_dtiles;
+        if (tile >= n_real) continue;
+        // the tile's tracks: first gallery row, rows to fetch (ceil16(count)) and row offset inside the tile
+        int grow[4], nrow[4], roff[4], nseg = 0;
+        uint32_t a_bytes = 0;
+        for (int q = 0; q < 4; ++q) {
+          const int t = seg[tile * 4 + q];
+          if (t < 0 || (q > 0 && seg[tile * 4 + q - 1] == t)) continue;
+          const int slot = a.trk_slot[t];
+          const int r16 = (a.gcount[slot] + 15) & ~15;
+          grow[nseg] = slot * a.budget; nrow[nseg] = r16; roff[nseg] = q * 32;
+          a_bytes += (uint32_t)r16 * 128u;
+          ++nseg;
+        }
+        const uint32_t stage_tx = 2 * a_bytes + 2 * b_plane;
+        for (int kb = 0; kb < num_kb; ++kb) {
+          ptx::mbar_wait(bar_empty + 8 * stage, phase ^ 1);
+          const uint32_t full = bar_full + 8 * stage;
+          const uint32_t sb = smem_base + stage * AT_STAGE_BYTES;
+          ptx::mbar_arrive_expect_tx(full, stage_tx);
+          for (int s = 0; s < nseg; ++s) {
+            int done = 0;
+#pragma unroll
+            for (int bi = 3; bi >= 0; --bi) {  // boxes of 128, 64, 32, 16 rows: the binary digits of nrow / 16
+              const int rows = 16 << bi;
+              if (nrow[s] & rows) {
+                const uint32_t dst = sb + (uint32_t)(roff[s] + done) * 128u;
+                ptx::tma_load_2d(dst, &tmR.m[bi], full, kb * AT_BK, grow[s] + done);
+                ptx::tma_load_2d(dst + AT_PLANE, &tmR.m[bi], full, dp + kb * AT_BK, grow[s] + done);
+                done += rows;
+              }
+            }
+          }
+          ptx::tma_load_2d(sb + 2 * AT_PLANE, &tmF, full, kb * AT_BK, dt * AT_BN);
+          ptx::tma_load_2d(sb + 2 * AT_PLANE + b_plane, &tmF, full, dp + kb * AT_BK, dt * AT_BN);
+          if (++stage == A2_STAGES) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      int stage = 0, as = 0;
+      uint32_t phase = 0, aphase = 0;
+      for (int w = blockIdx.x; w < total; w += gridDim.x) {
+        const int tile = w / n_dtiles, dt = w - tile * n_dtiles;
+        if (tile >= n_real) continue;
+        const int n_tile = min(bn_box, (a.M - dt * AT_BN + 15) & ~15);
+        const uint32_t idesc = ptx::umma_idesc_f16(AT_BM, n_tile);
+        ptx::mbar_wait(bar_tempty + 8 * as, aphase ^ 1);
+        ptx::tc_fence_after();
+        const uint32_t d_tmem = tmem_base + as * AT_BN;
+        for (int kb = 0; kb < num_kb; ++kb) {
+          ptx::mbar_wait(bar_full + 8 * stage, phase);
+          ptx::tc_fence_after();
+          const uint32_t sb = smem_base + stage * AT_STAGE_BYTES;
+#pragma unroll
+          for (int kk = 0; kk < AT_BK / 16; ++kk) {
+            const uint64_t ahi = ptx::umma_desc_k_sw128(sb + kk * 32);
+            const uint64_t alo = ptx::umma_desc_k_sw128(sb + AT_PLANE + kk * 32);
+            const uint64_t bhi = ptx::umma_desc_k_sw128(sb + 2 * AT_PLANE + kk * 32);
+            const uint64_t blo = ptx::umma_desc_k_sw128(sb + 2 * AT_PLANE + b_plane + kk * 32);
+            ptx::mma_f16_ss(d_tmem, alo, bhi, idesc, (kb | kk) != 0);
+            ptx::mma_f16_ss(d_tmem, ahi, blo, idesc, 1);
+            ptx::mma_f16_ss(d_tmem, ahi, bhi, idesc, 1);
+          }
+          ptx::mma_commit(bar_empty + 8 * stage);
+          if (++stage == A2_STAGES) { stage = 0; phase ^= 1; }
+        }
+        ptx::mma_commit(bar_tfull + 8 * as);
+        as ^= 1;
+        if (as == 0) aphase ^= 1;
+      }
+    }
+  } else {
+    const int q = warp & 3;               // TMEM lane quadrant of this warp = quadrant of the tile
+    const int e = threadIdx.x - 64;       // 0..127
+    int as = 0, it = 0;
+    uint32_t aphase = 0;
+    for (int w = blockIdx.x; w < total; w += gridDim.x, ++it) {
+      const int tile = w / n_dtiles, dt = w - tile * n_dtiles;
+      const bool real = tile < n_real;
+      const int n_cols = min(AT_BN, a.M - dt * AT_BN);
+      const int4 sg4 = *reinterpret_cast<const int4*>(seg + tile * 4);
+      auto SG = [&](int i) { return i == 0 ? sg4.x : (i == 1 ? sg4.y : (i == 2 ? sg4.z : sg4.w)); };  // (no local array)
+      const int t_mine = SG(q);
+      float* mypart = part + ((it & 1) * 4 + q) * AT_BN;
+      double* mytrk = trk + ((it & 1) * 4 + q) * 32;
+      // this quadrant's track state (every quadrant stages its own copy: the final pass reads the first quadrant's)
+      if (t_mine >= 0) {
+        if (lane < 4) mytrk[lane] = a.trk_mean[(size_t)t_mine * 8 + lane];
+        else if (lane < 20) mytrk[lane] = a.trk_SI ? a.trk_SI[(size_t)t_mine * 16 + (lane - 4)] : 0.0;
+        else if (lane == 20) mean_to_tlwh(a.trk_mean + (size_t)t_mine * 8, mytrk + 20);
+      }
+      if (real) {
+        int chunk = 0, cnt = 0;
+        if (t_mine >= 0) {
+#pragma unroll
+          for (int p = 0; p < 4; ++p) chunk += (p < q && SG(p) == t_mine) ? 1 : 0;
+          cnt = a.gcount[a.trk_slot[t_mine]];
+        }
+        ptx::mbar_wait(bar_tfull + 8 * as, aphase);
+        ptx::tc_fence_after();
+        const bool valid = t_mine >= 0 && chunk * 32 + lane < cnt;
+        const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + as * AT_BN;
+        if (t_mine >= 0) {  // warp-uniform
+#pragma unroll 1
+          for (int c = 0; c * 32 < n_cols; ++c) {
+            uint32_t r[32];
+            ptx::tmem_ld_32x32b_x32(taddr + c * 32, r);
+            ptx::tmem_ld_wait();
+            float v[32];
+#pragma unroll
+            for (int j = 0; j < 32; ++j) v[j] = valid ? __uint_as_float(r[j]) : -INFINITY;
+            mypart[c * 32 + lane] = colmax_transpose(v, lane);
+          }
+        }
+        ptx::tc_fence_before();
+        __syncwarp();
+        if (lane == 0) ptx::mbar_arrive(bar_tempty + 8 * as);
+        as ^= 1;
+        if (as == 0) aphase ^= 1;
+      }
+      asm volatile("bar.sync 1, 128;" ::: "memory");  // the four epilogue warps: partial maxima + track state visible
+      // final pass: every (track of the tile, detection column) pair, 128 threads striding over them
+      const float* p0 = part + (it & 1) * 4 * AT_BN;
+      const double* t0 = trk + (it & 1) * 4 * 32;
+      for (int item = e; item < 4 * n_cols; item += 128) {
+        const int sq = item / n_cols, col = item - sq * n_cols;   // sq = a quadrant that STARTS a track
+        const int t = SG(sq);
+        if (t < 0 || (real && sq > 0 && SG(sq - 1) == t)) continue;
+        const int m = dt * AT_BN + col;
+        const size_t o = (size_t)t * a.M + m;
+        const double* st = t0 + sq * 32;
+        if (a.out_app) {
+          double cost = INFTY_COST, raw = INFTY_COST;
+          if (real) {
+            float mx = p0[sq * AT_BN + col];
+#pragma unroll
+            for (int p = 1; p < 4; ++p)
+              if (p > sq && SG(p) == t) mx = fmaxf(mx, p0[p * AT_BN + col]);
+            raw = (double)__fsub_rn(1.0f, __fmul_rn(mx, UNIT_UNSCALE2));
+            cost = raw;
+          }
+          if (a.out_raw) a.out_raw[o] = raw;
+          if (!(a.flags & REIDB200_ASSOC_NO_GATE)) {
+            double z[4];
+            tlwh_to_xyah_f32(a.det_tlwh + (size_t)m * 4, z);
+            const double gd = maha(z, st, st + 4);
+            if (gd > CHI2INV95_4) cost = INFTY_COST;
+            cost = a.mc_lambda * cost + (1 - a.mc_lambda) * gd;
+          }
+          if ((a.flags & REIDB200_ASSOC_CLAMP_APP) && cost > a.max_dist) cost = a.max_dist + 1e-5;
+          a.out_app[o] = cost;
+        }
+        if (a.out_iou) {
+          double c = INFTY_COST;
+          if (!(a.trk_tsu[t] > 1)) c = 1.0 - iou_one<float>(st + 20, a.det_tlwh + (size_t)m * 4, a.iou_mode);
+          if ((a.flags & REIDB200_ASSOC_CLAMP_IOU) && c > a.max_iou_dist) c = a.max_iou_dist + 1e-5;
+          a.out_iou[o] = c;
+        }
+      }
+    }
+  }
+
+  ptx::tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    ptx::tc_fence_after();
+    ptx::tmem_dealloc(tmem_base, 512);
+  }
+}
+
 // ------------------------------------------------------------------------------------ stand-alone pieces
 template <typename CT>
 __global__ void iou_matrix_kernel(const double* __restrict__ bbox, int T, const CT* __restrict__ cand, int M, int mode,
@@ -584,12 +881,22 @@ __global__ void one_minus_kernel(float* __restrict__ x, size_t n) {
 
 using namespace reidb200;
 
+// ints of a frame schedule for T tracks: header (4) + 4 per tile, at most T tiles with rows + ceil(T / 4) without
+static size_t sched_ints(int T) { return 4 + 4 * ((size_t)T + (size_t)T / 4 + 2); }
+
+static int gallery_maps(reidb200_gallery* g) {
+  int rc = make_operand_map(&g->tm_gallery, g->packed, g->slots * g->budget, g->dp, AT_BM);
+  for (int i = 0; i < 4 && !rc; ++i) rc = make_operand_map(&g->tm_rows[i], g->packed, g->slots * g->budget, g->dp, 16 << i);
+  return rc;
+}
+
 extern "C" int reidb200_gallery_create(int slots, int budget, int d, reidb200_gallery** out) {
   RB_REQUIRE(out && slots > 0 && budget > 0 && d > 0, "gallery_create: bad argument");
   reidb200_gallery* g = new reidb200_gallery();
   g->slots = slots; g->budget = budget; g->d = d; g->dp = padded_dim(d);
   g->feats = nullptr; g->packed = nullptr; g->count = nullptr; g->head = nullptr; g->scratch = nullptr;
   g->det_packed = nullptr; g->det_cap = 1024;
+  g->sched = nullptr; g->sched_cap = slots > 1024 ? slots : 1024;
   g->scratch_rows = slots > 1024 ? slots : 1024;
   const size_t packed_sz = (size_t)slots * budget * 2 * g->dp * sizeof(__half);
   cudaError_t e = cudaMalloc(&g->feats, (size_t)slots * budget * d * sizeof(float));
@@ -599,13 +906,14 @@ extern "C" int reidb200_gallery_create(int slots, int budget, int d, reidb200_ga
   if (e == cudaSuccess) e = cudaMalloc(&g->count, (size_t)slots * sizeof(int32_t));
   if (e == cudaSuccess) e = cudaMalloc(&g->head, (size_t)slots * sizeof(int32_t));
   if (e == cudaSuccess) e = cudaMalloc(&g->scratch, (size_t)2 * g->scratch_rows * sizeof(int32_t));
+  if (e == cudaSuccess) e = cudaMalloc(&g->sched, sched_ints(g->sched_cap) * sizeof(int32_t));
   if (e == cudaSuccess) e = cudaMemset(g->count, 0, (size_t)slots * sizeof(int32_t));
   if (e == cudaSuccess) e = cudaMemset(g->head, 0, (size_t)slots * sizeof(int32_t));
   if (e != cudaSuccess) {
     reidb200_gallery_destroy(g);
     return cuda_fail(e, "gallery_create", __FILE__, __LINE__);
   }
-  int rc = make_operand_map(&g->tm_gallery, g->packed, slots * budget, g->dp, AT_BM);
+  int rc = gallery_maps(g);
   if (rc) { reidb200_gallery_destroy(g); return rc; }
   *out = g;
   return REIDB200_OK;
@@ -640,12 +948,13 @@ extern "C" int reidb200_gallery_resize(reidb200_gallery* g, int new_slots, int n
   cudaFree(g->feats); cudaFree(g->packed); cudaFree(g->count); cudaFree(g->head); cudaFree(g->scratch);
   g->feats = feats; g->packed = packed; g->count = count; g->head = head; g->scratch = scratch;
   g->slots = new_slots; g->budget = new_budget; g->scratch_rows = scratch_rows;
-  return make_operand_map(&g->tm_gallery, g->packed, new_slots * new_budget, g->dp, AT_BM);
+  return gallery_maps(g);
 }
 
 extern "C" int reidb200_gallery_destroy(reidb200_gallery* g) {
   if (!g) return REIDB200_OK;
   cudaFree(g->feats); cudaFree(g->packed); cudaFree(g->det_packed); cudaFree(g->count); cudaFree(g->head); cudaFree(g->scratch);
+  cudaFree(g->sched);
   delete g;
   return REIDB200_OK;
 }
@@ -730,11 +1039,34 @@ extern "C" int reidb200_assoc_frame(reidb200_gallery* g, const float* det_feat, 
   CUtensorMap tmF;
   int rc = make_operand_map(&tmF, g->det_packed, M, g->dp, bn_box);
   if (rc) return rc;
+  const int n_dtiles = ceil_div(M, AT_BN);
+  if (g->budget <= AT_BM && getenv("REIDB200_ASSOC_V2")) {
+    // rings of at most 128 rows: tracks packed into 128-row tiles by quadrants, count-aware loads (assoc_frame2_kernel)
+    if (T > g->sched_cap) {  // grows outside the steady state only (synchronises)
+      RB_CUDA(cudaStreamSynchronize(st));
+      cudaFree(g->sched);
+      g->sched = nullptr;
+      g->sched_cap = T + T / 2;
+      RB_CUDA(cudaMalloc(&g->sched, sched_ints(g->sched_cap) * sizeof(int32_t)));
+    }
+    { ProfScope _ps("assoc_schedule_kernel", st); assoc_schedule_kernel<<<1, 32, 0, st>>>(trk_slot, g->count, T, g->sched); }
+    RB_LAUNCH_CHECK("assoc_schedule_kernel");
+    static DeviceOnce attr2;
+    if (attr2.pending()) {
+      RB_CUDA(cudaFuncSetAttribute(assoc_frame2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)A2_SMEM));
+    }
+    RowMaps rm;
+    for (int i = 0; i < 4; ++i) rm.m[i] = g->tm_rows[i];
+    const long long most = ((long long)T + T / 4 + 2) * n_dtiles;  // upper bound of the work items (the count lives on the device)
+    const int grid = (int)(most < num_sms() ? most : num_sms());
+    { ProfScope _ps("assoc_frame_kernel", st); assoc_frame2_kernel<<<grid, AT_THREADS, A2_SMEM, st>>>(rm, tmF, a, g->dp, n_dtiles, bn_box, g->sched); }
+    RB_LAUNCH_CHECK("assoc_frame2_kernel");
+    return REIDB200_OK;
+  }
   static DeviceOnce attr_done;
   if (attr_done.pending()) {
     RB_CUDA(cudaFuncSetAttribute(assoc_frame_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)AT_SMEM));
   }
-  const int n_dtiles = ceil_div(M, AT_BN);
   const long long total = (long long)T * n_dtiles;
   const int grid = (int)(total < num_sms() ? total : num_sms());
   { ProfScope _ps("assoc_frame_kernel", st); assoc_frame_kernel<<<grid, AT_THREADS, AT_SMEM, st>>>(g->tm_gallery, tmF, a, g->dp, n_dtiles, bn_box); }
@@ -812,3 +1144,140 @@ extern "C" int reidb200_cosine_distance(const float* a, int na, int64_t lda, con
   RB_LAUNCH_CHECK("one_minus_kernel");
   return REIDB200_OK;
 }
+
+// ------------------------------------------------------------------------------------ one frame from host arrays
+// The per-frame host <-> device traffic of a tracker loop in two calls (crops before the backbone, costs
+// after it), each ONE pinned host -> device copy of the small per-frame tables, the kernels, and -- for the costs --
+// ONE device -> host copy of both float64 matrices into pinned memory the caller reads in place.  No per-frame
+// allocation, no Python-side marshalling: plain host pointers and sizes in, pointers into the pinned result out.
+struct reidb200_frame {
+  reidb200_gallery* g;
+  int max_dets, max_tracks;
+  size_t in_cap;            // bytes of one input staging buffer
+  uint8_t* h_in[2];         // pinned
+  uint8_t* d_in[2];
+  cudaEvent_t in_done[2];   // the H2D of staging buffer i has been consumed
+  double* h_out[2];         // pinned [2][max_tracks][max_dets]
+  double* d_out;
+  int turn_in, turn_out;
+};
+
+static size_t frame_in_bytes(int max_dets, int max_tracks) {
+  const size_t crops = (size_t)max_dets * (8 + 12);                                    // crop_off i64 | crop_geom i32[3]
+  const size_t costs = (size_t)max_dets * 16 + (size_t)max_tracks * (4 + 4 + 64 + 128);  // tlwh | slot | tsu | mean | SI
+  return align_up((crops > costs ? crops : costs) + 256, 256);
+}
+
+extern "C" int reidb200_frame_create(reidb200_gallery* g, int max_dets, int max_tracks, reidb200_frame** out) {
+  RB_REQUIRE(g && out && max_dets > 0 && max_tracks > 0, "frame_create: bad argument");
+  reidb200_frame* f = new reidb200_frame();
+  memset(f, 0, sizeof(*f));
+  f->g = g; f->max_dets = max_dets; f->max_tracks = max_tracks;
+  f->in_cap = frame_in_bytes(max_dets, max_tracks);
+  const size_t out_bytes = (size_t)2 * max_tracks * max_dets * sizeof(double);
+  cudaError_t e = cudaSuccess;
+  for (int i = 0; i < 2 && e == cudaSuccess; ++i) {
+    e = cudaMallocHost(&f->h_in[i], f->in_cap);
+    if (e == cudaSuccess) e = cudaMalloc(&f->d_in[i], f->in_cap);
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&f->in_done[i], cudaEventDisableTiming);
+    if (e == cudaSuccess) e = cudaMallocHost(&f->h_out[i], out_bytes);
+  }
+  if (e == cudaSuccess) e = cudaMalloc(&f->d_out, out_bytes);
+  if (e != cudaSuccess) {
+    reidb200_frame_destroy(f);
+    return cuda_fail(e, "frame_create", __FILE__, __LINE__);
+  }
+  *out = f;
+  return REIDB200_OK;
+}
+
+extern "C" int reidb200_frame_destroy(reidb200_frame* f) {
+  if (!f) return REIDB200_OK;
+  for (int i = 0; i < 2; ++i) {
+    if (f->h_in[i]) cudaFreeHost(f->h_in[i]);
+    if (f->d_in[i]) cudaFree(f->d_in[i]);
+    if (f->in_done[i]) cudaEventDestroy(f->in_done[i]);
+    if (f->h_out[i]) cudaFreeHost(f->h_out[i]);
+  }
+  if (f->d_out) cudaFree(f->d_out);
+  delete f;
+  return REIDB200_OK;
+}
+
+// next input staging pair (its previous copy must have been consumed: normally long ago)
+static int frame_next_in(reidb200_frame* f) {
+  const int i = f->turn_in;
+  f->turn_in ^= 1;
+  cudaEventSynchronize(f->in_done[i]);  // an event that was never recorded is complete
+  return i;
+}
+
+extern "C" int reidb200_frame_crops(reidb200_frame* f, const uint8_t* frame, int H, int W, const int32_t* xyxy_host, int n,
+                                    int out_h, int out_w, const float mean_host[3], const float std_host[3], float* out,
+                                    void* stream) {
+  if (n == 0) return REIDB200_OK;
+  RB_REQUIRE(f && frame && xyxy_host && out && n > 0 && H > 0 && W > 0, "frame_crops: bad argument");
+  RB_REQUIRE(n <= f->max_dets, "frame_crops: %d boxes exceed the context's %d", n, f->max_dets);
+  cudaStream_t st = (cudaStream_t)stream;
+  const int bi = frame_next_in(f);
+  int64_t* off = reinterpret_cast<int64_t*>(f->h_in[bi]);
+  int32_t* geom = reinterpret_cast<int32_t*>(f->h_in[bi] + (size_t)n * 8);
+  for (int i = 0; i < n; ++i) {
+    // img[y1:y2, x1:x2] (strong_sort.py:153-155): numpy clips the slice end at the frame border
+    const int x1 = xyxy_host[4 * i], y1 = xyxy_host[4 * i + 1];
+    const int x2 = xyxy_host[4 * i + 2] < W ? xyxy_host[4 * i + 2] : W, y2 = xyxy_host[4 * i + 3] < H ? xyxy_host[4 * i + 3] : H;
+    RB_REQUIRE(x1 >= 0 && y1 >= 0, "frame_crops: box %d has a negative origin", i);
+    RB_REQUIRE(x2 > x1 && y2 > y1, "frame_crops: empty crop: box %d has zero area after clamping", i);
+    off[i] = ((int64_t)y1 * W + x1) * 3;
+    geom[3 * i] = y2 - y1; geom[3 * i + 1] = x2 - x1; geom[3 * i + 2] = W * 3;
+  }
+  const size_t bytes = (size_t)n * 20;
+  RB_CUDA(cudaMemcpyAsync(f->d_in[bi], f->h_in[bi], bytes, cudaMemcpyHostToDevice, st));
+  RB_CUDA(cudaEventRecord(f->in_done[bi], st));
+  return reidb200_crop_resize_norm(frame, reinterpret_cast<const int64_t*>(f->d_in[bi]),
+                                   reinterpret_cast<const int32_t*>(f->d_in[bi] + (size_t)n * 8), n, out_h, out_w, mean_host,
+                                   std_host, REIDB200_RESIZE_CV_LINEAR, out, stream);
+}
+
+extern "C" int reidb200_frame_costs(reidb200_frame* f, const float* det_feat, int64_t ldf, const float* det_tlwh_host, int M,
+                                    const int32_t* trk_slot_host, const double* trk_mean_host, const double* trk_SI_host,
+                                    const int32_t* trk_tsu_host, int T, double mc_lambda, double max_dist, double max_iou_dist,
+                                    int iou_mode, int flags, const double** out_app_host, const double** out_iou_host,
+                                    void* stream) {
+  RB_REQUIRE(f && out_app_host && out_iou_host, "frame_costs: bad argument");
+  *out_app_host = *out_iou_host = nullptr;
+  if (T == 0 || M == 0) return REIDB200_OK;
+  RB_REQUIRE(det_feat && det_tlwh_host && trk_slot_host && trk_mean_host && trk_SI_host && trk_tsu_host && T > 0 && M > 0,
+             "frame_costs: bad argument");
+  RB_REQUIRE(M <= f->max_dets && T <= f->max_tracks, "frame_costs: %d detections / %d tracks exceed the context's %d / %d", M, T,
+             f->max_dets, f->max_tracks);
+  cudaStream_t st = (cudaStream_t)stream;
+  const int bi = frame_next_in(f);
+  // layout (every piece 8-byte aligned): mean f64[T,8] | SI f64[T,16] | tlwh f32[M,4] | slot i32[T] | tsu i32[T]
+  uint8_t* h = f->h_in[bi];
+  const size_t o_mean = 0, o_si = o_mean + (size_t)T * 64, o_tlwh = o_si + (size_t)T * 128, o_slot = o_tlwh + (size_t)M * 16,
+               o_tsu = o_slot + align_up((size_t)T * 4, 8), total = o_tsu + (size_t)T * 4;
+  memcpy(h + o_mean, trk_mean_host, (size_t)T * 64);
+  memcpy(h + o_si, trk_SI_host, (size_t)T * 128);
+  memcpy(h + o_tlwh, det_tlwh_host, (size_t)M * 16);
+  memcpy(h + o_slot, trk_slot_host, (size_t)T * 4);
+  memcpy(h + o_tsu, trk_tsu_host, (size_t)T * 4);
+  uint8_t* d = f->d_in[bi];
+  RB_CUDA(cudaMemcpyAsync(d, h, total, cudaMemcpyHostToDevice, st));
+  RB_CUDA(cudaEventRecord(f->in_done[bi], st));
+  double* app = f->d_out;
+  double* iou = f->d_out + (size_t)T * M;
+  int rc = reidb200_assoc_frame(f->g, det_feat, ldf, reinterpret_cast<const float*>(d + o_tlwh), M,
+                                reinterpret_cast<const int32_t*>(d + o_slot), reinterpret_cast<const double*>(d + o_mean),
+                                reinterpret_cast<const double*>(d + o_si), reinterpret_cast<const int32_t*>(d + o_tsu), T, mc_lambda,
+                                max_dist, max_iou_dist, iou_mode, flags, app, nullptr, iou, stream);
+  if (rc) return rc;
+  const int bo = f->turn_out;
+  f->turn_out ^= 1;
+  RB_CUDA(cudaMemcpyAsync(f->h_out[bo], f->d_out, (size_t)2 * T * M * sizeof(double), cudaMemcpyDeviceToHost, st));
+  RB_CUDA(cudaStreamSynchronize(st));
+  *out_app_host = f->h_out[bo];
+  *out_iou_host = f->h_out[bo] + (size_t)T * M;
+  return REIDB200_OK;
+}
+

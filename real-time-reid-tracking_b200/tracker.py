@@ -44,6 +44,97 @@ def frame_costs(metric, det_feat, det_tlwh, trk_ids, trk_confirmed, trk_mean, tr
                            out_app=out[0], out_iou=out[1])
 
 
+class FrameContext:
+    """A tracker loop's per-frame host <-> device traffic through two C calls (csrc/assoc.cu reidb200_frame_*): `crops`
+    before the backbone, `costs` after it.  Host arrays go in as plain pointers (they must already be C-contiguous with the
+    dtypes below: no per-frame conversion), each call makes ONE pinned host->device copy; `costs` returns numpy views of
+    the pinned result of ONE device->host copy.  One context per video stream (it owns the staging buffers).
+
+        fc = FrameContext(metric, max_dets=256, max_tracks=512)
+        batch = fc.crops(frame_cuda_u8, xyxy_int32)                 # f32[M,3,256,128] on the device, asynchronous
+        feats = backbone(batch)                                     # f32[M,d] CUDA
+        app, iou = fc.costs(feats, det_tlwh_f32, trk_ids, trk_confirmed, mean_f64, SI_f64, tsu_i32, 0.995, 0.2, 0.7)
+
+    app / iou are float64 [T,M] exactly as tracker.frame_costs(...clamp=True) + costs_to_host return them; they stay valid
+    until the call after the next."""
+
+    def __init__(self, metric, max_dets=256, max_tracks=512, out_size=(128, 256), norm=((0.5, 0.5, 0.5), (0.5, 0.5, 0.5))):
+        import ctypes as C
+
+        self.metric = metric
+        self.max_dets, self.max_tracks = int(max_dets), int(max_tracks)
+        self.out_w, self.out_h = int(out_size[0]), int(out_size[1])
+        self._mean, self._std = ops._f3(norm[0]), ops._f3(norm[1])
+        self._lib = L.load()
+        self._h = None
+        self._gallery = None
+        self._C = C
+        self._pa, self._pi = C.c_void_p(), C.c_void_p()
+        self._crops = None
+
+    def _handle(self, d=None):
+        if self._h is None or self._gallery is not self.metric._gallery:
+            if self.metric._gallery is None:
+                self.metric._ensure(int(d))
+            self.close()
+            self._gallery = self.metric._gallery
+            h = self._C.c_void_p()
+            with torch.cuda.device(self._gallery.device):
+                L.check(self._lib.reidb200_frame_create(self._gallery._h, self.max_dets, self.max_tracks, self._C.byref(h)))
+            self._h = h
+        return self._h
+
+    def close(self):
+        if getattr(self, "_h", None) is not None and L is not None:
+            self._lib.reidb200_frame_destroy(self._h)
+            self._h = None
+
+    __del__ = close
+
+    def crops(self, frame, xyxy, out=None):
+        """frame: u8[H,W,3] CUDA tensor; xyxy: int32 [M,4] host array -> f32[M,3,out_h,out_w] CUDA (asynchronous)."""
+        n = int(xyxy.shape[0])
+        H, W = int(frame.shape[0]), int(frame.shape[1])
+        if out is None:
+            if self._crops is None or self._crops.shape[0] < n:
+                self._crops = torch.empty((max(n, self.max_dets), 3, self.out_h, self.out_w), dtype=torch.float32, device=frame.device)
+            out = self._crops[:n]
+        if n:
+            if xyxy.dtype != np.int32 or not xyxy.flags.c_contiguous:
+                xyxy = np.ascontiguousarray(xyxy, dtype=np.int32)
+            L.check(self._lib.reidb200_frame_crops(self._handle(), frame.data_ptr(), H, W, xyxy.ctypes.data, n, self.out_h, self.out_w,
+                                                   self._mean, self._std, out.data_ptr(), L.stream_ptr()))
+        return out
+
+    def costs(self, det_feat, det_tlwh, trk_ids, trk_confirmed, trk_mean, trk_SI, trk_tsu, mc_lambda, max_dist=None,
+              max_iou_dist=0.7, iou_mode="iou", clamp=True, slots=None):
+        """(app f64[T,M], iou f64[T,M]) numpy views of the pinned result.  det_feat: f32[M,d] CUDA; det_tlwh f32[M,4],
+        trk_mean f64[T,8], trk_SI f64[T,16] (or [T,4,4]), trk_tsu i32[T]: C-contiguous host arrays.  `slots` (i32[T],
+        -1 = no gallery row, e.g. unconfirmed tracks) may be passed to skip the id -> slot lookup."""
+        T, M = len(trk_tsu), int(det_tlwh.shape[0])
+        if T == 0 or M == 0:
+            z = np.zeros((T, M))
+            return z, z.copy()
+        if slots is None:
+            slot_of = self.metric._slot_of
+            slots = np.fromiter((slot_of.get(int(i), -1) if c else -1 for i, c in zip(trk_ids, trk_confirmed)), np.int32, T)
+        max_dist = self.metric.matching_threshold if max_dist is None else max_dist
+        flags = (L.ASSOC_CLAMP_APP | L.ASSOC_CLAMP_IOU) if clamp else 0
+        f32, f64, i32 = np.float32, np.float64, np.int32
+        det_tlwh = det_tlwh if det_tlwh.dtype == f32 and det_tlwh.flags.c_contiguous else np.ascontiguousarray(det_tlwh, f32)
+        trk_mean = trk_mean if trk_mean.dtype == f64 and trk_mean.flags.c_contiguous else np.ascontiguousarray(trk_mean, f64)
+        trk_SI = trk_SI if trk_SI.dtype == f64 and trk_SI.flags.c_contiguous else np.ascontiguousarray(trk_SI, f64)
+        trk_tsu = trk_tsu if isinstance(trk_tsu, np.ndarray) and trk_tsu.dtype == i32 and trk_tsu.flags.c_contiguous else np.ascontiguousarray(trk_tsu, i32)
+        L.check(self._lib.reidb200_frame_costs(self._handle(det_feat.shape[1]), det_feat.data_ptr(), det_feat.stride(0), det_tlwh.ctypes.data, M,
+                                               slots.ctypes.data, trk_mean.ctypes.data, trk_SI.ctypes.data, trk_tsu.ctypes.data, T,
+                                               float(mc_lambda), float(max_dist), float(max_iou_dist),
+                                               L.IOU_DIOU if iou_mode == "diou" else L.IOU_PLAIN, flags,
+                                               self._C.byref(self._pa), self._C.byref(self._pi), L.stream_ptr()))
+        app = np.ctypeslib.as_array(self._C.cast(self._pa, self._C.POINTER(self._C.c_double)), shape=(T, M))
+        iou = np.ctypeslib.as_array(self._C.cast(self._pi, self._C.POINTER(self._C.c_double)), shape=(T, M))
+        return app, iou
+
+
 _host_out = {"bufs": [None, None], "turn": 0}
 
 

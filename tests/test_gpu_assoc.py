@@ -61,8 +61,13 @@ def test_gallery_ring_semantics(rb):
             np.testing.assert_allclose(np.stack(metric.samples[k]), np.stack(ref[k]), atol=1e-7)
 
 
-def test_sequence_costs_and_assignments(rb, golden):
+@pytest.mark.parametrize("packed", [False, True])
+def test_sequence_costs_and_assignments(rb, golden, monkeypatch, packed):
     from reidb200 import tracker as TR
+
+    monkeypatch.setenv("REIDB200_ASSOC_V2" if packed else "REIDB200_ASSOC_V1", "1")
+    if not packed:
+        monkeypatch.delenv("REIDB200_ASSOC_V2", raising=False)
 
     g = golden("assoc_seq")
     max_dist, max_iou, lam, budget = (float(g["cfg_max_dist"]), float(g["cfg_max_iou_dist"]), float(g["cfg_mc_lambda"]),
@@ -119,12 +124,18 @@ def test_mot_shaped_frame_vs_oracle(rb, M, T):
     assert keep1 == keep2 and len(keep1) > 0
 
 
-@pytest.mark.parametrize("M,T,budget,D", [(5, 3, 4, 24), (300, 40, 100, 96), (70, 9, 150, 512), (16, 130, 100, 64)])
-def test_tensor_core_kernel_vs_simt_vs_oracle(rb, M, T, budget, D):
+@pytest.mark.parametrize("packed", [False, True])
+@pytest.mark.parametrize("M,T,budget,D", [(5, 3, 4, 24), (300, 40, 100, 96), (70, 9, 150, 512), (16, 130, 100, 64), (200, 300, 100, 512),
+                                          (33, 57, 128, 128), (9, 21, 31, 64)])
+def test_tensor_core_kernel_vs_simt_vs_oracle(rb, monkeypatch, M, T, budget, D, packed):
     """tcgen05 frame kernel against the fp32 SIMT kernel and the oracle: > 256 detections (detection tiles), budget > 128
     (row tiles), feature dimension not a multiple of 64 (zero padded k-blocks), empty and unknown slots."""
     from reidb200 import ops, synth
 
+    # packed: tracks packed into 128-row tiles by quadrants with count-aware loads (assoc_frame2_kernel, rings <= 128 rows)
+    monkeypatch.setenv("REIDB200_ASSOC_V2" if packed else "REIDB200_ASSOC_V1", "1")
+    if not packed:
+        monkeypatch.delenv("REIDB200_ASSOC_V2", raising=False)
     fr = synth.mot_frame(M=M, T=T, budget=budget, D=D, seed=M + T)
     samples = fr["samples"]
     gal = ops.Gallery(T + 2, budget, D)
@@ -158,3 +169,34 @@ def test_empty_inputs(rb):
     assert m == [] and ut == [] and ud == []
     assert LA.min_cost_matching(None, 0.2, [], [], [], [])[0] == []
     assert IM.iou(np.array([0., 0, 1, 1]), np.zeros((0, 4))).shape == (0,)
+
+
+def test_frame_context_equals_frame_costs(rb, monkeypatch):
+    """tracker.FrameContext (two C calls per frame from host arrays) returns the crops of preprocess_frame and the cost
+    matrices of frame_costs + costs_to_host, bit for bit, over frames of different sizes through the same context."""
+    from reidb200 import matching as MT, preprocess, synth, tracker as TR
+
+    monkeypatch.setenv("REIDB200_ASSOC_V2", "1")
+    for seed, (M, T) in enumerate([(30, 100), (200, 300), (7, 12)]):
+        fr = synth.mot_frame(M=M, T=T, budget=100, D=128, seed=20 + seed)
+        metric = MT.NearestNeighborDistanceMetric("cosine", 0.2, 100, max_tracks=T)
+        metric.partial_fit(np.concatenate(fr["samples"], 0), np.repeat(np.arange(T), [len(s) for s in fr["samples"]]), list(range(T)))
+        fc = TR.FrameContext(metric, max_dets=256, max_tracks=512)
+        H, W = fr["img"].shape[:2]
+        xyxy = preprocess.xywh_to_xyxy(fr["det_xywh"], W, H)
+        xyxy = xyxy[(xyxy[:, 2] > xyxy[:, 0]) & (xyxy[:, 3] > xyxy[:, 1])]
+        frame = torch.from_numpy(fr["img"]).cuda()
+        conf = np.arange(T) % 5 != 0
+        for rep in range(3):  # the staging buffers alternate
+            crops = fc.crops(frame, xyxy)
+            assert torch.equal(crops, preprocess.preprocess_frame(frame, xyxy))
+            det_feat = torch.from_numpy(fr["det_feat"]).cuda()
+            app, iou = fc.costs(det_feat, fr["det_tlwh"], np.arange(T), conf, fr["trk_mean"], fr["trk_SI"], fr["trk_tsu"], 0.995, 0.2, 0.7)
+            a2, _, i2 = TR.frame_costs(metric, det_feat, fr["det_tlwh"], np.arange(T), conf, fr["trk_mean"], fr["trk_SI"], fr["trk_tsu"],
+                                       0.995, 0.2, 0.7)
+            assert np.array_equal(app, a2.cpu().numpy()) and np.array_equal(iou, i2.cpu().numpy())
+            assert (app[~conf] == 0.2 + 1e-5).all()   # unconfirmed rows: 1e5 before the clamp
+        with pytest.raises(ValueError):
+            fc.crops(frame, np.array([[5, 5, 5, 40]], np.int32))
+    z = fc.costs(det_feat[:0], fr["det_tlwh"][:0], [], [], np.zeros((0, 8)), np.zeros((0, 16)), np.zeros(0, np.int32), 0.995)
+    assert z[0].shape == (0, 0)

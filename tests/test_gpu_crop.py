@@ -91,3 +91,28 @@ def test_empty_and_bad_crops(rb):
         P.preprocess_frame(img, np.array([[5, 5, 5, 20]], np.int32))
     with pytest.raises(ValueError):
         P.preprocess_crops([np.zeros((0, 4, 3), np.uint8)])
+
+
+@pytest.mark.parametrize("kernel", ["v3", "v4"])
+def test_cv_linear_kernel_variants_bit_equal(rb, monkeypatch, kernel):
+    """Both crop kernels (thread = output column; thread = four adjacent columns with 128-bit stores and the conversion-free
+    byte -> float step) against the oracle, bit for bit, on a frame that holds every byte value in every channel, crops that
+    are up-scaled, down-scaled, one pixel wide, and clamped at the frame border."""
+    from reidb200 import preprocess as P
+
+    monkeypatch.setenv("REIDB200_CROP_V4" if kernel == "v4" else "REIDB200_CROP_V3", "1")
+    if kernel == "v3":
+        monkeypatch.delenv("REIDB200_CROP_V4", raising=False)
+    rng = np.random.default_rng(11)
+    H, W = 300, 420
+    img = rng.integers(0, 256, (H, W, 3), dtype=np.uint8)
+    img[:256, 0, :] = np.arange(256, dtype=np.uint8)[:, None]   # every byte value in every channel
+    img[0, :256, 1] = np.arange(256, dtype=np.uint8)
+    boxes = np.array([[0, 0, 1, 256], [0, 0, 256, 1], [0, 0, 420, 300], [17, 9, 145, 265], [100, 50, 131, 120], [3, 7, 303, 290],
+                      [400, 280, 420, 300], [50, 60, 51, 61], [10, 10, 138, 266]], np.int32)
+    got = P.preprocess_frame(img, boxes).cpu().numpy()
+    want = O.preprocess_deepsort([img[b[1]:b[3], b[0]:b[2]] for b in boxes])
+    assert np.array_equal(got, want)
+    got_i = P.preprocess_frame(img, boxes, norm=P.IMAGENET_NORM).cpu().numpy()   # std not a power of two: true division
+    want_i = O.preprocess_deepsort([img[b[1]:b[3], b[0]:b[2]] for b in boxes], mean=P.IMAGENET_NORM[0], std=P.IMAGENET_NORM[1])
+    assert np.array_equal(got_i, want_i)
