@@ -15,15 +15,14 @@
 struct reidb200_gallery {
   int slots, budget, d, dp;
   float* feats;      // [slots, budget, d] L2-normalised rows (ring per slot)
-  __half* packed;  // [slots*budget, 2*dp] the same rows as fp16 hi|lo planes: A operand of the tcgen05 frame kernel
+  __half* packed;    // the same rows as fp16 hi|lo planes in TILE-IMAGE layout (img_* below): A operand of the frame kernels
+  int rb;            // rows of one (slot, k-block, plane) region of `packed`: budget rounded up to 16
   int32_t* count;    // [slots] valid rows
   int32_t* head;     // [slots] next write position
   int32_t* scratch;  // [2*scratch_rows] per-row destination / rows-after
   int scratch_rows;
-  __half* det_packed;  // [det_cap, 2*dp] L2-normalised detection features of the current frame, hi|lo planes
-  int det_cap;
-  CUtensorMap tm_gallery;     // TMA descriptor of `packed` (box 64 x 128)
-  CUtensorMap tm_rows[4];     // the same tensor with boxes of 16 / 32 / 64 / 128 rows: count-aware loads of a track's rows
+  __half* det_packed;  // L2-normalised detection features of the current frame, tile-image layout, regions of det_cap rows
+  int det_cap;         // multiple of 16
   int32_t* sched;             // frame schedule written by assoc_schedule (tracks packed into 128-row tiles by 32-row quadrants)
   int sched_cap;              // tracks the schedule buffer holds
 };
@@ -36,6 +35,18 @@ constexpr double CHI2INV95_4 = 9.4877;    // boxmot/utils/matching.py:12-22
 // 22 significand bits survive); the frame kernel multiplies the accumulator by 2^-28.
 constexpr float UNIT_SCALE = 16384.0f;
 constexpr float UNIT_UNSCALE2 = 1.0f / (16384.0f * 16384.0f);
+
+// TILE-IMAGE layout of a packed operand (gallery ring, frame detections).  For every k-block of 64 features and each of
+// the two fp16 planes there is one contiguous REGION of `region_rows` rows x 128 bytes, and inside a region the 16-byte
+// chunks of row r are XOR-swizzled by (r & 7): exactly the bytes TMA's SWIZZLE_128B would leave in shared memory for a
+// K-major operand tile.  Any run of rows that starts at a multiple of 8 is therefore ONE contiguous piece of global memory
+// that a single cp.async.bulk drops into an operand stage -- measured: a 128-row x 64-column TMA tensor box is 128 separate
+// 128-byte requests (row pitch 2 KB), and at two tracks + 208 detections per stage the frame kernel spent ~2 us per
+// k-block waiting for ~670 of them.
+//   region index: gallery (slot * nkb + kb) * 2 + plane, detections kb * 2 + plane;  half index inside a region:
+__host__ __device__ __forceinline__ size_t img_half(int row, int kk) {  // kk = feature index inside the k-block (0..63)
+  return (size_t)row * 64 + (size_t)((((kk >> 3) ^ (row & 7)) << 3) | (kk & 7));
+}
 
 // ------------------------------------------------------------------------------------ gallery
 // dst[i] = ring position of row i (or -1 when a later row of the same call overwrites it)
@@ -58,7 +69,7 @@ __global__ void pf_assign_kernel(const int32_t* __restrict__ slot_of_row, int n,
 // warp per row: a / ||a|| in fp32 (matching.py:294-296), written to its ring position
 __global__ void __launch_bounds__(256)
 pf_write_kernel(const float* __restrict__ feats, int64_t ldf, const int32_t* __restrict__ slot_of_row,
-                const int32_t* __restrict__ dst, int n, int budget, int d, int dp, float* __restrict__ gal,
+                const int32_t* __restrict__ dst, int n, int budget, int d, int dp, int rb, float* __restrict__ gal,
                 __half* __restrict__ packed) {
   const int i = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int lane = threadIdx.x & 31;
@@ -69,23 +80,32 @@ pf_write_kernel(const float* __restrict__ feats, int64_t ldf, const int32_t* __r
   float s = 0.f;
   for (int k = lane; k < d; k += 32) { const float v = src[k]; s = fmaf(v, v, s); }
   s = sqrtf(warp_sum(s));
-  const size_t row = (size_t)slot_of_row[i] * budget + p;
-  float* o = gal + row * d;
-  __half* hi = packed + row * 2 * dp;
-  __half* lo = hi + dp;
-  for (int k = lane; k < d; k += 32) {
-    const float v = __fdiv_rn(src[k], s);
-    o[k] = v;
+  const int slot = slot_of_row[i];
+  float* o = gal + ((size_t)slot * budget + p) * d;
+  const int nkb = dp / 64;
+  const size_t region = (size_t)rb * 64;
+  for (int k = lane; k < dp; k += 32) {
+    const float v = k < d ? __fdiv_rn(src[k], s) : 0.f;
+    if (k < d) o[k] = v;
     const float vs = __fmul_rn(v, UNIT_SCALE);
     const __half h = __float2half_rn(vs);
-    hi[k] = h;
-    lo[k] = __float2half_rn(__fsub_rn(vs, __half2float(h)));
+    __half* hi = packed + ((size_t)(slot * nkb + (k >> 6)) * 2) * region + img_half(p, k & 63);
+    hi[0] = h;
+    hi[region] = __float2half_rn(__fsub_rn(vs, __half2float(h)));
   }
 }
 
 // warp per detection: f / ||f|| in fp32 (matching.py:294-296) split into fp16 hi|lo planes (B operand of the frame kernel)
+__device__ void assoc_schedule_block(const int32_t* __restrict__ trk_slot, const int32_t* __restrict__ gcount, int T,
+                                     int32_t* __restrict__ sched);
+
 __global__ void __launch_bounds__(256)
-det_pack_kernel(const float* __restrict__ feats, int64_t ldf, int n, int d, int dp, __half* __restrict__ packed) {
+det_pack_kernel(const float* __restrict__ feats, int64_t ldf, int n, int d, int dp, int det_rows, __half* __restrict__ packed,
+                const int32_t* __restrict__ trk_slot, const int32_t* __restrict__ gcount, int T, int32_t* __restrict__ sched) {
+  if (sched != nullptr && blockIdx.x == gridDim.x - 1) {  // the extra block: frame schedule of the packed-tile kernel
+    assoc_schedule_block(trk_slot, gcount, T, sched);
+    return;
+  }
   const int i = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int lane = threadIdx.x & 31;
   if (i >= n) return;
@@ -93,13 +113,13 @@ det_pack_kernel(const float* __restrict__ feats, int64_t ldf, int n, int d, int 
   float s = 0.f;
   for (int k = lane; k < d; k += 32) { const float v = src[k]; s = fmaf(v, v, s); }
   s = sqrtf(warp_sum(s));
-  __half* hi = packed + (size_t)i * 2 * dp;
-  __half* lo = hi + dp;
+  const size_t region = (size_t)det_rows * 64;
   for (int k = lane; k < dp; k += 32) {
     const float v = k < d ? __fmul_rn(__fdiv_rn(src[k], s), UNIT_SCALE) : 0.f;
     const __half h = __float2half_rn(v);
-    hi[k] = h;
-    lo[k] = __float2half_rn(__fsub_rn(v, __half2float(h)));
+    __half* hi = packed + ((size_t)(k >> 6) * 2) * region + img_half(i, k & 63);
+    hi[0] = h;
+    hi[region] = __float2half_rn(__fsub_rn(v, __half2float(h)));
   }
 }
 
@@ -137,15 +157,21 @@ __global__ void gal_read_kernel(const float* __restrict__ gal, const int32_t* __
 // to ring positions 0..count-1 of the new layout (head = count mod new budget), bit for bit
 __global__ void gal_resize_kernel(const float* __restrict__ src, const __half* __restrict__ src_packed,
                                   const int32_t* __restrict__ src_head, const int32_t* __restrict__ src_count, int old_budget,
-                                  int new_budget, int d, int dp, float* __restrict__ dst, __half* __restrict__ dst_packed,
-                                  int32_t* __restrict__ dst_head, int32_t* __restrict__ dst_count) {
+                                  int old_rb, int new_budget, int new_rb, int d, int dp, float* __restrict__ dst,
+                                  __half* __restrict__ dst_packed, int32_t* __restrict__ dst_head, int32_t* __restrict__ dst_count) {
   const int slot = blockIdx.x;
   const int c = src_count[slot], h = src_head[slot];
+  const int nkb = dp / 64;
+  const size_t reg_o = (size_t)old_rb * 64, reg_n = (size_t)new_rb * 64;
   for (int r = blockIdx.y; r < c; r += gridDim.y) {
-    const size_t from = (size_t)slot * old_budget + ((h - c + r) % old_budget + old_budget) % old_budget;
-    const size_t to = (size_t)slot * new_budget + r;
-    for (int k = threadIdx.x; k < d; k += blockDim.x) dst[to * d + k] = src[from * d + k];
-    for (int k = threadIdx.x; k < 2 * dp; k += blockDim.x) dst_packed[to * 2 * dp + k] = src_packed[from * 2 * dp + k];
+    const int from = ((h - c + r) % old_budget + old_budget) % old_budget;
+    for (int k = threadIdx.x; k < d; k += blockDim.x)
+      dst[((size_t)slot * new_budget + r) * d + k] = src[((size_t)slot * old_budget + from) * d + k];
+    for (int k = threadIdx.x; k < 2 * dp; k += blockDim.x) {  // both planes: the row moves to ring position r (re-swizzled)
+      const int plane = k >= dp ? 1 : 0, kf = k - plane * dp;
+      const size_t ro = (size_t)(slot * nkb + (kf >> 6)) * 2 + plane;
+      dst_packed[ro * reg_n + img_half(r, kf & 63)] = src_packed[ro * reg_o + img_half(from, kf & 63)];
+    }
   }
   if (blockIdx.y == 0 && threadIdx.x == 0) { dst_count[slot] = c; dst_head[slot] = c % new_budget; }
 }
@@ -366,7 +392,7 @@ __device__ __forceinline__ float colmax_transpose(float (&v)[32], int lane) {
 }
 
 __global__ void __launch_bounds__(AT_THREADS, 1)
-assoc_frame_kernel(const __grid_constant__ CUtensorMap tmG, const __grid_constant__ CUtensorMap tmF, AssocArgs a, int dp,
+assoc_frame_kernel(const __half* __restrict__ gpacked, int rb, const __half* __restrict__ dpacked, int det_rows, AssocArgs a, int dp,
                    int n_dtiles, int bn_box) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
@@ -384,7 +410,6 @@ assoc_frame_kernel(const __grid_constant__ CUtensorMap tmG, const __grid_constan
   const uint32_t smem_base = ptx::smem_u32(smem);
   const int num_kb = dp / AT_BK;
   const uint32_t b_plane = (uint32_t)bn_box * AT_BK * 2;
-  const uint32_t stage_tx = 2 * AT_PLANE + 2 * b_plane;
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < AT_STAGES; ++s) {
@@ -396,8 +421,6 @@ assoc_frame_kernel(const __grid_constant__ CUtensorMap tmG, const __grid_constan
       ptx::mbar_init(bar_tempty + 8 * s, 4);
     }
     ptx::fence_barrier_init();
-    ptx::prefetch_tensormap(&tmG);
-    ptx::prefetch_tensormap(&tmF);
   }
   if (warp == 1) {
     ptx::tmem_alloc(ptx::smem_u32(tmem_slot), 512);
@@ -408,6 +431,7 @@ assoc_frame_kernel(const __grid_constant__ CUtensorMap tmG, const __grid_constan
   ptx::tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
   const int total = a.T * n_dtiles;
+  const size_t greg = (size_t)rb * 64, dreg = (size_t)det_rows * 64;  // halfs per (k-block, plane) region
 
   if (warp == 0) {
     if (lane == 0) {
@@ -418,17 +442,21 @@ assoc_frame_kernel(const __grid_constant__ CUtensorMap tmG, const __grid_constan
         const int slot = a.trk_slot[t];
         const int cnt = slot >= 0 ? a.gcount[slot] : 0;
         const int rts = (cnt + AT_BM - 1) / AT_BM;
+        const int nb_rows = min(bn_box, (a.M - dt * AT_BN + 15) & ~15);  // detection rows of this tile (multiple of 16)
         for (int rt = 0; rt < rts; ++rt) {
-          const int arow = slot * a.budget + rt * AT_BM;
+          const int na_rows = min(AT_BM, (cnt - rt * AT_BM + 15) & ~15);  // ring rows fetched: the valid ones, rounded up to 16
+          const uint32_t a_bytes = (uint32_t)na_rows * 128u, b_bytes = (uint32_t)nb_rows * 128u;
           for (int kb = 0; kb < num_kb; ++kb) {
             ptx::mbar_wait(bar_empty + 8 * stage, phase ^ 1);
             const uint32_t full = bar_full + 8 * stage;
             const uint32_t sb = smem_base + stage * AT_STAGE_BYTES;
-            ptx::mbar_arrive_expect_tx(full, stage_tx);
-            ptx::tma_load_2d(sb, &tmG, full, kb * AT_BK, arow);
-            ptx::tma_load_2d(sb + AT_PLANE, &tmG, full, dp + kb * AT_BK, arow);
-            ptx::tma_load_2d(sb + 2 * AT_PLANE, &tmF, full, kb * AT_BK, dt * AT_BN);
-            ptx::tma_load_2d(sb + 2 * AT_PLANE + b_plane, &tmF, full, dp + kb * AT_BK, dt * AT_BN);
+            ptx::mbar_arrive_expect_tx(full, 2 * a_bytes + 2 * b_bytes);
+            const __half* ga = gpacked + ((size_t)(slot * num_kb + kb) * 2) * greg + (size_t)rt * AT_BM * 64;
+            const __half* gd = dpacked + ((size_t)kb * 2) * dreg + (size_t)dt * AT_BN * 64;
+            ptx::bulk_load(sb, ga, a_bytes, full);
+            ptx::bulk_load(sb + AT_PLANE, ga + greg, a_bytes, full);
+            ptx::bulk_load(sb + 2 * AT_PLANE, gd, b_bytes, full);
+            ptx::bulk_load(sb + 2 * AT_PLANE + b_plane, gd + dreg, b_bytes, full);
             if (++stage == AT_STAGES) { stage = 0; phase ^= 1; }
           }
         }
@@ -561,88 +589,124 @@ assoc_frame_kernel(const __grid_constant__ CUtensorMap tmG, const __grid_constan
 // the untouched rows hold, and those accumulator rows are masked.  Against one track per tile this halves the tiles (and
 // with them the re-streaming of the detection operand from L2) and reads the ring's valid rows only: DRAM traffic ~ sum of
 // count x 2 KB instead of the whole [slots, budget] ring.
-// Schedule (device side, assoc_schedule_kernel, one warp): sched[0] = tiles in total, sched[1] = tiles with rows;
+// Schedule (device side, assoc_schedule_block): sched[0] = tiles in total, sched[1] = tiles with rows;
 // sched[4 + 4 * tile + q] = track row index of quadrant q (or -1).  Tiles >= sched[1] list the tracks WITHOUT rows
 // (unknown slot / empty ring: every cost is 1e5 before the gate), four per tile, no MMA.
-constexpr int A2_STAGES = 2;
-constexpr size_t A2_SMEM = 1024 + (size_t)A2_STAGES * AT_STAGE_BYTES + 2 * 4 * AT_BN * sizeof(float) + 2 * 4 * 32 * sizeof(double) + 128;
+constexpr int A2_MAX_STAGES = 4;
+constexpr size_t A2_STAGE_BUDGET = 196 * 1024;  // operand stages share this much shared memory
+constexpr size_t A2_SMEM = 1024 + A2_STAGE_BUDGET + 2 * 4 * AT_BN * sizeof(float) + 2 * 4 * 32 * sizeof(double) + 128;
 
-__global__ void __launch_bounds__(32)
-assoc_schedule_kernel(const int32_t* __restrict__ trk_slot, const int32_t* __restrict__ gcount, int T, int32_t* __restrict__ sched) {
-  // One warp.  32 tracks at a time: every lane fetches its track's row count (the two dependent loads of all 32 tracks are
-  // in flight together), three ballots hand the 32 quadrant counts (0..4) to lane 0 as bit planes, and lane 0 runs the
-  // packing state machine on registers only; pass 2 appends the tracks without rows, four per tile.
-  const int lane = threadIdx.x;
-  int32_t* seg = sched + 4;
-  int tile = 0, q = 0;
-  for (int pass = 0; pass < 2; ++pass) {
-    for (int base = 0; base < T; base += 32) {
-      const int t = base + lane;
-      int nq = 0;
-      bool empty = false;
-      if (t < T) {
-        const int slot = trk_slot ? trk_slot[t] : -1;
-        const int cnt = slot >= 0 ? gcount[slot] : 0;
-        nq = min((cnt + 31) >> 5, 4);
-        empty = cnt <= 0;
-      }
-      const uint32_t b0 = __ballot_sync(0xffffffffu, nq & 1), b1 = __ballot_sync(0xffffffffu, nq & 2),
-                     b2 = __ballot_sync(0xffffffffu, nq & 4), be = __ballot_sync(0xffffffffu, empty);
-      if (lane == 0) {
-        const int n = min(32, T - base);
-        for (int i = 0; i < n; ++i) {
-          if (pass == 0) {
-            const int k = ((b0 >> i) & 1) | (((b1 >> i) & 1) << 1) | (((b2 >> i) & 1) << 2);
-            if (k == 0) continue;
-            if (q + k > 4) {
-              for (; q < 4; ++q) seg[tile * 4 + q] = -1;
-              ++tile; q = 0;
-            }
-            for (int j = 0; j < k; ++j) seg[tile * 4 + q + j] = base + i;
-            q += k;
-            if (q == 4) { ++tile; q = 0; }
-          } else if ((be >> i) & 1) {
-            seg[tile * 4 + q] = base + i;
-            if (++q == 4) { ++tile; q = 0; }
-          }
-        }
-      }
+// The schedule is computed by ONE extra block of the detection-packing launch (det_pack_kernel), concurrently with the
+// packing blocks, fully in parallel: a track's place is a closed form of its CLASS (quadrants needed: 4, 3, 2, 1, none)
+// and its rank inside the class --
+//   class 4: a tile each;  class 3: a tile each, quadrants 0-2, the fourth quadrant taken by one class-1 track while there
+//   are any;  class 2: two per tile;  remaining class 1: four per tile;  tracks without rows: four per row-less tile --
+// so one block-wide exclusive scan of the five class counts places every track (no serial pass: a single thread walking
+// 300 tracks took 55 us).
+constexpr int SCHED_THREADS = 256;
+
+__device__ void assoc_schedule_block(const int32_t* __restrict__ trk_slot, const int32_t* __restrict__ gcount, int T,
+                                     int32_t* __restrict__ sched) {
+  __shared__ int s_warp[SCHED_THREADS / 32][5];
+  __shared__ int s_tot[5];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  auto cls = [&](int t) {  // quadrants of track t: 0 (no rows) .. 4
+    const int slot = trk_slot ? trk_slot[t] : -1;
+    const int cnt = slot >= 0 ? gcount[slot] : 0;
+    return min((cnt + 31) >> 5, 4);
+  };
+  // tracks are dealt out in contiguous chunks: thread `tid` owns [t0, t1)
+  const int per = (T + SCHED_THREADS - 1) / SCHED_THREADS;
+  const int t0 = min(T, tid * per), t1 = min(T, t0 + per);
+  int c[5] = {0, 0, 0, 0, 0};
+  for (int t = t0; t < t1; ++t) {
+    const int k = cls(t);
+#pragma unroll
+    for (int j = 0; j < 5; ++j) c[j] += (k == j) ? 1 : 0;
+  }
+  int base[5];
+#pragma unroll
+  for (int j = 0; j < 5; ++j) {
+    int incl = c[j];
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int v = __shfl_up_sync(0xffffffffu, incl, o);
+      if (lane >= o) incl += v;
     }
-    if (lane == 0) {
-      if (q > 0) {
-        for (; q < 4; ++q) seg[tile * 4 + q] = -1;
-        ++tile; q = 0;
-      }
-      if (pass == 0) sched[1] = tile;
-      else sched[0] = tile;
+    base[j] = incl - c[j];
+    if (lane == 31) s_warp[warp][j] = incl;
+  }
+  __syncthreads();
+  if (tid < 5) {
+    int tot = 0;
+    for (int w = 0; w < SCHED_THREADS / 32; ++w) { const int v = s_warp[w][tid]; s_warp[w][tid] = tot; tot += v; }
+    s_tot[tid] = tot;
+  }
+  __syncthreads();
+  const int n0 = s_tot[0], n1 = s_tot[1], n2 = s_tot[2], n3 = s_tot[3], n4 = s_tot[4];
+  const int rest1 = max(n1 - n3, 0);
+  const int tile2 = n4 + n3, tile1 = tile2 + (n2 + 1) / 2, n_real = tile1 + (rest1 + 3) / 4, n_tiles = n_real + (n0 + 3) / 4;
+  int32_t* seg = sched + 4;
+  for (int i = tid; i < 4 * n_tiles; i += SCHED_THREADS) seg[i] = -1;
+  __syncthreads();
+  int r[5];
+#pragma unroll
+  for (int j = 0; j < 5; ++j) r[j] = base[j] + s_warp[warp][j];
+  for (int t = t0; t < t1; ++t) {
+    const int k = cls(t);
+    if (k == 4) {
+      const int tl = r[4]++;
+#pragma unroll
+      for (int q = 0; q < 4; ++q) seg[tl * 4 + q] = t;
+    } else if (k == 3) {
+      const int tl = n4 + r[3]++;
+#pragma unroll
+      for (int q = 0; q < 3; ++q) seg[tl * 4 + q] = t;
+    } else if (k == 2) {
+      const int i = r[2]++;
+      const int tl = tile2 + (i >> 1), q = (i & 1) * 2;
+      seg[tl * 4 + q] = t;
+      seg[tl * 4 + q + 1] = t;
+    } else if (k == 1) {
+      const int i = r[1]++;
+      if (i < n3) seg[(n4 + i) * 4 + 3] = t;   // the free quadrant of a class-3 tile
+      else seg[(tile1 + ((i - n3) >> 2)) * 4 + ((i - n3) & 3)] = t;
+    } else {
+      const int i = r[0]++;
+      seg[(n_real + (i >> 2)) * 4 + (i & 3)] = t;
     }
   }
+  if (tid == 0) { sched[0] = n_tiles; sched[1] = n_real; }
 }
 
-struct RowMaps { CUtensorMap m[4]; };  // boxes of 16, 32, 64, 128 rows
+constexpr int A2_THREADS = 320;  // TMA producer warp, MMA warp, 4 column-max warps, 4 finaliser warps
 
-__global__ void __launch_bounds__(AT_THREADS, 1)
-assoc_frame2_kernel(const __grid_constant__ RowMaps tmR, const __grid_constant__ CUtensorMap tmF, AssocArgs a, int dp,
-                    int n_dtiles, int bn_box, const int32_t* __restrict__ sched) {
+__global__ void __launch_bounds__(A2_THREADS, 1)
+assoc_frame2_kernel(const __half* __restrict__ gpacked, int rb, const __half* __restrict__ dpacked, int det_rows, AssocArgs a, int dp,
+                    int n_dtiles, int bn_box, int nst, const int32_t* __restrict__ sched, int debug) {
+  // bn_box = detection columns of one work item (multiple of 16, <= AT_BN): a frame's detections are split into n_dtiles
+  // column ranges so that every SM gets two or three items of which the epilogue of one overlaps the k-loop of the next
+  // (one 128 x 208 item per SM left its epilogue and the launch ramp fully exposed); nst = operand stages (2..4) that fit.
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
-  float* part = reinterpret_cast<float*>(smem + (size_t)A2_STAGES * AT_STAGE_BYTES);  // [2][4][AT_BN] per-quadrant column maxima
+  const uint32_t b_plane = (uint32_t)bn_box * AT_BK * 2;
+  const uint32_t stage_bytes = 2 * AT_PLANE + 2 * b_plane;  // multiple of 1024: bn_box is a multiple of 16
+  float* part = reinterpret_cast<float*>(smem + (size_t)nst * stage_bytes);  // [2][4][AT_BN] per-quadrant column maxima
   double* trk = reinterpret_cast<double*>(part + 2 * 4 * AT_BN);                       // [2][4][32] x4 | SI | tlwh box per segment
   uint64_t* bars = reinterpret_cast<uint64_t*>(trk + 2 * 4 * 32);
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * A2_STAGES + 4);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * A2_MAX_STAGES + 4);
 
   const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);
   const int lane = threadIdx.x & 31;
   const uint32_t bar_full = ptx::smem_u32(bars);
-  const uint32_t bar_empty = ptx::smem_u32(bars + A2_STAGES);
-  const uint32_t bar_tfull = ptx::smem_u32(bars + 2 * A2_STAGES);
-  const uint32_t bar_tempty = ptx::smem_u32(bars + 2 * A2_STAGES + 2);
+  const uint32_t bar_empty = ptx::smem_u32(bars + A2_MAX_STAGES);
+  const uint32_t bar_tfull = ptx::smem_u32(bars + 2 * A2_MAX_STAGES);
+  const uint32_t bar_tempty = ptx::smem_u32(bars + 2 * A2_MAX_STAGES + 2);
   const uint32_t smem_base = ptx::smem_u32(smem);
   const int num_kb = dp / AT_BK;
-  const uint32_t b_plane = (uint32_t)bn_box * AT_BK * 2;
 
   if (threadIdx.x == 0) {
-    for (int s = 0; s < A2_STAGES; ++s) {
+    for (int s = 0; s < nst; ++s) {
       ptx::mbar_init(bar_full + 8 * s, 1);
       ptx::mbar_init(bar_empty + 8 * s, 1);
     }
@@ -651,9 +715,6 @@ assoc_frame2_kernel(const __grid_constant__ RowMaps tmR, const __grid_constant__
       ptx::mbar_init(bar_tempty + 8 * s, 4);
     }
     ptx::fence_barrier_init();
-#pragma unroll
-    for (int i = 0; i < 4; ++i) ptx::prefetch_tensormap(&tmR.m[i]);
-    ptx::prefetch_tensormap(&tmF);
   }
   if (warp == 1) {
     ptx::tmem_alloc(ptx::smem_u32(tmem_slot), 512);
@@ -666,6 +727,7 @@ assoc_frame2_kernel(const __grid_constant__ RowMaps tmR, const __grid_constant__
   const int n_tiles = sched[0], n_real = sched[1];
   const int32_t* seg = sched + 4;
   const int total = n_tiles * n_dtiles;
+  const size_t greg = (size_t)rb * 64, dreg = (size_t)det_rows * 64;  // halfs per (k-block, plane) region
 
   if (warp == 0) {
     if (lane == 0) {
@@ -674,40 +736,39 @@ assoc_frame2_kernel(const __grid_constant__ RowMaps tmR, const __grid_constant__
       for (int w = blockIdx.x; w < total; w += gridDim.x) {
         const int tile = w / n_dtiles, dt = w - tile * n_dtiles;
         if (tile >= n_real) continue;
-        // the tile's tracks: first gallery row, rows to fetch (ceil16(count)) and row offset inside the tile
-        int grow[4], nrow[4], roff[4], nseg = 0;
+        // the tile's tracks: gallery slot, rows to fetch (ceil16(count)) and row offset inside the tile
+        int gslot[4], nrow[4], roff[4], nseg = 0;
         uint32_t a_bytes = 0;
         for (int q = 0; q < 4; ++q) {
           const int t = seg[tile * 4 + q];
           if (t < 0 || (q > 0 && seg[tile * 4 + q - 1] == t)) continue;
           const int slot = a.trk_slot[t];
           const int r16 = (a.gcount[slot] + 15) & ~15;
-          grow[nseg] = slot * a.budget; nrow[nseg] = r16; roff[nseg] = q * 32;
+          gslot[nseg] = slot; nrow[nseg] = r16; roff[nseg] = q * 32;
           a_bytes += (uint32_t)r16 * 128u;
           ++nseg;
         }
-        const uint32_t stage_tx = 2 * a_bytes + 2 * b_plane;
+        const int nb_rows = min(bn_box, (a.M - dt * bn_box + 15) & ~15);
+        const uint32_t b_bytes = (uint32_t)nb_rows * 128u;
+        // (debug: timing experiments only, REIDB200_ASSOC_DEBUG -- 1 = no gallery loads, 2 = no detection loads)
+        const uint32_t stage_tx = ((debug & 1) ? 0u : 2 * a_bytes) + ((debug & 2) ? 0u : 2 * b_bytes);
         for (int kb = 0; kb < num_kb; ++kb) {
           ptx::mbar_wait(bar_empty + 8 * stage, phase ^ 1);
           const uint32_t full = bar_full + 8 * stage;
-          const uint32_t sb = smem_base + stage * AT_STAGE_BYTES;
-          ptx::mbar_arrive_expect_tx(full, stage_tx);
-          for (int s = 0; s < nseg; ++s) {
-            int done = 0;
-#pragma unroll
-            for (int bi = 3; bi >= 0; --bi) {  // boxes of 128, 64, 32, 16 rows: the binary digits of nrow / 16
-              const int rows = 16 << bi;
-              if (nrow[s] & rows) {
-                const uint32_t dst = sb + (uint32_t)(roff[s] + done) * 128u;
-                ptx::tma_load_2d(dst, &tmR.m[bi], full, kb * AT_BK, grow[s] + done);
-                ptx::tma_load_2d(dst + AT_PLANE, &tmR.m[bi], full, dp + kb * AT_BK, grow[s] + done);
-                done += rows;
-              }
-            }
+          const uint32_t sb = smem_base + stage * stage_bytes;
+          if (stage_tx) ptx::mbar_arrive_expect_tx(full, stage_tx); else ptx::mbar_arrive(full);
+          for (int s = 0; s < nseg && !(debug & 1); ++s) {  // one contiguous piece per track and plane (tile-image layout)
+            const __half* ga = gpacked + ((size_t)(gslot[s] * num_kb + kb) * 2) * greg;
+            const uint32_t dst = sb + (uint32_t)roff[s] * 128u, bytes = (uint32_t)nrow[s] * 128u;
+            ptx::bulk_load(dst, ga, bytes, full);
+            ptx::bulk_load(dst + AT_PLANE, ga + greg, bytes, full);
           }
-          ptx::tma_load_2d(sb + 2 * AT_PLANE, &tmF, full, kb * AT_BK, dt * AT_BN);
-          ptx::tma_load_2d(sb + 2 * AT_PLANE + b_plane, &tmF, full, dp + kb * AT_BK, dt * AT_BN);
-          if (++stage == A2_STAGES) { stage = 0; phase ^= 1; }
+          const __half* gd = dpacked + ((size_t)kb * 2) * dreg + (size_t)dt * bn_box * 64;
+          if (!(debug & 2)) {
+            ptx::bulk_load(sb + 2 * AT_PLANE, gd, b_bytes, full);
+            ptx::bulk_load(sb + 2 * AT_PLANE + b_plane, gd + dreg, b_bytes, full);
+          }
+          if (++stage == nst) { stage = 0; phase ^= 1; }
         }
       }
     }
@@ -718,7 +779,7 @@ assoc_frame2_kernel(const __grid_constant__ RowMaps tmR, const __grid_constant__
       for (int w = blockIdx.x; w < total; w += gridDim.x) {
         const int tile = w / n_dtiles, dt = w - tile * n_dtiles;
         if (tile >= n_real) continue;
-        const int n_tile = min(bn_box, (a.M - dt * AT_BN + 15) & ~15);
+        const int n_tile = min(bn_box, (a.M - dt * bn_box + 15) & ~15);
         const uint32_t idesc = ptx::umma_idesc_f16(AT_BM, n_tile);
         ptx::mbar_wait(bar_tempty + 8 * as, aphase ^ 1);
         ptx::tc_fence_after();
@@ -726,7 +787,7 @@ assoc_frame2_kernel(const __grid_constant__ RowMaps tmR, const __grid_constant__
         for (int kb = 0; kb < num_kb; ++kb) {
           ptx::mbar_wait(bar_full + 8 * stage, phase);
           ptx::tc_fence_after();
-          const uint32_t sb = smem_base + stage * AT_STAGE_BYTES;
+          const uint32_t sb = smem_base + stage * stage_bytes;
 #pragma unroll
           for (int kk = 0; kk < AT_BK / 16; ++kk) {
             const uint64_t ahi = ptx::umma_desc_k_sw128(sb + kk * 32);
@@ -738,28 +799,33 @@ assoc_frame2_kernel(const __grid_constant__ RowMaps tmR, const __grid_constant__
             ptx::mma_f16_ss(d_tmem, ahi, bhi, idesc, 1);
           }
           ptx::mma_commit(bar_empty + 8 * stage);
-          if (++stage == A2_STAGES) { stage = 0; phase ^= 1; }
+          if (++stage == nst) { stage = 0; phase ^= 1; }
         }
         ptx::mma_commit(bar_tfull + 8 * as);
         as ^= 1;
         if (as == 0) aphase ^= 1;
       }
     }
-  } else {
-    const int q = warp & 3;               // TMEM lane quadrant of this warp = quadrant of the tile
-    const int e = threadIdx.x - 64;       // 0..127
+  } else if (warp < 6) {
+    // ===== column-max warps (2-5): TMEM lane quadrant q = quadrant of the tile.  They reduce the accumulator to per-
+    // quadrant column maxima in `part[buf]`, stage the quadrant's track state in `trk[buf]`, release the TMEM stage and
+    // hand the buffer to the finaliser warps (named barriers 1+buf "filled", 3+buf "drained"; two buffers).
+    const int q = warp & 3;
     int as = 0, it = 0;
     uint32_t aphase = 0;
     for (int w = blockIdx.x; w < total; w += gridDim.x, ++it) {
       const int tile = w / n_dtiles, dt = w - tile * n_dtiles;
       const bool real = tile < n_real;
-      const int n_cols = min(AT_BN, a.M - dt * AT_BN);
+      const int n_cols = min(bn_box, a.M - dt * bn_box);
       const int4 sg4 = *reinterpret_cast<const int4*>(seg + tile * 4);
       auto SG = [&](int i) { return i == 0 ? sg4.x : (i == 1 ? sg4.y : (i == 2 ? sg4.z : sg4.w)); };  // (no local array)
       const int t_mine = SG(q);
-      float* mypart = part + ((it & 1) * 4 + q) * AT_BN;
-      double* mytrk = trk + ((it & 1) * 4 + q) * 32;
-      // this quadrant's track state (every quadrant stages its own copy: the final pass reads the first quadrant's)
+      const int buf = it & 1;
+      float* mypart = part + (buf * 4 + q) * AT_BN;
+      double* mytrk = trk + (buf * 4 + q) * 32;
+      if (it >= 2) {  // the finalisers have drained this buffer (its previous occupant was item it - 2)
+        if (buf == 0) asm volatile("bar.sync 3, 256;" ::: "memory"); else asm volatile("bar.sync 4, 256;" ::: "memory");
+      }
       if (t_mine >= 0) {
         if (lane < 4) mytrk[lane] = a.trk_mean[(size_t)t_mine * 8 + lane];
         else if (lane < 20) mytrk[lane] = a.trk_SI ? a.trk_SI[(size_t)t_mine * 16 + (lane - 4)] : 0.0;
@@ -777,14 +843,16 @@ assoc_frame2_kernel(const __grid_constant__ RowMaps tmR, const __grid_constant__
         const bool valid = t_mine >= 0 && chunk * 32 + lane < cnt;
         const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + as * AT_BN;
         if (t_mine >= 0) {  // warp-uniform
+          const int nch = (n_cols + 31) >> 5;
+          uint32_t rn[32];
+          ptx::tmem_ld_32x32b_x32(taddr, rn);
 #pragma unroll 1
-          for (int c = 0; c * 32 < n_cols; ++c) {
-            uint32_t r[32];
-            ptx::tmem_ld_32x32b_x32(taddr + c * 32, r);
-            ptx::tmem_ld_wait();
+          for (int c = 0; c < nch; ++c) {  // the next chunk's accumulator columns are requested before this one is reduced
             float v[32];
+            ptx::tmem_ld_wait(rn);
 #pragma unroll
-            for (int j = 0; j < 32; ++j) v[j] = valid ? __uint_as_float(r[j]) : -INFINITY;
+            for (int j = 0; j < 32; ++j) v[j] = valid ? __uint_as_float(rn[j]) : -INFINITY;
+            if (c + 1 < nch) ptx::tmem_ld_32x32b_x32(taddr + (c + 1) * 32, rn);
             mypart[c * 32 + lane] = colmax_transpose(v, lane);
           }
         }
@@ -794,15 +862,28 @@ assoc_frame2_kernel(const __grid_constant__ RowMaps tmR, const __grid_constant__
         as ^= 1;
         if (as == 0) aphase ^= 1;
       }
-      asm volatile("bar.sync 1, 128;" ::: "memory");  // the four epilogue warps: partial maxima + track state visible
-      // final pass: every (track of the tile, detection column) pair, 128 threads striding over them
-      const float* p0 = part + (it & 1) * 4 * AT_BN;
-      const double* t0 = trk + (it & 1) * 4 * 32;
-      for (int item = e; item < 4 * n_cols; item += 128) {
+      if (buf == 0) asm volatile("bar.arrive 1, 256;" ::: "memory"); else asm volatile("bar.arrive 2, 256;" ::: "memory");
+    }
+  } else {
+    // ===== finaliser warps (6-9): every (track of the tile, detection column) pair -> 1 - max, Mahalanobis gate + blend +
+    // clamp and the IoU / DIoU row in fp64, while the column-max warps already reduce the next item
+    const int e = threadIdx.x - 192;       // 0..127
+    int it = 0;
+    for (int w = blockIdx.x; w < total; w += gridDim.x, ++it) {
+      const int tile = w / n_dtiles, dt = w - tile * n_dtiles;
+      const bool real = tile < n_real;
+      const int n_cols = min(bn_box, a.M - dt * bn_box);
+      const int4 sg4 = *reinterpret_cast<const int4*>(seg + tile * 4);
+      auto SG = [&](int i) { return i == 0 ? sg4.x : (i == 1 ? sg4.y : (i == 2 ? sg4.z : sg4.w)); };
+      const int buf = it & 1;
+      if (buf == 0) asm volatile("bar.sync 1, 256;" ::: "memory"); else asm volatile("bar.sync 2, 256;" ::: "memory");
+      const float* p0 = part + buf * 4 * AT_BN;
+      const double* t0 = trk + buf * 4 * 32;
+      for (int item = e; item < 4 * n_cols && !(debug & 4); item += 128) {
         const int sq = item / n_cols, col = item - sq * n_cols;   // sq = a quadrant that STARTS a track
         const int t = SG(sq);
         if (t < 0 || (real && sq > 0 && SG(sq - 1) == t)) continue;
-        const int m = dt * AT_BN + col;
+        const int m = dt * bn_box + col;
         const size_t o = (size_t)t * a.M + m;
         const double* st = t0 + sq * 32;
         if (a.out_app) {
@@ -833,6 +914,7 @@ assoc_frame2_kernel(const __grid_constant__ RowMaps tmR, const __grid_constant__
           a.out_iou[o] = c;
         }
       }
+      if (buf == 0) asm volatile("bar.arrive 3, 256;" ::: "memory"); else asm volatile("bar.arrive 4, 256;" ::: "memory");
     }
   }
 
@@ -884,25 +966,26 @@ using namespace reidb200;
 // ints of a frame schedule for T tracks: header (4) + 4 per tile, at most T tiles with rows + ceil(T / 4) without
 static size_t sched_ints(int T) { return 4 + 4 * ((size_t)T + (size_t)T / 4 + 2); }
 
-static int gallery_maps(reidb200_gallery* g) {
-  int rc = make_operand_map(&g->tm_gallery, g->packed, g->slots * g->budget, g->dp, AT_BM);
-  for (int i = 0; i < 4 && !rc; ++i) rc = make_operand_map(&g->tm_rows[i], g->packed, g->slots * g->budget, g->dp, 16 << i);
-  return rc;
+// bytes of the tile-image gallery: slots x k-blocks x 2 planes regions of rb rows x 128 bytes, plus one tile of slack so
+// that a fetch rounded up to 16 rows never leaves the allocation
+static size_t gallery_packed_bytes(int slots, int rb, int dp) {
+  return (size_t)slots * (dp / 64) * 2 * rb * 128 + (size_t)AT_BM * 128;
 }
 
 extern "C" int reidb200_gallery_create(int slots, int budget, int d, reidb200_gallery** out) {
   RB_REQUIRE(out && slots > 0 && budget > 0 && d > 0, "gallery_create: bad argument");
   reidb200_gallery* g = new reidb200_gallery();
   g->slots = slots; g->budget = budget; g->d = d; g->dp = padded_dim(d);
+  g->rb = (budget + 15) & ~15;
   g->feats = nullptr; g->packed = nullptr; g->count = nullptr; g->head = nullptr; g->scratch = nullptr;
   g->det_packed = nullptr; g->det_cap = 1024;
   g->sched = nullptr; g->sched_cap = slots > 1024 ? slots : 1024;
   g->scratch_rows = slots > 1024 ? slots : 1024;
-  const size_t packed_sz = (size_t)slots * budget * 2 * g->dp * sizeof(__half);
+  const size_t packed_sz = gallery_packed_bytes(slots, g->rb, g->dp);
   cudaError_t e = cudaMalloc(&g->feats, (size_t)slots * budget * d * sizeof(float));
   if (e == cudaSuccess) e = cudaMalloc(&g->packed, packed_sz);
   if (e == cudaSuccess) e = cudaMemset(g->packed, 0, packed_sz);
-  if (e == cudaSuccess) e = cudaMalloc(&g->det_packed, (size_t)g->det_cap * 2 * g->dp * sizeof(__half));
+  if (e == cudaSuccess) e = cudaMalloc(&g->det_packed, (size_t)g->det_cap * 2 * g->dp * sizeof(__half) + (size_t)AT_BN * 128);
   if (e == cudaSuccess) e = cudaMalloc(&g->count, (size_t)slots * sizeof(int32_t));
   if (e == cudaSuccess) e = cudaMalloc(&g->head, (size_t)slots * sizeof(int32_t));
   if (e == cudaSuccess) e = cudaMalloc(&g->scratch, (size_t)2 * g->scratch_rows * sizeof(int32_t));
@@ -913,8 +996,6 @@ extern "C" int reidb200_gallery_create(int slots, int budget, int d, reidb200_ga
     reidb200_gallery_destroy(g);
     return cuda_fail(e, "gallery_create", __FILE__, __LINE__);
   }
-  int rc = gallery_maps(g);
-  if (rc) { reidb200_gallery_destroy(g); return rc; }
   *out = g;
   return REIDB200_OK;
 }
@@ -927,7 +1008,8 @@ extern "C" int reidb200_gallery_resize(reidb200_gallery* g, int new_slots, int n
   if (new_slots == g->slots && new_budget == g->budget) return REIDB200_OK;
   cudaStream_t st = (cudaStream_t)stream;
   float* feats = nullptr; __half* packed = nullptr; int32_t *count = nullptr, *head = nullptr, *scratch = nullptr;
-  const size_t packed_sz = (size_t)new_slots * new_budget * 2 * g->dp * sizeof(__half);
+  const int new_rb = (new_budget + 15) & ~15;
+  const size_t packed_sz = gallery_packed_bytes(new_slots, new_rb, g->dp);
   const int scratch_rows = new_slots > 1024 ? new_slots : 1024;
   cudaError_t e = cudaMalloc(&feats, (size_t)new_slots * new_budget * g->d * sizeof(float));
   if (e == cudaSuccess) e = cudaMalloc(&packed, packed_sz);
@@ -942,13 +1024,13 @@ extern "C" int reidb200_gallery_resize(reidb200_gallery* g, int new_slots, int n
     return cuda_fail(e, "gallery_resize", __FILE__, __LINE__);
   }
   gal_resize_kernel<<<dim3(g->slots, g->budget < 16 ? g->budget : 16), 128, 0, st>>>(g->feats, g->packed, g->head, g->count, g->budget,
-                                                                                  new_budget, g->d, g->dp, feats, packed, head, count);
+                                                                                  g->rb, new_budget, new_rb, g->d, g->dp, feats, packed, head, count);
   RB_LAUNCH_CHECK("gal_resize_kernel");
   RB_CUDA(cudaStreamSynchronize(st));
   cudaFree(g->feats); cudaFree(g->packed); cudaFree(g->count); cudaFree(g->head); cudaFree(g->scratch);
   g->feats = feats; g->packed = packed; g->count = count; g->head = head; g->scratch = scratch;
-  g->slots = new_slots; g->budget = new_budget; g->scratch_rows = scratch_rows;
-  return gallery_maps(g);
+  g->slots = new_slots; g->budget = new_budget; g->rb = new_rb; g->scratch_rows = scratch_rows;
+  return REIDB200_OK;
 }
 
 extern "C" int reidb200_gallery_destroy(reidb200_gallery* g) {
@@ -971,7 +1053,7 @@ extern "C" int reidb200_gallery_partial_fit(reidb200_gallery* g, const float* fe
     { ProfScope _ps("pf_assign_kernel", st); pf_assign_kernel<<<ceil_div(nb, 128), 128, 0, st>>>(slot_of_row + b0, nb, g->budget, g->head, dst, after); }
     RB_LAUNCH_CHECK("pf_assign_kernel");
     { ProfScope _ps("pf_write_kernel", st); pf_write_kernel<<<ceil_div(nb, 8), 256, 0, st>>>(feats + (size_t)b0 * ldf, ldf, slot_of_row + b0, dst, nb, g->budget,
-                                                    g->d, g->dp, g->feats, g->packed); }
+                                                    g->d, g->dp, g->rb, g->feats, g->packed); }
     RB_LAUNCH_CHECK("pf_write_kernel");
     { ProfScope _ps("pf_update_kernel", st); pf_update_kernel<<<ceil_div(nb, 128), 128, 0, st>>>(slot_of_row + b0, after, nb, g->budget, g->head, g->count); }
     RB_LAUNCH_CHECK("pf_update_kernel");
@@ -1030,46 +1112,51 @@ extern "C" int reidb200_assoc_frame(reidb200_gallery* g, const float* det_feat, 
     RB_CUDA(cudaStreamSynchronize(st));
     cudaFree(g->det_packed);
     g->det_packed = nullptr;
-    g->det_cap = M + M / 2;
-    RB_CUDA(cudaMalloc(&g->det_packed, (size_t)g->det_cap * 2 * g->dp * sizeof(__half)));
+    g->det_cap = (M + M / 2 + 15) & ~15;
+    RB_CUDA(cudaMalloc(&g->det_packed, (size_t)g->det_cap * 2 * g->dp * sizeof(__half) + (size_t)AT_BN * 128));
   }
-  { ProfScope _ps("det_pack_kernel", st); det_pack_kernel<<<ceil_div(M, 8), 256, 0, st>>>(det_feat, ldf, M, g->d, g->dp, g->det_packed); }
+  const bool packed_tiles = g->budget <= AT_BM && !getenv("REIDB200_ASSOC_V1");
+  if (packed_tiles && T > g->sched_cap) {  // grows outside the steady state only (synchronises)
+    RB_CUDA(cudaStreamSynchronize(st));
+    cudaFree(g->sched);
+    g->sched = nullptr;
+    g->sched_cap = T + T / 2;
+    RB_CUDA(cudaMalloc(&g->sched, sched_ints(g->sched_cap) * sizeof(int32_t)));
+  }
+  { ProfScope _ps("det_pack_kernel", st); det_pack_kernel<<<ceil_div(M, 8) + (packed_tiles ? 1 : 0), 256, 0, st>>>(
+      det_feat, ldf, M, g->d, g->dp, g->det_cap, g->det_packed, trk_slot, g->count, T, packed_tiles ? g->sched : nullptr); }
   RB_LAUNCH_CHECK("det_pack_kernel");
-  const int bn_box = M >= AT_BN ? AT_BN : ((M + 15) & ~15);
-  CUtensorMap tmF;
-  int rc = make_operand_map(&tmF, g->det_packed, M, g->dp, bn_box);
-  if (rc) return rc;
-  const int n_dtiles = ceil_div(M, AT_BN);
-  if (g->budget <= AT_BM && getenv("REIDB200_ASSOC_V2")) {
-    // rings of at most 128 rows: tracks packed into 128-row tiles by quadrants, count-aware loads (assoc_frame2_kernel)
-    if (T > g->sched_cap) {  // grows outside the steady state only (synchronises)
-      RB_CUDA(cudaStreamSynchronize(st));
-      cudaFree(g->sched);
-      g->sched = nullptr;
-      g->sched_cap = T + T / 2;
-      RB_CUDA(cudaMalloc(&g->sched, sched_ints(g->sched_cap) * sizeof(int32_t)));
-    }
-    { ProfScope _ps("assoc_schedule_kernel", st); assoc_schedule_kernel<<<1, 32, 0, st>>>(trk_slot, g->count, T, g->sched); }
-    RB_LAUNCH_CHECK("assoc_schedule_kernel");
+  if (packed_tiles) {
+    // rings of at most 128 rows: tracks packed into 128-row tiles by quadrants, count-aware loads (assoc_frame2_kernel);
+    // the detections are split into column ranges of about 112 so that an SM gets several items to pipeline
+    const int width = getenv("REIDB200_ASSOC_BN") ? atoi(getenv("REIDB200_ASSOC_BN")) : 112;  // (experiments)
+    const int nd = ceil_div(M, width < 16 ? 16 : (width > AT_BN ? AT_BN : width));
+    const int bn = (ceil_div(M, nd) + 15) & ~15;
+    const int n_dt = ceil_div(M, bn);
+    const size_t stage_bytes = 2 * (size_t)AT_PLANE + 2 * (size_t)bn * AT_BK * 2;
+    int nst = (int)(A2_STAGE_BUDGET / stage_bytes);
+    nst = nst > A2_MAX_STAGES ? A2_MAX_STAGES : nst;
+    if (getenv("REIDB200_ASSOC_STAGES")) nst = nst < atoi(getenv("REIDB200_ASSOC_STAGES")) ? nst : atoi(getenv("REIDB200_ASSOC_STAGES"));
+    const int debug = getenv("REIDB200_ASSOC_DEBUG") ? atoi(getenv("REIDB200_ASSOC_DEBUG")) : 0;
     static DeviceOnce attr2;
     if (attr2.pending()) {
       RB_CUDA(cudaFuncSetAttribute(assoc_frame2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)A2_SMEM));
     }
-    RowMaps rm;
-    for (int i = 0; i < 4; ++i) rm.m[i] = g->tm_rows[i];
-    const long long most = ((long long)T + T / 4 + 2) * n_dtiles;  // upper bound of the work items (the count lives on the device)
+    const long long most = ((long long)T + T / 4 + 2) * n_dt;  // upper bound of the work items (the count lives on the device)
     const int grid = (int)(most < num_sms() ? most : num_sms());
-    { ProfScope _ps("assoc_frame_kernel", st); assoc_frame2_kernel<<<grid, AT_THREADS, A2_SMEM, st>>>(rm, tmF, a, g->dp, n_dtiles, bn_box, g->sched); }
+    { ProfScope _ps("assoc_frame_kernel", st); assoc_frame2_kernel<<<grid, A2_THREADS, A2_SMEM, st>>>(g->packed, g->rb, g->det_packed, g->det_cap, a, g->dp, n_dt, bn, nst, g->sched, debug); }
     RB_LAUNCH_CHECK("assoc_frame2_kernel");
     return REIDB200_OK;
   }
+  const int bn_box = M >= AT_BN ? AT_BN : ((M + 15) & ~15);
+  const int n_dtiles = ceil_div(M, AT_BN);
   static DeviceOnce attr_done;
   if (attr_done.pending()) {
     RB_CUDA(cudaFuncSetAttribute(assoc_frame_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)AT_SMEM));
   }
   const long long total = (long long)T * n_dtiles;
   const int grid = (int)(total < num_sms() ? total : num_sms());
-  { ProfScope _ps("assoc_frame_kernel", st); assoc_frame_kernel<<<grid, AT_THREADS, AT_SMEM, st>>>(g->tm_gallery, tmF, a, g->dp, n_dtiles, bn_box); }
+  { ProfScope _ps("assoc_frame_kernel", st); assoc_frame_kernel<<<grid, AT_THREADS, AT_SMEM, st>>>(g->packed, g->rb, g->det_packed, g->det_cap, a, g->dp, n_dtiles, bn_box); }
   RB_LAUNCH_CHECK("assoc_frame_kernel");
   return REIDB200_OK;
 }

@@ -406,7 +406,7 @@ extern "C" int reidb200_crop_resize_norm_ws(const uint8_t* src, const int64_t* c
     }
     {
       ProfScope _ps("crop_cv_linear_kernel", st);
-      const bool vec4 = (out_w & 3) == 0 && (reinterpret_cast<uintptr_t>(out) & 15) == 0 && getenv("REIDB200_CROP_V4");
+      const bool vec4 = (out_w & 3) == 0 && (reinterpret_cast<uintptr_t>(out) & 15) == 0 && !getenv("REIDB200_CROP_V3");
       if (vec4) {
         dim3 g4(ceil_div(out_h, CV4_WARPS * CV4_ROWS_PER_WARP), M);
         if (pow2) crop_cv_linear4_kernel<true><<<g4, CV4_WARPS * 32, 0, st>>>(src, crop_off, crop_geom, out_h, out_w, nrm, out);

@@ -398,7 +398,7 @@ def assoc_frame(gallery, det_feat, det_tlwh, trk_slot, trk_mean, trk_SI, trk_tsu
     if want_app:
         det_feat_t = _f32(det_feat, dev)
         slot_t = _i32(trk_slot, dev)
-        si_t = torch.as_tensor(trk_SI).to(device=dev, dtype=torch.float64).contiguous()
+        si_t = None if trk_SI is None else torch.as_tensor(trk_SI).to(device=dev, dtype=torch.float64).contiguous()  # (None: gate=False)
         app = out_app if out_app is not None else torch.empty((T, M), dtype=torch.float64, device=dev)
         raw = torch.empty((T, M), dtype=torch.float64, device=dev) if want_raw else None
     if want_iou:

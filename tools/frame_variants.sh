@@ -1,6 +1,6 @@
 #!/bin/bash
 # crop / association kernel variants side by side (bench.bench_assoc under the opt-in switches)
-for v in "REIDB200_CROP_V3=1 REIDB200_ASSOC_V1=1" "REIDB200_CROP_V4=1 REIDB200_ASSOC_V2=1"; do
+for v in "REIDB200_CROP_V3=1 REIDB200_ASSOC_V1=1" "REIDB200_NEW=1"; do
   echo "== $v"
   env $v timeout 600 python - <<'PY'
 import json, sys
