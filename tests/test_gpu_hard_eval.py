@@ -79,7 +79,7 @@ def test_eval_hard_market_shape_vs_oracle(rb):
     d = synth.market_like(Q=300, G=4000, D=128, n_ids=700, seed=2, orphan_frac=0.03, noise=1.5)
     cmc, ap = E.evaluate_all(*[torch.from_numpy(d[k]) for k in KEYS])
     ocmc, oap = O.evaluate_all(*[d[k] for k in KEYS])
-    assert ocmc[0] < 0.9 and np.unique(ocmc).size > 20
+    assert ocmc[0] < 0.9 and np.unique(ocmc).size > 8
     np.testing.assert_allclose(cmc.numpy(), ocmc, atol=1e-6)
     assert abs(ap - oap) < 1e-6
     G, Q = 4000, 300
