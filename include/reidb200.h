@@ -151,6 +151,10 @@ int reidb200_eval_cmc_map(const float* mat, int Q, int G, int64_t ldm, int desce
  * rank_out (optional) i32[N,k1]: the initial ranking (stage D2).
  * ------------------------------------------------------------------------------------------ */
 size_t reidb200_jaccard_workspace_bytes(int N, int d, int k1, int k2);
+/* The N x N squared-L2 matrix is never materialised (the initial ranking is selected inside the GEMM epilogue); only the
+ * rows the lambda blend reads are kept.  blend_rows = nrows of the output region when lambda_value > 0, else 0: the
+ * workspace for exactly that call (reidb200_jaccard_workspace_bytes covers any region: blend_rows = N). */
+size_t reidb200_jaccard_region_workspace_bytes(int N, int d, int k1, int k2, int blend_rows);
 int reidb200_jaccard(const float* feats, int N, int64_t ldf, int d, int k1, int k2, int use_float16,
                      float lambda_value, int row0, int nrows, int col0, int ncols, void* out,
                      int64_t ldo, int32_t* rank_out, void* workspace, size_t workspace_bytes,

@@ -69,22 +69,6 @@ int pack_rows_launch(const float* x, int rows, int64_t ldx, int d, void* packed,
   return REIDB200_OK;
 }
 
-// ------------------------------------------------------------------------------------ epilogue math
-__device__ __forceinline__ float dist_epilogue(int kind, float acc, float xx, float yy) {
-  switch (kind) {
-    case REIDB200_DIST_DOT:
-      return acc;
-    case REIDB200_DIST_SQL2:
-      return fmaf(-2.0f, acc, __fadd_rn(xx, yy));
-    case REIDB200_DIST_EUCLID:
-      return sqrtf(fmaxf(fmaf(-2.0f, acc, __fadd_rn(xx, yy)), 1e-12f));
-    default: {  // COSINE_HALF: (1 - xy / (|x| |y|)) / 2
-      const float den = __fmul_rn(sqrtf(xx), sqrtf(yy));
-      return __fmul_rn(__fsub_rn(1.0f, __fdiv_rn(acc, den)), 0.5f);
-    }
-  }
-}
-
 // ------------------------------------------------------------------------------------ tcgen05 kernel
 constexpr int BM = 128, BN = 256, BK = 64;
 constexpr int STAGES = 2;
@@ -119,12 +103,25 @@ struct GemmArgs {
   // epilogue store is then one contiguous 4 KB piece of DRAM instead of 32 pieces of 128 B a row stride apart.
   int blocked;
   int debug;      // timing experiments only (REIDB200_GEMM_DEBUG): 1 = no mirror store, 2 = no stores, 4 = no epilogue
+  SelArgs sel;    // sel.tau != null: selection fused into the epilogue (gemm.cuh); only sel.st_* of the output is stored
 };
 
 // tile index -> (tm, tn) of the CTA-pair kernel.  Symmetric mode enumerates the upper triangle column by column:
 // tile = tn (tn + 1) / 2 + tm, tm <= tn.
 __device__ __forceinline__ void pair_tile_coords(int tile, int tiles_m2, int symmetric, int& tm, int& tn) {
   if (!symmetric) { tm = tile % tiles_m2; tn = tile / tiles_m2; return; }
+  if (symmetric == 2) {
+    // selection mode: the diagonal tiles come first (every row meets its own 256 columns before anything else, which gives
+    // its threshold a first value), then the strict upper triangle column by column
+    if (tile < tiles_m2) { tm = tn = tile; return; }
+    const int u = tile - tiles_m2;
+    int b = (int)((sqrtf(8.0f * (float)u + 1.0f) + 1.0f) * 0.5f);  // u = b (b - 1) / 2 + tm, tm < b
+    while (b * (b + 1) / 2 <= u) ++b;
+    while (b * (b - 1) / 2 > u) --b;
+    tn = b;
+    tm = u - b * (b - 1) / 2;
+    return;
+  }
   int b = (int)((sqrtf(8.0f * (float)tile + 1.0f) - 1.0f) * 0.5f);
   while ((b + 1) * (b + 2) / 2 <= tile) ++b;
   while (b * (b + 1) / 2 > tile) --b;
@@ -177,6 +174,48 @@ __device__ __forceinline__ float epi_value(float r, float ia, float sv, float xx
 // accumulator-full barrier; the wait for the staging buffer (previous TMA store has read it) comes after the math.
 // `yw` = 64 floats of shared memory private to this warp (column norms | column scale factors of the current chunk,
 // read back as broadcast 128-bit loads).
+// ---- selection in the epilogue (SelArgs, gemm.cuh)
+__device__ __forceinline__ uint32_t sel_key_of(float v, int descending) {
+  const uint32_t u = float_to_ordered(v);
+  return descending ? ~u : u;
+}
+
+// append (key, idx) to `row`'s list; returns the row if this append completed a window (the caller tightens it), else -1
+__device__ __noinline__ int sel_append(const SelArgs& s, int row, uint32_t key, int idx) {
+  const uint32_t pos = atomicAdd(s.resv + row, 1u);
+  if (pos < (uint32_t)s.cap) {
+    s.list[(size_t)row * s.cap + pos] = ((unsigned long long)key << 32) | (uint32_t)idx;
+    __threadfence();  // the entry is visible before its commit
+  }
+  atomicAdd(s.comm + row, 1u);
+  return (pos + 1 <= (uint32_t)s.cap && (pos + 1) % (uint32_t)s.window == 0) ? row : -1;
+}
+
+// One warp: tau[row] <- min(tau[row], k-th smallest key of the row's `window` most recent entries).  Those entries are
+// elements of the row, so their k-th smallest is a valid upper bound of the row's k-th best value; and since they all
+// passed the previous threshold the bound shrinks geometrically (quantile k / window of the values below the old one)
+// until fewer than `window` further elements qualify.  Skipped when an append is in flight (commit != reserve).
+__device__ __noinline__ void sel_tighten_row(const SelArgs& s, int row, int lane) {
+  const uint32_t c = *reinterpret_cast<volatile uint32_t*>(s.comm + row);
+  const uint32_t r = *reinterpret_cast<volatile uint32_t*>(s.resv + row);
+  if (c != r || r > (uint32_t)s.cap || r < (uint32_t)s.window) return;  // warp-uniform (same addresses)
+  const unsigned long long* e = s.list + (size_t)row * s.cap + (r - s.window);
+  const int per = s.window >> 5;  // <= 16
+  uint32_t key[16];
+#pragma unroll
+  for (int i = 0; i < 16; ++i) key[i] = i < per ? (uint32_t)(__ldcg(e + i * 32 + lane) >> 32) : 0xffffffffu;
+  uint32_t lo = 0, hi = 0xffffffffu;
+  while (lo < hi) {
+    const uint32_t mid = lo + ((hi - lo) >> 1);
+    int cnt = 0;
+#pragma unroll
+    for (int i = 0; i < 16; ++i) cnt += key[i] <= mid;
+    cnt = __reduce_add_sync(0xffffffffu, cnt);
+    if (cnt >= s.k) hi = mid; else lo = mid + 1;
+  }
+  if (lane == 0) atomicMin(s.tau + row, lo);
+}
+
 template <int KIND>
 __device__ __forceinline__ void epilogue_slab(const GemmArgs& a, const CUtensorMap* tmO, uint32_t bar_full, uint32_t parity,
                                               uint32_t tmem_addr, int row0, int col_base, int c_first, int lane, float* sb,
@@ -316,6 +355,140 @@ __device__ __forceinline__ void epilogue_slab(const GemmArgs& a, const CUtensorM
   }
 }
 
+// Epilogue of one warp's accumulator columns in SELECTION mode: the same math as epilogue_slab, but instead of storing the
+// tile the warp filters it against the rows' thresholds (and, for a mirrored tile of a symmetric product, against the
+// thresholds of the columns).  Fast path per 32 x 32 chunk: the row minimum of the chunk (already needed) is compared with
+// the row's threshold and with the largest threshold among the chunk's 32 columns -- two compares; only a thread that
+// passes walks its 32 values and appends.  Rows whose list completed a window are tightened by the warp after the slab.
+// Only the part of the output inside sel.st_* is still stored (the query x gallery block the lambda blend reads).
+// `yw` = 64 floats of shared memory private to this warp: column norms (then the column thresholds, as uint) | column scales.
+template <int KIND>
+__device__ __forceinline__ void epilogue_select(const GemmArgs& a, const CUtensorMap* tmO, uint32_t bar_full, uint32_t parity,
+                                                uint32_t tmem_addr, int row0, int col_base, int c_first, int lane, float* sb,
+                                                float* yw, bool sym_t) {
+  const SelArgs& S = a.sel;
+  const int my_row = row0 + lane;
+  const int rows_here = min(32, a.m - row0);
+  const int nch = rows_here <= 0 ? 0 : min(BN / 32, (a.n - col_base + 31) >> 5);  // warp-uniform
+  uint32_t* tcw = reinterpret_cast<uint32_t*>(yw);  // the column thresholds take the place of the column norms after the math
+  float xx_mine = 0.f, ia_mine = 0.f, yn = 0.f, sn = 0.f;
+  uint32_t tau_row = 0u, tcn = 0u;
+  if (c_first < nch) {
+    if (my_row < a.m) {
+      if (KIND != REIDB200_DIST_DOT) xx_mine = __ldg(a.xx + my_row);
+      ia_mine = __ldg(a.isa + my_row);
+      tau_row = __ldcg(S.tau + my_row);  // (a stale value is only a looser filter)
+    }
+    if (col_base + c_first * 32 + lane < a.n) {
+      if (KIND != REIDB200_DIST_DOT) yn = __ldg(a.yy + col_base + c_first * 32 + lane);
+      sn = __ldg(a.isb + col_base + c_first * 32 + lane);
+      if (sym_t) tcn = __ldcg(S.tau + col_base + c_first * 32 + lane);
+    }
+  }
+  ptx::mbar_wait(bar_full, parity);
+  ptx::tc_fence_after();
+  if (c_first >= nch) return;
+  const bool st_rows = row0 < S.st_r1 && row0 + 32 > S.st_r0;        // direct block rows inside the stored region
+  const bool st_rows_t = sym_t && row0 < S.st_c1 && row0 + 32 > S.st_c0;  // mirrored block: these rows are its COLUMNS
+  int pending = -1;
+  uint32_t rn[32];
+  ptx::tmem_ld_32x32b_x32(tmem_addr + c_first * 32, rn);
+#pragma unroll 1
+  for (int c = c_first; c < nch; c += 2) {
+    const int col0 = col_base + c * 32;
+    yw[lane] = yn;
+    yw[32 + lane] = epi_colscale<KIND>(sn);
+    const uint32_t tc_cur = tcn;
+    const uint32_t tc_max = __reduce_max_sync(0xffffffffu, tcn);
+    float o[32];
+    ptx::tmem_ld_wait(rn);
+#pragma unroll
+    for (int j = 0; j < 32; ++j) o[j] = __uint_as_float(rn[j]);
+    if (c + 2 < nch) {
+      ptx::tmem_ld_32x32b_x32(tmem_addr + (c + 2) * 32, rn);
+      yn = 0.f; sn = 0.f; tcn = 0u;
+      if (col0 + 64 + lane < a.n) {
+        if (KIND != REIDB200_DIST_DOT) yn = __ldg(a.yy + col0 + 64 + lane);
+        sn = __ldg(a.isb + col0 + 64 + lane);
+        if (sym_t) tcn = __ldcg(S.tau + col0 + 64 + lane);
+      }
+    }
+    __syncwarp();
+    const bool full = col0 + 32 <= a.n;
+#pragma unroll
+    for (int j = 0; j < 32; j += 4) {
+      const float4 y4 = *reinterpret_cast<const float4*>(yw + j);
+      const float4 s4 = *reinterpret_cast<const float4*>(yw + 32 + j);
+      o[j + 0] = epi_value<KIND>(o[j + 0], ia_mine, s4.x, xx_mine, y4.x);
+      o[j + 1] = epi_value<KIND>(o[j + 1], ia_mine, s4.y, xx_mine, y4.y);
+      o[j + 2] = epi_value<KIND>(o[j + 2], ia_mine, s4.z, xx_mine, y4.z);
+      o[j + 3] = epi_value<KIND>(o[j + 3], ia_mine, s4.w, xx_mine, y4.w);
+    }
+    // best value of this thread's row over the chunk (columns beyond n do not take part)
+    float red = S.descending ? -INFINITY : INFINITY;
+    if (full) {
+      float t[16];
+#pragma unroll
+      for (int j = 0; j < 16; ++j) t[j] = S.descending ? fmaxf(o[j], o[j + 16]) : fminf(o[j], o[j + 16]);
+#pragma unroll
+      for (int w = 8; w >= 1; w >>= 1) {
+#pragma unroll
+        for (int j = 0; j < w; ++j) t[j] = S.descending ? fmaxf(t[j], t[j + w]) : fminf(t[j], t[j + w]);
+      }
+      red = t[0];
+    } else {
+#pragma unroll
+      for (int j = 0; j < 32; ++j)
+        if (col0 + j < a.n) red = S.descending ? fmaxf(red, o[j]) : fminf(red, o[j]);
+    }
+    __syncwarp();          // every lane has read the column norms / scales
+    tcw[lane] = tc_cur;
+    __syncwarp();
+    const uint32_t kred = sel_key_of(red, S.descending);
+    const bool row_ok = my_row < a.m;
+    if (row_ok && (kred <= tau_row || (sym_t && kred <= tc_max))) {
+      // slow path (rare once the thresholds are tight): walk the 32 values
+#pragma unroll
+      for (int j = 0; j < 32; ++j) {  // (fully unrolled: o[] must stay in registers)
+        const uint32_t kj = sel_key_of(o[j], S.descending);
+        const bool in = full || col0 + j < a.n;
+        if (in && kj <= tau_row) { const int p = sel_append(S, my_row, kj, col0 + j); if (p >= 0) pending = p; }
+        if (in && sym_t && kj <= tcw[j]) { const int p = sel_append(S, col0 + j, kj, my_row); if (p >= 0) pending = p; }
+      }
+    }
+    // ---- the part of the output that is still stored
+    const bool st_direct = st_rows && col0 < S.st_c1 && col0 + 32 > S.st_c0;
+    const bool st_mirror = st_rows_t && col0 < S.st_r1 && col0 + 32 > S.st_r0;
+    if (st_direct) {  // warp-uniform
+      if (lane == 0) ptx::bulk_wait_read<0>();
+      __syncwarp();
+#pragma unroll
+      for (int j = 0; j < 32; j += 4)
+        *reinterpret_cast<float4*>(sb + lane * 32 + (((j >> 2) ^ (lane & 7)) << 2)) = make_float4(o[j], o[j + 1], o[j + 2], o[j + 3]);
+      ptx::fence_proxy_async();
+      __syncwarp();
+      if (lane == 0) {
+        ptx::tma_store_2d(tmO, ptx::smem_u32(sb), col0, row0);
+        ptx::bulk_commit();
+      }
+    }
+    if (st_mirror && row_ok) {  // out[col0 + j, row0 + lane]: one coalesced 128-byte store per mirror row
+      float* mp = a.out + (size_t)col0 * a.ldo + my_row;
+#pragma unroll
+      for (int j = 0; j < 32; ++j)
+        if (col0 + j < a.n) mp[(size_t)j * a.ldo] = o[j];
+    }
+    __syncwarp();  // the threshold / norm staging of this chunk has been read by every lane
+  }
+  // ---- tighten the rows whose list completed a window during this slab (the warp works on one row at a time)
+  uint32_t pend = __ballot_sync(0xffffffffu, pending >= 0);
+  while (pend) {
+    const int src = __ffs(pend) - 1;
+    pend &= pend - 1;
+    sel_tighten_row(S, __shfl_sync(0xffffffffu, pending, src), lane);
+  }
+}
+
 template <int KIND>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
 gemm_split_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
@@ -421,8 +594,12 @@ gemm_split_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
     uint32_t aphase = 0;
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
       const int tm = tile % a.tiles_m, tn = tile / a.tiles_m;
-      epilogue_slab<KIND>(a, &tmO, bar_tfull + 8 * as, aphase, tmem_base + ((uint32_t)(q * 32) << 16) + as * BN,
-                          tm * BM + q * 32, tn * BN, c_first, lane, sbuf, yw_buf + (warp - 2) * 64, vec_ok);
+      if (a.sel.tau)
+        epilogue_select<KIND>(a, &tmO, bar_tfull + 8 * as, aphase, tmem_base + ((uint32_t)(q * 32) << 16) + as * BN,
+                              tm * BM + q * 32, tn * BN, c_first, lane, sbuf, yw_buf + (warp - 2) * 64, false);
+      else
+        epilogue_slab<KIND>(a, &tmO, bar_tfull + 8 * as, aphase, tmem_base + ((uint32_t)(q * 32) << 16) + as * BN,
+                            tm * BM + q * 32, tn * BN, c_first, lane, sbuf, yw_buf + (warp - 2) * 64, vec_ok);
       ptx::tc_fence_before();
       __syncwarp();
       if (lane == 0) ptx::mbar_arrive(bar_tempty + 8 * as);
@@ -563,9 +740,14 @@ gemm_split_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
     for (int tile = cluster_id; tile < total_tiles; tile += num_clusters) {
       int tm, tn;
       pair_tile_coords(tile, tiles_m2, a.symmetric, tm, tn);
-      epilogue_slab<KIND>(a, &tmO, bar_tfull + 8 * as, aphase, tmem_base + ((uint32_t)(q * 32) << 16) + as * BN,
-                          tm * 2 * BM + (int)rank * BM + q * 32, tn * BN, c_first, lane, sbuf, yw_buf + (warp - 2) * 64,
-                          vec_ok, a.symmetric && tn != tm);
+      if (a.sel.tau)
+        epilogue_select<KIND>(a, &tmO, bar_tfull + 8 * as, aphase, tmem_base + ((uint32_t)(q * 32) << 16) + as * BN,
+                              tm * 2 * BM + (int)rank * BM + q * 32, tn * BN, c_first, lane, sbuf, yw_buf + (warp - 2) * 64,
+                              a.symmetric && tn != tm);
+      else
+        epilogue_slab<KIND>(a, &tmO, bar_tfull + 8 * as, aphase, tmem_base + ((uint32_t)(q * 32) << 16) + as * BN,
+                            tm * 2 * BM + (int)rank * BM + q * 32, tn * BN, c_first, lane, sbuf, yw_buf + (warp - 2) * 64,
+                            vec_ok, a.symmetric && tn != tm);
       ptx::tc_fence_before();
       __syncwarp();
       if (lane == 0) ptx::mbar_arrive_leader(bar_tempty + 8 * as);
@@ -667,9 +849,27 @@ static int make_output_map(CUtensorMap* tm, float* out, int m, int n, int64_t ld
   return REIDB200_OK;
 }
 
+static int gemm_launch_impl(const void* packedA, const float* xx, const float* isa, int m, const void* packedB, const float* yy,
+                            const float* isb, int n, int d, int kind, float* out, int64_t ldo, cudaStream_t st, float* chunk_red,
+                            int64_t ld_chunk_red, int chunk_red_max, int blocked, const SelArgs* sel);
+
 int gemm_split_launch(const void* packedA, const float* xx, const float* isa, int m, const void* packedB, const float* yy,
                       const float* isb, int n, int d, int kind, float* out, int64_t ldo, cudaStream_t st, float* chunk_red,
                       int64_t ld_chunk_red, int chunk_red_max, int blocked) {
+  return gemm_launch_impl(packedA, xx, isa, m, packedB, yy, isb, n, d, kind, out, ldo, st, chunk_red, ld_chunk_red, chunk_red_max,
+                          blocked, nullptr);
+}
+
+int gemm_split_select_launch(const void* packedA, const float* xx, const float* isa, int m, const void* packedB, const float* yy,
+                             const float* isb, int n, int d, int kind, float* out, int64_t ldo, const SelArgs& sel, cudaStream_t st) {
+  RB_REQUIRE(sel.tau && sel.resv && sel.comm && sel.list && sel.cap > 0 && sel.k > 0 && sel.window >= sel.k && sel.window <= 512 &&
+             (sel.window & 31) == 0, "distmat(select): bad selection state");
+  return gemm_launch_impl(packedA, xx, isa, m, packedB, yy, isb, n, d, kind, out, ldo, st, nullptr, 0, 0, 0, &sel);
+}
+
+static int gemm_launch_impl(const void* packedA, const float* xx, const float* isa, int m, const void* packedB, const float* yy,
+                            const float* isb, int n, int d, int kind, float* out, int64_t ldo, cudaStream_t st, float* chunk_red,
+                            int64_t ld_chunk_red, int chunk_red_max, int blocked, const SelArgs* sel) {
   if (m == 0 || n == 0) return REIDB200_OK;
   RB_REQUIRE(isa && isb, "distmat: operand scales missing");
   RB_REQUIRE(kind >= 0 && kind <= 3, "distmat: unknown kind %d", kind);
@@ -686,9 +886,16 @@ int gemm_split_launch(const void* packedA, const float* xx, const float* isa, in
   a.tiles_m = ceil_div(m, BM); a.tiles_n = ceil_div(n, BN);
   a.kind = kind; a.xx = xx; a.yy = yy; a.isa = isa; a.isb = isb; a.out = out; a.ldo = ldo;
   a.cred = chunk_red; a.ldcr = ld_chunk_red; a.cred_max = chunk_red_max;
+  memset(&a.sel, 0, sizeof(a.sel));
+  const bool want_store = !sel || (sel->st_r1 > sel->st_r0 && sel->st_c1 > sel->st_c0);
+  if (sel) {
+    a.sel = *sel;
+    if (!want_store) { a.sel.st_r0 = a.sel.st_r1 = a.sel.st_c0 = a.sel.st_c1 = 0; }
+    RB_REQUIRE(!want_store || out, "distmat(select): a stored block needs an output matrix");
+  }
   CUtensorMap tmO;
   memset(&tmO, 0, sizeof(tmO));
-  a.tma_out = (ldo & 3) == 0 && (reinterpret_cast<uintptr_t>(out) & 15) == 0 &&
+  a.tma_out = out != nullptr && (ldo & 3) == 0 && (reinterpret_cast<uintptr_t>(out) & 15) == 0 &&
               (yy == nullptr || (reinterpret_cast<uintptr_t>(yy) & 15) == 0) && (reinterpret_cast<uintptr_t>(isb) & 15) == 0;
   a.blocked = blocked ? ceil_div(n, 32) : 0;
   if (blocked) {
@@ -699,9 +906,11 @@ int gemm_split_launch(const void* packedA, const float* xx, const float* isa, in
     rc = make_output_map(&tmO, out, m, n, ldo);
     if (rc) return rc;
   }
+  RB_REQUIRE(!sel || !want_store || a.tma_out, "distmat(select): the stored block needs 16-byte aligned rows");
   // self distances: compute the upper triangle of 256 x 256 tiles only and store every off-diagonal tile twice
   a.debug = getenv("REIDB200_GEMM_DEBUG") ? atoi(getenv("REIDB200_GEMM_DEBUG")) : 0;
-  a.symmetric = pair && a.tma_out && packedA == packedB && m == n && xx == yy && isa == isb && !getenv("REIDB200_GEMM_NOSYM");
+  a.symmetric = pair && (a.tma_out || sel) && packedA == packedB && m == n && xx == yy && isa == isb && !getenv("REIDB200_GEMM_NOSYM");
+  if (a.symmetric && sel) a.symmetric = 2;  // selection: diagonal tiles first (pair_tile_coords)
   void (*k1)(CUtensorMap, CUtensorMap, CUtensorMap, GemmArgs) = nullptr;
   void (*k2)(CUtensorMap, CUtensorMap, CUtensorMap, GemmArgs) = nullptr;
   switch (kind) {

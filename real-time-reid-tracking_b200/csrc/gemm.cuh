@@ -24,6 +24,58 @@ int gemm_split_launch(const void* packedA, const float* xx, const float* isa, in
                       const float* isb, int n, int d, int kind, float* out, int64_t ldo, cudaStream_t st,
                       float* chunk_red = nullptr, int64_t ld_chunk_red = 0, int chunk_red_max = 0, int blocked = 0);
 
+// epilogue formulas of the four kinds (shared by the GEMM, its SIMT cross-check and the selection redo)
+#ifdef __CUDACC__
+__device__ __forceinline__ float dist_epilogue(int kind, float acc, float xx, float yy) {
+  switch (kind) {
+    case REIDB200_DIST_DOT:
+      return acc;
+    case REIDB200_DIST_SQL2:
+      return fmaf(-2.0f, acc, __fadd_rn(xx, yy));
+    case REIDB200_DIST_EUCLID:
+      return sqrtf(fmaxf(fmaf(-2.0f, acc, __fadd_rn(xx, yy)), 1e-12f));
+    default: {  // COSINE_HALF: (1 - xy / (|x| |y|)) / 2
+      const float den = __fmul_rn(sqrtf(xx), sqrtf(yy));
+      return __fmul_rn(__fsub_rn(1.0f, __fdiv_rn(acc, den)), 0.5f);
+    }
+  }
+}
+
+#endif
+
+// ---- selection fused into the GEMM epilogue (no distance block): per output row an append-only candidate list and a
+// threshold that only tightens.  Invariant: tau[row] is the ordered key of an upper bound of the row's k-th best value
+// (there are at least k elements of the row whose key is <= tau), so every element of the true top-k passes the filter
+// `key <= tau` whenever it is produced, and the exact top-k is the k best entries of the list (topk.cu select_lists).
+//   tau   u32[m]  init 0xFFFFFFFF        resv / comm  u32[m]  entries reserved / committed (a list is readable when equal)
+//   list  u64[m, cap]  (key << 32) | column;  a row whose resv exceeds cap is redone exactly (knn_select_finish)
+// Symmetric products (A == B) use the same arrays for the mirrored element (row = column index, entry = row index).
+struct SelArgs {
+  uint32_t* tau;
+  uint32_t* resv;
+  uint32_t* comm;
+  unsigned long long* list;
+  int cap, k, window, descending;
+  int st_r0, st_r1, st_c0, st_c1;  // block of the output that is still STORED (rows [r0, r1) x columns [c0, c1)); empty = none
+};
+
+int gemm_split_select_launch(const void* packedA, const float* xx, const float* isa, int m, const void* packedB, const float* yy,
+                             const float* isb, int n, int d, int kind, float* out, int64_t ldo, const SelArgs& sel, cudaStream_t st);
+
+// candidate-list capacity / tightening window the selection uses for a given k (0: k not supported, use the materialising path)
+inline int sel_window(int k) { return k <= 25 ? 64 : (k <= 128 ? ((5 * k / 2 + 31) / 32) * 32 : 0); }
+inline int sel_cap(int k) { return k <= 25 ? 1024 : (k <= 128 ? 4096 : 0); }
+size_t sel_workspace_bytes(int m, int n, int k);
+// carve + initialise (stream-ordered) the selection state of m rows inside `ws`
+int sel_prepare(void* ws, size_t ws_bytes, int m, int n, int k, int descending, SelArgs* out, float** scratch_rows, cudaStream_t st);
+// the k best entries of every row's list -> out_d f32[m, k], out_i (i64 | i32)[m, k]; rows whose list overflowed (massive
+// ties) are redone exactly by a small persistent kernel from the packed operands (scratch: SEL_REDO_CTAS * n floats,
+// carved by sel_prepare); kind SQL2 or DOT
+constexpr int SEL_REDO_CTAS = 8;
+int knn_select_finish(const SelArgs& sel, int m, int n, int k, int kind, const void* packedA, const float* xx, const float* isa,
+                      const void* packedB, const float* yy, const float* isb, int d, int64_t index_base, float* out_d, void* out_i,
+                      int idx64, float* scratch_rows, cudaStream_t st);
+
 // TMA descriptor of a packed operand [rows, 2*dp] fp16: box = {64 k-elements, box_rows}, SWIZZLE_128B, OOB reads as zero.
 int make_operand_map(CUtensorMap* tm, const void* packed, int rows, int dp, int box_rows);
 

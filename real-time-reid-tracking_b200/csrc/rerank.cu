@@ -81,6 +81,48 @@ krecip_both_kernel(const int32_t* __restrict__ rank, int N, int k1_cols, int kc,
   if (lane == 0) { full_cnt[i] = cnt; half_cnt[i] = cnth; }
 }
 
+// ------------------------------------------------------------------------------------ D4: where x_i . x_c comes from
+// The reference computes dist = 2 - 2 x_i . X_e^T with one small torch.mm per row (faiss_utils.py:201-204).  Here the
+// squared-L2 value of a pair comes from one of two places:
+//   * a materialised squared-L2 matrix (reidb200_jaccard_from_rank: the caller owns one), or
+//   * when the k-NN was selected inside the GEMM epilogue (no N x N matrix exists): the row's own top-k1 list if the
+//     candidate is in it (the GEMM's value, bit for bit), else a direct fp32 dot product of the two feature rows
+//     (warp-cooperative, rows are L2 resident) put through the GEMM's epilogue formula.  Both evaluation paths (fused /
+//     dense output) run the same kernels, so their results stay bit-identical.
+struct PairSrc {
+  const float* sql2; int64_t lds;           // materialised matrix, or null
+  const float* feats; int64_t ldf; int d;   // fp32 feature rows (used when sql2 is null)
+  const int32_t* rank_i; const float* rank_d; int k1c;  // the rows' top-k1 lists
+};
+
+// one thread: squared L2 of (i, c) (the CTA fallback kernel for k1 > 32; the warp kernel has its own cooperative version)
+__device__ float pair_sql2_thread(const PairSrc& P, const float* __restrict__ sqnorm, int i, int c) {
+  if (P.sql2) return P.sql2[(size_t)i * P.lds + c];
+  for (int t = 0; t < P.k1c; ++t)
+    if (P.rank_i[(size_t)i * P.k1c + t] == c) return P.rank_d[(size_t)i * P.k1c + t];
+  const float* a = P.feats + (size_t)i * P.ldf;
+  const float* b = P.feats + (size_t)c * P.ldf;
+  float acc = 0.f;
+  for (int k = 0; k < P.d; ++k) acc = fmaf(a[k], b[k], acc);
+  return fmaf(-2.0f, acc, __fadd_rn(sqnorm[i], sqnorm[c]));
+}
+
+// one warp: x_i . x_c, every lane returns the sum (lane l owns elements 4l..4l+3, +128, ...)
+__device__ __forceinline__ float pair_dot_warp(const float* __restrict__ a, const float* __restrict__ b, int d, int lane, bool vec) {
+  float acc = 0.f;
+  if (vec) {
+    for (int k = lane * 4; k < d; k += 128) {
+      const float4 x = __ldg(reinterpret_cast<const float4*>(a + k)), y = __ldg(reinterpret_cast<const float4*>(b + k));
+      acc = fmaf(x.x, y.x, acc); acc = fmaf(x.y, y.y, acc); acc = fmaf(x.z, y.z, acc); acc = fmaf(x.w, y.w, acc);
+    }
+  } else {
+    for (int k0 = lane * 4; k0 < d; k0 += 128)
+      for (int e = 0; e < 4; ++e)
+        if (k0 + e < d) acc = fmaf(__ldg(a + k0 + e), __ldg(b + k0 + e), acc);
+  }
+  return warp_sum(acc);
+}
+
 // ------------------------------------------------------------------------------------ D4
 constexpr int EXP_THREADS = 128;
 
@@ -118,7 +160,7 @@ constexpr int EXP_MAX_K1 = 128;
 __global__ void __launch_bounds__(EXP_THREADS)
 expand_v_kernel(const int32_t* __restrict__ rfull, const int32_t* __restrict__ rfull_cnt, int wf,
                 const int32_t* __restrict__ rhalf, const int32_t* __restrict__ rhalf_cnt, int wh,
-                const float* __restrict__ sql2, int64_t lds, const float* __restrict__ sqnorm, int N, int cap, int P,
+                PairSrc src, const float* __restrict__ sqnorm, int N, int cap, int P,
                 int use_f16, int32_t* __restrict__ vcols, float* __restrict__ vvals, int32_t* __restrict__ vcnt) {
   extern __shared__ int sm_i[];
   int* K = sm_i;
@@ -183,7 +225,7 @@ expand_v_kernel(const int32_t* __restrict__ rfull, const int32_t* __restrict__ r
     const int c = K[r];
     if (c != SENT && (r == 0 || K[r - 1] != c)) {
       // dist = 2 - 2 x_i.x_c (faiss_utils.py:201-204), with x_i.x_c = (|x_i|^2 + |x_c|^2 - sql2)/2
-      const float dot = 0.5f * ((xi + sqnorm[c]) - sql2[(size_t)i * lds + c]);
+      const float dot = 0.5f * ((xi + sqnorm[c]) - pair_sql2_thread(src, sqnorm, i, c));
       const float nd = -(2.0f - 2.0f * dot);
       val[flag[r]] = nd;
       vcols[(size_t)i * cap + flag[r]] = c;
@@ -228,7 +270,7 @@ constexpr int EXW_WARPS = 4;
 __global__ void __launch_bounds__(EXW_WARPS * 32)
 expand_v_warp_kernel(const int32_t* __restrict__ rfull, const int32_t* __restrict__ rfull_cnt, int wf,
                      const int32_t* __restrict__ rhalf, const int32_t* __restrict__ rhalf_cnt, int wh,
-                     const float* __restrict__ sql2, int64_t lds, const float* __restrict__ sqnorm, int N, int cap,
+                     PairSrc src, const float* __restrict__ sqnorm, int N, int cap,
                      int use_f16, int32_t* __restrict__ vcols, float* __restrict__ vvals, int32_t* __restrict__ vcnt) {
   __shared__ int s_base[EXW_WARPS][32], s_nc[EXW_WARPS][32], s_inter[EXW_WARPS][32];
   constexpr uint32_t SENT = 0x7fffffffu;
@@ -299,13 +341,46 @@ expand_v_warp_kernel(const int32_t* __restrict__ rfull, const int32_t* __restric
   const float xi = sqnorm[i];
   float nd[8];
   float lmax = -INFINITY;
+  // squared L2 of (i, candidate) for this lane's unique candidates
+  float d2[8];
+  uint32_t need = 0;  // candidates whose value is neither in a matrix nor in the row's own top-k1 list
+#pragma unroll
+  for (int s = 0; s < 8; ++s) {
+    d2[s] = 0.f;
+    if (head[s]) {
+      const int c = (int)k[s];
+      if (src.sql2) {
+        d2[s] = src.sql2[(size_t)i * src.lds + c];
+      } else {
+        bool hit = false;
+        for (int t = 0; t < src.k1c; ++t)
+          if (src.rank_i[(size_t)i * src.k1c + t] == c) { d2[s] = src.rank_d[(size_t)i * src.k1c + t]; hit = true; }
+        if (!hit) need |= 1u << s;
+      }
+    }
+  }
+  if (!src.sql2) {  // warp-uniform: the misses of all lanes, one cooperative dot product each
+    const float* xa = src.feats + (size_t)i * src.ldf;
+    const bool vec = (src.d & 3) == 0 && (src.ldf & 3) == 0 && (reinterpret_cast<uintptr_t>(src.feats) & 15) == 0;
+#pragma unroll
+    for (int s = 0; s < 8; ++s) {
+      uint32_t todo = __ballot_sync(0xffffffffu, (need >> s) & 1u);
+      while (todo) {
+        const int owner = __ffs(todo) - 1;
+        todo &= todo - 1;
+        const int c = (int)__shfl_sync(0xffffffffu, k[s], owner);
+        const float dot = pair_dot_warp(xa, src.feats + (size_t)c * src.ldf, src.d, lane, vec);
+        if (lane == owner) d2[s] = fmaf(-2.0f, dot, __fadd_rn(xi, sqnorm[c]));
+      }
+    }
+  }
 #pragma unroll
   for (int s = 0; s < 8; ++s) {
     nd[s] = -INFINITY;
     if (head[s]) {
       // dist = 2 - 2 x_i.x_c (faiss_utils.py:201-204), with x_i.x_c = (|x_i|^2 + |x_c|^2 - sql2)/2
       const int c = (int)k[s];
-      const float dot = 0.5f * ((xi + sqnorm[c]) - sql2[(size_t)i * lds + c]);
+      const float dot = 0.5f * ((xi + sqnorm[c]) - d2[s]);
       nd[s] = -(2.0f - 2.0f * dot);
       lmax = fmaxf(lmax, nd[s]);
     }
@@ -795,10 +870,12 @@ static int rerank_check(int N, int k1, int k2, const RerankDims& d) {
 
 static size_t jaccard_rows_smem(int N, int cap) { return (size_t)((N + 3) & ~3) * 4 + (size_t)cap * 12 + 16; }
 
+// `sql2` (row stride lds) is read by the lambda blend only, for the output region; `src` says where the expansion's pair
+// values come from (PairSrc)
 static int jaccard_sparse_stages(const int32_t* rank, const float* sql2, int64_t lds, const float* sqnorm, int N, int k1,
                                  int k2, int use_f16, float lambda_value, int row0, int nrows, int col0, int ncols,
                                  void* out, int64_t ldo, const RerankDims& d, const SparseWs& w, cudaStream_t st,
-                                 const EvalFuse* ev = nullptr) {
+                                 const PairSrc& src, const EvalFuse* ev = nullptr) {
   static DeviceOnce attr;
   if (attr.pending()) {
     RB_CUDA(cudaFuncSetAttribute(expand_v_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 4096 * 12));
@@ -811,12 +888,12 @@ static int jaccard_sparse_stages(const int32_t* rank, const float* sql2, int64_t
   RB_LAUNCH_CHECK("krecip_both_kernel");
   if (k1 <= 32 && k1 + k1 * d.wh <= 256) {
     { ProfScope _ps("expand_v_kernel", st); expand_v_warp_kernel<<<ceil_div(N, EXW_WARPS), EXW_WARPS * 32, 0, st>>>(
-        w.rfull, w.rfull_cnt, k1, w.rhalf, w.rhalf_cnt, d.wh, sql2, lds, sqnorm, N, d.cap1, use_f16, w.v1cols, w.v1vals, w.v1cnt); }
+        w.rfull, w.rfull_cnt, k1, w.rhalf, w.rhalf_cnt, d.wh, src, sqnorm, N, d.cap1, use_f16, w.v1cols, w.v1vals, w.v1cnt); }
   } else {
     int expP = 32;
     while (expP < d.cap1) expP <<= 1;
-    { ProfScope _ps("expand_v_kernel", st); expand_v_kernel<<<N, EXP_THREADS, (size_t)expP * 12, st>>>(w.rfull, w.rfull_cnt, k1, w.rhalf, w.rhalf_cnt, d.wh, sql2,
-                                                                  lds, sqnorm, N, d.cap1, expP, use_f16, w.v1cols, w.v1vals,
+    { ProfScope _ps("expand_v_kernel", st); expand_v_kernel<<<N, EXP_THREADS, (size_t)expP * 12, st>>>(w.rfull, w.rfull_cnt, k1, w.rhalf, w.rhalf_cnt, d.wh, src,
+                                                                  sqnorm, N, d.cap1, expP, use_f16, w.v1cols, w.v1vals,
                                                                   w.v1cnt); }
   }
   RB_LAUNCH_CHECK("expand_v_kernel");
@@ -859,19 +936,49 @@ static int jaccard_sparse_stages(const int32_t* rank, const float* sql2, int64_t
 
 using namespace reidb200;
 
-extern "C" size_t reidb200_jaccard_workspace_bytes(int N, int d, int k1, int k2) {
+// Workspace of the k-NN + sparse stages of one merged set.  The squared-L2 matrix is NOT materialised: the initial ranking
+// is selected inside the GEMM epilogue (gemm.cuh SelArgs) and only the rows the lambda blend reads (`blend_rows` of them,
+// 0 when lambda == 0) are stored, in a block of whole 32-row groups.
+struct JacWs {
+  char* packed; float* sqn; float* isc;
+  float* blk;            // [blk_rows, lds] rows of the squared-L2 matrix kept for the blend (or null)
+  float* rank_d; int32_t* rank_i;
+  char* selws; size_t selbytes;
+  SparseWs w;
+};
+
+static int blend_block_rows(int blend_rows, int N) {  // rows of whole 32-row groups that cover any `blend_rows` consecutive rows
+  if (blend_rows <= 0) return 0;
+  const int r = ((blend_rows + 31) & ~31) + 32;
+  return r < ((N + 31) & ~31) ? r : ((N + 31) & ~31);
+}
+
+template <class C>
+static void carve_jaccard(C& c, int N, int d, int k1, int k2, const RerankDims& rd, int blend_rows, JacWs* out) {
+  JacWs t;
+  t.packed = c.template take<char>(packed_bytes(N, d));
+  t.sqn = c.template take<float>(N);
+  t.isc = c.template take<float>(N);
+  const int br = blend_block_rows(blend_rows, N);
+  t.blk = br ? c.template take<float>((size_t)br * rd.lds) : nullptr;
+  t.rank_d = c.template take<float>((size_t)N * k1);
+  t.rank_i = c.template take<int32_t>((size_t)N * k1);
+  t.selbytes = sel_workspace_bytes(N, N, k1);
+  t.selws = c.template take<char>(t.selbytes);
+  carve_sparse(c, N, k1, k2, rd, &t.w);
+  if (out) *out = t;
+}
+
+extern "C" size_t reidb200_jaccard_region_workspace_bytes(int N, int d, int k1, int k2, int blend_rows) {
   if (N <= 0 || d <= 0 || k1 <= 0 || k2 <= 0) return 0;
   const RerankDims rd = rerank_dims(N, k1, k2);
   NullCarver c;
-  c.take<char>(packed_bytes(N, d));
-  c.take<float>(N);
-  c.take<float>(N);
-  c.take<float>((size_t)N * rd.lds);
-  c.take<float>((size_t)N * k1);
-  c.take<int32_t>((size_t)N * k1);
-  c.take<float>((size_t)N * ceil_div((int)rd.lds, 32));
-  carve_sparse(c, N, k1, k2, rd, nullptr);
+  carve_jaccard(c, N, d, k1, k2, rd, blend_rows, nullptr);
   return align_up(c.off, 256);
+}
+
+extern "C" size_t reidb200_jaccard_workspace_bytes(int N, int d, int k1, int k2) {
+  return reidb200_jaccard_region_workspace_bytes(N, d, k1, k2, N);  // any region, any lambda
 }
 
 static int region_check(int N, int row0, int nrows, int col0, int ncols, int64_t ldo) {
@@ -898,8 +1005,36 @@ extern "C" int reidb200_jaccard_from_rank(const int32_t* rank, const float* sql2
   Carver c(workspace, workspace_bytes);
   SparseWs w;
   carve_sparse(c, N, k1, k2, rd, &w);
+  PairSrc src;
+  memset(&src, 0, sizeof(src));
+  src.sql2 = sql2; src.lds = lds;
   return jaccard_sparse_stages(rank, sql2, lds, sqnorm, N, k1, k2, use_float16, lambda_value, row0, nrows, col0, ncols,
-                               out, ldo, rd, w, (cudaStream_t)stream);
+                               out, ldo, rd, w, (cudaStream_t)stream, src);
+}
+
+// D2 for one merged set without the N x N matrix: pack, GEMM with the selection in its epilogue (the rows
+// [blend_row0, blend_row0 + blend_rows) x all columns of the squared-L2 matrix are still stored for the lambda blend, into
+// ws.blk), k best entries of every list.  Returns the VIRTUAL base of the stored rows (row i at base + i * lds) or null.
+static int knn_stage(const float* feats, int N, int64_t ldf, int d, int k1, const RerankDims& rd, int blend_row0, int blend_rows,
+                     int blend_col0, int blend_cols, const JacWs& ws, const float** sql2_virtual, cudaStream_t st) {
+  int rc = pack_rows_launch(feats, N, ldf, d, ws.packed, ws.sqn, ws.isc, st);
+  if (rc) return rc;
+  SelArgs sel;
+  float* redo_scratch = nullptr;
+  rc = sel_prepare(ws.selws, ws.selbytes, N, N, k1, 0, &sel, &redo_scratch, st);
+  if (rc) return rc;
+  float* vbase = nullptr;
+  if (blend_rows > 0) {
+    const int r0a = blend_row0 & ~31;  // the epilogue stores whole 32 x 32 boxes
+    RB_REQUIRE(ws.blk && ((blend_row0 + blend_rows + 31) & ~31) - r0a <= blend_block_rows(blend_rows, N), "jaccard: blend block too small");
+    vbase = ws.blk - (ptrdiff_t)r0a * rd.lds;
+    sel.st_r0 = blend_row0; sel.st_r1 = blend_row0 + blend_rows; sel.st_c0 = blend_col0; sel.st_c1 = blend_col0 + blend_cols;
+  }
+  rc = gemm_split_select_launch(ws.packed, ws.sqn, ws.isc, N, ws.packed, ws.sqn, ws.isc, N, d, REIDB200_DIST_SQL2, vbase, rd.lds, sel, st);
+  if (rc) return rc;
+  *sql2_virtual = vbase;
+  return knn_select_finish(sel, N, N, k1, REIDB200_DIST_SQL2, ws.packed, ws.sqn, ws.isc, ws.packed, ws.sqn, ws.isc, d, 0, ws.rank_d,
+                           ws.rank_i, 0, redo_scratch, st);
 }
 
 extern "C" int reidb200_jaccard(const float* feats, int N, int64_t ldf, int d, int k1, int k2, int use_float16,
@@ -911,30 +1046,23 @@ extern "C" int reidb200_jaccard(const float* feats, int N, int64_t ldf, int d, i
   if (rc) return rc;
   rc = region_check(N, row0, nrows, col0, ncols, ldo);
   if (rc) return rc;
-  RB_REQUIRE(workspace && workspace_bytes >= reidb200_jaccard_workspace_bytes(N, d, k1, k2), "jaccard: workspace too small");
+  const int blend_rows = lambda_value > 0.f ? nrows : 0;
+  RB_REQUIRE(workspace && workspace_bytes >= reidb200_jaccard_region_workspace_bytes(N, d, k1, k2, blend_rows), "jaccard: workspace too small");
   RB_REQUIRE((reinterpret_cast<uintptr_t>(workspace) & 255) == 0, "jaccard: workspace must be 256-byte aligned");
   cudaStream_t st = (cudaStream_t)stream;
   Carver c(workspace, workspace_bytes);
-  char* packed = c.take<char>(packed_bytes(N, d));
-  float* sqn = c.take<float>(N);
-  float* isc = c.take<float>(N);
-  float* sql2 = c.take<float>((size_t)N * rd.lds);
-  float* rank_d = c.take<float>((size_t)N * k1);
-  int32_t* rank_i = c.take<int32_t>((size_t)N * k1);
-  const int ldcr = ceil_div((int)rd.lds, 32);
-  float* cred = c.take<float>((size_t)N * ldcr);
-  SparseWs w;
-  carve_sparse(c, N, k1, k2, rd, &w);
-  rc = pack_rows_launch(feats, N, ldf, d, packed, sqn, isc, st);
+  JacWs ws;
+  carve_jaccard(c, N, d, k1, k2, rd, blend_rows, &ws);
+  const float* sql2v = nullptr;
+  rc = knn_stage(feats, N, ldf, d, k1, rd, row0, blend_rows, col0, ncols, ws, &sql2v, st);
   if (rc) return rc;
-  rc = gemm_split_launch(packed, sqn, isc, N, packed, sqn, isc, N, d, REIDB200_DIST_SQL2, sql2, rd.lds, st, cred, ldcr, 0, 0);
-  if (rc) return rc;
-  rc = topk_rows_launch(sql2, N, N, rd.lds, nullptr, k1, 0, 0, rank_d, rank_i, 0, st, cred, ldcr);
-  if (rc) return rc;
-  if (rank_out) RB_CUDA(cudaMemcpyAsync(rank_out, rank_i, (size_t)N * k1 * sizeof(int32_t), cudaMemcpyDeviceToDevice, st));
+  if (rank_out) RB_CUDA(cudaMemcpyAsync(rank_out, ws.rank_i, (size_t)N * k1 * sizeof(int32_t), cudaMemcpyDeviceToDevice, st));
   if (nrows == 0 || ncols == 0) return REIDB200_OK;
-  return jaccard_sparse_stages(rank_i, sql2, rd.lds, sqn, N, k1, k2, use_float16, lambda_value, row0, nrows, col0, ncols,
-                               out, ldo, rd, w, st);
+  PairSrc src;
+  memset(&src, 0, sizeof(src));
+  src.feats = feats; src.ldf = ldf; src.d = d; src.rank_i = ws.rank_i; src.rank_d = ws.rank_d; src.k1c = k1;
+  return jaccard_sparse_stages(ws.rank_i, sql2v, rd.lds, ws.sqn, N, k1, k2, use_float16, lambda_value, row0, nrows, col0, ncols,
+                               out, ldo, rd, ws.w, st, src);
 }
 
 extern "C" int reidb200_k_reciprocal(const int32_t* rank, int N, int k1_cols, int k, int32_t* out_idx, int32_t* out_cnt,
@@ -952,7 +1080,7 @@ extern "C" int reidb200_k_reciprocal(const int32_t* rank, int N, int k1_cols, in
 extern "C" size_t reidb200_rerank_eval_workspace_bytes(int N, int d, int k1, int k2, int Q, int G) {
   if (N <= 0 || d <= 0 || k1 <= 0 || k2 <= 0 || Q <= 0 || G <= 0) return 0;
   CarveSize c;
-  c.take<char>(reidb200_jaccard_workspace_bytes(N, d, k1, k2));
+  c.take<char>(reidb200_jaccard_region_workspace_bytes(N, d, k1, k2, Q));
   c.take<int32_t>(G);   // first-hit histogram
   c.take<double>(Q);    // per-query AP
   c.take<int32_t>(Q);   // first hit
@@ -976,8 +1104,9 @@ static int rerank_eval_impl(const float* feats, int G, int Q, int64_t ldf, int d
   int rc = rerank_check(N, k1, k2, rd);
   if (rc) return rc;
   cudaStream_t st = (cudaStream_t)stream;
+  const int blend_rows = lambda_value > 0.f ? Q : 0;
   Carver c0(workspace, workspace_bytes);
-  const size_t jbytes = reidb200_jaccard_workspace_bytes(N, d, k1, k2);
+  const size_t jbytes = reidb200_jaccard_region_workspace_bytes(N, d, k1, k2, Q);
   char* jws = c0.take<char>(jbytes);
   EvalFuse ev;
   ev.ql = ql; ev.qc = qc; ev.gl = gl; ev.gc = gc;
@@ -991,23 +1120,15 @@ static int rerank_eval_impl(const float* feats, int G, int Q, int64_t ldf, int d
   RB_CUDA(cudaMemsetAsync(ev.hist, 0, (size_t)G * sizeof(int32_t), st));
   RB_CUDA(cudaMemsetAsync(ev.status, 0, 64 * sizeof(int32_t), st));
   Carver c(jws, jbytes);
-  char* packed = c.take<char>(packed_bytes(N, d));
-  float* sqn = c.take<float>(N);
-  float* isc = c.take<float>(N);
-  float* sql2 = c.take<float>((size_t)N * rd.lds);
-  float* rank_d = c.take<float>((size_t)N * k1);
-  int32_t* rank_i = c.take<int32_t>((size_t)N * k1);
-  const int ldcr = ceil_div((int)rd.lds, 32);
-  float* cred = c.take<float>((size_t)N * ldcr);
-  SparseWs w;
-  carve_sparse(c, N, k1, k2, rd, &w);
-  rc = pack_rows_launch(feats, N, ldf, d, packed, sqn, isc, st);
+  JacWs ws;
+  carve_jaccard(c, N, d, k1, k2, rd, Q, &ws);
+  const float* sql2v = nullptr;
+  rc = knn_stage(feats, N, ldf, d, k1, rd, G, blend_rows, 0, G, ws, &sql2v, st);  // only the query x gallery block is stored
   if (rc) return rc;
-  rc = gemm_split_launch(packed, sqn, isc, N, packed, sqn, isc, N, d, REIDB200_DIST_SQL2, sql2, rd.lds, st, cred, ldcr, 0, 0);
-  if (rc) return rc;
-  rc = topk_rows_launch(sql2, N, N, rd.lds, nullptr, k1, 0, 0, rank_d, rank_i, 0, st, cred, ldcr);
-  if (rc) return rc;
-  rc = jaccard_sparse_stages(rank_i, sql2, rd.lds, sqn, N, k1, k2, 0, lambda_value, G, Q, 0, G, out_dist, ldo, rd, w, st, &ev);
+  PairSrc src;
+  memset(&src, 0, sizeof(src));
+  src.feats = feats; src.ldf = ldf; src.d = d; src.rank_i = ws.rank_i; src.rank_d = ws.rank_d; src.k1c = k1;
+  rc = jaccard_sparse_stages(ws.rank_i, sql2v, rd.lds, ws.sqn, N, k1, k2, 0, lambda_value, G, Q, 0, G, out_dist, ldo, rd, ws.w, st, src, &ev);
   if (rc) return rc;
   return eval_finalize_launch(ev.hist, ev.ap_q, Q, G, out_cmc, out_ap, st);
 }

@@ -11,6 +11,7 @@
 // If the candidate list overflows (heavy ties / adversarial order) the CTA falls back to an exact
 // bisection on the 32-bit ordered key.  Ties are broken by the lower id, like a stable argsort.
 #include <stdlib.h>
+#include <string.h>
 
 #include "gemm.cuh"
 
@@ -395,6 +396,155 @@ int topk_rows_launch(const float* vals, int rows, int cols, int64_t ldv, const i
   return REIDB200_OK;
 }
 
+// ------------------------------------------------------------------------------------ selection fused into the GEMM
+// (SelArgs, gemm.cuh): the GEMM epilogue has left every row an append-only list of (key, column) entries that holds
+// every element whose key was <= the row's threshold when it was produced, and a final threshold tau that is an upper
+// bound of the row's k-th best key.  One warp per row keeps the entries <= tau (ballot compaction into shared memory),
+// rank-sorts them by (key, column) and emits the k best -- ties -> lower column, like a stable argsort.  A row whose
+// list overflowed in the epilogue, or whose candidates do not fit (thousands of exact ties), is marked and redone
+// exactly by sel_redo_kernel.
+constexpr int SL_WARPS = 4;
+
+__global__ void __launch_bounds__(SL_WARPS * 32)
+select_lists_kernel(SelArgs s, int rows, int cols, int k, int descending, int64_t index_base, float* __restrict__ out_d,
+                    void* __restrict__ out_i, int idx64) {
+  __shared__ uint32_t ckey[SL_WARPS][TW_CAP];
+  __shared__ int32_t ccol[SL_WARPS][TW_CAP];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int row = blockIdx.x * SL_WARPS + warp;
+  if (row >= rows) return;
+  const uint32_t resv = s.resv[row];
+  if (resv > (uint32_t)s.cap) return;  // overflowed in the epilogue: sel_redo_kernel
+  const uint32_t tau = s.tau[row];
+  const unsigned long long* e = s.list + (size_t)row * s.cap;
+  const int kk = min(k, cols);
+  uint32_t* mk = ckey[warp];
+  int32_t* mc = ccol[warp];
+  int count = 0;
+  for (uint32_t i0 = 0; i0 < resv; i0 += 32) {
+    const uint32_t i = i0 + lane;
+    unsigned long long v = ~0ull;
+    if (i < resv) v = __ldcg(e + i);
+    const uint32_t key = (uint32_t)(v >> 32);
+    const bool take = i < resv && key <= tau;
+    const uint32_t tb = __ballot_sync(0xffffffffu, take);
+    const int pos = count + __popc(tb & ((1u << lane) - 1));
+    if (take && pos < TW_CAP) { mk[pos] = key; mc[pos] = (int32_t)(uint32_t)v; }
+    count += __popc(tb);
+  }
+  if (count > TW_CAP) {  // (uniform) massive ties: hand the row to the exact kernel
+    if (lane == 0) s.resv[row] = (uint32_t)s.cap + 1u;
+    return;
+  }
+  __syncwarp();
+  float* od = out_d + (size_t)row * k;
+  for (int x = lane; x < count; x += 32) {
+    const uint32_t key = mk[x];
+    const int col = mc[x];
+    int rank = 0;
+    for (int o = 0; o < count; ++o) {
+      const uint32_t ok = mk[o];
+      rank += (ok < key) || (ok == key && mc[o] < col);
+    }
+    if (rank < kk) {
+      od[rank] = sel_val(key, descending);
+      const int64_t gid = (int64_t)col + index_base;
+      if (idx64) reinterpret_cast<int64_t*>(out_i)[(size_t)row * k + rank] = gid;
+      else reinterpret_cast<int32_t*>(out_i)[(size_t)row * k + rank] = (int32_t)gid;
+    }
+  }
+  for (int x = max(kk, count) + lane; x < k; x += 32) {  // fewer columns than k: pad like faiss (distance = +/-inf, id = -1)
+    od[x] = descending ? -INFINITY : INFINITY;
+    if (idx64) reinterpret_cast<int64_t*>(out_i)[(size_t)row * k + x] = -1;
+    else reinterpret_cast<int32_t*>(out_i)[(size_t)row * k + x] = -1;
+  }
+}
+
+// Exact redo of the (rare) rows marked resv > cap: a few persistent CTAs scan the marks; a marked row's whole distance row
+// is recomputed from the packed operands -- x = (hi + lo) * 2^-e, fp32 FMA dot products, the GEMM's epilogue formula -- into
+// this CTA's scratch row, and the exact CTA-per-row selection runs on it.
+template <int NT>
+__global__ void __launch_bounds__(NT)
+sel_redo_kernel(SelArgs s, int rows, int cols, int k, int kind, const __half* __restrict__ pa, const float* __restrict__ xx,
+                const float* __restrict__ isa, const __half* __restrict__ pb, const float* __restrict__ yy,
+                const float* __restrict__ isb, int dp, int64_t index_base, float* __restrict__ out_d, void* __restrict__ out_i,
+                int idx64, float* __restrict__ scratch) {
+  __shared__ int todo[NT];
+  __shared__ int ntodo;
+  extern __shared__ __align__(16) float arow[];  // dp floats: the row's scaled features (hi + lo)
+  float* my = scratch + (size_t)blockIdx.x * cols;
+  const int desc = kind == REIDB200_DIST_DOT;
+  for (int base = blockIdx.x * NT; base < rows; base += gridDim.x * NT) {
+    if (threadIdx.x == 0) ntodo = 0;
+    __syncthreads();
+    const int r = base + threadIdx.x;
+    if (r < rows && s.resv[r] > (uint32_t)s.cap) todo[atomicAdd(&ntodo, 1)] = r;
+    __syncthreads();
+    const int n = ntodo;
+    for (int t = 0; t < n; ++t) {
+      const int row = todo[t];
+      const __half* a = pa + (size_t)row * 2 * dp;
+      for (int x = threadIdx.x; x < dp; x += NT) arow[x] = __half2float(a[x]) + __half2float(a[dp + x]);
+      __syncthreads();
+      const float ia = isa[row], xr = xx ? xx[row] : 0.f;
+      for (int c = threadIdx.x; c < cols; c += NT) {
+        const __half2* b = reinterpret_cast<const __half2*>(pb + (size_t)c * 2 * dp);
+        float acc = 0.f;
+        for (int x = 0; x < dp / 2; ++x) {
+          const float2 h = __half22float2(b[x]), l = __half22float2(b[dp / 2 + x]);
+          acc = fmaf(arow[2 * x], h.x + l.x, acc);
+          acc = fmaf(arow[2 * x + 1], h.y + l.y, acc);
+        }
+        my[c] = dist_epilogue(kind, __fmul_rn(__fmul_rn(acc, ia), isb[c]), xr, yy ? yy[c] : 0.f);
+      }
+      __syncthreads();
+      topk_row_body<0, NT>(row, my, cols, 0, nullptr, k, desc, index_base, out_d, out_i, idx64);
+      __syncthreads();
+    }
+  }
+}
+
+size_t sel_workspace_bytes(int m, int n, int k) {
+  CarveSize c;
+  c.take<uint32_t>(3 * (size_t)m);
+  c.take<unsigned long long>((size_t)m * sel_cap(k));
+  c.take<float>((size_t)SEL_REDO_CTAS * n);
+  return align_up(c.off, 256);
+}
+
+int sel_prepare(void* ws, size_t ws_bytes, int m, int n, int k, int descending, SelArgs* out, float** scratch_rows, cudaStream_t st) {
+  RB_REQUIRE(sel_cap(k) > 0, "select: k=%d outside the fused selection's range", k);
+  Carver c(ws, ws_bytes);
+  uint32_t* st3 = c.take<uint32_t>(3 * (size_t)m);
+  unsigned long long* list = c.take<unsigned long long>((size_t)m * sel_cap(k));
+  float* scratch = c.take<float>((size_t)SEL_REDO_CTAS * n);
+  RB_REQUIRE(c.ok(), "select: workspace too small");
+  RB_CUDA(cudaMemsetAsync(st3, 0xff, (size_t)m * sizeof(uint32_t), st));
+  RB_CUDA(cudaMemsetAsync(st3 + m, 0, 2 * (size_t)m * sizeof(uint32_t), st));
+  memset(out, 0, sizeof(*out));
+  out->tau = st3; out->resv = st3 + m; out->comm = st3 + 2 * (size_t)m; out->list = list;
+  out->cap = sel_cap(k); out->k = k; out->window = sel_window(k); out->descending = descending;
+  *scratch_rows = scratch;
+  return REIDB200_OK;
+}
+
+int knn_select_finish(const SelArgs& sel, int m, int n, int k, int kind, const void* packedA, const float* xx, const float* isa,
+                      const void* packedB, const float* yy, const float* isb, int d, int64_t index_base, float* out_d, void* out_i,
+                      int idx64, float* scratch_rows, cudaStream_t st) {
+  const int desc = kind == REIDB200_DIST_DOT;
+  { ProfScope _ps("select_lists_kernel", st); select_lists_kernel<<<ceil_div(m, SL_WARPS), SL_WARPS * 32, 0, st>>>(sel, m, n, k, desc, index_base, out_d, out_i, idx64); }
+  RB_LAUNCH_CHECK("select_lists_kernel");
+  const int dp = padded_dim(d);
+  static DeviceOnce attr;
+  if (attr.pending()) RB_CUDA(cudaFuncSetAttribute(sel_redo_kernel<512>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
+  RB_REQUIRE((size_t)dp * 4 <= 64 * 1024, "select: feature dimension %d too large for the redo kernel", d);
+  { ProfScope _ps("sel_redo_kernel", st); sel_redo_kernel<512><<<SEL_REDO_CTAS, 512, (size_t)dp * 4, st>>>(
+      sel, m, n, k, kind, static_cast<const __half*>(packedA), xx, isa, static_cast<const __half*>(packedB), yy, isb, dp, index_base,
+      out_d, out_i, idx64, scratch_rows); }
+  RB_LAUNCH_CHECK("sel_redo_kernel");
+  return REIDB200_OK;
+}
+
 // gallery columns per GEMM + select pass: distance block of at most 2^29 floats (2 GiB)
 // (REIDB200_KNN_BLOCK_FLOATS overrides the block size: lets the tests drive the multi-pass merge at small sizes)
 static int knn_chunk_cols(int nq, int nb) {
@@ -422,7 +572,12 @@ extern "C" int reidb200_topk_rows(const float* vals, int rows, int cols, int64_t
 
 // Shared body of knn / knn_packed: operands already packed; `c` carves the distance block, the chunk reductions and the
 // per-chunk candidate tables out of what is left of the workspace.
+// the selection runs inside the GEMM epilogue (no distance block) for k <= 128; REIDB200_KNN_MATERIALISE keeps the
+// distance-block path (tests / experiments)
+static bool knn_fused(int k) { return sel_cap(k) > 0 && !getenv("REIDB200_KNN_MATERIALISE"); }
+
 static void knn_scratch_size(CarveSize& c, int nq, int nb, int k) {
+  if (knn_fused(k)) { c.take<char>(sel_workspace_bytes(nq, nb, k)); return; }
   const int chunk = knn_chunk_cols(nq, nb);
   const int nchunks = ceil_div(nb, chunk);
   c.take<float>((size_t)nq * align_up((size_t)chunk, 4));
@@ -435,6 +590,20 @@ static void knn_scratch_size(CarveSize& c, int nq, int nb, int k) {
 
 static int knn_core(const char* pq, const float* qq, const float* isq, int nq, const char* pb, const float* bb,
                     const float* isb, int nb, int d, int k, int metric, int64_t index_base, float* out_d, void* out_i, int idx64, Carver& c, cudaStream_t st) {
+  if (knn_fused(k)) {
+    // one GEMM over the whole gallery, candidates filtered against per-row thresholds in its epilogue, then the k best of
+    // every row's list: no distance block, no per-block tables, no merge pass
+    const size_t bytes = sel_workspace_bytes(nq, nb, k);
+    char* sws = c.take<char>(bytes);
+    RB_REQUIRE(c.ok(), "knn: workspace too small");
+    SelArgs sel;
+    float* redo_scratch = nullptr;
+    int rc = sel_prepare(sws, bytes, nq, nb, k, metric == REIDB200_DIST_DOT, &sel, &redo_scratch, st);
+    if (rc) return rc;
+    rc = gemm_split_select_launch(pq, qq, isq, nq, pb, bb, isb, nb, d, metric, nullptr, 0, sel, st);
+    if (rc) return rc;
+    return knn_select_finish(sel, nq, nb, k, metric, pq, qq, isq, pb, bb, isb, d, index_base, out_d, out_i, idx64, redo_scratch, st);
+  }
   const int chunk = knn_chunk_cols(nq, nb);
   const int nchunks = ceil_div(nb, chunk);
   const int dp = padded_dim(d);

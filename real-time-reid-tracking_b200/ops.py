@@ -187,7 +187,7 @@ def jaccard(feats, k1=20, k2=6, use_float16=False, lambda_value=0.0, rows=None, 
     out = torch.empty((nrows, ncols), dtype=torch.float16 if use_float16 else torch.float32, device=dev)
     rank = torch.empty((N, k1), dtype=torch.int32, device=dev) if want_rank else None
     lib = L.load()
-    ws = L.workspace(lib.reidb200_jaccard_workspace_bytes(N, d, k1, k2), dev)
+    ws = L.workspace(lib.reidb200_jaccard_region_workspace_bytes(N, d, k1, k2, nrows if lambda_value > 0 else 0), dev)
     with torch.cuda.device(dev):
         L.check(lib.reidb200_jaccard(feats.data_ptr(), N, feats.stride(0), d, k1, k2, 1 if use_float16 else 0,
                                      float(lambda_value), row0, nrows, col0, ncols, out.data_ptr(), out.stride(0),
