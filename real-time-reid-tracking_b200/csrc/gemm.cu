@@ -111,15 +111,18 @@ struct GemmArgs {
 __device__ __forceinline__ void pair_tile_coords(int tile, int tiles_m2, int symmetric, int& tm, int& tn) {
   if (!symmetric) { tm = tile % tiles_m2; tn = tile / tiles_m2; return; }
   if (symmetric == 2) {
-    // selection mode: the diagonal tiles come first (every row meets its own 256 columns before anything else, which gives
-    // its threshold a first value), then the strict upper triangle column by column
-    if (tile < tiles_m2) { tm = tn = tile; return; }
-    const int u = tile - tiles_m2;
-    int b = (int)((sqrtf(8.0f * (float)u + 1.0f) + 1.0f) * 0.5f);  // u = b (b - 1) / 2 + tm, tm < b
-    while (b * (b + 1) / 2 <= u) ++b;
-    while (b * (b - 1) / 2 > u) --b;
-    tn = b;
-    tm = u - b * (b - 1) / 2;
+    // selection mode: BAND order -- band d holds the tiles (tm, tm + d), bands d = 0 (the diagonal: every row block's
+    // bootstrap tile), 1, 2, ...  Tiles that run at the same time then belong to different row AND column blocks (a block
+    // appears in at most two tiles of a band), so no row's list is appended to by many tiles at once while its threshold
+    // is still loose (column-by-column order put up to 74 tiles of one column block in flight: their mirrored appends
+    // flooded that block's lists before any of them could tighten).
+    const float s2 = 2.0f * (float)tiles_m2 + 1.0f;
+    int d = (int)((s2 - sqrtf(fmaxf(s2 * s2 - 8.0f * (float)tile, 0.0f))) * 0.5f);
+    auto off = [&](int dd) { return dd * tiles_m2 - dd * (dd - 1) / 2; };  // tiles before band dd
+    while (d > 0 && off(d) > tile) --d;
+    while (off(d + 1) <= tile) ++d;
+    tm = tile - off(d);
+    tn = tm + d;
     return;
   }
   int b = (int)((sqrtf(8.0f * (float)tile + 1.0f) - 1.0f) * 0.5f);
@@ -162,6 +165,66 @@ __device__ __forceinline__ float epi_value(float r, float ia, float sv, float xx
   return dist_epilogue(KIND, __fmul_rn(ra, sv), xx, yy);
 }
 
+// ---- selection in the epilogue (SelArgs, gemm.cuh)
+__device__ __forceinline__ uint32_t sel_key_of(float v, int descending) {
+  const uint32_t u = float_to_ordered(v);
+  return descending ? ~u : u;
+}
+
+// One thread appends the elements of `v[0..32)` whose key passes `tau` to `row`'s list and sketch: the passing ones are
+// counted first, ONE atomicAdd reserves their slots (every lane of the warp issues its own in the same instruction, so a
+// chunk costs one L2 round trip however many lanes append), then the entries are written and folded into the sketch by
+// reductions that return nothing.  idx of element j = idx0 + j.  `valid` = bit j set when element j exists.  Returns the
+// row when the append crossed a multiple of the window (the warp then tightens it), else -1.
+__device__ __forceinline__ int sel_append32(const SelArgs& s, int row, const float (&v)[32], uint32_t valid, uint32_t tau, int idx0) {
+  uint32_t mask = 0;
+#pragma unroll
+  for (int j = 0; j < 32; ++j) mask |= (sel_key_of(v[j], s.descending) <= tau ? 1u : 0u) << j;
+  mask &= valid;
+  if (mask == 0 || (s.debug & 1)) return -1;
+  const uint32_t cnt = __popc(mask);
+  const uint32_t base = atomicAdd(s.resv + row, cnt);
+  unsigned long long* lrow = s.list + (size_t)row * s.cap;
+  unsigned long long* srow = s.sketch + (size_t)row * s.W;
+  uint32_t pos = base;
+#pragma unroll
+  for (int j = 0; j < 32; ++j) {
+    if ((mask >> j) & 1u) {
+      const unsigned long long e = ((unsigned long long)sel_key_of(v[j], s.descending) << 32) | (uint32_t)(idx0 + j);
+      if (pos < (uint32_t)s.cap) lrow[pos] = e;
+      atomicMin(srow + ((uint32_t)(idx0 + j) & (uint32_t)(s.W - 1)), e);  // W is a power of two
+      ++pos;
+    }
+  }
+  return (base / (uint32_t)s.window) != ((base + cnt) / (uint32_t)s.window) ? row : -1;
+}
+
+// One warp: tau[row] <- min(tau[row], k-th smallest occupied slot of the row's sketch) (see SelArgs).  The W <= 512 slot
+// keys are sorted in registers (S per lane, warp_bitonic_sort) and element k - 1 is read off.
+template <int S>
+__device__ __forceinline__ void sel_tighten_sorted(const SelArgs& s, int row, int lane) {
+  const unsigned long long* e = s.sketch + (size_t)row * s.W;
+  uint32_t key[S], nov[S];
+#pragma unroll
+  for (int i = 0; i < S; ++i) {
+    const int slot = lane * S + i;
+    key[i] = slot < s.W ? (uint32_t)(__ldcg(e + slot) >> 32) : 0xffffffffu;  // an empty slot reads as key 0xFFFFFFFF
+  }
+  warp_bitonic_sort<S, false>(key, nov, lane);
+  const int pos = s.k - 1;
+  uint32_t mine = 0xffffffffu;
+#pragma unroll
+  for (int i = 0; i < S; ++i) mine = (pos % S) == i ? key[i] : mine;
+  const uint32_t kth = __shfl_sync(0xffffffffu, mine, pos / S);
+  if (lane == 0 && kth != 0xffffffffu) atomicMin(s.tau + row, kth);
+}
+
+__device__ __noinline__ void sel_tighten_row(const SelArgs& s, int row, int lane) {
+  if (s.W <= 64) sel_tighten_sorted<2>(s, row, lane);
+  else if (s.W <= 128) sel_tighten_sorted<4>(s, row, lane);
+  else sel_tighten_sorted<16>(s, row, lane);
+}
+
 // Epilogue of the accumulator columns owned by one warp: TMEM lane quadrant q = warp % 4 (thread = row), and every
 // second 32-column chunk of the 256-column tile (two warps share a quadrant: chunks c0, c0 + 2, ...), so that each
 // SM sub-partition has two epilogue warps to hide each other's latencies.
@@ -174,48 +237,6 @@ __device__ __forceinline__ float epi_value(float r, float ia, float sv, float xx
 // accumulator-full barrier; the wait for the staging buffer (previous TMA store has read it) comes after the math.
 // `yw` = 64 floats of shared memory private to this warp (column norms | column scale factors of the current chunk,
 // read back as broadcast 128-bit loads).
-// ---- selection in the epilogue (SelArgs, gemm.cuh)
-__device__ __forceinline__ uint32_t sel_key_of(float v, int descending) {
-  const uint32_t u = float_to_ordered(v);
-  return descending ? ~u : u;
-}
-
-// append (key, idx) to `row`'s list; returns the row if this append completed a window (the caller tightens it), else -1
-__device__ __noinline__ int sel_append(const SelArgs& s, int row, uint32_t key, int idx) {
-  const uint32_t pos = atomicAdd(s.resv + row, 1u);
-  if (pos < (uint32_t)s.cap) {
-    s.list[(size_t)row * s.cap + pos] = ((unsigned long long)key << 32) | (uint32_t)idx;
-    __threadfence();  // the entry is visible before its commit
-  }
-  atomicAdd(s.comm + row, 1u);
-  return (pos + 1 <= (uint32_t)s.cap && (pos + 1) % (uint32_t)s.window == 0) ? row : -1;
-}
-
-// One warp: tau[row] <- min(tau[row], k-th smallest key of the row's `window` most recent entries).  Those entries are
-// elements of the row, so their k-th smallest is a valid upper bound of the row's k-th best value; and since they all
-// passed the previous threshold the bound shrinks geometrically (quantile k / window of the values below the old one)
-// until fewer than `window` further elements qualify.  Skipped when an append is in flight (commit != reserve).
-__device__ __noinline__ void sel_tighten_row(const SelArgs& s, int row, int lane) {
-  const uint32_t c = *reinterpret_cast<volatile uint32_t*>(s.comm + row);
-  const uint32_t r = *reinterpret_cast<volatile uint32_t*>(s.resv + row);
-  if (c != r || r > (uint32_t)s.cap || r < (uint32_t)s.window) return;  // warp-uniform (same addresses)
-  const unsigned long long* e = s.list + (size_t)row * s.cap + (r - s.window);
-  const int per = s.window >> 5;  // <= 16
-  uint32_t key[16];
-#pragma unroll
-  for (int i = 0; i < 16; ++i) key[i] = i < per ? (uint32_t)(__ldcg(e + i * 32 + lane) >> 32) : 0xffffffffu;
-  uint32_t lo = 0, hi = 0xffffffffu;
-  while (lo < hi) {
-    const uint32_t mid = lo + ((hi - lo) >> 1);
-    int cnt = 0;
-#pragma unroll
-    for (int i = 0; i < 16; ++i) cnt += key[i] <= mid;
-    cnt = __reduce_add_sync(0xffffffffu, cnt);
-    if (cnt >= s.k) hi = mid; else lo = mid + 1;
-  }
-  if (lane == 0) atomicMin(s.tau + row, lo);
-}
-
 template <int KIND>
 __device__ __forceinline__ void epilogue_slab(const GemmArgs& a, const CUtensorMap* tmO, uint32_t bar_full, uint32_t parity,
                                               uint32_t tmem_addr, int row0, int col_base, int c_first, int lane, float* sb,
@@ -365,12 +386,20 @@ __device__ __forceinline__ void epilogue_slab(const GemmArgs& a, const CUtensorM
 template <int KIND>
 __device__ __forceinline__ void epilogue_select(const GemmArgs& a, const CUtensorMap* tmO, uint32_t bar_full, uint32_t parity,
                                                 uint32_t tmem_addr, int row0, int col_base, int c_first, int lane, float* sb,
-                                                float* yw, bool sym_t) {
+                                                float* yw, bool sym_t, bool boot, int gate_r, int gate_c, uint32_t gate_need) {
   const SelArgs& S = a.sel;
+  if (!boot && !(S.debug & 4)) {  // the bootstrap tiles of this tile's row block (and column block, if mirrored) have set the thresholds
+    if (lane == 0) {
+      while (*reinterpret_cast<volatile uint32_t*>(S.gate + gate_r) < gate_need) __nanosleep(64);
+      if (gate_c >= 0)
+        while (*reinterpret_cast<volatile uint32_t*>(S.gate + gate_c) < gate_need) __nanosleep(64);
+      __threadfence();
+    }
+    __syncwarp();
+  }
   const int my_row = row0 + lane;
   const int rows_here = min(32, a.m - row0);
   const int nch = rows_here <= 0 ? 0 : min(BN / 32, (a.n - col_base + 31) >> 5);  // warp-uniform
-  uint32_t* tcw = reinterpret_cast<uint32_t*>(yw);  // the column thresholds take the place of the column norms after the math
   float xx_mine = 0.f, ia_mine = 0.f, yn = 0.f, sn = 0.f;
   uint32_t tau_row = 0u, tcn = 0u;
   if (c_first < nch) {
@@ -387,7 +416,10 @@ __device__ __forceinline__ void epilogue_select(const GemmArgs& a, const CUtenso
   }
   ptx::mbar_wait(bar_full, parity);
   ptx::tc_fence_after();
-  if (c_first >= nch) return;
+  if (c_first >= nch) {  // nothing to do for this warp (ragged edge); a bootstrap tile still counts it
+    if (boot && lane == 0) atomicAdd(S.gate + gate_r, 1u);
+    return;
+  }
   const bool st_rows = row0 < S.st_r1 && row0 + 32 > S.st_r0;        // direct block rows inside the stored region
   const bool st_rows_t = sym_t && row0 < S.st_c1 && row0 + 32 > S.st_c0;  // mirrored block: these rows are its COLUMNS
   int pending = -1;
@@ -404,6 +436,10 @@ __device__ __forceinline__ void epilogue_select(const GemmArgs& a, const CUtenso
     ptx::tmem_ld_wait(rn);
 #pragma unroll
     for (int j = 0; j < 32; ++j) o[j] = __uint_as_float(rn[j]);
+    // the row's threshold is re-read for every chunk (requested here, used by the next chunk): several tiles work on the
+    // same row block at the same time, and each must see what the others' appends have tightened meanwhile
+    uint32_t tau_next = tau_row;
+    if (my_row < a.m) tau_next = __ldcg(S.tau + my_row);
     if (c + 2 < nch) {
       ptx::tmem_ld_32x32b_x32(tmem_addr + (c + 2) * 32, rn);
       yn = 0.f; sn = 0.f; tcn = 0u;
@@ -441,19 +477,50 @@ __device__ __forceinline__ void epilogue_select(const GemmArgs& a, const CUtenso
       for (int j = 0; j < 32; ++j)
         if (col0 + j < a.n) red = S.descending ? fmaxf(red, o[j]) : fminf(red, o[j]);
     }
-    __syncwarp();          // every lane has read the column norms / scales
-    tcw[lane] = tc_cur;
-    __syncwarp();
     const uint32_t kred = sel_key_of(red, S.descending);
     const bool row_ok = my_row < a.m;
-    if (row_ok && (kred <= tau_row || (sym_t && kred <= tc_max))) {
-      // slow path (rare once the thresholds are tight): walk the 32 values
+    if (boot && (S.debug & 8)) {
+    } else if (boot) {
+      // bootstrap tile (threshold still +inf): every column is a candidate.  No counters: column c of the tile goes to slot
+      // c of the row's list (the warp sets resv to the tile's valid column count afterwards; nobody else appends to these
+      // rows before the gate opens) and into the sketch by a reduction that returns nothing.
+      if (row_ok) {
+        unsigned long long* lrow = S.list + (size_t)my_row * S.cap + (col0 - col_base);
+        unsigned long long* srow = S.sketch + (size_t)my_row * S.W;
 #pragma unroll
-      for (int j = 0; j < 32; ++j) {  // (fully unrolled: o[] must stay in registers)
-        const uint32_t kj = sel_key_of(o[j], S.descending);
-        const bool in = full || col0 + j < a.n;
-        if (in && kj <= tau_row) { const int p = sel_append(S, my_row, kj, col0 + j); if (p >= 0) pending = p; }
-        if (in && sym_t && kj <= tcw[j]) { const int p = sel_append(S, col0 + j, kj, my_row); if (p >= 0) pending = p; }
+        for (int j = 0; j < 32; ++j) {
+          if (full || col0 + j < a.n) {
+            const unsigned long long e = ((unsigned long long)sel_key_of(o[j], S.descending) << 32) | (uint32_t)(col0 + j);
+            lrow[j] = e;
+            atomicMin(srow + ((uint32_t)(col0 + j) % (uint32_t)S.W), e);
+          }
+        }
+      }
+    } else if (!(S.debug & 16)) {
+      const uint32_t valid = full ? 0xffffffffu : ((1u << (a.n - col0)) - 1u);
+      // direct: this thread's row against its own threshold (entered by the lanes whose row minimum passes)
+      if (row_ok && kred <= tau_row) {
+        const int p = sel_append32(S, my_row, o, valid, tau_row, col0);
+        if (p >= 0) pending = p;
+      }
+      // mirror (symmetric product): the chunk is transposed through the staging box so that lane j holds column j, i.e. the
+      // 32 elements (row0 .. row0 + 31) of the mirrored row col0 + j, and the same code runs against that row's threshold
+      if (sym_t && __any_sync(0xffffffffu, row_ok && kred <= tc_max)) {
+        if (lane == 0) ptx::bulk_wait_read<0>();
+        __syncwarp();
+#pragma unroll
+        for (int j = 0; j < 32; j += 4)
+          *reinterpret_cast<float4*>(sb + lane * 32 + (((j >> 2) ^ (lane & 7)) << 2)) = make_float4(o[j], o[j + 1], o[j + 2], o[j + 3]);
+        __syncwarp();
+        float t[32];
+#pragma unroll
+        for (int rr = 0; rr < 32; ++rr) t[rr] = sb[rr * 32 + ((((lane >> 2) ^ (rr & 7)) << 2) | (lane & 3))];
+        __syncwarp();
+        const uint32_t rvalid = rows_here >= 32 ? 0xffffffffu : ((1u << rows_here) - 1u);
+        if (col0 + lane < a.n) {
+          const int p = sel_append32(S, col0 + lane, t, rvalid, tc_cur, row0);
+          if (p >= 0) pending = p;
+        }
       }
     }
     // ---- the part of the output that is still stored
@@ -478,18 +545,30 @@ __device__ __forceinline__ void epilogue_select(const GemmArgs& a, const CUtenso
       for (int j = 0; j < 32; ++j)
         if (col0 + j < a.n) mp[(size_t)j * a.ldo] = o[j];
     }
+    tau_row = tau_next;
     __syncwarp();  // the threshold / norm staging of this chunk has been read by every lane
+    // ---- tighten the rows whose list completed a window during this chunk (the warp works on one row at a time); done
+    // per chunk so that tiles working on the same rows at the same time see each other's progress early
+    uint32_t pend = __ballot_sync(0xffffffffu, pending >= 0 && !(S.debug & 2));
+    while (pend) {
+      const int src = __ffs(pend) - 1;
+      pend &= pend - 1;
+      sel_tighten_row(S, __shfl_sync(0xffffffffu, pending, src), lane);
+    }
+    pending = -1;
   }
-  // ---- tighten the rows whose list completed a window during this slab (the warp works on one row at a time)
-  uint32_t pend = __ballot_sync(0xffffffffu, pending >= 0);
-  while (pend) {
-    const int src = __ffs(pend) - 1;
-    pend &= pend - 1;
-    sel_tighten_row(S, __shfl_sync(0xffffffffu, pending, src), lane);
+  if (boot) {
+    // bootstrap tile: every row of this warp leaves with its list length set and a threshold taken from its sketch (its
+    // own 128 columns here at least, the sibling warp adds the other 128), then the warp opens the gate
+    if (my_row < a.m) S.resv[my_row] = (uint32_t)min(BN, a.n - col_base);
+    for (int r = 0; r < rows_here && !(S.debug & 2); ++r) sel_tighten_row(S, row0 + r, lane);
+    __threadfence();
+    __syncwarp();
+    if (lane == 0) atomicAdd(S.gate + gate_r, 1u);
   }
 }
 
-template <int KIND>
+template <int KIND, bool SELECT>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
 gemm_split_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                      const __grid_constant__ CUtensorMap tmO, GemmArgs a) {
@@ -594,9 +673,10 @@ gemm_split_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
     uint32_t aphase = 0;
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
       const int tm = tile % a.tiles_m, tn = tile / a.tiles_m;
-      if (a.sel.tau)
+      if (SELECT)
         epilogue_select<KIND>(a, &tmO, bar_tfull + 8 * as, aphase, tmem_base + ((uint32_t)(q * 32) << 16) + as * BN,
-                              tm * BM + q * 32, tn * BN, c_first, lane, sbuf, yw_buf + (warp - 2) * 64, false);
+                              tm * BM + q * 32, tn * BN, c_first, lane, sbuf, yw_buf + (warp - 2) * 64, false, tn == 0, tm, -1,
+                              (uint32_t)EPI_WARPS);
       else
         epilogue_slab<KIND>(a, &tmO, bar_tfull + 8 * as, aphase, tmem_base + ((uint32_t)(q * 32) << 16) + as * BN,
                             tm * BM + q * 32, tn * BN, c_first, lane, sbuf, yw_buf + (warp - 2) * 64, vec_ok);
@@ -627,7 +707,7 @@ constexpr int STAGE2_BYTES = 4 * A_BYTES;  // Ahi, Alo, Bhi(half), Blo(half): 64
 constexpr size_t GEMM2_SMEM = (size_t)STAGES2 * STAGE2_BYTES + EPI_WARPS * EPI_STAGE_FLOATS * 4 + EPI_YW_FLOATS * 4 + 128;
 static_assert(GEMM_SMEM <= 232448 && GEMM2_SMEM <= 232448, "shared memory budget (227 KB per CTA)");
 
-template <int KIND>
+template <int KIND, bool SELECT>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GEMM_THREADS, 1)
 gemm_split_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                       const __grid_constant__ CUtensorMap tmO, GemmArgs a) {
@@ -740,10 +820,11 @@ gemm_split_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
     for (int tile = cluster_id; tile < total_tiles; tile += num_clusters) {
       int tm, tn;
       pair_tile_coords(tile, tiles_m2, a.symmetric, tm, tn);
-      if (a.sel.tau)
+      if (SELECT)
         epilogue_select<KIND>(a, &tmO, bar_tfull + 8 * as, aphase, tmem_base + ((uint32_t)(q * 32) << 16) + as * BN,
                               tm * 2 * BM + (int)rank * BM + q * 32, tn * BN, c_first, lane, sbuf, yw_buf + (warp - 2) * 64,
-                              a.symmetric && tn != tm);
+                              a.symmetric && tn != tm, a.symmetric ? tn == tm : tn == 0, tm, (a.symmetric && tn != tm) ? tn : -1,
+                              2u * EPI_WARPS);
       else
         epilogue_slab<KIND>(a, &tmO, bar_tfull + 8 * as, aphase, tmem_base + ((uint32_t)(q * 32) << 16) + as * BN,
                             tm * 2 * BM + (int)rank * BM + q * 32, tn * BN, c_first, lane, sbuf, yw_buf + (warp - 2) * 64,
@@ -862,8 +943,8 @@ int gemm_split_launch(const void* packedA, const float* xx, const float* isa, in
 
 int gemm_split_select_launch(const void* packedA, const float* xx, const float* isa, int m, const void* packedB, const float* yy,
                              const float* isb, int n, int d, int kind, float* out, int64_t ldo, const SelArgs& sel, cudaStream_t st) {
-  RB_REQUIRE(sel.tau && sel.resv && sel.comm && sel.list && sel.cap > 0 && sel.k > 0 && sel.window >= sel.k && sel.window <= 512 &&
-             (sel.window & 31) == 0, "distmat(select): bad selection state");
+  RB_REQUIRE(sel.tau && sel.resv && sel.list && sel.sketch && sel.gate && sel.cap > 0 && sel.k > 0 && sel.W >= sel.k && sel.W <= 512 &&
+             (sel.W & 31) == 0 && sel.window > 0, "distmat(select): bad selection state");
   return gemm_launch_impl(packedA, xx, isa, m, packedB, yy, isb, n, d, kind, out, ldo, st, nullptr, 0, 0, 0, &sel);
 }
 
@@ -913,14 +994,21 @@ static int gemm_launch_impl(const void* packedA, const float* xx, const float* i
   if (a.symmetric && sel) a.symmetric = 2;  // selection: diagonal tiles first (pair_tile_coords)
   void (*k1)(CUtensorMap, CUtensorMap, CUtensorMap, GemmArgs) = nullptr;
   void (*k2)(CUtensorMap, CUtensorMap, CUtensorMap, GemmArgs) = nullptr;
-  switch (kind) {
-    case REIDB200_DIST_EUCLID: k1 = gemm_split_tc_kernel<REIDB200_DIST_EUCLID>; k2 = gemm_split_tc2_kernel<REIDB200_DIST_EUCLID>; break;
-    case REIDB200_DIST_COSINE_HALF: k1 = gemm_split_tc_kernel<REIDB200_DIST_COSINE_HALF>; k2 = gemm_split_tc2_kernel<REIDB200_DIST_COSINE_HALF>; break;
-    case REIDB200_DIST_DOT: k1 = gemm_split_tc_kernel<REIDB200_DIST_DOT>; k2 = gemm_split_tc2_kernel<REIDB200_DIST_DOT>; break;
-    default: k1 = gemm_split_tc_kernel<REIDB200_DIST_SQL2>; k2 = gemm_split_tc2_kernel<REIDB200_DIST_SQL2>; break;
+  if (sel) {  // selection in the epilogue: SQL2 (ascending) and DOT (descending) only, separate instantiations so that the
+              // storing kernels keep their register allocation
+    RB_REQUIRE(kind == REIDB200_DIST_SQL2 || kind == REIDB200_DIST_DOT, "distmat(select): metric must be SQL2 or DOT");
+    if (kind == REIDB200_DIST_DOT) { k1 = gemm_split_tc_kernel<REIDB200_DIST_DOT, true>; k2 = gemm_split_tc2_kernel<REIDB200_DIST_DOT, true>; }
+    else { k1 = gemm_split_tc_kernel<REIDB200_DIST_SQL2, true>; k2 = gemm_split_tc2_kernel<REIDB200_DIST_SQL2, true>; }
+  } else {
+    switch (kind) {
+      case REIDB200_DIST_EUCLID: k1 = gemm_split_tc_kernel<REIDB200_DIST_EUCLID, false>; k2 = gemm_split_tc2_kernel<REIDB200_DIST_EUCLID, false>; break;
+      case REIDB200_DIST_COSINE_HALF: k1 = gemm_split_tc_kernel<REIDB200_DIST_COSINE_HALF, false>; k2 = gemm_split_tc2_kernel<REIDB200_DIST_COSINE_HALF, false>; break;
+      case REIDB200_DIST_DOT: k1 = gemm_split_tc_kernel<REIDB200_DIST_DOT, false>; k2 = gemm_split_tc2_kernel<REIDB200_DIST_DOT, false>; break;
+      default: k1 = gemm_split_tc_kernel<REIDB200_DIST_SQL2, false>; k2 = gemm_split_tc2_kernel<REIDB200_DIST_SQL2, false>; break;
+    }
   }
-  static DeviceOnce attr_done[2][4];
-  if (attr_done[pair ? 1 : 0][kind].pending()) {
+  static DeviceOnce attr_done[2][2][4];
+  if (attr_done[sel ? 1 : 0][pair ? 1 : 0][kind].pending()) {
     RB_CUDA(cudaFuncSetAttribute(pair ? (const void*)k2 : (const void*)k1, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  (int)(pair ? GEMM2_SMEM : GEMM_SMEM)));
   }

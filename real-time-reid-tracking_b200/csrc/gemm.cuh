@@ -43,35 +43,52 @@ __device__ __forceinline__ float dist_epilogue(int kind, float acc, float xx, fl
 
 #endif
 
-// ---- selection fused into the GEMM epilogue (no distance block): per output row an append-only candidate list and a
-// threshold that only tightens.  Invariant: tau[row] is the ordered key of an upper bound of the row's k-th best value
-// (there are at least k elements of the row whose key is <= tau), so every element of the true top-k passes the filter
-// `key <= tau` whenever it is produced, and the exact top-k is the k best entries of the list (topk.cu select_lists).
-//   tau   u32[m]  init 0xFFFFFFFF        resv / comm  u32[m]  entries reserved / committed (a list is readable when equal)
-//   list  u64[m, cap]  (key << 32) | column;  a row whose resv exceeds cap is redone exactly (knn_select_finish)
+// ---- selection fused into the GEMM epilogue (no distance block): per output row an append-only candidate list, a small
+// SKETCH and a threshold that only tightens.
+//   tau    u32[m]      ordered key of an upper bound of the row's k-th best value (init 0xFFFFFFFF).  Invariant: at least k
+//                      elements of the row have key <= tau, so every element of the true top-k passes `key <= tau` whenever
+//                      it is produced, and the exact top-k is the k best entries of the list (topk.cu select_lists_kernel).
+//   list   u64[m, cap] (key << 32) | column, reserved through resv u32[m]; a row whose resv exceeds cap is redone exactly.
+//   sketch u64[m, W]   slot (column mod W) holds the smallest (key << 32 | column) appended for that residue class
+//                      (atomicMin, init all ones).  Occupied slots are DISTINCT elements of the row, so the k-th smallest
+//                      slot is a valid threshold; with W ~ 3k it sits near the rank -W ln(1 - k / W) ~ 1.2 k element of
+//                      everything produced so far, however much that is -- no ordering or commit protocol between the
+//                      appending warps is needed (an earlier version read back the list and had to skip whenever an append
+//                      was in flight: under the first wave's contention the thresholds never left +inf).
+// Bootstrap: a threshold starts at +inf, so the first tile a row meets appends all of its columns.  To keep that flood to
+// ONE tile per row, the first tile of every row block in the kernel's tile order (the diagonal tile of a symmetric
+// product, column tile 0 otherwise) is its bootstrap tile: epilogue warps of every other tile wait (gate[]) until the
+// bootstrap tiles of their row block -- and, for a mirrored tile, of their column block -- have finished and tightened.
+// Bootstrap tiles never wait and come first in every CTA's work list, so the wait cannot deadlock in the persistent grid.
 // Symmetric products (A == B) use the same arrays for the mirrored element (row = column index, entry = row index).
 struct SelArgs {
   uint32_t* tau;
   uint32_t* resv;
-  uint32_t* comm;
   unsigned long long* list;
-  int cap, k, window, descending;
-  int st_r0, st_r1, st_c0, st_c1;  // block of the output that is still STORED (rows [r0, r1) x columns [c0, c1)); empty = none
+  unsigned long long* sketch;
+  uint32_t* gate;                     // u32[row blocks], zero-init: epilogue warps that finished the row block's BOOTSTRAP tile
+  int cap, k, W, window, descending;  // W: sketch slots (multiple of 32, >= k); window: appends between two tightenings
+  int debug;                          // timing experiments only (REIDB200_SEL_DEBUG): 1 no appends, 2 no tightening, 4 no gates, 8 no boot work, 16 no slow path
+  int st_r0, st_r1, st_c0, st_c1;     // block of the output that is still STORED (rows [r0, r1) x columns [c0, c1)); empty = none
 };
 
 int gemm_split_select_launch(const void* packedA, const float* xx, const float* isa, int m, const void* packedB, const float* yy,
                              const float* isb, int n, int d, int kind, float* out, int64_t ldo, const SelArgs& sel, cudaStream_t st);
 
 // candidate-list capacity / tightening window the selection uses for a given k (0: k not supported, use the materialising path)
-inline int sel_window(int k) { return k <= 25 ? 64 : (k <= 128 ? ((5 * k / 2 + 31) / 32) * 32 : 0); }
+inline int sel_sketch(int k) { return k <= 21 ? 64 : (k <= 42 ? 128 : (k <= 100 ? 256 : (k <= 128 ? 512 : 0))); }  // slots W >= 2.5 k, a power of two <= 512
 inline int sel_cap(int k) { return k <= 25 ? 1024 : (k <= 128 ? 4096 : 0); }
 size_t sel_workspace_bytes(int m, int n, int k);
 // carve + initialise (stream-ordered) the selection state of m rows inside `ws`
 int sel_prepare(void* ws, size_t ws_bytes, int m, int n, int k, int descending, SelArgs* out, float** scratch_rows, cudaStream_t st);
 // the k best entries of every row's list -> out_d f32[m, k], out_i (i64 | i32)[m, k]; rows whose list overflowed (massive
-// ties) are redone exactly by a small persistent kernel from the packed operands (scratch: SEL_REDO_CTAS * n floats,
+// ties) are redone exactly by a small persistent kernel from the packed operands (scratch: sel_redo_ctas(n) * n floats,
 // carved by sel_prepare); kind SQL2 or DOT
-constexpr int SEL_REDO_CTAS = 8;
+// CTAs of the redo kernel: each owns a scratch row of n floats; about 256 MB of scratch in total, 8..296 CTAs
+inline int sel_redo_ctas(int n) {
+  long long c = (256ll << 20) / ((long long)(n > 0 ? n : 1) * 4);
+  return (int)(c < 8 ? 8 : (c > 296 ? 296 : c));
+}
 int knn_select_finish(const SelArgs& sel, int m, int n, int k, int kind, const void* packedA, const float* xx, const float* isa,
                       const void* packedB, const float* yy, const float* isb, int d, int64_t index_base, float* out_d, void* out_i,
                       int idx64, float* scratch_rows, cudaStream_t st);

@@ -10,6 +10,8 @@
 //   D7  Jaccard: min-sum over shared columns, 1 - t/(2-t)     jaccard_rows_kernel (CTA / output row,
 //       dense accumulator staged in shared memory, coalesced dense row written once)
 //   D8  optional lambda blend with the Euclidean distance (north_star; not in the reference)
+#include <stdlib.h>
+
 #include "evalmap.cuh"
 #include "gemm.cuh"
 
@@ -941,11 +943,27 @@ using namespace reidb200;
 // 0 when lambda == 0) are stored, in a block of whole 32-row groups.
 struct JacWs {
   char* packed; float* sqn; float* isc;
-  float* blk;            // [blk_rows, lds] rows of the squared-L2 matrix kept for the blend (or null)
+  float* blk;            // selection mode: [blk_rows, lds] rows of the squared-L2 matrix kept for the blend (or null)
+  float* mat; float* cred;  // matrix mode: the whole [N, lds] squared-L2 matrix + its per-(row, 32-column chunk) minima
   float* rank_d; int32_t* rank_i;
   char* selws; size_t selbytes;
   SparseWs w;
 };
+
+// Two ways to get the initial ranking (D2):
+//   matrix mode     the N x N squared-L2 matrix is written by the GEMM (with per-chunk minima) and the chunk-guided row
+//                   select reads ~k chunks per row.  Fastest up to a few 10^4 rows: at N = 19281 the GEMM with its stores
+//                   takes 0.47 ms + 0.095 ms of selection.
+//   selection mode  the k-NN is selected INSIDE the GEMM epilogue (gemm.cuh SelArgs): nothing but the rows the lambda blend
+//                   reads is stored.  Measured at N = 19281: 0.40 ms of GEMM + 0.2 ms for the bootstrap wave (every row's
+//                   first tile fills its list and sketch while the other CTAs wait at the gates) + the appends of ~0.45 %
+//                   of all elements through L2 atomics -- slower than matrix mode there, but the only way once N x N
+//                   floats stop fitting (N = 150 k: 90 GB) and cheaper per element as N grows (the acceptance rate falls
+//                   like k ln N / N).  Chosen from N; REIDB200_RERANK_SELECT=0/1 forces it (tests run both).
+static bool rerank_select_mode(int N) {
+  if (const char* e = getenv("REIDB200_RERANK_SELECT")) return atoi(e) != 0;
+  return N > 32768;
+}
 
 static int blend_block_rows(int blend_rows, int N) {  // rows of whole 32-row groups that cover any `blend_rows` consecutive rows
   if (blend_rows <= 0) return 0;
@@ -959,12 +977,19 @@ static void carve_jaccard(C& c, int N, int d, int k1, int k2, const RerankDims& 
   t.packed = c.template take<char>(packed_bytes(N, d));
   t.sqn = c.template take<float>(N);
   t.isc = c.template take<float>(N);
-  const int br = blend_block_rows(blend_rows, N);
-  t.blk = br ? c.template take<float>((size_t)br * rd.lds) : nullptr;
+  t.blk = t.mat = t.cred = nullptr;
+  t.selws = nullptr; t.selbytes = 0;
+  if (rerank_select_mode(N)) {
+    const int br = blend_block_rows(blend_rows, N);
+    t.blk = br ? c.template take<float>((size_t)br * rd.lds) : nullptr;
+    t.selbytes = sel_workspace_bytes(N, N, k1);
+    t.selws = c.template take<char>(t.selbytes);
+  } else {
+    t.mat = c.template take<float>((size_t)N * rd.lds);
+    t.cred = c.template take<float>((size_t)N * ceil_div((int)rd.lds, 32));
+  }
   t.rank_d = c.template take<float>((size_t)N * k1);
   t.rank_i = c.template take<int32_t>((size_t)N * k1);
-  t.selbytes = sel_workspace_bytes(N, N, k1);
-  t.selws = c.template take<char>(t.selbytes);
   carve_sparse(c, N, k1, k2, rd, &t.w);
   if (out) *out = t;
 }
@@ -1016,9 +1041,17 @@ extern "C" int reidb200_jaccard_from_rank(const int32_t* rank, const float* sql2
 // [blend_row0, blend_row0 + blend_rows) x all columns of the squared-L2 matrix are still stored for the lambda blend, into
 // ws.blk), k best entries of every list.  Returns the VIRTUAL base of the stored rows (row i at base + i * lds) or null.
 static int knn_stage(const float* feats, int N, int64_t ldf, int d, int k1, const RerankDims& rd, int blend_row0, int blend_rows,
-                     int blend_col0, int blend_cols, const JacWs& ws, const float** sql2_virtual, cudaStream_t st) {
+                     int blend_col0, int blend_cols, const JacWs& ws, const float** sql2_virtual, bool* have_matrix, cudaStream_t st) {
   int rc = pack_rows_launch(feats, N, ldf, d, ws.packed, ws.sqn, ws.isc, st);
   if (rc) return rc;
+  if (ws.mat) {  // matrix mode
+    const int ldcr = ceil_div((int)rd.lds, 32);
+    rc = gemm_split_launch(ws.packed, ws.sqn, ws.isc, N, ws.packed, ws.sqn, ws.isc, N, d, REIDB200_DIST_SQL2, ws.mat, rd.lds, st, ws.cred, ldcr, 0, 0);
+    if (rc) return rc;
+    *sql2_virtual = ws.mat;
+    *have_matrix = true;
+    return topk_rows_launch(ws.mat, N, N, rd.lds, nullptr, k1, 0, 0, ws.rank_d, ws.rank_i, 0, st, ws.cred, ldcr);
+  }
   SelArgs sel;
   float* redo_scratch = nullptr;
   rc = sel_prepare(ws.selws, ws.selbytes, N, N, k1, 0, &sel, &redo_scratch, st);
@@ -1033,6 +1066,7 @@ static int knn_stage(const float* feats, int N, int64_t ldf, int d, int k1, cons
   rc = gemm_split_select_launch(ws.packed, ws.sqn, ws.isc, N, ws.packed, ws.sqn, ws.isc, N, d, REIDB200_DIST_SQL2, vbase, rd.lds, sel, st);
   if (rc) return rc;
   *sql2_virtual = vbase;
+  *have_matrix = false;
   return knn_select_finish(sel, N, N, k1, REIDB200_DIST_SQL2, ws.packed, ws.sqn, ws.isc, ws.packed, ws.sqn, ws.isc, d, 0, ws.rank_d,
                            ws.rank_i, 0, redo_scratch, st);
 }
@@ -1054,13 +1088,15 @@ extern "C" int reidb200_jaccard(const float* feats, int N, int64_t ldf, int d, i
   JacWs ws;
   carve_jaccard(c, N, d, k1, k2, rd, blend_rows, &ws);
   const float* sql2v = nullptr;
-  rc = knn_stage(feats, N, ldf, d, k1, rd, row0, blend_rows, col0, ncols, ws, &sql2v, st);
+  bool have_matrix = false;
+  rc = knn_stage(feats, N, ldf, d, k1, rd, row0, blend_rows, col0, ncols, ws, &sql2v, &have_matrix, st);
   if (rc) return rc;
   if (rank_out) RB_CUDA(cudaMemcpyAsync(rank_out, ws.rank_i, (size_t)N * k1 * sizeof(int32_t), cudaMemcpyDeviceToDevice, st));
   if (nrows == 0 || ncols == 0) return REIDB200_OK;
   PairSrc src;
   memset(&src, 0, sizeof(src));
-  src.feats = feats; src.ldf = ldf; src.d = d; src.rank_i = ws.rank_i; src.rank_d = ws.rank_d; src.k1c = k1;
+  if (have_matrix) { src.sql2 = sql2v; src.lds = rd.lds; }
+  else { src.feats = feats; src.ldf = ldf; src.d = d; src.rank_i = ws.rank_i; src.rank_d = ws.rank_d; src.k1c = k1; }
   return jaccard_sparse_stages(ws.rank_i, sql2v, rd.lds, ws.sqn, N, k1, k2, use_float16, lambda_value, row0, nrows, col0, ncols,
                                out, ldo, rd, ws.w, st, src);
 }
@@ -1123,11 +1159,13 @@ static int rerank_eval_impl(const float* feats, int G, int Q, int64_t ldf, int d
   JacWs ws;
   carve_jaccard(c, N, d, k1, k2, rd, Q, &ws);
   const float* sql2v = nullptr;
-  rc = knn_stage(feats, N, ldf, d, k1, rd, G, blend_rows, 0, G, ws, &sql2v, st);  // only the query x gallery block is stored
+  bool have_matrix = false;
+  rc = knn_stage(feats, N, ldf, d, k1, rd, G, blend_rows, 0, G, ws, &sql2v, &have_matrix, st);  // selection mode stores the query x gallery block only
   if (rc) return rc;
   PairSrc src;
   memset(&src, 0, sizeof(src));
-  src.feats = feats; src.ldf = ldf; src.d = d; src.rank_i = ws.rank_i; src.rank_d = ws.rank_d; src.k1c = k1;
+  if (have_matrix) { src.sql2 = sql2v; src.lds = rd.lds; }
+  else { src.feats = feats; src.ldf = ldf; src.d = d; src.rank_i = ws.rank_i; src.rank_d = ws.rank_d; src.k1c = k1; }
   rc = jaccard_sparse_stages(ws.rank_i, sql2v, rd.lds, ws.sqn, N, k1, k2, 0, lambda_value, G, Q, 0, G, out_dist, ldo, rd, ws.w, st, src, &ev);
   if (rc) return rc;
   return eval_finalize_launch(ev.hist, ev.ap_q, Q, G, out_cmc, out_ap, st);

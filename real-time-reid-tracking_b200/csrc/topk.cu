@@ -432,9 +432,33 @@ select_lists_kernel(SelArgs s, int rows, int cols, int k, int descending, int64_
     if (take && pos < TW_CAP) { mk[pos] = key; mc[pos] = (int32_t)(uint32_t)v; }
     count += __popc(tb);
   }
-  if (count > TW_CAP) {  // (uniform) massive ties: hand the row to the exact kernel
-    if (lane == 0) s.resv[row] = (uint32_t)s.cap + 1u;
-    return;
+  if (count > TW_CAP) {
+    // the threshold is looser than the buffer: find the exact kk-th smallest key of the list by bisection (re-reading the
+    // list, which sits in L1 / L2) and collect again; only thousands of EXACT ties are left to the exact kernel
+    uint32_t lo = 0, hi = tau;
+    while (lo < hi) {
+      const uint32_t mid = lo + ((hi - lo) >> 1);
+      int cnt = 0;
+      for (uint32_t i = lane; i < resv; i += 32) cnt += (uint32_t)(__ldcg(e + i) >> 32) <= mid;
+      cnt = __reduce_add_sync(0xffffffffu, cnt);
+      if (cnt >= kk) hi = mid; else lo = mid + 1;
+    }
+    count = 0;
+    for (uint32_t i0 = 0; i0 < resv; i0 += 32) {
+      const uint32_t i = i0 + lane;
+      unsigned long long v = ~0ull;
+      if (i < resv) v = __ldcg(e + i);
+      const uint32_t key = (uint32_t)(v >> 32);
+      const bool take = i < resv && key <= lo;
+      const uint32_t tb = __ballot_sync(0xffffffffu, take);
+      const int pos = count + __popc(tb & ((1u << lane) - 1));
+      if (take && pos < TW_CAP) { mk[pos] = key; mc[pos] = (int32_t)(uint32_t)v; }
+      count += __popc(tb);
+    }
+    if (count > TW_CAP) {  // (uniform) massive ties: hand the row to the exact kernel
+      if (lane == 0) s.resv[row] = (uint32_t)s.cap + 1u;
+      return;
+    }
   }
   __syncwarp();
   float* od = out_d + (size_t)row * k;
@@ -506,24 +530,29 @@ sel_redo_kernel(SelArgs s, int rows, int cols, int k, int kind, const __half* __
 
 size_t sel_workspace_bytes(int m, int n, int k) {
   CarveSize c;
-  c.take<uint32_t>(3 * (size_t)m);
+  c.take<uint32_t>(2 * (size_t)m + (size_t)m / 128 + 2);
+  c.take<unsigned long long>((size_t)m * sel_sketch(k));
   c.take<unsigned long long>((size_t)m * sel_cap(k));
-  c.take<float>((size_t)SEL_REDO_CTAS * n);
+  c.take<float>((size_t)sel_redo_ctas(n) * n);
   return align_up(c.off, 256);
 }
 
 int sel_prepare(void* ws, size_t ws_bytes, int m, int n, int k, int descending, SelArgs* out, float** scratch_rows, cudaStream_t st) {
   RB_REQUIRE(sel_cap(k) > 0, "select: k=%d outside the fused selection's range", k);
   Carver c(ws, ws_bytes);
-  uint32_t* st3 = c.take<uint32_t>(3 * (size_t)m);
+  const size_t n_gate = (size_t)m / 128 + 2;
+  uint32_t* st2 = c.take<uint32_t>(2 * (size_t)m + n_gate);
+  unsigned long long* sketch = c.take<unsigned long long>((size_t)m * sel_sketch(k));
   unsigned long long* list = c.take<unsigned long long>((size_t)m * sel_cap(k));
-  float* scratch = c.take<float>((size_t)SEL_REDO_CTAS * n);
+  float* scratch = c.take<float>((size_t)sel_redo_ctas(n) * n);
   RB_REQUIRE(c.ok(), "select: workspace too small");
-  RB_CUDA(cudaMemsetAsync(st3, 0xff, (size_t)m * sizeof(uint32_t), st));
-  RB_CUDA(cudaMemsetAsync(st3 + m, 0, 2 * (size_t)m * sizeof(uint32_t), st));
+  RB_CUDA(cudaMemsetAsync(st2, 0xff, (size_t)m * sizeof(uint32_t), st));                       // tau = +inf
+  RB_CUDA(cudaMemsetAsync(st2 + m, 0, ((size_t)m + n_gate) * sizeof(uint32_t), st));           // resv = 0, gates closed
+  RB_CUDA(cudaMemsetAsync(sketch, 0xff, (size_t)m * sel_sketch(k) * sizeof(unsigned long long), st));  // empty slots
   memset(out, 0, sizeof(*out));
-  out->tau = st3; out->resv = st3 + m; out->comm = st3 + 2 * (size_t)m; out->list = list;
-  out->cap = sel_cap(k); out->k = k; out->window = sel_window(k); out->descending = descending;
+  out->tau = st2; out->resv = st2 + m; out->gate = st2 + 2 * (size_t)m; out->list = list; out->sketch = sketch;
+  out->cap = sel_cap(k); out->k = k; out->W = sel_sketch(k); out->window = 32; out->descending = descending;
+  out->debug = getenv("REIDB200_SEL_DEBUG") ? atoi(getenv("REIDB200_SEL_DEBUG")) : 0;
   *scratch_rows = scratch;
   return REIDB200_OK;
 }
@@ -532,13 +561,23 @@ int knn_select_finish(const SelArgs& sel, int m, int n, int k, int kind, const v
                       const void* packedB, const float* yy, const float* isb, int d, int64_t index_base, float* out_d, void* out_i,
                       int idx64, float* scratch_rows, cudaStream_t st) {
   const int desc = kind == REIDB200_DIST_DOT;
+  if (getenv("REIDB200_SEL_STATS")) {  // diagnostics only (synchronises): how long the candidate lists grew
+    cudaStreamSynchronize(st);
+    uint32_t* h = (uint32_t*)malloc((size_t)m * 4);
+    cudaMemcpy(h, sel.resv, (size_t)m * 4, cudaMemcpyDeviceToHost);
+    unsigned long long sum = 0; uint32_t mx = 0; int over = 0, big = 0;
+    for (int i = 0; i < m; ++i) { sum += h[i]; mx = h[i] > mx ? h[i] : mx; over += h[i] > (uint32_t)sel.cap; big += h[i] > 512; }
+    fprintf(stderr, "[sel] m=%d n=%d k=%d cap=%d: list length mean %.1f max %u, > 512: %d, overflow: %d\n", m, n, k, sel.cap,
+            (double)sum / m, mx, big, over);
+    free(h);
+  }
   { ProfScope _ps("select_lists_kernel", st); select_lists_kernel<<<ceil_div(m, SL_WARPS), SL_WARPS * 32, 0, st>>>(sel, m, n, k, desc, index_base, out_d, out_i, idx64); }
   RB_LAUNCH_CHECK("select_lists_kernel");
   const int dp = padded_dim(d);
   static DeviceOnce attr;
   if (attr.pending()) RB_CUDA(cudaFuncSetAttribute(sel_redo_kernel<512>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
   RB_REQUIRE((size_t)dp * 4 <= 64 * 1024, "select: feature dimension %d too large for the redo kernel", d);
-  { ProfScope _ps("sel_redo_kernel", st); sel_redo_kernel<512><<<SEL_REDO_CTAS, 512, (size_t)dp * 4, st>>>(
+  { ProfScope _ps("sel_redo_kernel", st); sel_redo_kernel<512><<<sel_redo_ctas(n), 512, (size_t)dp * 4, st>>>(
       sel, m, n, k, kind, static_cast<const __half*>(packedA), xx, isa, static_cast<const __half*>(packedB), yy, isb, dp, index_base,
       out_d, out_i, idx64, scratch_rows); }
   RB_LAUNCH_CHECK("sel_redo_kernel");
@@ -574,10 +613,20 @@ extern "C" int reidb200_topk_rows(const float* vals, int rows, int cols, int64_t
 // per-chunk candidate tables out of what is left of the workspace.
 // the selection runs inside the GEMM epilogue (no distance block) for k <= 128; REIDB200_KNN_MATERIALISE keeps the
 // distance-block path (tests / experiments)
-static bool knn_fused(int k) { return sel_cap(k) > 0 && !getenv("REIDB200_KNN_MATERIALISE"); }
+// Measured (profiles/r02_selection_experiments.md): with the slow path switched off the selecting GEMM is as fast as the
+// storing one (97 vs 94 ms per 10 k x 1 M x 2048 search) and the 9 ms row-select disappears, but every accepted element
+// (~1450 per row at k = 100) costs ~3 us of a lone epilogue lane's time -- 141 ms in all -- so the distance-block path
+// stays the default for k-NN; the selection is what the re-ranking step uses when N x N floats do not fit
+// (rerank.cu rerank_select_mode).  REIDB200_KNN_SELECT=1 selects it here (tests run both).
+static bool knn_fused(int k, int nb) {
+  if (sel_cap(k) == 0) return false;
+  if (const char* e = getenv("REIDB200_KNN_SELECT")) return atoi(e) != 0;
+  (void)nb;
+  return false;
+}
 
 static void knn_scratch_size(CarveSize& c, int nq, int nb, int k) {
-  if (knn_fused(k)) { c.take<char>(sel_workspace_bytes(nq, nb, k)); return; }
+  if (knn_fused(k, nb)) { c.take<char>(sel_workspace_bytes(nq, nb, k)); return; }
   const int chunk = knn_chunk_cols(nq, nb);
   const int nchunks = ceil_div(nb, chunk);
   c.take<float>((size_t)nq * align_up((size_t)chunk, 4));
@@ -590,7 +639,7 @@ static void knn_scratch_size(CarveSize& c, int nq, int nb, int k) {
 
 static int knn_core(const char* pq, const float* qq, const float* isq, int nq, const char* pb, const float* bb,
                     const float* isb, int nb, int d, int k, int metric, int64_t index_base, float* out_d, void* out_i, int idx64, Carver& c, cudaStream_t st) {
-  if (knn_fused(k)) {
+  if (knn_fused(k, nb)) {
     // one GEMM over the whole gallery, candidates filtered against per-row thresholds in its epilogue, then the k best of
     // every row's list: no distance block, no per-block tables, no merge pass
     const size_t bytes = sel_workspace_bytes(nq, nb, k);

@@ -8,7 +8,7 @@ grep -E 'passed|failed|FAILED|ERROR|full-size' gpurun_out/t_$tag.log | tail -30
 timeout 300 python __graft_entry__.py smoke > gpurun_out/smoke_$tag.log 2>&1; echo "smoke rc=$?" | tee -a gpurun_out/summary_$tag.txt
 tail -3 gpurun_out/smoke_$tag.log
 if [ "$NO_BENCH" != "1" ]; then
-  ( time timeout 1200 python bench.py "$@" > gpurun_out/bench_$tag.json 2> gpurun_out/bench_$tag.err ) 2>&1 | tail -3; echo "bench rc=$?" | tee -a gpurun_out/summary_$tag.txt
+  ( time timeout 420 python bench.py "$@" > gpurun_out/bench_$tag.json 2> gpurun_out/bench_$tag.err ) 2>&1 | tail -3; echo "bench rc=$?" | tee -a gpurun_out/summary_$tag.txt
   tail -5 gpurun_out/bench_$tag.err
   python - <<PY
 import json
