@@ -410,8 +410,53 @@ def bench_retrieval(args, rank, world, dev, barrier):
 
 
 def bench_rerank_sharded(args, rank, world, dev, barrier):
-    """(e3) one re-ranked evaluation split over the ranks -- filled in once shard.rerank_eval_sharded exists."""
-    return None
+    """(e3) ONE re-ranked evaluation split over the ranks (shard.rerank_eval_sharded): k-NN rows sharded + all-gather of the
+    ranking tables, sparse stages replicated, Jaccard + blend + CMC/mAP counting of this rank's query rows, one all-reduce.
+    Strong scaling (the same set on every rank), device-timed, max over ranks.  Two workloads: configs[1] (hard data) --
+    latency-bound at this size, reported for completeness -- and a merged set 2.5x larger in each dimension, where the
+    N x N work (9.2 GB of squared distances, never materialised as a whole) is what is being divided."""
+    import reidb200  # noqa: F401
+    from reidb200 import _lib as L, shard, synth
+
+    out = {"scaling": "strong", "ranks": world,
+           "collectives": "all_gather_into_tensor x2 (ranking tables i32 + f32 [N,k1]) + all_reduce(sum) f64[G+1]"}
+    for tag, (Q, G, ids) in (("market", (Q_FULL, G_FULL, IDS_FULL)), ("large", (8000, 40000, 1900))):
+        d = synth.market_like(Q=Q, G=G, D=D_FULL, n_ids=ids, seed=1, noise=HARD_NOISE)
+        a = [torch.from_numpy(d[k]).to(dev) for k in ("qf", "ql", "qc", "gf", "gl", "gc")]
+        fn = lambda: shard.rerank_eval_sharded(*a, K1, K2, LAMBDA, device=dev)
+        for _ in range(2):
+            cmc, ap = fn()
+        barrier()
+        steps = max(3, min(args.steps, 10))
+        ms = _timed(fn, steps, barrier)
+        t = torch.tensor([ms], dtype=torch.float64, device=dev)
+        if world > 1:
+            import torch.distributed as dist
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item()) / steps
+        # phases of one evaluation on this rank (CUDA events): k-NN rows, exchange of the tables, this rank's query rows
+        merged = torch.cat([a[3], a[0]], 0)
+        ev = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
+        barrier()
+        ev[0].record()
+        ri, rd = shard.initial_rank_sharded(merged, K1)
+        ev[1].record()
+        cmc2, ap2 = fn()
+        ev[2].record()
+        torch.cuda.synchronize()
+        N = Q + G
+        row = {"queries": Q, "gallery": G, "N": N, "ms_per_eval": ms, "pairs_per_s": Q * G / (ms * 1e-3),
+               "knn_stage_incl_allgather_ms": ev[0].elapsed_time(ev[1]),
+               "allgather_bytes_per_rank": int(2 * ((N + world - 1) // world) * K1 * 4) if world > 1 else 0,
+               "allreduce_bytes": (G + 1) * 8 if world > 1 else 0,
+               "result": {"rank1": float(cmc[0]), "mAP": float(ap)}}
+        out[tag] = row
+        del a, d, merged
+        torch.cuda.empty_cache()
+    out["ms_per_eval"] = out["large"]["ms_per_eval"]
+    out["note"] = ("market: N = 19281 is launch / latency bound (one GPU finishes the whole step in ~1.2 ms); large: N = 48000, "
+                   "the k-NN stage (N^2 D flops / P per rank) dominates and divides")
+    return out
 
 
 def bench_eval_c1(args, rank, world, dev, barrier, d0):

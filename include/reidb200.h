@@ -166,6 +166,21 @@ int reidb200_jaccard_from_rank(const int32_t* rank, const float* sql2, int64_t l
                                float lambda_value, int row0, int nrows, int col0, int ncols,
                                void* out, int64_t ldo, void* workspace, size_t workspace_bytes,
                                void* stream);
+/* Row-sharded re-ranking (one rank of a multi-GPU run; also reid/faiss_utils.py:172-181 search_option 2 / 3,
+ * where the initial ranking comes from an index object): stages D3-D8 for the output rows [row0, row0 + nrows) x columns
+ * [col0, col0 + ncols) from a GIVEN global initial ranking rank_i i32[N,k1] with its squared-L2 values rank_d f32[N,k1].
+ * No squared-L2 matrix of the merged set is needed: the expansion's pair values come from the rows' own top-k1 lists or a
+ * direct dot product of the fp32 feature rows.  blend_sql2 f32[nrows, ldb] = squared L2 of exactly the output block (only
+ * read when lambda_value > 0).  Either `out` (the block of the Jaccard / re-ranked distance, f32 or f16) or the fused
+ * evaluation (hist != NULL: the output rows are queries, the columns the gallery; ql / qc i32[nrows], gl / gc
+ * i32[ncols]; hist i32[ncols] first-hit histogram is ADDED to, ap_q f64[nrows], first i32[nrows], status i32[64]) or both. */
+size_t reidb200_rerank_rows_workspace_bytes(int N, int d, int k1, int k2);
+int reidb200_rerank_rows_from_rank(const float* feats, int N, int64_t ldf, int d, const int32_t* rank_i,
+                                   const float* rank_d, int k1, int k2, int use_float16, float lambda_value,
+                                   int row0, int nrows, int col0, int ncols, const float* blend_sql2, int64_t ldb,
+                                   void* out, int64_t ldo, const int32_t* ql, const int32_t* qc, const int32_t* gl,
+                                   const int32_t* gc, int32_t* hist, double* ap_q, int32_t* first, int32_t* status,
+                                   void* workspace, size_t workspace_bytes, void* stream);
 /* R(i,k) lists for inspection/tests: out_idx i32[N,k+1] (-1 padded), out_cnt i32[N]
  * (reid/faiss_utils.py:142-146). */
 int reidb200_k_reciprocal(const int32_t* rank, int N, int k1_cols, int k, int32_t* out_idx,

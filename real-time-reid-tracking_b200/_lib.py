@@ -13,7 +13,7 @@ import torch
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libreidb200.so")
-ABI_VERSION = 5
+ABI_VERSION = 6
 
 OK, EINVAL, ECUDA, ELIMIT = 0, -1, -2, -3
 RESIZE_CV_LINEAR, RESIZE_PIL_ANTIALIAS = 0, 1
@@ -53,6 +53,9 @@ SIGNATURES = {
     "reidb200_jaccard_region_workspace_bytes": (_sz, [_i, _i, _i, _i, _i]),
     "reidb200_jaccard": (_i, [_vp, _i, _i64, _i, _i, _i, _i, _f, _i, _i, _i, _i, _vp, _i64, _vp, _vp, _sz, _vp]),
     "reidb200_jaccard_from_rank": (_i, [_vp, _vp, _i64, _vp, _i, _i, _i, _i, _f, _i, _i, _i, _i, _vp, _i64, _vp, _sz, _vp]),
+    "reidb200_rerank_rows_workspace_bytes": (_sz, [_i, _i, _i, _i]),
+    "reidb200_rerank_rows_from_rank": (_i, [_vp, _i, _i64, _i, _vp, _vp, _i, _i, _i, _f, _i, _i, _i, _i, _vp, _i64, _vp, _i64,
+                                            _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _sz, _vp]),
     "reidb200_k_reciprocal": (_i, [_vp, _i, _i, _i, _vp, _vp, _vp]),
     "reidb200_gallery_create": (_i, [_i, _i, _i, C.POINTER(_vp)]),
     "reidb200_gallery_destroy": (_i, [_vp]),

@@ -1101,6 +1101,68 @@ extern "C" int reidb200_jaccard(const float* feats, int N, int64_t ldf, int d, i
                                out, ldo, rd, ws.w, st, src);
 }
 
+// ------------------------------------------------------------------------------------ row-sharded re-ranking
+// Stages D3-D8 for a block of OUTPUT ROWS from a given global initial ranking: what one rank of a multi-GPU re-ranking
+// runs after the k-NN tables of all ranks have been all-gathered.  No squared-L2 matrix of the merged set is needed: pair
+// values of the expansion come from the rows' top-k1 lists (rank_d) or a direct dot product of the feature rows; the
+// lambda blend reads `blend_sql2`, the squared L2 of just this block (rows [row0, +nrows) x columns [col0, +ncols)).
+__global__ void __launch_bounds__(256)
+row_sqnorm_kernel(const float* __restrict__ x, int rows, int64_t ldx, int d, float* __restrict__ sqnorm) {
+  const int r = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (r >= rows) return;
+  float s = 0.f;
+  for (int k = lane; k < d; k += 32) { const float v = __ldg(x + (size_t)r * ldx + k); s = fmaf(v, v, s); }  // pack_rows_kernel's order
+  s = warp_sum(s);
+  if (lane == 0) sqnorm[r] = s;
+}
+
+extern "C" size_t reidb200_rerank_rows_workspace_bytes(int N, int d, int k1, int k2) {
+  if (N <= 0 || d <= 0 || k1 <= 0 || k2 <= 0) return 0;
+  const RerankDims rd = rerank_dims(N, k1, k2);
+  NullCarver c;
+  c.take<float>(N);
+  carve_sparse(c, N, k1, k2, rd, nullptr);
+  return align_up(c.off, 256);
+}
+
+extern "C" int reidb200_rerank_rows_from_rank(const float* feats, int N, int64_t ldf, int d, const int32_t* rank_i,
+                                              const float* rank_d, int k1, int k2, int use_float16, float lambda_value,
+                                              int row0, int nrows, int col0, int ncols, const float* blend_sql2, int64_t ldb,
+                                              void* out, int64_t ldo, const int32_t* ql, const int32_t* qc, const int32_t* gl,
+                                              const int32_t* gc, int32_t* hist, double* ap_q, int32_t* first, int32_t* status,
+                                              void* workspace, size_t workspace_bytes, void* stream) {
+  RB_REQUIRE(feats && rank_i && rank_d && N > 0 && d > 0 && ldf >= d, "rerank_rows_from_rank: bad argument");
+  const RerankDims rd = rerank_dims(N, k1, k2);
+  int rc = rerank_check(N, k1, k2, rd);
+  if (rc) return rc;
+  rc = region_check(N, row0, nrows, col0, ncols, out ? ldo : ncols);
+  if (rc) return rc;
+  const bool eval = hist != nullptr;
+  RB_REQUIRE(out || eval, "rerank_rows_from_rank: neither an output block nor an evaluation requested");
+  RB_REQUIRE(!eval || (ql && qc && gl && gc && ap_q && first && status && !use_float16 && ncols <= JR_PF * JR_THREADS),
+             "rerank_rows_from_rank: the fused evaluation needs labels, fp32 and at most %d columns", JR_PF * JR_THREADS);
+  RB_REQUIRE(lambda_value <= 0.f || (blend_sql2 && ldb >= ncols), "rerank_rows_from_rank: the lambda blend needs the block's squared L2");
+  RB_REQUIRE(workspace && workspace_bytes >= reidb200_rerank_rows_workspace_bytes(N, d, k1, k2), "rerank_rows_from_rank: workspace too small");
+  if (nrows == 0 || ncols == 0) return REIDB200_OK;
+  cudaStream_t st = (cudaStream_t)stream;
+  Carver c(workspace, workspace_bytes);
+  float* sqn = c.take<float>(N);
+  SparseWs w;
+  carve_sparse(c, N, k1, k2, rd, &w);
+  { ProfScope _ps("row_sqnorm_kernel", st); row_sqnorm_kernel<<<ceil_div(N, 8), 256, 0, st>>>(feats, N, ldf, d, sqn); }
+  RB_LAUNCH_CHECK("row_sqnorm_kernel");
+  PairSrc src;
+  memset(&src, 0, sizeof(src));
+  src.feats = feats; src.ldf = ldf; src.d = d; src.rank_i = rank_i; src.rank_d = rank_d; src.k1c = k1;
+  // jaccard_rows reads blend[i * lds + col0 + c] with the ABSOLUTE row i: hand it the virtual base of the block
+  const float* vbase = blend_sql2 ? blend_sql2 - (ptrdiff_t)row0 * ldb - col0 : nullptr;
+  EvalFuse ev;
+  memset(&ev, 0, sizeof(ev));
+  if (eval) { ev.ql = ql; ev.qc = qc; ev.gl = gl; ev.gc = gc; ev.hist = hist; ev.ap_q = ap_q; ev.first = first; ev.status = status; }
+  return jaccard_sparse_stages(rank_i, vbase, ldb, sqn, N, k1, k2, use_float16, lambda_value, row0, nrows, col0, ncols, out, ldo, rd,
+                               w, st, src, eval ? &ev : nullptr);
+}
+
 extern "C" int reidb200_k_reciprocal(const int32_t* rank, int N, int k1_cols, int k, int32_t* out_idx, int32_t* out_cnt,
                                      void* stream) {
   RB_REQUIRE(rank && out_idx && out_cnt && N > 0 && k1_cols > 0 && k > 0, "k_reciprocal: bad argument");

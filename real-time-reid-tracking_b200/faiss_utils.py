@@ -226,11 +226,36 @@ def compute_jaccard_distance_device(target_features, k1=20, k2=6, use_float16=Fa
 
 def compute_jaccard_distance(target_features, k1=20, k2=6, print_flag=True, search_option=0, use_float16=False):
     """np.ndarray[N,N] (float32, or float16 with use_float16) Jaccard distance of one merged set.
-    Every search_option (faiss GPU raw / GPU index / sharded / CPU) is served by the same exact GPU k-NN."""
+    search_option 0 / 1 / 3 (faiss GPU raw array / GPU index / CPU index): one GPU, the whole step in libreidb200.
+    search_option 2 (faiss_utils.py:172-176: `index_init_gpu(ngpus, d)` = IndexShards over every visible GPU): the k-NN
+    stage is sharded --
+      * under torch.distributed (one process per GPU): shard.compute_jaccard_distance_sharded, rows of the merged set split
+        over the ranks, one all-gather of the ranking tables, the N x N output row-sharded and gathered;
+      * in a single process: the reference's own sequence, `index_init_gpu(ngpus, d)`, `index.add(features)`,
+        `index.search(features, k1)` on the IndexShards stand-in (one shard per visible GPU, merged on device 0), then the
+        sparse stages from that ranking (no N x N squared-L2 matrix is built)."""
     end = time.time()
     if print_flag:
         print('Computing jaccard distance...')
-    J = ops.jaccard(target_features, k1, k2, use_float16)
+    if search_option == 2:
+        import torch.distributed as dist
+
+        if dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1:
+            from . import shard
+
+            J = shard.compute_jaccard_distance_sharded(target_features, k1, k2, use_float16)
+        else:
+            feats = L.as_f32_cuda(target_features)
+            N = feats.shape[0]
+            if not 1 <= k1 < N:
+                raise ValueError("jaccard: need 1 <= k1 < N (k1=%d, N=%d)" % (k1, N))
+            index = index_init_gpu(torch.cuda.device_count(), feats.shape[1])
+            index.add(feats)
+            D, initial_rank = index.search_device(feats, k1)
+            J = ops.rerank_rows_from_rank(feats, initial_rank.to(feats.device), D.to(feats.device), k1, k2, (0, N), (0, N), 0.0, None,
+                                          use_float16)
+    else:
+        J = ops.jaccard(target_features, k1, k2, use_float16)
     out = J.cpu().numpy()
     if print_flag:
         print("Jaccard distance computing time cost: {}".format(time.time() - end))

@@ -195,6 +195,51 @@ def jaccard(feats, k1=20, k2=6, use_float16=False, lambda_value=0.0, rows=None, 
     return (out, rank) if want_rank else out
 
 
+def rerank_rows_from_rank(feats, rank_i, rank_d, k1, k2, rows, cols, lambda_value=0.0, blend_sql2=None, use_float16=False,
+                          want_out=True, labels=None):
+    """Stages D3-D8 for the output block rows x cols ((start, count) each) of one merged set from a GIVEN global initial
+    ranking (rank_i i32[N,k1], rank_d f32[N,k1] squared L2): what one rank of a multi-GPU re-ranking runs after the k-NN
+    tables have been gathered (csrc/rerank.cu reidb200_rerank_rows_from_rank).  blend_sql2 f32[nrows, >= ncols]: squared L2
+    of the block, needed when lambda_value > 0.  labels = (ql i32[nrows], qc, gl i32[ncols], gc) adds the fused evaluation:
+    returns (out or None, hist i32[ncols], ap_q f64[nrows], first i32[nrows]); else returns out."""
+    feats = _f32(feats)
+    dev = L.require_device(feats)
+    N, d = feats.shape
+    rank_i = _i32(rank_i, dev)
+    rank_d = _f32(rank_d, dev)
+    if rank_i.shape != (N, k1) or rank_d.shape != (N, k1):
+        raise ValueError("rerank_rows_from_rank: the ranking tables must be [N, k1]")
+    row0, nrows = rows
+    col0, ncols = cols
+    out = torch.empty((nrows, ncols), dtype=torch.float16 if use_float16 else torch.float32, device=dev) if want_out else None
+    ldb = 0
+    if lambda_value > 0:
+        if blend_sql2 is None or blend_sql2.shape[0] != nrows or blend_sql2.shape[1] < ncols or blend_sql2.stride(1) != 1:
+            raise ValueError("rerank_rows_from_rank: blend_sql2 f32[nrows, >= ncols] is required when lambda_value > 0")
+        ldb = blend_sql2.stride(0)
+    hist = ap_q = first = status = None
+    lab = [None] * 4
+    if labels is not None:
+        lab = [_i32(x, dev) for x in labels]
+        if lab[0].numel() != nrows or lab[1].numel() != nrows or lab[2].numel() != ncols or lab[3].numel() != ncols:
+            raise ValueError("rerank_rows_from_rank: label / camera vectors do not match the block")
+        hist = torch.zeros(ncols, dtype=torch.int32, device=dev)
+        ap_q = torch.zeros(nrows, dtype=torch.float64, device=dev)
+        first = torch.full((nrows,), -1, dtype=torch.int32, device=dev)
+        status = torch.zeros(64, dtype=torch.int32, device=dev)
+    lib = L.load()
+    ws = L.workspace(lib.reidb200_rerank_rows_workspace_bytes(N, d, k1, k2), dev)
+    with torch.cuda.device(dev):
+        L.check(lib.reidb200_rerank_rows_from_rank(feats.data_ptr(), N, feats.stride(0), d, rank_i.data_ptr(), rank_d.data_ptr(), k1, k2,
+                                                   1 if use_float16 else 0, float(lambda_value), row0, nrows, col0, ncols,
+                                                   L.ptr(blend_sql2) if lambda_value > 0 else 0, ldb, L.ptr(out), ncols,
+                                                   L.ptr(lab[0]), L.ptr(lab[1]), L.ptr(lab[2]), L.ptr(lab[3]), L.ptr(hist), L.ptr(ap_q),
+                                                   L.ptr(first), L.ptr(status), ws.data_ptr(), ws.numel(), L.stream_ptr()))
+    if labels is not None:
+        return out, hist, ap_q, first
+    return out
+
+
 def k_reciprocal_lists(rank, k):
     """R(i,k) for every row: (idx i32[N,k+1] padded with -1, cnt i32[N])."""
     dev = L.require_device(rank if isinstance(rank, torch.Tensor) else None)

@@ -208,3 +208,110 @@ def evaluate_all_sharded(qf, ql, qc, gf, gl, gc, group=None, device=None, local_
     cmc = part[:G].to(torch.float32) / torch.full((1,), float(Q), dtype=torch.float32, device=dev)
     ap = part[G] / Q
     return cmc, ap
+
+
+# --------------------------------------------------------------------------------------------- row-sharded re-ranking
+def _gather_rows(local, n_total, world, group):
+    """all-gather of a row-sharded table (rank r holds rows shard_bounds(n_total, world)[r], all but the last shards have
+    ceil(n_total / world) rows): ONE all_gather_into_tensor of equal-sized (padded) pieces; returns [n_total, ...]."""
+    if world == 1:
+        return local
+    per = (n_total + world - 1) // world
+    piece = local
+    if piece.shape[0] != per:
+        pad = torch.zeros((per - piece.shape[0],) + tuple(piece.shape[1:]), dtype=piece.dtype, device=piece.device)
+        piece = torch.cat([piece, pad], 0)
+    out = torch.empty((world * per,) + tuple(piece.shape[1:]), dtype=piece.dtype, device=piece.device)
+    dist.all_gather_into_tensor(out, piece.contiguous(), group=group)
+    return out[:n_total]
+
+
+def initial_rank_sharded(feats, k1, group=None, local_knn=None):
+    """Stage D2 of the re-ranking split over the ranks (the reference's search_option 2 builds the same table
+    through faiss IndexShards, reid/faiss_utils.py:172-176): rank r searches its ROWS [lo_r, hi_r) of the merged set against
+    all N rows (tcgen05 GEMM + row select) and the [rows, k1] pieces are exchanged with one all-gather each for the indices
+    and the squared-L2 values.  Returns (rank_i i32[N,k1], rank_d f32[N,k1]), identical on every rank."""
+    distributed = dist.is_available() and dist.is_initialized()
+    rank = dist.get_rank(group) if distributed else 0
+    world = dist.get_world_size(group) if distributed else 1
+    N = int(feats.shape[0])
+    lo, hi = shard_bounds(N, world)[rank]
+    if local_knn is not None:
+        D, I = local_knn(feats[lo:hi], feats, k1)
+    else:
+        D, I = ops.knn(feats[lo:hi], feats, k1, "sql2", idx64=False)
+    rank_i = _gather_rows(I.to(torch.int32), N, world, group)
+    rank_d = _gather_rows(D.to(torch.float32), N, world, group)
+    return rank_i, rank_d
+
+
+def rerank_eval_sharded(qf, ql, qc, gf, gl, gc, k1=20, k2=6, lambda_value=0.3, group=None, device=None, local_knn=None,
+                        local_rows=None):
+    """ONE k-reciprocal re-ranked evaluation across the ranks of `group` (one process per GPU), SURVEY 8e row 3:
+
+      1. k-NN stage, row-sharded: every rank searches N / P rows of merged = cat(gallery, query) against all N rows;
+         all-gather of the (index, squared L2)[N, k1] tables (2 x N k1 4 bytes in total: 3 MB at Market size).
+      2. sparse stages (reciprocal lists, expansion, query expansion, inverted index) from the global table: replicated --
+         they are ~0.25 ms of latency-bound kernels on 0.5 GB of tables, cheaper to redo than to exchange.
+      3. Jaccard + lambda blend + CMC / mAP counting for this rank's Q / P QUERY rows only (its block of the Q x G squared-L2
+         matrix comes from one more tcgen05 GEMM of Q / P x G), then ONE all-reduce(sum) of f64[G + 1] (first-hit counts +
+         AP sum), as evaluate_all_sharded does.
+
+    Returns (CMC f32[G], mAP f64[]) identical on every rank and equal to ops.rerank_eval on one GPU (same kernels on the same
+    pair values: CMC bit-identical, the AP sum up to summation order).  `local_knn` / `local_rows` are the injection points
+    of the gloo host-logic test."""
+    distributed = dist.is_available() and dist.is_initialized()
+    rank = dist.get_rank(group) if distributed else 0
+    world = dist.get_world_size(group) if distributed else 1
+    custom = local_knn is not None
+    if custom:
+        dev = torch.device("cpu") if device is None else torch.device(device)
+        as_f = lambda x: torch.as_tensor(np.asarray(x, np.float32) if not isinstance(x, torch.Tensor) else x).to(dev)
+    else:
+        dev = device or L.require_device()
+        as_f = lambda x: L.as_f32_cuda(x, dev)
+    lab = lambda x: (x if isinstance(x, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(np.asarray(x)))).reshape(-1).to(dev).to(torch.int32)
+    qf, gf = as_f(qf), as_f(gf)
+    ql, qc, gl, gc = lab(ql), lab(qc), lab(gl), lab(gc)
+    Q, G = int(qf.shape[0]), int(gf.shape[0])
+    if Q == 0 or G == 0:
+        raise ValueError("rerank_eval_sharded: empty query or gallery set")
+    merged = torch.cat([gf, qf], 0)
+    rank_i, rank_d = initial_rank_sharded(merged, k1, group, local_knn)
+    q0, q1 = shard_bounds(Q, world)[rank]
+    part = torch.zeros(G + 1, dtype=torch.float64, device=dev)
+    if q1 > q0:
+        if custom:
+            hist, ap_q = local_rows(merged, rank_i, rank_d, k1, k2, G + q0, q1 - q0, G, lambda_value, ql[q0:q1], qc[q0:q1], gl, gc)
+        else:
+            blend = None
+            if lambda_value > 0:
+                ld = (G + 31) // 32 * 32  # 128-byte rows: the fused kernel reads the block with 128-bit loads
+                blend = torch.empty((q1 - q0, ld), dtype=torch.float32, device=dev)
+                ops.distmat(merged[G + q0:G + q1], gf, "sql2", out=blend[:, :G])
+            _, hist, ap_q, _ = ops.rerank_rows_from_rank(merged, rank_i, rank_d, k1, k2, (G + q0, q1 - q0), (0, G), lambda_value, blend,
+                                                         want_out=False, labels=(ql[q0:q1], qc[q0:q1], gl, gc))
+        part[:G] = torch.cumsum(hist.to(torch.float64), 0)
+        part[G] = ap_q.sum()
+    if world > 1:
+        dist.all_reduce(part, op=dist.ReduceOp.SUM, group=group)
+    cmc = part[:G].to(torch.float32) / torch.full((1,), float(Q), dtype=torch.float32, device=dev)
+    return cmc, part[G] / Q
+
+
+def compute_jaccard_distance_sharded(feats, k1=20, k2=6, use_float16=False, group=None, gather=True):
+    """compute_jaccard_distance (reid/faiss_utils.py:149-244) across the ranks of `group`: the k-NN stage row-sharded with
+    one all-gather of the ranking tables, the sparse stages replicated, and the dense N x N OUTPUT row-sharded -- rank r
+    writes rows shard_bounds(N, world)[r].  gather=True all-gathers the row blocks so that every rank returns the full
+    matrix (the reference's contract); gather=False returns (row block, (lo, hi)) and never holds N x N on one GPU."""
+    distributed = dist.is_available() and dist.is_initialized()
+    rank = dist.get_rank(group) if distributed else 0
+    world = dist.get_world_size(group) if distributed else 1
+    feats = L.as_f32_cuda(feats)
+    N = int(feats.shape[0])
+    rank_i, rank_d = initial_rank_sharded(feats, k1, group)
+    lo, hi = shard_bounds(N, world)[rank]
+    block = ops.rerank_rows_from_rank(feats, rank_i, rank_d, k1, k2, (lo, hi - lo), (0, N), 0.0, None, use_float16)
+    if not gather:
+        return block, (lo, hi)
+    return _gather_rows(block, N, world, group)

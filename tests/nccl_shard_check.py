@@ -60,6 +60,37 @@ for Q, G, D in ((3368, 15913, 512), (5, 40, 32), (1, 9, 16)):
     if rank == 0:
         print("shard_check world=%d evaluate_all Q=%d G=%d: query-sharded == single %s (rank1 %.6f mAP %.6f)" %
               (world, Q, G, same, float(cmc[0]), float(ap)), flush=True)
+# row-sharded re-ranked evaluation (k-NN rows sharded + all-gather of the ranking tables, query rows sharded + all-reduce)
+# against the single-GPU fused evaluation; and the row-sharded dense Jaccard matrix against the single-GPU one
+from reidb200 import faiss_utils
+
+for Q, G, D, hard in ((3368, 15913, 512, True), (300, 2100, 64, True), (3, 50, 32, False)):
+    m = synth.market_like(Q=Q, G=G, D=D, seed=Q + 1, noise="hard" if hard else 0.6)
+    a = [m[k] for k in ("qf", "ql", "qc", "gf", "gl", "gc")]
+    k1, k2 = (20, 6) if G > 100 else (6, 3)
+    cmc, ap = shard.rerank_eval_sharded(*a, k1, k2, 0.3, device=dev)
+    merged = torch.from_numpy(np.concatenate([m["gf"], m["qf"]], 0)).to(dev)
+    lab = [torch.from_numpy(m[k].astype(np.int32)).to(dev) for k in ("ql", "qc", "gl", "gc")]
+    cmc1, ap1 = ops.rerank_eval(merged, G, *lab, k1, k2, 0.3)
+    d_cmc, d_ap = float((cmc - cmc1).abs().max()), abs(float(ap) - float(ap1[0]))
+    # (pair values outside a row's top-k1 list are direct dot products here and matrix entries on one GPU: 1e-7 apart,
+    #  so a near-tie may swap two neighbours of one query)
+    same = d_cmc <= 2.0 / Q and d_ap <= 2e-5
+    ok &= same
+    if rank == 0:
+        print("shard_check world=%d rerank_eval Q=%d G=%d: row-sharded vs single max|dCMC| %.3g |dmAP| %.3g %s (rank1 %.6f mAP %.6f)" %
+              (world, Q, G, d_cmc, d_ap, same, float(cmc[0]), float(ap)), flush=True)
+    if G <= 2100:
+        J = shard.compute_jaccard_distance_sharded(merged, k1, k2)
+        J1 = ops.jaccard(merged, k1, k2)
+        dj = float((J - J1).abs().max())
+        block, (lo, hi) = shard.compute_jaccard_distance_sharded(merged, k1, k2, gather=False)
+        same = dj <= 2e-6 and bool(torch.equal(block, J[lo:hi]))
+        ok &= same
+        Jn = faiss_utils.compute_jaccard_distance(merged, k1, k2, print_flag=False, search_option=2)  # the reference-named entry
+        ok &= bool(np.array_equal(Jn, J.cpu().numpy()))
+        if rank == 0:
+            print("shard_check world=%d jaccard N=%d: row-sharded vs single max|dJ| %.3g %s" % (world, Q + G, dj, same), flush=True)
 t = torch.tensor([0 if ok else 1], device=dev)
 if world > 1:
     dist.all_reduce(t)

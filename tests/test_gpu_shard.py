@@ -111,3 +111,38 @@ def test_sharded_evaluate_all_single_rank(rb):
     assert abs(float(ap) - apo) < 1e-6
     CMC, ap2 = evaluate.evaluate_all_sharded(qf, ql, qc, gf, gl, gc, verbose=False)
     assert isinstance(CMC, torch.FloatTensor) and ap2 == float(ap)
+
+
+@pytest.mark.parametrize("lam", [0.0, 0.3])
+def test_rerank_rows_from_rank_equals_the_one_gpu_step(rb, lam):
+    """The row-block entry a rank of the sharded re-ranking runs (given ranking tables, pair values from the top-k1 lists or
+    direct dot products, blend from the block's own squared L2) against the one-GPU step: same ranking -> Jaccard block
+    within 2e-6; with the fused evaluation the histogram / AP of the block's queries; search_option=2 in one process."""
+    from reidb200 import faiss_utils as F, ops, synth
+
+    d = synth.market_like(Q=120, G=900, D=64, n_ids=60, seed=5, noise="hard")
+    G, Q = 900, 120
+    N = G + Q
+    merged = torch.from_numpy(np.concatenate([d["gf"], d["qf"]], 0)).cuda()
+    lab = [torch.from_numpy(d[k].astype(np.int32)).cuda() for k in ("ql", "qc", "gl", "gc")]
+    J, rank = ops.jaccard(merged, 20, 6, want_rank=True)
+    Dk, Ik = ops.knn(merged, merged, 20, "sql2", idx64=False)
+    assert torch.equal(Ik, rank)
+    block = ops.rerank_rows_from_rank(merged, Ik, Dk, 20, 6, (200, 300), (0, N))
+    assert float((block - J[200:500]).abs().max()) <= 2e-6
+    # evaluation of a query sub-range, as a rank of shard.rerank_eval_sharded does it
+    q0, nq = 30, 50
+    blend = ops.distmat(merged[G + q0:G + q0 + nq], merged[:G], "sql2") if lam > 0 else None
+    out, hist, ap_q, first = ops.rerank_rows_from_rank(merged, Ik, Dk, 20, 6, (G + q0, nq), (0, G), lam, blend,
+                                                       labels=(lab[0][q0:q0 + nq], lab[1][q0:q0 + nq], lab[2], lab[3]))
+    cmc1, ap1, dist1, ap_q1, first1 = ops.rerank_eval(merged, G, *lab, 20, 6, lam, want_dist=True, per_query=True)
+    assert float((out - dist1[q0:q0 + nq]).abs().max()) <= 2e-6
+    same = (first == first1[q0:q0 + nq])
+    assert int(same.sum()) >= nq - 2 and float((ap_q - ap_q1[q0:q0 + nq])[same].abs().max()) <= 1e-3
+    f = first[first >= 0].long()
+    assert torch.equal(hist.long(), torch.bincount(f, minlength=G)[:G])
+    if lam == 0.0:
+        Jn = F.compute_jaccard_distance(merged, 20, 6, print_flag=False, search_option=2)
+        assert Jn.shape == (N, N) and np.abs(Jn - J.cpu().numpy()).max() <= 2e-6
+        with pytest.raises(ValueError):
+            F.compute_jaccard_distance(merged[:10], 20, 6, print_flag=False, search_option=2)

@@ -159,3 +159,60 @@ def test_sharded_evaluate_all_world2_gloo(tmp_path, Q):
     cmc, ap = O.evaluate_all(qf, ql, qc, gf, gl, gc)
     assert np.array_equal(r0["cmc"], cmc)  # integer counts / Q: exact
     assert abs(float(r0["ap"]) - ap) < 1e-12
+
+
+# ------------------------------------------------------------------ row-sharded re-ranked evaluation
+def _oracle_local_knn(x_rows, x_all, k1):
+    from oracle import reid_oracle as O
+
+    D, I = O.knn_l2(x_all.numpy(), x_rows.numpy(), k1)
+    return torch.from_numpy(D.astype(np.float32)), torch.from_numpy(I.astype(np.int32))
+
+
+def _oracle_local_rows(merged, rank_i, rank_d, k1, k2, row0, nrows, G, lam, ql, qc, gl, gc):
+    """(first-hit histogram i64[G], AP f64[nrows]) of query rows [row0, row0 + nrows) of the merged set from the GLOBAL
+    initial ranking, with the oracle's dense Jaccard stage."""
+    from oracle import reid_oracle as O
+
+    x = merged.numpy()
+    J = O.compute_jaccard_distance(x, k1, k2, initial_rank=rank_i.numpy().astype(np.int64))
+    q = x[row0:row0 + nrows]
+    dist = (J[row0:row0 + nrows, :G] * np.float32(1.0 - lam) + O.euclidean_dist(q, x[:G]) * np.float32(lam)).astype(np.float32)
+    ap_q, first = O.evaluate_per_query_from_dist(dist, ql.numpy(), qc.numpy(), gl.numpy(), gc.numpy())
+    hist = np.bincount(first[first >= 0], minlength=G)[:G]
+    return torch.from_numpy(hist), torch.from_numpy(ap_q)
+
+
+def _rerank_worker(rank, world, port, Q, out_dir):
+    sys.path.insert(0, ROOT)
+    import reidb200  # noqa: F401
+    from reidb200 import shard
+
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        qf, ql, qc, gf, gl, gc = _eval_case(Q, 61)
+        merged = torch.from_numpy(np.concatenate([gf, qf], 0))
+        ri, rd = shard.initial_rank_sharded(merged, 6, local_knn=_oracle_local_knn)
+        cmc, ap = shard.rerank_eval_sharded(qf, ql, qc, gf, gl, gc, 6, 3, 0.3, local_knn=_oracle_local_knn, local_rows=_oracle_local_rows)
+        np.savez(os.path.join(out_dir, "rr%d.npz" % rank), cmc=cmc.numpy(), ap=float(ap), ri=ri.numpy(), rd=rd.numpy())
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("Q", [13, 1])
+def test_sharded_rerank_eval_world2_gloo(tmp_path, Q):
+    """Partitioning, the padded all-gather of the ranking tables (61 + Q rows over 2 ranks: unequal shards), the query
+    shards and the all-reduce of first-hit counts + AP sum: every rank returns the single-process answer."""
+    from oracle import reid_oracle as O
+
+    mp.spawn(_rerank_worker, args=(2, _free_port(), Q, str(tmp_path)), nprocs=2, join=True)
+    r0, r1 = np.load(tmp_path / "rr0.npz"), np.load(tmp_path / "rr1.npz")
+    assert np.array_equal(r0["cmc"], r1["cmc"]) and r0["ap"] == r1["ap"] and np.array_equal(r0["ri"], r1["ri"])
+    qf, ql, qc, gf, gl, gc = _eval_case(Q, 61)
+    merged = np.concatenate([gf, qf], 0)
+    D, I = O.knn_l2(merged, merged, 6)
+    assert np.array_equal(r0["ri"], I) and np.array_equal(r0["rd"], D.astype(np.float32))
+    dist_qg = O.re_ranking_from_feats(qf, gf, 6, 3, 0.3)
+    cmc, ap = O.evaluate_all_from_dist(dist_qg, ql, qc, gl, gc)
+    assert np.array_equal(r0["cmc"], cmc) and abs(float(r0["ap"]) - ap) < 1e-12
