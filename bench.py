@@ -413,14 +413,15 @@ def bench_rerank_sharded(args, rank, world, dev, barrier):
     """(e3) ONE re-ranked evaluation split over the ranks (shard.rerank_eval_sharded): k-NN rows sharded + all-gather of the
     ranking tables, sparse stages replicated, Jaccard + blend + CMC/mAP counting of this rank's query rows, one all-reduce.
     Strong scaling (the same set on every rank), device-timed, max over ranks.  Two workloads: configs[1] (hard data) --
-    latency-bound at this size, reported for completeness -- and a merged set 2.5x larger in each dimension, where the
-    N x N work (9.2 GB of squared distances, never materialised as a whole) is what is being divided."""
+    latency-bound at this size, reported for completeness -- and a merged set of 48000 rows (32000 queries x 16000 gallery rows: the fused
+    evaluation keeps a query's gallery row in registers, <= 16384 columns), where the N x N work (9.2 GB of squared distances,
+    never materialised as a whole) is what is being divided."""
     import reidb200  # noqa: F401
     from reidb200 import _lib as L, shard, synth
 
     out = {"scaling": "strong", "ranks": world,
            "collectives": "all_gather_into_tensor x2 (ranking tables i32 + f32 [N,k1]) + all_reduce(sum) f64[G+1]"}
-    for tag, (Q, G, ids) in (("market", (Q_FULL, G_FULL, IDS_FULL)), ("large", (8000, 40000, 1900))):
+    for tag, (Q, G, ids) in (("market", (Q_FULL, G_FULL, IDS_FULL)), ("large", (32000, 16000, 1900))):
         d = synth.market_like(Q=Q, G=G, D=D_FULL, n_ids=ids, seed=1, noise=HARD_NOISE)
         a = [torch.from_numpy(d[k]).to(dev) for k in ("qf", "ql", "qc", "gf", "gl", "gc")]
         fn = lambda: shard.rerank_eval_sharded(*a, K1, K2, LAMBDA, device=dev)
