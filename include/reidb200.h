@@ -141,6 +141,22 @@ int reidb200_eval_cmc_map(const float* mat, int Q, int G, int64_t ldm, int desce
                           float* out_cmc, double* out_ap, double* out_ap_q, int32_t* out_first,
                           void* workspace, size_t workspace_bytes, void* stream);
 
+/* Allocation-free variant of reidb200_eval_cmc_map.  It has NO counterpart in the reference: it was added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid it).  Same arguments without the workspace: the scratch (first-hit histogram, per-query AP /
+ * first hit when out_ap_q / out_first are NULL, status words; 229 632 bytes) is a file-scope static __device__ array
+ * inside the library, held by every GPU that loads it until exit.  Limits: Q <= REIDB200_EVAL_STATIC_MAX_Q and
+ * G <= REIDB200_EVAL_STATIC_MAX_G, larger sizes are rejected with REIDB200_EINVAL (use reidb200_eval_cmc_map).  The call
+ * allocates nothing (no cudaMalloc / cudaFree, no allocating library routine).  All calls on a device share the array
+ * and it keeps the last call's contents: each call clears what must start at zero on `stream`, so calls on one stream
+ * are safe back to back, while calls that overlap on the GPU (different streams, no ordering) race. */
+#define REIDB200_EVAL_STATIC_MAX_Q 8192
+#define REIDB200_EVAL_STATIC_MAX_G 32768
+int reidb200_eval_cmc_map_static(const float* mat, int Q, int G, int64_t ldm, int descending,
+                                 const int32_t* ql, const int32_t* qc, const int32_t* gl, const int32_t* gc,
+                                 float* out_cmc, double* out_ap, double* out_ap_q, int32_t* out_first,
+                                 void* stream);
+
 /* ------------------------------------------------------------------------------------------
  * (3) k-reciprocal re-ranking (reid/faiss_utils.py:142-244 compute_jaccard_distance,
  *     k_reciprocal_neigh) on ONE merged set of N rows.

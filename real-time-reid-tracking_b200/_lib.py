@@ -13,7 +13,7 @@ import torch
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libreidb200.so")
-ABI_VERSION = 6
+ABI_VERSION = 7
 
 OK, EINVAL, ECUDA, ELIMIT = 0, -1, -2, -3
 RESIZE_CV_LINEAR, RESIZE_PIL_ANTIALIAS = 0, 1
@@ -49,6 +49,7 @@ SIGNATURES = {
     "reidb200_topk_rows": (_i, [_vp, _i, _i, _i64, _vp, _i, _i, _i64, _vp, _vp, _i, _vp]),
     "reidb200_eval_workspace_bytes": (_sz, [_i, _i]),
     "reidb200_eval_cmc_map": (_i, [_vp, _i, _i, _i64, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _sz, _vp]),
+    "reidb200_eval_cmc_map_static": (_i, [_vp, _i, _i, _i64, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "reidb200_jaccard_workspace_bytes": (_sz, [_i, _i, _i, _i]),
     "reidb200_jaccard_region_workspace_bytes": (_sz, [_i, _i, _i, _i, _i]),
     "reidb200_jaccard": (_i, [_vp, _i, _i64, _i, _i, _i, _i, _f, _i, _i, _i, _i, _vp, _i64, _vp, _vp, _sz, _vp]),

@@ -222,3 +222,60 @@ extern "C" int reidb200_eval_cmc_map(const float* mat, int Q, int G, int64_t ldm
   RB_LAUNCH_CHECK("eval_query_kernel");
   return eval_finalize_launch(hist, apq, Q, G, out_cmc, out_ap, st);
 }
+
+// ------------------------------------------------------------------------------------ allocation-free variant
+// No counterpart in the reference: added for callers that cannot allocate
+// (CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).  Same kernels as reidb200_eval_cmc_map;
+// the scratch (first-hit histogram, per-query AP / first hit when the caller does not want them, status words) lives in
+// ONE file-scope device array that every GPU loading the library holds until exit.  All calls share it and it keeps the
+// last call's contents: the histogram and status words are cleared on the stream at the start of every call, the
+// per-query arrays are fully overwritten; two calls that overlap on the GPU (different streams) race.
+constexpr int EVAL_STATIC_MAX_Q = REIDB200_EVAL_STATIC_MAX_Q;
+constexpr int EVAL_STATIC_MAX_G = REIDB200_EVAL_STATIC_MAX_G;
+constexpr size_t EVAL_STATIC_O_HIST = 0;                                                              // i32[MAX_G]
+constexpr size_t EVAL_STATIC_O_APQ = EVAL_STATIC_O_HIST + (size_t)EVAL_STATIC_MAX_G * sizeof(int32_t);  // f64[MAX_Q]
+constexpr size_t EVAL_STATIC_O_FIRST = EVAL_STATIC_O_APQ + (size_t)EVAL_STATIC_MAX_Q * sizeof(double);  // i32[MAX_Q]
+constexpr size_t EVAL_STATIC_O_STATUS = EVAL_STATIC_O_FIRST + (size_t)EVAL_STATIC_MAX_Q * sizeof(int32_t);  // i32[64]
+constexpr size_t EVAL_STATIC_BYTES = EVAL_STATIC_O_STATUS + 64 * sizeof(int32_t);                     // 229 632 B
+static_assert(EVAL_STATIC_O_APQ % 256 == 0 && EVAL_STATIC_O_FIRST % 256 == 0 && EVAL_STATIC_O_STATUS % 256 == 0, "scratch pieces stay 256-byte aligned");
+
+static __device__ __align__(256) unsigned char g_eval_static_scratch[EVAL_STATIC_BYTES];
+
+// The array's name is only a stand-in on the host: its device address is looked up once per device, with that device
+// current, and that pointer is what the kernels get.
+static int eval_static_scratch(unsigned char** out) {
+  static unsigned char* addr[64] = {};
+  int dev = 0;
+  RB_CUDA(cudaGetDevice(&dev));
+  RB_REQUIRE(dev >= 0 && dev < 64, "eval_cmc_map_static: device ordinal %d out of range", dev);
+  if (!addr[dev]) {
+    void* p = nullptr;
+    RB_CUDA(cudaGetSymbolAddress(&p, g_eval_static_scratch));
+    RB_REQUIRE(p != nullptr, "eval_cmc_map_static: no device address for the static scratch");
+    addr[dev] = static_cast<unsigned char*>(p);
+  }
+  *out = addr[dev];
+  return REIDB200_OK;
+}
+
+extern "C" int reidb200_eval_cmc_map_static(const float* mat, int Q, int G, int64_t ldm, int descending, const int32_t* ql,
+                                            const int32_t* qc, const int32_t* gl, const int32_t* gc, float* out_cmc,
+                                            double* out_ap, double* out_ap_q, int32_t* out_first, void* stream) {
+  RB_REQUIRE(Q > 0 && G > 0, "eval_cmc_map_static: empty query or gallery set (Q=%d, G=%d)", Q, G);
+  RB_REQUIRE(Q <= EVAL_STATIC_MAX_Q && G <= EVAL_STATIC_MAX_G,
+             "eval_cmc_map_static: Q=%d / G=%d exceed the static scratch (Q <= %d, G <= %d): use reidb200_eval_cmc_map with a workspace",
+             Q, G, EVAL_STATIC_MAX_Q, EVAL_STATIC_MAX_G);
+  RB_REQUIRE(mat && ql && qc && gl && gc && out_cmc && out_ap && ldm >= G, "eval_cmc_map_static: bad argument");
+  cudaStream_t st = (cudaStream_t)stream;
+  unsigned char* base = nullptr;
+  if (int rc = eval_static_scratch(&base)) return rc;
+  int32_t* hist = reinterpret_cast<int32_t*>(base + EVAL_STATIC_O_HIST);
+  double* apq = out_ap_q ? out_ap_q : reinterpret_cast<double*>(base + EVAL_STATIC_O_APQ);
+  int32_t* first = out_first ? out_first : reinterpret_cast<int32_t*>(base + EVAL_STATIC_O_FIRST);
+  int32_t* status = reinterpret_cast<int32_t*>(base + EVAL_STATIC_O_STATUS);
+  RB_CUDA(cudaMemsetAsync(hist, 0, (size_t)G * sizeof(int32_t), st));       // (the previous call's counts are still there)
+  RB_CUDA(cudaMemsetAsync(status, 0, 64 * sizeof(int32_t), st));
+  { ProfScope _ps("eval_query_kernel", st); eval_query_kernel<<<Q, EV_THREADS, 0, st>>>(mat, G, ldm, descending, ql, qc, gl, gc, apq, first, hist, status); }
+  RB_LAUNCH_CHECK("eval_query_kernel");
+  return eval_finalize_launch(hist, apq, Q, G, out_cmc, out_ap, st);
+}
