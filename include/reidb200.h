@@ -259,9 +259,11 @@ int reidb200_assoc_frame(reidb200_gallery* g, const float* det_feat, int64_t ldf
 /* ------------------------------------------------------------------------------------------
  * One tracking frame FROM HOST ARRAYS in two calls (crops before the backbone, costs after it), the way the reference's
  * per-frame code hands over its data (strong_sort.py:149-159 _get_features; sort/tracker.py:175-233 _match): plain host
- * pointers in, each call ONE pinned host->device copy of the small per-frame tables + the kernels; frame_costs ends with
- * ONE device->host copy of both float64 cost matrices into pinned memory and a stream synchronisation, and returns
- * pointers into that pinned result (valid until the call after the next).  No per-frame allocation.
+ * pointers in, each call ONE pinned host->device copy of the small per-frame tables + the kernels (for large frames the
+ * cost tables go up on the context's own side stream while `stream` is still busy with the crops / the embedding network);
+ * the association kernel writes both float64 cost matrices straight into mapped pinned memory (they cross PCIe while the
+ * kernel runs: no device->host copy behind it), frame_costs ends with a stream synchronisation and returns pointers into
+ * that pinned result (valid until the call after the next).  No per-frame allocation.
  *   frame      u8[H,W,3] on the DEVICE (where the detector left it); xyxy_host i32[n,4] crop boxes img[y1:y2, x1:x2]
  *              (slice ends are clipped at the frame border as numpy does; an empty crop is REIDB200_EINVAL)
  *   det_feat   f32[M,d] on the DEVICE (the backbone's output); everything else is host memory:

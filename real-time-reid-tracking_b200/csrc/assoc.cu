@@ -1243,10 +1243,14 @@ struct reidb200_frame {
   size_t in_cap;            // bytes of one input staging buffer
   uint8_t* h_in[2];         // pinned
   uint8_t* d_in[2];
-  cudaEvent_t in_done[2];   // the H2D of staging buffer i has been consumed
-  double* h_out[2];         // pinned [2][max_tracks][max_dets]
+  cudaEvent_t in_done[2];   // every consumer of staging pair i (copy and kernels) has finished
+  cudaEvent_t in_ready[2];  // the side-stream copy of staging pair i has landed
+  cudaStream_t copy;        // side stream of the cost tables' H2D: it overlaps whatever the caller's stream still runs
+  double* h_out[2];         // pinned + mapped [2][max_tracks][max_dets]
+  double* h_out_dev[2];     // the same buffers as the device sees them (zero-copy target of the finaliser warps)
   double* d_out;
   int turn_in, turn_out;
+  int zero_copy;            // 1: the kernel writes the cost blocks straight into h_out (no D2H copy behind the kernel)
 };
 
 static size_t frame_in_bytes(int max_dets, int max_tracks) {
@@ -1267,9 +1271,13 @@ extern "C" int reidb200_frame_create(reidb200_gallery* g, int max_dets, int max_
     e = cudaMallocHost(&f->h_in[i], f->in_cap);
     if (e == cudaSuccess) e = cudaMalloc(&f->d_in[i], f->in_cap);
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(&f->in_done[i], cudaEventDisableTiming);
-    if (e == cudaSuccess) e = cudaMallocHost(&f->h_out[i], out_bytes);
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&f->in_ready[i], cudaEventDisableTiming);
+    if (e == cudaSuccess) e = cudaHostAlloc(&f->h_out[i], out_bytes, cudaHostAllocMapped);
+    if (e == cudaSuccess) e = cudaHostGetDevicePointer(reinterpret_cast<void**>(&f->h_out_dev[i]), f->h_out[i], 0);
   }
   if (e == cudaSuccess) e = cudaMalloc(&f->d_out, out_bytes);
+  if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&f->copy, cudaStreamNonBlocking);
+  { const char* m = getenv("REIDB200_FRAME_MODE"); f->zero_copy = m ? atoi(m) : 3; }  // measured: profiles/r02_frame_modes.log
   if (e != cudaSuccess) {
     reidb200_frame_destroy(f);
     return cuda_fail(e, "frame_create", __FILE__, __LINE__);
@@ -1284,14 +1292,16 @@ extern "C" int reidb200_frame_destroy(reidb200_frame* f) {
     if (f->h_in[i]) cudaFreeHost(f->h_in[i]);
     if (f->d_in[i]) cudaFree(f->d_in[i]);
     if (f->in_done[i]) cudaEventDestroy(f->in_done[i]);
+    if (f->in_ready[i]) cudaEventDestroy(f->in_ready[i]);
     if (f->h_out[i]) cudaFreeHost(f->h_out[i]);
   }
   if (f->d_out) cudaFree(f->d_out);
+  if (f->copy) cudaStreamDestroy(f->copy);
   delete f;
   return REIDB200_OK;
 }
 
-// next input staging pair (its previous copy must have been consumed: normally long ago)
+// next input staging pair (whatever consumed it two calls ago must have finished: normally long ago)
 static int frame_next_in(reidb200_frame* f) {
   const int i = f->turn_in;
   f->turn_in ^= 1;
@@ -1320,10 +1330,11 @@ extern "C" int reidb200_frame_crops(reidb200_frame* f, const uint8_t* frame, int
   }
   const size_t bytes = (size_t)n * 20;
   RB_CUDA(cudaMemcpyAsync(f->d_in[bi], f->h_in[bi], bytes, cudaMemcpyHostToDevice, st));
+  const int rc = reidb200_crop_resize_norm(frame, reinterpret_cast<const int64_t*>(f->d_in[bi]),
+                                           reinterpret_cast<const int32_t*>(f->d_in[bi] + (size_t)n * 8), n, out_h, out_w,
+                                           mean_host, std_host, REIDB200_RESIZE_CV_LINEAR, out, stream);
   RB_CUDA(cudaEventRecord(f->in_done[bi], st));
-  return reidb200_crop_resize_norm(frame, reinterpret_cast<const int64_t*>(f->d_in[bi]),
-                                   reinterpret_cast<const int32_t*>(f->d_in[bi] + (size_t)n * 8), n, out_h, out_w, mean_host,
-                                   std_host, REIDB200_RESIZE_CV_LINEAR, out, stream);
+  return rc;
 }
 
 extern "C" int reidb200_frame_costs(reidb200_frame* f, const float* det_feat, int64_t ldf, const float* det_tlwh_host, int M,
@@ -1350,18 +1361,31 @@ extern "C" int reidb200_frame_costs(reidb200_frame* f, const float* det_feat, in
   memcpy(h + o_slot, trk_slot_host, (size_t)T * 4);
   memcpy(h + o_tsu, trk_tsu_host, (size_t)T * 4);
   uint8_t* d = f->d_in[bi];
-  RB_CUDA(cudaMemcpyAsync(d, h, total, cudaMemcpyHostToDevice, st));
-  RB_CUDA(cudaEventRecord(f->in_done[bi], st));
-  double* app = f->d_out;
-  double* iou = f->d_out + (size_t)T * M;
+  // mode bit 1: the tables go up on the side stream (they depend on nothing the caller's stream is doing: the crop kernel
+  // or the embedding network may still be running there), the kernels wait for them by event
+  // (worth its event pair only when the stream is still busy with a large crop launch: 93 vs 105 us at 200 boxes, 75 vs 62 us
+  // at 30; REIDB200_FRAME_MODE=7 forces it for every frame)
+  if ((f->zero_copy & 2) && (M >= 96 || (f->zero_copy & 4))) {
+    RB_CUDA(cudaMemcpyAsync(d, h, total, cudaMemcpyHostToDevice, f->copy));
+    RB_CUDA(cudaEventRecord(f->in_ready[bi], f->copy));
+    RB_CUDA(cudaStreamWaitEvent(st, f->in_ready[bi], 0));
+  } else {
+    RB_CUDA(cudaMemcpyAsync(d, h, total, cudaMemcpyHostToDevice, st));
+  }
+  const int bo = f->turn_out;
+  f->turn_out ^= 1;
+  // mode bit 0 (zero copy): the finaliser warps store the two [T, M] blocks straight into mapped pinned memory (write-only,
+  // row pieces of consecutive columns), so the 2*T*M*8 bytes cross PCIe WHILE the kernel runs instead of in a copy behind it
+  double* app = (f->zero_copy & 1) ? f->h_out_dev[bo] : f->d_out;
+  double* iou = app + (size_t)T * M;
   int rc = reidb200_assoc_frame(f->g, det_feat, ldf, reinterpret_cast<const float*>(d + o_tlwh), M,
                                 reinterpret_cast<const int32_t*>(d + o_slot), reinterpret_cast<const double*>(d + o_mean),
                                 reinterpret_cast<const double*>(d + o_si), reinterpret_cast<const int32_t*>(d + o_tsu), T, mc_lambda,
                                 max_dist, max_iou_dist, iou_mode, flags, app, nullptr, iou, stream);
+  RB_CUDA(cudaEventRecord(f->in_done[bi], st));
   if (rc) return rc;
-  const int bo = f->turn_out;
-  f->turn_out ^= 1;
-  RB_CUDA(cudaMemcpyAsync(f->h_out[bo], f->d_out, (size_t)2 * T * M * sizeof(double), cudaMemcpyDeviceToHost, st));
+  if (!(f->zero_copy & 1))
+    RB_CUDA(cudaMemcpyAsync(f->h_out[bo], f->d_out, (size_t)2 * T * M * sizeof(double), cudaMemcpyDeviceToHost, st));
   RB_CUDA(cudaStreamSynchronize(st));
   *out_app_host = f->h_out[bo];
   *out_iou_host = f->h_out[bo] + (size_t)T * M;
