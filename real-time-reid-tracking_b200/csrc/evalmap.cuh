@@ -115,6 +115,63 @@ __device__ __forceinline__ uint32_t eval_good_mask(int G, int q, const int32_t* 
   return mask;
 }
 
+// Tail of one query's evaluation, after the counting pass: sc->gpos[s] = number of non-junk items that precede good item
+// s but not good item s - 1 (all NT threads call it, right after the barrier that ends the counting pass).
+template <int NT>
+__device__ __forceinline__ void eval_ap_tail(EvalScratch* sc, int ngood, int q, double* __restrict__ ap_q,
+                                             int32_t* __restrict__ first, int32_t* __restrict__ hist) {
+  const int tid = threadIdx.x;
+  if (ngood <= 32) {
+    // the usual case (a Market query has ~17 good items): prefix, AP terms and the ordered sum stay inside warp 0 --
+    // shuffles instead of two more block barriers and two serial loops through shared memory; same operations in
+    // the same order as the general path below
+    if (tid < 32) {
+      int pe = tid < ngood ? sc->gpos[tid] : 0;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {  // inclusive prefix: position of good s among the non-junk items
+        const int up = __shfl_up_sync(0xffffffffu, pe, o);
+        if (tid >= o) pe += up;
+      }
+      const double d_recall = 1.0 / (double)ngood;
+      double term = 0.0;
+      if (tid < ngood) {
+        const double precision = (double)(tid + 1) * 1.0 / (double)(pe + 1);
+        const double old_precision = pe != 0 ? (double)tid * 1.0 / (double)pe : 1.0;
+        term = d_recall * (old_precision + precision) / 2;
+      }
+      double ap = 0.0;
+      for (int t = 0; t < ngood; ++t) ap = ap + __shfl_sync(0xffffffffu, term, t);
+      if (tid == 0) {
+        ap_q[q] = ap;
+        first[q] = pe;
+        atomicAdd(hist + pe, 1);
+      }
+    }
+    return;
+  }
+  if (tid == 0) {  // inclusive prefix: position of good s among the non-junk items
+    int run = 0;
+    for (int e = 0; e < ngood; ++e) { run += sc->gpos[e]; sc->gpos[e] = run; }
+  }
+  __syncthreads();
+  // AP: sum over goods in ascending position of d_recall * (old_precision + precision) / 2 (evaluate.py:94-103)
+  const double d_recall = 1.0 / (double)ngood;
+  for (int i = tid; i < ngood; i += NT) {
+    const int pe = sc->gpos[i];  // rows_good[i]
+    const double precision = (double)(i + 1) * 1.0 / (double)(pe + 1);
+    const double old_precision = pe != 0 ? (double)i * 1.0 / (double)pe : 1.0;
+    sc->terms[i] = d_recall * (old_precision + precision) / 2;
+  }
+  __syncthreads();
+  if (tid == 0) {
+    double ap = 0.0;
+    for (int t = 0; t < ngood; ++t) ap = ap + sc->terms[t];
+    ap_q[q] = ap;
+    first[q] = sc->gpos[0];
+    atomicAdd(hist + sc->gpos[0], 1);
+  }
+}
+
 // One query whose G row values live in registers: thread tid holds column ev_col<NT, VEC>(tid, k) in val[k], k < PF
 // (G <= NT * PF);
 // goodmask = eval_good_mask<NT, PF>() of the same query.
@@ -184,55 +241,7 @@ __device__ __forceinline__ void eval_row_in_registers(float (&val)[PF], uint32_t
     ev_count_before(sc, ngood, ev_key(v, descending), j, descending, my_l, my_c, gl, gc);
   }
   __syncthreads();
-  if (ngood <= 32) {
-    // the usual case (a Market query has ~17 good items): prefix, AP terms and the ordered sum stay inside warp 0 --
-    // shuffles instead of two more block barriers and two serial loops through shared memory; same operations in
-    // the same order as the general path below
-    if (tid < 32) {
-      int pe = tid < ngood ? sc->gpos[tid] : 0;
-#pragma unroll
-      for (int o = 1; o < 32; o <<= 1) {  // inclusive prefix: position of good s among the non-junk items
-        const int up = __shfl_up_sync(0xffffffffu, pe, o);
-        if (tid >= o) pe += up;
-      }
-      const double d_recall = 1.0 / (double)ngood;
-      double term = 0.0;
-      if (tid < ngood) {
-        const double precision = (double)(tid + 1) * 1.0 / (double)(pe + 1);
-        const double old_precision = pe != 0 ? (double)tid * 1.0 / (double)pe : 1.0;
-        term = d_recall * (old_precision + precision) / 2;
-      }
-      double ap = 0.0;
-      for (int t = 0; t < ngood; ++t) ap = ap + __shfl_sync(0xffffffffu, term, t);
-      if (tid == 0) {
-        ap_q[q] = ap;
-        first[q] = pe;
-        atomicAdd(hist + pe, 1);
-      }
-    }
-    return;
-  }
-  if (tid == 0) {  // inclusive prefix: position of good s among the non-junk items
-    int run = 0;
-    for (int e = 0; e < ngood; ++e) { run += sc->gpos[e]; sc->gpos[e] = run; }
-  }
-  __syncthreads();
-  // AP: sum over goods in ascending position of d_recall * (old_precision + precision) / 2 (evaluate.py:94-103)
-  const double d_recall = 1.0 / (double)ngood;
-  for (int i = tid; i < ngood; i += NT) {
-    const int pe = sc->gpos[i];  // rows_good[i]
-    const double precision = (double)(i + 1) * 1.0 / (double)(pe + 1);
-    const double old_precision = pe != 0 ? (double)i * 1.0 / (double)pe : 1.0;
-    sc->terms[i] = d_recall * (old_precision + precision) / 2;
-  }
-  __syncthreads();
-  if (tid == 0) {
-    double ap = 0.0;
-    for (int t = 0; t < ngood; ++t) ap = ap + sc->terms[t];
-    ap_q[q] = ap;
-    first[q] = sc->gpos[0];
-    atomicAdd(hist + sc->gpos[0], 1);
-  }
+  eval_ap_tail<NT>(sc, ngood, q, ap_q, first, hist);
 }
 
 // CMC[r] = float(#queries with first hit <= r) / Q ; mAP = (sum_q ap_q in query order) / Q (evalmap.cu, single CTA).

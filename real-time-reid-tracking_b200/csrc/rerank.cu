@@ -12,6 +12,7 @@
 //   D8  optional lambda blend with the Euclidean distance (north_star; not in the reference)
 #include <stdlib.h>
 
+#include <algorithm>
 #include "evalmap.cuh"
 #include "gemm.cuh"
 
@@ -808,6 +809,258 @@ jaccard_rows_kernel(const int32_t* __restrict__ qcols, const float* __restrict__
   }
 }
 
+// ------------------------------------------------------------------------------------ D7 + D8 + B4-B6, evaluation only
+// The fused re-ranked EVALUATION of one query row (fp32, lambda > 0, nothing stored) as a kernel of its own: same
+// arithmetic as jaccard_rows_kernel's fused path, bit for bit, organised around what a row of a hard evaluation set costs:
+//   * the accumulator covers only the output columns [col0, col0 + ncols) (partners outside it are dropped at the scatter)
+//     and is read exactly once more, by the thread that holds the column's squared distance in a register, in the same pass
+//     that tests "can this column precede the worst good item" -- no conversion pass, no finished/raw bookkeeping;
+//   * the query's good items are found by one scan of the gallery labels issued under the kernel's first loads, their
+//     squared distances re-read from the row (a few dozen L2 hits);
+//   * the scatter walks (entry, position) space in warp-contiguous chunks, lanes interleaved: coalesced list reads, each
+//     lane's entry index advances monotonically (no per-term search);
+//   * per column the common case is one uint4 shared-memory load and four compares.
+// Dynamic smem: acc[nc4] (2.30 fixed point) | max(entries: e_val[cap] e_beg[cap] e_off[cap + 1], EvalScratch) | glist.
+constexpr int JE_GLIST = EV_GOOD_CAP;
+
+struct JeRow {  // what the rare per-column path needs, kept in one place so that the call passes two pointers
+  EvalScratch* sc;
+  int ngood;
+  float worst_v, one_m_l, lambda_value;
+};
+
+// a column that may precede the worst good item: finish its value, exact compare, junk test, count
+static __device__ __noinline__ void je_column(const JeRow& r, unsigned int a, float d2, int j) {
+  const float jd = a ? jaccard_nonzero(__fmul_rn(__uint2float_rn(a), JR_UNFIX), 0) : 1.0f;
+  const float v = jr_blend_value(jd, d2, r.one_m_l, r.lambda_value);
+  if (!(v <= r.worst_v)) return;
+  const uint32_t kj = ev_key(v, 0);
+  EvalScratch* sc = r.sc;
+  int lo = 0, hi = r.ngood - 1;
+  if (!ev_before(kj, j, sc->skey[hi], sc->scol[hi], 0)) return;
+  while (lo < hi) {  // smallest s with j before good s (exists: j is before the worst good)
+    const int mid = (lo + hi) >> 1;
+    if (ev_before(kj, j, sc->skey[mid], sc->scol[mid], 0)) hi = mid; else lo = mid + 1;
+  }
+  atomicAdd(&sc->gpos[lo], 1);
+}
+
+// a gallery item with the query's id: good (other camera) or junk (same camera, evaluate.py:71-72: returns true)
+static __device__ __noinline__ bool je_label_hit(int* glist, int* n_good, int j, int32_t my_c, const int32_t* __restrict__ gc) {
+  if (__ldg(gc + j) == my_c) return true;
+  const int pos = atomicAdd(n_good, 1);
+  if (pos < JE_GLIST) glist[pos] = j;
+  return false;
+}
+
+// bit 4 g + u of word tid: column 4 (tid + g JR_THREADS) + u of the output block is junk for EVERY query (label -1,
+// evaluate.py:71) or lies beyond the block -- jaccard_eval_rows_kernel's thread tid holds exactly these columns
+__global__ void __launch_bounds__(JR_THREADS)
+junk_layout_kernel(const int32_t* __restrict__ gl, int ncols, uint32_t* __restrict__ junk32) {
+  const int tid = threadIdx.x;
+  uint32_t m = 0;
+  for (int k = 0; k < JR_PF; ++k) {
+    const int j = 4 * (tid + (k >> 2) * JR_THREADS) + (k & 3);
+    if (j >= ncols || __ldg(gl + j) == -1) m |= 1u << k;
+  }
+  junk32[tid] = m;
+}
+
+__global__ void __launch_bounds__(JR_THREADS, 2)
+jaccard_eval_rows_kernel(const int32_t* __restrict__ qcols, const float* __restrict__ qvals, const int32_t* __restrict__ qcnt,
+                         int cap, const int32_t* __restrict__ colptr, const int32_t* __restrict__ inv_row,
+                         const float* __restrict__ inv_val, int row0, int col0, int ncols, float lambda_value,
+                         const float* __restrict__ sql2, int64_t lds, int region_bytes,
+                         const uint32_t* __restrict__ junk32, EvalFuse ev) {
+  extern __shared__ __align__(16) unsigned int je_smem[];
+  const int nc4 = (ncols + 3) & ~3;
+  unsigned int* acci = je_smem;
+  unsigned char* region = reinterpret_cast<unsigned char*>(acci + nc4);
+  float* e_val = reinterpret_cast<float*>(region);
+  int* e_beg = reinterpret_cast<int*>(e_val + cap);
+  int* e_off = e_beg + cap;
+  EvalScratch* sc = reinterpret_cast<EvalScratch*>(region);  // alive once the entries are dead (after the scatter)
+  int* glist = reinterpret_cast<int*>(region + region_bytes);
+  __shared__ int warp_tot[JR_THREADS / 32];
+  __shared__ int s_ngood;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int q = blockIdx.x;
+  const int i = row0 + q;
+  if (tid == 0) s_ngood = 0;
+  __syncthreads();
+  // timing experiments (REIDB200_JE_DEBUG bit 16): thread 0 adds the cycles of each phase, /16, to status[8 + phase]
+  long long tick = (ev.enabled & 16) ? clock64() : 0;
+  auto phase_done = [&](int ph) {
+    if ((ev.enabled & 16) && tid == 0) {
+      const long long now = clock64();
+      atomicAdd(ev.status + 8 + ph, (int)((now - tick) >> 4));
+      tick = now;
+    }
+  };
+
+  // ---- the row's squared distances: requested now (the whole slice in flight), first used after the scatter
+  const float* srow = sql2 + (size_t)i * lds + col0;
+  float pre[JR_PF];
+#pragma unroll
+  for (int g = 0; g < JR_PF / 4; ++g) {
+    const int c0 = 4 * (tid + g * JR_THREADS);
+    // a group that straddles ncols still lies inside the row's allocation (lds >= the row length rounded up to 4)
+    const float4 v = c0 < ncols ? __ldg(reinterpret_cast<const float4*>(srow + c0)) : make_float4(0.f, 0.f, 0.f, 0.f);
+    pre[4 * g] = v.x; pre[4 * g + 1] = v.y; pre[4 * g + 2] = v.z; pre[4 * g + 3] = v.w;
+  }
+  const int n = qcnt[i];
+  const int32_t my_l = ev.ql[q], my_c = ev.qc[q];
+  // ---- the non-zeros of V_qe row i and the extents of their inverted lists
+  for (int t = tid; t < n; t += JR_THREADS) {
+    const float v = qvals[(size_t)i * cap + t];
+    const int j = qcols[(size_t)i * cap + t];
+    const int b = colptr[j], e = colptr[j + 1];
+    e_val[t] = v;
+    e_beg[t] = b;
+    e_off[t] = v == 0.f ? 0 : e - b;
+  }
+  for (int r = tid; r < nc4 / 4; r += JR_THREADS) reinterpret_cast<uint4*>(acci)[r] = make_uint4(0u, 0u, 0u, 0u);
+  // ---- good items of the query: same id, other camera (evaluate.py:66-70); labels are L2 resident across the queries
+  // The labels are read in the layout of the row values (thread = groups of four consecutive columns), so the thread
+  // also learns which of ITS columns are junk: bit 4 g + u of junkmask = label -1 (query independent: junk_layout_kernel)
+  // or same id and same camera (evaluate.py:71-72) -- the counting pass below then needs no label loads.
+  uint32_t junkmask = __ldg(junk32 + tid);
+  {
+    const int4* gl4 = reinterpret_cast<const int4*>(ev.gl);
+    const int full4 = ncols >> 2;
+#pragma unroll
+    for (int g = 0; g < JR_PF / 4; ++g) {
+      const int j4 = tid + g * JR_THREADS;
+      const int4 lab = j4 < full4 ? __ldg(gl4 + j4) : make_int4(-1, -1, -1, -1);
+      if ((lab.x == my_l) | (lab.y == my_l) | (lab.z == my_l) | (lab.w == my_l)) {
+        const int32_t ll[4] = {lab.x, lab.y, lab.z, lab.w};
+#pragma unroll
+        for (int x = 0; x < 4; ++x)
+          if (ll[x] == my_l && je_label_hit(glist, &s_ngood, 4 * j4 + x, my_c, ev.gc)) junkmask |= 1u << (4 * g + x);
+      }
+    }
+    // the columns behind the last whole group of four
+    for (int j = 4 * full4 + (tid == full4 % JR_THREADS ? 0 : 4); j < ncols; ++j)
+      if (__ldg(ev.gl + j) == my_l && je_label_hit(glist, &s_ngood, j, my_c, ev.gc))
+        junkmask |= 1u << (4 * (full4 / JR_THREADS) + (j & 3));
+  }
+  __syncthreads();
+  phase_done(0);
+  const int total = block_exclusive_scan(e_off, n, warp_tot);  // e_off[t] = first flat index of entry t
+  if (tid == 0) e_off[n] = total;
+  __syncthreads();
+  phase_done(1);
+  // ---- scatter: flat (entry, position) space in warp-contiguous chunks, lanes interleaved
+  {
+    constexpr int NW = JR_THREADS / 32, U = 4;
+    const int per_warp = ((total + NW - 1) / NW + 31) & ~31;
+    const int wb = warp * per_warp, we = min(total, wb + per_warp);
+    if (wb < we && !(ev.enabled & 2)) {
+      int t;
+      {  // largest t with e_off[t] <= first index of this lane (entries with an empty list share their successor's offset)
+        const int w = min(wb + lane, we - 1);
+        int lo = 0, hi = n - 1;
+        while (lo < hi) {
+          const int mid = (lo + hi + 1) >> 1;
+          if (e_off[mid] <= w) lo = mid; else hi = mid - 1;
+        }
+        t = lo;
+      }
+      int lo_t = e_off[t], hi_t = e_off[t + 1], beg_t = e_beg[t];  // the lane's current entry, reloaded when it changes
+      float val_t = e_val[t];
+      for (int w0 = wb + lane; w0 < we; w0 += U * 32) {
+        int rr[U];
+        float vv[U], mv[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+          const int w = w0 + u * 32;
+          rr[u] = -1;
+          if (w < we) {
+            if (w >= hi_t) {
+              do { ++t; hi_t = e_off[t + 1]; } while (w >= hi_t);
+              lo_t = e_off[t]; beg_t = e_beg[t]; val_t = e_val[t];
+            }
+            const int p = beg_t + (w - lo_t);
+            rr[u] = __ldg(inv_row + p) - col0;
+            vv[u] = __ldg(inv_val + p);
+            mv[u] = val_t;
+          }
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u)
+          if ((unsigned)rr[u] < (unsigned)ncols) atomicAdd(acci + rr[u], __float2uint_rn(__fmul_rn(fminf(mv[u], vv[u]), JR_FIX)));
+      }
+    }
+  }
+  __syncthreads();  // the accumulator is complete; the entries are dead: their shared memory is the evaluation scratch now
+  phase_done(2);
+  const int ngood = s_ngood;
+  if (ngood == 0) {  // the cmc[0] == -1 sentinel: query skipped (evaluate.py:43-45,80-82)
+    if (tid == 0) { ev.ap_q[q] = 0.0; ev.first[q] = -1; }
+    return;
+  }
+  if (ngood > EV_GOOD_CAP) {  // poison the result so that the caller fails loudly
+    if (tid == 0) { atomicExch(ev.status, 1); ev.ap_q[q] = __longlong_as_double(0x7ff8000000000000LL); ev.first[q] = -1; }
+    return;
+  }
+  const float one_m_l = 1.0f - lambda_value;
+  for (int e = tid; e < ngood; e += JR_THREADS) {  // final values of the good items
+    const int c = glist[e];
+    const unsigned int a = acci[c];
+    const float jd = a ? jaccard_nonzero(__fmul_rn(__uint2float_rn(a), JR_UNFIX), 0) : 1.0f;
+    sc->gcol[e] = c;
+    sc->gkey[e] = ev_key(jr_blend_value(jd, __ldg(srow + c), one_m_l, lambda_value), 0);
+  }
+  __syncthreads();
+  for (int e = tid; e < ngood; e += JR_THREADS) {  // rank-sort the goods into ranking order
+    const uint32_t k = sc->gkey[e];
+    const int c = sc->gcol[e];
+    int r = 0;
+    for (int f = 0; f < ngood; ++f) r += ev_before(sc->gkey[f], sc->gcol[f], k, c, 0);
+    sc->skey[r] = k;
+    sc->scol[r] = c;
+  }
+  for (int e = tid; e <= ngood; e += JR_THREADS) sc->gpos[e] = 0;
+  __syncthreads();
+  phase_done(3);
+  JeRow jr;
+  jr.sc = sc; jr.ngood = ngood;
+  jr.one_m_l = one_m_l; jr.lambda_value = lambda_value;
+  {
+    const uint32_t worst_o = sc->skey[ngood - 1];
+    jr.worst_v = __uint_as_float((worst_o & 0x80000000u) ? (worst_o & 0x7fffffffu) : ~worst_o);
+  }
+  // One branch-free superset test for every column, with or without shared neighbours (on hard data a fifth of a row has
+  // some): with t = the accumulated sum, jd = 1 - t / (2 - t) >= 1 - (t + t^2) / 2 on [0, 1], so
+  //   final <= w  =>  lambda * sqrt(d2) <= w - (1 - lambda) * (1 - (t + t^2) / 2)  =>  d2 <= (c0 + c1 * (t + t^2))^2
+  // with c0 = (w - (1 - lambda)) / lambda and c1 = (1 - lambda) / (2 lambda), both rounded up generously (relative 1e-5,
+  // absolute 4e-6 (|w| + 1): far above the few ulp the exact value can differ by; the 1.2e-12 covers the clamp of d2 at 1e-12).
+  // The exact value (an IEEE division and a square root) is computed only for the columns that pass.
+  const float w_s = __fadd_rn(jr.worst_v, __fmul_rn(__fadd_rn(fabsf(jr.worst_v), 1.0f), 4e-6f));
+  const float c0 = __fmul_rn(__fdiv_rn(__fsub_rn(w_s, one_m_l), lambda_value), w_s >= one_m_l ? 1.00001f : 0.99999f);
+  const float c1 = __fmul_rn(__fdiv_rn(one_m_l, __fadd_rn(lambda_value, lambda_value)), 1.00002f);
+#pragma unroll
+  for (int g = 0; g < JR_PF / 4; ++g) {
+    const int c0g = 4 * (tid + g * JR_THREADS);
+    if (c0g < ncols) {
+      const uint4 a4 = *reinterpret_cast<const uint4*>(acci + c0g);
+      const unsigned int aa[4] = {a4.x, a4.y, a4.z, a4.w};
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const float d2 = pre[4 * g + u];
+        const float t = __fmul_rn(__uint2float_rn(aa[u]), JR_UNFIX);
+        const float b = fmaxf(__fmaf_rn(c1, __fmaf_rn(t, t, t), c0), 0.f);
+        if (d2 <= __fmaf_rn(__fmul_rn(b, b), 1.0001f, 1.2e-12f) && !((junkmask >> (4 * g + u)) & 1u) && !(ev.enabled & 4))
+          je_column(jr, aa[u], d2, c0g + u);  // (columns beyond ncols carry the junk bit)
+      }
+    }
+  }
+  __syncthreads();
+  phase_done(4);
+  eval_ap_tail<JR_THREADS>(sc, ngood, q, ev.ap_q, ev.first, ev.hist);
+  phase_done(5);
+}
+
 // ------------------------------------------------------------------------------------ host side
 struct RerankDims {
   int half, wh, cap1, cap2;
@@ -826,6 +1079,7 @@ static RerankDims rerank_dims(int N, int k1, int k2) {
 
 struct SparseWs {
   int32_t *rfull, *rfull_cnt, *rhalf, *rhalf_cnt, *v1cols, *v1cnt, *v2cols, *v2cnt, *colcnt, *colptr, *cursor, *inv_row;
+  uint32_t* junk32;  // label == -1 bits of the output columns in jaccard_eval_rows_kernel's register layout
   float *v1vals, *v2vals, *inv_val;
 };
 
@@ -851,6 +1105,7 @@ static void carve_sparse(C& c, int N, int k1, int k2, const RerankDims& d, Spars
   t.cursor = c.template take<int32_t>(N + 1);
   t.inv_row = c.template take<int32_t>((size_t)N * d.cap2);
   t.inv_val = c.template take<float>((size_t)N * d.cap2);
+  t.junk32 = c.template take<uint32_t>(JR_THREADS);
   if (w) *w = t;
 }
 
@@ -884,6 +1139,7 @@ static int jaccard_sparse_stages(const int32_t* rank, const float* sql2, int64_t
     RB_CUDA(cudaFuncSetAttribute(qexpand_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 8192 * 12));
     RB_CUDA(cudaFuncSetAttribute(inv_scan_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448 - 256));
     RB_CUDA(cudaFuncSetAttribute(jaccard_rows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448 - 256));
+    RB_CUDA(cudaFuncSetAttribute(jaccard_eval_rows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448 - 256));
   }
   const int wpb = 8;
   { ProfScope _ps("krecip_kernel", st); krecip_both_kernel<<<ceil_div(N, wpb), wpb * 32, 0, st>>>(rank, N, k1, k1, d.wh, w.rfull, w.rfull_cnt, w.rhalf, w.rhalf_cnt); }
@@ -926,6 +1182,22 @@ static int jaccard_sparse_stages(const int32_t* rank, const float* sql2, int64_t
     evf = *ev;
     evf.enabled = 1;
     if (jr_smem < sizeof(EvalScratch) + 16) jr_smem = sizeof(EvalScratch) + 16;
+  }
+  // evaluation only (nothing stored, fp32, blended, 128-bit aligned row slices): the kernel built for it
+  if (ev && !out && !use_f16 && lambda_value > 0.f && ncols <= JR_PF * JR_THREADS && (col0 & 3) == 0 && (lds & 3) == 0 &&
+      ((reinterpret_cast<uintptr_t>(sql2) | reinterpret_cast<uintptr_t>(ev->gl)) & 15) == 0 && !getenv("REIDB200_JR_OLD")) {
+    const size_t region = align_up(std::max((size_t)jr_cap * 12 + 16, sizeof(EvalScratch)), 16);
+    const size_t je_smem = (size_t)((ncols + 3) & ~3) * 4 + region + (size_t)JE_GLIST * 4;
+    if (je_smem <= 232448 - 256) {
+      if (const char* dbg = getenv("REIDB200_JE_DEBUG")) evf.enabled |= atoi(dbg) & ~1;  // timing experiments only (wrong results)
+      { ProfScope _ps("junk_layout_kernel", st); junk_layout_kernel<<<1, JR_THREADS, 0, st>>>(ev->gl, ncols, w.junk32); }
+      RB_LAUNCH_CHECK("junk_layout_kernel");
+      { ProfScope _ps("jaccard_rows_kernel", st); jaccard_eval_rows_kernel<<<nrows, JR_THREADS, je_smem, st>>>(
+          w.v2cols, w.v2vals, w.v2cnt, d.cap2, w.colptr, w.inv_row, w.inv_val, row0, col0, ncols, lambda_value, sql2, lds,
+          (int)region, w.junk32, evf); }
+      RB_LAUNCH_CHECK("jaccard_eval_rows_kernel");
+      return REIDB200_OK;
+    }
   }
   { ProfScope _ps("jaccard_rows_kernel", st); jaccard_rows_kernel<<<nrows, JR_THREADS, jr_smem, st>>>(
       w.v2cols, w.v2vals, w.v2cnt, d.cap2, w.colptr, w.inv_row, w.inv_val, N, row0, col0, ncols, lambda_value, sql2, lds,

@@ -236,8 +236,13 @@ def rerank_rows_from_rank(feats, rank_i, rank_d, k1, k2, rows, cols, lambda_valu
                                                    L.ptr(lab[0]), L.ptr(lab[1]), L.ptr(lab[2]), L.ptr(lab[3]), L.ptr(hist), L.ptr(ap_q),
                                                    L.ptr(first), L.ptr(status), ws.data_ptr(), ws.numel(), L.stream_ptr()))
     if labels is not None:
+        global _last_status
+        _last_status = status  # (status words of the last fused evaluation: overflow flag + the kernels' debug counters)
         return out, hist, ap_q, first
     return out
+
+
+_last_status = None
 
 
 def k_reciprocal_lists(rank, k):

@@ -6,7 +6,8 @@ import reidb200
 from reidb200 import ops, synth
 import bench
 
-d = synth.market_like(Q=bench.Q_FULL, G=bench.G_FULL, D=bench.D_FULL, n_ids=bench.IDS_FULL, seed=0)
+# argv[2] = 'easy' for SURVEY 8d's recipe (noise 0.6); default = the hard data of the headline
+d = bench.market_set(0, hard=not (len(sys.argv) > 2 and sys.argv[2] == 'easy'))
 dev = torch.device("cuda", 0)
 merged = torch.from_numpy(np.concatenate([d["gf"], d["qf"]], 0)).to(dev)
 lab = {k: torch.from_numpy(d[k].astype(np.int32)).to(dev) for k in ("ql", "qc", "gl", "gc")}
