@@ -811,20 +811,68 @@ jaccard_rows_kernel(const int32_t* __restrict__ qcols, const float* __restrict__
 
 // ------------------------------------------------------------------------------------ D7 + D8 + B4-B6, evaluation only
 // The fused re-ranked EVALUATION of one query row (fp32, lambda > 0, nothing stored) as a kernel of its own: same
-// arithmetic as jaccard_rows_kernel's fused path, bit for bit, organised around what a row of a hard evaluation set costs:
+// arithmetic as jaccard_rows_kernel's fused path, bit for bit, organised around what a row of a HARD evaluation set costs
+// (75 non-zeros in the V_qe row, 6300 scatter terms, a fifth of the columns with shared neighbours, 75 -- up to 6000 --
+// columns ranked before the worst good item; profiles/r02_jaccard_eval_rows.md):
 //   * the accumulator covers only the output columns [col0, col0 + ncols) (partners outside it are dropped at the scatter)
-//     and is read exactly once more, by the thread that holds the column's squared distance in a register, in the same pass
-//     that tests "can this column precede the worst good item" -- no conversion pass, no finished/raw bookkeeping;
-//   * the query's good items are found by one scan of the gallery labels issued under the kernel's first loads, their
-//     squared distances re-read from the row (a few dozen L2 hits);
+//     and is read exactly once more, by the thread that holds the column's squared distance in a register;
+//   * the query's good items and same-camera junk come from per-query lists built once per evaluation
+//     (query_lists_kernel), the label -1 junk from a bit mask in the row kernel's register layout (junk_layout_kernel):
+//     no label is read per row;
 //   * the scatter walks (entry, position) space in warp-contiguous chunks, lanes interleaved: coalesced list reads, each
-//     lane's entry index advances monotonically (no per-term search);
-//   * per column the common case is one uint4 shared-memory load and four compares.
-// Dynamic smem: acc[nc4] (2.30 fixed point) | max(entries: e_val[cap] e_beg[cap] e_off[cap + 1], EvalScratch) | glist.
+//     lane's entry index advances monotonically, every load of a batch issued before the first loaded value is used;
+//   * per column ONE branch-free superset test (a quadratic lower bound of the Jaccard distance, no division, no square
+//     root), 32 independent chains per thread; the columns that pass are staged and their exact values computed by the
+//     whole CTA afterwards, evenly spread.
+// Dynamic smem: acc[nc4] (2.30 fixed point) | max(entries: e_val[cap] e_beg[cap] e_off[cap + 1], EvalScratch) |
+//               glist[JE_GLIST] gd2[JE_GLIST] jlist[QL_STRIDE].
+// REIDB200_JE_DEBUG (timing experiments): 2 = no scatter, 4 = no candidates (both give wrong results), 16 = cycles per
+// phase and row statistics into status[8..] (tools/je_phases.py).
 constexpr int JE_GLIST = EV_GOOD_CAP;
 
-struct JeRow {  // what the rare per-column path needs, kept in one place so that the call passes two pointers
+constexpr int QL_STRIDE = 128;  // gallery items with the query's id kept per query by query_lists_kernel (more: label scan in the row kernel)
+constexpr int JE_CAND = EV_GOOD_CAP;  // candidate columns staged per row (more: finished in place)
+
+// Per query: the gallery columns that carry the query's id (evaluate.py:66-72), bit 31 set when the camera is the same
+// (junk) and clear when it differs (a good item).  Eight queries per CTA share one pass over the label vector.
+// qlcnt[q] may exceed QL_STRIDE: the row kernel then scans the labels itself.
+constexpr int QLK_Q = 8;
+__global__ void __launch_bounds__(256)
+query_lists_kernel(const int32_t* __restrict__ ql, const int32_t* __restrict__ qc, const int32_t* __restrict__ gl,
+                   const int32_t* __restrict__ gc, int Q, int G, int32_t* __restrict__ qlist, int32_t* __restrict__ qlcnt) {
+  __shared__ int32_t s_l[QLK_Q], s_c[QLK_Q];
+  __shared__ int s_n[QLK_Q];
+  const int q0 = blockIdx.x * QLK_Q, tid = threadIdx.x;
+  if (tid < QLK_Q) {
+    const int q = min(q0 + tid, Q - 1);
+    s_l[tid] = ql[q]; s_c[tid] = qc[q]; s_n[tid] = 0;
+  }
+  __syncthreads();
+  int32_t ll[QLK_Q];
+#pragma unroll
+  for (int x = 0; x < QLK_Q; ++x) ll[x] = s_l[x];
+  for (int j = tid; j < G; j += 256) {
+    const int32_t l = __ldg(gl + j);
+    bool any = false;
+#pragma unroll
+    for (int x = 0; x < QLK_Q; ++x) any |= l == ll[x];
+    if (any) {
+      const int32_t c = __ldg(gc + j);
+      for (int x = 0; x < QLK_Q; ++x)
+        if (l == ll[x] && q0 + x < Q) {
+          const int pos = atomicAdd(&s_n[x], 1);
+          if (pos < QL_STRIDE) qlist[(size_t)(q0 + x) * QL_STRIDE + pos] = j | (c == s_c[x] ? (int32_t)0x80000000 : 0);
+        }
+    }
+  }
+  __syncthreads();
+  if (tid < QLK_Q && q0 + tid < Q) qlcnt[q0 + tid] = s_n[tid];
+}
+
+struct JeRow {  // what the exact per-column path needs, kept in one place so that the call passes one pointer
   EvalScratch* sc;
+  const int* jlist;  // same id, same camera columns of this query (query_lists_kernel), n_junk of them
+  int n_junk;
   int ngood;
   float worst_v, one_m_l, lambda_value;
 };
@@ -838,6 +886,8 @@ static __device__ __noinline__ void je_column(const JeRow& r, unsigned int a, fl
   EvalScratch* sc = r.sc;
   int lo = 0, hi = r.ngood - 1;
   if (!ev_before(kj, j, sc->skey[hi], sc->scol[hi], 0)) return;
+  for (int e = 0; e < r.n_junk; ++e)
+    if (r.jlist[e] == j) return;  // same id, same camera: junk (evaluate.py:71-72)
   while (lo < hi) {  // smallest s with j before good s (exists: j is before the worst good)
     const int mid = (lo + hi) >> 1;
     if (ev_before(kj, j, sc->skey[mid], sc->scol[mid], 0)) hi = mid; else lo = mid + 1;
@@ -845,12 +895,20 @@ static __device__ __noinline__ void je_column(const JeRow& r, unsigned int a, fl
   atomicAdd(&sc->gpos[lo], 1);
 }
 
-// a gallery item with the query's id: good (other camera) or junk (same camera, evaluate.py:71-72: returns true)
-static __device__ __noinline__ bool je_label_hit(int* glist, int* n_good, int j, int32_t my_c, const int32_t* __restrict__ gc) {
-  if (__ldg(gc + j) == my_c) return true;
-  const int pos = atomicAdd(n_good, 1);
-  if (pos < JE_GLIST) glist[pos] = j;
-  return false;
+// exclusive scan of data[0..n] (n + 1 values, data[n] = 0 on entry => data[n] = total on exit) by ONE warp
+__device__ __forceinline__ void warp_exclusive_scan(int* data, int n1, int lane) {
+  const int per = (n1 + 31) >> 5;
+  const int b = lane * per, e = min(n1, b + per);
+  int s = 0;
+  for (int t = b; t < e; ++t) s += data[t];
+  int incl = s;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const int v = __shfl_up_sync(0xffffffffu, incl, o);
+    if (lane >= o) incl += v;
+  }
+  int run = incl - s;
+  for (int t = b; t < e; ++t) { const int v = data[t]; data[t] = run; run += v; }
 }
 
 // bit 4 g + u of word tid: column 4 (tid + g JR_THREADS) + u of the output block is junk for EVERY query (label -1,
@@ -866,12 +924,17 @@ junk_layout_kernel(const int32_t* __restrict__ gl, int ncols, uint32_t* __restri
   junk32[tid] = m;
 }
 
+struct JeLists {  // per-query label lists (query_lists_kernel) + the label -1 layout (junk_layout_kernel)
+  const int32_t* qlist;
+  const int32_t* qlcnt;
+  const uint32_t* junk32;
+};
+
 __global__ void __launch_bounds__(JR_THREADS, 2)
 jaccard_eval_rows_kernel(const int32_t* __restrict__ qcols, const float* __restrict__ qvals, const int32_t* __restrict__ qcnt,
                          int cap, const int32_t* __restrict__ colptr, const int32_t* __restrict__ inv_row,
                          const float* __restrict__ inv_val, int row0, int col0, int ncols, float lambda_value,
-                         const float* __restrict__ sql2, int64_t lds, int region_bytes,
-                         const uint32_t* __restrict__ junk32, EvalFuse ev) {
+                         const float* __restrict__ sql2, int64_t lds, int region_bytes, JeLists lists, EvalFuse ev) {
   extern __shared__ __align__(16) unsigned int je_smem[];
   const int nc4 = (ncols + 3) & ~3;
   unsigned int* acci = je_smem;
@@ -880,14 +943,13 @@ jaccard_eval_rows_kernel(const int32_t* __restrict__ qcols, const float* __restr
   int* e_beg = reinterpret_cast<int*>(e_val + cap);
   int* e_off = e_beg + cap;
   EvalScratch* sc = reinterpret_cast<EvalScratch*>(region);  // alive once the entries are dead (after the scatter)
-  int* glist = reinterpret_cast<int*>(region + region_bytes);
-  __shared__ int warp_tot[JR_THREADS / 32];
-  __shared__ int s_ngood;
+  int* glist = reinterpret_cast<int*>(region + region_bytes);  // good columns [JE_GLIST]
+  float* gd2 = reinterpret_cast<float*>(glist + JE_GLIST);     // their squared distances [JE_GLIST]
+  int* jlist = reinterpret_cast<int*>(gd2 + JE_GLIST);         // same id, same camera columns [QL_STRIDE]
+  __shared__ int s_ngood, s_njunk, s_ncand;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int q = blockIdx.x;
   const int i = row0 + q;
-  if (tid == 0) s_ngood = 0;
-  __syncthreads();
   // timing experiments (REIDB200_JE_DEBUG bit 16): thread 0 adds the cycles of each phase, /16, to status[8 + phase]
   long long tick = (ev.enabled & 16) ? clock64() : 0;
   auto phase_done = [&](int ph) {
@@ -905,13 +967,28 @@ jaccard_eval_rows_kernel(const int32_t* __restrict__ qcols, const float* __restr
   for (int g = 0; g < JR_PF / 4; ++g) {
     const int c0 = 4 * (tid + g * JR_THREADS);
     // a group that straddles ncols still lies inside the row's allocation (lds >= the row length rounded up to 4)
-    const float4 v = c0 < ncols ? __ldg(reinterpret_cast<const float4*>(srow + c0)) : make_float4(0.f, 0.f, 0.f, 0.f);
+    // (streaming: the slice is read once; the inverted lists and label lists it would evict from L2 are re-read by every row)
+    const float4 v = c0 < ncols ? __ldcs(reinterpret_cast<const float4*>(srow + c0)) : make_float4(0.f, 0.f, 0.f, 0.f);
     pre[4 * g] = v.x; pre[4 * g + 1] = v.y; pre[4 * g + 2] = v.z; pre[4 * g + 3] = v.w;
   }
+  const int nl = lists.qlcnt[q];
+  if (tid == 0) { s_ncand = 0; s_ngood = 0; s_njunk = 0; }
+  // bit 4 g + u: this thread's column 4 (tid + g JR_THREADS) + u has label -1 or lies beyond the block
+  uint32_t junkmask = __ldg(lists.junk32 + tid);
+  // ---- the non-zeros of V_qe row i and the extents of their inverted lists.  The first JR_THREADS slots are read
+  // without waiting for the row's count (what the slots behind it hold is never used): one dependent round trip less
+  // on the kernel's critical path.
+  float v0 = 0.f;
+  int j0 = 0;
+  if (tid < cap) { v0 = __ldg(qvals + (size_t)i * cap + tid); j0 = __ldg(qcols + (size_t)i * cap + tid); }
   const int n = qcnt[i];
-  const int32_t my_l = ev.ql[q], my_c = ev.qc[q];
-  // ---- the non-zeros of V_qe row i and the extents of their inverted lists
-  for (int t = tid; t < n; t += JR_THREADS) {
+  if (tid < n) {
+    const int b = colptr[j0], e = colptr[j0 + 1];
+    e_val[tid] = v0;
+    e_beg[tid] = b;
+    e_off[tid] = v0 == 0.f ? 0 : e - b;
+  }
+  for (int t = tid + JR_THREADS; t < n; t += JR_THREADS) {
     const float v = qvals[(size_t)i * cap + t];
     const int j = qcols[(size_t)i * cap + t];
     const int b = colptr[j], e = colptr[j + 1];
@@ -919,37 +996,44 @@ jaccard_eval_rows_kernel(const int32_t* __restrict__ qcols, const float* __restr
     e_beg[t] = b;
     e_off[t] = v == 0.f ? 0 : e - b;
   }
+  if (tid == 0) e_off[n] = 0;  // the scan turns it into the total
   for (int r = tid; r < nc4 / 4; r += JR_THREADS) reinterpret_cast<uint4*>(acci)[r] = make_uint4(0u, 0u, 0u, 0u);
-  // ---- good items of the query: same id, other camera (evaluate.py:66-70); labels are L2 resident across the queries
-  // The labels are read in the layout of the row values (thread = groups of four consecutive columns), so the thread
-  // also learns which of ITS columns are junk: bit 4 g + u of junkmask = label -1 (query independent: junk_layout_kernel)
-  // or same id and same camera (evaluate.py:71-72) -- the counting pass below then needs no label loads.
-  uint32_t junkmask = __ldg(junk32 + tid);
-  {
-    const int4* gl4 = reinterpret_cast<const int4*>(ev.gl);
-    const int full4 = ncols >> 2;
-#pragma unroll
-    for (int g = 0; g < JR_PF / 4; ++g) {
-      const int j4 = tid + g * JR_THREADS;
-      const int4 lab = j4 < full4 ? __ldg(gl4 + j4) : make_int4(-1, -1, -1, -1);
-      if ((lab.x == my_l) | (lab.y == my_l) | (lab.z == my_l) | (lab.w == my_l)) {
-        const int32_t ll[4] = {lab.x, lab.y, lab.z, lab.w};
-#pragma unroll
-        for (int x = 0; x < 4; ++x)
-          if (ll[x] == my_l && je_label_hit(glist, &s_ngood, 4 * j4 + x, my_c, ev.gc)) junkmask |= 1u << (4 * g + x);
+  __syncthreads();  // (also: the counters are set for everybody)
+  phase_done(0);
+  // ---- warp 0 scans the list lengths; the other warps fetch the query's label lists meanwhile: good items (same id,
+  // other camera, evaluate.py:66-70) with their squared distances, and the same-camera junk (evaluate.py:71-72)
+  if (warp == 0) warp_exclusive_scan(e_off, n + 1, lane);
+  if (nl <= QL_STRIDE) {
+    for (int e = tid - 32; e < nl && warp != 0; e += JR_THREADS - 32) {
+      const int32_t item = __ldg(lists.qlist + (size_t)q * QL_STRIDE + e);
+      const int c = item & 0x7fffffff;
+      if (item < 0) {
+        jlist[atomicAdd(&s_njunk, 1)] = c;
+      } else {
+        const int pos = atomicAdd(&s_ngood, 1);
+        glist[pos] = c;
+        gd2[pos] = __ldg(srow + c);
       }
     }
-    // the columns behind the last whole group of four
-    for (int j = 4 * full4 + (tid == full4 % JR_THREADS ? 0 : 4); j < ncols; ++j)
-      if (__ldg(ev.gl + j) == my_l && je_label_hit(glist, &s_ngood, j, my_c, ev.gc))
-        junkmask |= 1u << (4 * (full4 / JR_THREADS) + (j & 3));
+  } else {
+    // more items with the query's id than query_lists_kernel keeps: scan the labels here; the same-camera junk goes
+    // straight into the junk bits of the threads that own those columns (n_junk stays 0)
+    const int32_t my_l = ev.ql[q], my_c = ev.qc[q];
+    for (int k = 0; k < JR_PF; ++k) {
+      const int j = 4 * (tid + (k >> 2) * JR_THREADS) + (k & 3);
+      if (j < ncols && __ldg(ev.gl + j) == my_l) {
+        if (__ldg(ev.gc + j) == my_c) {
+          junkmask |= 1u << k;
+        } else {
+          const int pos = atomicAdd(&s_ngood, 1);
+          if (pos < JE_GLIST) { glist[pos] = j; gd2[pos] = __ldg(srow + j); }
+        }
+      }
+    }
   }
   __syncthreads();
-  phase_done(0);
-  const int total = block_exclusive_scan(e_off, n, warp_tot);  // e_off[t] = first flat index of entry t
-  if (tid == 0) e_off[n] = total;
-  __syncthreads();
   phase_done(1);
+  const int total = e_off[n];
   // ---- scatter: flat (entry, position) space in warp-contiguous chunks, lanes interleaved
   {
     constexpr int NW = JR_THREADS / 32, U = 4;
@@ -969,26 +1053,28 @@ jaccard_eval_rows_kernel(const int32_t* __restrict__ qcols, const float* __restr
       int lo_t = e_off[t], hi_t = e_off[t + 1], beg_t = e_beg[t];  // the lane's current entry, reloaded when it changes
       float val_t = e_val[t];
       for (int w0 = wb + lane; w0 < we; w0 += U * 32) {
+        // NOTHING in the first loop may read a loaded value (the warp would wait there, in order, before it has issued
+        // the loads of the next u: one L2 round trip per term instead of one per batch -- measured 3x on this phase);
+        // indices behind the chunk's end are clamped to its last element and dropped in the second loop
         int rr[U];
         float vv[U], mv[U];
 #pragma unroll
         for (int u = 0; u < U; ++u) {
-          const int w = w0 + u * 32;
-          rr[u] = -1;
-          if (w < we) {
-            if (w >= hi_t) {
-              do { ++t; hi_t = e_off[t + 1]; } while (w >= hi_t);
-              lo_t = e_off[t]; beg_t = e_beg[t]; val_t = e_val[t];
-            }
-            const int p = beg_t + (w - lo_t);
-            rr[u] = __ldg(inv_row + p) - col0;
-            vv[u] = __ldg(inv_val + p);
-            mv[u] = val_t;
+          const int w = min(w0 + u * 32, we - 1);
+          if (w >= hi_t) {
+            do { ++t; hi_t = e_off[t + 1]; } while (w >= hi_t);
+            lo_t = e_off[t]; beg_t = e_beg[t]; val_t = e_val[t];
           }
+          const int p = beg_t + (w - lo_t);
+          rr[u] = __ldg(inv_row + p);
+          vv[u] = __ldg(inv_val + p);
+          mv[u] = val_t;
         }
 #pragma unroll
-        for (int u = 0; u < U; ++u)
-          if ((unsigned)rr[u] < (unsigned)ncols) atomicAdd(acci + rr[u], __float2uint_rn(__fmul_rn(fminf(mv[u], vv[u]), JR_FIX)));
+        for (int u = 0; u < U; ++u) {
+          const int c = rr[u] - col0;
+          if ((unsigned)c < (unsigned)ncols && w0 + u * 32 < we) atomicAdd(acci + c, __float2uint_rn(__fmul_rn(fminf(mv[u], vv[u]), JR_FIX)));
+        }
       }
     }
   }
@@ -1004,12 +1090,35 @@ jaccard_eval_rows_kernel(const int32_t* __restrict__ qcols, const float* __restr
     return;
   }
   const float one_m_l = 1.0f - lambda_value;
+  if (ngood <= 32) {
+    // the usual case: final values and the rank-sort inside warp 0 (shuffles, no block barrier in between)
+    if (warp == 0) {
+      uint32_t k = 0xffffffffu;
+      int c = 0x7fffffff;
+      if (lane < ngood) {
+        c = glist[lane];
+        const unsigned int a = acci[c];
+        const float jd = a ? jaccard_nonzero(__fmul_rn(__uint2float_rn(a), JR_UNFIX), 0) : 1.0f;
+        k = ev_key(jr_blend_value(jd, gd2[lane], one_m_l, lambda_value), 0);
+      }
+      int r = 0;
+#pragma unroll
+      for (int f = 0; f < 32; ++f) {  // (lanes behind ngood hold the largest key and column: never "before" anything)
+        const uint32_t kf = __shfl_sync(0xffffffffu, k, f);
+        const int cf = __shfl_sync(0xffffffffu, c, f);
+        r += ev_before(kf, cf, k, c, 0);
+      }
+      if (lane < ngood) { sc->skey[r] = k; sc->scol[r] = c; }
+      sc->gpos[lane] = 0;
+      if (lane == 0) sc->gpos[32] = 0;
+    }
+  } else {
   for (int e = tid; e < ngood; e += JR_THREADS) {  // final values of the good items
     const int c = glist[e];
     const unsigned int a = acci[c];
     const float jd = a ? jaccard_nonzero(__fmul_rn(__uint2float_rn(a), JR_UNFIX), 0) : 1.0f;
     sc->gcol[e] = c;
-    sc->gkey[e] = ev_key(jr_blend_value(jd, __ldg(srow + c), one_m_l, lambda_value), 0);
+    sc->gkey[e] = ev_key(jr_blend_value(jd, gd2[e], one_m_l, lambda_value), 0);
   }
   __syncthreads();
   for (int e = tid; e < ngood; e += JR_THREADS) {  // rank-sort the goods into ranking order
@@ -1021,10 +1130,11 @@ jaccard_eval_rows_kernel(const int32_t* __restrict__ qcols, const float* __restr
     sc->scol[r] = c;
   }
   for (int e = tid; e <= ngood; e += JR_THREADS) sc->gpos[e] = 0;
+  }
   __syncthreads();
   phase_done(3);
   JeRow jr;
-  jr.sc = sc; jr.ngood = ngood;
+  jr.sc = sc; jr.ngood = ngood; jr.jlist = jlist; jr.n_junk = s_njunk;
   jr.one_m_l = one_m_l; jr.lambda_value = lambda_value;
   {
     const uint32_t worst_o = sc->skey[ngood - 1];
@@ -1034,33 +1144,66 @@ jaccard_eval_rows_kernel(const int32_t* __restrict__ qcols, const float* __restr
   // some): with t = the accumulated sum, jd = 1 - t / (2 - t) >= 1 - (t + t^2) / 2 on [0, 1], so
   //   final <= w  =>  lambda * sqrt(d2) <= w - (1 - lambda) * (1 - (t + t^2) / 2)  =>  d2 <= (c0 + c1 * (t + t^2))^2
   // with c0 = (w - (1 - lambda)) / lambda and c1 = (1 - lambda) / (2 lambda), both rounded up generously (relative 1e-5,
-  // absolute 4e-6 (|w| + 1): far above the few ulp the exact value can differ by; the 1.2e-12 covers the clamp of d2 at 1e-12).
-  // The exact value (an IEEE division and a square root) is computed only for the columns that pass.
+  // absolute 4e-6 (|w| + 1): far above the few ulp the exact value can differ by; the 1.2e-12 covers the clamp of d2 at
+  // 1e-12).  The columns that pass are only STAGED here (column + squared distance): their exact values -- an IEEE
+  // division, a square root and a binary search each -- are computed afterwards, spread evenly over the CTA, instead
+  // of by whichever warp happens to own the query's neighbourhood.
   const float w_s = __fadd_rn(jr.worst_v, __fmul_rn(__fadd_rn(fabsf(jr.worst_v), 1.0f), 4e-6f));
   const float c0 = __fmul_rn(__fdiv_rn(__fsub_rn(w_s, one_m_l), lambda_value), w_s >= one_m_l ? 1.00001f : 0.99999f);
   const float c1 = __fmul_rn(__fdiv_rn(one_m_l, __fadd_rn(lambda_value, lambda_value)), 1.00002f);
+  int* cand_col = sc->gcol;                                  // (the unsorted good lists are dead after the rank-sort)
+  float* cand_d2 = reinterpret_cast<float*>(sc->gkey);
+  // pass 1: the 32 tests of the thread, branch-free (32 independent chains for the scheduler: with a branch per column
+  // the pass ran at the latency of one chain after the other); pass 2: the few set bits
+  uint32_t pass = 0;
 #pragma unroll
   for (int g = 0; g < JR_PF / 4; ++g) {
     const int c0g = 4 * (tid + g * JR_THREADS);
-    if (c0g < ncols) {
-      const uint4 a4 = *reinterpret_cast<const uint4*>(acci + c0g);
-      const unsigned int aa[4] = {a4.x, a4.y, a4.z, a4.w};
+    // (a group beyond the block reads the accumulator's first entries instead: its columns carry the junk bit)
+    const uint4 a4 = *reinterpret_cast<const uint4*>(acci + (c0g < ncols ? c0g : 0));
+    const unsigned int aa[4] = {a4.x, a4.y, a4.z, a4.w};
 #pragma unroll
-      for (int u = 0; u < 4; ++u) {
-        const float d2 = pre[4 * g + u];
-        const float t = __fmul_rn(__uint2float_rn(aa[u]), JR_UNFIX);
-        const float b = fmaxf(__fmaf_rn(c1, __fmaf_rn(t, t, t), c0), 0.f);
-        if (d2 <= __fmaf_rn(__fmul_rn(b, b), 1.0001f, 1.2e-12f) && !((junkmask >> (4 * g + u)) & 1u) && !(ev.enabled & 4))
-          je_column(jr, aa[u], d2, c0g + u);  // (columns beyond ncols carry the junk bit)
-      }
+    for (int u = 0; u < 4; ++u) {
+      const float t = __fmul_rn(__uint2float_rn(aa[u]), JR_UNFIX);
+      const float b = fmaxf(__fmaf_rn(c1, __fmaf_rn(t, t, t), c0), 0.f);
+      pass |= (pre[4 * g + u] <= __fmaf_rn(__fmul_rn(b, b), 1.0001f, 1.2e-12f) ? 1u : 0u) << (4 * g + u);
     }
+  }
+  pass &= ~junkmask;
+  if (ev.enabled & 4) pass = 0;
+  while (pass) {
+    const int k = __ffs(pass) - 1;
+    pass &= pass - 1;
+    float d2 = 0.f;
+#pragma unroll
+    for (int x = 0; x < JR_PF; ++x) d2 = x == k ? pre[x] : d2;  // (a register file has no dynamic index)
+    const int c = 4 * (tid + (k >> 2) * JR_THREADS) + (k & 3);
+    const int pos = atomicAdd(&s_ncand, 1);
+    if (pos < JE_CAND) { cand_col[pos] = c; cand_d2[pos] = d2; }
+    else je_column(jr, acci[c], d2, c);
   }
   __syncthreads();
   phase_done(4);
-  eval_ap_tail<JR_THREADS>(sc, ngood, q, ev.ap_q, ev.first, ev.hist);
+  if ((ev.enabled & 16) && tid == 0) {  // row statistics of the timing experiments
+    atomicAdd(ev.status + 16, s_ncand);
+    atomicMax(ev.status + 17, s_ncand);
+    if (s_ncand > JE_CAND) atomicAdd(ev.status + 18, 1);
+    atomicAdd(ev.status + 19, total >> 4);
+    atomicMax(ev.status + 20, total);
+    atomicAdd(ev.status + 21, n);
+  }
+  {
+    const int nc = min(s_ncand, JE_CAND);
+    for (int e = tid; e < nc; e += JR_THREADS) {
+      const int c = cand_col[e];
+      je_column(jr, acci[c], cand_d2[e], c);
+    }
+  }
+  __syncthreads();
   phase_done(5);
+  eval_ap_tail<JR_THREADS>(sc, ngood, q, ev.ap_q, ev.first, ev.hist);
+  phase_done(6);
 }
-
 // ------------------------------------------------------------------------------------ host side
 struct RerankDims {
   int half, wh, cap1, cap2;
@@ -1080,6 +1223,7 @@ static RerankDims rerank_dims(int N, int k1, int k2) {
 struct SparseWs {
   int32_t *rfull, *rfull_cnt, *rhalf, *rhalf_cnt, *v1cols, *v1cnt, *v2cols, *v2cnt, *colcnt, *colptr, *cursor, *inv_row;
   uint32_t* junk32;  // label == -1 bits of the output columns in jaccard_eval_rows_kernel's register layout
+  int32_t *qlist, *qlcnt;  // per output row (query): gallery columns with the query's id (query_lists_kernel)
   float *v1vals, *v2vals, *inv_val;
 };
 
@@ -1106,6 +1250,8 @@ static void carve_sparse(C& c, int N, int k1, int k2, const RerankDims& d, Spars
   t.inv_row = c.template take<int32_t>((size_t)N * d.cap2);
   t.inv_val = c.template take<float>((size_t)N * d.cap2);
   t.junk32 = c.template take<uint32_t>(JR_THREADS);
+  t.qlist = c.template take<int32_t>((size_t)N * QL_STRIDE);
+  t.qlcnt = c.template take<int32_t>(N);
   if (w) *w = t;
 }
 
@@ -1187,14 +1333,19 @@ static int jaccard_sparse_stages(const int32_t* rank, const float* sql2, int64_t
   if (ev && !out && !use_f16 && lambda_value > 0.f && ncols <= JR_PF * JR_THREADS && (col0 & 3) == 0 && (lds & 3) == 0 &&
       ((reinterpret_cast<uintptr_t>(sql2) | reinterpret_cast<uintptr_t>(ev->gl)) & 15) == 0 && !getenv("REIDB200_JR_OLD")) {
     const size_t region = align_up(std::max((size_t)jr_cap * 12 + 16, sizeof(EvalScratch)), 16);
-    const size_t je_smem = (size_t)((ncols + 3) & ~3) * 4 + region + (size_t)JE_GLIST * 4;
+    const size_t je_smem = (size_t)((ncols + 3) & ~3) * 4 + region + (size_t)JE_GLIST * 8 + (size_t)QL_STRIDE * 4;
     if (je_smem <= 232448 - 256) {
       if (const char* dbg = getenv("REIDB200_JE_DEBUG")) evf.enabled |= atoi(dbg) & ~1;  // timing experiments only (wrong results)
       { ProfScope _ps("junk_layout_kernel", st); junk_layout_kernel<<<1, JR_THREADS, 0, st>>>(ev->gl, ncols, w.junk32); }
       RB_LAUNCH_CHECK("junk_layout_kernel");
+      { ProfScope _ps("query_lists_kernel", st); query_lists_kernel<<<ceil_div(nrows, QLK_Q), 256, 0, st>>>(
+          ev->ql, ev->qc, ev->gl, ev->gc, nrows, ncols, w.qlist, w.qlcnt); }
+      RB_LAUNCH_CHECK("query_lists_kernel");
+      JeLists jl;
+      jl.qlist = w.qlist; jl.qlcnt = w.qlcnt; jl.junk32 = w.junk32;
       { ProfScope _ps("jaccard_rows_kernel", st); jaccard_eval_rows_kernel<<<nrows, JR_THREADS, je_smem, st>>>(
           w.v2cols, w.v2vals, w.v2cnt, d.cap2, w.colptr, w.inv_row, w.inv_val, row0, col0, ncols, lambda_value, sql2, lds,
-          (int)region, w.junk32, evf); }
+          (int)region, jl, evf); }
       RB_LAUNCH_CHECK("jaccard_eval_rows_kernel");
       return REIDB200_OK;
     }

@@ -117,7 +117,9 @@ def test_jaccard_other_k_vs_oracle(rb, k1, k2):
     np.testing.assert_allclose(J, Jo, atol=5e-6)
 
 
-@pytest.mark.parametrize("n_ids", [35, 8])  # ~16 good items per query (warp-level AP tail) and ~70 (general tail)
+# ~16 good items per query (warp-level AP tail), ~70 (general tail), ~190 (more items with the query's id than the per-query
+# label lists keep: the row kernel's own label scan)
+@pytest.mark.parametrize("n_ids", [35, 8, 3])
 @pytest.mark.parametrize("lam", [0.3, 0.0])
 def test_fused_rerank_eval_equals_two_calls(rb, lam, n_ids):
     """ops.rerank_eval (evaluation fused into the re-rank kernel) gives the CMC / mAP of jaccard + eval_cmc_map bit for
@@ -125,7 +127,7 @@ def test_fused_rerank_eval_equals_two_calls(rb, lam, n_ids):
     from reidb200 import ops, synth
 
     G, Q = (700 if n_ids == 35 else 701), 130  # 701: the last group of four columns straddles the end of the row
-    d = synth.market_like(Q=Q, G=G, D=64, n_ids=n_ids, seed=31)
+    d = synth.market_like(Q=Q, G=G, D=64, n_ids=n_ids, seed=31, noise=0.6 if n_ids > 3 else 1.5)
     d["gl"][::17] = -1                      # junk gallery rows
     d["ql"][5] = 10 ** 6                    # a query without any good match: the -1 sentinel path
     merged = torch.from_numpy(np.concatenate([d["gf"], d["qf"]], 0)).cuda()
