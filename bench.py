@@ -660,6 +660,10 @@ def run_ours(args):
             os.dup2(saved, 1)
             os.close(saved)
     L.require_device()
+    # pinned staging buffers of the end-to-end path on the NUMA node of this rank's GPU (reidb200/numa.py); --no-numa-bind
+    # leaves the process where the launcher put it
+    from reidb200 import numa
+    numa_info = {"node": None, "bound": False} if args.no_numa_bind else numa.bind_host_to_gpu(local)
 
     def barrier():
         torch.cuda.synchronize()
@@ -817,7 +821,7 @@ def run_ours(args):
         "clocks": clk,
         "e2e": {"value": e2e_value, "unit": "pairs/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
                 "mode": "evaluate.RerankedEvalStream(depth=2): H2D of set i+1 overlaps the kernels of set i",
-                "sync_call_value": e2e_sync_value},
+                "sync_call_value": e2e_sync_value, "host_numa": numa_info},
         "gpu_launches": int(launches),
         "roofline": {"kernel": "gemm_split_tc_kernel", "bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
                      "frac": (achieved / peak) if achieved else None, "traffic": traffic,
@@ -861,6 +865,7 @@ def main():
     ap.add_argument("--no-retrieval", action="store_true")
     ap.add_argument("--no-cpu-rows", action="store_true", help="skip the C1 / C3 / C4 / C5 host baselines (BASELINE.md section 2)")
     ap.add_argument("--no-sharded-rerank", action="store_true")
+    ap.add_argument("--no-numa-bind", action="store_true", help="do not bind the process to its GPU's NUMA node")
     ap.add_argument("--retrieval-gallery", type=int, default=RETR_G)
     args = ap.parse_args()
     if args.impl == "reference":
