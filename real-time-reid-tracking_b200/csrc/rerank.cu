@@ -851,19 +851,43 @@ query_lists_kernel(const int32_t* __restrict__ ql, const int32_t* __restrict__ q
   int32_t ll[QLK_Q];
 #pragma unroll
   for (int x = 0; x < QLK_Q; ++x) ll[x] = s_l[x];
-  for (int j = tid; j < G; j += 256) {
-    const int32_t l = __ldg(gl + j);
+  auto hit = [&](int j, int32_t l) {  // rare: a gallery item with the id of one of the CTA's queries
+    const int32_t c = __ldg(gc + j);
+    for (int x = 0; x < QLK_Q; ++x)
+      if (l == ll[x] && q0 + x < Q) {
+        const int pos = atomicAdd(&s_n[x], 1);
+        if (pos < QL_STRIDE) qlist[(size_t)(q0 + x) * QL_STRIDE + pos] = j | (c == s_c[x] ? (int32_t)0x80000000 : 0);
+      }
+  };
+  auto any_of = [&](int32_t l) {
     bool any = false;
 #pragma unroll
     for (int x = 0; x < QLK_Q; ++x) any |= l == ll[x];
-    if (any) {
-      const int32_t c = __ldg(gc + j);
-      for (int x = 0; x < QLK_Q; ++x)
-        if (l == ll[x] && q0 + x < Q) {
-          const int pos = atomicAdd(&s_n[x], 1);
-          if (pos < QL_STRIDE) qlist[(size_t)(q0 + x) * QL_STRIDE + pos] = j | (c == s_c[x] ? (int32_t)0x80000000 : 0);
-        }
+    return any;
+  };
+  // four labels per load, four loads in flight per thread (the pass is a chain of L2 round trips otherwise)
+  const int G4 = (reinterpret_cast<uintptr_t>(gl) & 15) == 0 ? G >> 2 : 0;
+  constexpr int UL = 4;
+  for (int j0 = tid; j0 < G4; j0 += 256 * UL) {
+    int4 lab[UL];
+#pragma unroll
+    for (int u = 0; u < UL; ++u) {
+      const int j4 = j0 + u * 256;
+      lab[u] = j4 < G4 ? __ldg(reinterpret_cast<const int4*>(gl) + j4) : make_int4(ll[0], ll[0], ll[0], ll[0]);
     }
+#pragma unroll
+    for (int u = 0; u < UL; ++u) {
+      const int j4 = j0 + u * 256;
+      if (j4 >= G4) continue;
+      if (any_of(lab[u].x)) hit(4 * j4, lab[u].x);
+      if (any_of(lab[u].y)) hit(4 * j4 + 1, lab[u].y);
+      if (any_of(lab[u].z)) hit(4 * j4 + 2, lab[u].z);
+      if (any_of(lab[u].w)) hit(4 * j4 + 3, lab[u].w);
+    }
+  }
+  for (int j = 4 * G4 + tid; j < G; j += 256) {
+    const int32_t l = __ldg(gl + j);
+    if (any_of(l)) hit(j, l);
   }
   __syncthreads();
   if (tid < QLK_Q && q0 + tid < Q) qlcnt[q0 + tid] = s_n[tid];
@@ -917,10 +941,15 @@ __global__ void __launch_bounds__(JR_THREADS)
 junk_layout_kernel(const int32_t* __restrict__ gl, int ncols, uint32_t* __restrict__ junk32) {
   const int tid = threadIdx.x;
   uint32_t m = 0;
-  for (int k = 0; k < JR_PF; ++k) {
+  int32_t lab[JR_PF];
+#pragma unroll
+  for (int k = 0; k < JR_PF; ++k) {  // all 32 loads in flight before the first compare
     const int j = 4 * (tid + (k >> 2) * JR_THREADS) + (k & 3);
-    if (j >= ncols || __ldg(gl + j) == -1) m |= 1u << k;
+    lab[k] = j < ncols ? __ldg(gl + j) : -1;
   }
+#pragma unroll
+  for (int k = 0; k < JR_PF; ++k)
+    if (lab[k] == -1) m |= 1u << k;
   junk32[tid] = m;
 }
 
