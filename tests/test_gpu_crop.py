@@ -94,22 +94,25 @@ def test_empty_and_bad_crops(rb):
 
 
 @pytest.mark.parametrize("kernel", ["v3", "v4"])
-def test_cv_linear_kernel_variants_bit_equal(rb, monkeypatch, kernel):
-    """Both crop kernels (thread = output column; thread = four adjacent columns with 128-bit stores and the conversion-free
-    byte -> float step) against the oracle, bit for bit, on a frame that holds every byte value in every channel, crops that
-    are up-scaled, down-scaled, one pixel wide, and clamped at the frame border."""
+@pytest.mark.parametrize("W", [420, 421, 423])
+def test_cv_linear_kernel_variants_bit_equal(rb, monkeypatch, kernel, W):
+    """Both crop kernels (v3: thread = output column; v4, the default: thread = four adjacent columns with 128-bit stores
+    and the conversion-free byte -> float step) against the oracle, bit for bit, on a frame that holds every byte value in
+    every channel, crops that are up-scaled, down-scaled, one pixel wide, and clamped at the frame border, for frame widths
+    whose row stride is and is not a multiple of four bytes."""
     from reidb200 import preprocess as P
 
-    monkeypatch.setenv("REIDB200_CROP_V4" if kernel == "v4" else "REIDB200_CROP_V3", "1")
+    monkeypatch.delenv("REIDB200_CROP_V3", raising=False)
     if kernel == "v3":
-        monkeypatch.delenv("REIDB200_CROP_V4", raising=False)
+        monkeypatch.setenv("REIDB200_CROP_V3", "1")
     rng = np.random.default_rng(11)
-    H, W = 300, 420
+    H = 300
     img = rng.integers(0, 256, (H, W, 3), dtype=np.uint8)
     img[:256, 0, :] = np.arange(256, dtype=np.uint8)[:, None]   # every byte value in every channel
     img[0, :256, 1] = np.arange(256, dtype=np.uint8)
-    boxes = np.array([[0, 0, 1, 256], [0, 0, 256, 1], [0, 0, 420, 300], [17, 9, 145, 265], [100, 50, 131, 120], [3, 7, 303, 290],
-                      [400, 280, 420, 300], [50, 60, 51, 61], [10, 10, 138, 266]], np.int32)
+    boxes = np.array([[0, 0, 1, 256], [0, 0, 256, 1], [0, 0, W, 300], [17, 9, 145, 265], [100, 50, 131, 120], [3, 7, 303, 290],
+                      [W - 20, 280, W, 300], [50, 60, 51, 61], [10, 10, 138, 266], [1, 0, 90, 300], [2, 1, 203, 299],
+                      [W - 7, 0, W, 300]], np.int32)
     got = P.preprocess_frame(img, boxes).cpu().numpy()
     want = O.preprocess_deepsort([img[b[1]:b[3], b[0]:b[2]] for b in boxes])
     assert np.array_equal(got, want)
