@@ -584,10 +584,13 @@ int knn_select_finish(const SelArgs& sel, int m, int n, int k, int kind, const v
   return REIDB200_OK;
 }
 
-// gallery columns per GEMM + select pass: distance block of at most 2^29 floats (2 GiB)
+// gallery columns per GEMM + select pass: distance block of at most 2^31 floats (8 GiB of the 180 GB)
 // (REIDB200_KNN_BLOCK_FLOATS overrides the block size: lets the tests drive the multi-pass merge at small sizes)
+// Measured at 10 k x 4 M x 2048, top-100 (profiles/r02_retrieval_blocks.log): the row select costs a fixed ~0.45 ms per
+// pass over 10 k rows, the GEMM loses DRAM page locality as the rows of its output block move apart --
+//   2 GiB: GEMM 373.8 + select 33.9 = 411.3 ms   8 GiB: 389.4 + 14.4 = 404.8   16 GiB: 395.0 + 11.9 = 407.5   32 GiB: 408.4
 static int knn_chunk_cols(int nq, int nb) {
-  long long block = 1LL << 29;
+  long long block = 1LL << 31;
   if (const char* e = getenv("REIDB200_KNN_BLOCK_FLOATS")) { const long long v = atoll(e); if (v >= 256) block = v; }
   long long c = block / (nq > 0 ? nq : 1);
   c = c / 256 * 256;
