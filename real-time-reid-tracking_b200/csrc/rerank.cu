@@ -853,6 +853,7 @@ query_lists_kernel(const int32_t* __restrict__ ql, const int32_t* __restrict__ q
   for (int x = 0; x < QLK_Q; ++x) ll[x] = s_l[x];
   auto hit = [&](int j, int32_t l) {  // rare: a gallery item with the id of one of the CTA's queries
     const int32_t c = __ldg(gc + j);
+#pragma unroll  // (a dynamic index would move ll[] to local memory for the whole kernel)
     for (int x = 0; x < QLK_Q; ++x)
       if (l == ll[x] && q0 + x < Q) {
         const int pos = atomicAdd(&s_n[x], 1);

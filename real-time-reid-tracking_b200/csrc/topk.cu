@@ -315,6 +315,33 @@ topk_chunk_warp_kernel(const float* __restrict__ vals, int rows, int cols, int64
   int count = 0;
   uint32_t* mk = ckey[warp];
   int32_t* mc = ccol[warp];
+  // The chunks whose minimum passes are first COLLECTED (lane u of `pending` holds the u-th of them), then fetched eight at
+  // a time: the chunk values come from DRAM (the matrix was just written and is larger than L2), and one dependent round
+  // trip per chunk -- ~25 per row -- was most of this kernel's time.
+  int pending = 0, np = 0;
+  auto flush = [&]() {
+    for (int u0 = 0; u0 < np; u0 += 8) {
+      uint32_t key8[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        const int ch = __shfl_sync(0xffffffffu, pending, (u0 + u) & 31);
+        const int col = ch * 32 + lane;
+        key8[u] = (u0 + u < np && col < cols) ? sel_key(__ldg(v + col), descending) : 0xffffffffu;
+      }
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        if (u0 + u >= np) break;  // warp-uniform
+        const int ch = __shfl_sync(0xffffffffu, pending, (u0 + u) & 31);
+        const int col = ch * 32 + lane;
+        const bool take = col < cols && key8[u] <= t0;
+        const uint32_t tb = __ballot_sync(0xffffffffu, take);
+        const int pos = count + __popc(tb & ((1u << lane) - 1));
+        if (take && pos < TW_CAP) { mk[pos] = key8[u]; mc[pos] = col; }
+        count += __popc(tb);
+      }
+    }
+    np = 0;
+  };
   for (int c0 = 0; c0 < nchunks; c0 += 32) {
     const int c = c0 + lane;
     const bool q = c < nchunks && sel_key(__ldg(cr + c), descending) <= t0;
@@ -322,15 +349,11 @@ topk_chunk_warp_kernel(const float* __restrict__ vals, int rows, int cols, int64
     while (todo) {
       const int b = __ffs(todo) - 1;
       todo &= todo - 1;
-      const int col = (c0 + b) * 32 + lane;
-      const uint32_t key = col < cols ? sel_key(__ldg(v + col), descending) : 0xffffffffu;
-      const bool take = col < cols && key <= t0;
-      const uint32_t tb = __ballot_sync(0xffffffffu, take);
-      const int pos = count + __popc(tb & ((1u << lane) - 1));
-      if (take && pos < TW_CAP) { mk[pos] = key; mc[pos] = col; }
-      count += __popc(tb);
+      if (lane == np) pending = c0 + b;
+      if (++np == 32) flush();
     }
   }
+  flush();
   if (count > TW_CAP) {  // hand the row to the exact CTA-per-row kernel
     if (lane == 0) cr[0] = __uint_as_float(TOPK_REDO_FLAG);
     return;
