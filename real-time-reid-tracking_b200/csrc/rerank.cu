@@ -419,7 +419,7 @@ qexpand_kernel(const int32_t* __restrict__ rank, int k1_cols, int k2, const int3
                const float* __restrict__ vvals, const int32_t* __restrict__ vcnt, int cap1, int cap2, int use_f16,
                int32_t* __restrict__ qcols, float* __restrict__ qvals, int32_t* __restrict__ qcnt,
                const int32_t* __restrict__ row_list, const int32_t* __restrict__ row_list_len, int N,
-               int32_t* __restrict__ colcnt) {
+               int32_t* __restrict__ colcnt, int32_t* __restrict__ qrank) {
   extern __shared__ int sm_i[];
   // rows: all of them, or (after qexpand_warp_kernel) the listed ones it left behind
   const int nrows = row_list ? *row_list_len : N;
@@ -483,7 +483,7 @@ qexpand_kernel(const int32_t* __restrict__ rank, int k1_cols, int k2, const int3
       const int slot = head[p];
       qcols[(size_t)i * cap2 + slot] = c;
       qvals[(size_t)i * cap2 + slot] = v;
-      if (colcnt && v != 0.f) atomicAdd(colcnt + c, 1);  // D6 column counts, fused
+      if (colcnt && v != 0.f) qrank[(size_t)i * cap2 + slot] = atomicAdd(colcnt + c, 1);  // D6 column counts, fused: the old value is the entry's place in its column
     }
   }
   if (tid == 0) qcnt[i] = nu;
@@ -500,7 +500,8 @@ __global__ void __launch_bounds__(QEW_WARPS * 32)
 qexpand_warp_kernel(const int32_t* __restrict__ rank, int k1_cols, int k2, const int32_t* __restrict__ vcols,
                     const float* __restrict__ vvals, const int32_t* __restrict__ vcnt, int N, int cap1, int cap2,
                     int use_f16, int32_t* __restrict__ qcols, float* __restrict__ qvals, int32_t* __restrict__ qcnt,
-                    int32_t* __restrict__ colcnt, int32_t* __restrict__ long_list, int32_t* __restrict__ long_len) {
+                    int32_t* __restrict__ colcnt, int32_t* __restrict__ qrank, int32_t* __restrict__ long_list,
+                    int32_t* __restrict__ long_len) {
   __shared__ int s_row[QEW_WARPS][32], s_off[QEW_WARPS][33];
   __shared__ uint32_t s_key[QEW_WARPS][256];
   __shared__ float s_val[QEW_WARPS][256];
@@ -564,7 +565,7 @@ qexpand_warp_kernel(const int32_t* __restrict__ rank, int k1_cols, int k2, const
       if (use_f16) val = __half2float(__float2half_rn(val));
       qcols[(size_t)i * cap2 + slot] = (int32_t)c;
       qvals[(size_t)i * cap2 + slot] = val;
-      if (colcnt && val != 0.f) atomicAdd(colcnt + c, 1);  // D6 column counts, fused
+      if (colcnt && val != 0.f) qrank[(size_t)i * cap2 + slot] = atomicAdd(colcnt + c, 1);  // D6 column counts, fused: the old value is the entry's place in its column
       ++slot;
     }
   if (lane == 0) qcnt[i] = nu;
@@ -572,11 +573,12 @@ qexpand_warp_kernel(const int32_t* __restrict__ rank, int k1_cols, int k2, const
 
 // ------------------------------------------------------------------------------------ D6
 __global__ void inv_count_kernel(const int32_t* __restrict__ cols, const float* __restrict__ vals,
-                                 const int32_t* __restrict__ cnt, int N, int cap, int32_t* __restrict__ colcnt) {
+                                 const int32_t* __restrict__ cnt, int N, int cap, int32_t* __restrict__ colcnt,
+                                 int32_t* __restrict__ qrank) {
   const int i = blockIdx.x;
   const int n = cnt[i];
   for (int t = threadIdx.x; t < n; t += blockDim.x)
-    if (vals[(size_t)i * cap + t] != 0.f) atomicAdd(colcnt + cols[(size_t)i * cap + t], 1);
+    if (vals[(size_t)i * cap + t] != 0.f) qrank[(size_t)i * cap + t] = atomicAdd(colcnt + cols[(size_t)i * cap + t], 1);
 }
 
 // colptr[0..N] = exclusive scan of colcnt; cursor = copy of colptr.  Single CTA; dynamic smem: N ints.
@@ -589,18 +591,34 @@ inv_scan_kernel(const int32_t* __restrict__ colcnt, int N, int32_t* __restrict__
   if (threadIdx.x == 0) colptr[N] = total;
 }
 
-__global__ void inv_fill_kernel(const int32_t* __restrict__ cols, const float* __restrict__ vals,
-                                const int32_t* __restrict__ cnt, int N, int cap, int32_t* __restrict__ cursor,
-                                int32_t* __restrict__ inv_row, float* __restrict__ inv_val) {
-  const int i = blockIdx.x;
+// Warp per row, four entries per lane in flight.  An entry's place in its column was fixed when the column was counted
+// (qrank = the return value of that atomic), so the fill is loads and stores only: with a cursor atomic per entry (CTA per
+// row) it ran at 7 % issue activity behind ~100 stalled warps per issue and the atomics' throttle (ncu, hard data).
+// The order inside an inverted list is whatever the counting atomics made it; its consumer sums order-independently.
+constexpr int IF_WARPS = 8;
+__global__ void __launch_bounds__(IF_WARPS * 32)
+inv_fill_kernel(const int32_t* __restrict__ cols, const float* __restrict__ vals, const int32_t* __restrict__ cnt,
+                const int32_t* __restrict__ qrank, int N, int cap, const int32_t* __restrict__ colptr,
+                int32_t* __restrict__ inv_row, float* __restrict__ inv_val) {
+  const int i = blockIdx.x * IF_WARPS + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+  if (i >= N) return;
   const int n = cnt[i];
-  for (int t = threadIdx.x; t < n; t += blockDim.x) {
-    const float v = vals[(size_t)i * cap + t];
-    if (v != 0.f) {
-      const int p = atomicAdd(cursor + cols[(size_t)i * cap + t], 1);
-      inv_row[p] = i;
-      inv_val[p] = v;
+  constexpr int U = 4;
+  for (int t0 = lane; t0 < n; t0 += 32 * U) {
+    float v[U];
+    int c[U], r[U], p[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int t = t0 + 32 * u;
+      v[u] = t < n ? vals[(size_t)i * cap + t] : 0.f;
+      c[u] = t < n ? cols[(size_t)i * cap + t] : 0;
+      r[u] = t < n ? qrank[(size_t)i * cap + t] : 0;
     }
+#pragma unroll
+    for (int u = 0; u < U; ++u) p[u] = v[u] != 0.f ? __ldg(colptr + c[u]) + r[u] : -1;
+#pragma unroll
+    for (int u = 0; u < U; ++u)
+      if (p[u] >= 0) { inv_row[p[u]] = i; inv_val[p[u]] = v[u]; }
   }
 }
 
@@ -837,6 +855,18 @@ constexpr int JE_CAND = EV_GOOD_CAP;  // candidate columns staged per row (more:
 // (junk) and clear when it differs (a good item).  Eight queries per CTA share one pass over the label vector.
 // qlcnt[q] may exceed QL_STRIDE: the row kernel then scans the labels itself.
 constexpr int QLK_Q = 8;
+// rare path, out of line on purpose: inlined at its 17 call sites the kernel did not fit the instruction cache
+// (ncu: 28 stalled warps per issue waiting for instructions, 55 us for 0.2 MB of labels)
+static __device__ __noinline__ void ql_hit(int j, int32_t l, const int32_t* s_l, const int32_t* s_c, int* s_n, int q0, int Q,
+                                           const int32_t* __restrict__ gc, int32_t* __restrict__ qlist) {
+  const int32_t c = __ldg(gc + j);
+  for (int x = 0; x < QLK_Q; ++x)
+    if (l == s_l[x] && q0 + x < Q) {
+      const int pos = atomicAdd(&s_n[x], 1);
+      if (pos < QL_STRIDE) qlist[(size_t)(q0 + x) * QL_STRIDE + pos] = j | (c == s_c[x] ? (int32_t)0x80000000 : 0);
+    }
+}
+
 __global__ void __launch_bounds__(256)
 query_lists_kernel(const int32_t* __restrict__ ql, const int32_t* __restrict__ qc, const int32_t* __restrict__ gl,
                    const int32_t* __restrict__ gc, int Q, int G, int32_t* __restrict__ qlist, int32_t* __restrict__ qlcnt) {
@@ -851,15 +881,7 @@ query_lists_kernel(const int32_t* __restrict__ ql, const int32_t* __restrict__ q
   int32_t ll[QLK_Q];
 #pragma unroll
   for (int x = 0; x < QLK_Q; ++x) ll[x] = s_l[x];
-  auto hit = [&](int j, int32_t l) {  // rare: a gallery item with the id of one of the CTA's queries
-    const int32_t c = __ldg(gc + j);
-#pragma unroll  // (a dynamic index would move ll[] to local memory for the whole kernel)
-    for (int x = 0; x < QLK_Q; ++x)
-      if (l == ll[x] && q0 + x < Q) {
-        const int pos = atomicAdd(&s_n[x], 1);
-        if (pos < QL_STRIDE) qlist[(size_t)(q0 + x) * QL_STRIDE + pos] = j | (c == s_c[x] ? (int32_t)0x80000000 : 0);
-      }
-  };
+  auto hit = [&](int j, int32_t l) { ql_hit(j, l, s_l, s_c, s_n, q0, Q, gc, qlist); };
   auto any_of = [&](int32_t l) {
     bool any = false;
 #pragma unroll
@@ -1254,6 +1276,7 @@ struct SparseWs {
   int32_t *rfull, *rfull_cnt, *rhalf, *rhalf_cnt, *v1cols, *v1cnt, *v2cols, *v2cnt, *colcnt, *colptr, *cursor, *inv_row;
   uint32_t* junk32;  // label == -1 bits of the output columns in jaccard_eval_rows_kernel's register layout
   int32_t *qlist, *qlcnt;  // per output row (query): gallery columns with the query's id (query_lists_kernel)
+  int32_t* qrank;          // place of every V_qe entry inside its column of the inverted index
   float *v1vals, *v2vals, *inv_val;
 };
 
@@ -1282,6 +1305,7 @@ static void carve_sparse(C& c, int N, int k1, int k2, const RerankDims& d, Spars
   t.junk32 = c.template take<uint32_t>(JR_THREADS);
   t.qlist = c.template take<int32_t>((size_t)N * QL_STRIDE);
   t.qlcnt = c.template take<int32_t>(N);
+  t.qrank = c.template take<int32_t>((size_t)N * d.cap2);
   if (w) *w = t;
 }
 
@@ -1336,19 +1360,19 @@ static int jaccard_sparse_stages(const int32_t* rank, const float* sql2, int64_t
     // D5 + the column counts of D6: warp kernel first, the CTA kernel picks up the rows it marked as too long
     { ProfScope _ps("qexpand_kernel", st); qexpand_warp_kernel<<<ceil_div(N, QEW_WARPS), QEW_WARPS * 32, 0, st>>>(
         rank, k1, k2, w.v1cols, w.v1vals, w.v1cnt, N, d.cap1, d.cap2, use_f16, w.v2cols, w.v2vals, w.v2cnt, w.colcnt,
-        w.cursor, w.colcnt + N + 1); }  // the cursor array is free until inv_scan_kernel: it holds the long-row list
+        w.qrank, w.cursor, w.colcnt + N + 1); }  // the cursor array is free until inv_scan_kernel: it holds the long-row list
     RB_LAUNCH_CHECK("qexpand_warp_kernel");
     { ProfScope _ps("qexpand_kernel(long rows)", st); qexpand_kernel<<<min(N, 2 * num_sms()), QE_THREADS, (size_t)d.cap2 * 12, st>>>(
         rank, k1, k2, w.v1cols, w.v1vals, w.v1cnt, d.cap1, d.cap2, use_f16, w.v2cols, w.v2vals, w.v2cnt, w.cursor, w.colcnt + N + 1, N,
-        w.colcnt); }
+        w.colcnt, w.qrank); }
     RB_LAUNCH_CHECK("qexpand_kernel");
   } else {
-    { ProfScope _ps("inv_count_kernel", st); inv_count_kernel<<<N, 128, 0, st>>>(w.v2cols, w.v2vals, w.v2cnt, N, d.cap2, w.colcnt); }
+    { ProfScope _ps("inv_count_kernel", st); inv_count_kernel<<<N, 128, 0, st>>>(w.v2cols, w.v2vals, w.v2cnt, N, d.cap2, w.colcnt, w.qrank); }
     RB_LAUNCH_CHECK("inv_count_kernel");
   }
   { ProfScope _ps("inv_scan_kernel", st); inv_scan_kernel<<<1, 1024, (size_t)N * sizeof(int), st>>>(w.colcnt, N, w.colptr, w.cursor); }
   RB_LAUNCH_CHECK("inv_scan_kernel");
-  { ProfScope _ps("inv_fill_kernel", st); inv_fill_kernel<<<N, 128, 0, st>>>(w.v2cols, w.v2vals, w.v2cnt, N, d.cap2, w.cursor, w.inv_row, w.inv_val); }
+  { ProfScope _ps("inv_fill_kernel", st); inv_fill_kernel<<<ceil_div(N, IF_WARPS), IF_WARPS * 32, 0, st>>>(w.v2cols, w.v2vals, w.v2cnt, w.qrank, N, d.cap2, w.colptr, w.inv_row, w.inv_val); }
   RB_LAUNCH_CHECK("inv_fill_kernel");
   const int jr_cap = k2 > 1 ? d.cap2 : d.cap1;
   EvalFuse evf;

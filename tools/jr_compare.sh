@@ -11,5 +11,6 @@ d = json.loads(sys.stdin.read().strip().splitlines()[-1])
 sh = d['kernel_share_of_step']; ev = d['ms_per_step_with_kernel_events']
 print('ms_per_step', round(d['ms_per_step'], 4), 'easy', round(d['survey_recipe']['ms_per_step'], 4), 'jaccard_rows_ms', round(sh['jaccard_rows_kernel'] * ev, 4), 'gemm_ms', round(sh['gemm_split_tc_kernel'] * ev, 4))
 print('result', d['result'], d['survey_recipe']['result'])
+print({k: round(v * ev * 1000, 1) for k, v in sh.items()})
 "
 done 2>&1 | tee gpurun_out/jr_compare.log
