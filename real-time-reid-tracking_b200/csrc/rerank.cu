@@ -13,6 +13,8 @@
 #include <stdlib.h>
 
 #include <algorithm>
+#include <mutex>
+#include <vector>
 #include "evalmap.cuh"
 #include "gemm.cuh"
 
@@ -1327,6 +1329,37 @@ static int rerank_check(int N, int k1, int k2, const RerankDims& d) {
 
 static size_t jaccard_rows_smem(int N, int cap) { return (size_t)((N + 3) & ~3) * 4 + (size_t)cap * 12 + 16; }
 
+// A second stream per caller stream for work that depends on the caller's INPUTS only (the label lists of the fused
+// evaluation): forked from `st` by an event, joined back by another, so it runs beside the sparse stages -- also inside a
+// CUDA graph capture of `st`, where the two events become the fork and join edges of the graph.
+struct SideLane {
+  cudaStream_t owner, side;
+  cudaEvent_t fork, join;
+};
+
+static SideLane* side_lane(cudaStream_t st) {
+  static std::mutex mu;
+  static std::vector<SideLane*> lanes;
+  std::lock_guard<std::mutex> lock(mu);
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) return nullptr;
+  // (stream handles are per device, and the default stream exists on every device: lanes are keyed by (device, stream))
+  static std::vector<int> lane_dev;
+  for (size_t i = 0; i < lanes.size(); ++i)
+    if (lanes[i]->owner == st && lane_dev[i] == dev) return lanes[i];
+  SideLane* l = new SideLane();
+  l->owner = st;
+  if (cudaStreamCreateWithFlags(&l->side, cudaStreamNonBlocking) != cudaSuccess ||
+      cudaEventCreateWithFlags(&l->fork, cudaEventDisableTiming) != cudaSuccess ||
+      cudaEventCreateWithFlags(&l->join, cudaEventDisableTiming) != cudaSuccess) {
+    delete l;
+    return nullptr;
+  }
+  lanes.push_back(l);
+  lane_dev.push_back(dev);
+  return l;
+}
+
 // `sql2` (row stride lds) is read by the lambda blend only, for the output region; `src` says where the expansion's pair
 // values come from (PairSrc)
 static int jaccard_sparse_stages(const int32_t* rank, const float* sql2, int64_t lds, const float* sqnorm, int N, int k1,
@@ -1340,6 +1373,30 @@ static int jaccard_sparse_stages(const int32_t* rank, const float* sql2, int64_t
     RB_CUDA(cudaFuncSetAttribute(inv_scan_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448 - 256));
     RB_CUDA(cudaFuncSetAttribute(jaccard_rows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448 - 256));
     RB_CUDA(cudaFuncSetAttribute(jaccard_eval_rows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448 - 256));
+  }
+  // evaluation only (nothing stored, fp32, blended, 128-bit aligned row slices): the kernel built for it, and its label
+  // lists -- which need the labels only -- on the side lane, beside the sparse stages
+  const int jr_cap = k2 > 1 ? d.cap2 : d.cap1;
+  const size_t je_region = align_up(std::max((size_t)jr_cap * 12 + 16, sizeof(EvalScratch)), 16);
+  const size_t je_smem = (size_t)((ncols + 3) & ~3) * 4 + je_region + (size_t)JE_GLIST * 8 + (size_t)QL_STRIDE * 4;
+  const bool eval_kernel = ev && !out && !use_f16 && lambda_value > 0.f && ncols <= JR_PF * JR_THREADS && (col0 & 3) == 0 &&
+                           (lds & 3) == 0 && ((reinterpret_cast<uintptr_t>(sql2) | reinterpret_cast<uintptr_t>(ev->gl)) & 15) == 0 &&
+                           je_smem <= 232448 - 256 && !getenv("REIDB200_JR_OLD");
+  SideLane* lane = nullptr;
+  if (eval_kernel) {
+    lane = getenv("REIDB200_NO_SIDE_LANE") ? nullptr : side_lane(st);
+    cudaStream_t ls = st;
+    if (lane) {
+      RB_CUDA(cudaEventRecord(lane->fork, st));
+      RB_CUDA(cudaStreamWaitEvent(lane->side, lane->fork, 0));
+      ls = lane->side;
+    }
+    { ProfScope _ps("junk_layout_kernel", ls); junk_layout_kernel<<<1, JR_THREADS, 0, ls>>>(ev->gl, ncols, w.junk32); }
+    RB_LAUNCH_CHECK("junk_layout_kernel");
+    { ProfScope _ps("query_lists_kernel", ls); query_lists_kernel<<<ceil_div(nrows, QLK_Q), 256, 0, ls>>>(
+        ev->ql, ev->qc, ev->gl, ev->gc, nrows, ncols, w.qlist, w.qlcnt); }
+    RB_LAUNCH_CHECK("query_lists_kernel");
+    if (lane) RB_CUDA(cudaEventRecord(lane->join, ls));
   }
   const int wpb = 8;
   { ProfScope _ps("krecip_kernel", st); krecip_both_kernel<<<ceil_div(N, wpb), wpb * 32, 0, st>>>(rank, N, k1, k1, d.wh, w.rfull, w.rfull_cnt, w.rhalf, w.rhalf_cnt); }
@@ -1374,7 +1431,6 @@ static int jaccard_sparse_stages(const int32_t* rank, const float* sql2, int64_t
   RB_LAUNCH_CHECK("inv_scan_kernel");
   { ProfScope _ps("inv_fill_kernel", st); inv_fill_kernel<<<ceil_div(N, IF_WARPS), IF_WARPS * 32, 0, st>>>(w.v2cols, w.v2vals, w.v2cnt, w.qrank, N, d.cap2, w.colptr, w.inv_row, w.inv_val); }
   RB_LAUNCH_CHECK("inv_fill_kernel");
-  const int jr_cap = k2 > 1 ? d.cap2 : d.cap1;
   EvalFuse evf;
   memset(&evf, 0, sizeof(evf));
   size_t jr_smem = jaccard_rows_smem(N, jr_cap);
@@ -1383,26 +1439,16 @@ static int jaccard_sparse_stages(const int32_t* rank, const float* sql2, int64_t
     evf.enabled = 1;
     if (jr_smem < sizeof(EvalScratch) + 16) jr_smem = sizeof(EvalScratch) + 16;
   }
-  // evaluation only (nothing stored, fp32, blended, 128-bit aligned row slices): the kernel built for it
-  if (ev && !out && !use_f16 && lambda_value > 0.f && ncols <= JR_PF * JR_THREADS && (col0 & 3) == 0 && (lds & 3) == 0 &&
-      ((reinterpret_cast<uintptr_t>(sql2) | reinterpret_cast<uintptr_t>(ev->gl)) & 15) == 0 && !getenv("REIDB200_JR_OLD")) {
-    const size_t region = align_up(std::max((size_t)jr_cap * 12 + 16, sizeof(EvalScratch)), 16);
-    const size_t je_smem = (size_t)((ncols + 3) & ~3) * 4 + region + (size_t)JE_GLIST * 8 + (size_t)QL_STRIDE * 4;
-    if (je_smem <= 232448 - 256) {
-      if (const char* dbg = getenv("REIDB200_JE_DEBUG")) evf.enabled |= atoi(dbg) & ~1;  // timing experiments only (wrong results)
-      { ProfScope _ps("junk_layout_kernel", st); junk_layout_kernel<<<1, JR_THREADS, 0, st>>>(ev->gl, ncols, w.junk32); }
-      RB_LAUNCH_CHECK("junk_layout_kernel");
-      { ProfScope _ps("query_lists_kernel", st); query_lists_kernel<<<ceil_div(nrows, QLK_Q), 256, 0, st>>>(
-          ev->ql, ev->qc, ev->gl, ev->gc, nrows, ncols, w.qlist, w.qlcnt); }
-      RB_LAUNCH_CHECK("query_lists_kernel");
-      JeLists jl;
-      jl.qlist = w.qlist; jl.qlcnt = w.qlcnt; jl.junk32 = w.junk32;
-      { ProfScope _ps("jaccard_rows_kernel", st); jaccard_eval_rows_kernel<<<nrows, JR_THREADS, je_smem, st>>>(
-          w.v2cols, w.v2vals, w.v2cnt, d.cap2, w.colptr, w.inv_row, w.inv_val, row0, col0, ncols, lambda_value, sql2, lds,
-          (int)region, jl, evf); }
-      RB_LAUNCH_CHECK("jaccard_eval_rows_kernel");
-      return REIDB200_OK;
-    }
+  if (eval_kernel) {
+    if (const char* dbg = getenv("REIDB200_JE_DEBUG")) evf.enabled |= atoi(dbg) & ~1;  // timing experiments only (wrong results)
+    if (lane) RB_CUDA(cudaStreamWaitEvent(st, lane->join, 0));
+    JeLists jl;
+    jl.qlist = w.qlist; jl.qlcnt = w.qlcnt; jl.junk32 = w.junk32;
+    { ProfScope _ps("jaccard_rows_kernel", st); jaccard_eval_rows_kernel<<<nrows, JR_THREADS, je_smem, st>>>(
+        w.v2cols, w.v2vals, w.v2cnt, d.cap2, w.colptr, w.inv_row, w.inv_val, row0, col0, ncols, lambda_value, sql2, lds,
+        (int)je_region, jl, evf); }
+    RB_LAUNCH_CHECK("jaccard_eval_rows_kernel");
+    return REIDB200_OK;
   }
   { ProfScope _ps("jaccard_rows_kernel", st); jaccard_rows_kernel<<<nrows, JR_THREADS, jr_smem, st>>>(
       w.v2cols, w.v2vals, w.v2cnt, d.cap2, w.colptr, w.inv_row, w.inv_val, N, row0, col0, ncols, lambda_value, sql2, lds,
