@@ -204,7 +204,9 @@ def bench_assoc(steps, warmup):
         conf = np.arange(T) % 7 != 0
         margs = (metric, det_feat, fr["det_tlwh"], np.arange(T), conf, fr["trk_mean"], fr["trk_SI"], fr["trk_tsu"], 0.995, 0.7, 0.2)
         match_us = {}
-        for tag, dl in (("host_lap", False), ("device_lap", True)):
+        # device_lap = exact mode (scipy's own assignment, ties and list orders included: one warp runs _lsap.cpp on the whole
+        # clamped matrix); device_lap_fast = the component-parallel solver (same matches, unmatched detections ascending)
+        for tag, dl in (("host_lap", False), ("device_lap", True), ("device_lap_fast", "fast")):
             for _ in range(3):
                 res = tracker.match_arrays(*margs, device_lap=dl)
             t0 = time.perf_counter()
@@ -212,13 +214,15 @@ def bench_assoc(steps, warmup):
                 res = tracker.match_arrays(*margs, device_lap=dl)
             match_us[tag] = (time.perf_counter() - t0) / n * 1e6
             match_us[tag + "_matches"] = len(res[0])
-        L.profile_enable(True)
-        for _ in range(20):
-            tracker.match_arrays(*margs, device_lap=True)
-        torch.cuda.synchronize()
-        lp = L.profile_read()
-        L.profile_enable(False)
-        match_us["lap_kernels_us"] = sum(lp[k][1] for k in ("lap_components_kernel", "lap_solve_kernel") if k in lp) / 20 * 1e3
+        for dl, key, names in ((True, "lap_exact_kernels_us", ("lap_exact_kernel",)),
+                               ("fast", "lap_kernels_us", ("lap_components_kernel", "lap_solve_kernel"))):
+            L.profile_enable(True)
+            for _ in range(20):
+                tracker.match_arrays(*margs, device_lap=dl)
+            torch.cuda.synchronize()
+            lp = L.profile_read()
+            L.profile_enable(False)
+            match_us[key] = sum(lp[k][1] for k in names if k in lp) / 20 * 1e3
         crop_us = prof["crop_cv_linear_kernel"][1] / prof["crop_cv_linear_kernel"][0] * 1e3
         assoc_us = prof["assoc_frame_kernel"][1] / prof["assoc_frame_kernel"][0] * 1e3
         crop_bytes = len(xyxy) * 3 * 256 * 128 * 4 + int((geom[:, 0].astype(np.int64) * geom[:, 1] * 3).sum())

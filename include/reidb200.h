@@ -393,6 +393,18 @@ int reidb200_center_columns(const float* x, int rows, int D, size_t ldx, float* 
 size_t reidb200_lap_workspace_bytes(int T, int M);
 int reidb200_lap_gated(const double* cost, int T, int M, size_t ld, const int32_t* row_cand, int nrc, double max_distance,
                        int32_t* match_col_of_row, int32_t* det_matched, int32_t* status, void* ws, size_t ws_bytes, void* stream);
+/* Exact mode: the assignment scipy.optimize.linear_sum_assignment returns for the clamped matrix of the candidate rows x
+ * candidate columns, TIES INCLUDED (one warp runs _lsap.cpp statement by statement), and with it the reference's
+ * `unmatched_detections` list in the reference's order (linear_assignment.py:61-76: the pairs scipy forms through gated
+ * entries decide where a detection lands in that list, hence which id a new track gets, tracker.py:175-233).
+ *   row_cand i32[nrc]: rows in the reference's track_indices order (rows already matched are skipped)
+ *   col_cand i32[<= max_cols], col_count i32[1] or NULL: columns in the reference's detection_indices order (device list +
+ *   device count, so that the list one solve writes feeds the next without a host round trip)
+ *   um_dets i32[>= max_cols], um_count i32[1]: out.  Matches go to match_col_of_row / det_matched like lap_gated. */
+int reidb200_lap_exact(const double* cost, int T, int M, size_t ld, const int32_t* row_cand, int nrc,
+                       const int32_t* col_cand, const int32_t* col_count, int max_cols, double max_distance,
+                       int32_t* match_col_of_row, int32_t* det_matched, int32_t* um_dets, int32_t* um_count,
+                       int32_t* status, void* stream);
 
 #ifdef __cplusplus
 }

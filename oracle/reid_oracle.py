@@ -862,3 +862,94 @@ def diminish_camera_bias(embeddings: np.ndarray, cams: np.ndarray, la: float = 0
         nrm = np.sqrt((y * y).sum(1, dtype=np.float32, keepdims=True))
         e[m] = y / nrm
     return e
+
+
+# ----------------------------------------------------------------------------------------- scipy's assignment, ties included
+def lsap_scipy_order(cost):
+    """(row_ind, col_ind) exactly as scipy.optimize.linear_sum_assignment returns them, INCLUDING its choice between
+    assignments of equal cost -- a statement-by-statement restatement of scipy/optimize/rectangular_lsap/
+    rectangular_lsap.cpp (Crouse's shortest augmenting path; scipy is an un-vendored dependency of the reference:
+    boxmot/trackers/strongsort/sort/linear_assignment.py:4,60).  The reference's unmatched lists inherit their order from
+    these ties (every gated entry costs max_distance + 1e-5), so the device solver's exact mode follows this function;
+    tests/test_oracle.py pins it against scipy itself on tie-heavy matrices."""
+    cost = np.asarray(cost, dtype=np.float64)
+    nr, nc = cost.shape
+    tr = nc < nr
+    if tr:
+        cost = np.ascontiguousarray(cost.T)
+        nr, nc = nc, nr
+    u, v = np.zeros(nr), np.zeros(nc)
+    col4row, row4col = -np.ones(nr, np.int64), -np.ones(nc, np.int64)
+    for cur in range(nr):
+        sp = np.full(nc, np.inf)
+        path = -np.ones(nc, np.int64)
+        SR, SC = np.zeros(nr, bool), np.zeros(nc, bool)
+        remaining = [nc - it - 1 for it in range(nc)]
+        num_remaining, sink, i, min_val = nc, -1, cur, 0.0
+        while sink == -1:
+            index, lowest = -1, np.inf
+            SR[i] = True
+            for it in range(num_remaining):
+                j = remaining[it]
+                r = min_val + cost[i, j] - u[i] - v[j]
+                if r < sp[j]:
+                    path[j] = i
+                    sp[j] = r
+                if sp[j] < lowest or (sp[j] == lowest and row4col[j] == -1):
+                    lowest = sp[j]
+                    index = it
+            min_val = lowest
+            if min_val == np.inf:
+                raise ValueError("cost matrix is infeasible")
+            j = remaining[index]
+            if row4col[j] == -1:
+                sink = j
+            else:
+                i = row4col[j]
+            SC[j] = True
+            num_remaining -= 1
+            remaining[index] = remaining[num_remaining]
+        u[cur] += min_val
+        for i2 in range(nr):
+            if SR[i2] and i2 != cur:
+                u[i2] += min_val - sp[col4row[i2]]
+        for j2 in range(nc):
+            if SC[j2]:
+                v[j2] -= min_val - sp[j2]
+        j = sink
+        while True:
+            i2 = path[j]
+            row4col[j] = i2
+            col4row[i2], j = j, col4row[i2]
+            if i2 == cur:
+                break
+    if tr:
+        order = np.argsort(col4row)
+        return col4row[order], np.arange(nr)[order]
+    return np.arange(nr), col4row
+
+
+def min_cost_matching_lists(cost, max_distance, track_indices, detection_indices, solver=None):
+    """linear_assignment.py:52-77 on a ready cost matrix: (matches, unmatched_tracks, unmatched_detections) in the
+    reference's order.  solver = scipy's linear_sum_assignment by default, lsap_scipy_order for the restatement."""
+    if solver is None:
+        from scipy.optimize import linear_sum_assignment as solver
+    if len(detection_indices) == 0 or len(track_indices) == 0:
+        return [], list(track_indices), list(detection_indices)
+    c = np.array(cost, dtype=np.float64, copy=True)
+    c[c > max_distance] = max_distance + 1e-5
+    rows, cols = solver(c)
+    matches, um_t, um_d = [], [], []
+    for col, d in enumerate(detection_indices):
+        if col not in cols:
+            um_d.append(d)
+    for row, t in enumerate(track_indices):
+        if row not in rows:
+            um_t.append(t)
+    for row, col in zip(rows, cols):
+        if c[row, col] > max_distance:
+            um_t.append(track_indices[row])
+            um_d.append(detection_indices[col])
+        else:
+            matches.append((track_indices[row], detection_indices[col]))
+    return matches, um_t, um_d

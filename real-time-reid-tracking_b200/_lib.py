@@ -13,7 +13,7 @@ import torch
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libreidb200.so")
-ABI_VERSION = 7
+ABI_VERSION = 8
 
 OK, EINVAL, ECUDA, ELIMIT = 0, -1, -2, -3
 RESIZE_CV_LINEAR, RESIZE_PIL_ANTIALIAS = 0, 1
@@ -91,6 +91,7 @@ SIGNATURES = {
     "reidb200_center_columns": (_i, [_vp, _i, _i, _sz, _vp, _sz, _vp, _vp]),
     "reidb200_lap_workspace_bytes": (_sz, [_i, _i]),
     "reidb200_lap_gated": (_i, [_vp, _i, _i, _sz, _vp, _i, _d, _vp, _vp, _vp, _vp, _sz, _vp]),
+    "reidb200_lap_exact": (_i, [_vp, _i, _i, _sz, _vp, _i, _vp, _vp, _i, _d, _vp, _vp, _vp, _vp, _vp, _vp]),
 }
 
 _lib = None

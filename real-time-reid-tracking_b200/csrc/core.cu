@@ -28,7 +28,7 @@ int num_sms() {
 
 extern "C" const char* reidb200_last_error(void) { return reidb200::g_err; }
 
-extern "C" int reidb200_abi_version(void) { return 7; }
+extern "C" int reidb200_abi_version(void) { return 8; }
 
 extern "C" int reidb200_check_device(void) {
   int dev = 0;

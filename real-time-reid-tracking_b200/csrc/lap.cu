@@ -301,6 +301,264 @@ lap_solve_kernel(const double* __restrict__ cost, size_t ld, double max_distance
   }
 }
 
+// ------------------------------------------------------------------------------------ exact mode
+// The SAME assignment scipy returns, ties included -- and with it the ORDER of the reference's unmatched lists (the pairs
+// scipy forms through gated entries, all of equal cost, decide where a detection lands in `unmatched_detections`, hence
+// which id a new track gets: linear_assignment.py:58-77, tracker.py:175-233).  One warp runs scipy's _lsap.cpp on the whole
+// clamped matrix of the candidate rows x candidate columns, statement by statement:
+//   * the smaller side is augmented (scipy transposes when there are more rows than columns);
+//   * reduced costs as ((min_val + c) - u[i]) - v[j] in float64;
+//   * the scan runs over `remaining` (columns not yet in the tree: filled in DESCENDING column order at the start of every
+//     augmentation, a visited column replaced by the last one) and resolves equal shortest-path costs the way the scalar
+//     loop does: the LAST unassigned column of the scan if there is one, else the FIRST column of the scan.
+// The sequential part never waits for global memory: the whole CTA first gathers the ADMISSIBLE entries (cost <=
+// max_distance; everything else costs the same constant) into a CSR by augmented-side row in shared memory; a step of the
+// search drops the current row's few entries into a dense row of constants, scans it, and takes them out again.  (When the
+// admissible entries do not fit, the scan reads the matrix directly.)
+// Checked against scipy on tie-heavy matrices: oracle/reid_oracle.py::lsap_scipy_order (CPU), tests/test_gpu_lap.py.
+constexpr int LX_THREADS = 256;
+
+struct LxSmem {  // sizes of the dynamic shared-memory tables, computed on the host
+  int side, cap;
+};
+
+__global__ void __launch_bounds__(LX_THREADS)
+lap_exact_kernel(const double* __restrict__ cost, size_t ld, const int32_t* __restrict__ row_cand, int nrc,
+                 const int32_t* __restrict__ col_cand, const int32_t* __restrict__ col_count, int max_cols, double max_distance,
+                 int32_t* __restrict__ match_col_of_row, int32_t* __restrict__ det_matched, int32_t* __restrict__ um_dets,
+                 int32_t* __restrict__ um_count, int32_t* __restrict__ status, LxSmem lay) {
+  extern __shared__ __align__(16) unsigned char lx_smem[];
+  __shared__ int s_nr, s_nc, s_total;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int ncc = min(col_count ? col_count[0] : max_cols, max_cols);
+  const int side = lay.side, cap = lay.cap;
+  double* u = reinterpret_cast<double*>(lx_smem);
+  double* v = u + side;
+  double* sp = v + side;
+  double* rowval = sp + side;
+  double* csr_val = rowval + side;
+  double* trip_val = csr_val + cap;
+  int32_t* path = reinterpret_cast<int32_t*>(trip_val + cap);
+  int32_t* a4b = path + side;
+  int32_t* b4a = a4b + side;
+  int32_t* remaining = b4a + side;
+  int32_t* R = remaining + side;
+  int32_t* C = R + side;
+  int32_t* off = C + side;          // [side + 1]
+  int32_t* fillc = off + side + 1;  // [side]
+  int32_t* stamp = fillc + side;    // [side] id of the step that wrote rowval[b] last
+  int32_t* csr_col = stamp + side;  // [cap]
+  int32_t* trip_a = csr_col + cap;  // [cap]
+  int32_t* trip_b = trip_a + cap;   // [cap]
+  unsigned char* SR = reinterpret_cast<unsigned char*>(trip_b + cap);
+  unsigned char* SC = SR + side;
+
+  // ---- candidate rows / columns still unmatched, in the order given (warp 0)
+  if (warp == 0) {
+    int nr = 0, nc = 0;
+    for (int t0 = 0; t0 < nrc; t0 += 32) {
+      const int t = t0 + lane;
+      const int r = t < nrc ? row_cand[t] : -1;
+      const bool keep = r >= 0 && match_col_of_row[r] < 0;
+      const unsigned m = __ballot_sync(0xffffffffu, keep);
+      if (keep) R[nr + __popc(m & ((1u << lane) - 1))] = r;
+      nr += __popc(m);
+    }
+    for (int t0 = 0; t0 < ncc; t0 += 32) {
+      const int t = t0 + lane;
+      const int c = t < ncc ? col_cand[t] : -1;
+      const bool keep = c >= 0 && det_matched[c] == 0;
+      const unsigned m = __ballot_sync(0xffffffffu, keep);
+      if (keep) C[nc + __popc(m & ((1u << lane) - 1))] = c;
+      nc += __popc(m);
+    }
+    if (lane == 0) { s_nr = nr; s_nc = nc; s_total = 0; }
+  }
+  __syncthreads();
+  const int nr = s_nr, nc = s_nc;
+  if (nr == 0 || nc == 0) {  // nothing to match: every candidate column stays unmatched, in its order
+    for (int t = tid; t < nc; t += LX_THREADS) um_dets[t] = C[t];
+    if (tid == 0) um_count[0] = nc;
+    return;
+  }
+  const bool tr = nc < nr;
+  const int na = tr ? nc : nr, nb = tr ? nr : nc;
+  const int32_t* A = tr ? C : R;
+  const int32_t* B = tr ? R : C;
+  const double gated = max_distance + 1e-5;
+  // ---- admissible entries -> CSR by augmented-side row (whole CTA)
+  for (int a = tid; a <= na; a += LX_THREADS) off[a] = 0;
+  for (int a = tid; a < na; a += LX_THREADS) fillc[a] = 0;
+  for (int b = tid; b < nb; b += LX_THREADS) rowval[b] = gated;
+  __syncthreads();
+  if (cap > 0) {
+    for (int p = warp; p < nr; p += LX_THREADS / 32) {
+      const double* crow = cost + (size_t)R[p] * ld;
+#pragma unroll 4
+      for (int q = lane; q < nc; q += 32) {
+        const double x = crow[C[q]];
+        if (x <= max_distance) {
+          const int e = atomicAdd(&s_total, 1);
+          const int a = tr ? q : p, b = tr ? p : q;
+          if (e < cap) { trip_val[e] = x; trip_a[e] = a; trip_b[e] = b; }
+          atomicAdd(&off[a + 1], 1);
+        }
+      }
+    }
+  }
+  __syncthreads();
+  const int total = s_total;
+  const bool use_csr = cap > 0 && total <= cap;
+  if (use_csr) {
+    if (warp == 0) {  // inclusive scan of the counts in off[1 .. na] -> row extents
+      const int per = (na + 31) >> 5;
+      const int b0 = 1 + lane * per, e0 = min(na + 1, b0 + per);
+      int sum = 0;
+      for (int t = b0; t < e0; ++t) sum += off[t];
+      int incl = sum;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const int x = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += x;
+      }
+      int run = incl - sum;
+      for (int t = b0; t < e0; ++t) { run += off[t]; off[t] = run; }
+    }
+    __syncthreads();
+    for (int e = tid; e < total; e += LX_THREADS) {
+      const int a = trip_a[e];
+      const int pos = off[a] + atomicAdd(&fillc[a], 1);
+      csr_val[pos] = trip_val[e];
+      csr_col[pos] = trip_b[e];
+    }
+  }
+  __syncthreads();
+
+  // ---- the search: scipy's loop, every scan spread over the CTA (a lone warp runs each dependent shared-memory access at
+  // full latency: 6700 cycles per augmentation measured, 3700 in this form; two barriers per step)
+  auto cst = [&](int a, int b) {  // direct read (the admissible entries did not fit)
+    const double x = tr ? cost[(size_t)B[b] * ld + A[a]] : cost[(size_t)A[a] * ld + B[b]];
+    return x <= max_distance ? x : gated;
+  };
+  __shared__ unsigned w_hi[LX_THREADS / 32], w_lo[LX_THREADS / 32];
+  __shared__ int w_free[LX_THREADS / 32], w_first[LX_THREADS / 32];
+  for (int a = tid; a < na; a += LX_THREADS) { u[a] = 0.0; b4a[a] = -1; }
+  for (int b = tid; b < nb; b += LX_THREADS) { v[b] = 0.0; a4b[b] = -1; stamp[b] = -1; }
+  int step_id = 0;
+  __syncthreads();
+  for (int cur = 0; cur < na; ++cur) {
+    for (int b = tid; b < nb; b += LX_THREADS) { sp[b] = INFINITY; SC[b] = 0; remaining[b] = nb - b - 1; }
+    for (int a = tid; a < na; a += LX_THREADS) SR[a] = 0;
+    int num_remaining = nb, sink = -1, i = cur;
+    double min_val = 0.0;
+    while (sink < 0) {
+      // row i of the clamped matrix = one constant + its few admissible entries, stamped with this step's id
+      if (use_csr)
+        for (int e = off[i] + tid; e < off[i + 1]; e += LX_THREADS) { rowval[csr_col[e]] = csr_val[e]; stamp[csr_col[e]] = step_id; }
+      if (tid == 0) SR[i] = 1;
+      __syncthreads();  // (also: the resets above, the previous step's bookkeeping, the previous row's augmentation)
+      const double ui = u[i];
+      double best = INFINITY;
+      int first_it = INT_MAX, lastfree_it = -1;
+      for (int it = tid; it < num_remaining; it += LX_THREADS) {
+        const int j = remaining[it];
+        const double c = use_csr ? (stamp[j] == step_id ? rowval[j] : gated) : cst(i, j);
+        const double r = min_val + c - ui - v[j];
+        double sv = sp[j];
+        if (r < sv) { sv = r; sp[j] = r; path[j] = i; }
+        const bool fr = a4b[j] < 0;
+        if (sv < best) { best = sv; first_it = it; lastfree_it = fr ? it : -1; }
+        else if (sv == best && fr) lastfree_it = it;
+      }
+      // the minimum (32-bit warp reductions over the ordered bit pattern of the double; + 0.0 folds -0.0 into +0.0 so that
+      // bit equality is numeric equality); among the threads that hold it, the last unassigned column of the scan, else
+      // the first column -- first inside each warp, then over the warps' results
+      best = best + 0.0;
+      unsigned long long key = (unsigned long long)__double_as_longlong(best);
+      key = (key >> 63) ? ~key : (key | 0x8000000000000000ull);
+      const unsigned khi = (unsigned)(key >> 32), klo = (unsigned)key;
+      unsigned mhi = __reduce_min_sync(0xffffffffu, khi);
+      unsigned mlo = __reduce_min_sync(0xffffffffu, khi == mhi ? klo : 0xffffffffu);
+      const bool mine = khi == mhi && klo == mlo;
+      int gfree = __reduce_max_sync(0xffffffffu, mine ? lastfree_it : -1);
+      int gfirst = __reduce_min_sync(0xffffffffu, mine ? first_it : INT_MAX);
+      if (lane == 0) { w_hi[warp] = mhi; w_lo[warp] = mlo; w_free[warp] = gfree; w_first[warp] = gfirst; }
+      __syncthreads();
+      mhi = 0xffffffffu; mlo = 0xffffffffu;
+#pragma unroll
+      for (int x = 0; x < LX_THREADS / 32; ++x)
+        if (w_hi[x] < mhi || (w_hi[x] == mhi && w_lo[x] < mlo)) { mhi = w_hi[x]; mlo = w_lo[x]; }
+      gfree = -1; gfirst = INT_MAX;
+#pragma unroll
+      for (int x = 0; x < LX_THREADS / 32; ++x)
+        if (w_hi[x] == mhi && w_lo[x] == mlo) { gfree = max(gfree, w_free[x]); gfirst = min(gfirst, w_first[x]); }
+      unsigned long long gk = ((unsigned long long)mhi << 32) | mlo;
+      gk = (gk >> 63) ? (gk & 0x7fffffffffffffffull) : ~gk;
+      const double gmin = __longlong_as_double((long long)gk);
+      if (!(gmin < INFINITY)) {  // NaN / inf costs: scipy raises; never spin
+        if (tid == 0) { atomicExch(status, 1); um_count[0] = 0; }
+        return;
+      }
+      const int index = gfree >= 0 ? gfree : gfirst;
+      min_val = gmin;
+      const int j = remaining[index];
+      const int owner = a4b[j];
+      const int last = remaining[num_remaining - 1];
+      __syncthreads();  // everybody has read remaining[] and the warps' results
+      if (tid == 0) { SC[j] = 1; remaining[index] = last; }
+      --num_remaining;
+      ++step_id;
+      if (owner < 0) sink = j; else i = owner;
+    }
+    __syncthreads();  // SC[sink] is set
+    if (tid == 0) u[cur] = u[cur] + min_val;
+    for (int a = tid; a < na; a += LX_THREADS)
+      if (SR[a] && a != cur) u[a] = u[a] + (min_val - sp[b4a[a]]);
+    for (int b = tid; b < nb; b += LX_THREADS)
+      if (SC[b]) v[b] = v[b] - (min_val - sp[b]);
+    __syncthreads();
+    if (tid == 0) {  // augment along the path back to cur
+      int j = sink;
+      for (int hop = 0; hop <= na; ++hop) {
+        const int a = path[j];
+        a4b[j] = a;
+        const int t = b4a[a];
+        b4a[a] = j;
+        j = t;
+        if (a == cur) break;
+      }
+    }
+    __syncthreads();
+  }
+  if (warp != 0) return;
+  // ---- the reference's lists (linear_assignment.py:61-76): columns scipy left unassigned, in column order; then, pair by
+  // pair in ROW order, matches (cost <= max_distance) and the gated pairs, whose detection joins the unmatched list
+  int cnt = 0;
+  if (!tr) {
+    for (int q0 = 0; q0 < nc; q0 += 32) {
+      const int q = q0 + lane;
+      const bool keep = q < nc && a4b[q] < 0;
+      const unsigned m = __ballot_sync(0xffffffffu, keep);
+      if (keep) um_dets[cnt + __popc(m & ((1u << lane) - 1))] = C[q];
+      cnt += __popc(m);
+    }
+  }
+  for (int p0 = 0; p0 < nr; p0 += 32) {
+    const int p = p0 + lane;
+    const int q = p < nr ? (tr ? a4b[p] : b4a[p]) : -1;
+    bool gated_pair = false;
+    if (q >= 0) {
+      const int row = R[p], col = C[q];
+      if (cost[(size_t)row * ld + col] <= max_distance) { match_col_of_row[row] = col; det_matched[col] = 1; }
+      else gated_pair = true;
+    }
+    const unsigned m = __ballot_sync(0xffffffffu, gated_pair);
+    if (gated_pair) um_dets[cnt + __popc(m & ((1u << lane) - 1))] = C[q];
+    cnt += __popc(m);
+  }
+  if (lane == 0) um_count[0] = cnt;
+}
+
 }  // namespace reidb200
 
 using namespace reidb200;
@@ -352,5 +610,43 @@ extern "C" int reidb200_lap_gated(const double* cost, int T, int M, size_t ld, c
                                                           match_col_of_row, det_matched, status);
   }
   RB_LAUNCH_CHECK("lap_solve_kernel");
+  return REIDB200_OK;
+}
+
+// Exact mode (see lap_exact_kernel): rows = row_cand (in that order, those still unmatched), columns = col_cand[0 ..
+// *col_count) (device list + device count, in that order, those still unmatched; col_count == NULL: all max_cols entries).
+// Writes the matches into match_col_of_row / det_matched like reidb200_lap_gated and the reference's
+// `unmatched_detections` list, in the reference's order, into um_dets[0 .. *um_count).
+extern "C" int reidb200_lap_exact(const double* cost, int T, int M, size_t ld, const int32_t* row_cand, int nrc,
+                                  const int32_t* col_cand, const int32_t* col_count, int max_cols, double max_distance,
+                                  int32_t* match_col_of_row, int32_t* det_matched, int32_t* um_dets, int32_t* um_count,
+                                  int32_t* status, void* stream) {
+  RB_REQUIRE(cost && col_cand && match_col_of_row && det_matched && um_dets && um_count && status && T > 0 && M > 0 && ld >= (size_t)M,
+             "lap_exact: bad argument");
+  RB_REQUIRE(nrc >= 0 && nrc <= T && max_cols >= 0 && max_cols <= M && (nrc == 0 || row_cand), "lap_exact: bad candidate lists");
+  RB_REQUIRE(nrc <= LAP_MAX_SIDE && max_cols <= LAP_MAX_SIDE, "lap_exact: at most %d rows / columns per solve", LAP_MAX_SIDE);
+  cudaStream_t st = (cudaStream_t)stream;
+  // shared memory: per-side arrays (4 f64 + 9 i32 + 2 u8 per element) + the admissible-entry tables (2 f64 + 3 i32 per
+  // entry); the tables get what is left of ~200 KB, at most 8192 entries, none below 256 (direct reads then)
+  const size_t side = (size_t)(nrc > max_cols ? nrc : max_cols) + 1;
+  const size_t per_side = 4 * sizeof(double) + 9 * sizeof(int32_t) + 2, per_entry = 2 * sizeof(double) + 3 * sizeof(int32_t);
+  const size_t budget = 200 * 1024;
+  size_t cap = budget > side * per_side + 64 ? (budget - side * per_side - 64) / per_entry : 0;
+  if (cap > 8192) cap = 8192;
+  if (cap < 256 || getenv("REIDB200_LAP_NO_CSR")) cap = 0;
+  cap &= ~(size_t)1;  // keeps the i32 tables behind the f64 tables 8-byte aligned
+  const size_t smem = side * per_side + cap * per_entry + 64;
+  static DeviceOnce attr;
+  if (attr.pending()) {
+    RB_CUDA(cudaFuncSetAttribute(lap_exact_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(budget + 4096)));
+  }
+  LxSmem lay;
+  lay.side = (int)side; lay.cap = (int)cap;
+  {
+    ProfScope _ps("lap_exact_kernel", st);
+    lap_exact_kernel<<<1, LX_THREADS, smem, st>>>(cost, ld, row_cand, nrc, col_cand, col_count, max_cols, max_distance,
+                                                  match_col_of_row, det_matched, um_dets, um_count, status, lay);
+  }
+  RB_LAUNCH_CHECK("lap_exact_kernel");
   return REIDB200_OK;
 }

@@ -689,6 +689,34 @@ def center_columns(x, want_mean=False):
 
 
 # ----------------------------------------------------------------------------------------- N1: assignment on device
+def lap_exact(cost, row_cand, col_cand, col_count, max_distance, match_col_of_row, det_matched, um_dets, um_count, status=None):
+    """min_cost_matching (linear_assignment.py:52-77) on the device cost matrix f64[T, M] with scipy's OWN assignment, ties
+    included (csrc/lap.cu lap_exact_kernel): rows `row_cand` (i32 device, the reference's track_indices order) x columns
+    `col_cand[:col_count]` (i32 device list + i32[1] device count, or col_count=None for the whole list; the reference's
+    detection_indices order); rows / columns matched so far are skipped.  Matches are recorded in match_col_of_row i32[T] /
+    det_matched i32[M]; um_dets i32[>= len(col_cand)] / um_count i32[1] receive the reference's unmatched_detections list
+    in the reference's order.  No host sync; returns the status tensor."""
+    if not (isinstance(cost, torch.Tensor) and cost.is_cuda and cost.dtype == torch.float64 and cost.dim() == 2 and cost.stride(1) == 1):
+        raise ValueError("lap_exact: a float64 CUDA matrix with unit column stride is required")
+    dev = cost.device
+    T, M = cost.shape
+    for name, t in (("row_cand", row_cand), ("col_cand", col_cand), ("match_col_of_row", match_col_of_row),
+                    ("det_matched", det_matched), ("um_dets", um_dets), ("um_count", um_count)):
+        if not (isinstance(t, torch.Tensor) and t.is_cuda and t.dtype == torch.int32 and t.is_contiguous()):
+            raise ValueError("lap_exact: %s must be a contiguous int32 CUDA tensor" % name)
+    if match_col_of_row.numel() != T or det_matched.numel() != M or um_dets.numel() < col_cand.numel() or um_count.numel() < 1:
+        raise ValueError("lap_exact: match_col_of_row i32[T], det_matched i32[M], um_dets i32[>= len(col_cand)], um_count i32[1]")
+    if status is None:
+        status = torch.zeros(1, dtype=torch.int32, device=dev)
+    if T and M:
+        with torch.cuda.device(dev):
+            L.check(L.load().reidb200_lap_exact(cost.data_ptr(), T, M, cost.stride(0), row_cand.data_ptr(), row_cand.numel(),
+                                                col_cand.data_ptr(), L.ptr(col_count), col_cand.numel(), float(max_distance),
+                                                match_col_of_row.data_ptr(), det_matched.data_ptr(), um_dets.data_ptr(),
+                                                um_count.data_ptr(), status.data_ptr(), L.stream_ptr()))
+    return status
+
+
 def lap_gated(cost, row_cand, max_distance, match_col_of_row, det_matched, status=None):
     """One min_cost_matching solve on the device cost matrix f64[T, M]: rows `row_cand` (i32, device) that are still
     unmatched x columns still unmatched; matches are recorded in match_col_of_row i32[T] / det_matched i32[M] in place.

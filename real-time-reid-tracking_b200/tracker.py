@@ -162,9 +162,10 @@ def costs_to_host(app, iou):
 def match_arrays(metric, det_feat, det_tlwh, trk_ids, trk_confirmed, trk_mean, trk_SI, trk_tsu, mc_lambda, max_iou_dist,
                  max_dist=None, iou_mode="iou", device_lap=False):
     """(matches [(track_row, det_idx)], unmatched_tracks, unmatched_detections) exactly as Tracker._match returns them.
-    device_lap=True solves both assignment stages on the device too: the same matches whenever scipy's
-    optimum is unique, unmatched detections listed in ascending order (scipy's pairing of gated leftovers, which orders
-    the reference's list, is not reproduced)."""
+    device_lap=True solves both assignment stages on the device too with scipy's own assignment, ties
+    included: the three lists come back in the reference's order (lap.cu exact mode).  device_lap="fast" is the
+    component-parallel solver: the same matches whenever scipy's optimum is unique, unmatched detections in ascending
+    order (scipy's pairing of gated leftovers, which orders the reference's list, is not reproduced)."""
     T, M = len(trk_ids), len(det_tlwh)
     max_dist = metric.matching_threshold if max_dist is None else max_dist
     confirmed = [i for i in range(T) if trk_confirmed[i]]
@@ -173,8 +174,10 @@ def match_arrays(metric, det_feat, det_tlwh, trk_ids, trk_confirmed, trk_mean, t
     if T and M:
         app, _, iou = frame_costs(metric, det_feat, det_tlwh, trk_ids, trk_confirmed, trk_mean, trk_SI, trk_tsu, mc_lambda,
                                   max_dist, max_iou_dist, iou_mode)
-        if device_lap:
+        if device_lap == "fast":
             return _match_on_device(app, iou, confirmed, unconfirmed, trk_tsu, max_dist, max_iou_dist)
+        if device_lap:
+            return _match_on_device_exact(app, iou, confirmed, unconfirmed, trk_tsu, max_dist, max_iou_dist)
         app, iou = costs_to_host(app, iou)  # one D2H
     # stage A: confirmed tracks x all detections, appearance cost (matching_cascade, single level)
     if len(confirmed) == 0 or M == 0:
@@ -232,6 +235,66 @@ def _match_on_device(app, iou, confirmed, unconfirmed, trk_tsu, max_dist, max_io
     rb = cand_b[(mt[cand_b] >= 0) & (mt_a[cand_b] < 0)] if cand_b.size else cand_b
     matches = list(zip(ra.tolist(), mt_a[ra].tolist())) + list(zip(rb.tolist(), mt[rb].tolist()))
     return matches, np.nonzero(mt < 0)[0].tolist(), np.nonzero(h[T:T + M] == 0)[0].tolist()
+
+
+def _match_on_device_exact(app, iou, confirmed, unconfirmed, trk_tsu, max_dist, max_iou_dist):
+    """Both stages of Tracker._match (tracker.py:175-233) on the device with the reference's list orders: stage A =
+    min_cost_matching of the confirmed rows x all detections on the appearance matrix, stage B = the unconfirmed rows +
+    the confirmed rows with time_since_update == 1 that stage A left unmatched x stage A's unmatched_detections IN ITS
+    ORDER on the IoU matrix.  One H2D (row lists, column list, initial state), two launches, one D2H."""
+    dev = app.device
+    T, M = app.shape
+    tsu = np.asarray(trk_tsu)
+    conf_a = np.asarray(confirmed, np.int32)
+    # the reference builds unmatched_tracks_a as list(set(confirmed) - matched): ascending for the row indices of a frame
+    cand_b = np.concatenate([np.asarray(unconfirmed, np.int32), conf_a[tsu[conf_a] == 1] if conf_a.size else conf_a]).astype(np.int32)
+    # state: match[T] = -1 | det_matched[M] = 0 | status[1] | match_a[T] | um_a[M] | n_a[1] | um_b[M] | n_b[1]
+    init = _lap_init.get(("x", T, M))
+    if init is None:
+        init = _lap_init[("x", T, M)] = np.concatenate([np.full(T, -1, np.int32), np.zeros(M + 1 + T + 2 * (M + 1), np.int32)])
+    dets = _lap_init.get(("d", M))
+    if dets is None:
+        dets = _lap_init[("d", M)] = np.arange(M, dtype=np.int32)
+    rows_a, rows_b, cols_a, state = L.staging(dev).upload([conf_a, cand_b, dets, init])
+    o = 0
+    match = state[o:o + T]; o += T
+    det_m = state[o:o + M]; o += M
+    status = state[o:o + 1]; o += 1
+    match_a = state[o:o + T]; o += T
+    um_a = state[o:o + M]; o += M
+    n_a = state[o:o + 1]; o += 1
+    um_b = state[o:o + M]; o += M
+    n_b = state[o:o + 1]
+    if conf_a.size:
+        ops.lap_exact(app, rows_a, cols_a, None, max_dist, match, det_m, um_a, n_a, status)
+    else:
+        um_a.copy_(cols_a)
+        n_a.fill_(M)
+    match_a.copy_(match)
+    if cand_b.size:
+        ops.lap_exact(iou, rows_b, um_a, n_a, max_iou_dist, match, det_m, um_b, n_b, status)
+    else:
+        um_b.copy_(um_a)
+        n_b.copy_(n_a)
+    key = (dev.index, state.numel())
+    host = _lap_host.get(key)
+    if host is None:
+        host = _lap_host[key] = torch.empty(state.numel(), dtype=torch.int32).pin_memory()
+    host.copy_(state, non_blocking=True)
+    torch.cuda.current_stream(dev).synchronize()
+    h = host.numpy()
+    if h[T + M]:
+        raise L.Reidb200Error("device assignment met non-finite costs")
+    mt, mt_a = h[:T], h[T + M + 1:2 * T + M + 1]
+    ob = 2 * T + M + 1 + M + 1
+    um_d = h[ob:ob + int(h[ob + M])].tolist()
+    ra = conf_a[mt_a[conf_a] >= 0] if conf_a.size else conf_a
+    rb = cand_b[(mt[cand_b] >= 0) & (mt_a[cand_b] < 0)] if cand_b.size else cand_b
+    matches = list(zip(ra.tolist(), mt_a[ra].tolist())) + list(zip(rb.tolist(), mt[rb].tolist()))
+    # the reference's unmatched_tracks: list(set(unmatched_tracks_a + unmatched_tracks_b)) -- a set of small ints
+    um_a_rows = [k for k in conf_a.tolist() if mt_a[k] < 0 and tsu[k] != 1]
+    um_b_rows = [k for k in cand_b.tolist() if mt[k] < 0]
+    return matches, list(set(um_a_rows + um_b_rows)), um_d
 
 
 _lap_init = {}

@@ -114,3 +114,53 @@ def test_tracker_match_on_device_equals_host(rb, golden):
     m_h, ut_h, ud_h = TR.match_arrays(*args)
     m_d, ut_d, ud_d = TR.match_arrays(*args, device_lap=True)
     assert sorted(m_d) == sorted(m_h) and len(m_h) > 50 and sorted(ut_d) == sorted(ut_h) and sorted(ud_d) == sorted(ud_h)
+    # exact mode: the three lists in the reference's ORDER (the order of unmatched_detections decides the ids of new tracks)
+    assert m_d == m_h and ut_d == ut_h and ud_d == ud_h
+    m_f, ut_f, ud_f = TR.match_arrays(*args, device_lap="fast")
+    assert sorted(m_f) == sorted(m_h) and sorted(ut_f) == sorted(ut_h) and ud_f == sorted(ud_h)
+
+
+def _exact_on_device(cost, max_distance, rows, cols):
+    from reidb200 import ops
+
+    T, M = cost.shape
+    dev = torch.device("cuda", 0)
+    c = torch.from_numpy(cost).to(dev)
+    match = torch.full((T,), -1, dtype=torch.int32, device=dev)
+    det = torch.zeros(M, dtype=torch.int32, device=dev)
+    um = torch.full((max(len(cols), 1),), -7, dtype=torch.int32, device=dev)
+    n = torch.zeros(1, dtype=torch.int32, device=dev)
+    rows_d = torch.tensor(rows, dtype=torch.int32, device=dev)
+    cols_d = torch.tensor(cols, dtype=torch.int32, device=dev)
+    status = ops.lap_exact(c, rows_d, cols_d, None, max_distance, match, det, um, n)
+    assert int(status.item()) == 0
+    m = match.cpu().numpy()
+    matches = [(r, int(m[r])) for r in rows if m[r] >= 0]
+    return matches, um.cpu().numpy()[:int(n.item())].tolist(), det.cpu().numpy()
+
+
+@pytest.mark.parametrize("T,M", [(40, 25), (25, 40), (33, 33), (300, 200), (200, 300), (1, 9), (9, 1), (70, 64)])
+def test_lap_exact_mode_reproduces_scipys_ties_and_list_order(rb, T, M):
+    """Exact mode against scipy run the reference's way on TIE-HEAVY matrices (gated entries all equal, coarse costs, rows
+    without any admissible entry): matches in row order and the unmatched_detections list in the reference's order; on
+    candidate subsets given in shuffled order too (stage B of Tracker._match gets its columns in stage A's list order)."""
+    rng = np.random.default_rng(T * 1000 + M)
+    for trial in range(6):
+        cost = rng.random((T, M))
+        thr = [0.02, 0.1, 0.4, 0.1, 0.1, 5.0][trial]
+        if trial == 3:
+            cost = np.round(cost, 1)           # exact ties between admissible entries as well
+        if trial == 4:
+            cost[:] = 0.9                      # nothing admissible: the pairing is pure tie-breaking
+        rows, cols = list(range(T)), list(range(M))
+        if trial in (1, 2) and min(T, M) > 4:
+            rows = rng.permutation(T)[: max(2, T * 2 // 3)].tolist()
+            cols = rng.permutation(M)[: max(2, M * 3 // 4)].tolist()
+        sub = cost[np.ix_(rows, cols)]
+        want_m, want_ut, want_ud = O.min_cost_matching_lists(sub, thr, rows, cols)
+        got_m, got_ud, det = _exact_on_device(cost, thr, rows, cols)
+        assert got_m == [(int(a), int(b)) for a, b in want_m], (T, M, trial)
+        assert got_ud == [int(x) for x in want_ud], (T, M, trial)
+        assert sorted(np.nonzero(det)[0].tolist()) == sorted(int(b) for _, b in want_m)
+        if trial == 4:
+            assert not want_m and len(want_ud) == len(cols)

@@ -196,3 +196,27 @@ def test_market_full_fixture_present_and_consistent(golden):
     assert abs(g["rr_ap_q"].sum() / 3368 - float(g["rr_map"])) < 1e-12
     assert np.all(np.diff(g["rr_cmc"]) >= 0) and np.all(np.diff(g["rank_dist"], axis=1) >= 0)
     assert np.array_equal(g["rank_vals"][:, 0], g["rank_rows"])  # self first
+
+
+def test_lsap_restatement_equals_scipy_on_tie_heavy_matrices():
+    """The restatement of scipy's rectangular_lsap.cpp (the model of the device solver's exact mode) returns scipy's own
+    assignment, ties included: gated matrices (every entry above the gate replaced by one constant, as min_cost_matching
+    does), coarse integer-like costs, both orientations, degenerate shapes."""
+    from scipy.optimize import linear_sum_assignment
+
+    rng = np.random.default_rng(0)
+    for trial in range(250):
+        T, M = int(rng.integers(1, 36)), int(rng.integers(1, 36))
+        c = rng.random((T, M))
+        thr = float(rng.choice([0.05, 0.2, 0.5, 2.0]))
+        c[c > thr] = thr + 1e-5
+        if trial % 3 == 0:
+            c = np.round(c, 1)
+        if trial % 7 == 0:
+            c[:] = thr + 1e-5  # nothing admissible at all: the pairing is pure tie-breaking
+        r0, c0 = linear_sum_assignment(c)
+        r1, c1 = O.lsap_scipy_order(c)
+        assert np.array_equal(r0, r1) and np.array_equal(c0, c1), (trial, T, M)
+        a = O.min_cost_matching_lists(c, thr, list(range(10, 10 + T)), list(range(100, 100 + M)))
+        b = O.min_cost_matching_lists(c, thr, list(range(10, 10 + T)), list(range(100, 100 + M)), solver=O.lsap_scipy_order)
+        assert a == b
