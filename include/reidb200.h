@@ -400,11 +400,13 @@ int reidb200_lap_gated(const double* cost, int T, int M, size_t ld, const int32_
  *   row_cand i32[nrc]: rows in the reference's track_indices order (rows already matched are skipped)
  *   col_cand i32[<= max_cols], col_count i32[1] or NULL: columns in the reference's detection_indices order (device list +
  *   device count, so that the list one solve writes feeds the next without a host round trip)
- *   um_dets i32[>= max_cols], um_count i32[1]: out.  Matches go to match_col_of_row / det_matched like lap_gated. */
+ *   um_dets i32[>= max_cols], um_count i32[1]: out.  um_rows i32[>= nrc], um_rows_count i32[1]: out, the reference's
+ *   `unmatched_tracks` list in its order (both NULL: not wanted).  Matches go to match_col_of_row / det_matched like
+ *   lap_gated. */
 int reidb200_lap_exact(const double* cost, int T, int M, size_t ld, const int32_t* row_cand, int nrc,
                        const int32_t* col_cand, const int32_t* col_count, int max_cols, double max_distance,
                        int32_t* match_col_of_row, int32_t* det_matched, int32_t* um_dets, int32_t* um_count,
-                       int32_t* status, void* stream);
+                       int32_t* um_rows, int32_t* um_rows_count, int32_t* status, void* stream);
 
 #ifdef __cplusplus
 }

@@ -91,7 +91,7 @@ SIGNATURES = {
     "reidb200_center_columns": (_i, [_vp, _i, _i, _sz, _vp, _sz, _vp, _vp]),
     "reidb200_lap_workspace_bytes": (_sz, [_i, _i]),
     "reidb200_lap_gated": (_i, [_vp, _i, _i, _sz, _vp, _i, _d, _vp, _vp, _vp, _vp, _sz, _vp]),
-    "reidb200_lap_exact": (_i, [_vp, _i, _i, _sz, _vp, _i, _vp, _vp, _i, _d, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "reidb200_lap_exact": (_i, [_vp, _i, _i, _sz, _vp, _i, _vp, _vp, _i, _d, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
 }
 
 _lib = None

@@ -326,7 +326,8 @@ __global__ void __launch_bounds__(LX_THREADS)
 lap_exact_kernel(const double* __restrict__ cost, size_t ld, const int32_t* __restrict__ row_cand, int nrc,
                  const int32_t* __restrict__ col_cand, const int32_t* __restrict__ col_count, int max_cols, double max_distance,
                  int32_t* __restrict__ match_col_of_row, int32_t* __restrict__ det_matched, int32_t* __restrict__ um_dets,
-                 int32_t* __restrict__ um_count, int32_t* __restrict__ status, LxSmem lay) {
+                 int32_t* __restrict__ um_count, int32_t* __restrict__ um_rows, int32_t* __restrict__ um_rows_count,
+                 int32_t* __restrict__ status, LxSmem lay) {
   extern __shared__ __align__(16) unsigned char lx_smem[];
   __shared__ int s_nr, s_nc, s_total;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -379,6 +380,10 @@ lap_exact_kernel(const double* __restrict__ cost, size_t ld, const int32_t* __re
   if (nr == 0 || nc == 0) {  // nothing to match: every candidate column stays unmatched, in its order
     for (int t = tid; t < nc; t += LX_THREADS) um_dets[t] = C[t];
     if (tid == 0) um_count[0] = nc;
+    if (um_rows) {  // (the reference returns track_indices as it got them)
+      for (int t = tid; t < nr; t += LX_THREADS) um_rows[t] = R[t];
+      if (tid == 0) um_rows_count[0] = nr;
+    }
     return;
   }
   const bool tr = nc < nr;
@@ -496,7 +501,7 @@ lap_exact_kernel(const double* __restrict__ cost, size_t ld, const int32_t* __re
       gk = (gk >> 63) ? (gk & 0x7fffffffffffffffull) : ~gk;
       const double gmin = __longlong_as_double((long long)gk);
       if (!(gmin < INFINITY)) {  // NaN / inf costs: scipy raises; never spin
-        if (tid == 0) { atomicExch(status, 1); um_count[0] = 0; }
+        if (tid == 0) { atomicExch(status, 1); um_count[0] = 0; if (um_rows) um_rows_count[0] = 0; }
         return;
       }
       const int index = gfree >= 0 ? gfree : gfirst;
@@ -533,7 +538,7 @@ lap_exact_kernel(const double* __restrict__ cost, size_t ld, const int32_t* __re
   if (warp != 0) return;
   // ---- the reference's lists (linear_assignment.py:61-76): columns scipy left unassigned, in column order; then, pair by
   // pair in ROW order, matches (cost <= max_distance) and the gated pairs, whose detection joins the unmatched list
-  int cnt = 0;
+  int cnt = 0, rcnt = 0;
   if (!tr) {
     for (int q0 = 0; q0 < nc; q0 += 32) {
       const int q = q0 + lane;
@@ -541,6 +546,14 @@ lap_exact_kernel(const double* __restrict__ cost, size_t ld, const int32_t* __re
       const unsigned m = __ballot_sync(0xffffffffu, keep);
       if (keep) um_dets[cnt + __popc(m & ((1u << lane) - 1))] = C[q];
       cnt += __popc(m);
+    }
+  } else if (um_rows) {  // rows scipy left unassigned (more rows than columns), in row order
+    for (int p0 = 0; p0 < nr; p0 += 32) {
+      const int p = p0 + lane;
+      const bool keep = p < nr && a4b[p] < 0;
+      const unsigned m = __ballot_sync(0xffffffffu, keep);
+      if (keep) um_rows[rcnt + __popc(m & ((1u << lane) - 1))] = R[p];
+      rcnt += __popc(m);
     }
   }
   for (int p0 = 0; p0 < nr; p0 += 32) {
@@ -553,10 +566,18 @@ lap_exact_kernel(const double* __restrict__ cost, size_t ld, const int32_t* __re
       else gated_pair = true;
     }
     const unsigned m = __ballot_sync(0xffffffffu, gated_pair);
-    if (gated_pair) um_dets[cnt + __popc(m & ((1u << lane) - 1))] = C[q];
+    const int at = __popc(m & ((1u << lane) - 1));
+    if (gated_pair) {
+      um_dets[cnt + at] = C[q];
+      if (um_rows) um_rows[rcnt + at] = R[p];
+    }
     cnt += __popc(m);
+    rcnt += __popc(m);
   }
-  if (lane == 0) um_count[0] = cnt;
+  if (lane == 0) {
+    um_count[0] = cnt;
+    if (um_rows) um_rows_count[0] = rcnt;
+  }
 }
 
 }  // namespace reidb200
@@ -616,14 +637,16 @@ extern "C" int reidb200_lap_gated(const double* cost, int T, int M, size_t ld, c
 // Exact mode (see lap_exact_kernel): rows = row_cand (in that order, those still unmatched), columns = col_cand[0 ..
 // *col_count) (device list + device count, in that order, those still unmatched; col_count == NULL: all max_cols entries).
 // Writes the matches into match_col_of_row / det_matched like reidb200_lap_gated and the reference's
-// `unmatched_detections` list, in the reference's order, into um_dets[0 .. *um_count).
+// `unmatched_detections` list, in the reference's order, into um_dets[0 .. *um_count), and (optional) its `unmatched_tracks`
+// list into um_rows[0 .. *um_rows_count).
 extern "C" int reidb200_lap_exact(const double* cost, int T, int M, size_t ld, const int32_t* row_cand, int nrc,
                                   const int32_t* col_cand, const int32_t* col_count, int max_cols, double max_distance,
                                   int32_t* match_col_of_row, int32_t* det_matched, int32_t* um_dets, int32_t* um_count,
-                                  int32_t* status, void* stream) {
+                                  int32_t* um_rows, int32_t* um_rows_count, int32_t* status, void* stream) {
   RB_REQUIRE(cost && col_cand && match_col_of_row && det_matched && um_dets && um_count && status && T > 0 && M > 0 && ld >= (size_t)M,
              "lap_exact: bad argument");
   RB_REQUIRE(nrc >= 0 && nrc <= T && max_cols >= 0 && max_cols <= M && (nrc == 0 || row_cand), "lap_exact: bad candidate lists");
+  RB_REQUIRE((um_rows == nullptr) == (um_rows_count == nullptr), "lap_exact: um_rows and um_rows_count go together");
   RB_REQUIRE(nrc <= LAP_MAX_SIDE && max_cols <= LAP_MAX_SIDE, "lap_exact: at most %d rows / columns per solve", LAP_MAX_SIDE);
   cudaStream_t st = (cudaStream_t)stream;
   // shared memory: per-side arrays (4 f64 + 9 i32 + 2 u8 per element) + the admissible-entry tables (2 f64 + 3 i32 per
@@ -645,7 +668,7 @@ extern "C" int reidb200_lap_exact(const double* cost, int T, int M, size_t ld, c
   {
     ProfScope _ps("lap_exact_kernel", st);
     lap_exact_kernel<<<1, LX_THREADS, smem, st>>>(cost, ld, row_cand, nrc, col_cand, col_count, max_cols, max_distance,
-                                                  match_col_of_row, det_matched, um_dets, um_count, status, lay);
+                                                  match_col_of_row, det_matched, um_dets, um_count, um_rows, um_rows_count, status, lay);
   }
   RB_LAUNCH_CHECK("lap_exact_kernel");
   return REIDB200_OK;

@@ -689,13 +689,15 @@ def center_columns(x, want_mean=False):
 
 
 # ----------------------------------------------------------------------------------------- N1: assignment on device
-def lap_exact(cost, row_cand, col_cand, col_count, max_distance, match_col_of_row, det_matched, um_dets, um_count, status=None):
+def lap_exact(cost, row_cand, col_cand, col_count, max_distance, match_col_of_row, det_matched, um_dets, um_count, status=None,
+              um_rows=None, um_rows_count=None):
     """min_cost_matching (linear_assignment.py:52-77) on the device cost matrix f64[T, M] with scipy's OWN assignment, ties
     included (csrc/lap.cu lap_exact_kernel): rows `row_cand` (i32 device, the reference's track_indices order) x columns
     `col_cand[:col_count]` (i32 device list + i32[1] device count, or col_count=None for the whole list; the reference's
     detection_indices order); rows / columns matched so far are skipped.  Matches are recorded in match_col_of_row i32[T] /
     det_matched i32[M]; um_dets i32[>= len(col_cand)] / um_count i32[1] receive the reference's unmatched_detections list
-    in the reference's order.  No host sync; returns the status tensor."""
+    in the reference's order; um_rows i32[>= len(row_cand)] / um_rows_count i32[1] (optional) its unmatched_tracks list.
+    No host sync; returns the status tensor."""
     if not (isinstance(cost, torch.Tensor) and cost.is_cuda and cost.dtype == torch.float64 and cost.dim() == 2 and cost.stride(1) == 1):
         raise ValueError("lap_exact: a float64 CUDA matrix with unit column stride is required")
     dev = cost.device
@@ -713,7 +715,8 @@ def lap_exact(cost, row_cand, col_cand, col_count, max_distance, match_col_of_ro
             L.check(L.load().reidb200_lap_exact(cost.data_ptr(), T, M, cost.stride(0), row_cand.data_ptr(), row_cand.numel(),
                                                 col_cand.data_ptr(), L.ptr(col_count), col_cand.numel(), float(max_distance),
                                                 match_col_of_row.data_ptr(), det_matched.data_ptr(), um_dets.data_ptr(),
-                                                um_count.data_ptr(), status.data_ptr(), L.stream_ptr()))
+                                                um_count.data_ptr(), L.ptr(um_rows), L.ptr(um_rows_count), status.data_ptr(),
+                                                L.stream_ptr()))
     return status
 
 

@@ -160,10 +160,11 @@ def costs_to_host(app, iou):
 
 
 def match_arrays(metric, det_feat, det_tlwh, trk_ids, trk_confirmed, trk_mean, trk_SI, trk_tsu, mc_lambda, max_iou_dist,
-                 max_dist=None, iou_mode="iou", device_lap=False):
+                 max_dist=None, iou_mode="iou", device_lap=True):
     """(matches [(track_row, det_idx)], unmatched_tracks, unmatched_detections) exactly as Tracker._match returns them.
-    device_lap=True solves both assignment stages on the device too with scipy's own assignment, ties
-    included: the three lists come back in the reference's order (lap.cu exact mode).  device_lap="fast" is the
+    device_lap=True (the default since the exact mode exists) solves both assignment stages on the device too (SURVEY 8f
+    N1) with scipy's own assignment, ties included: the three lists come back in the reference's order (lap.cu exact
+    mode).  device_lap=False runs scipy on the host, the reference's own solver.  device_lap="fast" is the
     component-parallel solver: the same matches whenever scipy's optimum is unique, unmatched detections in ascending
     order (scipy's pairing of gated leftovers, which orders the reference's list, is not reproduced)."""
     T, M = len(trk_ids), len(det_tlwh)
@@ -241,66 +242,80 @@ def _match_on_device_exact(app, iou, confirmed, unconfirmed, trk_tsu, max_dist, 
     """Both stages of Tracker._match (tracker.py:175-233) on the device with the reference's list orders: stage A =
     min_cost_matching of the confirmed rows x all detections on the appearance matrix, stage B = the unconfirmed rows +
     the confirmed rows with time_since_update == 1 that stage A left unmatched x stage A's unmatched_detections IN ITS
-    ORDER on the IoU matrix.  One H2D (row lists, column list, initial state), two launches, one D2H."""
+    ORDER on the IoU matrix.  The lists between and after the stages are built by the reference's own expressions
+    (list(set(...)) included: CPython's set order decides the row order of stage B), so stage A's row -> column table
+    comes back to the host before stage B is launched; stage A's detection list stays on the device."""
     dev = app.device
     T, M = app.shape
     tsu = np.asarray(trk_tsu)
     conf_a = np.asarray(confirmed, np.int32)
-    # the reference builds unmatched_tracks_a as list(set(confirmed) - matched): ascending for the row indices of a frame
-    cand_b = np.concatenate([np.asarray(unconfirmed, np.int32), conf_a[tsu[conf_a] == 1] if conf_a.size else conf_a]).astype(np.int32)
-    # state: match[T] = -1 | det_matched[M] = 0 | status[1] | match_a[T] | um_a[M] | n_a[1] | um_b[M] | n_b[1]
+    # state: match[T] = -1 | um_a[M] | n_a[1] | det_matched[M] = 0 | status[1] | um_b[M] | n_b[1] | um_rows[T] | n_rows[1]
     init = _lap_init.get(("x", T, M))
     if init is None:
-        init = _lap_init[("x", T, M)] = np.concatenate([np.full(T, -1, np.int32), np.zeros(M + 1 + T + 2 * (M + 1), np.int32)])
+        init = _lap_init[("x", T, M)] = np.concatenate([np.full(T, -1, np.int32), np.zeros(3 * (M + 1) + T + 1, np.int32)])
     dets = _lap_init.get(("d", M))
     if dets is None:
         dets = _lap_init[("d", M)] = np.arange(M, dtype=np.int32)
-    rows_a, rows_b, cols_a, state = L.staging(dev).upload([conf_a, cand_b, dets, init])
+    stg = L.staging(dev)
+    rows_a, cols_a, state = stg.upload([conf_a, dets, init])
     o = 0
     match = state[o:o + T]; o += T
-    det_m = state[o:o + M]; o += M
-    status = state[o:o + 1]; o += 1
-    match_a = state[o:o + T]; o += T
     um_a = state[o:o + M]; o += M
     n_a = state[o:o + 1]; o += 1
+    det_m = state[o:o + M]; o += M
+    status = state[o:o + 1]; o += 1
     um_b = state[o:o + M]; o += M
-    n_b = state[o:o + 1]
+    n_b = state[o:o + 1]; o += 1
+    um_rows = state[o:o + T]; o += T
+    n_rows = state[o:o + 1]
+    host = _lap_host.get((dev.index, state.numel()))
+    if host is None:
+        host = _lap_host[(dev.index, state.numel())] = torch.empty(state.numel(), dtype=torch.int32).pin_memory()
+    h = host.numpy()
+    stream = torch.cuda.current_stream(dev)
+    # ---- stage A
     if conf_a.size:
         ops.lap_exact(app, rows_a, cols_a, None, max_dist, match, det_m, um_a, n_a, status)
+        host.copy_(state, non_blocking=True)  # (a few KB: the whole state, so that the status word is current too)
+        stream.synchronize()
+        mt_a = h[:T].copy()
+        m_a = [(int(k), int(mt_a[k])) for k in confirmed if mt_a[k] >= 0]
+        n_um = int(h[T + M])
     else:
         um_a.copy_(cols_a)
         n_a.fill_(M)
-    match_a.copy_(match)
-    if cand_b.size:
-        ops.lap_exact(iou, rows_b, um_a, n_a, max_iou_dist, match, det_m, um_b, n_b, status)
+        m_a, n_um = [], M
+    um_trk_a = list(set(confirmed) - set(k for k, _ in m_a))
+    # ---- stage B
+    cand = list(unconfirmed) + [k for k in um_trk_a if tsu[k] == 1]
+    um_trk_a = [k for k in um_trk_a if tsu[k] != 1]
+    if len(cand) == 0 or n_um == 0:
+        m_b, um_trk_b = [], cand
+        if not conf_a.size:
+            host.copy_(state, non_blocking=True)
+            stream.synchronize()
+        um_d = h[T:T + n_um].tolist()
     else:
-        um_b.copy_(um_a)
-        n_b.copy_(n_a)
-    key = (dev.index, state.numel())
-    host = _lap_host.get(key)
-    if host is None:
-        host = _lap_host[key] = torch.empty(state.numel(), dtype=torch.int32).pin_memory()
-    host.copy_(state, non_blocking=True)
-    torch.cuda.current_stream(dev).synchronize()
-    h = host.numpy()
-    if h[T + M]:
+        cand_np = np.asarray(cand, np.int32)
+        (rows_b,) = stg.upload([cand_np])
+        ops.lap_exact(iou, rows_b, um_a, n_a, max_iou_dist, match, det_m, um_b, n_b, status, um_rows, n_rows)
+        host.copy_(state, non_blocking=True)
+        stream.synchronize()
+        mt = h[:T]
+        m_b = [(int(k), int(mt[k])) for k in cand if mt[k] >= 0]
+        ob = T + 2 * (M + 1)
+        um_d = h[ob:ob + int(h[ob + M])].tolist()
+        orr = ob + M + 1
+        um_trk_b = h[orr:orr + int(h[orr + T])].tolist()
+    if h[T + 2 * M + 1]:
         raise L.Reidb200Error("device assignment met non-finite costs")
-    mt, mt_a = h[:T], h[T + M + 1:2 * T + M + 1]
-    ob = 2 * T + M + 1 + M + 1
-    um_d = h[ob:ob + int(h[ob + M])].tolist()
-    ra = conf_a[mt_a[conf_a] >= 0] if conf_a.size else conf_a
-    rb = cand_b[(mt[cand_b] >= 0) & (mt_a[cand_b] < 0)] if cand_b.size else cand_b
-    matches = list(zip(ra.tolist(), mt_a[ra].tolist())) + list(zip(rb.tolist(), mt[rb].tolist()))
-    # the reference's unmatched_tracks: list(set(unmatched_tracks_a + unmatched_tracks_b)) -- a set of small ints
-    um_a_rows = [k for k in conf_a.tolist() if mt_a[k] < 0 and tsu[k] != 1]
-    um_b_rows = [k for k in cand_b.tolist() if mt[k] < 0]
-    return matches, list(set(um_a_rows + um_b_rows)), um_d
+    return m_a + m_b, list(set(um_trk_a + um_trk_b)), um_d
 
 
 _lap_init = {}
 
 
-def match(metric, tracks, detections, mc_lambda, max_iou_dist):
+def match(metric, tracks, detections, mc_lambda, max_iou_dist, device_lap=True):
     """Tracker._match on the reference's objects (Track: track_id, is_confirmed(), time_since_update, mean, kf.SI;
     Detection: tlwh float32, feature)."""
     T, M = len(tracks), len(detections)
@@ -312,4 +327,4 @@ def match(metric, tracks, detections, mc_lambda, max_iou_dist):
     det_tlwh = np.asarray([d.tlwh for d in detections], np.float32).reshape(M, 4)
     det_feat = np.asarray([np.asarray(d.feature) for d in detections], np.float32)
     return match_arrays(metric, det_feat, det_tlwh, [t.track_id for t in tracks], [t.is_confirmed() for t in tracks], mean, SI,
-                        [t.time_since_update for t in tracks], mc_lambda, max_iou_dist)
+                        [t.time_since_update for t in tracks], mc_lambda, max_iou_dist, device_lap=device_lap)

@@ -88,7 +88,10 @@ def test_sequence_costs_and_assignments(rb, golden, monkeypatch, packed):
                 np.testing.assert_allclose(app[conf], fr["app_gated"], rtol=1e-4, atol=1e-5)
                 assert np.array_equal(app[conf] > 1e4, fr["app_gated"] > 1e4)  # identical gate decisions
         m, ut, ud = TR.match_arrays(metric, fr["det_feat"], fr["det_tlwh"], fr["trk_id"], fr["trk_confirmed"], fr["trk_mean"],
-                                    fr["trk_SI"], fr["trk_tsu"], lam, max_iou, max_dist)
+                                    fr["trk_SI"], fr["trk_tsu"], lam, max_iou, max_dist, device_lap=False)  # scipy on the host
+        md, utd, udd = TR.match_arrays(metric, fr["det_feat"], fr["det_tlwh"], fr["trk_id"], fr["trk_confirmed"], fr["trk_mean"],
+                                       fr["trk_SI"], fr["trk_tsu"], lam, max_iou, max_dist)  # default: exact assignment on the device
+        assert (md, utd, udd) == (m, ut, ud)
         assert np.array_equal(np.array(sorted(m), np.int64).reshape(-1, 2), fr["matches"])  # bit-exact assignments
         assert sorted(ut) == fr["unmatched_tracks"].tolist()
         assert sorted(ud) == fr["unmatched_dets"].tolist()

@@ -111,11 +111,19 @@ def test_tracker_match_on_device_equals_host(rb, golden):
     metric.partial_fit(np.concatenate(fr["samples"], 0), targets, list(range(T)))
     conf = np.arange(T) % 7 != 0
     args = (metric, fr["det_feat"], fr["det_tlwh"], np.arange(T), conf, fr["trk_mean"], fr["trk_SI"], fr["trk_tsu"], 0.995, 0.7, 0.2)
-    m_h, ut_h, ud_h = TR.match_arrays(*args)
+    m_h, ut_h, ud_h = TR.match_arrays(*args, device_lap=False)
     m_d, ut_d, ud_d = TR.match_arrays(*args, device_lap=True)
     assert sorted(m_d) == sorted(m_h) and len(m_h) > 50 and sorted(ut_d) == sorted(ut_h) and sorted(ud_d) == sorted(ud_h)
     # exact mode: the three lists in the reference's ORDER (the order of unmatched_detections decides the ids of new tracks)
     assert m_d == m_h and ut_d == ut_h and ud_d == ud_h
+    # rows spread so that CPython's set order of the unmatched confirmed tracks is not ascending (the row order of stage B)
+    conf2 = np.ones(T, bool)
+    conf2[::5] = False
+    tsu2 = np.where(np.arange(T) % 3 == 0, 1, fr["trk_tsu"]).astype(np.int32)
+    args2 = (metric, fr["det_feat"], fr["det_tlwh"][:40], np.arange(T), conf2, fr["trk_mean"], fr["trk_SI"], tsu2, 0.995, 0.7, 0.2)
+    args2 = (metric, fr["det_feat"][:40], fr["det_tlwh"][:40]) + args2[3:]
+    h2, d2 = TR.match_arrays(*args2, device_lap=False), TR.match_arrays(*args2, device_lap=True)
+    assert d2[0] == h2[0] and d2[1] == h2[1] and d2[2] == h2[2] and len(h2[1]) > 100
     m_f, ut_f, ud_f = TR.match_arrays(*args, device_lap="fast")
     assert sorted(m_f) == sorted(m_h) and sorted(ut_f) == sorted(ut_h) and ud_f == sorted(ud_h)
 
