@@ -351,8 +351,8 @@ lap_exact_kernel(const double* __restrict__ cost, size_t ld, const int32_t* __re
   int32_t* csr_col = stamp + side;  // [cap]
   int32_t* trip_a = csr_col + cap;  // [cap]
   int32_t* trip_b = trip_a + cap;   // [cap]
-  unsigned char* SR = reinterpret_cast<unsigned char*>(trip_b + cap);
-  unsigned char* SC = SR + side;
+  int32_t* vis_col = trip_b + cap;   // [side] column chosen by step s of the current augmentation
+  int32_t* vis_pos = vis_col + side; // [side] its position in `remaining`
 
   // ---- candidate rows / columns still unmatched, in the order given (warp 0)
   if (warp == 0) {
@@ -446,38 +446,41 @@ lap_exact_kernel(const double* __restrict__ cost, size_t ld, const int32_t* __re
     return x <= max_distance ? x : gated;
   };
   __shared__ unsigned w_hi[LX_THREADS / 32], w_lo[LX_THREADS / 32];
-  __shared__ int w_free[LX_THREADS / 32], w_first[LX_THREADS / 32];
+  __shared__ int w_free[LX_THREADS / 32], w_first[LX_THREADS / 32], w_jfree[LX_THREADS / 32], w_jfirst[LX_THREADS / 32];
+  // Per augmentation only what the search TOUCHED is reset or updated: the first step writes every shortest-path cost
+  // (no reset of sp[]), the visited columns are kept as a list (vis_col / vis_pos, in visit order) for the dual
+  // updates, and `remaining` is put back to its canonical descending order at the visited positions only.
   for (int a = tid; a < na; a += LX_THREADS) { u[a] = 0.0; b4a[a] = -1; }
-  for (int b = tid; b < nb; b += LX_THREADS) { v[b] = 0.0; a4b[b] = -1; stamp[b] = -1; }
+  for (int b = tid; b < nb; b += LX_THREADS) { v[b] = 0.0; a4b[b] = -1; stamp[b] = -1; remaining[b] = nb - b - 1; }
   int step_id = 0;
   __syncthreads();
   for (int cur = 0; cur < na; ++cur) {
-    for (int b = tid; b < nb; b += LX_THREADS) { sp[b] = INFINITY; SC[b] = 0; remaining[b] = nb - b - 1; }
-    for (int a = tid; a < na; a += LX_THREADS) SR[a] = 0;
-    int num_remaining = nb, sink = -1, i = cur;
+    int num_remaining = nb, sink = -1, i = cur, nsteps = 0;
     double min_val = 0.0;
     while (sink < 0) {
       // row i of the clamped matrix = one constant + its few admissible entries, stamped with this step's id
       if (use_csr)
         for (int e = off[i] + tid; e < off[i + 1]; e += LX_THREADS) { rowval[csr_col[e]] = csr_val[e]; stamp[csr_col[e]] = step_id; }
-      if (tid == 0) SR[i] = 1;
-      __syncthreads();  // (also: the resets above, the previous step's bookkeeping, the previous row's augmentation)
+      __syncthreads();  // (also: the previous step's bookkeeping, the previous augmentation's updates)
       const double ui = u[i];
+      const bool first_step = nsteps == 0;
       double best = INFINITY;
       int first_it = INT_MAX, lastfree_it = -1;
       for (int it = tid; it < num_remaining; it += LX_THREADS) {
         const int j = remaining[it];
         const double c = use_csr ? (stamp[j] == step_id ? rowval[j] : gated) : cst(i, j);
         const double r = min_val + c - ui - v[j];
-        double sv = sp[j];
+        double sv = first_step ? INFINITY : sp[j];
         if (r < sv) { sv = r; sp[j] = r; path[j] = i; }
+        else if (first_step) sp[j] = sv;  // (r is not below infinity: an infinite reduced cost stays recorded as such)
         const bool fr = a4b[j] < 0;
         if (sv < best) { best = sv; first_it = it; lastfree_it = fr ? it : -1; }
         else if (sv == best && fr) lastfree_it = it;
       }
       // the minimum (32-bit warp reductions over the ordered bit pattern of the double; + 0.0 folds -0.0 into +0.0 so that
       // bit equality is numeric equality); among the threads that hold it, the last unassigned column of the scan, else
-      // the first column -- first inside each warp, then over the warps' results
+      // the first column -- first inside each warp, then over the warps' results (each warp publishes the columns too, so
+      // that nobody reads `remaining` while thread 0 updates it)
       best = best + 0.0;
       unsigned long long key = (unsigned long long)__double_as_longlong(best);
       key = (key >> 63) ? ~key : (key | 0x8000000000000000ull);
@@ -487,16 +490,24 @@ lap_exact_kernel(const double* __restrict__ cost, size_t ld, const int32_t* __re
       const bool mine = khi == mhi && klo == mlo;
       int gfree = __reduce_max_sync(0xffffffffu, mine ? lastfree_it : -1);
       int gfirst = __reduce_min_sync(0xffffffffu, mine ? first_it : INT_MAX);
-      if (lane == 0) { w_hi[warp] = mhi; w_lo[warp] = mlo; w_free[warp] = gfree; w_first[warp] = gfirst; }
+      if (lane == 0) {
+        w_hi[warp] = mhi; w_lo[warp] = mlo; w_free[warp] = gfree; w_first[warp] = gfirst;
+        w_jfree[warp] = gfree >= 0 ? remaining[gfree] : -1;
+        w_jfirst[warp] = gfirst != INT_MAX ? remaining[gfirst] : -1;
+      }
       __syncthreads();
       mhi = 0xffffffffu; mlo = 0xffffffffu;
 #pragma unroll
       for (int x = 0; x < LX_THREADS / 32; ++x)
         if (w_hi[x] < mhi || (w_hi[x] == mhi && w_lo[x] < mlo)) { mhi = w_hi[x]; mlo = w_lo[x]; }
       gfree = -1; gfirst = INT_MAX;
+      int jfree = -1, jfirst = -1;
 #pragma unroll
       for (int x = 0; x < LX_THREADS / 32; ++x)
-        if (w_hi[x] == mhi && w_lo[x] == mlo) { gfree = max(gfree, w_free[x]); gfirst = min(gfirst, w_first[x]); }
+        if (w_hi[x] == mhi && w_lo[x] == mlo) {
+          if (w_free[x] > gfree) { gfree = w_free[x]; jfree = w_jfree[x]; }
+          if (w_first[x] < gfirst) { gfirst = w_first[x]; jfirst = w_jfirst[x]; }
+        }
       unsigned long long gk = ((unsigned long long)mhi << 32) | mlo;
       gk = (gk >> 63) ? (gk & 0x7fffffffffffffffull) : ~gk;
       const double gmin = __longlong_as_double((long long)gk);
@@ -505,23 +516,31 @@ lap_exact_kernel(const double* __restrict__ cost, size_t ld, const int32_t* __re
         return;
       }
       const int index = gfree >= 0 ? gfree : gfirst;
+      const int j = gfree >= 0 ? jfree : jfirst;
       min_val = gmin;
-      const int j = remaining[index];
       const int owner = a4b[j];
-      const int last = remaining[num_remaining - 1];
-      __syncthreads();  // everybody has read remaining[] and the warps' results
-      if (tid == 0) { SC[j] = 1; remaining[index] = last; }
+      if (tid == 0) {  // (the next scan starts behind the next barrier)
+        vis_col[nsteps] = j;
+        vis_pos[nsteps] = index;
+        remaining[index] = remaining[num_remaining - 1];
+      }
       --num_remaining;
       ++step_id;
+      ++nsteps;
       if (owner < 0) sink = j; else i = owner;
     }
-    __syncthreads();  // SC[sink] is set
+    __syncthreads();  // the visit lists are complete
+    // dual updates (scipy: u[cur] += minVal; u[i] += minVal - sp[col4row[i]] for the other visited rows; v[j] -= minVal -
+    // sp[j] for the visited columns): step s >= 1 scanned the row that owns the column of step s - 1
+    for (int sidx = tid; sidx < nsteps; sidx += LX_THREADS) {
+      const int jc = vis_col[sidx];
+      const double d = min_val - sp[jc];
+      if (sidx + 1 < nsteps) { const int a = a4b[jc]; u[a] = u[a] + d; }  // the row scanned by step sidx + 1
+      v[jc] = v[jc] - d;
+      remaining[vis_pos[sidx]] = nb - vis_pos[sidx] - 1;  // back to the canonical order
+    }
     if (tid == 0) u[cur] = u[cur] + min_val;
-    for (int a = tid; a < na; a += LX_THREADS)
-      if (SR[a] && a != cur) u[a] = u[a] + (min_val - sp[b4a[a]]);
-    for (int b = tid; b < nb; b += LX_THREADS)
-      if (SC[b]) v[b] = v[b] - (min_val - sp[b]);
-    __syncthreads();
+    __syncthreads();  // a4b is read above and rewritten below
     if (tid == 0) {  // augment along the path back to cur
       int j = sink;
       for (int hop = 0; hop <= na; ++hop) {
@@ -533,8 +552,8 @@ lap_exact_kernel(const double* __restrict__ cost, size_t ld, const int32_t* __re
         if (a == cur) break;
       }
     }
-    __syncthreads();
   }
+  __syncthreads();
   if (warp != 0) return;
   // ---- the reference's lists (linear_assignment.py:61-76): columns scipy left unassigned, in column order; then, pair by
   // pair in ROW order, matches (cost <= max_distance) and the gated pairs, whose detection joins the unmatched list
@@ -649,10 +668,10 @@ extern "C" int reidb200_lap_exact(const double* cost, int T, int M, size_t ld, c
   RB_REQUIRE((um_rows == nullptr) == (um_rows_count == nullptr), "lap_exact: um_rows and um_rows_count go together");
   RB_REQUIRE(nrc <= LAP_MAX_SIDE && max_cols <= LAP_MAX_SIDE, "lap_exact: at most %d rows / columns per solve", LAP_MAX_SIDE);
   cudaStream_t st = (cudaStream_t)stream;
-  // shared memory: per-side arrays (4 f64 + 9 i32 + 2 u8 per element) + the admissible-entry tables (2 f64 + 3 i32 per
+  // shared memory: per-side arrays (4 f64 + 11 i32 per element) + the admissible-entry tables (2 f64 + 3 i32 per
   // entry); the tables get what is left of ~200 KB, at most 8192 entries, none below 256 (direct reads then)
   const size_t side = (size_t)(nrc > max_cols ? nrc : max_cols) + 1;
-  const size_t per_side = 4 * sizeof(double) + 9 * sizeof(int32_t) + 2, per_entry = 2 * sizeof(double) + 3 * sizeof(int32_t);
+  const size_t per_side = 4 * sizeof(double) + 11 * sizeof(int32_t), per_entry = 2 * sizeof(double) + 3 * sizeof(int32_t);
   const size_t budget = 200 * 1024;
   size_t cap = budget > side * per_side + 64 ? (budget - side * per_side - 64) / per_entry : 0;
   if (cap > 8192) cap = 8192;

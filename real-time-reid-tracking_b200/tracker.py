@@ -279,13 +279,14 @@ def _match_on_device_exact(app, iou, confirmed, unconfirmed, trk_tsu, max_dist, 
         host.copy_(state, non_blocking=True)  # (a few KB: the whole state, so that the status word is current too)
         stream.synchronize()
         mt_a = h[:T].copy()
-        m_a = [(int(k), int(mt_a[k])) for k in confirmed if mt_a[k] >= 0]
+        ra = conf_a[mt_a[conf_a] >= 0]
+        m_a = list(zip(ra.tolist(), mt_a[ra].tolist()))
         n_um = int(h[T + M])
     else:
         um_a.copy_(cols_a)
         n_a.fill_(M)
         m_a, n_um = [], M
-    um_trk_a = list(set(confirmed) - set(k for k, _ in m_a))
+    um_trk_a = list(set(confirmed) - set(ra.tolist())) if conf_a.size else []
     # ---- stage B
     cand = list(unconfirmed) + [k for k in um_trk_a if tsu[k] == 1]
     um_trk_a = [k for k in um_trk_a if tsu[k] != 1]
@@ -302,7 +303,8 @@ def _match_on_device_exact(app, iou, confirmed, unconfirmed, trk_tsu, max_dist, 
         host.copy_(state, non_blocking=True)
         stream.synchronize()
         mt = h[:T]
-        m_b = [(int(k), int(mt[k])) for k in cand if mt[k] >= 0]
+        rb = cand_np[mt[cand_np] >= 0]
+        m_b = list(zip(rb.tolist(), mt[rb].tolist()))
         ob = T + 2 * (M + 1)
         um_d = h[ob:ob + int(h[ob + M])].tolist()
         orr = ob + M + 1
