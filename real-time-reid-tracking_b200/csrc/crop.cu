@@ -219,6 +219,155 @@ crop_cv_linear4_kernel(const uint8_t* __restrict__ src, const int64_t* __restric
   }
 }
 
+// ---- v4p: v4 with the arithmetic on PACKED pairs of fp32 (Blackwell's f32x2 instructions: one issue slot for two
+// adjacent columns).  v4 is issue-bound (69 % issue activity, ~60 % of its instructions fp32 arithmetic).  Every operation
+// keeps its own rounding: the conversion's product + fma and the normalisation's subtract-then-multiply are packed; the two
+// products of a lerp are packed, their SUM is two scalar add.rn (ptxas contracts a packed mul.rn feeding a packed add.rn
+// into one FFMA2 -- seen in SASS -- which would change the last bit, so no packed add ever consumes a packed product).
+// Bit-identical to v4 / the oracle (tests/test_gpu_crop.py: every byte value, up / down-scaled, clamped crops).
+__device__ __forceinline__ unsigned long long pk2(float lo, float hi) {
+  unsigned long long r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+  return r;
+}
+__device__ __forceinline__ void upk2(unsigned long long v, float& lo, float& hi) { asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v)); }
+__device__ __forceinline__ unsigned long long mul2(unsigned long long a, unsigned long long b) {
+  unsigned long long r;
+  asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+  return r;
+}
+__device__ __forceinline__ unsigned long long add2(unsigned long long a, unsigned long long b) {
+  unsigned long long r;
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+  return r;
+}
+__device__ __forceinline__ unsigned long long fma2(unsigned long long a, unsigned long long b, unsigned long long c) {
+  unsigned long long r;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
+  return r;
+}
+// two bytes -> two floats / 255 (u8_over_255_v4 on both halves)
+__device__ __forceinline__ unsigned long long u8x2_over_255(uint32_t u0, uint32_t u1) {
+  const unsigned long long x = pk2(__uint_as_float(0x4B000000u | u0), __uint_as_float(0x4B000000u | u1));
+  const unsigned long long f = add2(x, pk2(-8388608.0f, -8388608.0f));  // exact: 2^23 + u - 2^23
+  const unsigned long long q = mul2(f, pk2(-0x1.fdfdfep-33f, -0x1.fdfdfep-33f));
+  return fma2(f, pk2(0x1.010102p-8f, 0x1.010102p-8f), q);
+}
+
+// horizontal lerp of one source row at this thread's four column taps; h[c][p] = packed columns (2p, 2p + 1) of channel c
+__device__ __forceinline__ void cv_hrow4p(const uint8_t* __restrict__ row, const CvTap4& t, unsigned long long (&h)[3][2]) {
+#pragma unroll
+  for (int p = 0; p < 2; ++p) {
+    const uint8_t* p00 = row + t.i0[2 * p];
+    const uint8_t* p01 = row + t.i1[2 * p];
+    const uint8_t* p10 = row + t.i0[2 * p + 1];
+    const uint8_t* p11 = row + t.i1[2 * p + 1];
+    const unsigned long long a0 = pk2(t.a0[2 * p], t.a0[2 * p + 1]), a1 = pk2(t.a1[2 * p], t.a1[2 * p + 1]);
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+      const unsigned long long m0 = mul2(u8x2_over_255(__ldg(p00 + c), __ldg(p10 + c)), a0);
+      const unsigned long long m1 = mul2(u8x2_over_255(__ldg(p01 + c), __ldg(p11 + c)), a1);
+      float m0l, m0h, m1l, m1h;
+      upk2(m0, m0l, m0h);
+      upk2(m1, m1l, m1h);
+      h[c][p] = pk2(__fadd_rn(m0l, m1l), __fadd_rn(m0h, m1h));
+    }
+  }
+}
+
+template <bool POW2>
+__global__ void __launch_bounds__(CV4_WARPS * 32)
+crop_cv_linear4p_kernel(const uint8_t* __restrict__ src, const int64_t* __restrict__ crop_off,
+                        const int32_t* __restrict__ crop_geom, int out_h, int out_w, CvNorm nrm, float* __restrict__ out) {
+  const int crop = blockIdx.y;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int y_base = (blockIdx.x * CV4_WARPS + warp) * CV4_ROWS_PER_WARP;
+  if (y_base >= out_h) return;  // whole warps leave; the kernel has no block-wide barrier
+  const int h = crop_geom[crop * 3 + 0], w = crop_geom[crop * 3 + 1], stride = crop_geom[crop * 3 + 2];
+  const uint8_t* base = src + crop_off[crop];
+  const int rows_here = min(CV4_ROWS_PER_WARP, out_h - y_base);
+  const double scale_y = 1.0 / ((double)out_h / (double)h);
+  const double scale_x = 1.0 / ((double)out_w / (double)w);
+  const size_t plane = (size_t)out_h * out_w;
+  for (int x0 = lane * 4; x0 < out_w; x0 += 128) {  // out_w is a multiple of 4 (host side)
+    CvTap4 t;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      float fx = (float)(((double)(x0 + j) + 0.5) * scale_x - 0.5);
+      int sx = (int)floorf(fx);
+      fx = __fsub_rn(fx, (float)sx);
+      int sx0;
+      if (sx < 0) { sx0 = 0; fx = 0.f; }
+      else if (sx >= w - 1) { sx0 = w - 1; fx = 0.f; }
+      else sx0 = sx;
+      t.i0[j] = sx0 * 3;
+      t.i1[j] = min(sx0 + 1, w - 1) * 3;
+      t.a1[j] = fx;
+      t.a0[j] = __fsub_rn(1.0f, fx);
+    }
+    int idA = -1, idB = -1;
+    unsigned long long hA[3][2], hB[3][2];
+    float* op = out + (size_t)crop * 3 * plane + (size_t)y_base * out_w + x0;
+    // every source line this thread will touch is pulled into L1 up front (independent requests): the kernel is bound by
+    // the dependent load -> convert -> lerp chain of each new source row (~1 us from L2 / DRAM, eight rows per warp in
+    // sequence), not by issue slots -- the packed arithmetic alone did not move it (32.2 vs 32.4 us)
+    {
+      const double fy0 = ((double)y_base + 0.5) * scale_y - 0.5, fy1 = ((double)(y_base + rows_here - 1) + 0.5) * scale_y - 0.5;
+      const int s_first = min(max((int)floor(fy0), 0), h - 1), s_last = min(max((int)floor(fy1) + 1, 0), h - 1);
+      for (int sy = s_first; sy <= s_last; ++sy) {
+        const uint8_t* rowp = base + (size_t)sy * stride;
+        asm volatile("prefetch.global.L1 [%0];" ::"l"(rowp + t.i0[0]));
+        asm volatile("prefetch.global.L1 [%0];" ::"l"(rowp + t.i1[3] + 2));
+      }
+    }
+#pragma unroll 1
+    for (int r = 0; r < rows_here; ++r) {
+      float fy = (float)(((double)(y_base + r) + 0.5) * scale_y - 0.5);
+      const int sy = (int)floorf(fy);
+      fy = __fsub_rn(fy, (float)sy);
+      const int sy0 = min(max(sy, 0), h - 1), sy1 = min(max(sy + 1, 0), h - 1);
+      const float b1 = fy, b0 = __fsub_rn(1.0f, fy);
+      if (sy0 == idB) {
+#pragma unroll
+        for (int c = 0; c < 3; ++c) { hA[c][0] = hB[c][0]; hA[c][1] = hB[c][1]; }
+      } else if (sy0 != idA) {
+        cv_hrow4p(base + (size_t)sy0 * stride, t, hA);
+      }
+      idA = sy0;
+      if (sy1 == sy0) {
+#pragma unroll
+        for (int c = 0; c < 3; ++c) { hB[c][0] = hA[c][0]; hB[c][1] = hA[c][1]; }
+      } else if (sy1 != idB || sy0 == idB) {
+        cv_hrow4p(base + (size_t)sy1 * stride, t, hB);
+      }
+      idB = sy1;
+      const unsigned long long b0p = pk2(b0, b0), b1p = pk2(b1, b1);
+#pragma unroll
+      for (int c = 0; c < 3; ++c) {
+        float o[4];
+#pragma unroll
+        for (int p = 0; p < 2; ++p) {
+          float al, ah, bl, bh;
+          upk2(mul2(hA[c][p], b0p), al, ah);
+          upk2(mul2(hB[c][p], b1p), bl, bh);
+          // (v - mean) then * 1 / std (a power of two) or / std: a subtract feeding a multiply cannot be contracted
+          const unsigned long long d = add2(pk2(__fadd_rn(al, bl), __fadd_rn(ah, bh)), pk2(-nrm.m[c], -nrm.m[c]));
+          if (POW2) {
+            upk2(mul2(d, pk2(nrm.inv[c], nrm.inv[c])), o[2 * p], o[2 * p + 1]);
+          } else {
+            float dl, dh;
+            upk2(d, dl, dh);
+            o[2 * p] = __fdiv_rn(dl, nrm.s[c]);
+            o[2 * p + 1] = __fdiv_rn(dh, nrm.s[c]);
+          }
+        }
+        __stcs(reinterpret_cast<float4*>(op + c * plane), make_float4(o[0], o[1], o[2], o[3]));
+      }
+      op += out_w;
+    }
+  }
+}
+
 // ---------------------------------------------------------------------------- PIL_ANTIALIAS
 // Pillow 12 ImagingResample, 8 bits per channel: coefficients in double, normalised, rounded to
 // 22-bit fixed point; horizontal pass into a uint8 intermediate, then the vertical pass.
@@ -407,7 +556,11 @@ extern "C" int reidb200_crop_resize_norm_ws(const uint8_t* src, const int64_t* c
     {
       ProfScope _ps("crop_cv_linear_kernel", st);
       const bool vec4 = (out_w & 3) == 0 && (reinterpret_cast<uintptr_t>(out) & 15) == 0 && !getenv("REIDB200_CROP_V3");
-      if (vec4) {
+      if (vec4 && !getenv("REIDB200_CROP_V4")) {
+        dim3 g4(ceil_div(out_h, CV4_WARPS * CV4_ROWS_PER_WARP), M);
+        if (pow2) crop_cv_linear4p_kernel<true><<<g4, CV4_WARPS * 32, 0, st>>>(src, crop_off, crop_geom, out_h, out_w, nrm, out);
+        else crop_cv_linear4p_kernel<false><<<g4, CV4_WARPS * 32, 0, st>>>(src, crop_off, crop_geom, out_h, out_w, nrm, out);
+      } else if (vec4) {
         dim3 g4(ceil_div(out_h, CV4_WARPS * CV4_ROWS_PER_WARP), M);
         if (pow2) crop_cv_linear4_kernel<true><<<g4, CV4_WARPS * 32, 0, st>>>(src, crop_off, crop_geom, out_h, out_w, nrm, out);
         else crop_cv_linear4_kernel<false><<<g4, CV4_WARPS * 32, 0, st>>>(src, crop_off, crop_geom, out_h, out_w, nrm, out);

@@ -93,18 +93,20 @@ def test_empty_and_bad_crops(rb):
         P.preprocess_crops([np.zeros((0, 4, 3), np.uint8)])
 
 
-@pytest.mark.parametrize("kernel", ["v3", "v4"])
+@pytest.mark.parametrize("kernel", ["v3", "v4", "v4p"])
 @pytest.mark.parametrize("W", [420, 421, 423])
 def test_cv_linear_kernel_variants_bit_equal(rb, monkeypatch, kernel, W):
-    """Both crop kernels (v3: thread = output column; v4, the default: thread = four adjacent columns with 128-bit stores
-    and the conversion-free byte -> float step) against the oracle, bit for bit, on a frame that holds every byte value in
+    """The crop kernels (v3: thread = output column; v4: thread = four adjacent columns with 128-bit stores and the
+    conversion-free byte -> float step; v4p, the default: v4 on packed f32x2 arithmetic with the source lines prefetched)
+    against the oracle, bit for bit, on a frame that holds every byte value in
     every channel, crops that are up-scaled, down-scaled, one pixel wide, and clamped at the frame border, for frame widths
     whose row stride is and is not a multiple of four bytes."""
     from reidb200 import preprocess as P
 
     monkeypatch.delenv("REIDB200_CROP_V3", raising=False)
-    if kernel == "v3":
-        monkeypatch.setenv("REIDB200_CROP_V3", "1")
+    monkeypatch.delenv("REIDB200_CROP_V4", raising=False)
+    if kernel != "v4p":
+        monkeypatch.setenv("REIDB200_CROP_V3" if kernel == "v3" else "REIDB200_CROP_V4", "1")
     rng = np.random.default_rng(11)
     H = 300
     img = rng.integers(0, 256, (H, W, 3), dtype=np.uint8)
