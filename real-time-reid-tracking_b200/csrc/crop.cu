@@ -305,8 +305,11 @@ crop_cv_linear4p_kernel(const uint8_t* __restrict__ src, const int64_t* __restri
       t.a1[j] = fx;
       t.a0[j] = __fsub_rn(1.0f, fx);
     }
-    int idA = -1, idB = -1;
-    unsigned long long hA[3][2], hB[3][2];
+    // two cached source rows P / Q (horizontally interpolated, packed); a row already held is never reloaded and never
+    // COPIED between the buffers (the copies of v4's "A = sy0, B = sy1" rotation were 19 % of its instructions): the
+    // vertical step simply reads whichever buffers hold sy0 and sy1 (all conditions are warp-uniform)
+    int idP = -1, idQ = -1;
+    unsigned long long hP[3][2], hQ[3][2];
     float* op = out + (size_t)crop * 3 * plane + (size_t)y_base * out_w + x0;
     // every source line this thread will touch is pulled into L1 up front (independent requests): the kernel is bound by
     // the dependent load -> convert -> lerp chain of each new source row (~1 us from L2 / DRAM, eight rows per warp in
@@ -320,27 +323,7 @@ crop_cv_linear4p_kernel(const uint8_t* __restrict__ src, const int64_t* __restri
         asm volatile("prefetch.global.L1 [%0];" ::"l"(rowp + t.i1[3] + 2));
       }
     }
-#pragma unroll 1
-    for (int r = 0; r < rows_here; ++r) {
-      float fy = (float)(((double)(y_base + r) + 0.5) * scale_y - 0.5);
-      const int sy = (int)floorf(fy);
-      fy = __fsub_rn(fy, (float)sy);
-      const int sy0 = min(max(sy, 0), h - 1), sy1 = min(max(sy + 1, 0), h - 1);
-      const float b1 = fy, b0 = __fsub_rn(1.0f, fy);
-      if (sy0 == idB) {
-#pragma unroll
-        for (int c = 0; c < 3; ++c) { hA[c][0] = hB[c][0]; hA[c][1] = hB[c][1]; }
-      } else if (sy0 != idA) {
-        cv_hrow4p(base + (size_t)sy0 * stride, t, hA);
-      }
-      idA = sy0;
-      if (sy1 == sy0) {
-#pragma unroll
-        for (int c = 0; c < 3; ++c) { hB[c][0] = hA[c][0]; hB[c][1] = hA[c][1]; }
-      } else if (sy1 != idB || sy0 == idB) {
-        cv_hrow4p(base + (size_t)sy1 * stride, t, hB);
-      }
-      idB = sy1;
+    auto emit = [&](const unsigned long long (&hA)[3][2], const unsigned long long (&hB)[3][2], float b0, float b1) {
       const unsigned long long b0p = pk2(b0, b0), b1p = pk2(b1, b1);
 #pragma unroll
       for (int c = 0; c < 3; ++c) {
@@ -363,6 +346,26 @@ crop_cv_linear4p_kernel(const uint8_t* __restrict__ src, const int64_t* __restri
         }
         __stcs(reinterpret_cast<float4*>(op + c * plane), make_float4(o[0], o[1], o[2], o[3]));
       }
+    };
+#pragma unroll 1
+    for (int r = 0; r < rows_here; ++r) {
+      float fy = (float)(((double)(y_base + r) + 0.5) * scale_y - 0.5);
+      const int sy = (int)floorf(fy);
+      fy = __fsub_rn(fy, (float)sy);
+      const int sy0 = min(max(sy, 0), h - 1), sy1 = min(max(sy + 1, 0), h - 1);
+      const float b1 = fy, b0 = __fsub_rn(1.0f, fy);
+      int a, b;  // which buffer holds sy0 / sy1 (0 = P, 1 = Q)
+      if (idP == sy0) a = 0;
+      else if (idQ == sy0) a = 1;
+      else if (idP == sy1) { cv_hrow4p(base + (size_t)sy0 * stride, t, hQ); idQ = sy0; a = 1; }
+      else { cv_hrow4p(base + (size_t)sy0 * stride, t, hP); idP = sy0; a = 0; }
+      if (sy1 == sy0) b = a;
+      else if (idP == sy1) b = 0;
+      else if (idQ == sy1) b = 1;
+      else if (a == 0) { cv_hrow4p(base + (size_t)sy1 * stride, t, hQ); idQ = sy1; b = 1; }
+      else { cv_hrow4p(base + (size_t)sy1 * stride, t, hP); idP = sy1; b = 0; }
+      if (a == 0) { if (b == 0) emit(hP, hP, b0, b1); else emit(hP, hQ, b0, b1); }
+      else { if (b == 0) emit(hQ, hP, b0, b1); else emit(hQ, hQ, b0, b1); }
       op += out_w;
     }
   }
