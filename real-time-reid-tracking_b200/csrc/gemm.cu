@@ -98,6 +98,17 @@ struct GemmArgs {
   int cred_max;
   int tma_out;  // the output tensor map is valid (16-byte aligned rows): epilogue stores through the TMA engine
   int symmetric;  // A == B (self distances): only tiles with tn >= tm are computed, each also stored transposed
+  // TRIANGLE mode of a symmetric product (`lower` != 0; the fused re-ranked evaluation): the tiles are computed with the
+  // roles of the two blocks swapped (row block >= column block) and stored ONCE -- element (i, c) exists iff
+  // (i >> 8) >= (c >> 8); nothing is stored transposed (half of the output bytes).  A row's view of the missing half is
+  // what the chunk-guided selection needs: per (mirror row, 32-column chunk) the minimum in `cred` as before and, in
+  // `cred2`, (ordered key of the SECOND smallest value & ~31) | position of the minimum inside the chunk.  A chunk whose
+  // second value cannot pass the row's bound contributes exactly its minimum, so topk.cu reads it from these two words;
+  // only chunks with two or more passing elements are gathered through the transposed location.  The two cross terms
+  // of the split product are issued in the opposite order so that every accumulator -- hence every stored value -- is
+  // bit-identical to the one the upper-triangle kernel produces for the same pair.
+  int lower;
+  uint32_t* cred2;
   // box-major output (the re-ranking workspace): the matrix is stored as 32 x 32 boxes of 4 KB, box (rb, cb) at float
   // offset (rb * blocked + cb) * 1024, row-major inside; blocked = boxes per box row (0 = plain row-major).  Every
   // epilogue store is then one contiguous 4 KB piece of DRAM instead of 32 pieces of 128 B a row stride apart.
@@ -338,15 +349,42 @@ __device__ __forceinline__ void epilogue_slab(const GemmArgs& a, const CUtensorM
 #pragma unroll
             for (int rr = 0; rr < 32; ++rr) v[rr] = rr < rows_here ? v[rr] : pad;
           }
+          if (KIND == REIDB200_DIST_SQL2 && a.cred2) {
+            // triangle mode (minimum only): tournament over (smallest, second smallest) pairs, then the place of the
+            // smallest (the lowest one among equals; equal values make second == smallest, which sends the chunk to the
+            // exact gather in topk.cu)
+            float mn[16], sc[16];
 #pragma unroll
-          for (int w = 16; w >= 1; w >>= 1) {
+            for (int rr = 0; rr < 16; ++rr) { mn[rr] = fminf(v[rr], v[rr + 16]); sc[rr] = fmaxf(v[rr], v[rr + 16]); }
 #pragma unroll
-            for (int rr = 0; rr < w; ++rr) v[rr] = red_max ? fmaxf(v[rr], v[rr + w]) : fminf(v[rr], v[rr + w]);
+            for (int w = 8; w >= 1; w >>= 1) {
+#pragma unroll
+              for (int rr = 0; rr < w; ++rr) {
+                const float m1 = mn[rr], m2 = mn[rr + w];
+                mn[rr] = fminf(m1, m2);
+                sc[rr] = fminf(fmaxf(m1, m2), fminf(sc[rr], sc[rr + w]));
+              }
+            }
+            int arg = 31;
+#pragma unroll
+            for (int rr = 30; rr >= 0; --rr) arg = v[rr] == mn[0] ? rr : arg;
+            if (col0 + lane < a.n) {
+              a.cred[(size_t)(col0 + lane) * a.ldcr + (row0 >> 5)] = mn[0];
+              a.cred2[(size_t)(col0 + lane) * a.ldcr + (row0 >> 5)] = (float_to_ordered(sc[0]) & ~31u) | (uint32_t)arg;
+            }
+          } else {
+#pragma unroll
+            for (int w = 16; w >= 1; w >>= 1) {
+#pragma unroll
+              for (int rr = 0; rr < w; ++rr) v[rr] = red_max ? fmaxf(v[rr], v[rr + w]) : fminf(v[rr], v[rr + w]);
+            }
+            const float red_t = v[0];
+            if (col0 + lane < a.n) a.cred[(size_t)(col0 + lane) * a.ldcr + (row0 >> 5)] = red_t;
           }
-          const float red_t = v[0];
-          if (col0 + lane < a.n) a.cred[(size_t)(col0 + lane) * a.ldcr + (row0 >> 5)] = red_t;
         }
-        if (a.blocked) {  // box (col0 / 32, row0 / 32), padded to whole boxes: no edge guards
+        if (KIND == REIDB200_DIST_SQL2 && a.lower) {
+          // triangle mode: nothing is stored transposed
+        } else if (a.blocked) {  // box (col0 / 32, row0 / 32), padded to whole boxes: no edge guards
           float* mp = a.out + ((size_t)(col0 >> 5) * a.blocked + (row0 >> 5)) * 1024 + lane;
 #pragma unroll
           for (int j = 0; j < 32; ++j) mp[j * 32] = o[j];
@@ -762,6 +800,7 @@ gemm_split_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
       for (int tile = cluster_id; tile < total_tiles; tile += num_clusters) {
         int tm, tn;
         pair_tile_coords(tile, tiles_m2, a.symmetric, tm, tn);
+        if (KIND == REIDB200_DIST_SQL2 && a.lower) { const int t = tm; tm = tn; tn = t; }
         const int arow = tm * 2 * BM + (int)rank * BM;
         const int brow = tn * BN + (int)rank * (BN / 2);
         for (int kb = 0; kb < a.num_kb; ++kb) {
@@ -784,6 +823,15 @@ gemm_split_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
       int stage = 0, as = 0;
       uint32_t phase = 0, aphase = 0;
       for (int tile = cluster_id; tile < total_tiles; tile += num_clusters) {
+        // triangle mode: an off-diagonal tile has the roles of its two blocks swapped and issues the two cross terms in
+        // the opposite order (same products, same order of accumulation as the upper-triangle tile); a diagonal tile is
+        // computed in full exactly as before
+        bool swapped = false;
+        if (KIND == REIDB200_DIST_SQL2 && !SELECT && a.lower) {
+          int tm, tn;
+          pair_tile_coords(tile, tiles_m2, a.symmetric, tm, tn);
+          swapped = tm != tn;
+        }
         ptx::mbar_wait(bar_tempty + 8 * as, aphase ^ 1);
         ptx::tc_fence_after();
         const uint32_t d_tmem = tmem_base + as * BN;
@@ -797,8 +845,13 @@ gemm_split_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
             const uint64_t alo = ptx::umma_desc_k_sw128(sb + A_BYTES + kk * 32);
             const uint64_t bhi = ptx::umma_desc_k_sw128(sb + 2 * A_BYTES + kk * 32);
             const uint64_t blo = ptx::umma_desc_k_sw128(sb + 3 * A_BYTES + kk * 32);
-            ptx::mma_f16_ss_2cta(d_tmem, alo, bhi, idesc, (kb | kk) != 0);
-            ptx::mma_f16_ss_2cta(d_tmem, ahi, blo, idesc, 1);
+            if (swapped) {
+              ptx::mma_f16_ss_2cta(d_tmem, ahi, blo, idesc, (kb | kk) != 0);
+              ptx::mma_f16_ss_2cta(d_tmem, alo, bhi, idesc, 1);
+            } else {
+              ptx::mma_f16_ss_2cta(d_tmem, alo, bhi, idesc, (kb | kk) != 0);
+              ptx::mma_f16_ss_2cta(d_tmem, ahi, blo, idesc, 1);
+            }
             ptx::mma_f16_ss_2cta(d_tmem, ahi, bhi, idesc, 1);
           }
           ptx::mma_commit_2cta(bar_empty + 8 * stage, 3);  // frees this stage in BOTH CTAs
@@ -820,6 +873,7 @@ gemm_split_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
     for (int tile = cluster_id; tile < total_tiles; tile += num_clusters) {
       int tm, tn;
       pair_tile_coords(tile, tiles_m2, a.symmetric, tm, tn);
+      if (!SELECT && KIND == REIDB200_DIST_SQL2 && a.lower) { const int t = tm; tm = tn; tn = t; }
       if (SELECT)
         epilogue_select<KIND>(a, &tmO, bar_tfull + 8 * as, aphase, tmem_base + ((uint32_t)(q * 32) << 16) + as * BN,
                               tm * 2 * BM + (int)rank * BM + q * 32, tn * BN, c_first, lane, sbuf, yw_buf + (warp - 2) * 64,
@@ -932,13 +986,20 @@ static int make_output_map(CUtensorMap* tm, float* out, int m, int n, int64_t ld
 
 static int gemm_launch_impl(const void* packedA, const float* xx, const float* isa, int m, const void* packedB, const float* yy,
                             const float* isb, int n, int d, int kind, float* out, int64_t ldo, cudaStream_t st, float* chunk_red,
-                            int64_t ld_chunk_red, int chunk_red_max, int blocked, const SelArgs* sel);
+                            int64_t ld_chunk_red, int chunk_red_max, int blocked, const SelArgs* sel, uint32_t* chunk_red2 = nullptr);
 
 int gemm_split_launch(const void* packedA, const float* xx, const float* isa, int m, const void* packedB, const float* yy,
                       const float* isb, int n, int d, int kind, float* out, int64_t ldo, cudaStream_t st, float* chunk_red,
                       int64_t ld_chunk_red, int chunk_red_max, int blocked) {
   return gemm_launch_impl(packedA, xx, isa, m, packedB, yy, isb, n, d, kind, out, ldo, st, chunk_red, ld_chunk_red, chunk_red_max,
                           blocked, nullptr);
+}
+
+int gemm_split_tri_launch(const void* packed, const float* sq, const float* isc, int n, int d, float* out, int64_t ldo,
+                          cudaStream_t st, float* chunk_red, uint32_t* chunk_red2, int64_t ld_chunk_red) {
+  RB_REQUIRE(chunk_red && chunk_red2 && out, "distmat(triangle): chunk reductions and an output matrix are required");
+  return gemm_launch_impl(packed, sq, isc, n, packed, sq, isc, n, d, REIDB200_DIST_SQL2, out, ldo, st, chunk_red, ld_chunk_red, 0, 0,
+                          nullptr, chunk_red2);
 }
 
 int gemm_split_select_launch(const void* packedA, const float* xx, const float* isa, int m, const void* packedB, const float* yy,
@@ -950,7 +1011,7 @@ int gemm_split_select_launch(const void* packedA, const float* xx, const float* 
 
 static int gemm_launch_impl(const void* packedA, const float* xx, const float* isa, int m, const void* packedB, const float* yy,
                             const float* isb, int n, int d, int kind, float* out, int64_t ldo, cudaStream_t st, float* chunk_red,
-                            int64_t ld_chunk_red, int chunk_red_max, int blocked, const SelArgs* sel) {
+                            int64_t ld_chunk_red, int chunk_red_max, int blocked, const SelArgs* sel, uint32_t* chunk_red2) {
   if (m == 0 || n == 0) return REIDB200_OK;
   RB_REQUIRE(isa && isb, "distmat: operand scales missing");
   RB_REQUIRE(kind >= 0 && kind <= 3, "distmat: unknown kind %d", kind);
@@ -992,6 +1053,13 @@ static int gemm_launch_impl(const void* packedA, const float* xx, const float* i
   a.debug = getenv("REIDB200_GEMM_DEBUG") ? atoi(getenv("REIDB200_GEMM_DEBUG")) : 0;
   a.symmetric = pair && (a.tma_out || sel) && packedA == packedB && m == n && xx == yy && isa == isb && !getenv("REIDB200_GEMM_NOSYM");
   if (a.symmetric && sel) a.symmetric = 2;  // selection: diagonal tiles first (pair_tile_coords)
+  a.lower = 0;
+  a.cred2 = nullptr;
+  if (chunk_red2) {  // triangle mode: the caller's selection relies on it, so it is never silently dropped
+    RB_REQUIRE(a.symmetric == 1 && !blocked && !chunk_red_max, "distmat(triangle): needs the symmetric CTA-pair kernel (n > %d, aligned rows)", BM);
+    a.lower = 1;
+    a.cred2 = chunk_red2;
+  }
   void (*k1)(CUtensorMap, CUtensorMap, CUtensorMap, GemmArgs) = nullptr;
   void (*k2)(CUtensorMap, CUtensorMap, CUtensorMap, GemmArgs) = nullptr;
   if (sel) {  // selection in the epilogue: SQL2 (ascending) and DOT (descending) only, separate instantiations so that the

@@ -24,6 +24,18 @@ int gemm_split_launch(const void* packedA, const float* xx, const float* isa, in
                       const float* isb, int n, int d, int kind, float* out, int64_t ldo, cudaStream_t st,
                       float* chunk_red = nullptr, int64_t ld_chunk_red = 0, int chunk_red_max = 0, int blocked = 0);
 
+// Self squared-L2 product in TRIANGLE mode (gemm.cu GemmArgs::lower): element (i, c) of out[n, n] is stored iff
+// (i >> 8) >= (c >> 8) (256-row tile blocks), bit-identical to gemm_split_launch's value; chunk_red f32[n, ld] holds the
+// minimum of EVERY (row, 32-column chunk) and chunk_red2 u32[n, ld], for the chunks of the missing half,
+// (ordered key of the chunk's second smallest value & ~31) | position of its minimum.  Needs n > 128 and 16-byte aligned
+// rows (tri_mode_ok); consumed by topk_rows_launch(..., chunk_red2) and PairSrc::tri in rerank.cu.
+int gemm_split_tri_launch(const void* packed, const float* sq, const float* isc, int n, int d, float* out, int64_t ldo,
+                          cudaStream_t st, float* chunk_red, uint32_t* chunk_red2, int64_t ld_chunk_red);
+// whether an n x n self product with a k-NN of k can run in triangle mode (the CTA-pair kernel and the chunk-guided selection)
+inline bool tri_mode_ok(int n, int k) { return n > 128 && (n + 31) / 32 >= (4 * k > 64 ? 4 * k : 64) && k <= 128; }
+// element (i, c) of a triangle-mode matrix is read at (c, i) when its own place was not stored
+__host__ __device__ inline bool tri_stored(int i, int c) { return (i >> 8) >= (c >> 8); }
+
 // epilogue formulas of the four kinds (shared by the GEMM, its SIMT cross-check and the selection redo)
 #ifdef __CUDACC__
 __device__ __forceinline__ float dist_epilogue(int kind, float acc, float xx, float yy) {
@@ -98,9 +110,10 @@ int make_operand_map(CUtensorMap* tm, const void* packed, int rows, int dp, int 
 
 // row-wise exact top-k (topk.cu); out_i is i64 when idx64 else i32; ids = cand_i[col] or col + index_base
 // chunk_red (optional): the per-32-column reductions written by gemm_split_launch for this matrix (consumed: rows the
-// warp-per-row selection hands to the exact kernel are flagged in it).
+// warp-per-row selection hands to the exact kernel are flagged in it).  chunk_red2 != null: `vals` is a triangle-mode
+// matrix (gemm_split_tri_launch; square, ascending).
 int topk_rows_launch(const float* vals, int rows, int cols, int64_t ldv, const int64_t* cand_i, int k, int descending,
                      int64_t index_base, float* out_d, void* out_i, int idx64, cudaStream_t st,
-                     float* chunk_red = nullptr, int64_t ld_chunk_red = 0);
+                     float* chunk_red = nullptr, int64_t ld_chunk_red = 0, const uint32_t* chunk_red2 = nullptr);
 
 }  // namespace reidb200

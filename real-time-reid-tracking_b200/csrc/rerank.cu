@@ -106,13 +106,14 @@ krecip_both_kernel(const int32_t* __restrict__ rank, int N, int k1_cols, int kc,
 //     dense output) run the same kernels, so their results stay bit-identical.
 struct PairSrc {
   const float* sql2; int64_t lds;           // materialised matrix, or null
+  int tri;                                  // the matrix is in triangle mode (gemm.cuh tri_stored): (i, c) may live at (c, i)
   const float* feats; int64_t ldf; int d;   // fp32 feature rows (used when sql2 is null)
   const int32_t* rank_i; const float* rank_d; int k1c;  // the rows' top-k1 lists
 };
 
 // one thread: squared L2 of (i, c) (the CTA fallback kernel for k1 > 32; the warp kernel has its own cooperative version)
 __device__ float pair_sql2_thread(const PairSrc& P, const float* __restrict__ sqnorm, int i, int c) {
-  if (P.sql2) return P.sql2[(size_t)i * P.lds + c];
+  if (P.sql2) return (P.tri && !tri_stored(i, c)) ? P.sql2[(size_t)c * P.lds + i] : P.sql2[(size_t)i * P.lds + c];
   for (int t = 0; t < P.k1c; ++t)
     if (P.rank_i[(size_t)i * P.k1c + t] == c) return P.rank_d[(size_t)i * P.k1c + t];
   const float* a = P.feats + (size_t)i * P.ldf;
@@ -365,7 +366,7 @@ expand_v_warp_kernel(const int32_t* __restrict__ rfull, const int32_t* __restric
     if (head[s]) {
       const int c = (int)k[s];
       if (src.sql2) {
-        d2[s] = src.sql2[(size_t)i * src.lds + c];
+        d2[s] = (src.tri && !tri_stored(i, c)) ? src.sql2[(size_t)c * src.lds + i] : src.sql2[(size_t)i * src.lds + c];
       } else {
         bool hit = false;
         for (int t = 0; t < src.k1c; ++t)
@@ -1478,6 +1479,7 @@ struct JacWs {
   char* packed; float* sqn; float* isc;
   float* blk;            // selection mode: [blk_rows, lds] rows of the squared-L2 matrix kept for the blend (or null)
   float* mat; float* cred;  // matrix mode: the whole [N, lds] squared-L2 matrix + its per-(row, 32-column chunk) minima
+  uint32_t* cred2;          // matrix mode: second word per chunk of the triangle-mode GEMM (gemm.cuh gemm_split_tri_launch)
   float* rank_d; int32_t* rank_i;
   char* selws; size_t selbytes;
   SparseWs w;
@@ -1511,6 +1513,7 @@ static void carve_jaccard(C& c, int N, int d, int k1, int k2, const RerankDims& 
   t.sqn = c.template take<float>(N);
   t.isc = c.template take<float>(N);
   t.blk = t.mat = t.cred = nullptr;
+  t.cred2 = nullptr;
   t.selws = nullptr; t.selbytes = 0;
   if (rerank_select_mode(N)) {
     const int br = blend_block_rows(blend_rows, N);
@@ -1520,6 +1523,7 @@ static void carve_jaccard(C& c, int N, int d, int k1, int k2, const RerankDims& 
   } else {
     t.mat = c.template take<float>((size_t)N * rd.lds);
     t.cred = c.template take<float>((size_t)N * ceil_div((int)rd.lds, 32));
+    t.cred2 = c.template take<uint32_t>((size_t)N * ceil_div((int)rd.lds, 32));
   }
   t.rank_d = c.template take<float>((size_t)N * k1);
   t.rank_i = c.template take<int32_t>((size_t)N * k1);
@@ -1574,11 +1578,28 @@ extern "C" int reidb200_jaccard_from_rank(const int32_t* rank, const float* sql2
 // [blend_row0, blend_row0 + blend_rows) x all columns of the squared-L2 matrix are still stored for the lambda blend, into
 // ws.blk), k best entries of every list.  Returns the VIRTUAL base of the stored rows (row i at base + i * lds) or null.
 static int knn_stage(const float* feats, int N, int64_t ldf, int d, int k1, const RerankDims& rd, int blend_row0, int blend_rows,
-                     int blend_col0, int blend_cols, const JacWs& ws, const float** sql2_virtual, bool* have_matrix, cudaStream_t st) {
+                     int blend_col0, int blend_cols, const JacWs& ws, const float** sql2_virtual, bool* have_matrix, cudaStream_t st,
+                     bool* tri_out = nullptr) {
   int rc = pack_rows_launch(feats, N, ldf, d, ws.packed, ws.sqn, ws.isc, st);
   if (rc) return rc;
   if (ws.mat) {  // matrix mode
     const int ldcr = ceil_div((int)rd.lds, 32);
+    // Triangle mode: every element stored once (half of the GEMM's output bytes).  Only for a caller that can live with
+    // it (tri_out != null: its expansion reads single elements through PairSrc::tri) and whose blend block is stored in
+    // place: rows whose tile block is not below the block of any of its columns.
+    // REIDB200_TRI=0 keeps the full matrix (A/B timing, tests); REIDB200_TRI=2 makes a call that cannot use it fail (tests).
+    const int tri_env = getenv("REIDB200_TRI") ? atoi(getenv("REIDB200_TRI")) : 1;
+    const bool tri = tri_out && tri_env != 0 && tri_mode_ok(N, k1) && !getenv("REIDB200_GEMM_NOSYM") && !getenv("REIDB200_GEMM_1CTA") &&
+                     (blend_rows <= 0 || blend_cols <= 0 || tri_stored(blend_row0, blend_col0 + blend_cols - 1));
+    RB_REQUIRE(tri || !tri_out || tri_env != 2, "rerank: REIDB200_TRI=2 but N=%d, k1=%d cannot run in triangle mode", N, k1);
+    if (tri_out) *tri_out = tri;
+    if (tri) {
+      rc = gemm_split_tri_launch(ws.packed, ws.sqn, ws.isc, N, d, ws.mat, rd.lds, st, ws.cred, ws.cred2, ldcr);
+      if (rc) return rc;
+      *sql2_virtual = ws.mat;
+      *have_matrix = true;
+      return topk_rows_launch(ws.mat, N, N, rd.lds, nullptr, k1, 0, 0, ws.rank_d, ws.rank_i, 0, st, ws.cred, ldcr, ws.cred2);
+    }
     rc = gemm_split_launch(ws.packed, ws.sqn, ws.isc, N, ws.packed, ws.sqn, ws.isc, N, d, REIDB200_DIST_SQL2, ws.mat, rd.lds, st, ws.cred, ldcr, 0, 0);
     if (rc) return rc;
     *sql2_virtual = ws.mat;
@@ -1755,11 +1776,12 @@ static int rerank_eval_impl(const float* feats, int G, int Q, int64_t ldf, int d
   carve_jaccard(c, N, d, k1, k2, rd, Q, &ws);
   const float* sql2v = nullptr;
   bool have_matrix = false;
-  rc = knn_stage(feats, N, ldf, d, k1, rd, G, blend_rows, 0, G, ws, &sql2v, &have_matrix, st);  // selection mode stores the query x gallery block only
+  bool tri = false;  // the query rows come LAST in the merged set, so their gallery columns are stored in place in triangle mode
+  rc = knn_stage(feats, N, ldf, d, k1, rd, G, blend_rows, 0, G, ws, &sql2v, &have_matrix, st, &tri);  // selection mode stores the query x gallery block only
   if (rc) return rc;
   PairSrc src;
   memset(&src, 0, sizeof(src));
-  if (have_matrix) { src.sql2 = sql2v; src.lds = rd.lds; }
+  if (have_matrix) { src.sql2 = sql2v; src.lds = rd.lds; src.tri = tri ? 1 : 0; }
   else { src.feats = feats; src.ldf = ldf; src.d = d; src.rank_i = ws.rank_i; src.rank_d = ws.rank_d; src.k1c = k1; }
   rc = jaccard_sparse_stages(ws.rank_i, sql2v, rd.lds, ws.sqn, N, k1, k2, 0, lambda_value, G, Q, 0, G, out_dist, ldo, rd, ws.w, st, src, &ev);
   if (rc) return rc;

@@ -67,7 +67,7 @@ __device__ __forceinline__ void cand_append(bool take, uint32_t key, int col, in
 template <int MODE, int NT>
 __device__ __forceinline__ void topk_row_body(const int row, const float* __restrict__ vals, int cols, int64_t ldv,
                                               const int64_t* __restrict__ cand_i, int k, int descending, int64_t index_base,
-                                              float* __restrict__ out_d, void* __restrict__ out_i, int idx64) {
+                                              float* __restrict__ out_d, void* __restrict__ out_i, int idx64, bool tri = false) {
   extern __shared__ __align__(16) uint32_t rowkey[];  // MODE 1: keys of the row
   __shared__ uint32_t ckey[TOPK_CAP];
   __shared__ int32_t ccol[TOPK_CAP];
@@ -79,9 +79,12 @@ __device__ __forceinline__ void topk_row_body(const int row, const float* __rest
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int kk = min(k, cols);
   float* od = out_d + (size_t)row * k;
-  const bool vec = (reinterpret_cast<uintptr_t>(v) & 15) == 0;
+  // `tri` (MODE 0 only): the row lives in a triangle-mode matrix (gemm.cuh tri_stored) -- scalar loads, element c of the
+  // row read at its transposed place when its own was not stored
+  const bool vec = !tri && (reinterpret_cast<uintptr_t>(v) & 15) == 0;
   const int ncol4 = vec ? (cols >> 2) : 0;
   const float4* v4 = reinterpret_cast<const float4*>(v);
+  auto ldat = [&](int c) -> float { return (tri && !tri_stored(row, c)) ? __ldg(vals + (size_t)c * ldv + row) : __ldg(v + c); };
   if (tid == 0) s_count = 0;
   uint32_t t0 = 0xffffffffu;
 
@@ -100,7 +103,7 @@ __device__ __forceinline__ void topk_row_body(const int row, const float* __rest
       m[g] = min(m[g], min(min(k0, k1), min(k2, k3)));
     }
     for (int c = ncol4 * 4 + tid; c < cols; c += NT) {
-      const uint32_t kc = sel_key(__ldg(v + c), descending);
+      const uint32_t kc = sel_key(ldat(c), descending);
       if (MODE == 1) rowkey[c] = kc;
       const int g = per_thread == 1 ? 0 : ((c / NT) & 1);
       m[g] = min(m[g], kc);
@@ -156,7 +159,7 @@ __device__ __forceinline__ void topk_row_body(const int row, const float* __rest
       }
       for (int c0 = ncol4 * 4; c0 < cols; c0 += NT) {
         const int c = c0 + tid;
-        const uint32_t key = c < cols ? sel_key(__ldg(v + c), descending) : 0xffffffffu;
+        const uint32_t key = c < cols ? sel_key(ldat(c), descending) : 0xffffffffu;
         cand_append(c < cols && key <= t0, key, c, lane, &s_count, ckey, ccol);
       }
     }
@@ -166,7 +169,7 @@ __device__ __forceinline__ void topk_row_body(const int row, const float* __rest
 
   if (count > TOPK_CAP) {
     // ---- fallback (heavy ties / adversarial order): exact k-th key by bisection over the row, ordered collection
-    auto key_at = [&](int c) -> uint32_t { return MODE == 1 ? rowkey[c] : sel_key(__ldg(v + c), descending); };
+    auto key_at = [&](int c) -> uint32_t { return MODE == 1 ? rowkey[c] : sel_key(ldat(c), descending); };
     uint32_t lo = 0, hi = 0xffffffffu;  // invariant: count(key <= hi) >= kk, count(key <= lo-1) < kk
     while (lo < hi) {
       const uint32_t mid = lo + ((hi - lo) >> 1);
@@ -251,7 +254,7 @@ template <int NT>
 __global__ void __launch_bounds__(NT)
 topk_rows_redo_kernel(const float* __restrict__ vals, int rows, int cols, int64_t ldv, int k, int descending,
                       int64_t index_base, float* __restrict__ out_d, void* __restrict__ out_i, int idx64,
-                      const float* __restrict__ flag_rows, int64_t ldcr) {
+                      const float* __restrict__ flag_rows, int64_t ldcr, int tri) {
   // every thread checks one row per pass (a contiguous block of NT rows per CTA); flagged rows are queued in shared memory
   __shared__ int todo[NT];
   __shared__ int ntodo;
@@ -263,7 +266,7 @@ topk_rows_redo_kernel(const float* __restrict__ vals, int rows, int cols, int64_
     __syncthreads();
     const int n = ntodo;
     for (int i = 0; i < n; ++i) {
-      topk_row_body<0, NT>(todo[i], vals, cols, ldv, nullptr, k, descending, index_base, out_d, out_i, idx64);
+      topk_row_body<0, NT>(todo[i], vals, cols, ldv, nullptr, k, descending, index_base, out_d, out_i, idx64, tri != 0);
       __syncthreads();
     }
   }
@@ -276,11 +279,15 @@ topk_rows_redo_kernel(const float* __restrict__ vals, int rows, int cols, int64_
 // become candidates (warp-ballot compaction, no atomics, no block barriers).  A rank sort of the candidates by
 // (key, column) emits the k best; ties -> lower column.  Rows with more than TW_CAP candidates (massive ties) are
 // flagged and redone by the exact CTA-per-row kernel.
-template <int S>
+// TRI: `vals` is a triangle-mode matrix (gemm.cuh gemm_split_tri_launch; ascending only).  A chunk of the half that was
+// not stored (tile block of the chunk > tile block of the row) whose second smallest value cannot pass t0 contributes its
+// minimum alone, taken from the two chunk words (value from chunk_red, column from chunk_red2) without touching the
+// matrix; the few chunks with two or more passing elements are read at their transposed place (32 sectors).
+template <int S, bool TRI>
 __global__ void __launch_bounds__(128)
 topk_chunk_warp_kernel(const float* __restrict__ vals, int rows, int cols, int64_t ldv, int k, int descending,
                        int64_t index_base, float* __restrict__ out_d, void* __restrict__ out_i, int idx64,
-                       float* __restrict__ chunk_red, int64_t ldcr) {
+                       float* __restrict__ chunk_red, int64_t ldcr, const uint32_t* __restrict__ chunk_red2) {
   __shared__ uint32_t ckey[4][TW_CAP];
   __shared__ int32_t ccol[4][TW_CAP];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -288,6 +295,8 @@ topk_chunk_warp_kernel(const float* __restrict__ vals, int rows, int cols, int64
   if (row >= rows) return;
   const float* v = vals + (size_t)row * ldv;
   float* cr = chunk_red + (size_t)row * ldcr;
+  const uint32_t* cr2 = TRI ? chunk_red2 + (size_t)row * ldcr : nullptr;
+  const int rt = row >> 8;  // TRI: chunks c with (c >> 3) > rt belong to the half that was not stored
   const int nchunks = (cols + 31) >> 5;
   const int kk = min(k, cols);
 
@@ -326,7 +335,8 @@ topk_chunk_warp_kernel(const float* __restrict__ vals, int rows, int cols, int64
       for (int u = 0; u < 8; ++u) {
         const int ch = __shfl_sync(0xffffffffu, pending, (u0 + u) & 31);
         const int col = ch * 32 + lane;
-        key8[u] = (u0 + u < np && col < cols) ? sel_key(__ldg(v + col), descending) : 0xffffffffu;
+        const float* src = (TRI && (ch >> 3) > rt) ? vals + (size_t)col * ldv + row : v + col;
+        key8[u] = (u0 + u < np && col < cols) ? sel_key(__ldg(src), descending) : 0xffffffffu;
       }
 #pragma unroll
       for (int u = 0; u < 8; ++u) {
@@ -344,7 +354,24 @@ topk_chunk_warp_kernel(const float* __restrict__ vals, int rows, int cols, int64
   };
   for (int c0 = 0; c0 < nchunks; c0 += 32) {
     const int c = c0 + lane;
-    const bool q = c < nchunks && sel_key(__ldg(cr + c), descending) <= t0;
+    const uint32_t ckeyc = c < nchunks ? sel_key(__ldg(cr + c), descending) : 0xffffffffu;
+    bool q = c < nchunks && ckeyc <= t0;
+    if (TRI) {
+      bool single = false;
+      uint32_t w2 = 0;
+      if (q && (c >> 3) > rt) {
+        w2 = __ldg(cr2 + c);
+        // (a lower bound of) the second smallest key does not pass: the minimum is the chunk's only candidate
+        single = (w2 & ~31u) > t0 && c * 32 + (int)(w2 & 31u) < cols;
+      }
+      const uint32_t sb = __ballot_sync(0xffffffffu, single);
+      if (sb) {
+        const int pos = count + __popc(sb & ((1u << lane) - 1));
+        if (single && pos < TW_CAP) { mk[pos] = ckeyc; mc[pos] = c * 32 + (int)(w2 & 31u); }
+        count += __popc(sb);
+      }
+      q = q && !single;
+    }
     uint32_t todo = __ballot_sync(0xffffffffu, q);
     while (todo) {
       const int b = __ffs(todo) - 1;
@@ -384,7 +411,7 @@ topk_chunk_warp_kernel(const float* __restrict__ vals, int rows, int cols, int64
 
 int topk_rows_launch(const float* vals, int rows, int cols, int64_t ldv, const int64_t* cand_i, int k, int descending,
                      int64_t index_base, float* out_d, void* out_i, int idx64, cudaStream_t st, float* chunk_red,
-                     int64_t ld_chunk_red) {
+                     int64_t ld_chunk_red, const uint32_t* chunk_red2) {
   if (rows == 0 || k == 0) return REIDB200_OK;
   RB_REQUIRE(k > 0 && k <= TOPK_MAX_K, "topk: k=%d outside [1,%d]", k, TOPK_MAX_K);
   RB_REQUIRE(cols >= 0 && ldv >= cols, "topk: bad cols/ld");
@@ -393,20 +420,32 @@ int topk_rows_launch(const float* vals, int rows, int cols, int64_t ldv, const i
   if (attr.pending()) {
     RB_CUDA(cudaFuncSetAttribute(topk_rows_kernel<1, 512>, cudaFuncAttributeMaxDynamicSharedMemorySize, TOPK_SMEM_ROW_MAX * 4));
   }
-  if (chunk_red != nullptr && cand_i == nullptr && nchunks >= 4 * k && nchunks >= 64 && k <= 128) {
+  const bool chunk_guided = chunk_red != nullptr && cand_i == nullptr && nchunks >= 4 * k && nchunks >= 64 && k <= 128;
+  RB_REQUIRE(!chunk_red2 || (chunk_guided && rows == cols && !descending),
+             "topk: a triangle-mode matrix needs the chunk-guided selection (square, ascending, n/32 >= max(64, 4k), k <= 128)");
+  if (chunk_guided) {
     // groups = 32*S >= 2k lane-local minima (S = 2, 4 or 8)
     const int grid = ceil_div(rows, 4);
+    const bool tri = chunk_red2 != nullptr;
     {
       ProfScope _ps("topk_rows_kernel", st);
-      if (k <= 32) topk_chunk_warp_kernel<2><<<grid, 128, 0, st>>>(vals, rows, cols, ldv, k, descending, index_base, out_d, out_i, idx64, chunk_red, ld_chunk_red);
-      else if (k <= 64) topk_chunk_warp_kernel<4><<<grid, 128, 0, st>>>(vals, rows, cols, ldv, k, descending, index_base, out_d, out_i, idx64, chunk_red, ld_chunk_red);
-      else topk_chunk_warp_kernel<8><<<grid, 128, 0, st>>>(vals, rows, cols, ldv, k, descending, index_base, out_d, out_i, idx64, chunk_red, ld_chunk_red);
+#define RB_TOPK_CHUNK(S, T) topk_chunk_warp_kernel<S, T><<<grid, 128, 0, st>>>(vals, rows, cols, ldv, k, descending, index_base, out_d, out_i, idx64, chunk_red, ld_chunk_red, chunk_red2)
+      if (tri) {
+        if (k <= 32) RB_TOPK_CHUNK(2, true);
+        else if (k <= 64) RB_TOPK_CHUNK(4, true);
+        else RB_TOPK_CHUNK(8, true);
+      } else {
+        if (k <= 32) RB_TOPK_CHUNK(2, false);
+        else if (k <= 64) RB_TOPK_CHUNK(4, false);
+        else RB_TOPK_CHUNK(8, false);
+      }
+#undef RB_TOPK_CHUNK
     }
     RB_LAUNCH_CHECK("topk_chunk_warp_kernel");
     // rows the warp kernel flagged (candidate overflow: massive ties) are redone exactly
     ProfScope _ps2("topk_rows_redo_kernel", st);
     topk_rows_redo_kernel<512><<<min(ceil_div(rows, 512), 2 * num_sms()), 512, 0, st>>>(vals, rows, cols, ldv, k, descending, index_base, out_d,
-                                                                       out_i, idx64, chunk_red, ld_chunk_red);
+                                                                       out_i, idx64, chunk_red, ld_chunk_red, tri ? 1 : 0);
   } else if (cols <= TOPK_SMEM_ROW_MAX) {
     ProfScope _ps("topk_rows_kernel", st);
     topk_rows_kernel<1, 512><<<rows, 512, align_up((size_t)cols * 4, 16), st>>>(vals, cols, ldv, cand_i, k, descending,
