@@ -283,7 +283,10 @@ topk_rows_redo_kernel(const float* __restrict__ vals, int rows, int cols, int64_
 // not stored (tile block of the chunk > tile block of the row) whose second smallest value cannot pass t0 contributes its
 // minimum alone, taken from the two chunk words (value from chunk_red, column from chunk_red2) without touching the
 // matrix; the few chunks with two or more passing elements are read at their transposed place (32 sectors).
-template <int S, bool TRI>
+// PIPE: the loads of the chunk words are issued in batches (two groups of S in the first pass, four 32-chunk groups -- and
+// their second words -- in the second) before any of them is used: the kernel was bound by one dependent L2 / DRAM round
+// trip per 32 chunks in each pass (ncu: long scoreboard 5.7 warps per issue at 40 resident warps).
+template <int S, bool TRI, bool PIPE>
 __global__ void __launch_bounds__(128)
 topk_chunk_warp_kernel(const float* __restrict__ vals, int rows, int cols, int64_t ldv, int k, int descending,
                        int64_t index_base, float* __restrict__ out_d, void* __restrict__ out_i, int idx64,
@@ -303,11 +306,24 @@ topk_chunk_warp_kernel(const float* __restrict__ vals, int rows, int cols, int64
   uint32_t m[S];
 #pragma unroll
   for (int s = 0; s < S; ++s) m[s] = 0xffffffffu;
-  for (int c0 = 0; c0 < nchunks; c0 += 32 * S) {
+  if (PIPE) {
+    for (int c0 = 0; c0 < nchunks; c0 += 64 * S) {
+      uint32_t t[2 * S];
 #pragma unroll
-    for (int s = 0; s < S; ++s) {
-      const int c = c0 + s * 32 + lane;
-      if (c < nchunks) m[s] = min(m[s], sel_key(__ldg(cr + c), descending));
+      for (int j = 0; j < 2 * S; ++j) {
+        const int c = c0 + j * 32 + lane;
+        t[j] = c < nchunks ? sel_key(__ldg(cr + c), descending) : 0xffffffffu;
+      }
+#pragma unroll
+      for (int j = 0; j < 2 * S; ++j) m[j % S] = min(m[j % S], t[j]);
+    }
+  } else {
+    for (int c0 = 0; c0 < nchunks; c0 += 32 * S) {
+#pragma unroll
+      for (int s = 0; s < S; ++s) {
+        const int c = c0 + s * 32 + lane;
+        if (c < nchunks) m[s] = min(m[s], sel_key(__ldg(cr + c), descending));
+      }
     }
   }
   uint32_t lo = 0, hi = 0xffffffffu;
@@ -352,18 +368,13 @@ topk_chunk_warp_kernel(const float* __restrict__ vals, int rows, int cols, int64
     }
     np = 0;
   };
-  for (int c0 = 0; c0 < nchunks; c0 += 32) {
+  // one group of 32 chunks: lane's chunk c0 + lane with its minimum's key and (TRI, missing half) its second word
+  auto chunk_group = [&](int c0, uint32_t ckeyc, uint32_t w2) {
     const int c = c0 + lane;
-    const uint32_t ckeyc = c < nchunks ? sel_key(__ldg(cr + c), descending) : 0xffffffffu;
     bool q = c < nchunks && ckeyc <= t0;
     if (TRI) {
-      bool single = false;
-      uint32_t w2 = 0;
-      if (q && (c >> 3) > rt) {
-        w2 = __ldg(cr2 + c);
-        // (a lower bound of) the second smallest key does not pass: the minimum is the chunk's only candidate
-        single = (w2 & ~31u) > t0 && c * 32 + (int)(w2 & 31u) < cols;
-      }
+      // (a lower bound of) the second smallest key does not pass: the minimum is the chunk's only candidate
+      const bool single = q && (c >> 3) > rt && (w2 & ~31u) > t0 && c * 32 + (int)(w2 & 31u) < cols;
       const uint32_t sb = __ballot_sync(0xffffffffu, single);
       if (sb) {
         const int pos = count + __popc(sb & ((1u << lane) - 1));
@@ -378,6 +389,28 @@ topk_chunk_warp_kernel(const float* __restrict__ vals, int rows, int cols, int64
       todo &= todo - 1;
       if (lane == np) pending = c0 + b;
       if (++np == 32) flush();
+    }
+  };
+  if (PIPE) {
+    for (int c0 = 0; c0 < nchunks; c0 += 128) {
+      uint32_t kx[4], wx[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int c = c0 + u * 32 + lane;
+        kx[u] = c < nchunks ? sel_key(__ldg(cr + c), descending) : 0xffffffffu;
+        wx[u] = (TRI && c < nchunks && (c >> 3) > rt) ? __ldg(cr2 + c) : 0u;
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u)
+        if (c0 + u * 32 < nchunks) chunk_group(c0 + u * 32, kx[u], wx[u]);  // warp-uniform
+    }
+  } else {
+    for (int c0 = 0; c0 < nchunks; c0 += 32) {
+      const int c = c0 + lane;
+      const uint32_t ckeyc = c < nchunks ? sel_key(__ldg(cr + c), descending) : 0xffffffffu;
+      uint32_t w2 = 0;
+      if (TRI && c < nchunks && ckeyc <= t0 && (c >> 3) > rt) w2 = __ldg(cr2 + c);
+      chunk_group(c0, ckeyc, w2);
     }
   }
   flush();
@@ -429,16 +462,15 @@ int topk_rows_launch(const float* vals, int rows, int cols, int64_t ldv, const i
     const bool tri = chunk_red2 != nullptr;
     {
       ProfScope _ps("topk_rows_kernel", st);
-#define RB_TOPK_CHUNK(S, T) topk_chunk_warp_kernel<S, T><<<grid, 128, 0, st>>>(vals, rows, cols, ldv, k, descending, index_base, out_d, out_i, idx64, chunk_red, ld_chunk_red, chunk_red2)
+#define RB_TOPK_CHUNK(S, T, P) topk_chunk_warp_kernel<S, T, P><<<grid, 128, 0, st>>>(vals, rows, cols, ldv, k, descending, index_base, out_d, out_i, idx64, chunk_red, ld_chunk_red, chunk_red2)
+#define RB_TOPK_CHUNK_S(T, P) do { if (k <= 32) RB_TOPK_CHUNK(2, T, P); else if (k <= 64) RB_TOPK_CHUNK(4, T, P); else RB_TOPK_CHUNK(8, T, P); } while (0)
+      const bool pipe = !(getenv("REIDB200_TOPK_PIPE") && atoi(getenv("REIDB200_TOPK_PIPE")) == 0);  // 0: one load round per 32 chunks (A/B)
       if (tri) {
-        if (k <= 32) RB_TOPK_CHUNK(2, true);
-        else if (k <= 64) RB_TOPK_CHUNK(4, true);
-        else RB_TOPK_CHUNK(8, true);
+        if (pipe) RB_TOPK_CHUNK_S(true, true); else RB_TOPK_CHUNK_S(true, false);
       } else {
-        if (k <= 32) RB_TOPK_CHUNK(2, false);
-        else if (k <= 64) RB_TOPK_CHUNK(4, false);
-        else RB_TOPK_CHUNK(8, false);
+        if (pipe) RB_TOPK_CHUNK_S(false, true); else RB_TOPK_CHUNK_S(false, false);
       }
+#undef RB_TOPK_CHUNK_S
 #undef RB_TOPK_CHUNK
     }
     RB_LAUNCH_CHECK("topk_chunk_warp_kernel");
