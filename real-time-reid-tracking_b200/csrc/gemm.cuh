@@ -32,7 +32,7 @@ int gemm_split_launch(const void* packedA, const float* xx, const float* isa, in
 int gemm_split_tri_launch(const void* packed, const float* sq, const float* isc, int n, int d, float* out, int64_t ldo,
                           cudaStream_t st, float* chunk_red, uint32_t* chunk_red2, int64_t ld_chunk_red);
 // whether an n x n self product with a k-NN of k can run in triangle mode (the CTA-pair kernel and the chunk-guided selection)
-inline bool tri_mode_ok(int n, int k) { return n > 128 && (n + 31) / 32 >= (4 * k > 64 ? 4 * k : 64) && k <= 128; }
+inline bool tri_mode_ok(int n, int k) { return n > 128 && n <= 32768 && (n + 31) / 32 >= (4 * k > 64 ? 4 * k : 64) && k <= 128; }  // (n <= 32768: 32-bit element offsets in topk.cu)
 // element (i, c) of a triangle-mode matrix is read at (c, i) when its own place was not stored
 __host__ __device__ inline bool tri_stored(int i, int c) { return (i >> 8) >= (c >> 8); }
 

@@ -326,16 +326,29 @@ topk_chunk_warp_kernel(const float* __restrict__ vals, int rows, int cols, int64
       }
     }
   }
-  uint32_t lo = 0, hi = 0xffffffffu;
-  while (lo < hi) {
-    const uint32_t mid = lo + ((hi - lo) >> 1);
-    int cnt = 0;
+  uint32_t t0;
+  if (PIPE && S == 2) {
+    // k <= 32 of 64 group minima: a register bitonic sort (21 exchange steps) instead of 32 bisection rounds of a warp
+    // reduction each -- the bisection was 17 % of this kernel's instructions; the k-th smallest key is the same number
+    uint32_t ms[S], none[S];
 #pragma unroll
-    for (int s = 0; s < S; ++s) cnt += m[s] <= mid;
-    cnt = __reduce_add_sync(0xffffffffu, cnt);
-    if (cnt >= kk) hi = mid; else lo = mid + 1;
+    for (int s = 0; s < S; ++s) { ms[s] = m[s]; none[s] = 0; }
+    warp_bitonic_sort<S, false>(ms, none, lane);
+    const int e = max(kk, 1) - 1;  // sorted element e lives in lane e / S, slot e % S
+    const uint32_t pick = (e % S) == 0 ? ms[0] : ms[S - 1];
+    t0 = __shfl_sync(0xffffffffu, pick, e / S);
+  } else {
+    uint32_t lo = 0, hi = 0xffffffffu;
+    while (lo < hi) {
+      const uint32_t mid = lo + ((hi - lo) >> 1);
+      int cnt = 0;
+#pragma unroll
+      for (int s = 0; s < S; ++s) cnt += m[s] <= mid;
+      cnt = __reduce_add_sync(0xffffffffu, cnt);
+      if (cnt >= kk) hi = mid; else lo = mid + 1;
+    }
+    t0 = lo;
   }
-  const uint32_t t0 = lo;
 
   int count = 0;
   uint32_t* mk = ckey[warp];
@@ -349,10 +362,19 @@ topk_chunk_warp_kernel(const float* __restrict__ vals, int rows, int cols, int64
       uint32_t key8[8];
 #pragma unroll
       for (int u = 0; u < 8; ++u) {
-        const int ch = __shfl_sync(0xffffffffu, pending, (u0 + u) & 31);
-        const int col = ch * 32 + lane;
-        const float* src = (TRI && (ch >> 3) > rt) ? vals + (size_t)col * ldv + row : v + col;
-        key8[u] = (u0 + u < np && col < cols) ? sel_key(__ldg(src), descending) : 0xffffffffu;
+        key8[u] = 0xffffffffu;
+        if (u0 + u < np) {  // warp-uniform
+          const int ch = __shfl_sync(0xffffffffu, pending, (u0 + u) & 31);
+          const int col = ch * 32 + lane;
+          if (TRI) {
+            // square matrix of at most 32768 rows (tri_mode_ok): element offsets fit 32 bits
+            const bool up = (ch >> 3) > rt;
+            const uint32_t off = (uint32_t)(up ? col : row) * (uint32_t)ldv + (uint32_t)(up ? row : col);
+            if (col < cols) key8[u] = sel_key(__ldg(vals + off), descending);
+          } else {
+            if (col < cols) key8[u] = sel_key(__ldg(v + col), descending);
+          }
+        }
       }
 #pragma unroll
       for (int u = 0; u < 8; ++u) {
@@ -454,7 +476,7 @@ int topk_rows_launch(const float* vals, int rows, int cols, int64_t ldv, const i
     RB_CUDA(cudaFuncSetAttribute(topk_rows_kernel<1, 512>, cudaFuncAttributeMaxDynamicSharedMemorySize, TOPK_SMEM_ROW_MAX * 4));
   }
   const bool chunk_guided = chunk_red != nullptr && cand_i == nullptr && nchunks >= 4 * k && nchunks >= 64 && k <= 128;
-  RB_REQUIRE(!chunk_red2 || (chunk_guided && rows == cols && !descending),
+  RB_REQUIRE(!chunk_red2 || (chunk_guided && rows == cols && rows <= 32768 && !descending),
              "topk: a triangle-mode matrix needs the chunk-guided selection (square, ascending, n/32 >= max(64, 4k), k <= 128)");
   if (chunk_guided) {
     // groups = 32*S >= 2k lane-local minima (S = 2, 4 or 8)
