@@ -300,7 +300,8 @@ int reidb200_cosine_distance(const float* a, int na, int64_t lda, const float* b
  * (the merged set of image_reid_inference.py:270); the Q x G block of the lambda-blended Jaccard distance is reduced
  * to CMC f32[G] / mAP f64[1] by the CTA that produces each query row, so the re-ranked matrix is not re-read and, with
  * out_dist == NULL, never written.  G <= 16384 (wider galleries: reidb200_jaccard + reidb200_eval_cmc_map).
- * The N x N squared-L2 matrix inside the workspace is kept in TRIANGLE mode when N >= 2017 (every element stored once,
+ * The N x N squared-L2 matrix inside the workspace is kept in TRIANGLE mode when ceil(N / 32) >= max(64, 4 k1) and
+ * N <= 32768 (N >= 2529 for k1 = 20; above 32768 rows there is no matrix at all) (every element stored once,
  * the row select reads the other half from two words per 32-column chunk): same bits in every output
  * as with the full matrix, which the environment variable REIDB200_TRI=0 restores.
  * replaces reid/faiss_utils.py:149-244 followed by reid/evaluate.py:33-105 on the re-ranked distance. */
